@@ -1,0 +1,715 @@
+// bsdf.cuh -- material programs: bitmap/constant textures, microfacet distributions, the rough
+// transmittance LUT and the nine in-scope BSDF models as a flattened node tree.
+//
+// Design: polymorphic BSDF objects of the reference become an array of MtsBsdfNode; the three
+// wrappers (coating, blendbsdf, bumpmap) recurse through a depth-bounded template so that the
+// call graph is finite (no device-side recursion/stack), the six leaf models are evaluated by
+// one switch.  typeMask = EAll and component = -1 throughout, which is how MIPathTracer::Li
+// queries BSDFs (src/integrators/path/path.cpp:178-207).
+#pragma once
+#include "scene.cuh"
+
+namespace mts {
+
+constexpr int kMaxBsdfDepth = 4;  // wrapper nesting levels supported above a leaf
+
+// ---------------------------------------------------------------------------------------
+// Textures: TMIPMap level 0 (include/mitsuba/render/mipmap.h:503-626)
+// ---------------------------------------------------------------------------------------
+DEVFN bool wrapCoord(int &x, int size, int mode, float &constant) {
+    if (x < 0 || x >= size) {
+        switch (mode) {
+            case MTS_WRAP_REPEAT: x = modulo(x, size); break;
+            case MTS_WRAP_CLAMP: x = clampi(x, 0, size - 1); break;
+            case MTS_WRAP_MIRROR: x = modulo(x, 2 * size); if (x >= size) x = 2 * size - x - 1; break;
+            case MTS_WRAP_ZERO: constant = 0.0f; return false;
+            default: constant = 1.0f; return false;
+        }
+    }
+    return true;
+}
+DEVFN float3 texel(const DTexture &t, int x, int y) {
+    float c;
+    if (!wrapCoord(x, t.width, t.wrapU, c)) return f3(c);
+    if (!wrapCoord(y, t.height, t.wrapV, c)) return f3(c);
+    size_t i = (size_t)y * t.width + x;
+    if (t.channels == 1) return f3(__half2float(__ldg(t.texels + i)));
+    uint2 raw = __ldg(reinterpret_cast<const uint2 *>(t.texels) + i);
+    __half2 a = *reinterpret_cast<__half2 *>(&raw.x), b = *reinterpret_cast<__half2 *>(&raw.y);
+    float2 fa = __half22float2(a), fb = __half22float2(b);
+    return f3(fa.x, fa.y, fb.x);
+}
+// evalBilinear(0, uv) / evalBox(0, uv), mipmap.h:566-596
+DEVFN float3 texLookup(const DTexture &t, float2 uv) {
+    if (t.filter == MTS_FILTER_NEAREST)
+        return texel(t, floorToInt(uv.x * t.width), floorToInt(uv.y * t.height));
+    if (!isfinite(uv.x) || !isfinite(uv.y)) return f3(0.0f);
+    float u = uv.x * t.width - 0.5f, v = uv.y * t.height - 0.5f;
+    int xPos = floorToInt(u), yPos = floorToInt(v);
+    float dx1 = u - xPos, dx2 = 1.0f - dx1, dy1 = v - yPos, dy2 = 1.0f - dy1;
+    return texel(t, xPos, yPos) * dx2 * dy2 + texel(t, xPos, yPos + 1) * dx2 * dy1 +
+           texel(t, xPos + 1, yPos) * dx1 * dy2 + texel(t, xPos + 1, yPos + 1) * dx1 * dy1;
+}
+// evalGradientBilinear(0, uv), mipmap.h:601-626
+DEVFN void texGradient(const DTexture &t, float2 uv, float3 &g0, float3 &g1) {
+    if (t.filter == MTS_FILTER_NEAREST || !isfinite(uv.x) || !isfinite(uv.y)) { g0 = g1 = f3(0.0f); return; }
+    float u = uv.x * t.width - 0.5f, v = uv.y * t.height - 0.5f;
+    int xPos = floorToInt(u), yPos = floorToInt(v);
+    float dx = u - xPos, dy = v - yPos;
+    float3 p00 = texel(t, xPos, yPos), p10 = texel(t, xPos + 1, yPos);
+    float3 p01 = texel(t, xPos, yPos + 1), p11 = texel(t, xPos + 1, yPos + 1);
+    float3 tmp = p01 + p10 - p11;
+    g0 = (p10 + p00 * (dy - 1) - tmp * dy) * (float)t.width;
+    g1 = (p01 + p00 * (dx - 1) - tmp * dx) * (float)t.height;
+}
+// Texture2D::eval (src/librender/texture.cpp:104-114) + ScalingTexture (src/textures/scale.cpp:86-88)
+DEVFN float3 evalTex(const DScene &S, const MtsTexRef &r, float2 uv) {
+    float3 s = f3(r.scale[0], r.scale[1], r.scale[2]);
+    if (r.tex < 0) return s;
+    const DTexture &t = S.textures[r.tex];
+    return texLookup(t, make_float2(uv.x * t.uvScale.x + t.uvOffset.x, uv.y * t.uvScale.y + t.uvOffset.y)) * s;
+}
+// Texture2D::evalGradient (texture.cpp:116-124) + ScalingTexture::evalGradient (scale.cpp:90-94)
+DEVFN void evalTexGradient(const DScene &S, const MtsTexRef &r, float2 uv, float3 &g0, float3 &g1) {
+    if (r.tex < 0) { g0 = g1 = f3(0.0f); return; }
+    const DTexture &t = S.textures[r.tex];
+    texGradient(t, make_float2(uv.x * t.uvScale.x + t.uvOffset.x, uv.y * t.uvScale.y + t.uvOffset.y), g0, g1);
+    float3 s = f3(r.scale[0], r.scale[1], r.scale[2]);
+    g0 = g0 * t.uvScale.x * s;
+    g1 = g1 * t.uvScale.y * s;
+}
+
+// ---------------------------------------------------------------------------------------
+// MicrofacetDistribution (src/bsdfs/microfacet.h), Beckmann + GGX
+// ---------------------------------------------------------------------------------------
+struct Microfacet {
+    bool ggx, sampleVisible;
+    float alphaU, alphaV;
+    DEVFN Microfacet(bool g, float au, float av, bool sv) : ggx(g), sampleVisible(sv) {
+        alphaU = fmaxf(au, 1e-4f); alphaV = fmaxf(av, 1e-4f);  // :70-71
+    }
+    DEVFN bool isIsotropic() const { return alphaU == alphaV; }
+    // :191-234
+    DEVFN float eval(float3 m) const {
+        if (cosTheta(m) <= 0) return 0.0f;
+        float ct2 = cosTheta2(m);
+        float be = ((m.x * m.x) / (alphaU * alphaU) + (m.y * m.y) / (alphaV * alphaV)) / ct2;
+        float result;
+        if (!ggx) result = fastexp(-be) / (kPi * alphaU * alphaV * ct2 * ct2);
+        else { float root = (1.0f + be) * ct2; result = 1.0f / (kPi * alphaU * alphaV * root * root); }
+        if (result * cosTheta(m) < 1e-20f) result = 0;
+        return result;
+    }
+    // :541-551
+    DEVFN float projectRoughness(float3 v) const {
+        float invSinTheta2 = 1 / sinTheta2(v);
+        if (isIsotropic() || invSinTheta2 <= 0) return alphaU;
+        float cosPhi2 = v.x * v.x * invSinTheta2, sinPhi2 = v.y * v.y * invSinTheta2;
+        return sqrtf(cosPhi2 * alphaU * alphaU + sinPhi2 * alphaV * alphaV);
+    }
+    // :477-514
+    DEVFN float smithG1(float3 v, float3 m) const {
+        if (dot(v, m) * cosTheta(v) <= 0) return 0.0f;
+        float tt = fabsf(tanTheta(v));
+        if (tt == 0.0f) return 1.0f;
+        float alpha = projectRoughness(v);
+        if (!ggx) {
+            float a = 1.0f / (alpha * tt);
+            if (a >= 1.6f) return 1.0f;
+            float aSqr = a * a;
+            return (3.535f * a + 2.181f * aSqr) / (1.0f + 2.276f * a + 2.577f * aSqr);
+        }
+        float root = alpha * tt;
+        return 2.0f / (1.0f + hypot2(1.0f, root));
+    }
+    DEVFN float G(float3 wi, float3 wo, float3 m) const { return smithG1(wi, m) * smithG1(wo, m); }
+    DEVFN float pdfAll(float3 m) const { return eval(m) * cosTheta(m); }  // :404-407
+    DEVFN float pdfVisible(float3 wi, float3 m) const {                    // :462-466
+        if (cosTheta(wi) == 0) return 0.0f;
+        return smithG1(wi, m) * absDot(wi, m) * eval(m) / fabsf(cosTheta(wi));
+    }
+    DEVFN float pdf(float3 wi, float3 m) const { return sampleVisible ? pdfVisible(wi, m) : pdfAll(m); }
+    // :287-395
+    DEVFN float3 sampleAll(float2 sample, float &pdf) const {
+        float cosThetaM, sinPhiM, cosPhiM, alphaSqr;
+        if (isIsotropic()) {
+            sincosf((2.0f * kPi) * sample.y, &sinPhiM, &cosPhiM);
+            alphaSqr = alphaU * alphaU;
+        } else {
+            float phiM = atanf(alphaV / alphaU * tanf(kPi + 2 * kPi * sample.y)) + kPi * floorf(2 * sample.y + 0.5f);
+            sincosf(phiM, &sinPhiM, &cosPhiM);
+            float cosSc = cosPhiM / alphaU, sinSc = sinPhiM / alphaV;
+            alphaSqr = 1.0f / (cosSc * cosSc + sinSc * sinSc);
+        }
+        if (!ggx) {
+            float tanThetaMSqr = alphaSqr * -fastlog(1.0f - sample.x);
+            cosThetaM = 1.0f / sqrtf(1.0f + tanThetaMSqr);
+            pdf = (1.0f - sample.x) / (kPi * alphaU * alphaV * cosThetaM * cosThetaM * cosThetaM);
+        } else {
+            float tanThetaMSqr = alphaSqr * sample.x / (1.0f - sample.x);
+            cosThetaM = 1.0f / sqrtf(1.0f + tanThetaMSqr);
+            float temp = 1 + tanThetaMSqr / alphaSqr;
+            pdf = kInvPi / (alphaU * alphaV * cosThetaM * cosThetaM * cosThetaM * temp * temp);
+        }
+        if (pdf < 1e-20f) pdf = 0;
+        float sinThetaM = sqrtf(fmaxf(0.0f, 1 - cosThetaM * cosThetaM));
+        return f3(sinThetaM * cosPhiM, sinThetaM * sinPhiM, cosThetaM);
+    }
+    // :573-697
+    DEVFN float2 sampleVisible11(float thetaI, float2 sample) const {
+        const float SQRT_PI_INV = 0.56418958354775628f;
+        float2 slope;
+        if (!ggx) {
+            if (thetaI < 1e-4f) {
+                float sp, cp;
+                float r = sqrtf(-fastlog(1.0f - sample.x));
+                sincosf(2 * kPi * sample.y, &sp, &cp);
+                return make_float2(r * cp, r * sp);
+            }
+            float tanThetaI = tanf(thetaI), cotThetaI = 1 / tanThetaI;
+            float a = -1, c = erf_as(cotThetaI);
+            float sample_x = fmaxf(sample.x, 1e-6f);
+            float fit = 1 + thetaI * (-0.876f + thetaI * (0.4265f - 0.0594f * thetaI));
+            float b = c - (1 + c) * powf(1 - sample_x, fit);
+            float normalization = 1 / (1 + c + SQRT_PI_INV * tanThetaI * expf(-cotThetaI * cotThetaI));
+            int it = 0;
+            while (++it < 10) {
+                if (!(b >= a && b <= c)) b = 0.5f * (a + c);
+                float invErf = erfinv_giles(b);
+                float value = normalization * (1 + b + SQRT_PI_INV * tanThetaI * expf(-invErf * invErf)) - sample_x;
+                float derivative = normalization * (1 - invErf * tanThetaI);
+                if (fabsf(value) < 1e-5f) break;
+                if (value > 0) c = b; else a = b;
+                b -= value / derivative;
+            }
+            slope.x = erfinv_giles(b);
+            slope.y = erfinv_giles(2.0f * fmaxf(sample.y, 1e-6f) - 1.0f);
+        } else {
+            if (thetaI < 1e-4f) {
+                float sp, cp;
+                float r = safe_sqrt(sample.x / (1 - sample.x));
+                sincosf(2 * kPi * sample.y, &sp, &cp);
+                return make_float2(r * cp, r * sp);
+            }
+            float tanThetaI = tanf(thetaI);
+            float a = 1 / tanThetaI;
+            float G1 = 2.0f / (1.0f + safe_sqrt(1.0f + 1.0f / (a * a)));
+            float A = 2.0f * sample.x / G1 - 1.0f;
+            if (fabsf(A) == 1) A -= signum(A) * kEps;
+            float tmp = 1.0f / (A * A - 1.0f);
+            float B = tanThetaI;
+            float D = safe_sqrt(B * B * tmp * tmp - (A * A - B * B) * tmp);
+            float slope_x_1 = B * tmp - D, slope_x_2 = B * tmp + D;
+            slope.x = (A < 0.0f || slope_x_2 > 1.0f / tanThetaI) ? slope_x_1 : slope_x_2;
+            float Sg;
+            if (sample.y > 0.5f) { Sg = 1.0f; sample.y = 2.0f * (sample.y - 0.5f); }
+            else { Sg = -1.0f; sample.y = 2.0f * (0.5f - sample.y); }
+            float z = (sample.y * (sample.y * (sample.y * (-0.365728915865723f) + 0.790235037209296f) - 0.424965825137544f) + 0.000152998850436920f) /
+                      (sample.y * (sample.y * (sample.y * (sample.y * 0.169507819808272f - 0.397203533833404f) - 0.232500544458471f) + 1.0f) - 0.539825872510702f);
+            slope.y = Sg * z * sqrtf(1.0f + slope.x * slope.x);
+        }
+        return slope;
+    }
+    // :421-459
+    DEVFN float3 sampleVisibleNormal(float3 _wi, float2 sample) const {
+        float3 wi = normalize(f3(alphaU * _wi.x, alphaV * _wi.y, _wi.z));
+        float theta = 0, phi = 0;
+        if (wi.z < 0.99999f) { theta = acosf(wi.z); phi = atan2f(wi.y, wi.x); }
+        float sp, cp; sincosf(phi, &sp, &cp);
+        float2 slope = sampleVisible11(theta, sample);
+        slope = make_float2(cp * slope.x - sp * slope.y, sp * slope.x + cp * slope.y);
+        slope.x *= alphaU; slope.y *= alphaV;
+        float normalization = 1.0f / sqrtf(slope.x * slope.x + slope.y * slope.y + 1.0f);
+        return f3(-slope.x * normalization, -slope.y * normalization, normalization);
+    }
+    // :243-256
+    DEVFN float3 sample(float3 wi, float2 s, float &pdf) const {
+        if (sampleVisible) { float3 m = sampleVisibleNormal(wi, s); pdf = pdfVisible(wi, m); return m; }
+        return sampleAll(s, pdf);
+    }
+};
+
+// ---------------------------------------------------------------------------------------
+// evalCubicInterp1D / 2D (src/libcore/spline.cpp:23-58, 236-297) on [0,1]
+// ---------------------------------------------------------------------------------------
+DEVFN float cubicInterp1D(float x, const float *values, int size) {
+    if (!(x >= 0.0f && x <= 1.0f)) return 0.0f;
+    float t = x * (size - 1);
+    int k = max(0, min((int)t, size - 2));
+    float f0 = __ldg(values + k), f1 = __ldg(values + k + 1), d0, d1;
+    if (k > 0) d0 = 0.5f * (f1 - __ldg(values + k - 1)); else d0 = f1 - f0;
+    if (k + 2 < size) d1 = 0.5f * (__ldg(values + k + 2) - f0); else d1 = f1 - f0;
+    t = t - (float)k;
+    float t2 = t * t, t3 = t2 * t;
+    return (2 * t3 - 3 * t2 + 1) * f0 + (-2 * t3 + 3 * t2) * f1 + (t3 - 2 * t2 + t) * d0 + (t3 - t2) * d1;
+}
+DEVFN void cubicWeights(float p, int size, int &knot, float w[4]) {
+    float t = p * (size - 1);
+    knot = min((int)t, size - 2);
+    t = t - (float)knot;
+    float t2 = t * t, t3 = t2 * t;
+    w[0] = 0.0f; w[1] = 2 * t3 - 3 * t2 + 1; w[2] = -2 * t3 + 3 * t2; w[3] = 0.0f;
+    float d0 = t3 - 2 * t2 + t, d1 = t3 - t2;
+    if (knot > 0) { w[2] += 0.5f * d0; w[0] -= 0.5f * d0; } else { w[2] += d0; w[1] -= d0; }
+    if (knot + 2 < size) { w[3] += 0.5f * d1; w[1] -= 0.5f * d1; } else { w[2] += d1; w[1] -= d1; }
+}
+DEVFN float cubicInterp2D(float px, float py, const float *values, int sx, int sy) {
+    if (!(px >= 0.0f && px <= 1.0f) || !(py >= 0.0f && py <= 1.0f)) return 0.0f;
+    float wx[4], wy[4]; int kx, ky;
+    cubicWeights(px, sx, kx, wx);
+    cubicWeights(py, sy, ky, wy);
+    float result = 0.0f;
+#pragma unroll
+    for (int y = -1; y <= 2; ++y) {
+#pragma unroll
+        for (int x = -1; x <= 2; ++x) {
+            float wxy = wx[x + 1] * wy[y + 1];
+            if (wxy == 0) continue;
+            result += __ldg(values + (ky + y) * sx + kx + x) * wxy;
+        }
+    }
+    return result;
+}
+// RoughTransmittance::eval on the host-reduced slices (src/bsdfs/rtrans.h:183-233)
+DEVFN float roughTransmittance(const DScene &S, const MtsBsdfNode &n, float ct, float alpha) {
+    if (!(ct >= 0)) return 0.f;
+    float warpedCosTheta = powf(fabsf(ct), 0.25f), result;
+    const float *tab = S.pool + n.lut[0];
+    if (!(n.flags & MTS_BF_RT_2D)) result = cubicInterp1D(warpedCosTheta, tab, n.lut[1]);
+    else {
+        float warpedAlpha = powf((alpha - n.f[0]) / (n.f[1] - n.f[0]), 0.25f);
+        result = cubicInterp2D(warpedCosTheta, warpedAlpha, tab, n.lut[1], n.lut[2]);
+    }
+    return fminf(1.0f, fmaxf(0.0f, result));
+}
+// 1 - m_internalRoughTransmittance->evalDiffuse(alpha)  (roughplastic.cpp:366, rtrans.h:249-285)
+DEVFN float roughInternalFdr(const DScene &S, const MtsBsdfNode &n, float alpha) {
+    if (!(n.flags & MTS_BF_RT_2D)) return n.f[3];
+    float warpedAlpha = powf((alpha - n.f[0]) / (n.f[1] - n.f[0]), 0.25f);
+    float r = cubicInterp1D(warpedAlpha, S.pool + n.lut[3], n.lut[2]);
+    return 1.0f - fminf(1.0f, fmaxf(0.0f, r));
+}
+
+DEVFN float3 reflectZ(float3 wi) { return f3(-wi.x, -wi.y, wi.z); }
+DEVFN float3 reflectM(float3 wi, float3 m) { return 2 * dot(wi, m) * m - wi; }
+// BSDF::getMeasure (include/mitsuba/render/bsdf.h)
+DEVFN int measureOf(uint32_t sampledType) { return (sampledType & MTS_ESMOOTH) ? MTS_MEASURE_SOLID_ANGLE : MTS_MEASURE_DISCRETE; }
+DEVFN float3 nodeEta(const MtsBsdfNode &n) { return f3(n.eta[0], n.eta[1], n.eta[2]); }
+DEVFN float3 nodeK(const MtsBsdfNode &n) { return f3(n.k[0], n.k[1], n.k[2]); }
+
+struct BSample { float3 wo; float pdf; float eta; uint32_t type; };
+
+// ---------------------------------------------------------------------------------------
+// leaf models
+// ---------------------------------------------------------------------------------------
+__device__ __noinline__ float3 leafEval(const DScene &S, const MtsBsdfNode &n, float2 uv, float3 wi, float3 wo, int measure) {
+    const bool solid = measure == MTS_MEASURE_SOLID_ANGLE, discrete = measure == MTS_MEASURE_DISCRETE;
+    switch (n.type) {
+    case MTS_BSDF_DIFFUSE:  // src/bsdfs/diffuse.cpp:110-118
+        if (!solid || cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return f3(0.0f);
+        return evalTex(S, n.t0, uv) * (kInvPi * cosTheta(wo));
+    case MTS_BSDF_CONDUCTOR:  // conductor.cpp:223-237
+        if (!discrete || cosTheta(wi) <= 0 || cosTheta(wo) <= 0 || fabsf(dot(reflectZ(wi), wo) - 1) > kDeltaEps) return f3(0.0f);
+        return evalTex(S, n.t0, uv) * fresnelConductorExact(cosTheta(wi), nodeEta(n), nodeK(n));
+    case MTS_BSDF_ROUGHCONDUCTOR: {  // roughconductor.cpp:257-294
+        if (!solid || cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return f3(0.0f);
+        float3 H = normalize(wo + wi);
+        Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+        const float D = distr.eval(H);
+        if (D == 0) return f3(0.0f);
+        const float3 F = fresnelConductorExact(dot(wi, H), nodeEta(n), nodeK(n)) * evalTex(S, n.t0, uv);
+        const float G = distr.G(wi, wo, H);
+        float model = D * G / (4.0f * cosTheta(wi));
+        return F * model;
+    }
+    case MTS_BSDF_PLASTIC: {  // plastic.cpp:245-278
+        if (cosTheta(wo) <= 0 || cosTheta(wi) <= 0) return f3(0.0f);
+        float eta = n.eta[0];
+        float Fi = fresnelDielectricExt(cosTheta(wi), eta);
+        if (discrete) {
+            if (fabsf(dot(reflectZ(wi), wo) - 1) < kDeltaEps) return evalTex(S, n.t1, uv) * Fi;
+        } else if (solid) {
+            float Fo = fresnelDielectricExt(cosTheta(wo), eta);
+            float3 diff = evalTex(S, n.t0, uv);
+            if (n.flags & MTS_BF_NONLINEAR) diff = diff / (f3(1.0f) - diff * n.f[0]); else diff = diff / (1 - n.f[0]);
+            float invEta2 = 1 / (eta * eta);
+            return diff * (squareToCosineHemispherePdf(wo) * invEta2 * (1 - Fi) * (1 - Fo));
+        }
+        return f3(0.0f);
+    }
+    case MTS_BSDF_ROUGHPLASTIC: {  // roughplastic.cpp:326-382
+        if (!solid || cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return f3(0.0f);
+        float eta = n.eta[0];
+        float a = average(evalTex(S, n.t2, uv));
+        Microfacet distr(n.flags & MTS_BF_GGX, a, a, n.flags & MTS_BF_SAMPLE_VISIBLE);
+        float3 result = f3(0.0f);
+        {
+            const float3 H = normalize(wo + wi);
+            const float D = distr.eval(H);
+            const float F = fresnelDielectricExt(dot(wi, H), eta);
+            const float G = distr.G(wi, wo, H);
+            float value = F * D * G / (4.0f * cosTheta(wi));
+            result += evalTex(S, n.t1, uv) * value;
+        }
+        {
+            float3 diff = evalTex(S, n.t0, uv);
+            float T12 = roughTransmittance(S, n, cosTheta(wi), distr.alphaU);
+            float T21 = roughTransmittance(S, n, cosTheta(wo), distr.alphaU);
+            float Fdr = roughInternalFdr(S, n, distr.alphaU);
+            if (n.flags & MTS_BF_NONLINEAR) diff = diff / (f3(1.0f) - diff * Fdr); else diff = diff / (1 - Fdr);
+            float invEta2 = 1.0f / (eta * eta);
+            result += diff * (kInvPi * cosTheta(wo) * T12 * T21 * invEta2);
+        }
+        return result;
+    }
+    case MTS_BSDF_DIELECTRIC: {  // dielectric.cpp:228-253
+        float eta = n.eta[0], invEta = 1 / eta;
+        float cosThetaT;
+        float F = fresnelDielectricExt(cosTheta(wi), cosThetaT, eta);
+        if (cosTheta(wi) * cosTheta(wo) >= 0) {
+            if (!discrete || fabsf(dot(reflectZ(wi), wo) - 1) > kDeltaEps) return f3(0.0f);
+            return evalTex(S, n.t0, uv) * F;
+        } else {
+            float scale = -(cosThetaT < 0 ? invEta : eta);
+            float3 refr = f3(scale * wi.x, scale * wi.y, cosThetaT);
+            if (!discrete || fabsf(dot(refr, wo) - 1) > kDeltaEps) return f3(0.0f);
+            float factor = cosThetaT < 0 ? invEta : eta;  // ERadiance
+            return evalTex(S, n.t1, uv) * factor * factor * (1 - F);
+        }
+    }
+    }
+    return f3(0.0f);
+}
+
+__device__ __noinline__ float leafPdf(const DScene &S, const MtsBsdfNode &n, float2 uv, float3 wi, float3 wo, int measure) {
+    const bool solid = measure == MTS_MEASURE_SOLID_ANGLE, discrete = measure == MTS_MEASURE_DISCRETE;
+    switch (n.type) {
+    case MTS_BSDF_DIFFUSE:  // diffuse.cpp:120-127
+        if (!solid || cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return 0.0f;
+        return squareToCosineHemispherePdf(wo);
+    case MTS_BSDF_CONDUCTOR:  // conductor.cpp:239-252
+        if (!discrete || cosTheta(wi) <= 0 || cosTheta(wo) <= 0 || fabsf(dot(reflectZ(wi), wo) - 1) > kDeltaEps) return 0.0f;
+        return 1.0f;
+    case MTS_BSDF_ROUGHCONDUCTOR: {  // roughconductor.cpp:296-321
+        if (!solid || cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return 0.0f;
+        float3 H = normalize(wo + wi);
+        Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+        if (distr.sampleVisible) return distr.eval(H) * distr.smithG1(wi, H) / (4.0f * cosTheta(wi));
+        return distr.pdf(wi, H) / (4 * absDot(wo, H));
+    }
+    case MTS_BSDF_PLASTIC: {  // plastic.cpp:280-307
+        if (cosTheta(wo) <= 0 || cosTheta(wi) <= 0) return 0.0f;
+        float Fi = fresnelDielectricExt(cosTheta(wi), n.eta[0]);
+        float w = n.f[2];
+        float probSpecular = (Fi * w) / (Fi * w + (1 - Fi) * (1 - w));
+        if (discrete) {
+            if (fabsf(dot(reflectZ(wi), wo) - 1) < kDeltaEps) return probSpecular;
+        } else if (solid) return squareToCosineHemispherePdf(wo) * (1 - probSpecular);
+        return 0.0f;
+    }
+    case MTS_BSDF_ROUGHPLASTIC: {  // roughplastic.cpp:384-437
+        if (!solid || cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return 0.0f;
+        float a = average(evalTex(S, n.t2, uv));
+        Microfacet distr(n.flags & MTS_BF_GGX, a, a, n.flags & MTS_BF_SAMPLE_VISIBLE);
+        const float3 H = normalize(wo + wi);
+        float w = n.f[2];
+        float probSpecular = 1 - roughTransmittance(S, n, cosTheta(wi), distr.alphaU);
+        probSpecular = (probSpecular * w) / (probSpecular * w + (1 - probSpecular) * (1 - w));
+        float probDiffuse = 1 - probSpecular;
+        const float dwh_dwo = 1.0f / (4.0f * dot(wo, H));
+        const float prob = distr.pdf(wi, H);
+        float result = prob * dwh_dwo * probSpecular;
+        result += probDiffuse * squareToCosineHemispherePdf(wo);
+        return result;
+    }
+    case MTS_BSDF_DIELECTRIC: {  // dielectric.cpp:255-275
+        float eta = n.eta[0], invEta = 1 / eta;
+        float cosThetaT;
+        float F = fresnelDielectricExt(cosTheta(wi), cosThetaT, eta);
+        if (cosTheta(wi) * cosTheta(wo) >= 0) {
+            if (!discrete || fabsf(dot(reflectZ(wi), wo) - 1) > kDeltaEps) return 0.0f;
+            return F;
+        } else {
+            float scale = -(cosThetaT < 0 ? invEta : eta);
+            float3 refr = f3(scale * wi.x, scale * wi.y, cosThetaT);
+            if (!discrete || fabsf(dot(refr, wo) - 1) > kDeltaEps) return 0.0f;
+            return 1 - F;
+        }
+    }
+    }
+    return 0.0f;
+}
+
+__device__ __noinline__ float3 leafSample(const DScene &S, const MtsBsdfNode &n, float2 uv, float3 wi, float2 sample, BSample &o) {
+    switch (n.type) {
+    case MTS_BSDF_DIFFUSE:  // diffuse.cpp:141-150
+        if (cosTheta(wi) <= 0) return f3(0.0f);
+        o.wo = squareToCosineHemisphere(sample);
+        o.eta = 1.0f; o.type = MTS_EDIFFUSE_REFLECTION;
+        o.pdf = squareToCosineHemispherePdf(o.wo);
+        return evalTex(S, n.t0, uv);
+    case MTS_BSDF_CONDUCTOR:  // conductor.cpp:270-286
+        if (cosTheta(wi) <= 0) return f3(0.0f);
+        o.type = MTS_EDELTA_REFLECTION; o.wo = reflectZ(wi); o.eta = 1.0f; o.pdf = 1;
+        return evalTex(S, n.t0, uv) * fresnelConductorExact(cosTheta(wi), nodeEta(n), nodeK(n));
+    case MTS_BSDF_ROUGHCONDUCTOR: {  // roughconductor.cpp:368-410
+        if (cosTheta(wi) < 0) return f3(0.0f);
+        Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+        float pdf;
+        float3 m = distr.sample(wi, sample, pdf);
+        o.pdf = pdf;
+        if (pdf == 0) return f3(0.0f);
+        o.wo = reflectM(wi, m); o.eta = 1.0f; o.type = MTS_EGLOSSY_REFLECTION;
+        if (cosTheta(o.wo) <= 0) return f3(0.0f);
+        float3 F = fresnelConductorExact(dot(wi, m), nodeEta(n), nodeK(n)) * evalTex(S, n.t0, uv);
+        float weight;
+        if (distr.sampleVisible) weight = distr.smithG1(o.wo, m);
+        else weight = distr.eval(m) * distr.G(wi, o.wo, m) * dot(wi, m) / (pdf * cosTheta(wi));
+        o.pdf = pdf / (4.0f * dot(o.wo, m));
+        return F * weight;
+    }
+    case MTS_BSDF_PLASTIC: {  // plastic.cpp:373-430
+        if (cosTheta(wi) <= 0) return f3(0.0f);
+        float eta = n.eta[0];
+        float Fi = fresnelDielectricExt(cosTheta(wi), eta);
+        o.eta = 1.0f;
+        float w = n.f[2];
+        float probSpecular = (Fi * w) / (Fi * w + (1 - Fi) * (1 - w));
+        if (sample.x < probSpecular) {
+            o.type = MTS_EDELTA_REFLECTION; o.wo = reflectZ(wi); o.pdf = probSpecular;
+            return evalTex(S, n.t1, uv) * Fi / probSpecular;
+        }
+        o.type = MTS_EDIFFUSE_REFLECTION;
+        o.wo = squareToCosineHemisphere(make_float2((sample.x - probSpecular) / (1 - probSpecular), sample.y));
+        float Fo = fresnelDielectricExt(cosTheta(o.wo), eta);
+        float3 diff = evalTex(S, n.t0, uv);
+        if (n.flags & MTS_BF_NONLINEAR) diff = diff / (f3(1.0f) - diff * n.f[0]); else diff = diff / (1 - n.f[0]);
+        o.pdf = (1 - probSpecular) * squareToCosineHemispherePdf(o.wo);
+        float invEta2 = 1 / (eta * eta);
+        return diff * (invEta2 * (1 - Fi) * (1 - Fo) / (1 - probSpecular));
+    }
+    case MTS_BSDF_ROUGHPLASTIC: {  // roughplastic.cpp:439-501
+        if (cosTheta(wi) <= 0) return f3(0.0f);
+        bool choseSpecular = true;
+        float a = average(evalTex(S, n.t2, uv));
+        Microfacet distr(n.flags & MTS_BF_GGX, a, a, n.flags & MTS_BF_SAMPLE_VISIBLE);
+        float w = n.f[2];
+        float probSpecular = 1 - roughTransmittance(S, n, cosTheta(wi), distr.alphaU);
+        probSpecular = (probSpecular * w) / (probSpecular * w + (1 - probSpecular) * (1 - w));
+        if (sample.y < probSpecular) sample.y /= probSpecular;
+        else { sample.y = (sample.y - probSpecular) / (1 - probSpecular); choseSpecular = false; }
+        if (choseSpecular) {
+            float dummy;
+            float3 m = distr.sampleVisible ? distr.sampleVisibleNormal(wi, sample) : distr.sampleAll(sample, dummy);
+            o.wo = reflectM(wi, m); o.type = MTS_EGLOSSY_REFLECTION;
+            if (cosTheta(o.wo) <= 0) return f3(0.0f);
+        } else {
+            o.type = MTS_EDIFFUSE_REFLECTION;
+            o.wo = squareToCosineHemisphere(sample);
+        }
+        o.eta = 1.0f;
+        o.pdf = leafPdf(S, n, uv, wi, o.wo, MTS_MEASURE_SOLID_ANGLE);
+        if (o.pdf == 0) return f3(0.0f);
+        return leafEval(S, n, uv, wi, o.wo, MTS_MEASURE_SOLID_ANGLE) / o.pdf;
+    }
+    case MTS_BSDF_DIELECTRIC: {  // dielectric.cpp:277-299
+        float eta = n.eta[0], invEta = 1 / eta;
+        float cosThetaT;
+        float F = fresnelDielectricExt(cosTheta(wi), cosThetaT, eta);
+        if (sample.x <= F) {
+            o.type = MTS_EDELTA_REFLECTION; o.wo = reflectZ(wi); o.eta = 1.0f; o.pdf = F;
+            return evalTex(S, n.t0, uv);
+        }
+        o.type = MTS_EDELTA_TRANSMISSION;
+        float scale = -(cosThetaT < 0 ? invEta : eta);
+        o.wo = f3(scale * wi.x, scale * wi.y, cosThetaT);
+        o.eta = cosThetaT < 0 ? eta : invEta;
+        o.pdf = 1 - F;
+        float factor = cosThetaT < 0 ? invEta : eta;
+        return evalTex(S, n.t1, uv) * (factor * factor);
+    }
+    }
+    return f3(0.0f);
+}
+
+// ---------------------------------------------------------------------------------------
+// wrappers
+// ---------------------------------------------------------------------------------------
+// Surface context the wrappers need (bumpmap perturbs the frame; textures only need uv).
+struct Surf {
+    float2 uv;
+    float3 dpdu, dpdv, geoN;
+    Frame sh;
+};
+
+// BumpMap::getFrame (src/bsdfs/bumpmap.cpp:135-159)
+DEVFN Frame bumpFrame(const DScene &S, const MtsBsdfNode &n, const Surf &su) {
+    float3 g0, g1;
+    evalTexGradient(S, n.t0, su.uv, g0, g1);
+    float dDispDu = luminance(g0), dDispDv = luminance(g1);
+    float3 dpdu = su.dpdu + su.sh.n * (dDispDu - dot(su.sh.n, su.dpdu));
+    float3 dpdv = su.dpdv + su.sh.n * (dDispDv - dot(su.sh.n, su.dpdv));
+    Frame r;
+    r.n = normalize(cross(dpdu, dpdv));
+    r.s = normalize(dpdu - r.n * dot(r.n, dpdu));
+    r.t = cross(r.n, r.s);
+    if (dot(r.n, su.geoN) < 0) r.n = -r.n;
+    return r;
+}
+// SmoothCoating::refractIn / refractOut (src/bsdfs/coating.cpp:208-219)
+DEVFN float3 coatRefractIn(float eta, float3 wi, float &R) {
+    float cosThetaT, invEta = 1 / eta;
+    R = fresnelDielectricExt(fabsf(cosTheta(wi)), cosThetaT, eta);
+    return f3(invEta * wi.x, invEta * wi.y, -signum(cosTheta(wi)) * cosThetaT);
+}
+DEVFN float3 coatRefractOut(float eta, float3 wi, float &R) {
+    float cosThetaT, invEta = 1 / eta;
+    R = fresnelDielectricExt(fabsf(cosTheta(wi)), cosThetaT, invEta);
+    return f3(eta * wi.x, eta * wi.y, -signum(cosTheta(wi)) * cosThetaT);
+}
+
+template <int D> struct Bsdf {
+    typedef Bsdf<D + 1> Next;
+
+    static __device__ __noinline__ float3 eval(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
+        const MtsBsdfNode &n = S.nodes[node];
+        switch (n.type) {
+        case MTS_BSDF_COATING: {  // coating.cpp:221-258
+            float eta = n.eta[0], invEta = 1 / eta;
+            if (measure == MTS_MEASURE_DISCRETE && fabsf(dot(reflectZ(wi), wo) - 1) < kDeltaEps)
+                return evalTex(S, n.t1, su.uv) * fresnelDielectricExt(fabsf(cosTheta(wi)), eta);
+            float R12, R21;
+            float3 wiP = coatRefractIn(eta, wi, R12), woP = coatRefractIn(eta, wo, R21);
+            if (R12 == 1 || R21 == 1) return f3(0.0f);
+            float3 result = Next::eval(S, n.child[0], su, wiP, woP, measure) * (1 - R12) * (1 - R21);
+            float3 sigmaA = evalTex(S, n.t0, su.uv) * n.f[0];
+            if (!isZero(sigmaA)) result *= vexp(-sigmaA * (1 / fabsf(cosTheta(wiP)) + 1 / fabsf(cosTheta(woP))));
+            if (measure == MTS_MEASURE_SOLID_ANGLE) result *= invEta * invEta * cosTheta(wo) / cosTheta(woP);
+            return result;
+        }
+        case MTS_BSDF_BLEND: {  // blendbsdf.cpp:135-152
+            float weight = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.uv))));
+            return Next::eval(S, n.child[0], su, wi, wo, measure) * (1 - weight) + Next::eval(S, n.child[1], su, wi, wo, measure) * weight;
+        }
+        case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:161-177
+            Surf pert = su;
+            pert.sh = bumpFrame(S, n, su);
+            float3 wiP = pert.sh.toLocal(su.sh.toWorld(wi)), woP = pert.sh.toLocal(su.sh.toWorld(wo));
+            if (cosTheta(wo) * cosTheta(woP) <= 0) return f3(0.0f);
+            return Next::eval(S, n.child[0], pert, wiP, woP, measure);
+        }
+        default: return leafEval(S, n, su.uv, wi, wo, measure);
+        }
+    }
+
+    static __device__ __noinline__ float pdf(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
+        const MtsBsdfNode &n = S.nodes[node];
+        switch (n.type) {
+        case MTS_BSDF_COATING: {  // coating.cpp:260-296
+            float eta = n.eta[0], invEta = 1 / eta;
+            float R12;
+            float3 wiP = coatRefractIn(eta, wi, R12);
+            float w = n.f[2];
+            float probSpecular = (R12 * w) / (R12 * w + (1 - R12) * (1 - w));
+            if (measure == MTS_MEASURE_DISCRETE && fabsf(dot(reflectZ(wi), wo) - 1) < kDeltaEps) return probSpecular;
+            float R21;
+            float3 woP = coatRefractIn(eta, wo, R21);
+            if (R12 == 1 || R21 == 1) return 0.0f;
+            float p = Next::pdf(S, n.child[0], su, wiP, woP, measure);
+            if (measure == MTS_MEASURE_SOLID_ANGLE) p *= invEta * invEta * cosTheta(wo) / cosTheta(woP);
+            return p * (1 - probSpecular);
+        }
+        case MTS_BSDF_BLEND: {  // blendbsdf.cpp:154-173
+            float weight = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.uv))));
+            return Next::pdf(S, n.child[0], su, wi, wo, measure) * (1 - weight) + Next::pdf(S, n.child[1], su, wi, wo, measure) * weight;
+        }
+        case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:179-197
+            Surf pert = su;
+            pert.sh = bumpFrame(S, n, su);
+            float3 wiP = pert.sh.toLocal(su.sh.toWorld(wi)), woP = pert.sh.toLocal(su.sh.toWorld(wo));
+            if (cosTheta(wo) * cosTheta(woP) <= 0) return 0;
+            return Next::pdf(S, n.child[0], pert, wiP, woP, measure);
+        }
+        default: return leafPdf(S, n, su.uv, wi, wo, measure);
+        }
+    }
+
+    static __device__ __noinline__ float3 sample(const DScene &S, int node, const Surf &su, float3 wi, float2 sample, BSample &o) {
+        const MtsBsdfNode &n = S.nodes[node];
+        switch (n.type) {
+        case MTS_BSDF_COATING: {  // coating.cpp:298-371
+            float eta = n.eta[0], invEta = 1 / eta;
+            float R12;
+            float3 wiPrime = coatRefractIn(eta, wi, R12);
+            float w = n.f[2];
+            float probSpecular = (R12 * w) / (R12 * w + (1 - R12) * (1 - w));
+            bool choseSpecular = true;
+            if (sample.x < probSpecular) sample.x /= probSpecular;
+            else { sample.x = (sample.x - probSpecular) / (1 - probSpecular); choseSpecular = false; }
+            if (choseSpecular) {
+                o.type = MTS_EDELTA_REFLECTION; o.wo = reflectZ(wi); o.eta = 1.0f; o.pdf = probSpecular;
+                return evalTex(S, n.t1, su.uv) * (R12 / o.pdf);
+            }
+            if (R12 == 1.0f) return f3(0.0f);
+            float3 result = Next::sample(S, n.child[0], su, wiPrime, sample, o);
+            if (isZero(result)) return f3(0.0f);
+            float3 woPrime = o.wo;
+            float3 sigmaA = evalTex(S, n.t0, su.uv) * n.f[0];
+            if (!isZero(sigmaA)) result *= vexp(-sigmaA * (1 / fabsf(cosTheta(wiPrime)) + 1 / fabsf(cosTheta(woPrime))));
+            float R21;
+            o.wo = coatRefractOut(eta, woPrime, R21);
+            if (R21 == 1.0f) return f3(0.0f);
+            o.pdf *= 1.0f - probSpecular;
+            result = result / (1.0f - probSpecular);
+            result *= (1 - R12) * (1 - R21);
+            if (measureOf(o.type) == MTS_MEASURE_SOLID_ANGLE) o.pdf *= invEta * invEta * cosTheta(o.wo) / cosTheta(woPrime);
+            return result;
+        }
+        case MTS_BSDF_BLEND: {  // blendbsdf.cpp:223-262
+            float w1 = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.uv))));
+            float w0 = 1 - w1;
+            int entry;
+            if (sample.x < w0) { entry = 0; sample.x /= w0; } else { entry = 1; sample.x = (sample.x - w0) / w1; }
+            float wEntry = entry ? w1 : w0, wOther = entry ? w0 : w1;
+            float3 result = Next::sample(S, n.child[entry], su, wi, sample, o);
+            if (isZero(result)) return result;
+            result *= wEntry * o.pdf;
+            o.pdf *= wEntry;
+            int measure = measureOf(o.type);
+            o.pdf += Next::pdf(S, n.child[1 - entry], su, wi, o.wo, measure) * wOther;
+            result += Next::eval(S, n.child[1 - entry], su, wi, o.wo, measure) * wOther;
+            return result / o.pdf;
+        }
+        case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:221-240
+            Surf pert = su;
+            pert.sh = bumpFrame(S, n, su);
+            float3 wiP = pert.sh.toLocal(su.sh.toWorld(wi));
+            float3 result = Next::sample(S, n.child[0], pert, wiP, sample, o);
+            if (!isZero(result)) {
+                float3 woP = o.wo;
+                o.wo = su.sh.toLocal(pert.sh.toWorld(woP));
+                if (cosTheta(o.wo) * cosTheta(woP) <= 0) return f3(0.0f);
+            }
+            return result;
+        }
+        default: return leafSample(S, n, su.uv, wi, sample, o);
+        }
+    }
+};
+
+// recursion floor: below kMaxBsdfDepth wrappers only leaves are legal (set_bsdfs enforces it)
+template <> struct Bsdf<kMaxBsdfDepth> {
+    static __device__ __noinline__ float3 eval(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
+        return leafEval(S, S.nodes[node], su.uv, wi, wo, measure);
+    }
+    static __device__ __noinline__ float pdf(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
+        return leafPdf(S, S.nodes[node], su.uv, wi, wo, measure);
+    }
+    static __device__ __noinline__ float3 sample(const DScene &S, int node, const Surf &su, float3 wi, float2 sample, BSample &o) {
+        return leafSample(S, S.nodes[node], su.uv, wi, sample, o);
+    }
+};
+
+typedef Bsdf<0> BsdfRoot;
+
+} // namespace mts

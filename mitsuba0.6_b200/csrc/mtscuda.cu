@@ -1,0 +1,809 @@
+// mtscuda.cu -- libmtscuda: context management, scene upload, the wavefront render loop and the
+// C ABI of include/mtscuda.h.  sm_100a only; there is no CPU path in this library.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "bvh_build.h"
+#include "wavefront.cuh"
+
+using namespace mts;
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string &msg) { g_err = msg; return code; }
+
+#define CUDA_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) \
+    return fail(MTS_ECUDA, std::string(#x) + ": " + cudaGetErrorString(e_)); } while (0)
+
+struct HostShape {
+    DShape d;
+    bool isEmitter = false;
+    float lo[3], hi[3];  // analytic bounds
+};
+
+struct HostTex { MtsTextureDesc d; std::vector<__half> texels; };
+
+struct HostEmitter {
+    MtsEmitterDesc d;
+    std::vector<float> env;  // rgb floats, half-rounded
+};
+
+// double-precision 4x4 helpers for the one-off host set-up
+struct M4 { double m[4][4]; };
+M4 m4From(const float *p) { M4 r; for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) r.m[i][j] = p[4 * i + j]; return r; }
+M4 m4Inverse(const M4 &a) {
+    double w[4][8];
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) { w[i][j] = a.m[i][j]; w[i][j + 4] = (i == j); }
+    for (int c = 0; c < 4; ++c) {
+        int piv = c;
+        for (int r = c + 1; r < 4; ++r) if (std::fabs(w[r][c]) > std::fabs(w[piv][c])) piv = r;
+        for (int j = 0; j < 8; ++j) std::swap(w[c][j], w[piv][j]);
+        double d = w[c][c];
+        for (int j = 0; j < 8; ++j) w[c][j] /= d;
+        for (int r = 0; r < 4; ++r) if (r != c) { double f = w[r][c]; for (int j = 0; j < 8; ++j) w[r][j] -= f * w[c][j]; }
+    }
+    M4 r; for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) r.m[i][j] = w[i][j + 4];
+    return r;
+}
+Affine toAffine(const M4 &a) {
+    Affine r;
+    r.r0 = make_float4((float)a.m[0][0], (float)a.m[0][1], (float)a.m[0][2], (float)a.m[0][3]);
+    r.r1 = make_float4((float)a.m[1][0], (float)a.m[1][1], (float)a.m[1][2], (float)a.m[1][3]);
+    r.r2 = make_float4((float)a.m[2][0], (float)a.m[2][1], (float)a.m[2][2], (float)a.m[2][3]);
+    return r;
+}
+void hPoint(const Affine &m, const float p[3], float out[3]) {
+    out[0] = m.r0.x * p[0] + m.r0.y * p[1] + m.r0.z * p[2] + m.r0.w;
+    out[1] = m.r1.x * p[0] + m.r1.y * p[1] + m.r1.z * p[2] + m.r1.w;
+    out[2] = m.r2.x * p[0] + m.r2.y * p[1] + m.r2.z * p[2] + m.r2.w;
+}
+void hVec(const Affine &m, const float p[3], float out[3]) {
+    out[0] = m.r0.x * p[0] + m.r0.y * p[1] + m.r0.z * p[2];
+    out[1] = m.r1.x * p[0] + m.r1.y * p[1] + m.r1.z * p[2];
+    out[2] = m.r2.x * p[0] + m.r2.y * p[1] + m.r2.z * p[2];
+}
+float hLen(const float v[3]) { return std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]); }
+float hLum(const float *p) { return p[0] * 0.212671f + p[1] * 0.715160f + p[2] * 0.072169f; }
+
+} // namespace
+
+struct MtsContext {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int numSMs = 148;
+    // staged scene
+    MtsCamera cam; bool hasCam = false;
+    MtsFilm film; bool hasFilm = false;
+    std::vector<MtsBsdfNode> nodes;
+    std::vector<float> pool;
+    std::vector<HostTex> textures;
+    std::vector<HostShape> shapes;
+    std::vector<float> positions, normals, texcoords, tangents;
+    std::vector<uint32_t> indices;
+    std::vector<HostEmitter> emitters;
+    int envIndex = -1;
+    // device scene
+    DScene ds;
+    std::vector<void *> sceneAllocs;
+    bool built = false;
+    float4 *filmInternal = nullptr, *filmBound = nullptr;
+    // wavefront
+    Wavefront wf; std::vector<void *> wfAllocs; uint32_t wfCapacity = 0;
+    MtsStats stats;
+
+    MtsContext() { std::memset(&ds, 0, sizeof(ds)); std::memset(&wf, 0, sizeof(wf)); std::memset(&stats, 0, sizeof(stats)); }
+    void freeScene() { for (void *p : sceneAllocs) cudaFree(p); sceneAllocs.clear(); built = false; }
+    void freeWavefront() { for (void *p : wfAllocs) cudaFree(p); wfAllocs.clear(); wfCapacity = 0; }
+    float4 *filmPtr() const { return filmBound ? filmBound : filmInternal; }
+};
+
+namespace {
+
+template <class T> int devUpload(MtsContext *c, const T *host, size_t n, const T **out) {
+    *out = nullptr;
+    if (n == 0) return MTS_OK;
+    T *d = nullptr;
+    CUDA_TRY(cudaMalloc(&d, sizeof(T) * n));
+    c->sceneAllocs.push_back(d);
+    CUDA_TRY(cudaMemcpyAsync(d, host, sizeof(T) * n, cudaMemcpyHostToDevice, c->stream));
+    *out = d;
+    return MTS_OK;
+}
+
+int bsdfDepth(const std::vector<MtsBsdfNode> &nodes, int i, int guard = 0) {
+    if (i < 0 || i >= (int)nodes.size() || guard > 64) return 1000;
+    const MtsBsdfNode &n = nodes[i];
+    if (n.type == MTS_BSDF_COATING || n.type == MTS_BSDF_BUMPMAP) return 1 + bsdfDepth(nodes, n.child[0], guard + 1);
+    if (n.type == MTS_BSDF_BLEND) return 1 + std::max(bsdfDepth(nodes, n.child[0], guard + 1), bsdfDepth(nodes, n.child[1], guard + 1));
+    return 0;
+}
+
+int ensureWavefront(MtsContext *c, uint32_t cap) {
+    if (c->wfCapacity >= cap) return MTS_OK;
+    c->freeWavefront();
+    Wavefront &w = c->wf;
+    auto alloc = [&](void **p, size_t bytes) -> cudaError_t {
+        cudaError_t e = cudaMalloc(p, bytes);
+        if (e == cudaSuccess) c->wfAllocs.push_back(*p);
+        return e;
+    };
+    CUDA_TRY(alloc((void **)&w.rayO, sizeof(float4) * cap)); CUDA_TRY(alloc((void **)&w.rayD, sizeof(float4) * cap));
+    CUDA_TRY(alloc((void **)&w.hit, sizeof(float4) * cap)); CUDA_TRY(alloc((void **)&w.thr, sizeof(float4) * cap));
+    CUDA_TRY(alloc((void **)&w.L, sizeof(float4) * cap)); CUDA_TRY(alloc((void **)&w.meta, sizeof(uint4) * cap));
+    CUDA_TRY(alloc((void **)&w.shO, sizeof(float4) * cap)); CUDA_TRY(alloc((void **)&w.shD, sizeof(float4) * cap));
+    CUDA_TRY(alloc((void **)&w.shC, sizeof(float4) * cap));
+    CUDA_TRY(alloc((void **)&w.queue[0], 4 * (size_t)cap)); CUDA_TRY(alloc((void **)&w.queue[1], 4 * (size_t)cap));
+    CUDA_TRY(alloc((void **)&w.doneQ, 4 * (size_t)cap));
+    CUDA_TRY(alloc((void **)&w.ctr, sizeof(Counters)));
+    w.capacity = cap;
+    c->wfCapacity = cap;
+    return MTS_OK;
+}
+
+// ---- kernels behind the per-function entry points -------------------------------------------
+__global__ void k_hook_sample_rays(const DScene S, int64_t n, const float *sp, float *out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float3 o, d, rx, ry; float mint, maxt;
+    cameraRay(S.cam, make_float2(sp[2 * i], sp[2 * i + 1]), o, d, mint, maxt, &rx, &ry);
+    float *q = out + 16 * i;
+    q[0] = o.x; q[1] = o.y; q[2] = o.z; q[3] = mint; q[4] = d.x; q[5] = d.y; q[6] = d.z; q[7] = maxt;
+    q[8] = rx.x; q[9] = rx.y; q[10] = rx.z; q[11] = 0; q[12] = ry.x; q[13] = ry.y; q[14] = ry.z; q[15] = 0;
+}
+
+__global__ void k_hook_trace(const DScene S, int64_t n, const float *rays, int shadow, float *hits, int32_t *ids, Counters *ctr) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    TraceCounters tc = {0, 0};
+    if (i < n) {
+        const float *r = rays + 8 * i;
+        float3 o = f3(r[0], r[1], r[2]), d = f3(r[4], r[5], r[6]);
+        RayHit h;
+        float *q = hits + 4 * i;
+        if (shadow) {
+            bool occ = sceneIntersect<true, true>(S, o, d, r[3], r[7], h, &tc);
+            q[0] = occ ? 0.0f : kInf; q[1] = q[2] = q[3] = 0;
+            if (ids) { ids[2 * i] = ids[2 * i + 1] = -1; }
+        } else {
+            bool ok = sceneIntersect<false, true>(S, o, d, r[3], r[7], h, &tc);
+            if (ok) {
+                const float4 *rec = reinterpret_cast<const float4 *>(S.prims + h.prim);
+                float4 p0 = rec[0], p1 = rec[1], p2 = rec[2];
+                bool tri = __float_as_int(p2.w) == 0;
+                q[0] = h.t; q[1] = tri ? h.u : 0.0f; q[2] = tri ? h.v : 0.0f; q[3] = 0;
+                if (ids) { ids[2 * i] = __float_as_int(p0.w); ids[2 * i + 1] = tri ? __float_as_int(p1.w) : 0; }
+            } else {
+                q[0] = kInf; q[1] = q[2] = q[3] = 0;
+                if (ids) { ids[2 * i] = ids[2 * i + 1] = -1; }
+            }
+        }
+    }
+    if (ctr) { atomicAdd(&ctr->nodesVisited, (unsigned long long)tc.nodes); atomicAdd(&ctr->primsTested, (unsigned long long)tc.prims); }
+}
+
+__global__ void k_hook_hit_records(const DScene S, int64_t n, const float *rays, float *out, int32_t *ids) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *r = rays + 8 * i;
+    float3 o = f3(r[0], r[1], r[2]), d = f3(r[4], r[5], r[6]);
+    RayHit h; float *q = out + 24 * i;
+    if (!sceneIntersect<false, false>(S, o, d, r[3], r[7], h)) {
+        for (int k = 0; k < 24; ++k) q[k] = 0;
+        q[3] = kInf;
+        if (ids) { ids[2 * i] = ids[2 * i + 1] = -1; }
+        return;
+    }
+    Hit its; fillHit(S, o, d, h, its);
+    q[0] = its.p.x; q[1] = its.p.y; q[2] = its.p.z; q[3] = its.t;
+    q[4] = its.geoN.x; q[5] = its.geoN.y; q[6] = its.geoN.z; q[7] = its.uv.x;
+    q[8] = its.sh.n.x; q[9] = its.sh.n.y; q[10] = its.sh.n.z; q[11] = its.uv.y;
+    q[12] = its.dpdu.x; q[13] = its.dpdu.y; q[14] = its.dpdu.z; q[15] = 0;
+    q[16] = its.dpdv.x; q[17] = its.dpdv.y; q[18] = its.dpdv.z; q[19] = 0;
+    q[20] = its.wi.x; q[21] = its.wi.y; q[22] = its.wi.z; q[23] = 0;
+    if (ids) { ids[2 * i] = its.shape; ids[2 * i + 1] = its.prim; }
+}
+
+DEVFN Surf surfFromArray(const float *s) {
+    Surf su;
+    su.uv = make_float2(s[0], s[1]);
+    su.dpdu = f3(s[4], s[5], s[6]); su.dpdv = f3(s[8], s[9], s[10]);
+    float3 n = f3(s[12], s[13], s[14]);
+    su.geoN = n;
+    su.sh = shadingFrame(n, su.dpdu);
+    return su;
+}
+__global__ void k_hook_bsdf_eval_pdf(const DScene S, int bsdf, int64_t n, const float *surf, const float *wi, const float *wo,
+                                     int measure, float *outV, float *outP) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Surf su = surfFromArray(surf + 16 * i);
+    float3 a = f3(wi[3 * i], wi[3 * i + 1], wi[3 * i + 2]), b = f3(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]);
+    float3 v = BsdfRoot::eval(S, bsdf, su, a, b, measure);
+    outV[3 * i] = v.x; outV[3 * i + 1] = v.y; outV[3 * i + 2] = v.z;
+    outP[i] = BsdfRoot::pdf(S, bsdf, su, a, b, measure);
+}
+__global__ void k_hook_bsdf_sample(const DScene S, int bsdf, int64_t n, const float *surf, const float *wi, const float *u, float *out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Surf su = surfFromArray(surf + 16 * i);
+    float3 a = f3(wi[3 * i], wi[3 * i + 1], wi[3 * i + 2]);
+    BSample bs; bs.wo = f3(0.0f); bs.pdf = 0; bs.eta = 1; bs.type = 0;
+    float3 w = BsdfRoot::sample(S, bsdf, su, a, make_float2(u[2 * i], u[2 * i + 1]), bs);
+    float *q = out + 12 * i;
+    if (isZero(w)) { for (int k = 0; k < 12; ++k) q[k] = 0; return; }
+    q[0] = w.x; q[1] = w.y; q[2] = w.z; q[3] = bs.pdf; q[4] = bs.wo.x; q[5] = bs.wo.y; q[6] = bs.wo.z;
+    q[7] = bs.eta; q[8] = (float)bs.type; q[9] = q[10] = q[11] = 0;
+}
+__global__ void k_hook_sample_emitter(const DScene S, int64_t n, const float *ref, const float *refn, const float *u, float *out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    DRec r; r.ref = f3(ref[3 * i], ref[3 * i + 1], ref[3 * i + 2]); r.refN = f3(refn[3 * i], refn[3 * i + 1], refn[3 * i + 2]);
+    r.pdf = 0; r.emitter = -1; r.measure = 0; r.dist = 0; r.d = r.n = r.p = f3(0.0f);
+    float3 v = sampleEmitterDirect(S, r, make_float2(u[2 * i], u[2 * i + 1]));
+    float *q = out + 16 * i;
+    if (isZero(v) && r.pdf == 0) { for (int k = 0; k < 16; ++k) q[k] = 0; q[15] = -1; return; }
+    q[0] = v.x; q[1] = v.y; q[2] = v.z; q[3] = r.pdf; q[4] = r.d.x; q[5] = r.d.y; q[6] = r.d.z; q[7] = r.dist;
+    q[8] = r.p.x; q[9] = r.p.y; q[10] = r.p.z; q[11] = (float)r.measure; q[12] = r.n.x; q[13] = r.n.y; q[14] = r.n.z;
+    q[15] = (float)r.emitter;
+}
+__global__ void k_hook_eval_env(const DScene S, int64_t n, const float *d, float *out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float3 dir = f3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
+    float3 v = envEval(S.env, dir);
+    out[4 * i] = v.x; out[4 * i + 1] = v.y; out[4 * i + 2] = v.z;
+    out[4 * i + 3] = envPdfDirection(S.env, xfVec(S.env.toLocal, dir)) * S.env.prob;
+}
+__global__ void k_hook_splat(const DScene S, int64_t n, const float *pos, const float *val) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    splatSample(S, make_float2(pos[2 * i], pos[2 * i + 1]), f3(val[3 * i], val[3 * i + 1], val[3 * i + 2]));
+}
+
+// device staging of host arrays for the hooks
+struct Staged {
+    std::vector<void *> ptrs;
+    ~Staged() { for (void *p : ptrs) cudaFree(p); }
+    template <class T> T *in(const T *h, size_t n, cudaStream_t st) {
+        T *d = nullptr;
+        if (cudaMalloc(&d, sizeof(T) * std::max<size_t>(n, 1)) != cudaSuccess) return nullptr;
+        ptrs.push_back(d);
+        if (n) cudaMemcpyAsync(d, h, sizeof(T) * n, cudaMemcpyHostToDevice, st);
+        return d;
+    }
+    template <class T> T *out(size_t n) {
+        T *d = nullptr;
+        if (cudaMalloc(&d, sizeof(T) * std::max<size_t>(n, 1)) != cudaSuccess) return nullptr;
+        ptrs.push_back(d);
+        return d;
+    }
+};
+inline int gridFor(int64_t n, int bs = 128) { return (int)std::max<int64_t>(1, (n + bs - 1) / bs); }
+
+int syncCheck(MtsContext *c, const char *what) {
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(MTS_ECUDA, std::string(what) + ": " + cudaGetErrorString(e));
+    return MTS_OK;
+}
+
+} // namespace
+
+// =============================================================================================
+extern "C" {
+
+MTS_API const char *mtscuda_last_error(void) { return g_err.c_str(); }
+
+MTS_API int mtscuda_create(int device, MtsContext **out) {
+    if (!out) return fail(MTS_EINVAL, "null out pointer");
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(MTS_ECUDA, std::string("no CUDA device available (libmtscuda has no CPU fallback): ") + cudaGetErrorString(e));
+    if (device < 0 || device >= count) return fail(MTS_EINVAL, "bad device index");
+    CUDA_TRY(cudaSetDevice(device));
+    MtsContext *c = new MtsContext();
+    c->device = device;
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    c->numSMs = prop.multiProcessorCount;
+    CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    *out = c;
+    return MTS_OK;
+}
+
+MTS_API void mtscuda_destroy(MtsContext *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    c->freeScene(); c->freeWavefront();
+    if (c->filmInternal) cudaFree(c->filmInternal);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+MTS_API int mtscuda_set_camera(MtsContext *c, const MtsCamera *cam) {
+    c->cam = *cam; c->hasCam = true; c->ds.cam = *cam;
+    return MTS_OK;
+}
+
+MTS_API int mtscuda_set_film(MtsContext *c, const MtsFilm *f) {
+    if (f->width <= 0 || f->height <= 0 || !(f->filter_radius > 0)) return fail(MTS_EINVAL, "bad film description");
+    CUDA_TRY(cudaSetDevice(c->device));
+    if (c->filmInternal) { cudaFree(c->filmInternal); c->filmInternal = nullptr; }
+    c->film = *f; c->hasFilm = true; c->filmBound = nullptr;
+    size_t bytes = sizeof(float4) * (size_t)f->width * f->height;
+    CUDA_TRY(cudaMalloc(&c->filmInternal, bytes));
+    CUDA_TRY(cudaMemsetAsync(c->filmInternal, 0, bytes, c->stream));
+    c->ds.film = c->filmInternal; c->ds.filmW = f->width; c->ds.filmH = f->height;
+    c->ds.filterRadius = f->filter_radius;
+    std::memcpy(c->ds.filterTable, f->filter_table, sizeof(f->filter_table));
+    return MTS_OK;
+}
+
+MTS_API int mtscuda_add_texture(MtsContext *c, const MtsTextureDesc *d, const float *texels) {
+    if (d->channels != 1 && d->channels != 3) return fail(MTS_EINVAL, "texture channels must be 1 or 3");
+    if (d->width <= 0 || d->height <= 0) return fail(MTS_EINVAL, "bad texture size");
+    if (d->filter != MTS_FILTER_NEAREST && d->filter != MTS_FILTER_BILINEAR) return fail(MTS_EINVAL, "unsupported texture filter");
+    HostTex t; t.d = *d;
+    size_t npix = (size_t)d->width * d->height;
+    int stride = d->channels == 1 ? 1 : 4;  // RGB padded to half4
+    t.texels.resize(npix * stride);
+    for (size_t i = 0; i < npix; ++i) {
+        if (d->channels == 1) t.texels[i] = __float2half_rn(texels[i]);
+        else {
+            for (int k = 0; k < 3; ++k) t.texels[4 * i + k] = __float2half_rn(texels[3 * i + k]);
+            t.texels[4 * i + 3] = __float2half_rn(0.0f);
+        }
+    }
+    c->textures.push_back(std::move(t)); c->built = false;
+    return (int)c->textures.size() - 1;
+}
+
+MTS_API int mtscuda_set_float_pool(MtsContext *c, const float *data, int64_t n) { c->pool.assign(data, data + n); c->built = false; return MTS_OK; }
+
+MTS_API int mtscuda_set_bsdfs(MtsContext *c, const MtsBsdfNode *nodes, int32_t n) {
+    c->nodes.assign(nodes, nodes + n); c->built = false;
+    for (int i = 0; i < n; ++i) {
+        if (nodes[i].type < MTS_BSDF_DIFFUSE || nodes[i].type > MTS_BSDF_BUMPMAP) return fail(MTS_EINVAL, "unknown BSDF type");
+        if (bsdfDepth(c->nodes, i) > kMaxBsdfDepth)
+            return fail(MTS_EINVAL, "BSDF nesting deeper than 4 wrapper levels (coating/blendbsdf/bumpmap) is not supported");
+    }
+    return MTS_OK;
+}
+
+MTS_API int mtscuda_add_mesh(MtsContext *c, const MtsMeshDesc *m) {
+    if (!m->positions || !m->indices || m->ntris == 0) return fail(MTS_EINVAL, "Encountered an empty triangle mesh!");
+    HostShape s; std::memset(&s.d, 0, sizeof(DShape));
+    s.d.type = SHAPE_MESH; s.d.bsdf = m->bsdf; s.d.emitter = -1;
+    uint32_t vOff = (uint32_t)(c->positions.size() / 3), tOff = (uint32_t)(c->indices.size() / 3);
+    s.d.vtxOffset = vOff; s.d.triOffset = tOff; s.d.ntris = m->ntris;
+    s.d.flags = (m->normals ? 1u : 0u) | (m->texcoords ? 2u : 0u) | (m->tangents ? 4u : 0u);
+    c->positions.insert(c->positions.end(), m->positions, m->positions + 3 * (size_t)m->nverts);
+    // the optional per-vertex arrays are kept index-aligned with `positions`
+    c->normals.resize(c->positions.size(), 0.0f);
+    if (m->normals) std::memcpy(&c->normals[3 * (size_t)vOff], m->normals, sizeof(float) * 3 * (size_t)m->nverts);
+    c->texcoords.resize(c->positions.size() / 3 * 2, 0.0f);
+    if (m->texcoords) std::memcpy(&c->texcoords[2 * (size_t)vOff], m->texcoords, sizeof(float) * 2 * (size_t)m->nverts);
+    size_t i0 = c->indices.size();
+    c->indices.resize(i0 + 3 * (size_t)m->ntris);
+    for (size_t i = 0; i < 3 * (size_t)m->ntris; ++i) {
+        if (m->indices[i] >= m->nverts) return fail(MTS_EINVAL, "mesh index out of range");
+        c->indices[i0 + i] = m->indices[i] + vOff;
+    }
+    c->tangents.resize(c->indices.size() * 2, 0.0f);
+    if (m->tangents) std::memcpy(&c->tangents[6 * (size_t)tOff], m->tangents, sizeof(float) * 6 * (size_t)m->ntris);
+    c->shapes.push_back(s); c->built = false;
+    return (int)c->shapes.size() - 1;
+}
+
+MTS_API int mtscuda_add_rectangle(MtsContext *c, const float tw[16], int32_t bsdf) {
+    HostShape s; std::memset(&s.d, 0, sizeof(DShape));
+    s.d.type = SHAPE_RECT; s.d.bsdf = bsdf; s.d.emitter = -1;
+    M4 o2w = m4From(tw), w2o = m4Inverse(o2w);
+    s.d.o2w = toAffine(o2w); s.d.w2o = toAffine(w2o);
+    // Rectangle::configure (src/shapes/rectangle.cpp:102-113)
+    const float ex[3] = {2, 0, 0}, ey[3] = {0, 2, 0};
+    float du[3], dv[3]; hVec(s.d.o2w, ex, du); hVec(s.d.o2w, ey, dv);
+    float nn[3] = {(float)w2o.m[2][0], (float)w2o.m[2][1], (float)w2o.m[2][2]};  // inverse-transpose * (0,0,1)
+    float nl = hLen(nn);
+    s.d.dpdu = make_float4(du[0], du[1], du[2], 0); s.d.dpdv = make_float4(dv[0], dv[1], dv[2], 0);
+    s.d.normal = make_float4(nn[0] / nl, nn[1] / nl, nn[2] / nl, 0);
+    s.d.invArea = 1.0f / (hLen(du) * hLen(dv));
+    const float corners[4][3] = {{-1, -1, 0}, {1, -1, 0}, {1, 1, 0}, {-1, 1, 0}};
+    for (int a = 0; a < 3; ++a) { s.lo[a] = INFINITY; s.hi[a] = -INFINITY; }
+    for (auto &cr : corners) { float p[3]; hPoint(s.d.o2w, cr, p); for (int a = 0; a < 3; ++a) { s.lo[a] = std::min(s.lo[a], p[a]); s.hi[a] = std::max(s.hi[a], p[a]); } }
+    c->shapes.push_back(s); c->built = false;
+    return (int)c->shapes.size() - 1;
+}
+
+MTS_API int mtscuda_add_sphere(MtsContext *c, const float o2wf[16], float radius, int32_t flip, int32_t bsdf) {
+    if (!(radius > 0)) return fail(MTS_EINVAL, "Cannot create spheres of radius <= 0");
+    HostShape s; std::memset(&s.d, 0, sizeof(DShape));
+    s.d.type = SHAPE_SPHERE; s.d.bsdf = bsdf; s.d.emitter = -1; s.d.flip = flip != 0; s.d.radius = radius;
+    M4 o2w = m4From(o2wf), w2o = m4Inverse(o2w);
+    s.d.o2w = toAffine(o2w); s.d.w2o = toAffine(w2o);
+    const float zero[3] = {0, 0, 0}; float ctr[3]; hPoint(s.d.o2w, zero, ctr);
+    s.d.center = make_float4(ctr[0], ctr[1], ctr[2], 0);
+    s.d.invArea = 1.0f / (4 * kPi * radius * radius);
+    for (int a = 0; a < 3; ++a) { s.lo[a] = ctr[a] - radius; s.hi[a] = ctr[a] + radius; }
+    c->shapes.push_back(s); c->built = false;
+    return (int)c->shapes.size() - 1;
+}
+
+MTS_API int mtscuda_add_emitter(MtsContext *c, const MtsEmitterDesc *d) {
+    HostEmitter e; e.d = *d; e.d.env_texels = nullptr;
+    if (d->type == MTS_EMITTER_AREA) {
+        if (d->shape < 0 || d->shape >= (int)c->shapes.size()) return fail(MTS_EINVAL, "area emitter: bad shape id");
+        c->shapes[d->shape].d.emitter = (int)c->emitters.size();
+        c->shapes[d->shape].isEmitter = true;
+    } else if (d->type == MTS_EMITTER_ENVMAP) {
+        if (c->envIndex >= 0) return fail(MTS_EINVAL, "only one environment emitter is allowed");
+        if (!d->env_texels || d->env_width <= 0 || d->env_height <= 0) return fail(MTS_EINVAL, "envmap without texels");
+        size_t n = (size_t)d->env_width * d->env_height * 3;
+        e.env.resize(n);
+        for (size_t i = 0; i < n; ++i) e.env[i] = __half2float(__float2half_rn(d->env_texels[i]));  // TMIPMap half storage
+        c->envIndex = (int)c->emitters.size();
+    } else if (d->type != MTS_EMITTER_POINT) return fail(MTS_EINVAL, "unsupported emitter type");
+    c->emitters.push_back(std::move(e)); c->built = false;
+    return (int)c->emitters.size() - 1;
+}
+
+MTS_API int mtscuda_build(MtsContext *c) {
+    CUDA_TRY(cudaSetDevice(c->device));
+    if (c->emitters.empty())
+        return fail(MTS_EINVAL, "scene has no emitters (the reference would add a sunsky emitter, which is out of scope)");
+    if (c->nodes.empty()) return fail(MTS_EINVAL, "no BSDFs set");
+    for (auto &s : c->shapes) if (s.d.bsdf < 0 || s.d.bsdf >= (int)c->nodes.size()) return fail(MTS_EINVAL, "shape references a bad BSDF index");
+    for (auto &n : c->nodes) {
+        const MtsTexRef *tr[3] = {&n.t0, &n.t1, &n.t2};
+        for (auto t : tr) if (t->tex >= (int)c->textures.size()) return fail(MTS_EINVAL, "BSDF references a bad texture index");
+    }
+    c->freeScene();
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0, c->stream);
+    DScene &S = c->ds;
+    int rc;
+    // geometry
+    if ((rc = devUpload(c, c->positions.data(), c->positions.size(), &S.positions))) return rc;
+    if ((rc = devUpload(c, c->normals.data(), c->normals.size(), &S.normals))) return rc;
+    if ((rc = devUpload(c, c->texcoords.data(), c->texcoords.size(), &S.texcoords))) return rc;
+    if ((rc = devUpload(c, c->indices.data(), c->indices.size(), &S.indices))) return rc;
+    if ((rc = devUpload(c, c->tangents.data(), c->tangents.size(), &S.tangents))) return rc;
+    // area CDFs of emitter meshes: TriMesh::prepareSamplingTable (src/librender/trimesh.cpp:388-403),
+    // sequential fp32 accumulation like DiscreteDistribution::append/normalize
+    std::vector<float> cdfs;
+    BvhBuildInput bin;
+    uint32_t primOffset = 0;
+    for (size_t si = 0; si < c->shapes.size(); ++si) {
+        HostShape &s = c->shapes[si];
+        if (s.d.type == SHAPE_MESH) {
+            bin.meshes.push_back({s.d.triOffset, s.d.ntris, primOffset, (int)si});
+            primOffset += s.d.ntris;
+            if (s.isEmitter) {
+                s.d.cdfOffset = (uint32_t)cdfs.size();
+                cdfs.push_back(0.0f);
+                float acc = 0.0f;
+                for (uint32_t t = 0; t < s.d.ntris; ++t) {
+                    const uint32_t *ix = &c->indices[3 * ((size_t)s.d.triOffset + t)];
+                    const float *p0 = &c->positions[3 * (size_t)ix[0]], *p1 = &c->positions[3 * (size_t)ix[1]], *p2 = &c->positions[3 * (size_t)ix[2]];
+                    float a[3] = {p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2]}, b[3] = {p2[0] - p0[0], p2[1] - p0[1], p2[2] - p0[2]};
+                    float cr[3] = {a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0]};
+                    acc += 0.5f * hLen(cr);
+                    cdfs.push_back(acc);
+                }
+                float norm = 1.0f / acc;
+                for (uint32_t t = 1; t <= s.d.ntris; ++t) cdfs[s.d.cdfOffset + t] *= norm;
+                cdfs[s.d.cdfOffset + s.d.ntris] = 1.0f;
+                s.d.invArea = 1.0f / acc;
+            }
+        } else {
+            BvhAnalytic a; a.primOffset = primOffset++; a.shape = (int)si; a.type = s.d.type;
+            for (int k = 0; k < 3; ++k) { a.lo[k] = s.lo[k]; a.hi[k] = s.hi[k]; }
+            bin.analytic.push_back(a);
+        }
+    }
+    if ((rc = devUpload(c, cdfs.data(), cdfs.size(), &S.areaCdfs))) return rc;
+    std::vector<DShape> dshapes; for (auto &s : c->shapes) dshapes.push_back(s.d);
+    if ((rc = devUpload(c, dshapes.data(), dshapes.size(), &S.shapes))) return rc;
+    S.numShapes = (int)dshapes.size();
+    // acceleration structure
+    bin.numPrims = (int)primOffset; bin.positions = S.positions; bin.indices = S.indices;
+    BvhBuildOutput bout; std::string berr;
+    if (!buildBvh(bin, bout, c->stream, berr)) return fail(MTS_ECUDA, "BVH build failed: " + berr);
+    if (bout.nodes) c->sceneAllocs.push_back(bout.nodes);
+    if (bout.prims) c->sceneAllocs.push_back(bout.prims);
+    S.bvh = bout.nodes; S.prims = bout.prims; S.numPrims = bin.numPrims;
+    // materials
+    if ((rc = devUpload(c, c->nodes.data(), c->nodes.size(), &S.nodes))) return rc;
+    S.numNodes = (int)c->nodes.size();
+    if ((rc = devUpload(c, c->pool.data(), c->pool.size(), &S.pool))) return rc;
+    std::vector<DTexture> dtex;
+    for (auto &t : c->textures) {
+        DTexture d; const __half *dev = nullptr;
+        if ((rc = devUpload(c, t.texels.data(), t.texels.size(), &dev))) return rc;
+        d.texels = dev; d.width = t.d.width; d.height = t.d.height; d.channels = t.d.channels;
+        d.wrapU = t.d.wrap_u; d.wrapV = t.d.wrap_v; d.filter = t.d.filter;
+        d.uvScale = make_float2(t.d.uv_scale[0], t.d.uv_scale[1]); d.uvOffset = make_float2(t.d.uv_offset[0], t.d.uv_offset[1]);
+        dtex.push_back(d);
+    }
+    if ((rc = devUpload(c, dtex.data(), dtex.size(), &S.textures))) return rc;
+    S.numTextures = (int)dtex.size();
+    // emitter pmf (src/librender/scene.cpp:375-380)
+    std::vector<float> ecdf(1, 0.0f);
+    for (auto &e : c->emitters) ecdf.push_back(ecdf.back() + e.d.sampling_weight);
+    { float sum = ecdf.back(); if (!(sum > 0)) return fail(MTS_EINVAL, "emitter sampling weights sum to zero");
+      float norm = 1.0f / sum; for (size_t j = 1; j < ecdf.size(); ++j) ecdf[j] *= norm; ecdf.back() = 1.0f; }
+    std::vector<DEmitter> dem;
+    for (size_t i = 0; i < c->emitters.size(); ++i) {
+        const MtsEmitterDesc &d = c->emitters[i].d;
+        DEmitter e; e.type = d.type; e.shape = d.shape;
+        e.radiance = make_float3(d.radiance[0], d.radiance[1], d.radiance[2]);
+        e.position = make_float3(d.position[0], d.position[1], d.position[2]);
+        e.prob = ecdf[i + 1] - ecdf[i];
+        dem.push_back(e);
+    }
+    if ((rc = devUpload(c, dem.data(), dem.size(), &S.emitters))) return rc;
+    if ((rc = devUpload(c, ecdf.data(), ecdf.size(), &S.emitterCdf))) return rc;
+    S.numEmitters = (int)dem.size();
+    // environment map: EnvironmentMap::configure CDFs (src/emitters/envmap.cpp:260-329), fp32 sequential sums
+    S.hasEnv = 0;
+    if (c->envIndex >= 0) {
+        HostEmitter &he = c->emitters[c->envIndex];
+        const int w = he.d.env_width, h = he.d.env_height;
+        std::vector<float> cdfCols((size_t)(w + 1) * h), cdfRows(h + 1), rowWeights(h);
+        size_t colPos = 0, rowPos = 0; float rowSum = 0.0f;
+        cdfRows[rowPos++] = 0;
+        for (int y = 0; y < h; ++y) {
+            float colSum = 0;
+            cdfCols[colPos++] = 0;
+            for (int x = 0; x < w; ++x) { colSum += hLum(&he.env[((size_t)y * w + x) * 3]); cdfCols[colPos++] = colSum; }
+            float normalization = 1.0f / colSum;
+            for (int x = 1; x < w; ++x) cdfCols[colPos - x - 1] *= normalization;
+            cdfCols[colPos - 1] = 1.0f;
+            float weight = std::sin((y + 0.5f) * kPi / h);
+            rowWeights[y] = weight;
+            rowSum += colSum * weight;
+            cdfRows[rowPos++] = rowSum;
+        }
+        float normalization = 1.0f / rowSum;
+        for (int y = 1; y < h; ++y) cdfRows[rowPos - y - 1] *= normalization;
+        cdfRows[rowPos - 1] = 1.0f;
+        if (rowSum == 0) return fail(MTS_EINVAL, "The environment map is completely black -- this is not allowed.");
+        if (!std::isfinite(rowSum)) return fail(MTS_EINVAL, "The environment map contains an invalid floating point value (nan/inf) -- giving up.");
+        std::vector<__half> tex((size_t)w * h * 4);
+        for (size_t i = 0; i < (size_t)w * h; ++i) {
+            for (int k = 0; k < 3; ++k) tex[4 * i + k] = __float2half_rn(he.env[3 * i + k]);
+            tex[4 * i + 3] = __float2half_rn(0.0f);
+        }
+        DEnvmap &E = S.env;
+        if ((rc = devUpload(c, tex.data(), tex.size(), &E.texels))) return rc;
+        if ((rc = devUpload(c, cdfRows.data(), cdfRows.size(), &E.cdfRows))) return rc;
+        if ((rc = devUpload(c, cdfCols.data(), cdfCols.size(), &E.cdfCols))) return rc;
+        if ((rc = devUpload(c, rowWeights.data(), rowWeights.size(), &E.rowWeights))) return rc;
+        E.width = w; E.height = h; E.scale = he.d.scale;
+        E.normalization = 1.0f / (rowSum * (2 * kPi / w) * (kPi / h));
+        M4 tw = m4From(he.d.to_world), tl = m4Inverse(tw);
+        E.toWorld = toAffine(tw); E.toLocal = toAffine(tl);
+        // m_sceneBSphere: scene AABB incl. the sensor position, radius * 1.5 (envmap.cpp:331-341, scene.cpp:386-398)
+        float lo[3], hi[3];
+        for (int a = 0; a < 3; ++a) { lo[a] = bin.numPrims ? bout.lo[a] : 0.0f; hi[a] = bin.numPrims ? bout.hi[a] : 0.0f; }
+        if (c->hasCam) {
+            const float camP[3] = {c->cam.camera_to_world[3], c->cam.camera_to_world[7], c->cam.camera_to_world[11]};
+            for (int a = 0; a < 3; ++a) {
+                if (!bin.numPrims) lo[a] = hi[a] = camP[a];
+                lo[a] = std::min(lo[a], camP[a]); hi[a] = std::max(hi[a], camP[a]);
+            }
+        }
+        float ctr[3], ext[3];
+        for (int a = 0; a < 3; ++a) { ctr[a] = (lo[a] + hi[a]) * 0.5f; ext[a] = hi[a] - ctr[a]; }
+        E.bsCenter = make_float3(ctr[0], ctr[1], ctr[2]);
+        E.bsRadius = std::max(kEps, hLen(ext) * 1.5f);
+        E.emitterIndex = c->envIndex; E.prob = ecdf[c->envIndex + 1] - ecdf[c->envIndex];
+        S.hasEnv = 1;
+    }
+    cudaEventRecord(e1, c->stream);
+    if ((rc = syncCheck(c, "build"))) return rc;
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    c->stats.build_ms = ms;
+    c->stats.kernel_launches = (uint64_t)bout.launches;
+    c->built = true;
+    return MTS_OK;
+}
+
+MTS_API int mtscuda_bind_film(MtsContext *c, void *device_ptr) {
+    if (!c->hasFilm) return fail(MTS_ESTATE, "bind_film before set_film");
+    c->filmBound = (float4 *)device_ptr;
+    c->ds.film = c->filmPtr();
+    return MTS_OK;
+}
+
+MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile const int *cancel, MtsStats *stats) {
+    if (!c->built || !c->hasCam || !c->hasFilm) return fail(MTS_ESTATE, "render before build/set_camera/set_film");
+    // MonteCarloIntegrator parameter validation (src/librender/integrator.cpp:190-225)
+    if (P->rr_depth <= 0) return fail(MTS_EINVAL, "'rrDepth' must be set to a value greater than zero!");
+    if (P->max_depth <= 0 && P->max_depth != -1) return fail(MTS_EINVAL, "'maxDepth' must be set to -1 (infinite) or a value greater than zero!");
+    if (P->spp < 0) return fail(MTS_EINVAL, "negative sample count");
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    DScene &S = c->ds;
+    S.film = c->filmPtr(); S.cam = c->cam;
+    const int W = c->film.width, H = c->film.height;
+    RenderConst R;
+    R.maxDepth = P->max_depth; R.rrDepth = P->rr_depth; R.strictNormals = P->strict_normals; R.hideEmitters = P->hide_emitters;
+    R.seed = P->seed; R.sampleOffset = P->sample_offset; R.sampleStride = P->sample_stride > 0 ? P->sample_stride : 1;
+    R.tilesX = (W + 7) / 8; R.tilesY = (H + 3) / 4; R.paddedPixels = (uint32_t)R.tilesX * R.tilesY * 32u;
+    const unsigned long long totalItems = (unsigned long long)R.paddedPixels * (unsigned long long)P->spp;
+    uint32_t cap = P->wavefront_size > 0 ? (uint32_t)P->wavefront_size : (1u << 22);
+    cap = (uint32_t)std::min<unsigned long long>(std::max<unsigned long long>(totalItems, 32), cap);
+    cap = (cap + 31u) & ~31u;
+    int rc;
+    if ((rc = ensureWavefront(c, cap))) return rc;
+    const Wavefront &Wf = c->wf;
+    if (P->clear_film) CUDA_TRY(cudaMemsetAsync(S.film, 0, sizeof(float4) * (size_t)W * H, st));
+    CUDA_TRY(cudaMemsetAsync(Wf.ctr, 0, sizeof(Counters), st));
+
+    const bool timing = true;
+    struct Span { cudaEvent_t a, b; int kind; };
+    std::vector<Span> spans;
+    auto begin = [&](int kind) { if (!timing) return; Span s; cudaEventCreate(&s.a); cudaEventCreate(&s.b); s.kind = kind; cudaEventRecord(s.a, st); spans.push_back(s); };
+    auto end = [&]() { if (!timing) return; cudaEventRecord(spans.back().b, st); };
+    cudaEvent_t ev0, ev1; cudaEventCreate(&ev0); cudaEventCreate(&ev1);
+    cudaEventRecord(ev0, st);
+
+    const int gridTrace = c->numSMs * 8, gridShade = c->numSMs * 4, gridWide = c->numSMs * 8;
+    uint64_t launches = 0, normalRays = 0, shadowRays = 0;
+    Counters hc;
+    bool cancelled = false;
+    for (unsigned long long first = 0; first < totalItems && !cancelled; first += cap) {
+        uint32_t count = (uint32_t)std::min<unsigned long long>(cap, totalItems - first);
+        int cur = 0;
+        k_reset_bounce<<<1, 1, 0, st>>>(Wf.ctr, 0);
+        begin(0);
+        k_raygen<<<gridWide, 256, 0, st>>>(S, Wf, R, first, count, 0);
+        end();
+        launches += 2;
+        uint32_t active = count;  // upper bound; the real count is on the device
+        for (int bounce = 0; active > 0; ++bounce) {
+            if (cancel && *cancel) { cancelled = true; break; }
+            k_reset_bounce<<<1, 1, 0, st>>>(Wf.ctr, cur ^ 1);
+            begin(1); k_intersect<false><<<gridTrace, 128, 0, st>>>(S, Wf, cur); end();
+            begin(2); k_shade<<<gridShade, 128, 0, st>>>(S, Wf, R, cur); end();
+            begin(3); k_shadow<false><<<gridTrace, 128, 0, st>>>(S, Wf); end();
+            begin(4); k_splat<<<gridWide, 256, 0, st>>>(S, Wf, R); end();
+            launches += 5;
+            CUDA_TRY(cudaMemcpyAsync(&hc, Wf.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaStreamSynchronize(st));
+            normalRays += hc.qCount[cur];
+            shadowRays += hc.shadowCount;
+            active = hc.qCount[cur ^ 1];
+            cur ^= 1;
+            if (bounce > 4096) break;  // safety net for maxDepth = -1 with rr disabled by huge rrDepth
+        }
+    }
+    cudaEventRecord(ev1, st);
+    if ((rc = syncCheck(c, "render"))) return rc;
+    MtsStats &sx = c->stats;
+    float build_ms = sx.build_ms;
+    std::memset(&sx, 0, sizeof(sx));
+    sx.build_ms = build_ms;
+    cudaEventElapsedTime(&sx.render_ms, ev0, ev1);
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    for (auto &s : spans) {
+        float ms = 0; cudaEventElapsedTime(&ms, s.a, s.b);
+        float *dst = s.kind == 0 ? &sx.raygen_ms : s.kind == 1 ? &sx.intersect_ms : s.kind == 2 ? &sx.shade_ms : s.kind == 3 ? &sx.shadow_ms : &sx.splat_ms;
+        *dst += ms;
+        cudaEventDestroy(s.a); cudaEventDestroy(s.b);
+    }
+    CUDA_TRY(cudaMemcpy(&hc, Wf.ctr, sizeof(Counters), cudaMemcpyDeviceToHost));
+    sx.camera_samples = (uint64_t)W * H * (uint64_t)P->spp;
+    sx.normal_rays = normalRays; sx.shadow_rays = shadowRays;
+    sx.path_length_sum = hc.pathLenSum;
+    sx.kernel_launches = launches;
+    if (stats) *stats = sx;
+    return cancelled ? fail(MTS_ECANCELLED, "render cancelled") : MTS_OK;
+}
+
+MTS_API int mtscuda_read_film(MtsContext *c, float *out) {
+    if (!c->hasFilm) return fail(MTS_ESTATE, "no film");
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    CUDA_TRY(cudaMemcpy(out, c->filmPtr(), sizeof(float4) * (size_t)c->film.width * c->film.height, cudaMemcpyDeviceToHost));
+    return MTS_OK;
+}
+
+MTS_API int mtscuda_get_stats(MtsContext *c, MtsStats *s) { *s = c->stats; return MTS_OK; }
+
+// ---- per-function entry points --------------------------------------------------------------
+#define HOOK_PREAMBLE(needBuilt) \
+    if ((needBuilt) && !c->built) return fail(MTS_ESTATE, "call build() first"); \
+    CUDA_TRY(cudaSetDevice(c->device)); \
+    Staged sg; cudaStream_t st = c->stream; c->ds.film = c->filmPtr(); c->ds.cam = c->cam;
+#define NEED(p) if (!(p)) return fail(MTS_ECUDA, "device allocation failed")
+
+MTS_API int mtscuda_sample_rays(MtsContext *c, int64_t n, const float *sp, float *out) {
+    if (!c->hasCam) return fail(MTS_ESTATE, "no camera");
+    HOOK_PREAMBLE(false)
+    float *dsp = sg.in(sp, 2 * n, st), *dout = sg.out<float>(16 * n); NEED(dsp && dout);
+    k_hook_sample_rays<<<gridFor(n), 128, 0, st>>>(c->ds, n, dsp, dout);
+    CUDA_TRY(cudaMemcpyAsync(out, dout, sizeof(float) * 16 * n, cudaMemcpyDeviceToHost, st));
+    return syncCheck(c, "sample_rays");
+}
+
+MTS_API int mtscuda_trace(MtsContext *c, int64_t n, const float *rays, int32_t shadow, float *hits, int32_t *ids) {
+    HOOK_PREAMBLE(true)
+    float *dr = sg.in(rays, 8 * n, st), *dh = sg.out<float>(4 * n); int32_t *di = sg.out<int32_t>(2 * n);
+    Counters *ctr = sg.out<Counters>(1); NEED(dr && dh && di && ctr);
+    CUDA_TRY(cudaMemsetAsync(ctr, 0, sizeof(Counters), st));
+    k_hook_trace<<<gridFor(n), 128, 0, st>>>(c->ds, n, dr, shadow, dh, di, ctr);
+    CUDA_TRY(cudaMemcpyAsync(hits, dh, sizeof(float) * 4 * n, cudaMemcpyDeviceToHost, st));
+    if (ids) CUDA_TRY(cudaMemcpyAsync(ids, di, sizeof(int32_t) * 2 * n, cudaMemcpyDeviceToHost, st));
+    Counters hc;
+    CUDA_TRY(cudaMemcpyAsync(&hc, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+    int rc = syncCheck(c, "trace");
+    c->stats.bvh_nodes_visited = hc.nodesVisited; c->stats.bvh_prims_tested = hc.primsTested;
+    return rc;
+}
+
+MTS_API int mtscuda_hit_records(MtsContext *c, int64_t n, const float *rays, float *out, int32_t *ids) {
+    HOOK_PREAMBLE(true)
+    float *dr = sg.in(rays, 8 * n, st), *dout = sg.out<float>(24 * n); int32_t *di = sg.out<int32_t>(2 * n); NEED(dr && dout && di);
+    k_hook_hit_records<<<gridFor(n), 128, 0, st>>>(c->ds, n, dr, dout, di);
+    CUDA_TRY(cudaMemcpyAsync(out, dout, sizeof(float) * 24 * n, cudaMemcpyDeviceToHost, st));
+    if (ids) CUDA_TRY(cudaMemcpyAsync(ids, di, sizeof(int32_t) * 2 * n, cudaMemcpyDeviceToHost, st));
+    return syncCheck(c, "hit_records");
+}
+
+MTS_API int mtscuda_bsdf_eval_pdf(MtsContext *c, int32_t bsdf, int64_t n, const float *surf, const float *wi, const float *wo,
+                                  int32_t measure, float *out_value, float *out_pdf) {
+    if (bsdf < 0 || bsdf >= (int)c->nodes.size()) return fail(MTS_EINVAL, "bad bsdf index");
+    HOOK_PREAMBLE(true)
+    float *ds_ = sg.in(surf, 16 * n, st), *dwi = sg.in(wi, 3 * n, st), *dwo = sg.in(wo, 3 * n, st);
+    float *dv = sg.out<float>(3 * n), *dp = sg.out<float>(n); NEED(ds_ && dwi && dwo && dv && dp);
+    k_hook_bsdf_eval_pdf<<<gridFor(n), 128, 0, st>>>(c->ds, bsdf, n, ds_, dwi, dwo, measure, dv, dp);
+    CUDA_TRY(cudaMemcpyAsync(out_value, dv, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(out_pdf, dp, sizeof(float) * n, cudaMemcpyDeviceToHost, st));
+    return syncCheck(c, "bsdf_eval_pdf");
+}
+
+MTS_API int mtscuda_bsdf_sample(MtsContext *c, int32_t bsdf, int64_t n, const float *surf, const float *wi, const float *u, float *out) {
+    if (bsdf < 0 || bsdf >= (int)c->nodes.size()) return fail(MTS_EINVAL, "bad bsdf index");
+    HOOK_PREAMBLE(true)
+    float *ds_ = sg.in(surf, 16 * n, st), *dwi = sg.in(wi, 3 * n, st), *du = sg.in(u, 2 * n, st), *dout = sg.out<float>(12 * n);
+    NEED(ds_ && dwi && du && dout);
+    k_hook_bsdf_sample<<<gridFor(n), 128, 0, st>>>(c->ds, bsdf, n, ds_, dwi, du, dout);
+    CUDA_TRY(cudaMemcpyAsync(out, dout, sizeof(float) * 12 * n, cudaMemcpyDeviceToHost, st));
+    return syncCheck(c, "bsdf_sample");
+}
+
+MTS_API int mtscuda_sample_emitter_direct(MtsContext *c, int64_t n, const float *ref, const float *refn, const float *u, float *out) {
+    HOOK_PREAMBLE(true)
+    float *dr = sg.in(ref, 3 * n, st), *dn = sg.in(refn, 3 * n, st), *du = sg.in(u, 2 * n, st), *dout = sg.out<float>(16 * n);
+    NEED(dr && dn && du && dout);
+    k_hook_sample_emitter<<<gridFor(n), 128, 0, st>>>(c->ds, n, dr, dn, du, dout);
+    CUDA_TRY(cudaMemcpyAsync(out, dout, sizeof(float) * 16 * n, cudaMemcpyDeviceToHost, st));
+    return syncCheck(c, "sample_emitter_direct");
+}
+
+MTS_API int mtscuda_eval_environment(MtsContext *c, int64_t n, const float *d, float *out) {
+    if (!c->built || !c->ds.hasEnv) return fail(MTS_ESTATE, "no environment emitter");
+    HOOK_PREAMBLE(true)
+    float *dd = sg.in(d, 3 * n, st), *dout = sg.out<float>(4 * n); NEED(dd && dout);
+    k_hook_eval_env<<<gridFor(n), 128, 0, st>>>(c->ds, n, dd, dout);
+    CUDA_TRY(cudaMemcpyAsync(out, dout, sizeof(float) * 4 * n, cudaMemcpyDeviceToHost, st));
+    return syncCheck(c, "eval_environment");
+}
+
+MTS_API int mtscuda_splat(MtsContext *c, int64_t n, const float *pos, const float *value, int32_t clear_first) {
+    if (!c->hasFilm) return fail(MTS_ESTATE, "no film");
+    HOOK_PREAMBLE(false)
+    if (clear_first) CUDA_TRY(cudaMemsetAsync(c->ds.film, 0, sizeof(float4) * (size_t)c->film.width * c->film.height, st));
+    float *dp = sg.in(pos, 2 * n, st), *dv = sg.in(value, 3 * n, st); NEED(dp && dv);
+    k_hook_splat<<<gridFor(n), 128, 0, st>>>(c->ds, n, dp, dv);
+    return syncCheck(c, "splat");
+}
+
+} // extern "C"

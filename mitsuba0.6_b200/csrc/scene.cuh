@@ -1,0 +1,95 @@
+// scene.cuh -- device-side scene layout (the data layout in HBM; see DESIGN.md "Data layout").
+#pragma once
+#include "common.cuh"
+
+namespace mts {
+
+// Bitmap texture, level 0 only (TMIPMap stores half precision; 3-channel texels are padded to
+// half4 so one bilinear tap is one aligned 8-byte load).
+struct DTexture {
+    const __half *texels;
+    int width, height, channels;  // channels: 1 or 3 (3 -> stored as 4 halves)
+    int wrapU, wrapV, filter;
+    float2 uvScale, uvOffset;
+};
+
+enum { SHAPE_MESH = 0, SHAPE_RECT = 1, SHAPE_SPHERE = 2 };
+
+struct DShape {
+    int type, bsdf, emitter, flip;
+    // mesh: offsets into the concatenated vertex / triangle arrays
+    uint32_t vtxOffset, triOffset, ntris, flags;  // flags: 1 normals, 2 uvs, 4 tangents
+    uint32_t cdfOffset;                           // area CDF (ntris+1 floats) when the mesh is an emitter
+    float invArea;
+    float radius;
+    float pad;
+    Affine o2w, w2o;                              // rectangle / sphere
+    float4 dpdu, dpdv, normal, center;            // rectangle frame / sphere centre
+};
+
+struct DEmitter {
+    int type, shape;
+    float3 radiance;   // area radiance / point intensity
+    float3 position;
+    float prob;        // discrete selection probability (Scene::m_emitterPDF)
+};
+
+struct DEnvmap {
+    const __half *texels;    // half4 per texel
+    const float *cdfRows, *cdfCols, *rowWeights;
+    int width, height;
+    float normalization, scale;
+    Affine toWorld, toLocal;
+    float3 bsCenter; float bsRadius;
+    int emitterIndex;
+    float prob;
+};
+
+// Two-wide BVH node, 64 bytes: both child boxes + child links (4 x float4 loads per visit).
+struct BvhNode {
+    float4 a;  // lo0.xyz, hi0.x
+    float4 b;  // hi0.yz, lo1.xy
+    float4 c;  // lo1.z, hi1.xyz
+    int4 link; // child0, child1 (node index, or first primitive when count > 0), count0, count1
+};
+
+// 48-byte primitive record in leaf order.
+//   triangle: p0 = (v0, shape), p1 = (e1 = v1-v0, prim index), p2 = (e2 = v2-v0, 0)
+//   analytic: p0.w = shape, p2.w = 1 (rectangle) / 2 (sphere)
+struct PrimRecord { float4 p0, p1, p2; };
+
+struct DScene {
+    // materials
+    const MtsBsdfNode *nodes; int numNodes;
+    const DTexture *textures; int numTextures;
+    const float *pool;
+    // geometry
+    const DShape *shapes; int numShapes;
+    const float *positions;   // 3 floats / vertex
+    const float *normals;     // 3 floats / vertex (valid where the shape has normals)
+    const float *texcoords;   // 2 floats / vertex
+    const uint32_t *indices;  // 3 / triangle, already offset into the global vertex arrays
+    const float *tangents;    // 6 floats / triangle
+    const float *areaCdfs;
+    const BvhNode *bvh; const PrimRecord *prims; int numPrims;
+    // emitters
+    const DEmitter *emitters; const float *emitterCdf; int numEmitters;
+    DEnvmap env; int hasEnv;
+    // sensor + film
+    MtsCamera cam;
+    float4 *film; int filmW, filmH;
+    float filterRadius; float filterTable[MTS_FILTER_RESOLUTION + 1];
+};
+
+// Full hit record (subset of `Intersection`, include/mitsuba/render/shape.h:36-172)
+struct Hit {
+    float3 p; float t;
+    float3 geoN;
+    Frame sh;
+    float2 uv;
+    float3 dpdu, dpdv;
+    float3 wi;
+    int shape, prim;
+};
+
+} // namespace mts

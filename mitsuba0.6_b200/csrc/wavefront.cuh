@@ -1,0 +1,313 @@
+// wavefront.cuh -- the path-tracing hot path as a wavefront of sm_100a kernels.
+//
+// MIPathTracer::Li (src/integrators/path/path.cpp:119-294) is a per-sample recursive loop of
+// virtual calls.  Here one wavefront holds P path slots in SoA float4 arrays; every bounce runs
+//   intersect (closest hit) -> shade (emission + MIS, NEE sample, BSDF sample, Russian roulette)
+//   -> shadow (any-hit for the NEE rays) -> splat (finished paths into the film)
+// over compacted index queues built with warp-aggregated atomics (__ballot_sync/__popc, one
+// atomicAdd per warp).  All kernels are persistent grid-stride kernels whose trip count is read
+// from device memory, so a bounce needs no host round trip to size its launches.
+#pragma once
+#include "bsdf.cuh"
+#include "emitter.cuh"
+
+namespace mts {
+
+struct Counters {
+    uint32_t qCount[2];     // active queue sizes (ping-pong)
+    uint32_t shadowCount;
+    uint32_t doneCount;
+    unsigned long long pathLenSum;
+    unsigned long long nodesVisited, primsTested;  // instrumented traces only
+};
+
+struct Wavefront {
+    float4 *rayO, *rayD;     // o.xyz + mint, d.xyz + maxt
+    float4 *hit;             // t, u, v, prim slot (int bits)
+    float4 *thr;             // throughput rgb, eta
+    float4 *L;               // radiance rgb, pdf of the BSDF sample that produced the current ray
+    uint4 *meta;             // pixel index, global sample index, depth | flags << 16, unused
+    float4 *shO, *shD, *shC; // shadow ray origin/dir (+mint/maxt), contribution rgb + path slot
+    uint32_t *queue[2];
+    uint32_t *doneQ;
+    Counters *ctr;
+    uint32_t capacity;
+};
+
+struct RenderConst {
+    int maxDepth, rrDepth, strictNormals, hideEmitters;
+    uint32_t seed;
+    int sampleOffset, sampleStride;
+    int tilesX, tilesY;      // 8x4 pixel tiles
+    uint32_t paddedPixels;   // tilesX*tilesY*32
+};
+
+enum { PF_SCATTERED = 1, PF_PREV_DELTA = 2, PF_PREV_REFN_OK = 4 };
+
+// One atomicAdd per warp: returns this thread's slot (valid only where pred is true).
+DEVFN uint32_t warpAppend(uint32_t *counter, bool pred) {
+    unsigned active = __activemask();
+    unsigned mask = __ballot_sync(active, pred);
+    if (!pred) return 0xffffffffu;
+    int lane = threadIdx.x & 31;
+    int leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(mask));
+    base = __shfl_sync(mask, base, leader);
+    return base + __popc(mask & ((1u << lane) - 1));
+}
+
+DEVFN Surf surfOf(const Hit &h) {
+    Surf s; s.uv = h.uv; s.dpdu = h.dpdu; s.dpdv = h.dpdv; s.geoN = h.geoN; s.sh = h.sh; return s;
+}
+
+// ---- raygen: SamplingIntegrator::renderBlock sample loop + sampleRayDifferential -------------
+__global__ void __launch_bounds__(256) k_raygen(const DScene S, const Wavefront W, const RenderConst R,
+                                                unsigned long long firstItem, uint32_t count, int qsel) {
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < ((count + 31u) & ~31u); j += gridDim.x * blockDim.x) {
+        bool valid = j < count;
+        uint32_t pixel = 0, sample = 0;
+        int x = 0, y = 0;
+        if (valid) {
+            unsigned long long g = firstItem + j;
+            uint32_t sLocal = (uint32_t)(g / R.paddedPixels), pp = (uint32_t)(g % R.paddedPixels);
+            uint32_t tile = pp >> 5, lane = pp & 31;
+            x = (int)(tile % R.tilesX) * 8 + (int)(lane & 7);
+            y = (int)(tile / R.tilesX) * 4 + (int)(lane >> 3);
+            valid = x < S.filmW && y < S.filmH;
+            pixel = (uint32_t)y * S.filmW + x;
+            sample = (uint32_t)(R.sampleOffset + (int)sLocal * R.sampleStride);
+        }
+        if (valid) {
+            float4 u = rand4(R.seed, pixel, sample, 0);
+            float3 o, d; float mint, maxt;
+            cameraRay(S.cam, make_float2(x + u.x, y + u.y), o, d, mint, maxt);
+            W.rayO[j] = make_float4(o.x, o.y, o.z, mint);
+            W.rayD[j] = make_float4(d.x, d.y, d.z, maxt);
+            W.thr[j] = make_float4(1, 1, 1, 1);
+            W.L[j] = make_float4(0, 0, 0, 0);
+            W.meta[j] = make_uint4(pixel, sample, 1u, 0u);
+        }
+        uint32_t slot = warpAppend(&W.ctr->qCount[qsel], valid);
+        if (valid) W.queue[qsel][slot] = j;
+    }
+}
+
+// ---- intersect: Scene::rayIntersect -> ShapeKDTree::rayIntersect(ray, its) --------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_intersect(const DScene S, const Wavefront W, int qsel) {
+    const uint32_t count = W.ctr->qCount[qsel];
+    TraceCounters tc = {0, 0};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        uint32_t slot = W.queue[qsel][i];
+        float4 ro = W.rayO[slot], rd = W.rayD[slot];
+        RayHit h;
+        sceneIntersect<false, COUNT>(S, f3(ro), f3(rd), ro.w, rd.w, h, &tc);
+        W.hit[slot] = make_float4(h.t, h.u, h.v, __int_as_float(h.prim));
+    }
+    if (COUNT) { atomicAdd(&W.ctr->nodesVisited, (unsigned long long)tc.nodes); atomicAdd(&W.ctr->primsTested, (unsigned long long)tc.prims); }
+}
+
+// ---- shadow: ShapeKDTree::rayIntersect(ray) for Scene::sampleEmitterDirect --------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_shadow(const DScene S, const Wavefront W) {
+    const uint32_t count = W.ctr->shadowCount;
+    TraceCounters tc = {0, 0};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        float4 ro = W.shO[i], rd = W.shD[i];
+        RayHit h;
+        bool occluded = sceneIntersect<true, COUNT>(S, f3(ro), f3(rd), ro.w, rd.w, h, &tc);
+        if (!occluded) {
+            float4 c = W.shC[i];
+            uint32_t slot = (uint32_t)__float_as_int(c.w);
+            float4 l = W.L[slot];
+            l.x += c.x; l.y += c.y; l.z += c.z;
+            W.L[slot] = l;
+        }
+    }
+    if (COUNT) { atomicAdd(&W.ctr->nodesVisited, (unsigned long long)tc.nodes); atomicAdd(&W.ctr->primsTested, (unsigned long long)tc.prims); }
+}
+
+// ---- shade: one iteration of the Li loop ----------------------------------------------------
+struct ShadeOut { bool next, shadow, done; float4 shO, shD, shC; };
+
+DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, uint32_t slot, ShadeOut &out) {
+    out.next = false; out.shadow = false; out.done = true;
+    float4 ro = W.rayO[slot], rd = W.rayD[slot], hv = W.hit[slot];
+    float4 tv = W.thr[slot], lv = W.L[slot];
+    uint4 meta = W.meta[slot];
+    float3 o = f3(ro), d = f3(rd);
+    float3 thr = f3(tv), L = f3(lv);
+    float eta = tv.w, prevPdf = lv.w;
+    uint32_t depth = meta.z & 0xffffu, flags = meta.z >> 16;
+    const int prim = __float_as_int(hv.w);
+    const bool first = depth == 1;
+
+    auto finish = [&]() { W.L[slot] = make_float4(L.x, L.y, L.z, 0); W.meta[slot] = make_uint4(meta.x, meta.y, depth | (flags << 16), 0); };
+
+    if (prim < 0) {
+        // path.cpp:136-143 (camera ray) / :238-248,257-264 (BSDF-sampled ray escaping to the envmap)
+        if (S.hasEnv) {
+            if (first) {
+                if (!R.hideEmitters) L += thr * envEval(S.env, d);
+            } else {
+                float nearT, farT;  // fillDirectSamplingRecord, envmap.cpp:358-374
+                if (bsphereIntersect(S.env, o, d, nearT, farT) && !(nearT > 0) && !(farT < 0)) {
+                    float lumPdf = (flags & PF_PREV_DELTA) ? 0.0f : envPdfDirection(S.env, xfVec(S.env.toLocal, d)) * S.env.prob;
+                    L += thr * envEval(S.env, d) * miWeight(prevPdf, lumPdf);
+                }
+            }
+        }
+        finish();
+        return;
+    }
+
+    RayHit rh; rh.t = hv.x; rh.u = hv.y; rh.v = hv.z; rh.prim = prim;
+    Hit its;
+    fillHit(S, o, d, rh, its);
+    const DShape &shape = S.shapes[its.shape];
+
+    if (shape.emitter >= 0) {
+        const DEmitter &em = S.emitters[shape.emitter];
+        float3 Le = areaLe(em, its.sh.n, -d);
+        if (first) {
+            if (!R.hideEmitters) L += thr * Le;  // path.cpp:148-150
+        } else {
+            // path.cpp:257-264 with Scene::pdfEmitterDirect (scene.cpp:949-952) and AreaLight::pdfDirect (area.cpp:174-183)
+            float lumPdf = 0.0f;
+            if (!(flags & PF_PREV_DELTA) && (flags & PF_PREV_REFN_OK) && dot(d, its.sh.n) < 0)
+                lumPdf = shapePdfDirect(shape, o, d, its.sh.n, its.t) * em.prob;
+            L += thr * Le * miWeight(prevPdf, lumPdf);
+        }
+    }
+
+    if (!first) {
+        // Russian roulette of the previous iteration (path.cpp:276-286): `depth` was already incremented
+        if ((int)(depth - 1) >= R.rrDepth) {
+            float q = fminf(maxc(thr) * eta * eta, 0.95f);
+            float4 u = rand4(R.seed, meta.x, meta.y, 2 * depth - 2);
+            if (u.x >= q) { finish(); return; }
+            thr = thr / q;
+        }
+    }
+
+    // path.cpp:156-165
+    if ((R.maxDepth > 0 && (int)depth >= R.maxDepth) ||
+        (R.strictNormals && dot(d, its.geoN) * cosTheta(its.wi) >= 0)) { finish(); return; }
+
+    const int bsdf = shape.bsdf;
+    const uint32_t lobes = S.nodes[bsdf].lobes;
+    const Surf su = surfOf(its);
+    float4 u = rand4(R.seed, meta.x, meta.y, 2 * depth - 1);
+
+    // ---- direct illumination sampling (path.cpp:172-200) ----
+    float3 refN = ((lobes & (MTS_ETRANSMISSION | MTS_EBACKSIDE)) == 0) ? its.sh.n : f3(0.0f);  // records.inl:160-164
+    if (lobes & MTS_ESMOOTH) {
+        DRec dr; dr.ref = its.p; dr.refN = refN; dr.pdf = 0; dr.emitter = -1; dr.measure = 0; dr.dist = 0;
+        dr.d = f3(0.0f); dr.n = f3(0.0f); dr.p = f3(0.0f);
+        float3 value = sampleEmitterDirect(S, dr, make_float2(u.x, u.y));
+        if (!isZero(value)) {
+            float3 wo = its.sh.toLocal(dr.d);
+            float3 bsdfVal = BsdfRoot::eval(S, bsdf, su, its.wi, wo, MTS_MEASURE_SOLID_ANGLE);
+            if (!isZero(bsdfVal) && (!R.strictNormals || dot(its.geoN, dr.d) * cosTheta(wo) > 0)) {
+                // area and environment emitters are "on surface"; the point emitter is not
+                bool onSurface = S.emitters[dr.emitter].type != MTS_EMITTER_POINT;
+                float bsdfPdf = (onSurface && dr.measure == MTS_MEASURE_SOLID_ANGLE)
+                    ? BsdfRoot::pdf(S, bsdf, su, its.wi, wo, MTS_MEASURE_SOLID_ANGLE) : 0.0f;
+                float3 c = thr * value * bsdfVal * miWeight(dr.pdf, bsdfPdf);
+                out.shadow = true;
+                out.shO = make_float4(dr.ref.x, dr.ref.y, dr.ref.z, kEps);
+                out.shD = make_float4(dr.d.x, dr.d.y, dr.d.z, dr.dist * (1 - kShadowEps));
+                out.shC = make_float4(c.x, c.y, c.z, __int_as_float((int)slot));
+            }
+        }
+    }
+
+    // ---- BSDF sampling (path.cpp:203-253) ----
+    BSample bs; bs.pdf = 0; bs.eta = 1; bs.type = 0; bs.wo = f3(0.0f);
+    float3 bsdfWeight = BsdfRoot::sample(S, bsdf, su, its.wi, make_float2(u.z, u.w), bs);
+    if (isZero(bsdfWeight)) { finish(); return; }
+    flags |= PF_SCATTERED;
+    const float3 wo = its.sh.toWorld(bs.wo);
+    if (R.strictNormals && dot(its.geoN, wo) * cosTheta(bs.wo) <= 0) { finish(); return; }
+
+    thr *= bsdfWeight;
+    eta *= bs.eta;
+    flags &= ~(uint32_t)(PF_PREV_DELTA | PF_PREV_REFN_OK);
+    if (bs.type & MTS_EDELTA) flags |= PF_PREV_DELTA;
+    if (dot(wo, refN) >= 0) flags |= PF_PREV_REFN_OK;
+    depth += 1;
+
+    W.rayO[slot] = make_float4(its.p.x, its.p.y, its.p.z, kEps);
+    W.rayD[slot] = make_float4(wo.x, wo.y, wo.z, kInf);
+    W.thr[slot] = make_float4(thr.x, thr.y, thr.z, eta);
+    W.L[slot] = make_float4(L.x, L.y, L.z, bs.pdf);
+    W.meta[slot] = make_uint4(meta.x, meta.y, depth | (flags << 16), 0);
+    out.next = true; out.done = false;
+}
+
+__global__ void __launch_bounds__(128) k_shade(const DScene S, const Wavefront W, const RenderConst R, int qsel) {
+    const uint32_t count = W.ctr->qCount[qsel];
+    const uint32_t rounded = (count + 31u) & ~31u;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
+        ShadeOut out; out.next = out.shadow = out.done = false;
+        uint32_t slot = 0;
+        if (i < count) {
+            slot = W.queue[qsel][i];
+            shadePath(S, W, R, slot, out);
+        }
+        uint32_t a = warpAppend(&W.ctr->qCount[qsel ^ 1], out.next);
+        if (out.next) W.queue[qsel ^ 1][a] = slot;
+        uint32_t b = warpAppend(&W.ctr->shadowCount, out.shadow);
+        if (out.shadow) { W.shO[b] = out.shO; W.shD[b] = out.shD; W.shC[b] = out.shC; }
+        uint32_t c = warpAppend(&W.ctr->doneCount, out.done);
+        if (out.done) W.doneQ[c] = slot;
+    }
+}
+
+// ---- splat: ImageBlock::put(pos, spec, alpha) (include/mitsuba/render/imageblock.h:124-204) ----
+DEVFN void filmAdd(float4 *dst, float4 v) {
+#if __CUDA_ARCH__ >= 900
+    atomicAdd(dst, v);  // one 16-byte vector reduction per tap
+#else
+    atomicAdd(&dst->x, v.x); atomicAdd(&dst->y, v.y); atomicAdd(&dst->z, v.z); atomicAdd(&dst->w, v.w);
+#endif
+}
+DEVFN void splatSample(const DScene &S, float2 samplePos, float3 value) {
+    // reject invalid samples like put() does (:147-151)
+    if (!(isfinite(value.x) && isfinite(value.y) && isfinite(value.z)) || value.x < 0 || value.y < 0 || value.z < 0) return;
+    const float r = S.filterRadius;
+    const float scaleFactor = MTS_FILTER_RESOLUTION / r;
+    const float px = samplePos.x - 0.5f, py = samplePos.y - 0.5f;
+    int minx = max((int)ceilf(px - r), 0), miny = max((int)ceilf(py - r), 0);
+    int maxx = min((int)floorf(px + r), S.filmW - 1), maxy = min((int)floorf(py + r), S.filmH - 1);
+    for (int y = miny; y <= maxy; ++y) {
+        float wy = S.filterTable[min((int)fabsf((y - py) * scaleFactor), MTS_FILTER_RESOLUTION)];
+        for (int x = minx; x <= maxx; ++x) {
+            float w = S.filterTable[min((int)fabsf((x - px) * scaleFactor), MTS_FILTER_RESOLUTION)] * wy;
+            if (w == 0.0f) continue;
+            filmAdd(S.film + (size_t)y * S.filmW + x, make_float4(w * value.x, w * value.y, w * value.z, w));
+        }
+    }
+}
+__global__ void __launch_bounds__(256) k_splat(const DScene S, const Wavefront W, const RenderConst R) {
+    const uint32_t count = W.ctr->doneCount;
+    unsigned long long lenSum = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        uint32_t slot = W.doneQ[i];
+        float4 l = W.L[slot];
+        uint4 meta = W.meta[slot];
+        float4 u = rand4(R.seed, meta.x, meta.y, 0);
+        int x = (int)(meta.x % (uint32_t)S.filmW), y = (int)(meta.x / (uint32_t)S.filmW);
+        splatSample(S, make_float2(x + u.x, y + u.y), f3(l));
+        lenSum += meta.z & 0xffffu;
+    }
+    for (int o = 16; o > 0; o >>= 1) lenSum += __shfl_xor_sync(0xffffffffu, lenSum, o);
+    if ((threadIdx.x & 31) == 0 && lenSum) atomicAdd(&W.ctr->pathLenSum, lenSum);
+}
+
+__global__ void k_reset_bounce(Counters *c, int nextSel) {
+    c->qCount[nextSel] = 0; c->shadowCount = 0; c->doneCount = 0;
+}
+
+} // namespace mts

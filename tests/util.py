@@ -1,0 +1,164 @@
+"""Shared helpers for the parity tests: a 'material zoo' scene that instantiates every in-scope BSDF
+(incl. nested wrappers, both microfacet distributions, textured parameters) and every emitter kind."""
+import numpy as np
+
+import mts_b200 as M
+from mitsuba0_6_b200 import hostmath as hm, scenes
+from mitsuba0_6_b200.scene import Plugin, Point, Spectrum
+
+F = np.float32
+
+
+def _tex(seed, channels=3, size=64, **kw):
+    rng = np.random.RandomState(seed)
+    t = Plugin("texture", "bitmap", filterType="bilinear", gamma=1.0, **kw)
+    t.data["bitmap"] = rng.uniform(0.05, 0.95, (size, size, channels)).astype(F)
+    return t
+
+
+def zoo_bsdfs():
+    CU, AU, AL = scenes.CU, scenes.AU, scenes.AL
+    z = {}
+    z["diffuse"] = Plugin("bsdf", "diffuse", reflectance=Spectrum(0.2, 0.5, 0.7))
+    d = Plugin("bsdf", "diffuse")
+    d.add(_tex(1, uvscale=3.0), "reflectance")
+    z["diffuse_tex"] = d
+    z["conductor"] = Plugin("bsdf", "conductor", **CU)
+    z["conductor_spec"] = Plugin("bsdf", "conductor", specularReflectance=Spectrum(0.9, 0.8, 0.7), extEta=1.33, **AU)
+    z["rc_beckmann"] = Plugin("bsdf", "roughconductor", distribution="beckmann", alpha=0.3, **CU)
+    z["rc_ggx"] = Plugin("bsdf", "roughconductor", distribution="ggx", alpha=0.1, **AU)
+    z["rc_beckmann_aniso"] = Plugin("bsdf", "roughconductor", distribution="beckmann", alphaU=0.1, alphaV=0.3, **AL)
+    z["rc_ggx_aniso"] = Plugin("bsdf", "roughconductor", distribution="ggx", alphaU=0.2, alphaV=0.3, **CU)
+    z["rc_ggx_all"] = Plugin("bsdf", "roughconductor", distribution="ggx", alpha=0.25, sampleVisible=False, **CU)
+    z["rc_beckmann_all"] = Plugin("bsdf", "roughconductor", distribution="beckmann", alphaU=0.15, alphaV=0.4, sampleVisible=False, **AL)
+    rct = Plugin("bsdf", "roughconductor", distribution="ggx", **AU)
+    at = Plugin("texture", "scale", scale=0.5)
+    at.add(_tex(2, channels=1))
+    rct.add(at, "alpha")
+    z["rc_ggx_texalpha"] = rct
+    z["plastic"] = Plugin("bsdf", "plastic", intIOR=1.49, diffuseReflectance=Spectrum(0.5, 0.3, 0.2))
+    z["plastic_nl"] = Plugin("bsdf", "plastic", intIOR=1.9, extIOR="water", nonlinear=True,
+                             diffuseReflectance=Spectrum(0.8, 0.7, 0.1), specularReflectance=Spectrum(0.6))
+    z["rp_beckmann"] = Plugin("bsdf", "roughplastic", distribution="beckmann", alpha=0.7, intIOR=1.49)
+    z["rp_ggx"] = Plugin("bsdf", "roughplastic", distribution="ggx", alpha=0.15, intIOR=1.6, nonlinear=True,
+                         diffuseReflectance=Spectrum(0.2, 0.4, 0.8))
+    rpt = Plugin("bsdf", "roughplastic", distribution="ggx", intIOR=1.5)
+    at2 = Plugin("texture", "scale", scale=0.4)
+    at2.add(_tex(3, channels=1))
+    rpt.add(at2, "alpha")
+    rpt.add(_tex(4), "diffuseReflectance")
+    z["rp_ggx_tex"] = rpt
+    z["dielectric"] = Plugin("bsdf", "dielectric", intIOR="bk7")
+    z["dielectric_water_air"] = Plugin("bsdf", "dielectric", intIOR="water", extIOR="air",
+                                       specularTransmittance=Spectrum(0.9, 0.95, 1.0))
+    c = Plugin("bsdf", "coating", intIOR=1.5, thickness=1.0, sigmaA=Spectrum(0.1, 0.2, 0.3))
+    c.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.6, 0.5, 0.3)))
+    z["coating_diffuse"] = c
+    c2 = Plugin("bsdf", "coating", intIOR=1.7, thickness=2.0)
+    c2.add(Plugin("bsdf", "roughconductor", distribution="ggx", alpha=0.2, **CU))
+    z["coating_rc"] = c2
+    b = Plugin("bsdf", "blendbsdf", weight=0.3)
+    b.add(Plugin("bsdf", "conductor", **AU))
+    b.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.5)))
+    z["blend_cond_diff"] = b
+    b2 = Plugin("bsdf", "blendbsdf")
+    b2.add(_tex(5, channels=1), "weight")
+    b2.add(Plugin("bsdf", "roughplastic", distribution="beckmann", alpha=0.2, intIOR=1.49))
+    b2.add(Plugin("bsdf", "dielectric", intIOR=1.5))
+    z["blend_tex_rp_diel"] = b2
+    bm = Plugin("bsdf", "bumpmap")
+    bm.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.7, 0.6, 0.5)))
+    bt = Plugin("texture", "scale", scale=0.05)
+    bt.add(_tex(6, channels=1, uvscale=2.0))
+    bm.add(bt)
+    z["bump_diffuse"] = bm
+    bm2 = Plugin("bsdf", "bumpmap")
+    cc = Plugin("bsdf", "coating", intIOR=1.5, sigmaA=Spectrum(0.05, 0.1, 0.2))
+    cc.add(Plugin("bsdf", "roughconductor", distribution="beckmann", alpha=0.2, **CU))
+    bm2.add(cc)
+    bt2 = Plugin("texture", "scale", scale=0.02)
+    bt2.add(_tex(7, channels=1))
+    bm2.add(bt2)
+    z["bump_coating_rc"] = bm2
+    cb = Plugin("bsdf", "coating", intIOR=1.5)   # coating over a bump-mapped blend: 3 wrapper levels
+    inner_b = Plugin("bsdf", "blendbsdf", weight=0.6)
+    inner_b.add(Plugin("bsdf", "plastic", intIOR=1.5))
+    inner_b.add(Plugin("bsdf", "roughconductor", distribution="ggx", alpha=0.3, **AL))
+    ib = Plugin("bsdf", "bumpmap")
+    ib.add(inner_b)
+    bt3 = Plugin("texture", "scale", scale=0.03)
+    bt3.add(_tex(8, channels=1))
+    ib.add(bt3)
+    cb.add(ib)
+    z["coating_bump_blend"] = cb
+    return z
+
+
+def zoo_scene(width=64, height=48, spp=4, emitters=("area_rect", "area_sphere", "area_mesh", "point", "envmap")):
+    """Every BSDF on its own sphere + one of each emitter kind + a textured cube and a mesh."""
+    sc = Plugin("scene", "")
+    sc.add(Plugin("integrator", "path", maxDepth=6))
+    s = Plugin("sensor", "perspective", toWorld=hm.look_at([0, 6, 14], [0, 1, 0], [0, 1, 0]), fov=50.0)
+    s.add(Plugin("sampler", "independent", sampleCount=spp))
+    film = Plugin("film", "hdrfilm", width=width, height=height)
+    film.add(Plugin("rfilter", "gaussian"))
+    s.add(film)
+    sc.add(s)
+    z = zoo_bsdfs()
+    names = list(z)
+    for i, nm in enumerate(names):
+        sp = Plugin("shape", "sphere", center=Point((i % 7 - 3) * 2.2, 1.0 + 2.2 * (i // 7), -(i // 7)), radius=1.0)
+        sp.add(z[nm])
+        sc.add(sp)
+    floor = Plugin("shape", "rectangle", toWorld=hm.rotate([1, 0, 0], -90) @ hm.scale([12, 12, 1]))
+    floor.add(z["diffuse_tex"])
+    sc.add(floor)
+    cube = Plugin("shape", "cube", toWorld=hm.translate([5, 0.8, 4]) @ hm.rotate([0, 1, 0], 25) @ hm.scale([0.8, 0.8, 0.8]))
+    cube.add(z["bump_diffuse"])
+    sc.add(cube)
+    pos, idx, nrm, uv = scenes.torus_knot(60, 16)
+    knot = Plugin("shape", "mesh", toWorld=hm.translate([-5, 1.5, 4]))
+    knot.data.update(positions=pos, indices=idx, normals=nrm, texcoords=uv)
+    knot.add(z["rc_ggx"])
+    sc.add(knot)
+    if "area_rect" in emitters:
+        r = Plugin("shape", "rectangle", toWorld=hm.translate([0, 9, 2]) @ hm.rotate([1, 0, 0], 90) @ hm.scale([1.5, 1.0, 1]))
+        r.add(Plugin("emitter", "area", radiance=Spectrum(20, 18, 15)))
+        sc.add(r)
+    if "area_sphere" in emitters:
+        sp = Plugin("shape", "sphere", center=Point(-7, 5, 3), radius=0.5)
+        sp.add(Plugin("emitter", "area", radiance=Spectrum(30, 10, 10), samplingWeight=2.0))
+        sc.add(sp)
+    if "area_mesh" in emitters:
+        cb = Plugin("shape", "cube", toWorld=hm.translate([7, 5, 3]) @ hm.scale([0.4, 0.3, 0.5]))
+        cb.add(Plugin("emitter", "area", radiance=Spectrum(5, 15, 25)))
+        sc.add(cb)
+    if "point" in emitters:
+        sc.add(Plugin("emitter", "point", position=Point(0, 4, 8), intensity=Spectrum(40, 40, 60)))
+    if "envmap" in emitters:
+        env = Plugin("emitter", "envmap", scale=0.7, toWorld=hm.rotate([1, 0, 0], 40.0))
+        env.data["bitmap"] = scenes.synthetic_envmap(128, 64)
+        sc.add(env)
+    return sc, z
+
+
+def make_pair(scene):
+    """(cuda, oracle) CudaPath objects of the same flattened scene."""
+    flat = M.flatten(scene)
+    gpu, cpu = M.CudaPath(flat, backend="cuda"), M.CudaPath(flat, backend="oracle")
+    gpu.preprocess()
+    cpu.preprocess()
+    return gpu, cpu, flat
+
+
+def random_dirs(rng, n, hemisphere=None):
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    if hemisphere == "+":
+        d[:, 2] = np.abs(d[:, 2])
+    return d.astype(F)
+
+
+def rel_err(a, b, floor=1e-6):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return np.abs(a - b) / np.maximum(np.maximum(np.abs(a), np.abs(b)), floor)
