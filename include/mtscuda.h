@@ -203,6 +203,7 @@ typedef struct MtsRenderParams {
     uint32_t seed;
     int32_t clear_film;      /* 1: zero the film first (Scene::render does film->clear()) */
     int32_t wavefront_size;  /* path slots per wavefront; 0 = default */
+    int32_t instrument;      /* 1: count BVH nodes visited / primitives tested (slower; never used for timing) */
 } MtsRenderParams;
 
 typedef struct MtsStats {
@@ -211,8 +212,11 @@ typedef struct MtsStats {
     uint64_t shadow_rays;        /* "Shadow rays traced", src/librender/skdtree.cpp:47 */
     uint64_t path_length_sum;    /* "Average path length" numerator, src/integrators/path/path.cpp:290-291 */
     uint64_t kernel_launches;    /* CUDA kernels launched by this render() */
-    uint64_t bvh_nodes_visited;  /* filled only by instrumented traces */
+    uint64_t bvh_nodes_visited;  /* closest-hit rays; filled only by instrumented runs */
     uint64_t bvh_prims_tested;
+    uint64_t bvh_nodes_visited_shadow; /* shadow rays; instrumented runs only */
+    uint64_t bvh_prims_tested_shadow;
+    uint64_t intersect_launches, shade_launches, shadow_launches, splat_launches;
     float render_ms;             /* device time of the whole render() (CUDA events) */
     float intersect_ms, shade_ms, shadow_ms, splat_ms, raygen_ms;
     float build_ms;              /* BVH build time of the last build() */
@@ -254,6 +258,10 @@ MTS_API int MTS_FN(read_film)(MtsContext *ctx, float *out_rgbw);
 /* Use caller-provided device memory (width*height float4) as the film accumulator, e.g. a torch
  * tensor that is then reduced with NCCL; NULL restores the internal buffer.  CUDA library only. */
 MTS_API int MTS_FN(bind_film)(MtsContext *ctx, void *device_ptr);
+/* Launch everything on a caller-owned CUDA stream (a cudaStream_t passed as void*, e.g. torch's current
+ * stream so that the caller's CUDA events and NCCL calls are ordered with the render); NULL restores the
+ * context's own stream.  CUDA library only. */
+MTS_API int MTS_FN(set_stream)(MtsContext *ctx, void *cuda_stream);
 MTS_API int MTS_FN(get_stats)(MtsContext *ctx, MtsStats *stats);
 
 /* ---- per-function entry points (parity tests bind these; the reference-side equivalents

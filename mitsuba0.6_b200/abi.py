@@ -80,13 +80,16 @@ class RenderParams(C.Structure):
     _fields_ = [("spp", C.c_int32), ("sample_offset", C.c_int32), ("sample_stride", C.c_int32),
                 ("max_depth", C.c_int32), ("rr_depth", C.c_int32), ("strict_normals", C.c_int32),
                 ("hide_emitters", C.c_int32), ("seed", C.c_uint32), ("clear_film", C.c_int32),
-                ("wavefront_size", C.c_int32)]
+                ("wavefront_size", C.c_int32), ("instrument", C.c_int32)]
 
 
 class Stats(C.Structure):
     _fields_ = [("camera_samples", C.c_uint64), ("normal_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("path_length_sum", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("bvh_nodes_visited", C.c_uint64), ("bvh_prims_tested", C.c_uint64),
+                ("bvh_nodes_visited_shadow", C.c_uint64), ("bvh_prims_tested_shadow", C.c_uint64),
+                ("intersect_launches", C.c_uint64), ("shade_launches", C.c_uint64),
+                ("shadow_launches", C.c_uint64), ("splat_launches", C.c_uint64),
                 ("render_ms", C.c_float), ("intersect_ms", C.c_float), ("shade_ms", C.c_float),
                 ("shadow_ms", C.c_float), ("splat_ms", C.c_float), ("raygen_ms", C.c_float),
                 ("build_ms", C.c_float), ("upload_ms", C.c_float)]
@@ -99,7 +102,7 @@ class Stats(C.Structure):
 ABI_SYMBOLS = [
     "last_error", "create", "destroy", "set_camera", "set_film", "add_texture", "set_float_pool",
     "set_bsdfs", "add_mesh", "add_rectangle", "add_sphere", "add_emitter", "build", "render",
-    "read_film", "bind_film", "get_stats", "sample_rays", "trace", "hit_records", "bsdf_eval_pdf",
+    "read_film", "bind_film", "set_stream", "get_stats", "sample_rays", "trace", "hit_records", "bsdf_eval_pdf",
     "bsdf_sample", "sample_emitter_direct", "eval_environment", "splat",
 ]
 
@@ -147,6 +150,7 @@ def load(backend):
         "render": (C.c_int, [vp, C.POINTER(RenderParams), C.POINTER(C.c_int), C.POINTER(Stats)]),
         "read_film": (C.c_int, [vp, fp]),
         "bind_film": (C.c_int, [vp, vp]),
+        "set_stream": (C.c_int, [vp, vp]),
         "get_stats": (C.c_int, [vp, C.POINTER(Stats)]),
         "sample_rays": (C.c_int, [vp, i64, fp, fp]),
         "trace": (C.c_int, [vp, i64, fp, i32, fp, fp]),
@@ -266,6 +270,9 @@ class Context:
 
     def bind_film(self, device_ptr):
         self._check(self.fn["bind_film"](self.h, C.c_void_p(device_ptr)))
+
+    def set_stream(self, cuda_stream):
+        self._check(self.fn["set_stream"](self.h, C.c_void_p(cuda_stream)))
 
     def get_stats(self):
         st = Stats()

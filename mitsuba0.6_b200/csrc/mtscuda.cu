@@ -73,7 +73,7 @@ float hLum(const float *p) { return p[0] * 0.212671f + p[1] * 0.715160f + p[2] *
 
 struct MtsContext {
     int device = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, ownStream = nullptr;
     int numSMs = 148;
     // staged scene
     MtsCamera cam; bool hasCam = false;
@@ -310,7 +310,8 @@ MTS_API int mtscuda_create(int device, MtsContext **out) {
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, device));
     c->numSMs = prop.multiProcessorCount;
-    CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&c->ownStream, cudaStreamNonBlocking));
+    c->stream = c->ownStream;
     *out = c;
     return MTS_OK;
 }
@@ -320,7 +321,7 @@ MTS_API void mtscuda_destroy(MtsContext *c) {
     cudaSetDevice(c->device);
     c->freeScene(); c->freeWavefront();
     if (c->filmInternal) cudaFree(c->filmInternal);
-    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->ownStream) cudaStreamDestroy(c->ownStream);
     delete c;
 }
 
@@ -621,6 +622,13 @@ MTS_API int mtscuda_bind_film(MtsContext *c, void *device_ptr) {
     return MTS_OK;
 }
 
+MTS_API int mtscuda_set_stream(MtsContext *c, void *cuda_stream) {
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->ownStream;
+    return MTS_OK;
+}
+
 MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile const int *cancel, MtsStats *stats) {
     if (!c->built || !c->hasCam || !c->hasFilm) return fail(MTS_ESTATE, "render before build/set_camera/set_film");
     // MonteCarloIntegrator parameter validation (src/librender/integrator.cpp:190-225)
@@ -670,9 +678,15 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
         for (int bounce = 0; active > 0; ++bounce) {
             if (cancel && *cancel) { cancelled = true; break; }
             k_reset_bounce<<<1, 1, 0, st>>>(Wf.ctr, cur ^ 1);
-            begin(1); k_intersect<false><<<gridTrace, 128, 0, st>>>(S, Wf, cur); end();
+            begin(1);
+            if (P->instrument) k_intersect<true><<<gridTrace, 128, 0, st>>>(S, Wf, cur);
+            else k_intersect<false><<<gridTrace, 128, 0, st>>>(S, Wf, cur);
+            end();
             begin(2); k_shade<<<gridShade, 128, 0, st>>>(S, Wf, R, cur); end();
-            begin(3); k_shadow<false><<<gridTrace, 128, 0, st>>>(S, Wf); end();
+            begin(3);
+            if (P->instrument) k_shadow<true><<<gridTrace, 128, 0, st>>>(S, Wf);
+            else k_shadow<false><<<gridTrace, 128, 0, st>>>(S, Wf);
+            end();
             begin(4); k_splat<<<gridWide, 256, 0, st>>>(S, Wf, R); end();
             launches += 5;
             CUDA_TRY(cudaMemcpyAsync(&hc, Wf.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
@@ -696,6 +710,8 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
         float ms = 0; cudaEventElapsedTime(&ms, s.a, s.b);
         float *dst = s.kind == 0 ? &sx.raygen_ms : s.kind == 1 ? &sx.intersect_ms : s.kind == 2 ? &sx.shade_ms : s.kind == 3 ? &sx.shadow_ms : &sx.splat_ms;
         *dst += ms;
+        if (s.kind == 1) sx.intersect_launches++; else if (s.kind == 2) sx.shade_launches++;
+        else if (s.kind == 3) sx.shadow_launches++; else if (s.kind == 4) sx.splat_launches++;
         cudaEventDestroy(s.a); cudaEventDestroy(s.b);
     }
     CUDA_TRY(cudaMemcpy(&hc, Wf.ctr, sizeof(Counters), cudaMemcpyDeviceToHost));
@@ -703,6 +719,8 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
     sx.normal_rays = normalRays; sx.shadow_rays = shadowRays;
     sx.path_length_sum = hc.pathLenSum;
     sx.kernel_launches = launches;
+    sx.bvh_nodes_visited = hc.nodesVisited; sx.bvh_prims_tested = hc.primsTested;
+    sx.bvh_nodes_visited_shadow = hc.nodesVisitedShadow; sx.bvh_prims_tested_shadow = hc.primsTestedShadow;
     if (stats) *stats = sx;
     return cancelled ? fail(MTS_ECANCELLED, "render cancelled") : MTS_OK;
 }

@@ -18,7 +18,8 @@ struct Counters {
     uint32_t shadowCount;
     uint32_t doneCount;
     unsigned long long pathLenSum;
-    unsigned long long nodesVisited, primsTested;  // instrumented traces only
+    unsigned long long nodesVisited, primsTested;  // instrumented traces only (closest hit)
+    unsigned long long nodesVisitedShadow, primsTestedShadow;
 };
 
 struct Wavefront {
@@ -125,7 +126,7 @@ __global__ void __launch_bounds__(128) k_shadow(const DScene S, const Wavefront 
             W.L[slot] = l;
         }
     }
-    if (COUNT) { atomicAdd(&W.ctr->nodesVisited, (unsigned long long)tc.nodes); atomicAdd(&W.ctr->primsTested, (unsigned long long)tc.prims); }
+    if (COUNT) { atomicAdd(&W.ctr->nodesVisitedShadow, (unsigned long long)tc.nodes); atomicAdd(&W.ctr->primsTestedShadow, (unsigned long long)tc.prims); }
 }
 
 // ---- shade: one iteration of the Li loop ----------------------------------------------------
@@ -146,6 +147,9 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
     auto finish = [&]() { W.L[slot] = make_float4(L.x, L.y, L.z, 0); W.meta[slot] = make_uint4(meta.x, meta.y, depth | (flags << 16), 0); };
 
     if (prim < 0) {
+        // the reference bumps rRec.depth only after a valid hit (path.cpp:272-276); `depth` was already
+        // incremented when this ray was queued, so undo that for the path-length statistic
+        if (!first) depth -= 1;
         // path.cpp:136-143 (camera ray) / :238-248,257-264 (BSDF-sampled ray escaping to the envmap)
         if (S.hasEnv) {
             if (first) {

@@ -478,6 +478,7 @@ class FlatScene:
                               % (p.type, ", ".join(SUPPORTED_BSDFS)))
         n = abi.BsdfNode()
         n.child[0] = n.child[1] = -1
+        n.t0.tex = n.t1.tex = n.t2.tex = -1  # unused texture slots
         idx = len(self.nodes)
         self.nodes.append(n)
         self._bsdf_ids[key] = idx

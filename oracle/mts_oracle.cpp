@@ -256,6 +256,8 @@ bool traverse(const MtsContext &c, V3 o, V3 d, float mint, float maxt, bool shad
     return found;
 }
 
+thread_local uint64_t t_normalRays = 0, t_shadowRays = 0;
+
 /* ShapeKDTree::rayIntersect epsilon logic (src/librender/skdtree.cpp:112-142, 207-226).
  * The AABB clip only bounds [mint,maxt]; primitives all lie inside, so it is omitted. */
 bool sceneIntersect(MtsContext &c, V3 o, V3 d, float rmint, float rmaxt, bool shadow, Hit &h) {
@@ -265,7 +267,7 @@ bool sceneIntersect(MtsContext &c, V3 o, V3 d, float rmint, float rmaxt, bool sh
         if (!shadow) m = std::max(m, kEps);
         rayMinT *= m;
     }
-    if (shadow) c.shadowRays.fetch_add(1, std::memory_order_relaxed); else c.normalRays.fetch_add(1, std::memory_order_relaxed);
+    if (shadow) ++t_shadowRays; else ++t_normalRays; /* per-thread; summed after the parallel loop */
     if (!(rmaxt > rayMinT)) return false;
     return traverse(c, o, d, rayMinT, rmaxt, shadow, h);
 }
@@ -903,6 +905,7 @@ MTS_API int mtsoracle_render(MtsContext *c, const MtsRenderParams *P, volatile c
 #endif
         std::vector<float> &buf = tfilm[tid];
         buf.assign((size_t)W * H * 4, 0.0f);
+        t_normalRays = t_shadowRays = 0;
 #pragma omp for schedule(dynamic, 1)
         for (int y = 0; y < H; ++y) {
             if (cancel && *cancel) { cancelled = true; continue; }
@@ -920,8 +923,13 @@ MTS_API int mtsoracle_render(MtsContext *c, const MtsRenderParams *P, volatile c
                 }
             }
         }
+        c->normalRays.fetch_add(t_normalRays); c->shadowRays.fetch_add(t_shadowRays);
+        t_normalRays = t_shadowRays = 0;
     }
-    for (auto &b : tfilm) if (!b.empty()) for (size_t i = 0; i < c->filmBuf.size(); ++i) c->filmBuf[i] += b[i];
+    /* ImageBlock merge (Film::put(block)): per-thread accumulators summed in thread order */
+    const long long nf = (long long)c->filmBuf.size();
+#pragma omp parallel for schedule(static)
+    for (long long i = 0; i < nf; ++i) { float acc = c->filmBuf[i]; for (auto &b : tfilm) if (!b.empty()) acc += b[i]; c->filmBuf[i] = acc; }
     MtsStats &st = c->stats;
     st.camera_samples = (uint64_t)W * H * P->spp;
     st.normal_rays = c->normalRays; st.shadow_rays = c->shadowRays; st.path_length_sum = pathLen;
@@ -932,6 +940,7 @@ MTS_API int mtsoracle_render(MtsContext *c, const MtsRenderParams *P, volatile c
 
 MTS_API int mtsoracle_read_film(MtsContext *c, float *out) { std::memcpy(out, c->filmBuf.data(), c->filmBuf.size() * sizeof(float)); return MTS_OK; }
 MTS_API int mtsoracle_bind_film(MtsContext *, void *) { return fail(MTS_EINVAL, "bind_film: device memory is a CUDA-library concept"); }
+MTS_API int mtsoracle_set_stream(MtsContext *, void *) { return fail(MTS_EINVAL, "set_stream: CUDA streams are a CUDA-library concept"); }
 MTS_API int mtsoracle_get_stats(MtsContext *c, MtsStats *s) { *s = c->stats; return MTS_OK; }
 
 MTS_API int mtsoracle_sample_rays(MtsContext *c, int64_t n, const float *sp, float *out) {
