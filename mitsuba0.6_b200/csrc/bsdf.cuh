@@ -19,7 +19,7 @@ constexpr int kMaxBsdfDepth = 4;  // wrapper nesting levels supported above a le
 DEVFN bool wrapCoord(int &x, int size, int mode, float &constant) {
     if (x < 0 || x >= size) {
         switch (mode) {
-            case MTS_WRAP_REPEAT: x = modulo(x, size); break;
+            case MTS_WRAP_REPEAT: x = wrapRepeat(x, size); break;
             case MTS_WRAP_CLAMP: x = clampi(x, 0, size - 1); break;
             case MTS_WRAP_MIRROR: x = modulo(x, 2 * size); if (x >= size) x = 2 * size - x - 1; break;
             case MTS_WRAP_ZERO: constant = 0.0f; return false;
@@ -273,11 +273,11 @@ DEVFN float cubicInterp2D(float px, float py, const float *values, int sx, int s
 // RoughTransmittance::eval on the host-reduced slices (src/bsdfs/rtrans.h:183-233)
 DEVFN float roughTransmittance(const DScene &S, const MtsBsdfNode &n, float ct, float alpha) {
     if (!(ct >= 0)) return 0.f;
-    float warpedCosTheta = powf(fabsf(ct), 0.25f), result;
+    float warpedCosTheta = sqrtf(sqrtf(fabsf(ct))), result;  // std::pow(x, 0.25)
     const float *tab = S.pool + n.lut[0];
     if (!(n.flags & MTS_BF_RT_2D)) result = cubicInterp1D(warpedCosTheta, tab, n.lut[1]);
     else {
-        float warpedAlpha = powf((alpha - n.f[0]) / (n.f[1] - n.f[0]), 0.25f);
+        float warpedAlpha = sqrtf(sqrtf((alpha - n.f[0]) / (n.f[1] - n.f[0])));
         result = cubicInterp2D(warpedCosTheta, warpedAlpha, tab, n.lut[1], n.lut[2]);
     }
     return fminf(1.0f, fmaxf(0.0f, result));
@@ -285,7 +285,7 @@ DEVFN float roughTransmittance(const DScene &S, const MtsBsdfNode &n, float ct, 
 // 1 - m_internalRoughTransmittance->evalDiffuse(alpha)  (roughplastic.cpp:366, rtrans.h:249-285)
 DEVFN float roughInternalFdr(const DScene &S, const MtsBsdfNode &n, float alpha) {
     if (!(n.flags & MTS_BF_RT_2D)) return n.f[3];
-    float warpedAlpha = powf((alpha - n.f[0]) / (n.f[1] - n.f[0]), 0.25f);
+    float warpedAlpha = sqrtf(sqrtf((alpha - n.f[0]) / (n.f[1] - n.f[0])));
     float r = cubicInterp1D(warpedAlpha, S.pool + n.lut[3], n.lut[2]);
     return 1.0f - fminf(1.0f, fmaxf(0.0f, r));
 }
@@ -540,6 +540,9 @@ struct Surf {
     float2 uv;
     float3 dpdu, dpdv, geoN;
     Frame sh;
+    // one-entry cache of the perturbed frame: eval, pdf and sample of one hit share a single gradient lookup
+    mutable int bumpNode;
+    mutable Frame bumpCache;
 };
 
 // BumpMap::getFrame (src/bsdfs/bumpmap.cpp:135-159)
@@ -555,6 +558,12 @@ DEVFN Frame bumpFrame(const DScene &S, const MtsBsdfNode &n, const Surf &su) {
     r.t = cross(r.n, r.s);
     if (dot(r.n, su.geoN) < 0) r.n = -r.n;
     return r;
+}
+DEVFN Frame bumpFrameCached(const DScene &S, int node, const MtsBsdfNode &n, const Surf &su) {
+    if (su.bumpNode == node) return su.bumpCache;
+    Frame f = bumpFrame(S, n, su);
+    su.bumpNode = node; su.bumpCache = f;
+    return f;
 }
 // SmoothCoating::refractIn / refractOut (src/bsdfs/coating.cpp:208-219)
 DEVFN float3 coatRefractIn(float eta, float3 wi, float &R) {
@@ -592,8 +601,9 @@ template <int D> struct Bsdf {
             return Next::eval(S, n.child[0], su, wi, wo, measure) * (1 - weight) + Next::eval(S, n.child[1], su, wi, wo, measure) * weight;
         }
         case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:161-177
+            Frame bf = bumpFrameCached(S, node, n, su);
             Surf pert = su;
-            pert.sh = bumpFrame(S, n, su);
+            pert.sh = bf; pert.bumpNode = -1;
             float3 wiP = pert.sh.toLocal(su.sh.toWorld(wi)), woP = pert.sh.toLocal(su.sh.toWorld(wo));
             if (cosTheta(wo) * cosTheta(woP) <= 0) return f3(0.0f);
             return Next::eval(S, n.child[0], pert, wiP, woP, measure);
@@ -624,8 +634,9 @@ template <int D> struct Bsdf {
             return Next::pdf(S, n.child[0], su, wi, wo, measure) * (1 - weight) + Next::pdf(S, n.child[1], su, wi, wo, measure) * weight;
         }
         case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:179-197
+            Frame bf = bumpFrameCached(S, node, n, su);
             Surf pert = su;
-            pert.sh = bumpFrame(S, n, su);
+            pert.sh = bf; pert.bumpNode = -1;
             float3 wiP = pert.sh.toLocal(su.sh.toWorld(wi)), woP = pert.sh.toLocal(su.sh.toWorld(wo));
             if (cosTheta(wo) * cosTheta(woP) <= 0) return 0;
             return Next::pdf(S, n.child[0], pert, wiP, woP, measure);
@@ -681,8 +692,9 @@ template <int D> struct Bsdf {
             return result / o.pdf;
         }
         case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:221-240
+            Frame bf = bumpFrameCached(S, node, n, su);
             Surf pert = su;
-            pert.sh = bumpFrame(S, n, su);
+            pert.sh = bf; pert.bumpNode = -1;
             float3 wiP = pert.sh.toLocal(su.sh.toWorld(wi));
             float3 result = Next::sample(S, n.child[0], pert, wiP, sample, o);
             if (!isZero(result)) {

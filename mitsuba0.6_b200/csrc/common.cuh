@@ -65,6 +65,8 @@ DEVFN float safe_acos(float v) { return acosf(fminf(1.0f, fmaxf(-1.0f, v))); }
 DEVFN float signum(float v) { return copysignf(1.0f, v); }
 DEVFN int floorToInt(float v) { return (int)floorf(v); }
 DEVFN int modulo(int a, int b) { int r = a % b; return (r < 0) ? r + b : r; }
+// modulo(x, size) for texture wrapping; power-of-two sizes (the common case) avoid the integer division
+DEVFN int wrapRepeat(int x, int size) { return (size & (size - 1)) == 0 ? (x & (size - 1)) : modulo(x, size); }
 DEVFN int clampi(int v, int lo, int hi) { return min(hi, max(lo, v)); }
 
 // src/libcore/math.cpp:74-87

@@ -104,7 +104,7 @@ DEVFN float shapePdfDirect(const DShape &s, float3 ref, float3 d, float3 n, floa
 
 // ---- EnvironmentMap (src/emitters/envmap.cpp) -------------------------------------------------
 DEVFN float3 envTexel(const DEnvmap &e, int x, int y) {  // repeat-u / clamp-v (:145-146,179)
-    x = modulo(x, e.width); y = clampi(y, 0, e.height - 1);
+    x = wrapRepeat(x, e.width); y = clampi(y, 0, e.height - 1);
     uint2 raw = __ldg(reinterpret_cast<const uint2 *>(e.texels) + (size_t)y * e.width + x);
     float2 fa = __half22float2(*reinterpret_cast<__half2 *>(&raw.x)), fb = __half22float2(*reinterpret_cast<__half2 *>(&raw.y));
     return f3(fa.x, fa.y, fb.x);

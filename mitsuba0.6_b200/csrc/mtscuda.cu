@@ -123,7 +123,8 @@ int bsdfDepth(const std::vector<MtsBsdfNode> &nodes, int i, int guard = 0) {
 }
 
 int ensureWavefront(MtsContext *c, uint32_t cap) {
-    if (c->wfCapacity >= cap) return MTS_OK;
+    const uint32_t numKeys = (uint32_t)c->nodes.size() + 1;
+    if (c->wfCapacity >= cap && c->wf.numKeys == numKeys) return MTS_OK;
     c->freeWavefront();
     Wavefront &w = c->wf;
     auto alloc = [&](void **p, size_t bytes) -> cudaError_t {
@@ -138,6 +139,10 @@ int ensureWavefront(MtsContext *c, uint32_t cap) {
     CUDA_TRY(alloc((void **)&w.shC, sizeof(float4) * cap));
     CUDA_TRY(alloc((void **)&w.queue[0], 4 * (size_t)cap)); CUDA_TRY(alloc((void **)&w.queue[1], 4 * (size_t)cap));
     CUDA_TRY(alloc((void **)&w.doneQ, 4 * (size_t)cap));
+    CUDA_TRY(alloc((void **)&w.keys, 4 * (size_t)cap)); CUDA_TRY(alloc((void **)&w.sorted, 4 * (size_t)cap));
+    CUDA_TRY(alloc((void **)&w.keyCount, 4 * 3 * (size_t)numKeys));
+    CUDA_TRY(cudaMemsetAsync(w.keyCount, 0, 4 * 3 * (size_t)numKeys, c->stream));
+    w.numKeys = numKeys;
     CUDA_TRY(alloc((void **)&w.ctr, sizeof(Counters)));
     w.capacity = cap;
     c->wfCapacity = cap;
@@ -213,6 +218,7 @@ DEVFN Surf surfFromArray(const float *s) {
     float3 n = f3(s[12], s[13], s[14]);
     su.geoN = n;
     su.sh = shadingFrame(n, su.dpdu);
+    su.bumpNode = -1;
     return su;
 }
 __global__ void k_hook_bsdf_eval_pdf(const DScene S, int bsdf, int64_t n, const float *surf, const float *wi, const float *wo,
@@ -653,6 +659,7 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
     const Wavefront &Wf = c->wf;
     if (P->clear_film) CUDA_TRY(cudaMemsetAsync(S.film, 0, sizeof(float4) * (size_t)W * H, st));
     CUDA_TRY(cudaMemsetAsync(Wf.ctr, 0, sizeof(Counters), st));
+    CUDA_TRY(cudaMemsetAsync(Wf.keyCount, 0, 4 * 3 * (size_t)Wf.numKeys, st));
 
     const bool timing = true;
     struct Span { cudaEvent_t a, b; int kind; };
@@ -682,13 +689,17 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
             if (P->instrument) k_intersect<true><<<gridTrace, 128, 0, st>>>(S, Wf, cur);
             else k_intersect<false><<<gridTrace, 128, 0, st>>>(S, Wf, cur);
             end();
-            begin(2); k_shade<<<gridShade, 128, 0, st>>>(S, Wf, R, cur); end();
+            begin(2);
+            k_sort_offsets<<<1, 32, 0, st>>>(Wf);
+            k_sort_scatter<<<gridWide, 256, 0, st>>>(Wf, cur);
+            k_shade<<<gridShade, 128, 0, st>>>(S, Wf, R, cur);
+            end();
             begin(3);
             if (P->instrument) k_shadow<true><<<gridTrace, 128, 0, st>>>(S, Wf);
             else k_shadow<false><<<gridTrace, 128, 0, st>>>(S, Wf);
             end();
             begin(4); k_splat<<<gridWide, 256, 0, st>>>(S, Wf, R); end();
-            launches += 5;
+            launches += 7;
             CUDA_TRY(cudaMemcpyAsync(&hc, Wf.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
             CUDA_TRY(cudaStreamSynchronize(st));
             normalRays += hc.qCount[cur];

@@ -31,6 +31,11 @@ struct Wavefront {
     float4 *shO, *shD, *shC; // shadow ray origin/dir (+mint/maxt), contribution rgb + path slot
     uint32_t *queue[2];
     uint32_t *doneQ;
+    // material sort of the active queue: key 0 = miss, 1 + root BSDF node otherwise
+    uint32_t *keys;          // per queue position, written by intersect
+    uint32_t *sorted;        // queue[cur] reordered by key; what shade consumes
+    uint32_t *keyCount;      // numKeys histogram, then numKeys offsets, then numKeys cursors
+    uint32_t numKeys;
     Counters *ctr;
     uint32_t capacity;
 };
@@ -59,7 +64,7 @@ DEVFN uint32_t warpAppend(uint32_t *counter, bool pred) {
 }
 
 DEVFN Surf surfOf(const Hit &h) {
-    Surf s; s.uv = h.uv; s.dpdu = h.dpdu; s.dpdv = h.dpdv; s.geoN = h.geoN; s.sh = h.sh; return s;
+    Surf s; s.uv = h.uv; s.dpdu = h.dpdu; s.dpdv = h.dpdv; s.geoN = h.geoN; s.sh = h.sh; s.bumpNode = -1; return s;
 }
 
 // ---- raygen: SamplingIntegrator::renderBlock sample loop + sampleRayDifferential -------------
@@ -94,19 +99,72 @@ __global__ void __launch_bounds__(256) k_raygen(const DScene S, const Wavefront 
     }
 }
 
+// Lanes of a warp that hold the same key elect a leader that reserves room for all of them with one atomicAdd.
+// Returns this lane's position (valid only where key != kNoKey).
+constexpr uint32_t kNoKey = 0xffffffffu;
+DEVFN uint32_t keyedAppend(uint32_t *counters, uint32_t key) {
+    unsigned active = __activemask();
+    unsigned peers = __match_any_sync(active, key);
+    if (key == kNoKey) return 0;
+    int lane = threadIdx.x & 31;
+    int leader = __ffs(peers) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counters + key, __popc(peers));
+    base = __shfl_sync(peers, base, leader);
+    return base + __popc(peers & ((1u << lane) - 1));
+}
+
 // ---- intersect: Scene::rayIntersect -> ShapeKDTree::rayIntersect(ray, its) --------------------
+// Also emits the shade sort key of every ray (0 = escaped, 1 + BSDF root of the hit shape) and its histogram.
 template <bool COUNT>
 __global__ void __launch_bounds__(128) k_intersect(const DScene S, const Wavefront W, int qsel) {
     const uint32_t count = W.ctr->qCount[qsel];
+    const uint32_t rounded = (count + 31u) & ~31u;
     TraceCounters tc = {0, 0};
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-        uint32_t slot = W.queue[qsel][i];
-        float4 ro = W.rayO[slot], rd = W.rayD[slot];
-        RayHit h;
-        sceneIntersect<false, COUNT>(S, f3(ro), f3(rd), ro.w, rd.w, h, &tc);
-        W.hit[slot] = make_float4(h.t, h.u, h.v, __int_as_float(h.prim));
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
+        uint32_t key = kNoKey;
+        if (i < count) {
+            uint32_t slot = W.queue[qsel][i];
+            float4 ro = W.rayO[slot], rd = W.rayD[slot];
+            RayHit h;
+            sceneIntersect<false, COUNT>(S, f3(ro), f3(rd), ro.w, rd.w, h, &tc);
+            W.hit[slot] = make_float4(h.t, h.u, h.v, __int_as_float(h.prim));
+            key = 0;
+            if (h.prim >= 0) {
+                int shape = __float_as_int(__ldg(reinterpret_cast<const float4 *>(S.prims + h.prim)).w);
+                key = 1u + (uint32_t)S.shapes[shape].bsdf;
+            }
+            W.keys[i] = key;
+        }
+        keyedAppend(W.keyCount, key);
     }
     if (COUNT) { atomicAdd(&W.ctr->nodesVisited, (unsigned long long)tc.nodes); atomicAdd(&W.ctr->primsTested, (unsigned long long)tc.prims); }
+}
+
+// ---- material sort: counting sort of the active queue by key (histogram from intersect) --------
+__global__ void k_sort_offsets(const Wavefront W) {
+    // one warp; numKeys is small (BSDF nodes + 1)
+    uint32_t *cnt = W.keyCount, *off = W.keyCount + W.numKeys, *cur = W.keyCount + 2 * W.numKeys;
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < W.numKeys; base += 32) {
+        uint32_t k = base + threadIdx.x;
+        uint32_t v = k < W.numKeys ? cnt[k] : 0, incl = v;
+        for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if ((int)threadIdx.x >= o) incl += t; }
+        if (k < W.numKeys) { off[k] = carry + incl - v; cur[k] = 0; cnt[k] = 0; }
+        carry += __shfl_sync(0xffffffffu, incl, 31);
+    }
+}
+__global__ void __launch_bounds__(256) k_sort_scatter(const Wavefront W, int qsel) {
+    const uint32_t count = W.ctr->qCount[qsel];
+    const uint32_t rounded = (count + 31u) & ~31u;
+    const uint32_t *off = W.keyCount + W.numKeys;
+    uint32_t *cur = W.keyCount + 2 * W.numKeys;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
+        uint32_t key = kNoKey, slot = 0;
+        if (i < count) { key = W.keys[i]; slot = W.queue[qsel][i]; }
+        uint32_t pos = keyedAppend(cur, key);
+        if (key != kNoKey) W.sorted[off[key] + pos] = slot;
+    }
 }
 
 // ---- shadow: ShapeKDTree::rayIntersect(ray) for Scene::sampleEmitterDirect --------------------
@@ -257,7 +315,7 @@ __global__ void __launch_bounds__(128) k_shade(const DScene S, const Wavefront W
         ShadeOut out; out.next = out.shadow = out.done = false;
         uint32_t slot = 0;
         if (i < count) {
-            slot = W.queue[qsel][i];
+            slot = W.sorted[i];
             shadePath(S, W, R, slot, out);
         }
         uint32_t a = warpAppend(&W.ctr->qCount[qsel ^ 1], out.next);
