@@ -317,7 +317,7 @@ def run_cuda(args):
         ispp = max(1, min(spp_rank, 4))
         g3.render(spp=ispp, read_back=False, seed=0, instrument=True)
         si = g3.stats
-        node_bytes = 64
+        node_bytes = 80   # one eight-wide compressed node (WideNode, scene.cuh)
         nodes_per_ray = si.bvh_nodes_visited / max(si.normal_rays, 1)
         prims_per_ray = si.bvh_prims_tested / max(si.normal_rays, 1)
         nodes_per_sray = si.bvh_nodes_visited_shadow / max(si.shadow_rays, 1)

@@ -18,7 +18,7 @@
 namespace mts {
 
 constexpr int NB = 16;            // SAH bins per axis
-constexpr int kMaxLeaf = 4;       // primitives per leaf upper bound when the SAH prefers a leaf
+constexpr int kMaxLeaf = 3;       // primitives per leaf (a wide-node leaf child encodes 1..3 in unary)
 constexpr float kCostTrav = 1.0f, kCostIsect = 1.2f;
 
 struct BuildNode {
@@ -243,45 +243,13 @@ __global__ void k_scatter(int n, const uint32_t *__restrict__ idxIn, const int *
     nodeOfOut[dst] = flags[i] ? nd.left : nd.right;
 }
 
-// ---- emission -----------------------------------------------------------------------------
-__global__ void k_inner_flags(int nNodes, const BuildNode *__restrict__ nodes, int *flags) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < nNodes) flags[i] = nodes[i].left >= 0;
-}
-
-__global__ void k_emit_nodes(int nNodes, const BuildNode *__restrict__ nodes, const int *__restrict__ innerIndex, BvhNode *out) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nNodes) return;
-    const BuildNode &nd = nodes[i];
-    if (nd.left < 0) return;
-    const BuildNode &L = nodes[nd.left], &R = nodes[nd.right];
-    BvhNode o;
-    o.a = make_float4(L.lo[0], L.lo[1], L.lo[2], L.hi[0]);
-    o.b = make_float4(L.hi[1], L.hi[2], R.lo[0], R.lo[1]);
-    o.c = make_float4(R.lo[2], R.hi[0], R.hi[1], R.hi[2]);
-    o.link.x = L.left >= 0 ? innerIndex[nd.left] : L.begin;
-    o.link.z = L.left >= 0 ? 0 : (L.end - L.begin);
-    o.link.y = R.left >= 0 ? innerIndex[nd.right] : R.begin;
-    o.link.w = R.left >= 0 ? 0 : (R.end - R.begin);
-    out[innerIndex[i]] = o;
-}
-
-// root is a leaf (tiny scenes): one node whose first child holds everything
-__global__ void k_emit_single(const BuildNode *nodes, BvhNode *out) {
-    const BuildNode &r = nodes[0];
-    BvhNode o;
-    o.a = make_float4(r.lo[0], r.lo[1], r.lo[2], r.hi[0]);
-    o.b = make_float4(r.hi[1], r.hi[2], 0, 0);
-    o.c = make_float4(0, 0, 0, 0);
-    o.link = make_int4(r.begin, -1, r.end - r.begin, 0);
-    out[0] = o;
-}
-
-__global__ void k_emit_prims(int n, const uint32_t *__restrict__ order, const PrimSource *__restrict__ src,
-                             const float *__restrict__ pos, const uint32_t *__restrict__ idx, PrimRecord *out) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    PrimSource s = src[order[i]];
+// ---- collapse: binary tree -> eight-wide compressed nodes ----------------------------------------
+// One thread per wide node, one launch per level of the wide tree.  Wide node k is built from the binary
+// subtree rooted at srcNode[k]: its two children are expanded greedily (largest surface area first) until
+// eight are open or only leaves remain, the children are assigned to octant slots, their boxes are quantised
+// to the 8-bit grid of the node, inner children are appended to the node array (contiguous, slot order) and the
+// primitives of leaf children are appended to the primitive array (contiguous, slot order).
+__device__ __forceinline__ PrimRecord makePrimRecord(const PrimSource &s, const float *__restrict__ pos, const uint32_t *__restrict__ idx) {
     PrimRecord r;
     if (s.type == 0) {
         size_t gt = (size_t)s.triOffset + s.prim;
@@ -297,7 +265,114 @@ __global__ void k_emit_prims(int n, const uint32_t *__restrict__ order, const Pr
         r.p1 = make_float4(0, 0, 0, __int_as_float(0));
         r.p2 = make_float4(0, 0, 0, __int_as_float(s.type));
     }
-    out[i] = r;
+    return r;
+}
+
+// smallest biased exponent e such that the 8-bit grid origin + q * 2^(e-127), q in 0..255, covers [lo, hi]
+__device__ __forceinline__ int gridExponent(float lo, float hi) {
+    float ext = fmaxf(hi - lo, 1e-30f);
+    int e;
+    frexpf(ext / 255.0f, &e);            // ext/255 = m * 2^e, m in [0.5, 1)  ->  2^e >= ext/255
+    e = max(-126, min(127, e));
+    while (e < 127 && lo + 255.0f * __int_as_float((e + 127) << 23) < hi) ++e;   // guard fp rounding
+    return e + 127;
+}
+
+__global__ void k_collapse(int levelStart, int levelEnd, const BuildNode *__restrict__ bn, const uint32_t *__restrict__ order,
+                           int *srcNode, WideNode *out, int *nodeCounter, int *primCounter,
+                           const PrimSource *__restrict__ src, const float *__restrict__ pos, const uint32_t *__restrict__ idx,
+                           PrimRecord *prims) {
+    int k = levelStart + blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= levelEnd) return;
+    const int root = srcNode[k];
+    const BuildNode N = bn[root];
+    int child[8]; int n = 0;
+    if (N.left < 0) { child[0] = root; n = 1; }   // the whole scene is one leaf
+    else {
+        child[0] = N.left; child[1] = N.right; n = 2;
+        while (n < 8) {
+            int best = -1; float bestArea = -1.0f;
+            for (int i = 0; i < n; ++i) {
+                const BuildNode &c = bn[child[i]];
+                if (c.left >= 0) { float a = halfArea(c.lo, c.hi); if (a > bestArea) { bestArea = a; best = i; } }
+            }
+            if (best < 0) break;
+            int c = child[best];
+            child[best] = bn[c].left; child[n++] = bn[c].right;
+        }
+    }
+    // octant slot assignment: greedily take the (child, slot) pair whose centroid offset projects furthest onto the
+    // slot's diagonal direction
+    float cx[8], cy[8], cz[8];
+    const float ncx = 0.5f * (N.lo[0] + N.hi[0]), ncy = 0.5f * (N.lo[1] + N.hi[1]), ncz = 0.5f * (N.lo[2] + N.hi[2]);
+    for (int i = 0; i < n; ++i) {
+        const BuildNode &c = bn[child[i]];
+        cx[i] = 0.5f * (c.lo[0] + c.hi[0]) - ncx; cy[i] = 0.5f * (c.lo[1] + c.hi[1]) - ncy; cz[i] = 0.5f * (c.lo[2] + c.hi[2]) - ncz;
+    }
+    int slotOf[8]; int childIn[8];
+    for (int i = 0; i < 8; ++i) { slotOf[i] = -1; childIn[i] = -1; }
+    for (int it = 0; it < n; ++it) {
+        float bestC = -INFINITY; int bi = -1, bs = -1;
+        for (int i = 0; i < n; ++i) {
+            if (slotOf[i] >= 0) continue;
+            for (int sl = 0; sl < 8; ++sl) {
+                if (childIn[sl] >= 0) continue;
+                float c = ((sl & 1) ? cx[i] : -cx[i]) + ((sl & 2) ? cy[i] : -cy[i]) + ((sl & 4) ? cz[i] : -cz[i]);
+                if (c > bestC) { bestC = c; bi = i; bs = sl; }
+            }
+        }
+        slotOf[bi] = bs; childIn[bs] = bi;
+    }
+    // grid
+    const int ex = gridExponent(N.lo[0], N.hi[0]), ey = gridExponent(N.lo[1], N.hi[1]), ez = gridExponent(N.lo[2], N.hi[2]);
+    const float sx = __int_as_float(ex << 23), sy = __int_as_float(ey << 23), sz = __int_as_float(ez << 23);
+    uint32_t imask = 0; int nInner = 0, nPrims = 0;
+    for (int sl = 0; sl < 8; ++sl) {
+        int i = childIn[sl];
+        if (i < 0) continue;
+        const BuildNode &c = bn[child[i]];
+        if (c.left >= 0) { imask |= 1u << sl; ++nInner; } else nPrims += c.end - c.begin;
+    }
+    const int childBase = nInner ? atomicAdd(nodeCounter, nInner) : 0;
+    const int primBase = nPrims ? atomicAdd(primCounter, nPrims) : 0;
+    uint32_t meta[2] = {0, 0}, q[6][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}};
+    int innerRank = 0, primOff = 0;
+    for (int sl = 0; sl < 8; ++sl) {
+        int i = childIn[sl];
+        const int w = sl >> 2, sh = (sl & 3) * 8;
+        if (i < 0) {   // empty slot: inverted box, never hit
+            for (int a = 0; a < 3; ++a) { q[a][w] |= 255u << sh; }
+            continue;
+        }
+        const BuildNode &c = bn[child[i]];
+        // conservative quantisation: lo rounds down, hi rounds up, then verified in the arithmetic of the traversal
+        const float lo[3] = {N.lo[0], N.lo[1], N.lo[2]}, sc[3] = {sx, sy, sz};
+        for (int a = 0; a < 3; ++a) {
+            int ql = (int)floorf((c.lo[a] - lo[a]) / sc[a]), qh = (int)ceilf((c.hi[a] - lo[a]) / sc[a]);
+            ql = max(0, min(255, ql)); qh = max(0, min(255, qh));
+            while (ql > 0 && lo[a] + (float)ql * sc[a] > c.lo[a]) --ql;
+            while (qh < 255 && lo[a] + (float)qh * sc[a] < c.hi[a]) ++qh;
+            q[a][w] |= (uint32_t)ql << sh; q[3 + a][w] |= (uint32_t)qh << sh;
+        }
+        if (c.left >= 0) {
+            meta[w] |= (uint32_t)((1u << 5) | (24u + sl)) << sh;
+            srcNode[childBase + innerRank] = child[i];
+            ++innerRank;
+        } else {
+            const int cnt = c.end - c.begin;   // 1..3
+            const uint32_t unary = cnt == 1 ? 1u : (cnt == 2 ? 3u : 7u);
+            meta[w] |= (uint32_t)((unary << 5) | (uint32_t)primOff) << sh;
+            for (int j = 0; j < cnt; ++j) prims[primBase + primOff + j] = makePrimRecord(src[order[c.begin + j]], pos, idx);
+            primOff += cnt;
+        }
+    }
+    WideNode o;
+    o.n0 = make_float4(N.lo[0], N.lo[1], N.lo[2], __int_as_float((int)((uint32_t)ex | ((uint32_t)ey << 8) | ((uint32_t)ez << 16) | (imask << 24))));
+    o.n1 = make_uint4((uint32_t)childBase, (uint32_t)primBase, meta[0], meta[1]);
+    o.n2 = make_uint4(q[0][0], q[0][1], q[1][0], q[1][1]);
+    o.n3 = make_uint4(q[2][0], q[2][1], q[3][0], q[3][1]);
+    o.n4 = make_uint4(q[4][0], q[4][1], q[5][0], q[5][1]);
+    out[k] = o;
 }
 
 __global__ void k_fill_tri_sources(uint32_t ntris, uint32_t primOffset, int shape, uint32_t triOffset, PrimSource *src) {
@@ -317,7 +392,7 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
     float4 *pLo = nullptr, *pHi = nullptr; uint32_t *idxA = nullptr, *idxB = nullptr; int *nodeA = nullptr, *nodeB = nullptr;
     BuildNode *nodes = nullptr; int *flags = nullptr, *scan = nullptr, *box = nullptr, *nodeCount = nullptr;
     Bin *bins = nullptr; size_t binCap = 0; void *cubTmp = nullptr; size_t cubBytes = 0;
-    PrimSource *src = nullptr; int *innerIdx = nullptr;
+    PrimSource *src = nullptr; WideNode *wide = nullptr; int *srcNode = nullptr, *primCounter = nullptr;
     int launches = 0;
     if (n == 0) { out.nodes = nullptr; out.prims = nullptr; out.numNodes = 0; return true; }
     {
@@ -383,21 +458,33 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
         if ((size_t)cnt > maxNodes) { err = "BVH build: node overflow"; goto fail; }
     }
     const int nBuild = levelEnd;
-    // compact inner nodes -> traversal nodes
-    k_inner_flags<<<blocks(nBuild), 256, 0, st>>>(nBuild, nodes, flags);
-    CK(cub::DeviceScan::ExclusiveSum(cubTmp, cubBytes, flags, scan, nBuild, st));
-    int lastFlag = 0, lastScan = 0;
-    CK(cudaMemcpyAsync(&lastFlag, flags + nBuild - 1, 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(&lastScan, scan + nBuild - 1, 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    int nInner = lastFlag + lastScan;
-    out.numNodes = nInner > 0 ? nInner : 1;
-    CK(cudaMalloc(&out.nodes, sizeof(BvhNode) * out.numNodes));
-    CK(cudaMalloc(&out.prims, sizeof(PrimRecord) * n));
-    if (nInner > 0) k_emit_nodes<<<blocks(nBuild), 256, 0, st>>>(nBuild, nodes, scan, out.nodes);
-    else k_emit_single<<<1, 1, 0, st>>>(nodes, out.nodes);
-    k_emit_prims<<<blocks(n), 256, 0, st>>>(n, idxA, src, in.positions, in.indices, out.prims);
-    launches += 4;
+    // collapse into eight-wide nodes, level by level (the wide tree of 10M triangles is ~10 levels deep)
+    {
+        const size_t maxWide = (size_t)nBuild / 2 + 2;   // every wide node consumes at least one binary inner node
+        CK(cudaMalloc(&wide, sizeof(WideNode) * maxWide));
+        CK(cudaMalloc(&srcNode, 4 * maxWide));
+        CK(cudaMalloc(&primCounter, 4));
+        CK(cudaMalloc(&out.prims, sizeof(PrimRecord) * n));
+        int zero = 0, one = 1;
+        CK(cudaMemcpyAsync(srcNode, &zero, 4, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(primCounter, &zero, 4, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(nodeCount, &one, 4, cudaMemcpyHostToDevice, st));
+        int ws = 0, we = 1;
+        while (ws < we) {
+            k_collapse<<<blocks(we - ws, 64), 64, 0, st>>>(ws, we, nodes, idxA, srcNode, wide, nodeCount, primCounter, src,
+                                                         in.positions, in.indices, out.prims);
+            ++launches;
+            int cnt = 0;
+            CK(cudaMemcpyAsync(&cnt, nodeCount, 4, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            if ((size_t)cnt > maxWide) { err = "BVH collapse: node overflow"; goto fail; }
+            ws = we; we = cnt;
+        }
+        out.numNodes = we;
+        CK(cudaMalloc(&out.nodes, sizeof(WideNode) * (size_t)we));
+        CK(cudaMemcpyAsync(out.nodes, wide, sizeof(WideNode) * (size_t)we, cudaMemcpyDeviceToDevice, st));
+        CK(cudaStreamSynchronize(st));
+    }
     BuildNode root;
     CK(cudaMemcpyAsync(&root, nodes, sizeof(root), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
@@ -407,11 +494,11 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
     out.buildNodes = nBuild;
     }
     cudaFree(pLo); cudaFree(pHi); cudaFree(idxA); cudaFree(idxB); cudaFree(nodeA); cudaFree(nodeB); cudaFree(nodes);
-    cudaFree(flags); cudaFree(scan); cudaFree(box); cudaFree(nodeCount); cudaFree(bins); cudaFree(cubTmp); cudaFree(src); cudaFree(innerIdx);
+    cudaFree(flags); cudaFree(scan); cudaFree(box); cudaFree(nodeCount); cudaFree(bins); cudaFree(cubTmp); cudaFree(src); cudaFree(wide); cudaFree(srcNode); cudaFree(primCounter);
     return true;
 fail:
     cudaFree(pLo); cudaFree(pHi); cudaFree(idxA); cudaFree(idxB); cudaFree(nodeA); cudaFree(nodeB); cudaFree(nodes);
-    cudaFree(flags); cudaFree(scan); cudaFree(box); cudaFree(nodeCount); cudaFree(bins); cudaFree(cubTmp); cudaFree(src); cudaFree(innerIdx);
+    cudaFree(flags); cudaFree(scan); cudaFree(box); cudaFree(nodeCount); cudaFree(bins); cudaFree(cubTmp); cudaFree(src); cudaFree(wide); cudaFree(srcNode); cudaFree(primCounter);
     if (out.nodes) cudaFree(out.nodes);
     if (out.prims) cudaFree(out.prims);
     out = BvhBuildOutput();

@@ -20,8 +20,8 @@ struct BvhBuildInput {
 };
 
 struct BvhBuildOutput {
-    BvhNode *nodes = nullptr;     // device; caller frees with cudaFree
-    PrimRecord *prims = nullptr;  // device, leaf order
+    WideNode *nodes = nullptr;    // device; caller frees with cudaFree
+    PrimRecord *prims = nullptr;  // device, in wide-node leaf order
     int numNodes = 0;
     int buildNodes = 0;
     int launches = 0;

@@ -63,66 +63,49 @@ DEVFN bool primIntersect(const DScene &S, int slot, float3 o, float3 d, float mi
     return ok;
 }
 
-DEVFN float2 slab(float lox, float loy, float loz, float hix, float hiy, float hiz, float3 o, float3 inv, float tmin, float tmax) {
-    float tx0 = (lox - o.x) * inv.x, tx1 = (hix - o.x) * inv.x;
-    float ty0 = (loy - o.y) * inv.y, ty1 = (hiy - o.y) * inv.y;
-    float tz0 = (loz - o.z) * inv.z, tz1 = (hiz - o.z) * inv.z;
-    float tn = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fmaxf(fminf(tz0, tz1), tmin));
-    float tf = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fminf(fmaxf(tz0, tz1), tmax));
-    return make_float2(tn, tf);
-}
-
 struct TraceCounters { unsigned nodes, prims; };
 
-// Stack-based while-while traversal of the two-wide BVH.  ANY = shadow ray (first hit terminates).
-// The 1.0000004 slack on the far distance keeps boundary hits from being culled by the box test.
-template <bool ANY, bool COUNT>
-DEVFN bool traverse(const DScene &S, float3 o, float3 d, float mint, float maxt, RayHit &best, TraceCounters *ctr) {
-    best.prim = -1; best.t = maxt;
-    float3 inv = f3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-    int stack[64];
-    int sp = 0;
-    int node = 0;
-    while (true) {
-        const float4 *np = reinterpret_cast<const float4 *>(S.bvh + node);
-        float4 a = __ldg(np), b = __ldg(np + 1), c = __ldg(np + 2);
-        int4 link = __ldg(reinterpret_cast<const int4 *>(np + 3));
-        if (COUNT) ctr->nodes++;
-        float2 t0 = slab(a.x, a.y, a.z, a.w, b.x, b.y, o, inv, mint, best.t);
-        float2 t1 = slab(b.z, b.w, c.x, c.y, c.z, c.w, o, inv, mint, best.t);
-        bool h0 = t0.x <= t0.y * 1.0000004f, h1 = t1.x <= t1.y * 1.0000004f;
-        int next = -1;
-        // leaves are intersected immediately, inner children are ordered near-first
+DEVFN uint32_t byteOf(uint32_t v, int j) { return (v >> (8 * j)) & 0xffu; }
+// float(byte j of v), exact, without an I2F: the byte is spliced into the mantissa of 2^23 and 2^23 is subtracted
+DEVFN float byteToFloat(uint32_t v, int j) { return __uint_as_float(__byte_perm(v, 0x4B000000u, 0x7540u + j)) - 8388608.0f; }
+
+// Intersects the ray with the eight quantised child boxes of one wide node and returns the hit mask:
+// bits 24..31 = inner children ordered front to back (bit 24 + (slot ^ oct)), bits 0..23 = primitives of the
+// leaf children that were hit (offsets from the node's first primitive).
+DEVFN uint32_t wideNodeHits(const float4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
+                            float3 o, float3 idir, uint32_t oct, float tmin, float tmax) {
+    const uint32_t ew = (uint32_t)__float_as_int(n0.w);
+    const float sx = __int_as_float((int)((ew & 0xffu) << 23)), sy = __int_as_float((int)(((ew >> 8) & 0xffu) << 23)),
+                sz = __int_as_float((int)(((ew >> 16) & 0xffu) << 23));
+    const float ax = sx * idir.x, ay = sy * idir.y, az = sz * idir.z;
+    const float bx = (n0.x - o.x) * idir.x, by = (n0.y - o.y) * idir.y, bz = (n0.z - o.z) * idir.z;
+    const uint32_t oct4 = oct * 0x01010101u;
+    const float tmaxS = tmax * 1.0000004f;   // slack: boundary hits are never culled by the box test
+    uint32_t hitmask = 0;
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            bool hk = k ? h1 : h0;
-            int cnt = k ? link.w : link.z;
-            int first = k ? link.y : link.x;
-            if (hk && cnt > 0) {
-                for (int i = first; i < first + cnt; ++i) {
-                    if (COUNT) ctr->prims++;
-                    RayHit h;
-                    if (primIntersect(S, i, o, d, mint, best.t, h)) {
-                        if (ANY) { best = h; return true; }
-                        if (h.t < best.t || best.prim < 0) best = h;
-                    }
-                }
-            }
+    for (int half = 0; half < 2; ++half) {
+        const uint32_t meta4 = half ? n1.w : n1.z;
+        const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t innerMask4 = (isInner4 >> 4) * 0xffu;
+        const uint32_t bitIndex4 = (meta4 ^ (oct4 & innerMask4)) & 0x1f1f1f1fu;
+        const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
+        const uint32_t qlox = half ? n2.y : n2.x, qloy = half ? n2.w : n2.z, qloz = half ? n3.y : n3.x;
+        const uint32_t qhix = half ? n3.w : n3.z, qhiy = half ? n4.y : n4.x, qhiz = half ? n4.w : n4.z;
+        // the plane the ray enters through depends on the sign of the direction
+        const uint32_t nx = idir.x < 0 ? qhix : qlox, fx = idir.x < 0 ? qlox : qhix;
+        const uint32_t ny = idir.y < 0 ? qhiy : qloy, fy = idir.y < 0 ? qloy : qhiy;
+        const uint32_t nz = idir.z < 0 ? qhiz : qloz, fz = idir.z < 0 ? qloz : qhiz;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float t0x = fmaf(byteToFloat(nx, j), ax, bx), t1x = fmaf(byteToFloat(fx, j), ax, bx);
+            float t0y = fmaf(byteToFloat(ny, j), ay, by), t1y = fmaf(byteToFloat(fy, j), ay, by);
+            float t0z = fmaf(byteToFloat(nz, j), az, bz), t1z = fmaf(byteToFloat(fz, j), az, bz);
+            float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
+            float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmaxS));
+            if (cmin <= cmax) hitmask |= byteOf(childBits4, j) << byteOf(bitIndex4, j);
         }
-        bool in0 = h0 && link.z == 0 && link.x >= 0, in1 = h1 && link.w == 0 && link.y >= 0;  // link < 0: empty child
-        if (in0 && in1) {
-            bool firstIs0 = t0.x <= t1.x;
-            next = firstIs0 ? link.x : link.y;
-            if (sp < 64) stack[sp++] = firstIs0 ? link.y : link.x;
-        } else if (in0) next = link.x;
-        else if (in1) next = link.y;
-        if (next < 0) {
-            if (sp == 0) break;
-            next = stack[--sp];
-        }
-        node = next;
     }
-    return best.prim >= 0;
+    return hitmask;
 }
 
 // ShapeKDTree::rayIntersect epsilon handling (src/librender/skdtree.cpp:112-142 closest hit,
@@ -136,12 +119,80 @@ DEVFN float adaptiveMinT(float3 o, float mint, bool shadow) {
     }
     return mint;
 }
+
+// Stack-based traversal of the eight-wide compressed BVH, one ray per thread, as a resumable state machine so
+// that the queue kernels can refill idle lanes of a warp between steps.  The state is a node group (first
+// child index + pending front-to-back hit bits + inner mask); groups that still hold work are pushed when a
+// nearer child is entered.  ANY = shadow ray (the first hit terminates).
+template <bool ANY, bool COUNT>
+struct Traversal {
+    float3 o, d, idir;
+    float mint;
+    uint32_t oct;
+    RayHit best;
+    uint2 ngroup;
+    int sp;
+    uint2 stack[32];
+
+    // returns false when the ray is finished before it starts (empty scene / empty interval)
+    DEVFN bool init(const DScene &S, float3 o_, float3 d_, float rayMinT, float rayMaxT) {
+        o = o_; d = d_;
+        mint = adaptiveMinT(o, rayMinT, ANY);
+        best.prim = -1; best.t = rayMaxT; best.u = best.v = 0;
+        if (S.numPrims == 0 || !(rayMaxT > mint)) { best.t = kInf; return false; }
+        const float tiny = 1e-30f;
+        idir = f3(1.0f / (fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x)),
+                  1.0f / (fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y)),
+                  1.0f / (fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z)));
+        oct = (idir.x >= 0 ? 1u : 0u) | (idir.y >= 0 ? 2u : 0u) | (idir.z >= 0 ? 4u : 0u);
+        sp = 0;
+        ngroup = make_uint2(0u, 0x80000000u);
+        return true;
+    }
+
+    // one node visit + the primitive tests it produced; returns true when the traversal has finished
+    DEVFN bool step(const DScene &S, TraceCounters *ctr) {
+        // enter the nearest pending inner child of the current node group
+        const int bit = 31 - __clz((int)ngroup.y);
+        ngroup.y &= ~(1u << bit);
+        const uint32_t slot = (uint32_t)(bit - 24) ^ oct;
+        const uint32_t rel = __popc(ngroup.y & 0xffu & ~(0xffffffffu << slot));
+        const uint32_t nodeIdx = ngroup.x + rel;
+        if ((ngroup.y & 0xff000000u) && sp < 32) stack[sp++] = ngroup;
+        const float4 *np = reinterpret_cast<const float4 *>(S.bvh + nodeIdx);
+        const float4 n0 = __ldg(np);
+        const uint4 n1 = __ldg(reinterpret_cast<const uint4 *>(np + 1)), n2 = __ldg(reinterpret_cast<const uint4 *>(np + 2)),
+                    n3 = __ldg(reinterpret_cast<const uint4 *>(np + 3)), n4 = __ldg(reinterpret_cast<const uint4 *>(np + 4));
+        if (COUNT) ctr->nodes++;
+        const uint32_t hits = wideNodeHits(n0, n1, n2, n3, n4, o, idir, oct, mint, best.t);
+        ngroup = make_uint2(n1.x, (hits & 0xff000000u) | ((uint32_t)__float_as_int(n0.w) >> 24));
+        uint32_t pending = hits & 0x00ffffffu;
+        while (pending) {
+            const int j = __ffs((int)pending) - 1;
+            pending &= pending - 1;
+            if (COUNT) ctr->prims++;
+            RayHit h;
+            if (primIntersect(S, (int)(n1.y + j), o, d, mint, best.t, h)) {
+                if (ANY) { best = h; return true; }
+                if (h.t < best.t || best.prim < 0) best = h;
+            }
+        }
+        if ((ngroup.y & 0xff000000u) == 0) {
+            if (sp == 0) return true;
+            ngroup = stack[--sp];
+        }
+        return false;
+    }
+    DEVFN bool hit() const { return best.prim >= 0; }
+    DEVFN RayHit result() const { RayHit r = best; if (r.prim < 0) { r.t = kInf; r.u = r.v = 0; } return r; }
+};
+
 template <bool ANY, bool COUNT>
 DEVFN bool sceneIntersect(const DScene &S, float3 o, float3 d, float mint, float maxt, RayHit &h, TraceCounters *ctr = nullptr) {
-    float rayMinT = adaptiveMinT(o, mint, ANY);
-    h.prim = -1; h.t = kInf; h.u = h.v = 0;
-    if (S.numPrims == 0 || !(maxt > rayMinT)) return false;
-    return traverse<ANY, COUNT>(S, o, d, rayMinT, maxt, h, ctr);
+    Traversal<ANY, COUNT> tr;
+    if (tr.init(S, o, d, mint, maxt)) while (!tr.step(S, ctr)) { }
+    h = tr.result();
+    return tr.hit();
 }
 
 DEVFN float3 loadF3(const float *base, uint32_t i) {

@@ -45,12 +45,19 @@ struct DEnvmap {
     float prob;
 };
 
-// Two-wide BVH node, 64 bytes: both child boxes + child links (4 x float4 loads per visit).
-struct BvhNode {
-    float4 a;  // lo0.xyz, hi0.x
-    float4 b;  // hi0.yz, lo1.xy
-    float4 c;  // lo1.z, hi1.xyz
-    int4 link; // child0, child1 (node index, or first primitive when count > 0), count0, count1
+// Eight-wide BVH node with quantised child boxes, 80 bytes = five 16-byte loads per visit (the layout of
+// Ylitie, Karras, Laine: "Efficient Incoherent Ray Traversal on GPUs Through Compressed Wide BVHs", HPG 2017).
+//   n0   origin p.xyz of the node box; w = ex | ey << 8 | ez << 16 | imask << 24
+//        (e* = biased exponents of the per-axis grid scale 2^e, imask bit s = slot s holds an inner node)
+//   n1   x = index of the first child node, y = slot of the first primitive of the leaf children,
+//        z,w = meta[0..3], meta[4..7]: inner child in slot s -> 001 | (24 + s); leaf -> unary prim count (1..3) in
+//        the top three bits | offset from n1.y in the low five; empty slot -> 0
+//   n2   qlo.x[0..7], qlo.y[0..7]   n3   qlo.z[0..7], qhi.x[0..7]   n4   qhi.y[0..7], qhi.z[0..7]   (one byte per slot)
+// Slot s lies towards (s&1 ? +x : -x, s&2 ? +y : -y, s&4 ? +z : -z) of the node centre, so that slot ^ rayOctant
+// orders the children front to back without sorting.
+struct WideNode {
+    float4 n0;
+    uint4 n1, n2, n3, n4;
 };
 
 // 48-byte primitive record in leaf order.
@@ -71,7 +78,7 @@ struct DScene {
     const uint32_t *indices;  // 3 / triangle, already offset into the global vertex arrays
     const float *tangents;    // 6 floats / triangle
     const float *areaCdfs;
-    const BvhNode *bvh; const PrimRecord *prims; int numPrims;
+    const WideNode *bvh; const PrimRecord *prims; int numPrims;
     // emitters
     const DEmitter *emitters; const float *emitterCdf; int numEmitters;
     DEnvmap env; int hasEnv;

@@ -17,6 +17,7 @@ struct Counters {
     uint32_t qCount[2];     // active queue sizes (ping-pong)
     uint32_t shadowCount;
     uint32_t doneCount;
+    uint32_t cursor[2];     // next unclaimed ray of the intersect / shadow queue (persistent warps pull from these)
     unsigned long long pathLenSum;
     unsigned long long nodesVisited, primsTested;  // instrumented traces only (closest hit)
     unsigned long long nodesVisitedShadow, primsTestedShadow;
@@ -114,31 +115,93 @@ DEVFN uint32_t keyedAppend(uint32_t *counters, uint32_t key) {
     return base + __popc(peers & ((1u << lane) - 1));
 }
 
+// ---- persistent-warp ray queue driver -----------------------------------------------------------
+// Every warp keeps 32 traversals in flight: lanes whose ray has finished pull the next ray index from a global
+// cursor (one atomicAdd per warp) as soon as fewer than kRefillBelow lanes are still busy, instead of idling
+// until the slowest ray of the warp is done.  LOAD(i, traversal) starts ray i, DONE(i, traversal) consumes it.
+constexpr int kRefillBelow = 24;
+
+template <bool ANY, bool COUNT, class Load, class Done>
+DEVFN void traceQueue(const DScene &S, uint32_t count, uint32_t *cursor, TraceCounters *tc, Load load, Done done) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    Traversal<ANY, COUNT> tr;
+    uint32_t item = 0;
+    bool busy = false, exhausted = false;
+    while (true) {
+        if (!exhausted) {
+            // refill idle lanes
+            const unsigned idle = __ballot_sync(full, !busy);
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(cursor, (uint32_t)__popc(idle));
+            base = __shfl_sync(full, base, 0);
+            if (!busy) {
+                item = base + __popc(idle & ((1u << lane) - 1));
+                if (item < count) {
+                    busy = load(item, tr);
+                    if (!busy) done(item, tr);   // finished before it started (empty interval)
+                }
+            }
+            exhausted = base + __popc(idle) >= count;
+        }
+        unsigned active = __ballot_sync(full, busy);
+        if (!active) { if (exhausted) break; else continue; }
+        // traverse until too few lanes are busy (and there is more work to fetch)
+        do {
+            if (busy && tr.step(S, tc)) { done(item, tr); busy = false; }
+            active = __ballot_sync(full, busy);
+        } while (active && (exhausted || __popc(active) >= kRefillBelow));
+    }
+}
+
 // ---- intersect: Scene::rayIntersect -> ShapeKDTree::rayIntersect(ray, its) --------------------
 // Also emits the shade sort key of every ray (0 = escaped, 1 + BSDF root of the hit shape) and its histogram.
 template <bool COUNT>
 __global__ void __launch_bounds__(128) k_intersect(const DScene S, const Wavefront W, int qsel) {
     const uint32_t count = W.ctr->qCount[qsel];
-    const uint32_t rounded = (count + 31u) & ~31u;
     TraceCounters tc = {0, 0};
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
-        uint32_t key = kNoKey;
-        if (i < count) {
-            uint32_t slot = W.queue[qsel][i];
+    const uint32_t *queue = W.queue[qsel];
+    traceQueue<false, COUNT>(S, count, &W.ctr->cursor[0], &tc,
+        [&](uint32_t i, Traversal<false, COUNT> &tr) {
+            uint32_t slot = queue[i];
             float4 ro = W.rayO[slot], rd = W.rayD[slot];
-            RayHit h;
-            sceneIntersect<false, COUNT>(S, f3(ro), f3(rd), ro.w, rd.w, h, &tc);
+            return tr.init(S, f3(ro), f3(rd), ro.w, rd.w);
+        },
+        [&](uint32_t i, const Traversal<false, COUNT> &tr) {
+            uint32_t slot = queue[i];
+            RayHit h = tr.result();
             W.hit[slot] = make_float4(h.t, h.u, h.v, __int_as_float(h.prim));
-            key = 0;
+            uint32_t key = 0;
             if (h.prim >= 0) {
                 int shape = __float_as_int(__ldg(reinterpret_cast<const float4 *>(S.prims + h.prim)).w);
                 key = 1u + (uint32_t)S.shapes[shape].bsdf;
             }
             W.keys[i] = key;
-        }
-        keyedAppend(W.keyCount, key);
-    }
+            keyedAppend(W.keyCount, key);   // lanes finishing in the same step share one atomicAdd per key
+        });
     if (COUNT) { atomicAdd(&W.ctr->nodesVisited, (unsigned long long)tc.nodes); atomicAdd(&W.ctr->primsTested, (unsigned long long)tc.prims); }
+}
+
+// ---- shadow: ShapeKDTree::rayIntersect(ray) for Scene::sampleEmitterDirect --------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_shadow(const DScene S, const Wavefront W) {
+    const uint32_t count = W.ctr->shadowCount;
+    TraceCounters tc = {0, 0};
+    traceQueue<true, COUNT>(S, count, &W.ctr->cursor[1], &tc,
+        [&](uint32_t i, Traversal<true, COUNT> &tr) {
+            float4 ro = W.shO[i], rd = W.shD[i];
+            return tr.init(S, f3(ro), f3(rd), ro.w, rd.w);
+        },
+        [&](uint32_t i, const Traversal<true, COUNT> &tr) {
+            if (!tr.hit()) {
+                float4 c = W.shC[i];
+                uint32_t slot = (uint32_t)__float_as_int(c.w);
+                float4 l = W.L[slot];
+                l.x += c.x; l.y += c.y; l.z += c.z;
+                W.L[slot] = l;
+            }
+        });
+    if (COUNT) { atomicAdd(&W.ctr->nodesVisitedShadow, (unsigned long long)tc.nodes); atomicAdd(&W.ctr->primsTestedShadow, (unsigned long long)tc.prims); }
 }
 
 // ---- material sort: counting sort of the active queue by key (histogram from intersect) --------
@@ -165,26 +228,6 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const Wavefront W, int qse
         uint32_t pos = keyedAppend(cur, key);
         if (key != kNoKey) W.sorted[off[key] + pos] = slot;
     }
-}
-
-// ---- shadow: ShapeKDTree::rayIntersect(ray) for Scene::sampleEmitterDirect --------------------
-template <bool COUNT>
-__global__ void __launch_bounds__(128) k_shadow(const DScene S, const Wavefront W) {
-    const uint32_t count = W.ctr->shadowCount;
-    TraceCounters tc = {0, 0};
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-        float4 ro = W.shO[i], rd = W.shD[i];
-        RayHit h;
-        bool occluded = sceneIntersect<true, COUNT>(S, f3(ro), f3(rd), ro.w, rd.w, h, &tc);
-        if (!occluded) {
-            float4 c = W.shC[i];
-            uint32_t slot = (uint32_t)__float_as_int(c.w);
-            float4 l = W.L[slot];
-            l.x += c.x; l.y += c.y; l.z += c.z;
-            W.L[slot] = l;
-        }
-    }
-    if (COUNT) { atomicAdd(&W.ctr->nodesVisitedShadow, (unsigned long long)tc.nodes); atomicAdd(&W.ctr->primsTestedShadow, (unsigned long long)tc.prims); }
 }
 
 // ---- shade: one iteration of the Li loop ----------------------------------------------------
@@ -369,7 +412,7 @@ __global__ void __launch_bounds__(256) k_splat(const DScene S, const Wavefront W
 }
 
 __global__ void k_reset_bounce(Counters *c, int nextSel) {
-    c->qCount[nextSel] = 0; c->shadowCount = 0; c->doneCount = 0;
+    c->qCount[nextSel] = 0; c->shadowCount = 0; c->doneCount = 0; c->cursor[0] = c->cursor[1] = 0;
 }
 
 } // namespace mts

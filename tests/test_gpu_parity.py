@@ -48,16 +48,24 @@ def check_trace(gpu, cpu, rays):
     hc, ic = cpu.ctx.trace(rays)
     hit_g, hit_c = np.isfinite(hg[:, 0]), np.isfinite(hc[:, 0])
     same = (hit_g == hit_c) & (ig == ic).all(axis=1)
-    # non-grazing agreement must be exact; disagreements may only come from rays that graze an edge /
-    # silhouette (different but equally valid triangle tests: Wald projection vs Moeller-Trumbore)
+    # Non-grazing agreement must be exact.  A disagreement is excused only if it is (a) a tie -- both sides hit at the
+    # same distance (coincident surfaces, shared edges: which primitive "wins" is arbitrary in the reference too) -- or
+    # (b) grazing -- the ORACLE ITSELF gives the GPU's answer when the direction is perturbed by 1e-4 (the ray runs
+    # along an edge / silhouette; Wald's projection test and Moeller-Trumbore are equally valid there).
     bad = np.nonzero(~same)[0]
-    frac = len(bad) / len(rays)
-    assert frac < 2e-4, "hit/prim-id mismatch on %d of %d rays" % (len(bad), len(rays))
-    for i in bad[:50]:
-        # grazing: the two candidate hits are (nearly) at the same distance or the barycentrics sit on an edge
-        ts = [t for t in (hg[i, 0], hc[i, 0]) if np.isfinite(t)]
-        edge = min(abs(hg[i, 1]), abs(hg[i, 2]), abs(1 - hg[i, 1] - hg[i, 2]), abs(hc[i, 1]), abs(hc[i, 2]), abs(1 - hc[i, 1] - hc[i, 2]))
-        assert len(ts) < 2 or abs(ts[0] - ts[1]) < 1e-3 * max(1, ts[0]) or edge < 1e-3, (i, hg[i], hc[i], ig[i], ic[i])
+    assert len(bad) / len(rays) < 1e-3, "hit/prim-id mismatch on %d of %d rays" % (len(bad), len(rays))
+    if len(bad):
+        tie = hit_g[bad] & hit_c[bad] & (np.abs(hg[bad, 0] - hc[bad, 0]) <= 1e-4 * np.maximum(1, hc[bad, 0]))
+        rest = bad[~tie]
+        excused = np.zeros(len(rest), dtype=bool)
+        jr = np.random.RandomState(len(rays))
+        for _ in range(16):
+            jit = rays[rest].copy()
+            jit[:, 4:7] += jr.normal(scale=1e-4, size=(len(rest), 3)).astype(F)
+            jit[:, 4:7] /= np.linalg.norm(jit[:, 4:7], axis=1, keepdims=True)
+            _, ij = cpu.ctx.trace(jit)
+            excused |= (ij == ig[rest]).all(axis=1)
+        assert excused.all(), ("non-grazing intersection mismatch", rays[rest[~excused]][:5], ig[rest[~excused]][:5], ic[rest[~excused]][:5])
     ok = same & hit_g
     assert np.all(np.abs(hg[ok, 0] - hc[ok, 0]) <= 1e-4 * np.maximum(1, hc[ok, 0]))
     tri = ok & (np.abs(hc[:, 1:3]).sum(1) > 0)
