@@ -106,23 +106,52 @@ __global__ void k_clear_bins(Bin *bins, size_t n) {
 }
 
 // ---- per level ------------------------------------------------------------------------------
-__global__ void k_bin(int n, const uint32_t *__restrict__ idx, const int *__restrict__ nodeOf,
+// Every block bins a contiguous chunk of the (node-partitioned) primitive order.  A node's primitives are
+// contiguous, so when the first and last primitive of the chunk belong to the same open node the whole chunk does:
+// it is then binned in shared memory and flushed with one global atomic per non-empty bin entry, which removes the
+// same-address contention of the top levels (all 10^7 primitives in a handful of nodes).  Mixed chunks (deep
+// levels, many small nodes) use global atomics directly.
+constexpr int kBinChunk = 2048;
+__global__ void __launch_bounds__(256) k_bin(int n, const uint32_t *__restrict__ idx, const int *__restrict__ nodeOf,
                       const float4 *__restrict__ pLo, const float4 *__restrict__ pHi,
                       const BuildNode *__restrict__ nodes, int levelStart, Bin *bins) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    int node = nodeOf[i];
-    if (node < levelStart) return;  // finished (leaf) or not part of this level
-    const BuildNode &nd = nodes[node];
-    uint32_t p = idx[i];
-    float4 l = pLo[p], h = pHi[p];
-    float c[3] = {0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z)};
-    int ol[3] = {ordF(l.x), ordF(l.y), ordF(l.z)}, oh[3] = {ordF(h.x), ordF(h.y), ordF(h.z)};
-    Bin *nb = bins + (size_t)(node - levelStart) * 3 * NB;
-    for (int a = 0; a < 3; ++a) {
-        Bin *b = nb + a * NB + binOf(c[a], nd.clo[a], nd.chi[a]);
-        atomicAdd(&b->count, 1);
-        for (int k = 0; k < 3; ++k) { atomicMin(&b->lo[k], ol[k]); atomicMax(&b->hi[k], oh[k]); }
+    __shared__ Bin sbin[3 * NB];
+    const int c0 = blockIdx.x * kBinChunk, c1 = min(n, c0 + kBinChunk);
+    if (c0 >= n) return;
+    const int nodeFirst = nodeOf[c0], nodeLast = nodeOf[c1 - 1];
+    const bool uniform = nodeFirst == nodeLast && nodeFirst >= levelStart;   // finished leaves all read -1
+    if (uniform) {
+        for (int i = threadIdx.x; i < 3 * NB; i += blockDim.x) {
+            Bin b; b.count = 0;
+            for (int a = 0; a < 3; ++a) { b.lo[a] = 0x7fffffff; b.hi[a] = (int)0x80000000; }
+            sbin[i] = b;
+        }
+        __syncthreads();
+    }
+    for (int i = c0 + threadIdx.x; i < c1; i += blockDim.x) {
+        int node = uniform ? nodeFirst : nodeOf[i];
+        if (node < levelStart) continue;  // finished (leaf) or not part of this level
+        const BuildNode &nd = nodes[node];
+        uint32_t p = idx[i];
+        float4 l = pLo[p], h = pHi[p];
+        float c[3] = {0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z)};
+        int ol[3] = {ordF(l.x), ordF(l.y), ordF(l.z)}, oh[3] = {ordF(h.x), ordF(h.y), ordF(h.z)};
+        Bin *nb = uniform ? sbin : bins + (size_t)(node - levelStart) * 3 * NB;
+        for (int a = 0; a < 3; ++a) {
+            Bin *b = nb + a * NB + binOf(c[a], nd.clo[a], nd.chi[a]);
+            atomicAdd(&b->count, 1);
+            for (int k = 0; k < 3; ++k) { atomicMin(&b->lo[k], ol[k]); atomicMax(&b->hi[k], oh[k]); }
+        }
+    }
+    if (uniform) {
+        __syncthreads();
+        Bin *nb = bins + (size_t)(nodeFirst - levelStart) * 3 * NB;
+        for (int i = threadIdx.x; i < 3 * NB; i += blockDim.x) {
+            const Bin &b = sbin[i];
+            if (!b.count) continue;
+            atomicAdd(&nb[i].count, b.count);
+            for (int k = 0; k < 3; ++k) { atomicMin(&nb[i].lo[k], b.lo[k]); atomicMax(&nb[i].hi[k], b.hi[k]); }
+        }
     }
 }
 
@@ -444,7 +473,7 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
             CK(cudaMalloc(&bins, sizeof(Bin) * binCap));
         }
         k_clear_bins<<<blocks(nb), 256, 0, st>>>(bins, nb);
-        k_bin<<<blocks(n), 256, 0, st>>>(n, idxA, nodeA, pLo, pHi, nodes, levelStart, bins);
+        k_bin<<<blocks(n, kBinChunk), 256, 0, st>>>(n, idxA, nodeA, pLo, pHi, nodes, levelStart, bins);
         k_split<<<blocks(levelEnd - levelStart, 64), 64, 0, st>>>(levelStart, levelEnd, nodes, bins, nodeCount);
         k_flags<<<blocks(n), 256, 0, st>>>(n, idxA, nodeA, pLo, pHi, nodes, levelStart, flags);
         CK(cub::DeviceScan::ExclusiveSum(cubTmp, cubBytes, flags, scan, n, st));

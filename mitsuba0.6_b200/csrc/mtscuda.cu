@@ -22,10 +22,39 @@ int fail(int code, const std::string &msg) { g_err = msg; return code; }
 struct HostShape {
     DShape d;
     bool isEmitter = false;
+    uint32_t nverts = 0;  // mesh
     float lo[3], hi[3];  // analytic bounds
 };
 
-struct HostTex { MtsTextureDesc d; std::vector<__half> texels; };
+struct HostTex { MtsTextureDesc d; __half *texels = nullptr; };  // texels live on the device (converted there)
+
+// Growable device array: scene buffers are appended straight from the caller's host pointers (no host staging
+// copy), so the plugin-facing upload runs at PCIe speed.
+template <class T> struct DevVec {
+    T *data = nullptr; size_t size = 0, cap = 0;
+    cudaError_t reserve(size_t n, cudaStream_t st) {
+        if (n <= cap) return cudaSuccess;
+        size_t ncap = std::max(n, cap + cap / 2);
+        T *nd = nullptr;
+        cudaError_t e = cudaMalloc(&nd, sizeof(T) * ncap);
+        if (e != cudaSuccess) return e;
+        if (size) e = cudaMemcpyAsync(nd, data, sizeof(T) * size, cudaMemcpyDeviceToDevice, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (data) cudaFree(data);
+        data = nd; cap = ncap;
+        return e;
+    }
+    // append n elements from host memory (or zeros when host == nullptr)
+    cudaError_t append(const T *host, size_t n, cudaStream_t st) {
+        cudaError_t e = reserve(size + n, st);
+        if (e != cudaSuccess || n == 0) return e;
+        if (host) e = cudaMemcpyAsync(data + size, host, sizeof(T) * n, cudaMemcpyHostToDevice, st);
+        else e = cudaMemsetAsync(data + size, 0, sizeof(T) * n, st);
+        size += n;
+        return e;
+    }
+    void release() { if (data) cudaFree(data); data = nullptr; size = cap = 0; }
+};
 
 struct HostEmitter {
     MtsEmitterDesc d;
@@ -82,8 +111,9 @@ struct MtsContext {
     std::vector<float> pool;
     std::vector<HostTex> textures;
     std::vector<HostShape> shapes;
-    std::vector<float> positions, normals, texcoords, tangents;
-    std::vector<uint32_t> indices;
+    DevVec<float> positions, normals, texcoords, tangents;   // concatenated over all meshes, on the device
+    DevVec<uint32_t> indices;                                 // already offset into the global vertex arrays
+    int *errFlag = nullptr;                                   // device flag written by validation kernels
     std::vector<HostEmitter> emitters;
     int envIndex = -1;
     // device scene
@@ -97,6 +127,13 @@ struct MtsContext {
 
     MtsContext() { std::memset(&ds, 0, sizeof(ds)); std::memset(&wf, 0, sizeof(wf)); std::memset(&stats, 0, sizeof(stats)); }
     void freeScene() { for (void *p : sceneAllocs) cudaFree(p); sceneAllocs.clear(); built = false; }
+    void freeGeometry() {
+        positions.release(); normals.release(); texcoords.release(); tangents.release(); indices.release();
+        for (auto &t : textures) if (t.texels) cudaFree(t.texels);
+        textures.clear();
+        if (errFlag) cudaFree(errFlag);
+        errFlag = nullptr;
+    }
     void freeWavefront() { for (void *p : wfAllocs) cudaFree(p); wfAllocs.clear(); wfCapacity = 0; }
     float4 *filmPtr() const { return filmBound ? filmBound : filmInternal; }
 };
@@ -147,6 +184,26 @@ int ensureWavefront(MtsContext *c, uint32_t cap) {
     w.capacity = cap;
     c->wfCapacity = cap;
     return MTS_OK;
+}
+
+// ---- upload helpers --------------------------------------------------------------------------
+// float texels -> half storage (TMIPMap keeps half precision); RGB is padded to half4
+__global__ void k_texels_to_half(const float *__restrict__ src, __half *__restrict__ dst, size_t npix, int channels) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    if (channels == 1) dst[i] = __float2half_rn(src[i]);
+    else {
+        dst[4 * i] = __float2half_rn(src[3 * i]); dst[4 * i + 1] = __float2half_rn(src[3 * i + 1]);
+        dst[4 * i + 2] = __float2half_rn(src[3 * i + 2]); dst[4 * i + 3] = __float2half_rn(0.0f);
+    }
+}
+// mesh-local vertex indices -> global ones, with the range check of the mesh loaders
+__global__ void k_offset_indices(uint32_t *idx, size_t n, uint32_t nverts, uint32_t vOff, int *err) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t v = idx[i];
+    if (v >= nverts) { *err = 1; v = 0; }
+    idx[i] = v + vOff;
 }
 
 // ---- kernels behind the per-function entry points -------------------------------------------
@@ -325,7 +382,7 @@ MTS_API int mtscuda_create(int device, MtsContext **out) {
 MTS_API void mtscuda_destroy(MtsContext *c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    c->freeScene(); c->freeWavefront();
+    c->freeScene(); c->freeWavefront(); c->freeGeometry();
     if (c->filmInternal) cudaFree(c->filmInternal);
     if (c->ownStream) cudaStreamDestroy(c->ownStream);
     delete c;
@@ -354,18 +411,21 @@ MTS_API int mtscuda_add_texture(MtsContext *c, const MtsTextureDesc *d, const fl
     if (d->channels != 1 && d->channels != 3) return fail(MTS_EINVAL, "texture channels must be 1 or 3");
     if (d->width <= 0 || d->height <= 0) return fail(MTS_EINVAL, "bad texture size");
     if (d->filter != MTS_FILTER_NEAREST && d->filter != MTS_FILTER_BILINEAR) return fail(MTS_EINVAL, "unsupported texture filter");
+    CUDA_TRY(cudaSetDevice(c->device));
     HostTex t; t.d = *d;
-    size_t npix = (size_t)d->width * d->height;
-    int stride = d->channels == 1 ? 1 : 4;  // RGB padded to half4
-    t.texels.resize(npix * stride);
-    for (size_t i = 0; i < npix; ++i) {
-        if (d->channels == 1) t.texels[i] = __float2half_rn(texels[i]);
-        else {
-            for (int k = 0; k < 3; ++k) t.texels[4 * i + k] = __float2half_rn(texels[3 * i + k]);
-            t.texels[4 * i + 3] = __float2half_rn(0.0f);
-        }
+    const size_t npix = (size_t)d->width * d->height;
+    const int stride = d->channels == 1 ? 1 : 4;  // RGB padded to half4
+    float *tmp = nullptr;
+    CUDA_TRY(cudaMalloc(&tmp, sizeof(float) * npix * d->channels));
+    cudaError_t e = cudaMalloc(&t.texels, sizeof(__half) * npix * stride);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(tmp, texels, sizeof(float) * npix * d->channels, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) {
+        k_texels_to_half<<<(unsigned)((npix + 255) / 256), 256, 0, c->stream>>>(tmp, t.texels, npix, d->channels);
+        e = cudaStreamSynchronize(c->stream);
     }
-    c->textures.push_back(std::move(t)); c->built = false;
+    cudaFree(tmp);
+    if (e != cudaSuccess) { if (t.texels) cudaFree(t.texels); return fail(MTS_ECUDA, std::string("add_texture: ") + cudaGetErrorString(e)); }
+    c->textures.push_back(t); c->built = false;
     return (int)c->textures.size() - 1;
 }
 
@@ -383,25 +443,26 @@ MTS_API int mtscuda_set_bsdfs(MtsContext *c, const MtsBsdfNode *nodes, int32_t n
 
 MTS_API int mtscuda_add_mesh(MtsContext *c, const MtsMeshDesc *m) {
     if (!m->positions || !m->indices || m->ntris == 0) return fail(MTS_EINVAL, "Encountered an empty triangle mesh!");
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
     HostShape s; std::memset(&s.d, 0, sizeof(DShape));
     s.d.type = SHAPE_MESH; s.d.bsdf = m->bsdf; s.d.emitter = -1;
-    uint32_t vOff = (uint32_t)(c->positions.size() / 3), tOff = (uint32_t)(c->indices.size() / 3);
-    s.d.vtxOffset = vOff; s.d.triOffset = tOff; s.d.ntris = m->ntris;
+    const uint32_t vOff = (uint32_t)(c->positions.size / 3), tOff = (uint32_t)(c->indices.size / 3);
+    s.d.vtxOffset = vOff; s.d.triOffset = tOff; s.d.ntris = m->ntris; s.nverts = m->nverts;
     s.d.flags = (m->normals ? 1u : 0u) | (m->texcoords ? 2u : 0u) | (m->tangents ? 4u : 0u);
-    c->positions.insert(c->positions.end(), m->positions, m->positions + 3 * (size_t)m->nverts);
-    // the optional per-vertex arrays are kept index-aligned with `positions`
-    c->normals.resize(c->positions.size(), 0.0f);
-    if (m->normals) std::memcpy(&c->normals[3 * (size_t)vOff], m->normals, sizeof(float) * 3 * (size_t)m->nverts);
-    c->texcoords.resize(c->positions.size() / 3 * 2, 0.0f);
-    if (m->texcoords) std::memcpy(&c->texcoords[2 * (size_t)vOff], m->texcoords, sizeof(float) * 2 * (size_t)m->nverts);
-    size_t i0 = c->indices.size();
-    c->indices.resize(i0 + 3 * (size_t)m->ntris);
-    for (size_t i = 0; i < 3 * (size_t)m->ntris; ++i) {
-        if (m->indices[i] >= m->nverts) return fail(MTS_EINVAL, "mesh index out of range");
-        c->indices[i0 + i] = m->indices[i] + vOff;
-    }
-    c->tangents.resize(c->indices.size() * 2, 0.0f);
-    if (m->tangents) std::memcpy(&c->tangents[6 * (size_t)tOff], m->tangents, sizeof(float) * 6 * (size_t)m->ntris);
+    if (!c->errFlag) { CUDA_TRY(cudaMalloc(&c->errFlag, sizeof(int))); CUDA_TRY(cudaMemsetAsync(c->errFlag, 0, sizeof(int), st)); }
+    // the optional per-vertex / per-triangle arrays are kept index-aligned with positions / indices (zeros where absent)
+    CUDA_TRY(c->positions.append(m->positions, 3 * (size_t)m->nverts, st));
+    CUDA_TRY(c->normals.append(m->normals, 3 * (size_t)m->nverts, st));
+    CUDA_TRY(c->texcoords.append(m->texcoords, 2 * (size_t)m->nverts, st));
+    CUDA_TRY(c->indices.append(m->indices, 3 * (size_t)m->ntris, st));
+    CUDA_TRY(c->tangents.append(m->tangents, 6 * (size_t)m->ntris, st));
+    const size_t ni = 3 * (size_t)m->ntris;
+    k_offset_indices<<<(unsigned)((ni + 255) / 256), 256, 0, st>>>(c->indices.data + 3 * (size_t)tOff, ni, m->nverts, vOff, c->errFlag);
+    int err = 0;
+    CUDA_TRY(cudaMemcpyAsync(&err, c->errFlag, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));   // also guarantees the caller's buffers have been consumed
+    if (err) { CUDA_TRY(cudaMemsetAsync(c->errFlag, 0, sizeof(int), st)); return fail(MTS_EINVAL, "mesh index out of range"); }
     c->shapes.push_back(s); c->built = false;
     return (int)c->shapes.size() - 1;
 }
@@ -473,14 +534,11 @@ MTS_API int mtscuda_build(MtsContext *c) {
     cudaEventRecord(e0, c->stream);
     DScene &S = c->ds;
     int rc;
-    // geometry
-    if ((rc = devUpload(c, c->positions.data(), c->positions.size(), &S.positions))) return rc;
-    if ((rc = devUpload(c, c->normals.data(), c->normals.size(), &S.normals))) return rc;
-    if ((rc = devUpload(c, c->texcoords.data(), c->texcoords.size(), &S.texcoords))) return rc;
-    if ((rc = devUpload(c, c->indices.data(), c->indices.size(), &S.indices))) return rc;
-    if ((rc = devUpload(c, c->tangents.data(), c->tangents.size(), &S.tangents))) return rc;
+    // geometry already lives on the device (appended by add_mesh)
+    S.positions = c->positions.data; S.normals = c->normals.data; S.texcoords = c->texcoords.data;
+    S.indices = c->indices.data; S.tangents = c->tangents.data;
     // area CDFs of emitter meshes: TriMesh::prepareSamplingTable (src/librender/trimesh.cpp:388-403),
-    // sequential fp32 accumulation like DiscreteDistribution::append/normalize
+    // sequential fp32 accumulation like DiscreteDistribution::append/normalize (host, from a read-back of that mesh)
     std::vector<float> cdfs;
     BvhBuildInput bin;
     uint32_t primOffset = 0;
@@ -490,12 +548,16 @@ MTS_API int mtscuda_build(MtsContext *c) {
             bin.meshes.push_back({s.d.triOffset, s.d.ntris, primOffset, (int)si});
             primOffset += s.d.ntris;
             if (s.isEmitter) {
+                std::vector<float> pos(3 * (size_t)s.nverts); std::vector<uint32_t> idx(3 * (size_t)s.d.ntris);
+                CUDA_TRY(cudaMemcpyAsync(pos.data(), c->positions.data + 3 * (size_t)s.d.vtxOffset, sizeof(float) * pos.size(), cudaMemcpyDeviceToHost, c->stream));
+                CUDA_TRY(cudaMemcpyAsync(idx.data(), c->indices.data + 3 * (size_t)s.d.triOffset, sizeof(uint32_t) * idx.size(), cudaMemcpyDeviceToHost, c->stream));
+                CUDA_TRY(cudaStreamSynchronize(c->stream));
                 s.d.cdfOffset = (uint32_t)cdfs.size();
                 cdfs.push_back(0.0f);
                 float acc = 0.0f;
                 for (uint32_t t = 0; t < s.d.ntris; ++t) {
-                    const uint32_t *ix = &c->indices[3 * ((size_t)s.d.triOffset + t)];
-                    const float *p0 = &c->positions[3 * (size_t)ix[0]], *p1 = &c->positions[3 * (size_t)ix[1]], *p2 = &c->positions[3 * (size_t)ix[2]];
+                    const uint32_t *ix = &idx[3 * (size_t)t];
+                    const float *p0 = &pos[3 * (size_t)(ix[0] - s.d.vtxOffset)], *p1 = &pos[3 * (size_t)(ix[1] - s.d.vtxOffset)], *p2 = &pos[3 * (size_t)(ix[2] - s.d.vtxOffset)];
                     float a[3] = {p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2]}, b[3] = {p2[0] - p0[0], p2[1] - p0[1], p2[2] - p0[2]};
                     float cr[3] = {a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0]};
                     acc += 0.5f * hLen(cr);
@@ -529,9 +591,8 @@ MTS_API int mtscuda_build(MtsContext *c) {
     if ((rc = devUpload(c, c->pool.data(), c->pool.size(), &S.pool))) return rc;
     std::vector<DTexture> dtex;
     for (auto &t : c->textures) {
-        DTexture d; const __half *dev = nullptr;
-        if ((rc = devUpload(c, t.texels.data(), t.texels.size(), &dev))) return rc;
-        d.texels = dev; d.width = t.d.width; d.height = t.d.height; d.channels = t.d.channels;
+        DTexture d;
+        d.texels = t.texels; d.width = t.d.width; d.height = t.d.height; d.channels = t.d.channels;
         d.wrapU = t.d.wrap_u; d.wrapV = t.d.wrap_v; d.filter = t.d.filter;
         d.uvScale = make_float2(t.d.uv_scale[0], t.d.uv_scale[1]); d.uvOffset = make_float2(t.d.uv_offset[0], t.d.uv_offset[1]);
         dtex.push_back(d);
@@ -669,6 +730,7 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
     cudaEvent_t ev0, ev1; cudaEventCreate(&ev0); cudaEventCreate(&ev1);
     cudaEventRecord(ev0, st);
 
+    const int shadeMinB = getenv("MTS_SHADE_MINB") ? atoi(getenv("MTS_SHADE_MINB")) : 4;
     const int gridTrace = c->numSMs * 8, gridShade = c->numSMs * 4, gridWide = c->numSMs * 8;
     uint64_t launches = 0, normalRays = 0, shadowRays = 0;
     Counters hc;
@@ -692,7 +754,13 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
             begin(2);
             k_sort_offsets<<<1, 32, 0, st>>>(Wf);
             k_sort_scatter<<<gridWide, 256, 0, st>>>(Wf, cur);
-            k_shade<<<gridShade, 128, 0, st>>>(S, Wf, R, cur);
+            switch (shadeMinB) {
+            case 3: k_shade<3><<<c->numSMs * 3, 128, 0, st>>>(S, Wf, R, cur); break;
+            case 5: k_shade<5><<<c->numSMs * 5, 128, 0, st>>>(S, Wf, R, cur); break;
+            case 6: k_shade<6><<<c->numSMs * 6, 128, 0, st>>>(S, Wf, R, cur); break;
+            case 8: k_shade<8><<<c->numSMs * 8, 128, 0, st>>>(S, Wf, R, cur); break;
+            default: k_shade<4><<<c->numSMs * 4, 128, 0, st>>>(S, Wf, R, cur); break;
+            }
             end();
             begin(3);
             if (P->instrument) k_shadow<true><<<gridTrace, 128, 0, st>>>(S, Wf);

@@ -351,7 +351,8 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
     out.next = true; out.done = false;
 }
 
-__global__ void __launch_bounds__(128) k_shade(const DScene S, const Wavefront W, const RenderConst R, int qsel) {
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) k_shade(const DScene S, const Wavefront W, const RenderConst R, int qsel) {
     const uint32_t count = W.ctr->qCount[qsel];
     const uint32_t rounded = (count + 31u) & ~31u;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
