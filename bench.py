@@ -52,7 +52,7 @@ def parse_args():
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (debug)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--ref-seconds", type=float, default=20.0, help="CPU seconds per reference-arm step / cpu_baseline")
+    ap.add_argument("--ref-spp", type=int, default=0, help="spp of the bounded CPU sample (reference arm / cpu_baseline); 0 = per-workload default")
     return ap.parse_args()
 
 
@@ -151,29 +151,65 @@ def measured_peak():
 RAY_IN, HIT_OUT, SHADOW_OUT, PRIM_BYTES = 32, 16, 4, 48
 
 
-def cpu_sample(flat, kw, seconds, threads=None):
-    """Time the CPU implementation of the path (the oracle port, or oracle/_ref when it exists) on a bounded
-    sample of the workload: the full frame at a reduced spp chosen so the run takes about `seconds`."""
-    import mts_b200 as M
-    if threads:
-        os.environ["OMP_NUM_THREADS"] = str(threads)
-    cores = int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1))
-    cpu = M.CudaPath(flat, backend="oracle")
-    t0 = time.time()
-    cpu.preprocess()
-    build_s = time.time() - t0
-    cpu.render(spp=1, read_back=False)                      # calibration pass (also warms caches)
-    per_spp = max(cpu.stats.render_ms / 1e3, 1e-3)
-    spp = int(max(1, min(kw["spp"], seconds / per_spp)))
-    cpu.render(spp=spp, read_back=False, seed=1)
-    st = cpu.stats
-    s = st.render_ms / 1e3
-    out = dict(value=st.camera_samples / s / 1e6, unit="Msamples/s", cores=cores, kind="port",
-               sample="full %dx%d frame at %d spp (of %d), %.1f s CPU render; kd-tree/BVH build %.1f s excluded"
-                      % (flat.film_size[0], flat.film_size[1], spp, kw["spp"], s, build_s),
-               mrays_per_s=(st.normal_rays + st.shadow_rays) / s / 1e6, ms=st.render_ms)
-    cpu.close()
-    return out
+REF_SPP = {"terrain": 8, "spheres": 16, "cornell": 64, "caustics": 16, "terrain_small": 8}   # bounded CPU samples
+
+
+def reference_built():
+    return os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libmtsref.so"))
+
+
+class CpuArm:
+    """The CPU implementation of the path on the host cores, on a bounded sample of the workload (the full frame at a
+    reduced spp).  kind "reference" = the reference's OWN code (oracle/_ref: unchanged Mitsuba 0.6 sources, its
+    Scheduler with one LocalWorker per core, 32x32 blocks); kind "port" = the oracle restatement (OpenMP), used only
+    when oracle/_ref has not been built."""
+
+    def __init__(self, name, sc, flat, kw, spp=0):
+        import copy
+        self.kw, self.flat = kw, flat
+        self.spp = int(spp or min(kw["spp"], REF_SPP.get(name, 8)))
+        t0 = time.time()
+        if reference_built():
+            sys.path.insert(0, os.path.join(ROOT, "oracle", "refbuild"))
+            import mtsref
+            self.kind = "reference"
+            sc2 = copy.copy(sc)
+            sc2.children = list(sc.children)
+            for i, (n, c) in enumerate(sc2.children):       # same scene, sampleCount = the bounded spp
+                if c.kind == "sensor":
+                    s2 = copy.copy(c)
+                    s2.children = [(m, (copy.copy(d) if d.kind == "sampler" else d)) for m, d in c.children]
+                    for m, d in s2.children:
+                        if d.kind == "sampler":
+                            d.props = dict(d.props, sampleCount=self.spp)
+                    sc2.children[i] = (n, s2)
+            self.ref = mtsref.RefScene(sc2)
+            self.cores = mtsref.load().mtsref_thread_count()
+            self.build_s = self.ref.kd_build_s
+        else:
+            import mts_b200 as M
+            self.kind = "port"
+            self.cores = int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1))
+            self.cpu = M.CudaPath(flat, backend="oracle")
+            self.cpu.preprocess()
+            self.build_s = self.cpu.ctx.get_stats().build_ms / 1e3
+        self.setup_s = time.time() - t0
+
+    def step(self, seed=1):
+        W, H = self.flat.film_size
+        if self.kind == "reference":
+            self.ref.render()
+            s = self.ref.render_s
+            rays = self.ref.stats.get("normal_rays", 0) + self.ref.stats.get("shadow_rays", 0)
+        else:
+            self.cpu.render(spp=self.spp, read_back=False, seed=seed)
+            st = self.cpu.stats
+            s, rays = st.render_ms / 1e3, st.normal_rays + st.shadow_rays
+        samples = W * H * self.spp
+        return dict(value=samples / s / 1e6, unit="Msamples/s", cores=self.cores, kind=self.kind,
+                    sample="full %dx%d frame at %d spp (of %d): %.1f s of CPU render on %d threads; kd-tree build %.1f s and scene "
+                           "loading excluded" % (W, H, self.spp, self.kw["spp"], s, self.cores, self.build_s),
+                    mrays_per_s=rays / s / 1e6, ms=s * 1e3)
 
 
 def run_reference(args):
@@ -182,10 +218,11 @@ def run_reference(args):
     if rank != 0:
         return
     sc, flat, kw, desc, gen_s = build_scene(args.workload, args.spp)
+    arm = CpuArm(args.workload, sc, flat, kw, args.ref_spp)
     vals = []
     base = None
     for i in range(args.warmup + args.steps):
-        base = cpu_sample(flat, kw, args.ref_seconds)
+        base = arm.step(seed=i)
         if i >= args.warmup:
             vals.append(base)
     v = float(np.mean([b["value"] for b in vals]))
@@ -352,7 +389,7 @@ def run_cuda(args):
         if e2e:
             line["e2e"] = e2e
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = {k: v for k, v in cpu_sample(flat, kw, args.ref_seconds).items() if k != "ms"}
+            line["cpu_baseline"] = {k: v for k, v in CpuArm(args.workload, sc, flat, kw, args.ref_spp).step().items() if k != "ms"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

@@ -658,6 +658,13 @@ MTS_API int mtscuda_build(MtsContext *c) {
         // m_sceneBSphere: scene AABB incl. the sensor position, radius * 1.5 (envmap.cpp:331-341, scene.cpp:386-398)
         float lo[3], hi[3];
         for (int a = 0; a < 3; ++a) { lo[a] = bin.numPrims ? bout.lo[a] : 0.0f; hi[a] = bin.numPrims ? bout.hi[a] : 0.0f; }
+        if (bin.numPrims) {   // the kd-tree enlarges its AABB (include/mitsuba/render/gkdtree.h:1218-1221, eps = 1e-3)
+            const float eps = 1e-3f;
+            for (int a = 0; a < 3; ++a) {
+                lo[a] = lo[a] - ((hi[a] - lo[a]) * eps + eps);
+                hi[a] = hi[a] + ((hi[a] - lo[a]) * eps + eps);   // uses the already enlarged minimum, as the reference does
+            }
+        }
         if (c->hasCam) {
             const float camP[3] = {c->cam.camera_to_world[3], c->cam.camera_to_world[7], c->cam.camera_to_world[11]};
             for (int a = 0; a < 3; ++a) {

@@ -454,23 +454,29 @@ def uv_tangents(positions, texcoords, indices):
 
 
 def cube_mesh(to_world):
-    """The `cube` shape: 24 vertices / 12 triangles with per-face normals and [0,1]^2 uvs
-    (src/shapes/cube.cpp:73-108); generated per face rather than from a table."""
-    faces = [  # (normal, u axis, v axis)
-        ((0, 0, -1), (0, 1, 0), (1, 0, 0)), ((0, 0, 1), (1, 0, 0), (0, 1, 0)),
-        ((0, -1, 0), (1, 0, 0), (0, 0, 1)), ((0, 1, 0), (0, 0, 1), (1, 0, 0)),
-        ((-1, 0, 0), (0, 0, 1), (0, 1, 0)), ((1, 0, 0), (0, 1, 0), (0, 0, 1)),
+    """The `cube` shape: 24 vertices / 12 triangles with per-face normals and [0,1]^2 uvs, in the vertex / face /
+    triangle order of the reference's tables (src/shapes/cube.cpp:22-28, 75-104) so that primitive indices and the
+    per-face uv parameterisation agree: faces -y, +y, +x, +z, -x, -z; every face is the quad
+    v0, v0+2a, v0+2a+2b, v0+2b with uvs (0,1), (1,1), (1,0), (0,0) and triangles (0,1,2), (3,0,2)."""
+    faces = [  # (normal, first corner v0, edge direction a, edge direction b)
+        ((0, -1, 0), (1, -1, -1), (0, 0, 1), (-1, 0, 0)),
+        ((0, 1, 0), (1, 1, -1), (-1, 0, 0), (0, 0, 1)),
+        ((1, 0, 0), (1, -1, -1), (0, 1, 0), (0, 0, 1)),
+        ((0, 0, 1), (1, -1, 1), (0, 1, 0), (-1, 0, 0)),
+        ((-1, 0, 0), (-1, -1, 1), (0, 1, 0), (0, 0, -1)),
+        ((0, 0, -1), (1, 1, -1), (0, -1, 0), (-1, 0, 0)),
     ]
     pos, nrm, uv, idx = [], [], [], []
     m = np.asarray(to_world, dtype=np.float64)
-    for n, ua, va in faces:
-        n, ua, va = (np.array(x, dtype=np.float64) for x in (n, ua, va))
+    for n, v0, ea, eb in faces:
+        n, v0, ea, eb = (np.array(x, dtype=np.float64) for x in (n, v0, ea, eb))
         base = len(pos)
-        for (su, sv) in ((-1, -1), (1, -1), (1, 1), (-1, 1)):
-            pos.append(xform_point(m, n + su * ua + sv * va))
-            nn = xform_normal(m, n)
-            nrm.append(nn / np.linalg.norm(nn))
-            uv.append(((su + 1) / 2.0, (sv + 1) / 2.0))
+        nn = xform_normal(m, n)
+        nn = nn / np.linalg.norm(nn)
+        for corner, tc in ((v0, (0, 1)), (v0 + 2 * ea, (1, 1)), (v0 + 2 * ea + 2 * eb, (1, 0)), (v0 + 2 * eb, (0, 0))):
+            pos.append(xform_point(m, corner))
+            nrm.append(nn)
+            uv.append(tc)
         idx += [(base, base + 1, base + 2), (base + 3, base, base + 2)]
     return (np.array(pos, dtype=F), np.array(nrm, dtype=F), np.array(uv, dtype=F), np.array(idx, dtype=np.uint32))
 

@@ -783,9 +783,13 @@ def flatten(scene):
         if em is not None:
             if em.type != "area":
                 raise Unsupported("only `area` emitters can be attached to shapes")
-            fs.emitters.append((_emitter_desc(type=abi.EMITTER_AREA, shape=sid, radiance=Spectrum(em.get("radiance", Spectrum(1.0))),
+            area_emitters.append((_emitter_desc(type=abi.EMITTER_AREA, shape=sid, radiance=Spectrum(em.get("radiance", Spectrum(1.0))),
                                               sampling_weight=float(em.get("samplingWeight", 1.0))), None))
 
+    # Emitter order = Scene::m_emitters order: scene-level emitters as they are added (Scene::addChild,
+    # scene.cpp:497-516), then the area emitters of the shapes in shape order (Scene::initialize -> addShape,
+    # scene.cpp:322-336, 570-571).  The order fixes which emitter a given sample selects (Scene::m_emitterPDF).
+    area_emitters = []
     for _, c in scene.children:
         if c.kind == "shape":
             add_shape(c)
@@ -822,6 +826,7 @@ def flatten(scene):
             pass  # top-level definitions that shapes <ref> to
         else:
             raise Unsupported("scene-level <%s> is out of scope" % c.kind)
+    fs.emitters += area_emitters
     if not fs.emitters:
         raise Unsupported("the scene has no emitters; the reference would silently add a `sunsky` emitter "
                           "(src/librender/scene.cpp:358-373), which is out of scope")

@@ -869,6 +869,11 @@ MTS_API int mtsoracle_build(MtsContext *c) {
         e.normalization = 1.0f / (rowSum * (2 * kPi / e.w) * (kPi / e.h));
         /* scene AABB incl. the sensor position (scene.cpp:386-398), AABB::getBSphere, radius*1.5 */
         V3 lo = c->sceneLo, hi = c->sceneHi;
+        if (!pb.empty()) { /* the kd-tree enlarges its AABB (include/mitsuba/render/gkdtree.h:1218-1221, eps = 1e-3) */
+            const float eps = 1e-3f;
+            lo = lo - ((hi - lo) * eps + V3(eps));
+            hi = hi + ((hi - lo) * eps + V3(eps));   /* uses the already enlarged minimum, as the reference does */
+        }
         if (c->hasCam) {
             V3 camP = m44_from(c->cam.camera_to_world).pointAffine(V3(0.0f));
             for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], camP[a]); hi[a] = std::max(hi[a], camP[a]); }

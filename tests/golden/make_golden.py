@@ -1,0 +1,89 @@
+#!/usr/bin/env python
+"""Generate the golden vectors of tests/golden/ by running the REFERENCE ITSELF (oracle/_ref: the unchanged
+Mitsuba 0.6 sources of /root/reference compiled by oracle/refbuild/Makefile) on seeded inputs.
+
+    python tests/golden/make_golden.py            # needs /root/reference + a built oracle/_ref; ~5 minutes on 8 cores
+
+The inputs are regenerated from fixed seeds by tests/golden_io.py (shared with the tests); only the reference's
+outputs are stored.  The files travel with the repository, so the tests need neither /root/reference nor oracle/_ref.
+"""
+import os
+import sys
+import time
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "oracle", "refbuild"))
+
+import numpy as np  # noqa: E402
+import mts_b200 as M  # noqa: E402,F401
+import golden_io as G  # noqa: E402
+import mtsref  # noqa: E402
+
+
+def probes():
+    sc, z = G.zoo()
+    rs = mtsref.RefScene(sc)
+    out = {}
+    for name, p in z.items():
+        surf, wi, wo, u = G.bsdf_inputs(name)
+        rb = rs.bsdf(p)
+        smp = rs.bsdf_sample(rb, surf, wi, u)
+        wo2 = G.eval_directions(smp, wo)
+        out["bsdf/%s/sample" % name] = smp
+        for tag, meas in (("sa", 1), ("disc", 4)):
+            v, pdf = rs.bsdf_eval_pdf(rb, surf, wi, wo2, meas)
+            out["bsdf/%s/eval_%s" % (name, tag)] = v
+            out["bsdf/%s/pdf_%s" % (name, tag)] = pdf
+        out["bsdf/%s/type" % name] = np.array([rs.bsdf_type(rb)], dtype=np.int64)
+    rays = G.trace_rays()
+    h, ids = rs.trace(rays)
+    out["trace/t"], out["trace/ids"] = h[:, 0].copy(), ids
+    sr = G.shadow_rays(rays, h)
+    out["trace/shadow"] = rs.trace(sr, shadow=True)[0][:, 0].copy()
+    rec, ids2 = rs.hit_records(rays[:G.N_RECORDS])
+    out["records/rec"], out["records/ids"] = rec, ids2
+    ref, refn, u = G.emitter_inputs()
+    out["emitter/sample"] = rs.sample_emitter_direct(ref, refn, u)
+    out["env/eval"] = rs.eval_environment(G.env_dirs())
+    out["sensor/rays"] = rs.sample_rays(G.sensor_positions())
+    pos, val = G.splat_inputs()
+    out["film/gaussian"] = rs.splat(pos, val)
+    # box filter: the Cornell film
+    rc = mtsref.RefScene(G.cornell_small(spp=1))
+    pos, val = G.splat_inputs(w=G.CORNELL_RES, h=G.CORNELL_RES)
+    out["film/box"] = rc.splat(pos, val)
+    out["sensor/rays_cornell"] = rc.sample_rays(G.sensor_positions(w=G.CORNELL_RES, h=G.CORNELL_RES))
+    return out
+
+
+def images():
+    out = {}
+    for name, make in G.IMAGE_SCENES.items():
+        sc = make()
+        t0 = time.time()
+        rs = mtsref.RefScene(sc)
+        film = rs.render()
+        st = rs.stats
+        w, h, spp = G.scene_dims(sc)
+        out["image/%s/rgb" % name] = M.develop(film).astype(np.float16)   # converged image; fp16 keeps the fixture small
+        out["image/%s/stats" % name] = np.array([st.get("normal_rays", 0) / (w * h * spp), st.get("shadow_rays", 0) / (w * h * spp),
+                                                 st.get("avg_path_length", 0), rs.render_s, mtsref.load().mtsref_thread_count()], dtype=np.float64)
+        print("%-10s %dx%d %d spp: reference render %.1f s (total %.1f s), rays/sample %.3f + %.3f, avg path length %.2f"
+              % (name, w, h, spp, rs.render_s, time.time() - t0, out["image/%s/stats" % name][0], out["image/%s/stats" % name][1],
+                 out["image/%s/stats" % name][2]), flush=True)
+    return out
+
+
+if __name__ == "__main__":
+    if not mtsref.available():
+        raise SystemExit("oracle/_ref is not built: make -C oracle/refbuild (needs /root/reference)")
+    p = probes()
+    np.savez_compressed(os.path.join(HERE, "probes.npz"), **p)
+    print("probes.npz: %d arrays" % len(p))
+    if "--no-images" not in sys.argv:
+        im = images()
+        np.savez_compressed(os.path.join(HERE, "images.npz"), **im)
+        print("images.npz: %d arrays" % len(im))

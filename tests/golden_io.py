@@ -1,0 +1,110 @@
+"""Seeded inputs shared by tests/golden/make_golden.py (which feeds them to the REFERENCE build) and by the tests
+(which feed them to the oracle restatement and to the CUDA library).  Changing anything here invalidates the
+fixtures: regenerate them with make_golden.py."""
+import os
+import zlib
+
+import numpy as np
+
+import mts_b200 as M  # noqa: F401
+from mitsuba0_6_b200 import abi, scenes
+import util
+
+F = np.float32
+HERE = os.path.dirname(os.path.abspath(__file__))
+N_BSDF, N_RAYS, N_RECORDS, N_EMIT, N_ENV, N_SENSOR, N_SPLAT = 768, 24000, 6000, 8000, 6000, 2000, 6000
+ZOO_W, ZOO_H, CORNELL_RES = 96, 64, 96
+
+
+def zoo(spp=4):
+    return util.zoo_scene(width=ZOO_W, height=ZOO_H, spp=spp)
+
+
+def cornell_small(spp=64):
+    return scenes.cornell_box(CORNELL_RES, CORNELL_RES, spp)
+
+
+def bsdf_inputs(name):
+    rng = np.random.RandomState(zlib.crc32(name.encode()))
+    n = N_BSDF
+    surf = abi.default_surface(n, rng.rand(n, 2))
+    wi = util.random_dirs(rng, n)
+    wo = util.random_dirs(rng, n)
+    u = rng.rand(n, 2).astype(F)
+    return surf, wi, wo, u
+
+
+def eval_directions(reference_sample, wo):
+    """eval/pdf are queried at the direction the REFERENCE sampled (so that delta lobes are exercised) where it
+    sampled one, at a random direction otherwise."""
+    ok = reference_sample[:, 3] > 0
+    return np.where(ok[:, None], reference_sample[:, 4:7], wo).astype(F)
+
+
+def trace_rays():
+    rng = np.random.RandomState(3)
+    lo, hi = np.array([-9, 0, -4.0]), np.array([9, 9, 6.0])
+    a, b = rng.uniform(lo, hi, (N_RAYS, 3)), rng.uniform(lo, hi, (N_RAYS, 3))
+    d = b - a
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.zeros((N_RAYS, 8), dtype=F)
+    rays[:, 0:3], rays[:, 3], rays[:, 4:7], rays[:, 7] = a, 1e-4, d, np.inf
+    return rays
+
+
+def shadow_rays(rays, reference_hits):
+    sr = rays.copy()
+    t = reference_hits[:, 0]
+    sr[:, 7] = np.where(np.isfinite(t), t * 1.5, 10.0)
+    return sr
+
+
+def emitter_inputs():
+    rng = np.random.RandomState(5)
+    n = N_EMIT
+    ref = rng.uniform([-8, 0.1, -3], [8, 6, 5], (n, 3)).astype(F)
+    refn = util.random_dirs(rng, n)
+    refn[::2] = 0
+    return ref, refn, rng.rand(n, 2).astype(F)
+
+
+def env_dirs():
+    return util.random_dirs(np.random.RandomState(6), N_ENV)
+
+
+def sensor_positions(w=ZOO_W, h=ZOO_H):
+    rng = np.random.RandomState(7)
+    return (rng.rand(N_SENSOR, 2) * [w, h]).astype(F)
+
+
+def splat_inputs(w=ZOO_W, h=ZOO_H):
+    rng = np.random.RandomState(8)
+    pos = (rng.rand(N_SPLAT, 2) * [w + 2, h + 2] - 1).astype(F)   # includes samples outside the film
+    val = rng.rand(N_SPLAT, 3).astype(F)
+    val[::97] = np.nan                                            # invalid samples are rejected by put()
+    val[5::101, 1] = -1.0
+    return pos, val
+
+
+def scene_dims(sc):
+    s = sc.child("sensor")
+    f = s.child("film")
+    return int(f.get("width")), int(f.get("height")), int(s.child("sampler").get("sampleCount"))
+
+
+# converged reference renders (small frames, many samples) of the zoo scene and of reduced versions of the
+# BASELINE.json configurations
+IMAGE_SCENES = {
+    "zoo": lambda: zoo(spp=8192)[0],
+    "cornell": lambda: scenes.cornell_box(CORNELL_RES, CORNELL_RES, 4096),
+    "spheres": lambda: scenes.material_spheres(128, 128, 8192, env_size=(512, 256)),
+    "caustics": lambda: scenes.caustic_scene(96, 96, 16384, knot=(120, 40)),
+    "terrain": lambda: scenes.terrain_scene(160, 90, 4096, grid=200, tex_size=256, env_size=(512, 256)),
+}
+
+
+def load(name):
+    path = os.path.join(HERE, "golden", name)
+    if not os.path.exists(path):
+        raise FileNotFoundError("%s is missing: run tests/golden/make_golden.py where /root/reference is mounted" % path)
+    return np.load(path)
