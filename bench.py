@@ -256,7 +256,7 @@ def run_cuda(args):
     W, H = flat.film_size
     spp_total = kw["spp"]
     # sample-index sharding: rank r renders global samples r, r+N, r+2N, ...
-    spp_rank = spp_total // world + (1 if rank < spp_total % world else 0)
+    spp_rank, _, _ = M.sharding.shard_samples(spp_total, rank, world)
 
     gpu = M.CudaPath(flat, backend="cuda", device=local)
     t0 = time.time()
@@ -271,7 +271,7 @@ def run_cuda(args):
     def step(seed):
         gpu.render(spp=spp_rank, read_back=False, seed=seed, sample_offset=rank, sample_stride=world)
         if world > 1:
-            dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)   # NCCL sum of the float4 film over NVLink
+            M.sharding.reduce_film(film)   # NCCL sum of the float4 film over NVLink (the path's only exchange step)
         return gpu.stats
 
     def sync():

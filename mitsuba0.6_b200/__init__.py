@@ -11,12 +11,12 @@ import ctypes as _C
 
 import numpy as np
 
-from . import abi, hostmath, scene as _scene
+from . import abi, hostmath, scene as _scene, sharding
 from .abi import Context, MtsError
 from .scene import Plugin, Spectrum, Point, load_xml, to_xml, flatten, upload, Unsupported
 
 __all__ = ["CudaPath", "Context", "MtsError", "Plugin", "Spectrum", "Point", "load_xml", "to_xml",
-           "flatten", "upload", "Unsupported", "develop", "rel_mse", "abi", "hostmath"]
+           "flatten", "upload", "Unsupported", "develop", "rel_mse", "abi", "hostmath", "sharding"]
 
 
 def develop(film_rgbw):

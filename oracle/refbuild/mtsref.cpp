@@ -32,6 +32,7 @@
 #include <mitsuba/render/integrator.h>
 #include <mitsuba/render/shape.h>
 #include <chrono>
+#include <iostream>
 #include <map>
 #include <string>
 
@@ -100,7 +101,12 @@ int mtsref_init(const char *root, int nthreads, int logLevel) {
     Spectrum::staticInitialization();
     Bitmap::staticInitialization();
     Scheduler::staticInitialization();
-    Thread::getThread()->getLogger()->setLogLevel((ELogLevel)logLevel);
+    /* stdout belongs to the caller (bench.py prints one JSON line there): log to stderr, no progress bar */
+    Logger *logger = Thread::getThread()->getLogger();
+    logger->clearAppenders();
+    logger->addAppender(new StreamAppender(&std::cerr));
+    logger->setLogLevel((ELogLevel)logLevel);
+    ProgressReporter::setEnabled(false);
     ref<FileResolver> fr = Thread::getThread()->getFileResolver();
     fr->appendPath(fs::path(root));
     if (nthreads <= 0) nthreads = getCoreCount();

@@ -132,6 +132,7 @@ class RefScene:
         if p.kind == "film":
             props.setdefault("fileFormat", "pfm")     # OpenEXR is not compiled into the oracle build
             props.setdefault("banner", False)
+            props.setdefault("componentFormat", "float32")
         if p.kind == "integrator" and ptype == "cudapath":
             ptype = "path"
         pr = lib.mtsref_props_new((ptype or "scene").encode())
