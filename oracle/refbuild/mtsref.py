@@ -85,7 +85,8 @@ class RefObject:
 class RefScene:
     """The reference object graph of one Plugin tree."""
 
-    def __init__(self, scene, threads=0, scratch=None):
+    def __init__(self, scene, threads=0, scratch=None, integrator=None):
+        self.integrator = integrator   # e.g. "cudapath": render with the drop-in plugin instead of the scene's `path`
         from mitsuba0_6_b200 import scene as ms   # Plugin / Spectrum / Point, asset writers
         self.ms = ms
         self.lib = load(threads)
@@ -133,8 +134,8 @@ class RefScene:
             props.setdefault("fileFormat", "pfm")     # OpenEXR is not compiled into the oracle build
             props.setdefault("banner", False)
             props.setdefault("componentFormat", "float32")
-        if p.kind == "integrator" and ptype == "cudapath":
-            ptype = "path"
+        if p.kind == "integrator":
+            ptype = self.integrator or ("path" if ptype == "cudapath" else ptype)
         pr = lib.mtsref_props_new((ptype or "scene").encode())
         for k, v in props.items():
             kb = k.encode()

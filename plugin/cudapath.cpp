@@ -1,0 +1,532 @@
+/*
+ * cudapath -- drop-in Mitsuba 0.6 integrator plugin that renders with the B200-native path tracer (libmtscuda).
+ *
+ * Build it inside a Mitsuba 0.6 tree as src/integrators/cudapath/cudapath.cpp (SConscript line:
+ *     plugins += env.SharedLibrary('cudapath', ['cudapath/cudapath.cpp'], LIBS = env['LIBS'] + ['mtscuda'])
+ * ) and use it from an unchanged scene file with <integrator type="cudapath"> -- same parameters as `path`
+ * (maxDepth, rrDepth, strictNormals, hideEmitters; src/librender/integrator.cpp:190-225).  In this repository it is
+ * compiled against the reference sources by oracle/refbuild/Makefile and exercised through the reference's own
+ * PluginManager (tests/test_gpu_plugin.py).
+ *
+ * The class is an `Integrator` (not a `SamplingIntegrator`: there is no per-ray Li()).  render() flattens the
+ * configured object graph into the plain-C scene description of include/mtscuda.h, renders, and hands the result to
+ * the Film as one ESpectrumAlphaWeight ImageBlock (Film::put), i.e. through the same develop path as the CPU
+ * integrators.  Plugin classes such as SmoothDiffuse or BitmapTexture are private to their .so files and have no
+ * getters, so the material graph is read through the mechanism Mitsuba itself uses to ship scenes to render nodes:
+ * it is serialized into a MemoryStream (every class writes its configured members in a fixed order, e.g.
+ * src/bsdfs/roughplastic.cpp serialize()) and that stream is parsed here.  Scenes using plugins outside the scope of
+ * the path are rejected with Log(EError, ...), never rendered differently.
+ */
+#include <mitsuba/render/scene.h>
+#include <mitsuba/render/renderqueue.h>
+#include <mitsuba/render/renderjob.h>
+#include <mitsuba/render/imageblock.h>
+#include <mitsuba/render/trimesh.h>
+#include <mitsuba/core/mstream.h>
+#include <mitsuba/core/bitmap.h>
+#include <mitsuba/core/statistics.h>
+#include <mitsuba/core/fresolver.h>
+#include <mitsuba/core/fstream.h>
+#include <map>
+#include <vector>
+
+#include "mtscuda.h"
+
+/* RoughTransmittance (the precomputed transmittance tables of roughplastic) is a header of the bsdfs directory */
+#define protected public
+#include "microfacet.h"
+#include "rtrans.h"
+#undef protected
+
+MTS_NAMESPACE_BEGIN
+
+static StatsCounter statLaunches("cudapath", "CUDA kernel launches");
+
+class CudaPath : public Integrator {
+public:
+    CudaPath(const Properties &props) : Integrator(props), m_cancel(0) {
+        /* identical to MonteCarloIntegrator (src/librender/integrator.cpp:190-225) */
+        m_rrDepth = props.getInteger("rrDepth", 5);
+        m_maxDepth = props.getInteger("maxDepth", -1);
+        m_strictNormals = props.getBoolean("strictNormals", false);
+        m_hideEmitters = props.getBoolean("hideEmitters", false);
+        m_device = props.getInteger("device", 0);          /* optional extras must be queried */
+        m_seed = (uint32_t) props.getInteger("seed", 0);
+        if (m_rrDepth <= 0)
+            Log(EError, "'rrDepth' must be set to a value greater than zero!");
+        if (m_maxDepth <= 0 && m_maxDepth != -1)
+            Log(EError, "'maxDepth' must be set to -1 (infinite) or a value greater than zero!");
+    }
+
+    CudaPath(Stream *stream, InstanceManager *manager) : Integrator(stream, manager), m_cancel(0) {
+        m_rrDepth = stream->readInt();
+        m_maxDepth = stream->readInt();
+        m_strictNormals = stream->readBool();
+        m_hideEmitters = stream->readBool();
+        m_device = stream->readInt();
+        m_seed = stream->readUInt();
+    }
+
+    void serialize(Stream *stream, InstanceManager *manager) const {
+        Integrator::serialize(stream, manager);
+        stream->writeInt(m_rrDepth);
+        stream->writeInt(m_maxDepth);
+        stream->writeBool(m_strictNormals);
+        stream->writeBool(m_hideEmitters);
+        stream->writeInt(m_device);
+        stream->writeUInt(m_seed);
+    }
+
+    void cancel() { m_cancel = 1; }   /* may arrive from another thread (scene.cpp:451-456) */
+
+    bool render(Scene *scene, RenderQueue *queue, const RenderJob *job, int sceneResID, int sensorResID, int samplerResID) {
+        m_cancel = 0;
+        MtsContext *ctx = NULL;
+        check(NULL, mtscuda_create(m_device, &ctx));
+        bool ok = false;
+        try {
+            Flattener f(this, ctx);
+            f.run(scene);
+            check(ctx, mtscuda_build(ctx));
+
+            Film *film = scene->getFilm();
+            const Vector2i size = film->getCropSize();
+            MtsRenderParams p;
+            memset(&p, 0, sizeof(p));
+            p.spp = (int32_t) scene->getSampler()->getSampleCount();
+            p.sample_offset = 0; p.sample_stride = 1;
+            p.max_depth = m_maxDepth; p.rr_depth = m_rrDepth;
+            p.strict_normals = m_strictNormals; p.hide_emitters = m_hideEmitters;
+            p.seed = m_seed; p.clear_film = 1;
+            Log(EInfo, "Starting render job (%ix%i, " SIZE_T_FMT " samples, CUDA device %i) ..", size.x, size.y,
+                scene->getSampler()->getSampleCount(), m_device);
+            MtsStats st;
+            int rc = mtscuda_render(ctx, &p, &m_cancel, &st);
+            if (rc == MTS_ECANCELLED) {
+                Log(EWarn, "Rendering was cancelled");
+            } else {
+                check(ctx, rc);
+                statLaunches += st.kernel_launches;
+                Log(EInfo, "cudapath: %.1f ms on the device, %.1f Msamples/s, %.1f Mrays/s (BVH build %.1f ms)",
+                    st.render_ms, st.camera_samples / (st.render_ms * 1e3), (st.normal_rays + st.shadow_rays) / (st.render_ms * 1e3), st.build_ms);
+                /* film: (sum w*R, sum w*G, sum w*B, sum w) -> one ESpectrumAlphaWeight block (hdrfilm.cpp:391-393) */
+                std::vector<float> rgbw((size_t) size.x * size.y * 4);
+                check(ctx, mtscuda_read_film(ctx, rgbw.data()));
+                ref<ImageBlock> block = new ImageBlock(Bitmap::ESpectrumAlphaWeight, size, film->getReconstructionFilter());
+                block->setOffset(film->getCropOffset());
+                block->clear();
+                Bitmap *bmp = block->getBitmap();
+                const int border = block->getBorderSize(), ch = bmp->getChannelCount(), bw = bmp->getWidth();
+                Float *dst = bmp->getFloatData();
+                for (int y = 0; y < size.y; ++y) for (int x = 0; x < size.x; ++x) {
+                    const float *s = &rgbw[4 * ((size_t) y * size.x + x)];
+                    Float *d = dst + ((size_t) (y + border) * bw + (x + border)) * ch;
+                    Spectrum spec; spec.fromLinearRGB(s[0], s[1], s[2]);
+                    for (int k = 0; k < SPECTRUM_SAMPLES; ++k) d[k] = spec[k];
+                    d[SPECTRUM_SAMPLES] = s[3];       /* alpha accumulates w * 1 */
+                    d[SPECTRUM_SAMPLES + 1] = s[3];   /* weight */
+                }
+                film->put(block);
+                ok = true;
+            }
+        } catch (...) {
+            mtscuda_destroy(ctx);
+            throw;
+        }
+        mtscuda_destroy(ctx);
+        return ok;
+    }
+
+    std::string toString() const {
+        std::ostringstream oss;
+        oss << "CudaPath[" << endl << "  maxDepth = " << m_maxDepth << "," << endl << "  rrDepth = " << m_rrDepth << ","
+            << endl << "  strictNormals = " << m_strictNormals << "," << endl << "  device = " << m_device << endl << "]";
+        return oss.str();
+    }
+
+    MTS_DECLARE_CLASS()
+
+private:
+    /* libmtscuda error -> Log(EError) (throws std::runtime_error, src/libcore/logger.cpp:147) */
+    void check(MtsContext *, int rc) const {
+        if (rc < 0)
+            Log(EError, "libmtscuda: %s", mtscuda_last_error());
+    }
+
+    /* ------------------------------------------------------------------------------------------------------- */
+    struct TexInfo { MtsTexRef ref; Spectrum min, max, avg; bool constant; };
+
+    class Flattener {
+    public:
+        Flattener(const CudaPath *owner, MtsContext *ctx) : m_owner(owner), m_ctx(ctx) {}
+
+        void run(const Scene *scene) {
+            sensorAndFilm(scene);
+            /* shapes in Scene::m_shapes order; area emitters are appended after the scene-level emitters, which is
+               the order of Scene::m_emitters (scene.cpp:322-336, 497-516) */
+            const ref_vector<Shape> &shapes = const_cast<Scene *>(scene)->getShapes();
+            std::vector<std::pair<const Emitter *, int> > areaEmitters;
+            std::vector<int> shapeIds(shapes.size());
+            std::vector<int> shapeBsdf(shapes.size());
+            for (size_t i = 0; i < shapes.size(); ++i) {
+                const Shape *s = shapes[i].get();
+                if (s->hasSubsurface() || s->isMediumTransition())
+                    err("subsurface scattering and participating media are out of scope for cudapath");
+                shapeBsdf[i] = bsdf(s->getBSDF());
+            }
+            /* all textures / BSDF nodes are known now */
+            if (!m_pool.empty()) m_owner->check(m_ctx, mtscuda_set_float_pool(m_ctx, m_pool.data(), (int64_t) m_pool.size()));
+            m_owner->check(m_ctx, mtscuda_set_bsdfs(m_ctx, m_nodes.data(), (int32_t) m_nodes.size()));
+            for (size_t i = 0; i < shapes.size(); ++i) {
+                shapeIds[i] = shape(shapes[i].get(), shapeBsdf[i]);
+                if (shapes[i]->isEmitter()) areaEmitters.push_back(std::make_pair(shapes[i]->getEmitter(), shapeIds[i]));
+            }
+            const ref_vector<Emitter> &emitters = const_cast<Scene *>(scene)->getEmitters();
+            for (size_t i = 0; i < emitters.size(); ++i) {
+                const Emitter *e = emitters[i].get();
+                int sid = -1;
+                for (size_t k = 0; k < areaEmitters.size(); ++k) if (areaEmitters[k].first == e) sid = areaEmitters[k].second;
+                emitter(e, sid);
+            }
+        }
+
+    private:
+        void err(const std::string &msg) const { SLog(EError, "cudapath: %s", msg.c_str()); }
+
+        static void toRowMajor(const Transform &t, float *out) {
+            const Matrix4x4 &m = t.getMatrix();
+            for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) out[4 * i + j] = (float) m.m[i][j];
+        }
+
+        /* ---- sensor + film (perspective.cpp:126-178, film.cpp, rfilter.h:76-77) ---- */
+        void sensorAndFilm(const Scene *scene) {
+            const Sensor *sensor = scene->getSensor();
+            if (sensor->getClass()->getName() != "PerspectiveCameraImpl" && !sensor->getClass()->derivesFrom(MTS_CLASS(PerspectiveCamera)))
+                err("a `perspective` sensor is required (sensor class " + sensor->getClass()->getName() + " is out of scope)");
+            const PerspectiveCamera *cam = static_cast<const PerspectiveCamera *>(sensor);
+            const Film *film = sensor->getFilm();
+            const Vector2i filmSize = film->getSize(), cropSize = film->getCropSize();
+            const Point2i cropOffset = film->getCropOffset();
+            const Float aspect = sensor->getAspect();
+            Vector2 relSize((Float) cropSize.x / (Float) filmSize.x, (Float) cropSize.y / (Float) filmSize.y);
+            Point2 relOffset((Float) cropOffset.x / (Float) filmSize.x, (Float) cropOffset.y / (Float) filmSize.y);
+            Transform cameraToSample =
+                  Transform::scale(Vector(1.0f / relSize.x, 1.0f / relSize.y, 1.0f))
+                * Transform::translate(Vector(-relOffset.x, -relOffset.y, 0.0f))
+                * Transform::scale(Vector(-0.5f, -0.5f * aspect, 1.0f))
+                * Transform::translate(Vector(-1.0f, -1.0f / aspect, 0.0f))
+                * Transform::perspective(cam->getXFov(), cam->getNearClip(), cam->getFarClip());
+            Transform sampleToCamera = cameraToSample.inverse();
+            Vector2 invRes(1.0f / cropSize.x, 1.0f / cropSize.y);
+            Vector dx = sampleToCamera(Point(invRes.x, 0.0f, 0.0f)) - sampleToCamera(Point(0.0f));
+            Vector dy = sampleToCamera(Point(0.0f, invRes.y, 0.0f)) - sampleToCamera(Point(0.0f));
+            MtsCamera c;
+            toRowMajor(sampleToCamera, c.sample_to_camera);
+            toRowMajor(cam->getWorldTransform()->eval(0), c.camera_to_world);
+            for (int i = 0; i < 3; ++i) { c.dx[i] = dx[i]; c.dy[i] = dy[i]; }
+            c.near_clip = cam->getNearClip(); c.far_clip = cam->getFarClip();
+            c.inv_resolution[0] = invRes.x; c.inv_resolution[1] = invRes.y;
+            m_owner->check(m_ctx, mtscuda_set_camera(m_ctx, &c));
+
+            if (film->hasAlpha())
+                SLog(EWarn, "cudapath: the film requests an alpha channel; alpha is reported as the filter weight");
+            const ReconstructionFilter *rf = film->getReconstructionFilter();
+            MtsFilm mf;
+            mf.width = cropSize.x; mf.height = cropSize.y; mf.filter_radius = rf->getRadius();
+            for (int i = 0; i <= MTS_FILTER_RESOLUTION; ++i)   /* m_values[i] through the public accessor */
+                mf.filter_table[i] = rf->evalDiscretized((i + 0.5f) * rf->getRadius() / MTS_FILTER_RESOLUTION);
+            mf.filter_table[MTS_FILTER_RESOLUTION] = 0;
+            m_owner->check(m_ctx, mtscuda_set_film(m_ctx, &mf));
+            if (scene->getSampler()->getClass()->getName() != "IndependentSampler")
+                err("sampler class " + scene->getSampler()->getClass()->getName() + " is out of scope (independent)");
+        }
+
+        /* ---- shapes ---- */
+        int shape(const Shape *s, int bsdfIndex) {
+            const std::string cls = s->getClass()->getName();
+            const Properties &props = s->getProperties();
+            if (cls == "Rectangle") {
+                Transform tw = props.getTransform("toWorld", Transform());
+                if (props.getBoolean("flipNormals", false)) tw = tw * Transform::scale(Vector(1, 1, -1));
+                float m[16]; toRowMajor(tw, m);
+                int id = mtscuda_add_rectangle(m_ctx, m, bsdfIndex);
+                m_owner->check(m_ctx, id);
+                return id;
+            } else if (cls == "Sphere") {
+                /* sphere.cpp:100-130: the scale of toWorld is folded into the radius */
+                Transform o2w = props.getTransform("toWorld", Transform()) * Transform::translate(Vector(props.getPoint("center", Point(0.0f))));
+                Float radius = props.getFloat("radius", 1.0f);
+                if (props.hasProperty("toWorld")) {
+                    Float r = o2w(Vector(1, 0, 0)).length();
+                    o2w = o2w * Transform::scale(Vector(1 / r));
+                    radius *= r;
+                }
+                float m[16]; toRowMajor(o2w, m);
+                int id = mtscuda_add_sphere(m_ctx, m, radius, props.getBoolean("flipNormals", false) ? 1 : 0, bsdfIndex);
+                m_owner->check(m_ctx, id);
+                return id;
+            } else if (s->getClass()->derivesFrom(MTS_CLASS(TriMesh))) {
+                const TriMesh *mesh = static_cast<const TriMesh *>(s);
+                MtsMeshDesc d;
+                memset(&d, 0, sizeof(d));
+                d.positions = (const float *) mesh->getVertexPositions();
+                d.normals = mesh->hasVertexNormals() ? (const float *) mesh->getVertexNormals() : NULL;
+                d.texcoords = mesh->hasVertexTexcoords() ? (const float *) mesh->getVertexTexcoords() : NULL;
+                d.indices = (const uint32_t *) mesh->getTriangles();
+                d.tangents = mesh->hasUVTangents() ? (const float *) mesh->getUVTangents() : NULL;
+                d.nverts = (uint32_t) mesh->getVertexCount(); d.ntris = (uint32_t) mesh->getTriangleCount();
+                d.bsdf = bsdfIndex;
+                int id = mtscuda_add_mesh(m_ctx, &d);
+                m_owner->check(m_ctx, id);
+                return id;
+            }
+            err("shape class " + cls + " is out of scope (rectangle, sphere, triangle meshes)");
+            return -1;
+        }
+
+        /* ---- emitters ---- */
+        void emitter(const Emitter *e, int shapeId) {
+            const std::string cls = e->getClass()->getName();
+            const Properties &props = e->getProperties();
+            MtsEmitterDesc d;
+            memset(&d, 0, sizeof(d));
+            d.shape = -1; d.sampling_weight = e->getSamplingWeight(); d.scale = 1;
+            toRowMajor(Transform(), d.to_world);
+            ref<Bitmap> bmp;
+            if (cls == "AreaLight") {
+                if (shapeId < 0) err("area emitter without a shape");
+                d.type = MTS_EMITTER_AREA; d.shape = shapeId;
+                Float r, g, b; props.getSpectrum("radiance", Spectrum::getD65()).toLinearRGB(r, g, b);
+                d.radiance[0] = r; d.radiance[1] = g; d.radiance[2] = b;
+            } else if (cls == "PointEmitter") {
+                d.type = MTS_EMITTER_POINT;
+                Float r, g, b; (props.getSpectrum("intensity", Spectrum::getD65())).toLinearRGB(r, g, b);
+                d.radiance[0] = r; d.radiance[1] = g; d.radiance[2] = b;
+                Point p = e->getWorldTransform()->eval(0)(Point(0.0f));
+                d.position[0] = p.x; d.position[1] = p.y; d.position[2] = p.z;
+            } else if (cls == "EnvironmentMap") {
+                d.type = MTS_EMITTER_ENVMAP;
+                d.scale = props.getFloat("scale", 1.0f);
+                toRowMajor(e->getWorldTransform()->eval(0), d.to_world);
+                bmp = e->getBitmap()->convert(Bitmap::ERGB, Bitmap::EFloat32, 1.0f);   /* level 0 of the MIP map */
+                d.env_width = bmp->getWidth(); d.env_height = bmp->getHeight();
+                d.env_texels = bmp->getFloat32Data();
+            } else
+                err("emitter class " + cls + " is out of scope (area, point, envmap)");
+            m_owner->check(m_ctx, mtscuda_add_emitter(m_ctx, &d));
+        }
+
+        /* ---- materials: parse the serialized object graph ---- */
+        int bsdf(const BSDF *b) {
+            if (!b) err("shape without a BSDF");
+            std::map<const BSDF *, int>::iterator it = m_bsdfIds.find(b);
+            if (it != m_bsdfIds.end()) return it->second;
+            ref<MemoryStream> ms = new MemoryStream();
+            ref<InstanceManager> mgr = new InstanceManager();
+            mgr->serialize(ms, b);
+            ms->seek(0);
+            std::map<uint32_t, int> seen;
+            std::map<uint32_t, TexInfo> tex;   /* object ids are unique per InstanceManager, i.e. per root BSDF */
+            int idx = parseBsdf(ms, seen, tex);
+            m_bsdfIds[b] = idx;
+            return idx;
+        }
+
+        static Spectrum lum3(Float v) { return Spectrum(v); }
+
+        TexInfo constant(const Spectrum &v) {
+            TexInfo t; Float r, g, b; v.toLinearRGB(r, g, b);
+            t.ref.scale[0] = r; t.ref.scale[1] = g; t.ref.scale[2] = b; t.ref.tex = -1;
+            t.min = t.max = t.avg = v; t.constant = true;
+            return t;
+        }
+
+        TexInfo parseTexture(Stream *s, std::map<uint32_t, TexInfo> &seen) {
+            uint32_t id = s->readUInt();
+            if (id == 0) err("missing texture");
+            if (seen.count(id)) return seen[id];
+            std::string cls = s->readString();
+            TexInfo t;
+            if (cls == "ConstantSpectrumTexture") t = constant(Spectrum(s));
+            else if (cls == "ConstantFloatTexture") t = constant(Spectrum(s->readFloat()));
+            else if (cls == "ScalingTexture") {          /* src/textures/scale.cpp:147-151 */
+                t = parseTexture(s, seen);
+                Spectrum sc(s);
+                Float r, g, b; sc.toLinearRGB(r, g, b);
+                t.ref.scale[0] *= r; t.ref.scale[1] *= g; t.ref.scale[2] *= b;
+                t.min *= sc; t.max *= sc; t.avg *= sc;
+            } else if (cls == "BitmapTexture") {         /* src/textures/bitmap.cpp:401-430 */
+                Point2 uvOffset(s); Vector2 uvScale(s);
+                std::string filename = s->readString();
+                uint32_t filterType = s->readUInt(), wrapU = s->readUInt(), wrapV = s->readUInt();
+                Float gamma = s->readFloat();
+                s->readFloat();                          /* maxAnisotropy */
+                std::string channel = s->readString();
+                size_t size = s->readSize();
+                if (!channel.empty()) err("bitmap `channel` selection is not supported by cudapath");
+                ref<MemoryStream> img = new MemoryStream(size);
+                s->copyTo(img, size);
+                img->seek(0);
+                ref<Bitmap> bmp = new Bitmap(Bitmap::EAuto, img);
+                if (gamma != 0) bmp->setGamma(gamma);
+                const bool mono = bmp->getPixelFormat() == Bitmap::ELuminance || bmp->getPixelFormat() == Bitmap::ELuminanceAlpha;
+                ref<Bitmap> lin = bmp->convert(mono ? Bitmap::ELuminance : Bitmap::ERGB, Bitmap::EFloat32, 1.0f);
+                /* EMIPFilterType: ENearest 0, EBilinear 1, ETrilinear 2, EEWA 3 (mipmap.h) */
+                if (filterType > 1)
+                    err("bitmap filterType ewa/trilinear is not supported yet by cudapath (use bilinear or nearest)");
+                MtsTextureDesc d;
+                d.width = lin->getWidth(); d.height = lin->getHeight(); d.channels = mono ? 1 : 3;
+                /* ReconstructionFilter::EBoundaryCondition: EClamp 0, ERepeat 1, EMirror 2, EZero 3, EOne 4 */
+                static const int wrapMap[5] = { MTS_WRAP_CLAMP, MTS_WRAP_REPEAT, MTS_WRAP_MIRROR, MTS_WRAP_ZERO, MTS_WRAP_ONE };
+                d.wrap_u = wrapMap[std::min(wrapU, 4u)]; d.wrap_v = wrapMap[std::min(wrapV, 4u)];
+                d.filter = filterType == 0 ? MTS_FILTER_NEAREST : MTS_FILTER_BILINEAR;
+                d.uv_scale[0] = uvScale.x; d.uv_scale[1] = uvScale.y; d.uv_offset[0] = uvOffset.x; d.uv_offset[1] = uvOffset.y;
+                int tid = mtscuda_add_texture(m_ctx, &d, lin->getFloat32Data());
+                m_owner->check(m_ctx, tid);
+                /* statistics on the half-precision texels the MIP map stores */
+                const float *px = lin->getFloat32Data();
+                const size_t n = (size_t) d.width * d.height;
+                double sum[3] = {0, 0, 0}; float mn[3] = {1e30f, 1e30f, 1e30f}, mx[3] = {-1e30f, -1e30f, -1e30f};
+                for (size_t i = 0; i < n; ++i) for (int c = 0; c < 3; ++c) {
+                    float v = (float) half(px[d.channels == 1 ? i : 3 * i + c]);
+                    sum[c] += v; mn[c] = std::min(mn[c], v); mx[c] = std::max(mx[c], v);
+                }
+                t.ref.scale[0] = t.ref.scale[1] = t.ref.scale[2] = 1; t.ref.tex = tid; t.constant = false;
+                t.min.fromLinearRGB(mn[0], mn[1], mn[2]); t.max.fromLinearRGB(mx[0], mx[1], mx[2]);
+                t.avg.fromLinearRGB((Float) (sum[0] / n), (Float) (sum[1] / n), (Float) (sum[2] / n));
+            } else
+                err("texture class " + cls + " is out of scope (bitmap, scale, constants)");
+            seen[id] = t;
+            return t;
+        }
+
+        /* BSDF::ensureEnergyConservation (src/librender/bsdf.cpp:85-113) */
+        static TexInfo conserve(TexInfo t, Float maxAllowed = 1.0f) {
+            Float actual = t.max.max();
+            if (actual > maxAllowed) {
+                Float sc = 0.99f * (maxAllowed / actual);
+                for (int i = 0; i < 3; ++i) t.ref.scale[i] *= sc;
+                t.min *= sc; t.max *= sc; t.avg *= sc;
+            }
+            return t;
+        }
+
+        int parseBsdf(Stream *s, std::map<uint32_t, int> &seen, std::map<uint32_t, TexInfo> &tex) {
+            uint32_t id = s->readUInt();
+            if (id == 0) err("missing nested BSDF");
+            if (seen.count(id)) return seen[id];
+            std::string cls = s->readString();
+            s->readBool();                               /* BSDF::serialize: m_ensureEnergyConservation */
+            MtsBsdfNode n;
+            memset(&n, 0, sizeof(n));
+            n.child[0] = n.child[1] = -1; n.t0.tex = n.t1.tex = n.t2.tex = -1;
+            const int idx = (int) m_nodes.size();
+            m_nodes.push_back(n);
+            seen[id] = idx;
+            if (cls == "SmoothDiffuse") {
+                TexInfo r = conserve(parseTexture(s, tex));
+                n.type = MTS_BSDF_DIFFUSE; n.t0 = r.ref;
+                n.lobes = r.max.max() > 0 ? MTS_EDIFFUSE_REFLECTION : 0;
+            } else if (cls == "SmoothConductor") {
+                TexInfo r = conserve(parseTexture(s, tex));
+                Spectrum eta(s), k(s);
+                n.type = MTS_BSDF_CONDUCTOR; n.t0 = r.ref; n.lobes = MTS_EDELTA_REFLECTION;
+                setRGB(eta, n.eta); setRGB(k, n.k);
+            } else if (cls == "RoughConductor") {
+                uint32_t type = s->readUInt(); bool sv = s->readBool();
+                TexInfo au = parseTexture(s, tex), av = parseTexture(s, tex), r = conserve(parseTexture(s, tex));
+                Spectrum eta(s), k(s);
+                n.type = MTS_BSDF_ROUGHCONDUCTOR; n.flags = distrFlags(type, sv);
+                n.t0 = r.ref; n.t1 = au.ref; n.t2 = av.ref; n.lobes = MTS_EGLOSSY_REFLECTION;
+                setRGB(eta, n.eta); setRGB(k, n.k);
+            } else if (cls == "SmoothPlastic") {
+                Float eta = s->readFloat(); bool nonlinear = s->readBool();
+                TexInfo sp = conserve(parseTexture(s, tex)), df = conserve(parseTexture(s, tex));
+                n.type = MTS_BSDF_PLASTIC; n.eta[0] = eta; n.t0 = df.ref; n.t1 = sp.ref;
+                if (nonlinear) n.flags |= MTS_BF_NONLINEAR;
+                n.f[0] = fresnelDiffuseReflectance(1 / eta, false);      /* plastic.cpp:193-194 */
+                n.f[1] = fresnelDiffuseReflectance(eta, false);
+                Float dAvg = df.avg.getLuminance(), sAvg = sp.avg.getLuminance();
+                n.f[2] = sAvg / (dAvg + sAvg);
+                n.lobes = MTS_EDELTA_REFLECTION | MTS_EDIFFUSE_REFLECTION;
+            } else if (cls == "RoughPlastic") {
+                uint32_t type = s->readUInt(); bool sv = s->readBool();
+                TexInfo sp = conserve(parseTexture(s, tex)), df = conserve(parseTexture(s, tex)), al = parseTexture(s, tex);
+                Float eta = s->readFloat(); bool nonlinear = s->readBool();
+                n.type = MTS_BSDF_ROUGHPLASTIC; n.flags = distrFlags(type, sv) | (nonlinear ? MTS_BF_NONLINEAR : 0);
+                n.eta[0] = eta; n.t0 = df.ref; n.t1 = sp.ref; n.t2 = al.ref;
+                Float dAvg = df.avg.getLuminance(), sAvg = sp.avg.getLuminance();
+                n.f[2] = sAvg / (dAvg + sAvg);
+                /* roughplastic.cpp:277-298: reduce the transmittance tables to the slices the kernels interpolate */
+                ref<RoughTransmittance> ext = new RoughTransmittance((MicrofacetDistribution::EType) type);
+                ext->checkEta(eta); ext->checkAlpha(al.min.average()); ext->checkAlpha(al.max.average());
+                ref<RoughTransmittance> in = ext->clone();
+                ext->setEta(eta); in->setEta(1 / eta);
+                n.f[0] = ext->getAlphaMin(); n.f[1] = ext->getAlphaMax();
+                n.lut[1] = (int32_t) ext->m_thetaSamples; n.lut[2] = (int32_t) ext->m_alphaSamples;
+                if (al.constant) {
+                    Float alpha = (al.ref.scale[0] + al.ref.scale[1] + al.ref.scale[2]) * (1.0f / 3.0f);
+                    ext->setAlpha(alpha);
+                    n.lut[0] = (int32_t) m_pool.size();
+                    m_pool.insert(m_pool.end(), ext->m_trans, ext->m_trans + ext->m_thetaSamples);
+                    n.f[3] = 1 - in->evalDiffuse(std::max(alpha, (Float) 1e-4f));
+                } else {
+                    n.flags |= MTS_BF_RT_2D;
+                    n.lut[0] = (int32_t) m_pool.size();
+                    m_pool.insert(m_pool.end(), ext->m_trans, ext->m_trans + ext->m_alphaSamples * ext->m_thetaSamples);
+                    n.lut[3] = (int32_t) m_pool.size();
+                    m_pool.insert(m_pool.end(), in->m_diffTrans, in->m_diffTrans + in->m_alphaSamples);
+                }
+                n.lobes = MTS_EGLOSSY_REFLECTION | MTS_EDIFFUSE_REFLECTION;
+            } else if (cls == "SmoothDielectric") {
+                Float eta = s->readFloat();
+                TexInfo r = conserve(parseTexture(s, tex)), t = conserve(parseTexture(s, tex));
+                n.type = MTS_BSDF_DIELECTRIC; n.eta[0] = eta; n.t0 = r.ref; n.t1 = t.ref;
+                n.lobes = MTS_EDELTA_REFLECTION | MTS_EDELTA_TRANSMISSION | MTS_EBACKSIDE;
+            } else if (cls == "SmoothCoating") {
+                Float eta = s->readFloat(), thickness = s->readFloat();
+                int nested = parseBsdf(s, seen, tex);
+                TexInfo sig = parseTexture(s, tex), sp = conserve(parseTexture(s, tex));
+                n.type = MTS_BSDF_COATING; n.eta[0] = eta; n.f[0] = thickness; n.t0 = sig.ref; n.t1 = sp.ref; n.child[0] = nested;
+                Float avgAbsorption = (sig.avg * (-2 * thickness)).exp().average();   /* coating.cpp:181-183 */
+                n.f[2] = 1.0f / (avgAbsorption + 1.0f);
+                n.lobes = m_nodes[nested].lobes | MTS_EDELTA_REFLECTION | MTS_EBACKSIDE;
+            } else if (cls == "BlendBSDF") {
+                TexInfo w = parseTexture(s, tex);
+                int a = parseBsdf(s, seen, tex), b = parseBsdf(s, seen, tex);
+                n.type = MTS_BSDF_BLEND; n.t0 = w.ref; n.child[0] = a; n.child[1] = b;
+                n.lobes = m_nodes[a].lobes | m_nodes[b].lobes;
+            } else if (cls == "BumpMap") {
+                int nested = parseBsdf(s, seen, tex);
+                TexInfo d = parseTexture(s, tex);
+                n.type = MTS_BSDF_BUMPMAP; n.t0 = d.ref; n.child[0] = nested; n.lobes = m_nodes[nested].lobes;
+            } else
+                err("BSDF class " + cls + " is out of scope (diffuse, conductor, roughconductor, plastic, roughplastic, "
+                    "dielectric, coating, blendbsdf, bumpmap)");
+            m_nodes[idx] = n;
+            return idx;
+        }
+
+        static void setRGB(const Spectrum &v, float *out) { Float r, g, b; v.toLinearRGB(r, g, b); out[0] = r; out[1] = g; out[2] = b; }
+        int distrFlags(uint32_t type, bool sampleVisible) const {
+            if (type != MicrofacetDistribution::EBeckmann && type != MicrofacetDistribution::EGGX)
+                err("microfacet distribution is out of scope (beckmann, ggx)");
+            return (type == MicrofacetDistribution::EGGX ? MTS_BF_GGX : 0) | (sampleVisible ? MTS_BF_SAMPLE_VISIBLE : 0);
+        }
+
+        const CudaPath *m_owner;
+        MtsContext *m_ctx;
+        std::vector<MtsBsdfNode> m_nodes;
+        std::vector<float> m_pool;
+        std::map<const BSDF *, int> m_bsdfIds;
+    };
+
+    int m_maxDepth, m_rrDepth, m_device;
+    bool m_strictNormals, m_hideEmitters;
+    uint32_t m_seed;
+    volatile int m_cancel;
+};
+
+MTS_IMPLEMENT_CLASS_S(CudaPath, false, Integrator)
+MTS_EXPORT_PLUGIN(CudaPath, "B200-native CUDA path tracer");
+MTS_NAMESPACE_END

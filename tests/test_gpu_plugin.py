@@ -1,0 +1,43 @@
+"""The drop-in boundary for real: plugin/cudapath.cpp, compiled against the reference sources (oracle/_ref), is loaded
+by the REFERENCE's own PluginManager as <integrator type="cudapath">, flattens the live reference object graph, renders
+through libmtscuda on the GPU and hands the film back through Film::put -- the unchanged reference then develops it.
+Compared with the reference's own `path` renders (tests/golden/images.npz)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import mts_b200 as M
+import golden_io as G
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle", "refbuild"))
+import mtsref  # noqa: E402
+
+needs_ref = pytest.mark.skipif(not os.path.exists(os.path.join(mtsref.REF_DIR, "plugins", "cudapath.so")),
+                               reason="oracle/_ref (reference build + cudapath.so) is not present")
+
+
+@needs_ref
+@pytest.mark.parametrize("name,bar", [("cornell", 1e-3), ("zoo", 1.5e-2), ("terrain", 1e-3), ("spheres", 5e-3)])
+def test_cudapath_plugin_in_reference_host(name, bar):
+    gold = G.load("images.npz")
+    sc = G.IMAGE_SCENES[name]()
+    rs = mtsref.RefScene(sc, integrator="cudapath")          # the reference's Scene + RenderJob drive our plugin
+    img = M.develop(rs.render())
+    ref = gold["image/%s/rgb" % name].astype(np.float32)
+    assert np.isfinite(img).all() and img.mean() > 0
+    err = M.rel_mse(img, ref)
+    print("cudapath.so inside the reference host: relMSE(%s) = %.3g" % (name, err))
+    assert abs(img.mean() / ref.mean() - 1) < 0.02
+    assert err < bar, (name, err)
+
+
+@needs_ref
+def test_cudapath_plugin_parameter_errors():
+    sc = G.cornell_small(spp=1)
+    sc.child("integrator").props["rrDepth"] = 0
+    with pytest.raises(mtsref.RefError, match="rrDepth"):
+        mtsref.RefScene(sc, integrator="cudapath")
