@@ -107,7 +107,8 @@ ABI_SYMBOLS = [
 ]
 
 LIB_PATHS = {
-    "cuda": os.path.join(_HERE, "csrc", "libmtscuda.so"),
+    # MTS_CUDA_LIB selects an experimental build of the same library (kernel tuning sweeps); never a different back end
+    "cuda": os.environ.get("MTS_CUDA_LIB") or os.path.join(_HERE, "csrc", "libmtscuda.so"),
     "oracle": os.path.join(_ROOT, "oracle", "libmtsoracle.so"),
 }
 PREFIX = {"cuda": "mtscuda_", "oracle": "mtsoracle_"}

@@ -16,27 +16,60 @@ constexpr int kMaxBsdfDepth = 4;  // wrapper nesting levels supported above a le
 // ---------------------------------------------------------------------------------------
 // Textures: TMIPMap level 0 (include/mitsuba/render/mipmap.h:503-626)
 // ---------------------------------------------------------------------------------------
-DEVFN bool wrapCoord(int &x, int size, int mode, float &constant) {
-    if (x < 0 || x >= size) {
-        switch (mode) {
-            case MTS_WRAP_REPEAT: x = wrapRepeat(x, size); break;
-            case MTS_WRAP_CLAMP: x = clampi(x, 0, size - 1); break;
-            case MTS_WRAP_MIRROR: x = modulo(x, 2 * size); if (x >= size) x = 2 * size - x - 1; break;
-            case MTS_WRAP_ZERO: constant = 0.0f; return false;
-            default: constant = 1.0f; return false;
-        }
+// evalTexel coordinate handling (mipmap.h:503-563): returns the wrapped coordinate, or -1 / -2 when the lookup
+// yields the constant 0 / 1 (EZero / EOne boundary conditions)
+DEVFN int wrapCoord(int x, int size, int mode) {
+    if (x >= 0 && x < size) return x;
+    switch (mode) {
+        case MTS_WRAP_REPEAT: return wrapRepeat(x, size);
+        case MTS_WRAP_CLAMP: return clampi(x, 0, size - 1);
+        case MTS_WRAP_MIRROR: { int m = wrapRepeat(x, 2 * size); return m >= size ? 2 * size - m - 1 : m; }
+        case MTS_WRAP_ZERO: return -1;
+        default: return -2;
     }
-    return true;
+}
+// The four texels of a bilinear footprint.  Coordinates are wrapped once per row / column and all four loads are
+// issued back to back (one round trip to L2/HBM instead of four dependent ones).
+struct Quad { float3 p00, p10, p01, p11; };
+DEVFN Quad texQuad(const DTexture &t, int x0, int y0) {
+    const int xa = wrapCoord(x0, t.width, t.wrapU), xb = wrapCoord(x0 + 1, t.width, t.wrapU);
+    const int ya = wrapCoord(y0, t.height, t.wrapV), yb = wrapCoord(y0 + 1, t.height, t.wrapV);
+    const int cxa = max(xa, 0), cxb = max(xb, 0), cya = max(ya, 0), cyb = max(yb, 0);
+    const size_t i00 = (size_t)cya * t.width + cxa, i10 = (size_t)cya * t.width + cxb,
+                 i01 = (size_t)cyb * t.width + cxa, i11 = (size_t)cyb * t.width + cxb;
+    Quad q;
+    if (t.channels == 1) {
+        const __half h00 = __ldg(t.texels + i00), h10 = __ldg(t.texels + i10), h01 = __ldg(t.texels + i01), h11 = __ldg(t.texels + i11);
+        q.p00 = f3(__half2float(h00)); q.p10 = f3(__half2float(h10)); q.p01 = f3(__half2float(h01)); q.p11 = f3(__half2float(h11));
+    } else {
+        const uint2 *tx = reinterpret_cast<const uint2 *>(t.texels);
+        const uint2 r00 = __ldg(tx + i00), r10 = __ldg(tx + i10), r01 = __ldg(tx + i01), r11 = __ldg(tx + i11);
+        auto cvt = [](uint2 raw) {
+            float2 fa = __half22float2(*reinterpret_cast<const __half2 *>(&raw.x)), fb = __half22float2(*reinterpret_cast<const __half2 *>(&raw.y));
+            return f3(fa.x, fa.y, fb.x);
+        };
+        q.p00 = cvt(r00); q.p10 = cvt(r10); q.p01 = cvt(r01); q.p11 = cvt(r11);
+    }
+    // EZero / EOne boundary conditions (rare): a coordinate outside the image yields the constant
+    const int bx0 = xa < 0 ? xa : 0, bx1 = xb < 0 ? xb : 0, by0 = ya < 0 ? ya : 0, by1 = yb < 0 ? yb : 0;
+    if (bx0 | bx1 | by0 | by1) {
+        auto konst = [](int cx, int cy) { return f3((cx == -2 || (cx == 0 && cy == -2)) ? 1.0f : 0.0f); };  // u is tested first
+        if (bx0 | by0) q.p00 = konst(bx0, by0);
+        if (bx1 | by0) q.p10 = konst(bx1, by0);
+        if (bx0 | by1) q.p01 = konst(bx0, by1);
+        if (bx1 | by1) q.p11 = konst(bx1, by1);
+    }
+    return q;
 }
 DEVFN float3 texel(const DTexture &t, int x, int y) {
-    float c;
-    if (!wrapCoord(x, t.width, t.wrapU, c)) return f3(c);
-    if (!wrapCoord(y, t.height, t.wrapV, c)) return f3(c);
-    size_t i = (size_t)y * t.width + x;
+    const int xa = wrapCoord(x, t.width, t.wrapU);
+    if (xa < 0) return f3(xa == -2 ? 1.0f : 0.0f);
+    const int ya = wrapCoord(y, t.height, t.wrapV);
+    if (ya < 0) return f3(ya == -2 ? 1.0f : 0.0f);
+    size_t i = (size_t)ya * t.width + xa;
     if (t.channels == 1) return f3(__half2float(__ldg(t.texels + i)));
     uint2 raw = __ldg(reinterpret_cast<const uint2 *>(t.texels) + i);
-    __half2 a = *reinterpret_cast<__half2 *>(&raw.x), b = *reinterpret_cast<__half2 *>(&raw.y);
-    float2 fa = __half22float2(a), fb = __half22float2(b);
+    float2 fa = __half22float2(*reinterpret_cast<__half2 *>(&raw.x)), fb = __half22float2(*reinterpret_cast<__half2 *>(&raw.y));
     return f3(fa.x, fa.y, fb.x);
 }
 // evalBilinear(0, uv) / evalBox(0, uv), mipmap.h:566-596
@@ -47,8 +80,8 @@ DEVFN float3 texLookup(const DTexture &t, float2 uv) {
     float u = uv.x * t.width - 0.5f, v = uv.y * t.height - 0.5f;
     int xPos = floorToInt(u), yPos = floorToInt(v);
     float dx1 = u - xPos, dx2 = 1.0f - dx1, dy1 = v - yPos, dy2 = 1.0f - dy1;
-    return texel(t, xPos, yPos) * dx2 * dy2 + texel(t, xPos, yPos + 1) * dx2 * dy1 +
-           texel(t, xPos + 1, yPos) * dx1 * dy2 + texel(t, xPos + 1, yPos + 1) * dx1 * dy1;
+    const Quad q = texQuad(t, xPos, yPos);
+    return q.p00 * dx2 * dy2 + q.p01 * dx2 * dy1 + q.p10 * dx1 * dy2 + q.p11 * dx1 * dy1;
 }
 // evalGradientBilinear(0, uv), mipmap.h:601-626
 DEVFN void texGradient(const DTexture &t, float2 uv, float3 &g0, float3 &g1) {
@@ -56,11 +89,10 @@ DEVFN void texGradient(const DTexture &t, float2 uv, float3 &g0, float3 &g1) {
     float u = uv.x * t.width - 0.5f, v = uv.y * t.height - 0.5f;
     int xPos = floorToInt(u), yPos = floorToInt(v);
     float dx = u - xPos, dy = v - yPos;
-    float3 p00 = texel(t, xPos, yPos), p10 = texel(t, xPos + 1, yPos);
-    float3 p01 = texel(t, xPos, yPos + 1), p11 = texel(t, xPos + 1, yPos + 1);
-    float3 tmp = p01 + p10 - p11;
-    g0 = (p10 + p00 * (dy - 1) - tmp * dy) * (float)t.width;
-    g1 = (p01 + p00 * (dx - 1) - tmp * dx) * (float)t.height;
+    const Quad q = texQuad(t, xPos, yPos);
+    float3 tmp = q.p01 + q.p10 - q.p11;
+    g0 = (q.p10 + q.p00 * (dy - 1) - tmp * dy) * (float)t.width;
+    g1 = (q.p01 + q.p00 * (dx - 1) - tmp * dx) * (float)t.height;
 }
 // Texture2D::eval (src/librender/texture.cpp:104-114) + ScalingTexture (src/textures/scale.cpp:86-88)
 DEVFN float3 evalTex(const DScene &S, const MtsTexRef &r, float2 uv) {

@@ -65,8 +65,17 @@ DEVFN float safe_acos(float v) { return acosf(fminf(1.0f, fmaxf(-1.0f, v))); }
 DEVFN float signum(float v) { return copysignf(1.0f, v); }
 DEVFN int floorToInt(float v) { return (int)floorf(v); }
 DEVFN int modulo(int a, int b) { int r = a % b; return (r < 0) ? r + b : r; }
-// modulo(x, size) for texture wrapping; power-of-two sizes (the common case) avoid the integer division
-DEVFN int wrapRepeat(int x, int size) { return (size & (size - 1)) == 0 ? (x & (size - 1)) : modulo(x, size); }
+// modulo(x, size) for texture wrapping (result in [0, size)).  Power-of-two sizes use a mask; other sizes use a
+// float reciprocal with an exact integer correction (texel coordinates are far below 2^23), so no integer division
+// is ever executed, whichever side the compiler predicates.
+DEVFN int wrapRepeat(int x, int size) {
+    if ((size & (size - 1)) == 0) return x & (size - 1);
+    int q = __float2int_rd((float)x * (1.0f / (float)size));
+    int r = x - q * size;
+    if (r < 0) r += size;
+    if (r >= size) r -= size;
+    return r;
+}
 DEVFN int clampi(int v, int lo, int hi) { return min(hi, max(lo, v)); }
 
 // src/libcore/math.cpp:74-87

@@ -214,28 +214,29 @@ DEVFN void fillHit(const DScene &S, float3 o, float3 d, const RayHit &rh, Hit &i
         size_t gt = (size_t)s.triOffset + tri;
         uint32_t i0 = __ldg(S.indices + 3 * gt), i1 = __ldg(S.indices + 3 * gt + 1), i2 = __ldg(S.indices + 3 * gt + 2);
         float bx = 1 - rh.u - rh.v, by = rh.u, bz = rh.v;
+        // All per-vertex / per-triangle attribute arrays are index-aligned with the positions (zeros where a mesh has
+        // none), so every gather is issued unconditionally and back to back -- one memory round trip -- and the
+        // shape flags only select what is used.
         float3 q0 = loadF3(S.positions, i0), q1 = loadF3(S.positions, i1), q2 = loadF3(S.positions, i2);
+        float3 n0 = loadF3(S.normals, i0), n1 = loadF3(S.normals, i1), n2 = loadF3(S.normals, i2);
+        float2 t0 = __ldg(reinterpret_cast<const float2 *>(S.texcoords) + i0), t1 = __ldg(reinterpret_cast<const float2 *>(S.texcoords) + i1),
+               t2 = __ldg(reinterpret_cast<const float2 *>(S.texcoords) + i2);
+        float3 tgu = loadF3(S.tangents, 2 * (uint32_t)gt), tgv = loadF3(S.tangents, 2 * (uint32_t)gt + 1);
         its.p = q0 * bx + q1 * by + q2 * bz;
         float3 side1 = q1 - q0, side2 = q2 - q0;
         float3 faceNormal = cross(side1, side2);
         float len = length(faceNormal);
         if (!isZero(faceNormal)) faceNormal = faceNormal / len;
-        if (s.flags & 4) {
-            its.dpdu = loadF3(S.tangents, 2 * (uint32_t)gt);
-            its.dpdv = loadF3(S.tangents, 2 * (uint32_t)gt + 1);
-        } else { its.dpdu = side1; its.dpdv = side2; }
+        if (s.flags & 4) { its.dpdu = tgu; its.dpdv = tgv; }
+        else { its.dpdu = side1; its.dpdv = side2; }
         float3 shN;
         if (s.flags & 1) {
-            shN = normalize(loadF3(S.normals, i0) * bx + loadF3(S.normals, i1) * by + loadF3(S.normals, i2) * bz);
+            shN = normalize(n0 * bx + n1 * by + n2 * bz);
             if (dot(faceNormal, shN) < 0) faceNormal = -faceNormal;
         } else shN = faceNormal;
         its.geoN = faceNormal;
-        if (s.flags & 2) {
-            float2 t0 = make_float2(__ldg(S.texcoords + 2 * (size_t)i0), __ldg(S.texcoords + 2 * (size_t)i0 + 1));
-            float2 t1 = make_float2(__ldg(S.texcoords + 2 * (size_t)i1), __ldg(S.texcoords + 2 * (size_t)i1 + 1));
-            float2 t2 = make_float2(__ldg(S.texcoords + 2 * (size_t)i2), __ldg(S.texcoords + 2 * (size_t)i2 + 1));
-            its.uv = make_float2(t0.x * bx + t1.x * by + t2.x * bz, t0.y * bx + t1.y * by + t2.y * bz);
-        } else its.uv = make_float2(by, bz);
+        if (s.flags & 2) its.uv = make_float2(t0.x * bx + t1.x * by + t2.x * bz, t0.y * bx + t1.y * by + t2.y * bz);
+        else its.uv = make_float2(by, bz);
         its.sh = shadingFrame(shN, its.dpdu);
     } else if (type == 1) {
         its.prim = 0;

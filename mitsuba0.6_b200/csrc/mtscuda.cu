@@ -738,7 +738,7 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
     cudaEventRecord(ev0, st);
 
     const int shadeMinB = getenv("MTS_SHADE_MINB") ? atoi(getenv("MTS_SHADE_MINB")) : 4;
-    const int gridTrace = c->numSMs * 8, gridShade = c->numSMs * 4, gridWide = c->numSMs * 8;
+    const int gridTrace = c->numSMs * TRACE_MINB, gridShade = c->numSMs * 4, gridWide = c->numSMs * 8;
     uint64_t launches = 0, normalRays = 0, shadowRays = 0;
     Counters hc;
     bool cancelled = false;

@@ -119,7 +119,13 @@ DEVFN uint32_t keyedAppend(uint32_t *counters, uint32_t key) {
 // Every warp keeps 32 traversals in flight: lanes whose ray has finished pull the next ray index from a global
 // cursor (one atomicAdd per warp) as soon as fewer than kRefillBelow lanes are still busy, instead of idling
 // until the slowest ray of the warp is done.  LOAD(i, traversal) starts ray i, DONE(i, traversal) consumes it.
-constexpr int kRefillBelow = 24;
+#ifndef TRACE_MINB
+#define TRACE_MINB 8
+#endif
+#ifndef REFILL_BELOW
+#define REFILL_BELOW 24
+#endif
+constexpr int kRefillBelow = REFILL_BELOW;
 
 template <bool ANY, bool COUNT, class Load, class Done>
 DEVFN void traceQueue(const DScene &S, uint32_t count, uint32_t *cursor, TraceCounters *tc, Load load, Done done) {
@@ -157,7 +163,7 @@ DEVFN void traceQueue(const DScene &S, uint32_t count, uint32_t *cursor, TraceCo
 // ---- intersect: Scene::rayIntersect -> ShapeKDTree::rayIntersect(ray, its) --------------------
 // Also emits the shade sort key of every ray (0 = escaped, 1 + BSDF root of the hit shape) and its histogram.
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_intersect(const DScene S, const Wavefront W, int qsel) {
+__global__ void __launch_bounds__(128, TRACE_MINB) k_intersect(const DScene S, const Wavefront W, int qsel) {
     const uint32_t count = W.ctr->qCount[qsel];
     TraceCounters tc = {0, 0};
     const uint32_t *queue = W.queue[qsel];
@@ -184,7 +190,7 @@ __global__ void __launch_bounds__(128) k_intersect(const DScene S, const Wavefro
 
 // ---- shadow: ShapeKDTree::rayIntersect(ray) for Scene::sampleEmitterDirect --------------------
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_shadow(const DScene S, const Wavefront W) {
+__global__ void __launch_bounds__(128, TRACE_MINB) k_shadow(const DScene S, const Wavefront W) {
     const uint32_t count = W.ctr->shadowCount;
     TraceCounters tc = {0, 0};
     traceQueue<true, COUNT>(S, count, &W.ctr->cursor[1], &tc,
