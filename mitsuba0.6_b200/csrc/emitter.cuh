@@ -109,8 +109,10 @@ DEVFN float3 envTexel(const DEnvmap &e, int x, int y) {  // repeat-u / clamp-v (
     float2 fa = __half22float2(*reinterpret_cast<__half2 *>(&raw.x)), fb = __half22float2(*reinterpret_cast<__half2 *>(&raw.y));
     return f3(fa.x, fa.y, fb.x);
 }
-DEVFN uint32_t envSampleReuse(const float *cdf, uint32_t size, float &sample) {  // :657-662
-    uint32_t lo = 0, hi = size + 1;
+DEVFN uint32_t envSampleReuse(const float *cdf, uint32_t size, float &sample, const uint16_t *guide, int G) {  // :657-662
+    // std::lower_bound over the size+1 CDF entries, started from the guide cell of the sample
+    const int k = min((int)(sample * (float)G), G - 1);
+    uint32_t lo = __ldg(guide + k), hi = __ldg(guide + k + 1);
     while (lo < hi) { uint32_t mid = (lo + hi) >> 1; if (__ldg(cdf + mid) < sample) lo = mid + 1; else hi = mid; }
     uint32_t index = min((uint32_t)max((int)lo - 1, 0), size - 1);
     float c0 = __ldg(cdf + index), c1 = __ldg(cdf + index + 1);
@@ -125,8 +127,8 @@ DEVFN void envBilinear(const DEnvmap &e, float px, float py, float3 &value1, flo
 }
 // internalSampleDirection (:567-600)
 DEVFN void envSampleDirection(const DEnvmap &e, float2 sample, float3 &d, float3 &value, float &pdf) {
-    uint32_t row = envSampleReuse(e.cdfRows, e.height, sample.y);
-    uint32_t col = envSampleReuse(e.cdfCols + (size_t)row * (e.width + 1), e.width, sample.x);
+    uint32_t row = envSampleReuse(e.cdfRows, e.height, sample.y, e.guideRows, kGuideRows);
+    uint32_t col = envSampleReuse(e.cdfCols + (size_t)row * (e.width + 1), e.width, sample.x, e.guideCols + (size_t)row * (kGuideCols + 1), kGuideCols);
     float posx = (float)col + intervalToTent(sample.x), posy = (float)row + intervalToTent(sample.y);
     float3 value1, value2; int yPos;
     envBilinear(e, posx, posy, value1, value2, yPos);

@@ -651,6 +651,21 @@ MTS_API int mtscuda_build(MtsContext *c) {
         if ((rc = devUpload(c, cdfRows.data(), cdfRows.size(), &E.cdfRows))) return rc;
         if ((rc = devUpload(c, cdfCols.data(), cdfCols.size(), &E.cdfCols))) return rc;
         if ((rc = devUpload(c, rowWeights.data(), rowWeights.size(), &E.rowWeights))) return rc;
+        // guide tables of the two CDF levels: guide[k] = std::lower_bound(cdf, cdf + n + 1, k / G) - cdf
+        auto makeGuide = [](const float *cdf, int n, int G, uint16_t *out) {
+            int pos = 0;
+            for (int k = 0; k <= G; ++k) {
+                const float v = (float)k / (float)G;
+                while (pos <= n && cdf[pos] < v) ++pos;
+                out[k] = (uint16_t)std::min(pos, n);
+            }
+        };
+        if (w > 65534 || h > 65534) return fail(MTS_EINVAL, "Environment maps images must be smaller than 65536 pixels in width and height");
+        std::vector<uint16_t> gRows(kGuideRows + 1), gCols((size_t)h * (kGuideCols + 1));
+        makeGuide(cdfRows.data(), h, kGuideRows, gRows.data());
+        for (int y = 0; y < h; ++y) makeGuide(&cdfCols[(size_t)y * (w + 1)], w, kGuideCols, &gCols[(size_t)y * (kGuideCols + 1)]);
+        if ((rc = devUpload(c, gRows.data(), gRows.size(), &E.guideRows))) return rc;
+        if ((rc = devUpload(c, gCols.data(), gCols.size(), &E.guideCols))) return rc;
         E.width = w; E.height = h; E.scale = he.d.scale;
         E.normalization = 1.0f / (rowSum * (2 * kPi / w) * (kPi / h));
         M4 tw = m4From(he.d.to_world), tl = m4Inverse(tw);
@@ -719,7 +734,7 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
     R.seed = P->seed; R.sampleOffset = P->sample_offset; R.sampleStride = P->sample_stride > 0 ? P->sample_stride : 1;
     R.tilesX = (W + 7) / 8; R.tilesY = (H + 3) / 4; R.paddedPixels = (uint32_t)R.tilesX * R.tilesY * 32u;
     const unsigned long long totalItems = (unsigned long long)R.paddedPixels * (unsigned long long)P->spp;
-    uint32_t cap = P->wavefront_size > 0 ? (uint32_t)P->wavefront_size : (1u << 22);
+    uint32_t cap = P->wavefront_size > 0 ? (uint32_t)P->wavefront_size : (1u << 25);   // 32 Mi path slots (5.5 GB of state): large wavefronts amortise the latency-bound tail bounces
     cap = (uint32_t)std::min<unsigned long long>(std::max<unsigned long long>(totalItems, 32), cap);
     cap = (cap + 31u) & ~31u;
     int rc;
