@@ -124,6 +124,11 @@ DEVFN float adaptiveMinT(float3 o, float mint, bool shadow) {
 // that the queue kernels can refill idle lanes of a warp between steps.  The state is a node group (first
 // child index + pending front-to-back hit bits + inner mask); groups that still hold work are pushed when a
 // nearer child is entered.  ANY = shadow ray (the first hit terminates).
+#ifndef NODE_ITERS
+#define NODE_ITERS 4
+#endif
+constexpr int kNodeIters = NODE_ITERS;
+
 template <bool ANY, bool COUNT>
 struct Traversal {
     float3 o, d, idir;
@@ -150,29 +155,40 @@ struct Traversal {
         return true;
     }
 
-    // one node visit + the primitive tests it produced; returns true when the traversal has finished
+    // "while-while" step: visit nodes until one yields primitive hits (at most kNodeIters visits, so that the lanes of
+    // a warp reach the primitive tests together instead of trickling in one by one), then test those primitives.
+    // Returns true when the traversal has finished.
     DEVFN bool step(const DScene &S, TraceCounters *ctr) {
-        // enter the nearest pending inner child of the current node group
-        const int bit = 31 - __clz((int)ngroup.y);
-        ngroup.y &= ~(1u << bit);
-        const uint32_t slot = (uint32_t)(bit - 24) ^ oct;
-        const uint32_t rel = __popc(ngroup.y & 0xffu & ~(0xffffffffu << slot));
-        const uint32_t nodeIdx = ngroup.x + rel;
-        if ((ngroup.y & 0xff000000u) && sp < 32) stack[sp++] = ngroup;
-        const float4 *np = reinterpret_cast<const float4 *>(S.bvh + nodeIdx);
-        const float4 n0 = __ldg(np);
-        const uint4 n1 = __ldg(reinterpret_cast<const uint4 *>(np + 1)), n2 = __ldg(reinterpret_cast<const uint4 *>(np + 2)),
-                    n3 = __ldg(reinterpret_cast<const uint4 *>(np + 3)), n4 = __ldg(reinterpret_cast<const uint4 *>(np + 4));
-        if (COUNT) ctr->nodes++;
-        const uint32_t hits = wideNodeHits(n0, n1, n2, n3, n4, o, idir, oct, mint, best.t);
-        ngroup = make_uint2(n1.x, (hits & 0xff000000u) | ((uint32_t)__float_as_int(n0.w) >> 24));
-        uint32_t pending = hits & 0x00ffffffu;
+        uint32_t pending = 0, primBase = 0;
+#pragma unroll 1
+        for (int it = 0; it < kNodeIters; ++it) {
+            // enter the nearest pending inner child of the current node group
+            const int bit = 31 - __clz((int)ngroup.y);
+            ngroup.y &= ~(1u << bit);
+            const uint32_t slot = (uint32_t)(bit - 24) ^ oct;
+            const uint32_t rel = __popc(ngroup.y & 0xffu & ~(0xffffffffu << slot));
+            const uint32_t nodeIdx = ngroup.x + rel;
+            if ((ngroup.y & 0xff000000u) && sp < 32) stack[sp++] = ngroup;
+            const float4 *np = reinterpret_cast<const float4 *>(S.bvh + nodeIdx);
+            const float4 n0 = __ldg(np);
+            const uint4 n1 = __ldg(reinterpret_cast<const uint4 *>(np + 1)), n2 = __ldg(reinterpret_cast<const uint4 *>(np + 2)),
+                        n3 = __ldg(reinterpret_cast<const uint4 *>(np + 3)), n4 = __ldg(reinterpret_cast<const uint4 *>(np + 4));
+            if (COUNT) ctr->nodes++;
+            const uint32_t hits = wideNodeHits(n0, n1, n2, n3, n4, o, idir, oct, mint, best.t);
+            ngroup = make_uint2(n1.x, (hits & 0xff000000u) | ((uint32_t)__float_as_int(n0.w) >> 24));
+            pending = hits & 0x00ffffffu; primBase = n1.y;
+            if (pending) break;
+            if ((ngroup.y & 0xff000000u) == 0) {
+                if (sp == 0) return true;
+                ngroup = stack[--sp];
+            }
+        }
         while (pending) {
             const int j = __ffs((int)pending) - 1;
             pending &= pending - 1;
             if (COUNT) ctr->prims++;
             RayHit h;
-            if (primIntersect(S, (int)(n1.y + j), o, d, mint, best.t, h)) {
+            if (primIntersect(S, (int)(primBase + j), o, d, mint, best.t, h)) {
                 if (ANY) { best = h; return true; }
                 if (h.t < best.t || best.prim < 0) best = h;
             }

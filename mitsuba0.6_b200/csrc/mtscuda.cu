@@ -104,6 +104,7 @@ struct MtsContext {
     int device = 0;
     cudaStream_t stream = nullptr, ownStream = nullptr;
     int numSMs = 148;
+    size_t l2Bytes = 0, l2WindowBytes = 0, maxWindow = 0; float l2HitRatio = 0;   // persisting-L2 set-up (0 = off)
     // staged scene
     MtsCamera cam; bool hasCam = false;
     MtsFilm film; bool hasFilm = false;
@@ -373,6 +374,13 @@ MTS_API int mtscuda_create(int device, MtsContext **out) {
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, device));
     c->numSMs = prop.multiProcessorCount;
+    // Opt-in (MTS_L2_WINDOW=1): measured on cfg3 it LOSES 4.5 % -- the traversal gains nothing (its hot nodes already
+    // stay in the 126 MB L2) while the carve-out halves the L2 left to the shade stage.
+    if (getenv("MTS_L2_WINDOW") && prop.persistingL2CacheMaxSize > 0) {
+        c->l2Bytes = std::min<size_t>((size_t)prop.persistingL2CacheMaxSize, (size_t)prop.l2CacheSize / 2);
+        c->maxWindow = (size_t)prop.accessPolicyMaxWindowSize;
+        if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, c->l2Bytes) != cudaSuccess) { c->l2Bytes = 0; cudaGetLastError(); }
+    }
     CUDA_TRY(cudaStreamCreateWithFlags(&c->ownStream, cudaStreamNonBlocking));
     c->stream = c->ownStream;
     *out = c;
@@ -585,6 +593,11 @@ MTS_API int mtscuda_build(MtsContext *c) {
     if (bout.nodes) c->sceneAllocs.push_back(bout.nodes);
     if (bout.prims) c->sceneAllocs.push_back(bout.prims);
     S.bvh = bout.nodes; S.prims = bout.prims; S.numPrims = bin.numPrims;
+    if (c->l2Bytes && bout.numNodes > 0) {
+        // nodes are stored level by level (breadth first), so a prefix window covers the top of the tree
+        c->l2WindowBytes = std::min<size_t>(sizeof(WideNode) * (size_t)bout.numNodes, c->maxWindow);
+        c->l2HitRatio = (float)std::min(1.0, (double)c->l2Bytes / (double)c->l2WindowBytes);
+    }
     // materials
     if ((rc = devUpload(c, c->nodes.data(), c->nodes.size(), &S.nodes))) return rc;
     S.numNodes = (int)c->nodes.size();
@@ -711,6 +724,22 @@ MTS_API int mtscuda_bind_film(MtsContext *c, void *device_ptr) {
     return MTS_OK;
 }
 
+// L2-persisting access window over the wide BVH nodes for the traversal kernels: the top levels of the tree are
+// touched by every ray and should not be evicted by the streaming gathers of the shade stage.
+static void setBvhWindow(MtsContext *c, cudaStream_t st, bool on) {
+    if (!c->l2Bytes) return;
+    cudaStreamAttrValue v;
+    std::memset(&v, 0, sizeof(v));
+    if (on) {
+        v.accessPolicyWindow.base_ptr = (void *)c->ds.bvh;
+        v.accessPolicyWindow.num_bytes = c->l2WindowBytes;
+        v.accessPolicyWindow.hitRatio = c->l2HitRatio;
+        v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    }
+    cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v);
+}
+
 MTS_API int mtscuda_set_stream(MtsContext *c, void *cuda_stream) {
     CUDA_TRY(cudaSetDevice(c->device));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
@@ -753,7 +782,7 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
     cudaEventRecord(ev0, st);
 
     const int shadeMinB = getenv("MTS_SHADE_MINB") ? atoi(getenv("MTS_SHADE_MINB")) : 4;
-    const int gridTrace = c->numSMs * TRACE_MINB, gridShade = c->numSMs * 4, gridWide = c->numSMs * 8;
+    const int gridTrace = c->numSMs * TRACE_MINB, gridWide = c->numSMs * 8;
     uint64_t launches = 0, normalRays = 0, shadowRays = 0;
     Counters hc;
     bool cancelled = false;
@@ -770,8 +799,10 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
             if (cancel && *cancel) { cancelled = true; break; }
             k_reset_bounce<<<1, 1, 0, st>>>(Wf.ctr, cur ^ 1);
             begin(1);
+            setBvhWindow(c, st, true);
             if (P->instrument) k_intersect<true><<<gridTrace, 128, 0, st>>>(S, Wf, cur);
             else k_intersect<false><<<gridTrace, 128, 0, st>>>(S, Wf, cur);
+            setBvhWindow(c, st, false);
             end();
             begin(2);
             k_sort_offsets<<<1, 32, 0, st>>>(Wf);
@@ -785,8 +816,10 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
             }
             end();
             begin(3);
+            setBvhWindow(c, st, true);
             if (P->instrument) k_shadow<true><<<gridTrace, 128, 0, st>>>(S, Wf);
             else k_shadow<false><<<gridTrace, 128, 0, st>>>(S, Wf);
+            setBvhWindow(c, st, false);
             end();
             begin(4); k_splat<<<gridWide, 256, 0, st>>>(S, Wf, R); end();
             launches += 7;
