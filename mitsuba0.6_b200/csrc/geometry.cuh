@@ -65,22 +65,48 @@ DEVFN bool primIntersect(const DScene &S, int slot, float3 o, float3 d, float mi
 
 struct TraceCounters { unsigned nodes, prims; };
 
-DEVFN uint32_t byteOf(uint32_t v, int j) { return (v >> (8 * j)) & 0xffu; }
-// float(byte j of v), exact, without an I2F: the byte is spliced into the mantissa of 2^23 and 2^23 is subtracted
-DEVFN float byteToFloat(uint32_t v, int j) { return __uint_as_float(__byte_perm(v, 0x4B000000u, 0x7540u + j)) - 8388608.0f; }
+DEVFN uint32_t byteOf(uint32_t v, int j) { return __byte_perm(v, 0u, 0x4440u | j); }   // one PRMT
+// 1 + (byte j of v) * 2^-15, exact, in one PRMT: the byte is spliced into mantissa bits 8..15 of 1.0f.  The constant
+// offset is folded into the plane equation below, so decoding a quantised plane costs no floating-point instruction.
+// `one` holds the bits of 1.0f in a register the compiler cannot fold (see wideNodeHits), so that the selector is
+// the PRMT immediate; with a literal 1.0f ptxas spends a MOV per PRMT on the selector instead.
+DEVFN float byteToUnit(uint32_t v, int j, uint32_t one) { return __uint_as_float(__byte_perm(v, one, 0x7604u | (j << 4))); }
+// Blackwell packed fp32 FMA (FFMA2): d = a * (b, b) + c on a register pair -- entry and exit distance of one child
+// slab in one instruction.
+DEVFN float2 ffma2(float qn, float qf, float b, float2 c) {
+    unsigned long long ua, ub, uc, ud;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(ua) : "f"(qn), "f"(qf));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(ub) : "f"(b));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(uc) : "f"(c.x), "f"(c.y));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(ud) : "l"(ua), "l"(ub), "l"(uc));
+    float2 d;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(ud));
+    return d;
+}
 
 // Intersects the ray with the eight quantised child boxes of one wide node and returns the hit mask:
 // bits 24..31 = inner children ordered front to back (bit 24 + (slot ^ oct)), bits 0..23 = primitives of the
 // leaf children that were hit (offsets from the node's first primitive).
+//
+// A child plane sits at origin + q * 2^e (q = 0..255), i.e. at ray distance t = q * a + b with a = 2^e / d and
+// b = (origin - o) / d.  With u = 1 + q * 2^-15 (byteToUnit) this is t = u * A + (b - A), A = a * 2^15.  The
+// subtraction b - A rounds at the magnitude of A (128 node extents), an error of at most 2^-9 of one
+// quantisation step; the entry planes are therefore moved out by delta = |A| * 2^-22 towards the ray origin and the
+// exit planes away from it, which keeps the test conservative (watertight) at no per-child cost.
 DEVFN uint32_t wideNodeHits(const float4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
                             float3 o, float3 idir, uint32_t oct, float tmin, float tmax) {
     const uint32_t ew = (uint32_t)__float_as_int(n0.w);
-    const float sx = __int_as_float((int)((ew & 0xffu) << 23)), sy = __int_as_float((int)(((ew >> 8) & 0xffu) << 23)),
-                sz = __int_as_float((int)(((ew >> 16) & 0xffu) << 23));
-    const float ax = sx * idir.x, ay = sy * idir.y, az = sz * idir.z;
-    const float bx = (n0.x - o.x) * idir.x, by = (n0.y - o.y) * idir.y, bz = (n0.z - o.z) * idir.z;
+    // 2^(e + 15); the builder keeps e + 15 below the exponent range (scene extents are nowhere near 2^112)
+    const float sx = __int_as_float((int)(((ew & 0xffu) + 15u) << 23)), sy = __int_as_float((int)((((ew >> 8) & 0xffu) + 15u) << 23)),
+                sz = __int_as_float((int)((((ew >> 16) & 0xffu) + 15u) << 23));
+    const float Ax = sx * idir.x, Ay = sy * idir.y, Az = sz * idir.z;
+    const float bx = fmaf(n0.x - o.x, idir.x, -Ax), by = fmaf(n0.y - o.y, idir.y, -Ay), bz = fmaf(n0.z - o.z, idir.z, -Az);
+    const float kSlack = 2.3841858e-7f;  // 2^-22
+    const float dx = fabsf(Ax) * kSlack, dy = fabsf(Ay) * kSlack, dz = fabsf(Az) * kSlack;
+    const float2 Bx = make_float2(bx - dx, bx + dx), By = make_float2(by - dy, by + dy), Bz = make_float2(bz - dz, bz + dz);
     const uint32_t oct4 = oct * 0x01010101u;
     const float tmaxS = tmax * 1.0000004f;   // slack: boundary hits are never culled by the box test
+    const uint32_t one = 0x3F800000u | (n1.x >> 31);   // child indices stay below 2^31: always the bits of 1.0f
     uint32_t hitmask = 0;
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
@@ -97,11 +123,11 @@ DEVFN uint32_t wideNodeHits(const float4 n0, const uint4 n1, const uint4 n2, con
         const uint32_t nz = idir.z < 0 ? qhiz : qloz, fz = idir.z < 0 ? qloz : qhiz;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            float t0x = fmaf(byteToFloat(nx, j), ax, bx), t1x = fmaf(byteToFloat(fx, j), ax, bx);
-            float t0y = fmaf(byteToFloat(ny, j), ay, by), t1y = fmaf(byteToFloat(fy, j), ay, by);
-            float t0z = fmaf(byteToFloat(nz, j), az, bz), t1z = fmaf(byteToFloat(fz, j), az, bz);
-            float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
-            float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmaxS));
+            const float2 tx = ffma2(byteToUnit(nx, j, one), byteToUnit(fx, j, one), Ax, Bx);
+            const float2 ty = ffma2(byteToUnit(ny, j, one), byteToUnit(fy, j, one), Ay, By);
+            const float2 tz = ffma2(byteToUnit(nz, j, one), byteToUnit(fz, j, one), Az, Bz);
+            float cmin = fmaxf(fmaxf(tx.x, ty.x), fmaxf(tz.x, tmin));
+            float cmax = fminf(fminf(tx.y, ty.y), fminf(tz.y, tmaxS));
             if (cmin <= cmax) hitmask |= byteOf(childBits4, j) << byteOf(bitIndex4, j);
         }
     }
@@ -145,7 +171,7 @@ struct Traversal {
         mint = adaptiveMinT(o, rayMinT, ANY);
         best.prim = -1; best.t = rayMaxT; best.u = best.v = 0;
         if (S.numPrims == 0 || !(rayMaxT > mint)) { best.t = kInf; return false; }
-        const float tiny = 1e-30f;
+        const float tiny = 1e-24f;   // keeps 2^15 * extent / d finite (wideNodeHits)
         idir = f3(1.0f / (fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x)),
                   1.0f / (fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y)),
                   1.0f / (fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z)));

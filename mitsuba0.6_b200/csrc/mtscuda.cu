@@ -807,6 +807,7 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
             begin(2);
             k_sort_offsets<<<1, 32, 0, st>>>(Wf);
             k_sort_scatter<<<gridWide, 256, 0, st>>>(Wf, cur);
+            k_shade_miss<<<gridWide, 256, 0, st>>>(S, Wf, R, cur);
             switch (shadeMinB) {
             case 3: k_shade<3><<<c->numSMs * 3, 128, 0, st>>>(S, Wf, R, cur); break;
             case 5: k_shade<5><<<c->numSMs * 5, 128, 0, st>>>(S, Wf, R, cur); break;
@@ -822,7 +823,7 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
             setBvhWindow(c, st, false);
             end();
             begin(4); k_splat<<<gridWide, 256, 0, st>>>(S, Wf, R); end();
-            launches += 7;
+            launches += 8;
             CUDA_TRY(cudaMemcpyAsync(&hc, Wf.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
             CUDA_TRY(cudaStreamSynchronize(st));
             normalRays += hc.qCount[cur];

@@ -253,26 +253,6 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
 
     auto finish = [&]() { W.L[slot] = make_float4(L.x, L.y, L.z, 0); W.meta[slot] = make_uint4(meta.x, meta.y, depth | (flags << 16), 0); };
 
-    if (prim < 0) {
-        // the reference bumps rRec.depth only after a valid hit (path.cpp:272-276); `depth` was already
-        // incremented when this ray was queued, so undo that for the path-length statistic
-        if (!first) depth -= 1;
-        // path.cpp:136-143 (camera ray) / :238-248,257-264 (BSDF-sampled ray escaping to the envmap)
-        if (S.hasEnv) {
-            if (first) {
-                if (!R.hideEmitters) L += thr * envEval(S.env, d);
-            } else {
-                float nearT, farT;  // fillDirectSamplingRecord, envmap.cpp:358-374
-                if (bsphereIntersect(S.env, o, d, nearT, farT) && !(nearT > 0) && !(farT < 0)) {
-                    float lumPdf = (flags & PF_PREV_DELTA) ? 0.0f : envPdfDirection(S.env, xfVec(S.env.toLocal, d)) * S.env.prob;
-                    L += thr * envEval(S.env, d) * miWeight(prevPdf, lumPdf);
-                }
-            }
-        }
-        finish();
-        return;
-    }
-
     RayHit rh; rh.t = hv.x; rh.u = hv.y; rh.v = hv.z; rh.prim = prim;
     Hit its;
     fillHit(S, o, d, rh, its);
@@ -357,11 +337,55 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
     out.next = true; out.done = false;
 }
 
+// Escaped rays (sort key 0) are shaded by their own small kernel: no hit record, no BSDF code, 40 registers, full
+// occupancy -- after the first bounce three of four rays of an outdoor scene end here.
+// path.cpp:136-143 (camera ray) / :238-248,257-264 (BSDF-sampled ray escaping to the envmap)
+__global__ void __launch_bounds__(256) k_shade_miss(const DScene S, const Wavefront W, const RenderConst R, int qsel) {
+    const uint32_t total = W.ctr->qCount[qsel];
+    const uint32_t count = W.numKeys > 1 ? min(W.keyCount[W.numKeys + 1], total) : total;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ((count + 31u) & ~31u); i += gridDim.x * blockDim.x) {
+        const bool valid = i < count;
+        uint32_t slot = 0;
+        if (valid) {
+            slot = W.sorted[i];
+            const uint4 meta = W.meta[slot];
+            uint32_t depth = meta.z & 0xffffu;
+            const uint32_t flags = meta.z >> 16;
+            const bool first = depth == 1;
+            // the reference bumps rRec.depth only after a valid hit (path.cpp:272-276); `depth` was already
+            // incremented when this ray was queued, so undo that for the path-length statistic
+            if (!first) depth -= 1;
+            float4 lv = W.L[slot];
+            if (S.hasEnv && !(first && R.hideEmitters)) {
+                const float3 d = f3(W.rayD[slot]);
+                const float3 thr = f3(W.thr[slot]);
+                float3 L = f3(lv);
+                if (first) {
+                    L += thr * envEval(S.env, d);
+                } else {
+                    const float3 o = f3(W.rayO[slot]);
+                    float nearT, farT;  // fillDirectSamplingRecord, envmap.cpp:358-374
+                    if (bsphereIntersect(S.env, o, d, nearT, farT) && !(nearT > 0) && !(farT < 0)) {
+                        float lumPdf = (flags & PF_PREV_DELTA) ? 0.0f : envPdfDirection(S.env, xfVec(S.env.toLocal, d)) * S.env.prob;
+                        L += thr * envEval(S.env, d) * miWeight(lv.w, lumPdf);
+                    }
+                }
+                lv = make_float4(L.x, L.y, L.z, 0);
+            }
+            W.L[slot] = make_float4(lv.x, lv.y, lv.z, 0);
+            W.meta[slot] = make_uint4(meta.x, meta.y, depth | (flags << 16), 0);
+        }
+        uint32_t c = warpAppend(&W.ctr->doneCount, valid);
+        if (valid) W.doneQ[c] = slot;
+    }
+}
+
 template <int MINB>
 __global__ void __launch_bounds__(128, MINB) k_shade(const DScene S, const Wavefront W, const RenderConst R, int qsel) {
     const uint32_t count = W.ctr->qCount[qsel];
-    const uint32_t rounded = (count + 31u) & ~31u;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
+    const uint32_t firstHit = W.numKeys > 1 ? min(W.keyCount[W.numKeys + 1], count) : count;   // keys >= 1; key 0 -> k_shade_miss
+    const uint32_t rounded = firstHit + ((count - firstHit + 31u) & ~31u);
+    for (uint32_t i = firstHit + blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
         ShadeOut out; out.next = out.shadow = out.done = false;
         uint32_t slot = 0;
         if (i < count) {
