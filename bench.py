@@ -85,6 +85,33 @@ def scene_bytes(flat):
     return int(n)
 
 
+def pin_scene(flat):
+    """Re-homes the large host arrays of the flattened scene (vertex/index/tangent buffers, texels) in pinned
+    (page-locked) host memory, so that the H2D copies of the e2e leg run from pinned memory as the bench contract
+    asks.  The arrays stay ordinary numpy views; libmtscuda sees plain host pointers either way."""
+    import torch
+    keep = []
+
+    def pin(a):
+        if not isinstance(a, np.ndarray) or a.nbytes < (1 << 16):
+            return a
+        a = np.ascontiguousarray(a)
+        t = torch.from_numpy(a).pin_memory()
+        keep.append(t)
+        return t.numpy()
+
+    flat.textures = [(d, pin(t)) for d, t in flat.textures]
+    flat.emitters = [(d, pin(t) if t is not None else None) for d, t in flat.emitters]
+    shapes = []
+    for s in flat.shapes:
+        if s[0] == "mesh":
+            s = (s[0], {k: pin(v) for k, v in s[1].items()}) + tuple(s[2:])
+        shapes.append(s)
+    flat.shapes = shapes
+    flat._pinned = keep   # owns the page-locked storage
+    return flat
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
 
@@ -322,6 +349,7 @@ def run_cuda(args):
         gpu.close()
         del gpu
         torch.cuda.synchronize()
+        pin_scene(flat)
         e2e_ms = []
         for i in range(1 + max(1, min(args.steps, 2))):
             sync()

@@ -174,6 +174,8 @@ typedef struct MtsMeshDesc {
     const float *tangents;    /* ntris*6 (dpdu, dpdv; TriMesh::computeUVTangents, src/librender/trimesh.cpp:683-743) or NULL */
     uint32_t nverts, ntris;
     int32_t bsdf;             /* root node index */
+    int32_t uv_tangents;      /* 1: `tangents` is ignored and TriMesh::computeUVTangents (trimesh.cpp:683-743) runs on the
+                                 device from positions/texcoords -- saves the 24 B/triangle upload; 0: use `tangents` */
 } MtsMeshDesc;
 
 /* ---- emitters --------------------------------------------------------------- */

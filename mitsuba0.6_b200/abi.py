@@ -66,7 +66,7 @@ class Film(C.Structure):
 class MeshDesc(C.Structure):
     _fields_ = [("positions", C.c_void_p), ("normals", C.c_void_p), ("texcoords", C.c_void_p),
                 ("indices", C.c_void_p), ("tangents", C.c_void_p),
-                ("nverts", C.c_uint32), ("ntris", C.c_uint32), ("bsdf", C.c_int32)]
+                ("nverts", C.c_uint32), ("ntris", C.c_uint32), ("bsdf", C.c_int32), ("uv_tangents", C.c_int32)]
 
 
 class EmitterDesc(C.Structure):
@@ -231,13 +231,22 @@ class Context:
         arr = (BsdfNode * len(nodes))(*nodes)
         self._check(self.fn["set_bsdfs"](self.h, arr, len(nodes)))
 
-    def add_mesh(self, positions, indices, normals=None, texcoords=None, tangents=None, bsdf=0):
+    def add_mesh(self, positions, indices, normals=None, texcoords=None, tangents=None, bsdf=0, uv_tangents=False):
+        """uv_tangents=True asks for TriMesh::computeUVTangents: on the device for libmtscuda (flag in the descriptor),
+        on the host (hostmath.uv_tangents, the numpy mirror) for the oracle, which takes explicit tangents only."""
         pos = f32(positions, (-1, 3))
         idx = np.ascontiguousarray(indices, dtype=np.uint32).reshape(-1, 3)
         nrm = None if normals is None else f32(normals, (-1, 3))
         uv = None if texcoords is None else f32(texcoords, (-1, 2))
+        flag = 0
+        if uv_tangents and uv is not None and tangents is None:
+            if self.lib._backend == "cuda":
+                flag = 1
+            else:
+                from . import hostmath
+                tangents = hostmath.uv_tangents(pos, uv, idx)
         tg = None if tangents is None else f32(tangents, (-1, 6))
-        d = MeshDesc(ptr(pos), ptr(nrm), ptr(uv), ptr(idx), ptr(tg), pos.shape[0], idx.shape[0], bsdf)
+        d = MeshDesc(ptr(pos), ptr(nrm), ptr(uv), ptr(idx), ptr(tg), pos.shape[0], idx.shape[0], bsdf, flag)
         return self._check(self.fn["add_mesh"](self.h, C.byref(d)))
 
     def add_rectangle(self, to_world, bsdf):

@@ -11,7 +11,13 @@
 
 namespace mts {
 
-constexpr int kMaxBsdfDepth = 4;  // wrapper nesting levels supported above a leaf
+#ifndef BSDF_MAX_DEPTH
+#define BSDF_MAX_DEPTH 4
+#endif
+#ifndef BSDF_NESTED_ATTR
+#define BSDF_NESTED_ATTR __noinline__
+#endif
+constexpr int kMaxBsdfDepth = BSDF_MAX_DEPTH;  // wrapper nesting levels supported above a leaf
 
 // ---------------------------------------------------------------------------------------
 // Textures: TMIPMap level 0 (include/mitsuba/render/mipmap.h:503-626)
@@ -612,7 +618,7 @@ DEVFN float3 coatRefractOut(float eta, float3 wi, float &R) {
 template <int D> struct Bsdf {
     typedef Bsdf<D + 1> Next;
 
-    static __device__ __noinline__ float3 eval(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
+    static __device__ BSDF_NESTED_ATTR float3 eval(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
         const MtsBsdfNode &n = S.nodes[node];
         switch (n.type) {
         case MTS_BSDF_COATING: {  // coating.cpp:221-258
@@ -644,7 +650,7 @@ template <int D> struct Bsdf {
         }
     }
 
-    static __device__ __noinline__ float pdf(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
+    static __device__ BSDF_NESTED_ATTR float pdf(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
         const MtsBsdfNode &n = S.nodes[node];
         switch (n.type) {
         case MTS_BSDF_COATING: {  // coating.cpp:260-296
@@ -677,7 +683,7 @@ template <int D> struct Bsdf {
         }
     }
 
-    static __device__ __noinline__ float3 sample(const DScene &S, int node, const Surf &su, float3 wi, float2 sample, BSample &o) {
+    static __device__ BSDF_NESTED_ATTR float3 sample(const DScene &S, int node, const Surf &su, float3 wi, float2 sample, BSample &o) {
         const MtsBsdfNode &n = S.nodes[node];
         switch (n.type) {
         case MTS_BSDF_COATING: {  // coating.cpp:298-371
@@ -743,13 +749,13 @@ template <int D> struct Bsdf {
 
 // recursion floor: below kMaxBsdfDepth wrappers only leaves are legal (set_bsdfs enforces it)
 template <> struct Bsdf<kMaxBsdfDepth> {
-    static __device__ __noinline__ float3 eval(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
+    static __device__ BSDF_NESTED_ATTR float3 eval(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
         return leafEval(S, S.nodes[node], su.uv, wi, wo, measure);
     }
-    static __device__ __noinline__ float pdf(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
+    static __device__ BSDF_NESTED_ATTR float pdf(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
         return leafPdf(S, S.nodes[node], su.uv, wi, wo, measure);
     }
-    static __device__ __noinline__ float3 sample(const DScene &S, int node, const Surf &su, float3 wi, float2 sample, BSample &o) {
+    static __device__ BSDF_NESTED_ATTR float3 sample(const DScene &S, int node, const Surf &su, float3 wi, float2 sample, BSample &o) {
         return leafSample(S, S.nodes[node], su.uv, wi, sample, o);
     }
 };

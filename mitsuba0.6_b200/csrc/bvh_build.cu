@@ -20,6 +20,7 @@ namespace mts {
 constexpr int NB = 16;            // SAH bins per axis
 constexpr int kMaxLeaf = 3;       // primitives per leaf (a wide-node leaf child encodes 1..3 in unary)
 constexpr float kCostTrav = 1.0f, kCostIsect = 1.2f;
+constexpr int kSmall = 32;        // nodes of at most one primitive per lane are finished by k_small_subtrees
 
 struct BuildNode {
     float lo[3], hi[3];     // box
@@ -160,11 +161,18 @@ __device__ __forceinline__ float halfArea(const float lo[3], const float hi[3]) 
     return dx * dy + dy * dz + dz * dx;
 }
 
-__global__ void k_split(int levelStart, int levelEnd, BuildNode *nodes, const Bin *__restrict__ bins, int *nodeCount) {
+__global__ void k_split(int levelStart, int levelEnd, BuildNode *nodes, const Bin *__restrict__ bins, int *nodeCount,
+                        int *smallList, int *smallCount) {
     int node = levelStart + blockIdx.x * blockDim.x + threadIdx.x;
     if (node >= levelEnd) return;
     BuildNode nd = nodes[node];
     const int count = nd.end - nd.begin;
+    if (count <= kSmall) {
+        // finished for the level-synchronous phase (left = right = -1 since creation); k_small_subtrees builds the
+        // whole subtree of this node with one warp once the large nodes are done
+        if (count > 1) smallList[atomicAdd(smallCount, 1)] = node;
+        return;
+    }
     const Bin *nb = bins + (size_t)(node - levelStart) * 3 * NB;
     float bestCost = INFINITY; int bestAxis = -1, bestBin = -1, bestNL = 0;
     float bLlo[3], bLhi[3], bRlo[3], bRhi[3];
@@ -270,6 +278,121 @@ __global__ void k_scatter(int n, const uint32_t *__restrict__ idxIn, const int *
     else dst = nd.begin + nd.nLeft + ((i - nd.begin) - leftBefore);
     idxOut[dst] = idxIn[i];
     nodeOfOut[dst] = flags[i] ? nd.left : nd.right;
+}
+
+// ---- small subtrees: one warp finishes a node of <= 32 primitives --------------------------------------
+// The level-synchronous passes above touch all n primitives per level, which is wasteful once the open nodes hold
+// a few dozen primitives each (two thirds of the levels of a 10^7-triangle tree).  Here every such node is handed
+// to one warp: the primitives live in shared memory (one per lane), splits are chosen by an exact SAH sweep over the
+// three axes (every primitive's centroid is a candidate plane; ties broken by position, so a split always exists),
+// the partition is a ballot/popc prefix, and the warp recurses over an explicit stack until only leaves remain.
+__global__ void __launch_bounds__(128) k_small_subtrees(const int *__restrict__ smallList, int nSmall, BuildNode *nodes, uint32_t *idx,
+                                                        const float4 *__restrict__ pLo, const float4 *__restrict__ pHi, int *nodeCount) {
+    __shared__ float4 sLo[4][32], sHi[4][32];   // .w of sLo = primitive id bits
+    __shared__ int3 sStack[4][32];
+    const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int w = blockIdx.x * 4 + wib;
+    if (w >= nSmall) return;
+    const unsigned full = 0xffffffffu;
+    const int root = smallList[w];
+    const int b0 = nodes[root].begin, m = nodes[root].end - b0;
+    if (lane < m) {
+        uint32_t p = idx[b0 + lane];
+        float4 l = pLo[p], h = pHi[p];
+        l.w = __uint_as_float(p);
+        sLo[wib][lane] = l; sHi[wib][lane] = h;
+    }
+    int sp = 0;
+    if (lane == 0) sStack[wib][0] = make_int3(root, 0, m);
+    sp = 1;
+    __syncwarp();
+    while (sp > 0) {
+        const int3 top = sStack[wib][--sp];
+        const int nid = top.x, b = top.y, e = top.z, cnt = e - b;
+        if (cnt <= 1) continue;
+        const bool in = lane >= b && lane < e;
+        const float4 myLo = sLo[wib][lane], myHi = sHi[wib][lane];
+        const float myC[3] = {0.5f * (myLo.x + myHi.x), 0.5f * (myLo.y + myHi.y), 0.5f * (myLo.z + myHi.z)};
+        float bestCost = INFINITY; int bestAxis = 0;
+        float bL[6], bR[6]; int bNL = 0;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            float llo[3] = {INFINITY, INFINITY, INFINITY}, lhi[3] = {-INFINITY, -INFINITY, -INFINITY};
+            float rlo[3] = {INFINITY, INFINITY, INFINITY}, rhi[3] = {-INFINITY, -INFINITY, -INFINITY};
+            int nL = 0;
+            for (int j = b; j < e; ++j) {
+                const float4 l = sLo[wib][j], h = sHi[wib][j];   // broadcast reads
+                const float cj = a == 0 ? 0.5f * (l.x + h.x) : (a == 1 ? 0.5f * (l.y + h.y) : 0.5f * (l.z + h.z));
+                const bool left = cj < myC[a] || (cj == myC[a] && j <= lane);
+                if (left) {
+                    llo[0] = fminf(llo[0], l.x); llo[1] = fminf(llo[1], l.y); llo[2] = fminf(llo[2], l.z);
+                    lhi[0] = fmaxf(lhi[0], h.x); lhi[1] = fmaxf(lhi[1], h.y); lhi[2] = fmaxf(lhi[2], h.z);
+                    ++nL;
+                } else {
+                    rlo[0] = fminf(rlo[0], l.x); rlo[1] = fminf(rlo[1], l.y); rlo[2] = fminf(rlo[2], l.z);
+                    rhi[0] = fmaxf(rhi[0], h.x); rhi[1] = fmaxf(rhi[1], h.y); rhi[2] = fmaxf(rhi[2], h.z);
+                }
+            }
+            if (in && nL < cnt) {
+                const float cost = halfArea(llo, lhi) * nL + halfArea(rlo, rhi) * (cnt - nL);
+                if (cost < bestCost) {
+                    bestCost = cost; bestAxis = a; bNL = nL;
+                    for (int k = 0; k < 3; ++k) { bL[k] = llo[k]; bL[3 + k] = lhi[k]; bR[k] = rlo[k]; bR[3 + k] = rhi[k]; }
+                }
+            }
+        }
+        // warp argmin (ties -> lowest lane)
+        float c = bestCost; int who = lane;
+        for (int o = 16; o > 0; o >>= 1) {
+            const float oc = __shfl_xor_sync(full, c, o); const int ow = __shfl_xor_sync(full, who, o);
+            if (oc < c || (oc == c && ow < who)) { c = oc; who = ow; }
+        }
+        // parent box for the leaf criterion of k_split
+        float plo[3], phi[3];
+        for (int k = 0; k < 3; ++k) { plo[k] = __ldcg(&nodes[nid].lo[k]); phi[k] = __ldcg(&nodes[nid].hi[k]); }   // written by lane 0 one level up
+        const float parentArea = fmaxf(halfArea(plo, phi), 1e-30f);
+        const float splitCost = kCostTrav + kCostIsect * c / parentArea, leafCost = kCostIsect * cnt;
+        if (!(c < INFINITY) || (cnt <= kMaxLeaf && leafCost <= splitCost)) {
+            if (cnt <= kMaxLeaf) continue;   // leaf
+            // no finite-cost split (NaN/inf boxes) on a node that is too big for a leaf: halve by position
+            who = b + cnt / 2 - 1; bestAxis = -1;
+        }
+        const int axis = __shfl_sync(full, bestAxis, who & 31);
+        int nL; bool goLeft;
+        if (axis < 0) { nL = cnt / 2; goLeft = lane < b + nL; for (int k = 0; k < 3; ++k) { bL[k] = bR[k] = plo[k]; bL[3 + k] = bR[3 + k] = phi[k]; } }
+        else {
+            const float cs = __shfl_sync(full, axis == 0 ? myC[0] : (axis == 1 ? myC[1] : myC[2]), who);
+            const float mc = axis == 0 ? myC[0] : (axis == 1 ? myC[1] : myC[2]);
+            goLeft = mc < cs || (mc == cs && lane <= who);
+            nL = __shfl_sync(full, bNL, who);
+            for (int k = 0; k < 6; ++k) { bL[k] = __shfl_sync(full, bL[k], who); bR[k] = __shfl_sync(full, bR[k], who); }
+        }
+        const unsigned inMask = __ballot_sync(full, in);
+        const unsigned leftMask = __ballot_sync(full, in && goLeft);
+        const unsigned rightMask = inMask & ~leftMask;
+        const unsigned below = (1u << lane) - 1u;
+        const int dst = goLeft ? b + __popc(leftMask & below) : b + nL + __popc(rightMask & below);
+        __syncwarp();
+        if (in) { sLo[wib][dst] = myLo; sHi[wib][dst] = myHi; }
+        int c0 = 0;
+        if (lane == 0) {
+            c0 = atomicAdd(nodeCount, 2);
+            BuildNode L, R;
+            L.left = L.right = R.left = R.right = -1; L.axis = R.axis = 0; L.splitBin = R.splitBin = -1; L.nLeft = R.nLeft = 0; L.pad = R.pad = 0;
+            for (int k = 0; k < 3; ++k) {
+                L.lo[k] = L.clo[k] = bL[k]; L.hi[k] = L.chi[k] = bL[3 + k];
+                R.lo[k] = R.clo[k] = bR[k]; R.hi[k] = R.chi[k] = bR[3 + k];
+            }
+            L.begin = b0 + b; L.end = b0 + b + nL; R.begin = L.end; R.end = b0 + e;
+            nodes[c0] = L; nodes[c0 + 1] = R;
+            nodes[nid].left = c0; nodes[nid].right = c0 + 1; nodes[nid].axis = max(axis, 0); nodes[nid].nLeft = nL;
+            sStack[wib][sp] = make_int3(c0 + 1, b + nL, e);
+            sStack[wib][sp + 1] = make_int3(c0, b, b + nL);
+        }
+        sp += 2;
+        __syncwarp();
+    }
+    if (lane < m) idx[b0 + lane] = __float_as_uint(sLo[wib][lane].w);
 }
 
 // ---- collapse: binary tree -> eight-wide compressed nodes ----------------------------------------
@@ -422,6 +545,7 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
     BuildNode *nodes = nullptr; int *flags = nullptr, *scan = nullptr, *box = nullptr, *nodeCount = nullptr;
     Bin *bins = nullptr; size_t binCap = 0; void *cubTmp = nullptr; size_t cubBytes = 0;
     PrimSource *src = nullptr; WideNode *wide = nullptr; int *srcNode = nullptr, *primCounter = nullptr;
+    int *smallList = nullptr, *smallCount = nullptr;
     int launches = 0;
     if (n == 0) { out.nodes = nullptr; out.prims = nullptr; out.numNodes = 0; return true; }
     {
@@ -433,6 +557,8 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
     CK(cudaMalloc(&flags, 4 * maxNodes)); CK(cudaMalloc(&scan, 4 * maxNodes));
     CK(cudaMalloc(&box, 4 * 12)); CK(cudaMalloc(&nodeCount, 4));
     CK(cudaMalloc(&src, sizeof(PrimSource) * n));
+    CK(cudaMalloc(&smallList, 4 * ((size_t)n / 2 + 1))); CK(cudaMalloc(&smallCount, 4));
+    CK(cudaMemsetAsync(smallCount, 0, 4, st));
     CK(cub::DeviceScan::ExclusiveSum(nullptr, cubBytes, flags, scan, (int)maxNodes, st));
     CK(cudaMalloc(&cubTmp, cubBytes));
 
@@ -474,7 +600,7 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
         }
         k_clear_bins<<<blocks(nb), 256, 0, st>>>(bins, nb);
         k_bin<<<blocks(n, kBinChunk), 256, 0, st>>>(n, idxA, nodeA, pLo, pHi, nodes, levelStart, bins);
-        k_split<<<blocks(levelEnd - levelStart, 64), 64, 0, st>>>(levelStart, levelEnd, nodes, bins, nodeCount);
+        k_split<<<blocks(levelEnd - levelStart, 64), 64, 0, st>>>(levelStart, levelEnd, nodes, bins, nodeCount, smallList, smallCount);
         k_flags<<<blocks(n), 256, 0, st>>>(n, idxA, nodeA, pLo, pHi, nodes, levelStart, flags);
         CK(cub::DeviceScan::ExclusiveSum(cubTmp, cubBytes, flags, scan, n, st));
         k_scatter<<<blocks(n), 256, 0, st>>>(n, idxA, nodeA, flags, scan, nodes, levelStart, idxB, nodeB);
@@ -486,7 +612,19 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
         levelStart = levelEnd; levelEnd = cnt;
         if ((size_t)cnt > maxNodes) { err = "BVH build: node overflow"; goto fail; }
     }
-    const int nBuild = levelEnd;
+    int nBuild = levelEnd;
+    {
+        int nSmall = 0;
+        CK(cudaMemcpyAsync(&nSmall, smallCount, 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (nSmall > 0) {
+            k_small_subtrees<<<blocks(nSmall, 4), 128, 0, st>>>(smallList, nSmall, nodes, idxA, pLo, pHi, nodeCount);
+            ++launches;
+            CK(cudaMemcpyAsync(&nBuild, nodeCount, 4, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            if ((size_t)nBuild > maxNodes) { err = "BVH build: node overflow"; goto fail; }
+        }
+    }
     // collapse into eight-wide nodes, level by level (the wide tree of 10M triangles is ~10 levels deep)
     {
         const size_t maxWide = (size_t)nBuild / 2 + 2;   // every wide node consumes at least one binary inner node
@@ -523,11 +661,11 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
     out.buildNodes = nBuild;
     }
     cudaFree(pLo); cudaFree(pHi); cudaFree(idxA); cudaFree(idxB); cudaFree(nodeA); cudaFree(nodeB); cudaFree(nodes);
-    cudaFree(flags); cudaFree(scan); cudaFree(box); cudaFree(nodeCount); cudaFree(bins); cudaFree(cubTmp); cudaFree(src); cudaFree(wide); cudaFree(srcNode); cudaFree(primCounter);
+    cudaFree(flags); cudaFree(scan); cudaFree(box); cudaFree(nodeCount); cudaFree(bins); cudaFree(cubTmp); cudaFree(src); cudaFree(wide); cudaFree(srcNode); cudaFree(primCounter); cudaFree(smallList); cudaFree(smallCount);
     return true;
 fail:
     cudaFree(pLo); cudaFree(pHi); cudaFree(idxA); cudaFree(idxB); cudaFree(nodeA); cudaFree(nodeB); cudaFree(nodes);
-    cudaFree(flags); cudaFree(scan); cudaFree(box); cudaFree(nodeCount); cudaFree(bins); cudaFree(cubTmp); cudaFree(src); cudaFree(wide); cudaFree(srcNode); cudaFree(primCounter);
+    cudaFree(flags); cudaFree(scan); cudaFree(box); cudaFree(nodeCount); cudaFree(bins); cudaFree(cubTmp); cudaFree(src); cudaFree(wide); cudaFree(srcNode); cudaFree(primCounter); cudaFree(smallList); cudaFree(smallCount);
     if (out.nodes) cudaFree(out.nodes);
     if (out.prims) cudaFree(out.prims);
     out = BvhBuildOutput();

@@ -207,6 +207,38 @@ __global__ void k_offset_indices(uint32_t *idx, size_t n, uint32_t nverts, uint3
     idx[i] = v + vOff;
 }
 
+// TriMesh::computeUVTangents (src/librender/trimesh.cpp:683-743), one triangle per thread; the products and
+// differences are rounded separately (no FMA contraction) so that the result equals the host computation bit for bit.
+__global__ void k_uv_tangents(const uint32_t *__restrict__ idx, size_t ntris, const float *__restrict__ pos,
+                              const float *__restrict__ uv, float *__restrict__ tang) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ntris) return;
+    const uint32_t i0 = idx[3 * i], i1 = idx[3 * i + 1], i2 = idx[3 * i + 2];
+    const float3 v0 = f3(pos[3 * (size_t)i0], pos[3 * (size_t)i0 + 1], pos[3 * (size_t)i0 + 2]);
+    const float3 v1 = f3(pos[3 * (size_t)i1], pos[3 * (size_t)i1 + 1], pos[3 * (size_t)i1 + 2]);
+    const float3 v2 = f3(pos[3 * (size_t)i2], pos[3 * (size_t)i2 + 1], pos[3 * (size_t)i2 + 2]);
+    const float2 t0 = reinterpret_cast<const float2 *>(uv)[i0], t1 = reinterpret_cast<const float2 *>(uv)[i1], t2 = reinterpret_cast<const float2 *>(uv)[i2];
+    const float3 dP1 = v1 - v0, dP2 = v2 - v0;
+    const float du1 = t1.x - t0.x, dv1 = t1.y - t0.y, du2 = t2.x - t0.x, dv2 = t2.y - t0.y;
+    auto mul = [](float a, float b) { return __fmul_rn(a, b); };
+    auto sub = [](float a, float b) { return __fsub_rn(a, b); };
+    const float3 n = f3(sub(mul(dP1.y, dP2.z), mul(dP1.z, dP2.y)), sub(mul(dP1.z, dP2.x), mul(dP1.x, dP2.z)), sub(mul(dP1.x, dP2.y), mul(dP1.y, dP2.x)));
+    const float len = sqrtf(__fadd_rn(__fadd_rn(mul(n.x, n.x), mul(n.y, n.y)), mul(n.z, n.z)));
+    float3 dpdu = f3(0.0f), dpdv = f3(0.0f);
+    if (len != 0) {
+        const float det = sub(mul(du1, dv2), mul(dv1, du2));
+        if (det == 0) {
+            coordinateSystem(n / len, dpdu, dpdv);
+        } else {
+            const float inv = 1.0f / det;
+            dpdu = f3(mul(sub(mul(dv2, dP1.x), mul(dv1, dP2.x)), inv), mul(sub(mul(dv2, dP1.y), mul(dv1, dP2.y)), inv), mul(sub(mul(dv2, dP1.z), mul(dv1, dP2.z)), inv));
+            dpdv = f3(mul(__fadd_rn(mul(-du2, dP1.x), mul(du1, dP2.x)), inv), mul(__fadd_rn(mul(-du2, dP1.y), mul(du1, dP2.y)), inv), mul(__fadd_rn(mul(-du2, dP1.z), mul(du1, dP2.z)), inv));
+        }
+    }
+    float *o = tang + 6 * i;
+    o[0] = dpdu.x; o[1] = dpdu.y; o[2] = dpdu.z; o[3] = dpdv.x; o[4] = dpdv.y; o[5] = dpdv.z;
+}
+
 // ---- kernels behind the per-function entry points -------------------------------------------
 __global__ void k_hook_sample_rays(const DScene S, int64_t n, const float *sp, float *out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -457,16 +489,20 @@ MTS_API int mtscuda_add_mesh(MtsContext *c, const MtsMeshDesc *m) {
     s.d.type = SHAPE_MESH; s.d.bsdf = m->bsdf; s.d.emitter = -1;
     const uint32_t vOff = (uint32_t)(c->positions.size / 3), tOff = (uint32_t)(c->indices.size / 3);
     s.d.vtxOffset = vOff; s.d.triOffset = tOff; s.d.ntris = m->ntris; s.nverts = m->nverts;
-    s.d.flags = (m->normals ? 1u : 0u) | (m->texcoords ? 2u : 0u) | (m->tangents ? 4u : 0u);
+    const bool deviceTangents = m->uv_tangents == 1 && m->texcoords;
+    s.d.flags = (m->normals ? 1u : 0u) | (m->texcoords ? 2u : 0u) | ((m->tangents || deviceTangents) ? 4u : 0u);
     if (!c->errFlag) { CUDA_TRY(cudaMalloc(&c->errFlag, sizeof(int))); CUDA_TRY(cudaMemsetAsync(c->errFlag, 0, sizeof(int), st)); }
     // the optional per-vertex / per-triangle arrays are kept index-aligned with positions / indices (zeros where absent)
     CUDA_TRY(c->positions.append(m->positions, 3 * (size_t)m->nverts, st));
     CUDA_TRY(c->normals.append(m->normals, 3 * (size_t)m->nverts, st));
     CUDA_TRY(c->texcoords.append(m->texcoords, 2 * (size_t)m->nverts, st));
     CUDA_TRY(c->indices.append(m->indices, 3 * (size_t)m->ntris, st));
-    CUDA_TRY(c->tangents.append(m->tangents, 6 * (size_t)m->ntris, st));
+    CUDA_TRY(c->tangents.append(deviceTangents ? nullptr : m->tangents, 6 * (size_t)m->ntris, st));
     const size_t ni = 3 * (size_t)m->ntris;
     k_offset_indices<<<(unsigned)((ni + 255) / 256), 256, 0, st>>>(c->indices.data + 3 * (size_t)tOff, ni, m->nverts, vOff, c->errFlag);
+    if (deviceTangents)
+        k_uv_tangents<<<(unsigned)((m->ntris + 255) / 256), 256, 0, st>>>(c->indices.data + 3 * (size_t)tOff, m->ntris, c->positions.data,
+                                                                          c->texcoords.data, c->tangents.data + 6 * (size_t)tOff);
     int err = 0;
     CUDA_TRY(cudaMemcpyAsync(&err, c->errFlag, sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));   // also guarantees the caller's buffers have been consumed

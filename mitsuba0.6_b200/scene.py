@@ -772,11 +772,10 @@ def flatten(scene):
                     nrm = hm.vertex_normals(pos, idx)  # TriMesh::computeNormals
                 elif sp.get("flipNormals", False):
                     nrm = -np.asarray(nrm)
-            tang = hm.uv_tangents(pos, uv, idx) if uv is not None else None
             fs.shapes.append(("mesh", dict(positions=np.asarray(pos, dtype=F), indices=np.asarray(idx, dtype=np.uint32),
                                            normals=None if nrm is None else np.asarray(nrm, dtype=F),
                                            texcoords=None if uv is None else np.asarray(uv, dtype=F),
-                                           tangents=tang, bsdf=b)))
+                                           tangents=None, uv_tangents=uv is not None, bsdf=b)))
         else:
             raise Unsupported("shape '%s' is out of scope (rectangle, sphere, cube, serialized/in-memory meshes)" % sp.type)
         sid = len(fs.shapes) - 1
@@ -849,7 +848,8 @@ def upload(fs, ctx):
             ctx.add_sphere(s[1], s[2], s[3], s[4])
         else:
             d = s[1]
-            ctx.add_mesh(d["positions"], d["indices"], d["normals"], d["texcoords"], d["tangents"], d["bsdf"])
+            ctx.add_mesh(d["positions"], d["indices"], d["normals"], d["texcoords"], d["tangents"], d["bsdf"],
+                         uv_tangents=d.get("uv_tangents", False))
     for d, tex in fs.emitters:
         ctx.add_emitter(d, tex)
     ctx.build()

@@ -273,7 +273,10 @@ private:
                 d.normals = mesh->hasVertexNormals() ? (const float *) mesh->getVertexNormals() : NULL;
                 d.texcoords = mesh->hasVertexTexcoords() ? (const float *) mesh->getVertexTexcoords() : NULL;
                 d.indices = (const uint32_t *) mesh->getTriangles();
-                d.tangents = mesh->hasUVTangents() ? (const float *) mesh->getUVTangents() : NULL;
+                /* the reference already holds TriMesh::computeUVTangents' output; the library recomputes the same
+                   values on the device (bit-identical, no FMA contraction) instead of uploading 24 B/triangle */
+                d.tangents = NULL;
+                d.uv_tangents = (mesh->hasUVTangents() && d.texcoords) ? 1 : 0;
                 d.nverts = (uint32_t) mesh->getVertexCount(); d.ntris = (uint32_t) mesh->getTriangleCount();
                 d.bsdf = bsdfIndex;
                 int id = mtscuda_add_mesh(m_ctx, &d);

@@ -21,7 +21,7 @@ for it in range(3):
         if s[0] == "rectangle": ctx.add_rectangle(s[1], s[2])
         elif s[0] == "sphere": ctx.add_sphere(s[1], s[2], s[3], s[4])
         else:
-            d = s[1]; ctx.add_mesh(d["positions"], d["indices"], d["normals"], d["texcoords"], d["tangents"], d["bsdf"])
+            d = s[1]; ctx.add_mesh(d["positions"], d["indices"], d["normals"], d["texcoords"], d["tangents"], d["bsdf"], uv_tangents=d.get("uv_tangents", False))
     t_mesh = time.time() - tt
     tt = time.time()
     for d, tex in flat.emitters: ctx.add_emitter(d, tex)
