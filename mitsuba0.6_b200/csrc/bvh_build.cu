@@ -14,6 +14,10 @@
 #include <cub/device/device_scan.cuh>
 #include <vector>
 #include "bvh_build.h"
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 
 namespace mts {
 
@@ -64,27 +68,35 @@ __global__ void k_init(int n, uint32_t *idx, int *nodeOf) {
     if (i < n) { idx[i] = i; nodeOf[i] = 0; }
 }
 
-// root bounds: block reduce + atomics into an ordered-int box
-__global__ void k_root_bounds(int n, const float4 *__restrict__ pLo, const float4 *__restrict__ pHi, int *box /*12*/) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-    float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
-    if (i < n) {
-        float4 l = pLo[i], h = pHi[i];
-        lo[0] = l.x; lo[1] = l.y; lo[2] = l.z; hi[0] = h.x; hi[1] = h.y; hi[2] = h.z;
-        for (int a = 0; a < 3; ++a) clo[a] = chi[a] = 0.5f * (lo[a] + hi[a]);
+// root bounds: grid-stride accumulation, warp shuffle + shared-memory block reduce, 12 atomics per block into an
+// ordered-int box
+__global__ void __launch_bounds__(256) k_root_bounds(int n, const float4 *__restrict__ pLo, const float4 *__restrict__ pHi, int *box /*12*/) {
+    __shared__ float sred[8][12];
+    float v[12];   // lo, hi, clo, chi
+    for (int a = 0; a < 3; ++a) { v[a] = INFINITY; v[3 + a] = -INFINITY; v[6 + a] = INFINITY; v[9 + a] = -INFINITY; }
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 l = pLo[i], h = pHi[i];
+        const float lo[3] = {l.x, l.y, l.z}, hi[3] = {h.x, h.y, h.z};
+        for (int a = 0; a < 3; ++a) {
+            const float c = 0.5f * (lo[a] + hi[a]);
+            v[a] = fminf(v[a], lo[a]); v[3 + a] = fmaxf(v[3 + a], hi[a]);
+            v[6 + a] = fminf(v[6 + a], c); v[9 + a] = fmaxf(v[9 + a], c);
+        }
     }
-    for (int a = 0; a < 3; ++a) {
+    for (int k = 0; k < 12; ++k) {
+        const bool isMin = (k / 3) % 2 == 0;
         for (int o = 16; o > 0; o >>= 1) {
-            lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
-            hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
-            clo[a] = fminf(clo[a], __shfl_xor_sync(0xffffffffu, clo[a], o));
-            chi[a] = fmaxf(chi[a], __shfl_xor_sync(0xffffffffu, chi[a], o));
+            const float t = __shfl_xor_sync(0xffffffffu, v[k], o);
+            v[k] = isMin ? fminf(v[k], t) : fmaxf(v[k], t);
         }
-        if ((threadIdx.x & 31) == 0) {
-            atomicMin(box + a, ordF(lo[a])); atomicMax(box + 3 + a, ordF(hi[a]));
-            atomicMin(box + 6 + a, ordF(clo[a])); atomicMax(box + 9 + a, ordF(chi[a]));
-        }
+        if ((threadIdx.x & 31) == 0) sred[threadIdx.x >> 5][k] = v[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < 12) {
+        const int k = threadIdx.x; const bool isMin = (k / 3) % 2 == 0;
+        float r = sred[0][k];
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) r = isMin ? fminf(r, sred[w][k]) : fmaxf(r, sred[w][k]);
+        if (isMin) atomicMin(box + k, ordF(r)); else atomicMax(box + k, ordF(r));
     }
 }
 
@@ -129,19 +141,47 @@ __global__ void __launch_bounds__(256) k_bin(int n, const uint32_t *__restrict__
         }
         __syncthreads();
     }
-    for (int i = c0 + threadIdx.x; i < c1; i += blockDim.x) {
-        int node = uniform ? nodeFirst : nodeOf[i];
-        if (node < levelStart) continue;  // finished (leaf) or not part of this level
-        const BuildNode &nd = nodes[node];
-        uint32_t p = idx[i];
-        float4 l = pLo[p], h = pHi[p];
-        float c[3] = {0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z)};
-        int ol[3] = {ordF(l.x), ordF(l.y), ordF(l.z)}, oh[3] = {ordF(h.x), ordF(h.y), ordF(h.z)};
-        Bin *nb = uniform ? sbin : bins + (size_t)(node - levelStart) * 3 * NB;
+    // The primitive order is node-partitioned and spatially coherent, so the 32 primitives of a warp fall into a
+    // handful of (node, bin) pairs: each distinct pair is reduced across the warp with redux.sync (identity values for
+    // the lanes outside the group) and its leader issues the seven atomics -- instead of seven contended atomics per lane.
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    for (int base = c0; base < c1; base += blockDim.x) {
+        const int i = base + threadIdx.x;
+        bool valid = i < c1;
+        int node = -1;
+        if (valid) { node = uniform ? nodeFirst : nodeOf[i]; valid = node >= levelStart; }  // else finished (leaf) / not part of this level
+        float c[3] = {0, 0, 0}; int ol[3] = {0, 0, 0}, oh[3] = {0, 0, 0};
+        float clo[3] = {0, 0, 0}, chi[3] = {0, 0, 0};
+        if (valid) {
+            const BuildNode &nd = nodes[node];
+            const uint32_t p = idx[i];
+            const float4 l = pLo[p], h = pHi[p];
+            c[0] = 0.5f * (l.x + h.x); c[1] = 0.5f * (l.y + h.y); c[2] = 0.5f * (l.z + h.z);
+            ol[0] = ordF(l.x); ol[1] = ordF(l.y); ol[2] = ordF(l.z); oh[0] = ordF(h.x); oh[1] = ordF(h.y); oh[2] = ordF(h.z);
+            for (int a = 0; a < 3; ++a) { clo[a] = nd.clo[a]; chi[a] = nd.chi[a]; }
+        }
+        const long long nodeBase = uniform ? 0 : (long long)(node - levelStart) * 3 * NB;
         for (int a = 0; a < 3; ++a) {
-            Bin *b = nb + a * NB + binOf(c[a], nd.clo[a], nd.chi[a]);
-            atomicAdd(&b->count, 1);
-            for (int k = 0; k < 3; ++k) { atomicMin(&b->lo[k], ol[k]); atomicMax(&b->hi[k], oh[k]); }
+            const long long key = valid ? nodeBase + a * NB + binOf(c[a], clo[a], chi[a]) : -1;
+            unsigned todo = __ballot_sync(full, valid);
+            while (todo) {
+                const int leader = __ffs(todo) - 1;
+                const long long k = __shfl_sync(full, key, leader);
+                const bool mine = valid && key == k;
+                const unsigned grp = __ballot_sync(full, mine);
+                const int l0 = __reduce_min_sync(full, mine ? ol[0] : 0x7fffffff), l1 = __reduce_min_sync(full, mine ? ol[1] : 0x7fffffff),
+                          l2 = __reduce_min_sync(full, mine ? ol[2] : 0x7fffffff);
+                const int h0 = __reduce_max_sync(full, mine ? oh[0] : (int)0x80000000), h1 = __reduce_max_sync(full, mine ? oh[1] : (int)0x80000000),
+                          h2 = __reduce_max_sync(full, mine ? oh[2] : (int)0x80000000);
+                if (lane == leader) {
+                    Bin *b = (uniform ? sbin : bins) + k;
+                    atomicAdd(&b->count, __popc(grp));
+                    atomicMin(&b->lo[0], l0); atomicMin(&b->lo[1], l1); atomicMin(&b->lo[2], l2);
+                    atomicMax(&b->hi[0], h0); atomicMax(&b->hi[1], h1); atomicMax(&b->hi[2], h2);
+                }
+                todo &= ~grp;
+            }
         }
     }
     if (uniform) {
@@ -548,6 +588,10 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
     int *smallList = nullptr, *smallCount = nullptr;
     int launches = 0;
     if (n == 0) { out.nodes = nullptr; out.prims = nullptr; out.numNodes = 0; return true; }
+    const bool trace = getenv("MTS_BUILD_TRACE") != nullptr;
+    auto now = [&]() { if (trace) cudaStreamSynchronize(st); return std::chrono::steady_clock::now(); };
+    auto t0 = now();
+    auto lap = [&](const char *what) { if (!trace) return; auto t1 = now(); fprintf(stderr, "[bvh] %-10s %.2f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count()); t0 = t1; };
     {
     const size_t maxNodes = 2 * (size_t)n + 2;
     CK(cudaMalloc(&pLo, sizeof(float4) * n)); CK(cudaMalloc(&pHi, sizeof(float4) * n));
@@ -562,6 +606,7 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
     CK(cub::DeviceScan::ExclusiveSum(nullptr, cubBytes, flags, scan, (int)maxNodes, st));
     CK(cudaMalloc(&cubTmp, cubBytes));
 
+    lap("alloc");
     // primitive sources + bounds
     for (const auto &m : in.meshes) {
         if (!m.ntris) continue;
@@ -586,10 +631,11 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
         CK(cudaStreamSynchronize(st));
     }
     k_init<<<blocks(n), 256, 0, st>>>(n, idxA, nodeA);
-    k_root_bounds<<<blocks(n), 256, 0, st>>>(n, pLo, pHi, box);
+    k_root_bounds<<<std::min(blocks(n), 148 * 8), 256, 0, st>>>(n, pLo, pHi, box);
     k_set_root<<<1, 1, 0, st>>>(nodes, box, n);
     launches += 3;
 
+    lap("bounds");
     int levelStart = 0, levelEnd = 1;
     while (levelStart < levelEnd) {
         size_t nb = (size_t)(levelEnd - levelStart) * 3 * NB;
@@ -612,6 +658,7 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
         levelStart = levelEnd; levelEnd = cnt;
         if ((size_t)cnt > maxNodes) { err = "BVH build: node overflow"; goto fail; }
     }
+    lap("levels");
     int nBuild = levelEnd;
     {
         int nSmall = 0;
@@ -625,6 +672,7 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
             if ((size_t)nBuild > maxNodes) { err = "BVH build: node overflow"; goto fail; }
         }
     }
+    lap("small");
     // collapse into eight-wide nodes, level by level (the wide tree of 10M triangles is ~10 levels deep)
     {
         const size_t maxWide = (size_t)nBuild / 2 + 2;   // every wide node consumes at least one binary inner node
@@ -659,9 +707,11 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
     for (int a = 0; a < 3; ++a) { out.lo[a] = root.lo[a]; out.hi[a] = root.hi[a]; }
     out.launches = launches;
     out.buildNodes = nBuild;
+    lap("collapse");
     }
     cudaFree(pLo); cudaFree(pHi); cudaFree(idxA); cudaFree(idxB); cudaFree(nodeA); cudaFree(nodeB); cudaFree(nodes);
     cudaFree(flags); cudaFree(scan); cudaFree(box); cudaFree(nodeCount); cudaFree(bins); cudaFree(cubTmp); cudaFree(src); cudaFree(wide); cudaFree(srcNode); cudaFree(primCounter); cudaFree(smallList); cudaFree(smallCount);
+    lap("free");
     return true;
 fail:
     cudaFree(pLo); cudaFree(pHi); cudaFree(idxA); cudaFree(idxB); cudaFree(nodeA); cudaFree(nodeB); cudaFree(nodes);

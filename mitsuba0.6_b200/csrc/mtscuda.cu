@@ -58,7 +58,7 @@ template <class T> struct DevVec {
 
 struct HostEmitter {
     MtsEmitterDesc d;
-    std::vector<float> env;  // rgb floats, half-rounded
+    float *envRaw = nullptr;   // device copy of the caller's rgb float texels (freed after build)
 };
 
 // double-precision 4x4 helpers for the one-off host set-up
@@ -134,6 +134,7 @@ struct MtsContext {
         textures.clear();
         if (errFlag) cudaFree(errFlag);
         errFlag = nullptr;
+        for (auto &e : emitters) { if (e.envRaw) cudaFree(e.envRaw); e.envRaw = nullptr; }
     }
     void freeWavefront() { for (void *p : wfAllocs) cudaFree(p); wfAllocs.clear(); wfCapacity = 0; }
     float4 *filmPtr() const { return filmBound ? filmBound : filmInternal; }
@@ -237,6 +238,55 @@ __global__ void k_uv_tangents(const uint32_t *__restrict__ idx, size_t ntris, co
     }
     float *o = tang + 6 * i;
     o[0] = dpdu.x; o[1] = dpdu.y; o[2] = dpdu.z; o[3] = dpdv.x; o[4] = dpdv.y; o[5] = dpdv.z;
+}
+
+// EnvironmentMap::configure (src/emitters/envmap.cpp:260-329) on the device.  The reference accumulates every CDF
+// sequentially in fp32; one thread per image row reproduces exactly that order (products and sums rounded
+// separately, no FMA contraction), so the tables equal the host computation bit for bit.  The same thread rounds
+// the row's texels to half (TMIPMap storage) and fills the row's guide table.
+__global__ void k_env_rows(const float *__restrict__ raw, int w, int h, const float *__restrict__ rowWeights, __half *__restrict__ tex,
+                           float *__restrict__ cdfCols, float *__restrict__ rowTerm, uint16_t *__restrict__ guideCols, int G) {
+    const int y = blockIdx.x * blockDim.x + threadIdx.x;
+    if (y >= h) return;
+    float *cdf = cdfCols + (size_t)y * (w + 1);
+    float colSum = 0.0f;
+    cdf[0] = 0.0f;
+    for (int x = 0; x < w; ++x) {
+        const size_t i = (size_t)y * w + x;
+        const __half r = __float2half_rn(raw[3 * i]), g = __float2half_rn(raw[3 * i + 1]), b = __float2half_rn(raw[3 * i + 2]);
+        tex[4 * i] = r; tex[4 * i + 1] = g; tex[4 * i + 2] = b; tex[4 * i + 3] = __float2half_rn(0.0f);
+        const float lum = __fadd_rn(__fadd_rn(__fmul_rn(__half2float(r), 0.212671f), __fmul_rn(__half2float(g), 0.715160f)), __fmul_rn(__half2float(b), 0.072169f));
+        colSum = __fadd_rn(colSum, lum);
+        cdf[x + 1] = colSum;
+    }
+    const float normalization = __fdiv_rn(1.0f, colSum);
+    for (int x = 1; x < w; ++x) cdf[x] = __fmul_rn(cdf[x], normalization);
+    cdf[w] = 1.0f;
+    rowTerm[y] = __fmul_rn(colSum, rowWeights[y]);
+    // guide[k] = std::lower_bound(cdf, cdf + w + 1, k / G) - cdf
+    uint16_t *guide = guideCols + (size_t)y * (G + 1);
+    int pos = 0;
+    for (int k = 0; k <= G; ++k) {
+        const float v = __fdiv_rn((float)k, (float)G);
+        while (pos <= w && cdf[pos] < v) ++pos;
+        guide[k] = (uint16_t)min(pos, w);
+    }
+}
+__global__ void k_env_finish(const float *__restrict__ rowTerm, int h, float *__restrict__ cdfRows, uint16_t *__restrict__ guideRows, int G, float *rowSumOut) {
+    if (blockIdx.x || threadIdx.x) return;
+    float rowSum = 0.0f;
+    cdfRows[0] = 0.0f;
+    for (int y = 0; y < h; ++y) { rowSum = __fadd_rn(rowSum, rowTerm[y]); cdfRows[y + 1] = rowSum; }
+    const float normalization = __fdiv_rn(1.0f, rowSum);
+    for (int y = 1; y < h; ++y) cdfRows[y] = __fmul_rn(cdfRows[y], normalization);
+    cdfRows[h] = 1.0f;
+    int pos = 0;
+    for (int k = 0; k <= G; ++k) {
+        const float v = __fdiv_rn((float)k, (float)G);
+        while (pos <= h && cdfRows[pos] < v) ++pos;
+        guideRows[k] = (uint16_t)min(pos, h);
+    }
+    *rowSumOut = rowSum;
 }
 
 // ---- kernels behind the per-function entry points -------------------------------------------
@@ -555,8 +605,11 @@ MTS_API int mtscuda_add_emitter(MtsContext *c, const MtsEmitterDesc *d) {
         if (c->envIndex >= 0) return fail(MTS_EINVAL, "only one environment emitter is allowed");
         if (!d->env_texels || d->env_width <= 0 || d->env_height <= 0) return fail(MTS_EINVAL, "envmap without texels");
         size_t n = (size_t)d->env_width * d->env_height * 3;
-        e.env.resize(n);
-        for (size_t i = 0; i < n; ++i) e.env[i] = __half2float(__float2half_rn(d->env_texels[i]));  // TMIPMap half storage
+        if (d->env_width > 65534 || d->env_height > 65534) return fail(MTS_EINVAL, "Environment maps images must be smaller than 65536 pixels in width and height");
+        CUDA_TRY(cudaSetDevice(c->device));
+        CUDA_TRY(cudaMalloc(&e.envRaw, sizeof(float) * n));   // straight from the caller's buffer; rounded to half on the device
+        CUDA_TRY(cudaMemcpyAsync(e.envRaw, d->env_texels, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
         c->envIndex = (int)c->emitters.size();
     } else if (d->type != MTS_EMITTER_POINT) return fail(MTS_EINVAL, "unsupported emitter type");
     c->emitters.push_back(std::move(e)); c->built = false;
@@ -670,51 +723,28 @@ MTS_API int mtscuda_build(MtsContext *c) {
     if (c->envIndex >= 0) {
         HostEmitter &he = c->emitters[c->envIndex];
         const int w = he.d.env_width, h = he.d.env_height;
-        std::vector<float> cdfCols((size_t)(w + 1) * h), cdfRows(h + 1), rowWeights(h);
-        size_t colPos = 0, rowPos = 0; float rowSum = 0.0f;
-        cdfRows[rowPos++] = 0;
-        for (int y = 0; y < h; ++y) {
-            float colSum = 0;
-            cdfCols[colPos++] = 0;
-            for (int x = 0; x < w; ++x) { colSum += hLum(&he.env[((size_t)y * w + x) * 3]); cdfCols[colPos++] = colSum; }
-            float normalization = 1.0f / colSum;
-            for (int x = 1; x < w; ++x) cdfCols[colPos - x - 1] *= normalization;
-            cdfCols[colPos - 1] = 1.0f;
-            float weight = std::sin((y + 0.5f) * kPi / h);
-            rowWeights[y] = weight;
-            rowSum += colSum * weight;
-            cdfRows[rowPos++] = rowSum;
-        }
-        float normalization = 1.0f / rowSum;
-        for (int y = 1; y < h; ++y) cdfRows[rowPos - y - 1] *= normalization;
-        cdfRows[rowPos - 1] = 1.0f;
+        std::vector<float> rowWeights(h);
+        for (int y = 0; y < h; ++y) rowWeights[y] = std::sin((y + 0.5f) * kPi / h);
+        DEnvmap &E = S.env;
+        if ((rc = devUpload(c, rowWeights.data(), rowWeights.size(), &E.rowWeights))) return rc;
+        auto devAlloc = [&](size_t bytes, void **out) -> int {
+            CUDA_TRY(cudaMalloc(out, bytes)); c->sceneAllocs.push_back(*out); return MTS_OK;
+        };
+        __half *tex = nullptr; float *cdfCols = nullptr, *cdfRows = nullptr, *rowTerm = nullptr; uint16_t *gRows = nullptr, *gCols = nullptr;
+        if ((rc = devAlloc(sizeof(__half) * 4 * (size_t)w * h, (void **)&tex))) return rc;
+        if ((rc = devAlloc(sizeof(float) * (size_t)(w + 1) * h, (void **)&cdfCols))) return rc;
+        if ((rc = devAlloc(sizeof(float) * (size_t)(h + 1), (void **)&cdfRows))) return rc;
+        if ((rc = devAlloc(sizeof(float) * (size_t)(h + 1), (void **)&rowTerm))) return rc;   // [h] receives the total
+        if ((rc = devAlloc(sizeof(uint16_t) * (size_t)(kGuideRows + 1), (void **)&gRows))) return rc;
+        if ((rc = devAlloc(sizeof(uint16_t) * (size_t)h * (kGuideCols + 1), (void **)&gCols))) return rc;
+        k_env_rows<<<(h + 63) / 64, 64, 0, c->stream>>>(he.envRaw, w, h, E.rowWeights, tex, cdfCols, rowTerm, gCols, kGuideCols);
+        k_env_finish<<<1, 32, 0, c->stream>>>(rowTerm, h, cdfRows, gRows, kGuideRows, rowTerm + h);
+        float rowSum = 0.0f;
+        CUDA_TRY(cudaMemcpyAsync(&rowSum, rowTerm + h, sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
         if (rowSum == 0) return fail(MTS_EINVAL, "The environment map is completely black -- this is not allowed.");
         if (!std::isfinite(rowSum)) return fail(MTS_EINVAL, "The environment map contains an invalid floating point value (nan/inf) -- giving up.");
-        std::vector<__half> tex((size_t)w * h * 4);
-        for (size_t i = 0; i < (size_t)w * h; ++i) {
-            for (int k = 0; k < 3; ++k) tex[4 * i + k] = __float2half_rn(he.env[3 * i + k]);
-            tex[4 * i + 3] = __float2half_rn(0.0f);
-        }
-        DEnvmap &E = S.env;
-        if ((rc = devUpload(c, tex.data(), tex.size(), &E.texels))) return rc;
-        if ((rc = devUpload(c, cdfRows.data(), cdfRows.size(), &E.cdfRows))) return rc;
-        if ((rc = devUpload(c, cdfCols.data(), cdfCols.size(), &E.cdfCols))) return rc;
-        if ((rc = devUpload(c, rowWeights.data(), rowWeights.size(), &E.rowWeights))) return rc;
-        // guide tables of the two CDF levels: guide[k] = std::lower_bound(cdf, cdf + n + 1, k / G) - cdf
-        auto makeGuide = [](const float *cdf, int n, int G, uint16_t *out) {
-            int pos = 0;
-            for (int k = 0; k <= G; ++k) {
-                const float v = (float)k / (float)G;
-                while (pos <= n && cdf[pos] < v) ++pos;
-                out[k] = (uint16_t)std::min(pos, n);
-            }
-        };
-        if (w > 65534 || h > 65534) return fail(MTS_EINVAL, "Environment maps images must be smaller than 65536 pixels in width and height");
-        std::vector<uint16_t> gRows(kGuideRows + 1), gCols((size_t)h * (kGuideCols + 1));
-        makeGuide(cdfRows.data(), h, kGuideRows, gRows.data());
-        for (int y = 0; y < h; ++y) makeGuide(&cdfCols[(size_t)y * (w + 1)], w, kGuideCols, &gCols[(size_t)y * (kGuideCols + 1)]);
-        if ((rc = devUpload(c, gRows.data(), gRows.size(), &E.guideRows))) return rc;
-        if ((rc = devUpload(c, gCols.data(), gCols.size(), &E.guideCols))) return rc;
+        E.texels = tex; E.cdfRows = cdfRows; E.cdfCols = cdfCols; E.guideRows = gRows; E.guideCols = gCols;
         E.width = w; E.height = h; E.scale = he.d.scale;
         E.normalization = 1.0f / (rowSum * (2 * kPi / w) * (kPi / h));
         M4 tw = m4From(he.d.to_world), tl = m4Inverse(tw);
