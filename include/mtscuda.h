@@ -66,7 +66,8 @@ enum {
     MTS_BSDF_DIELECTRIC = 5,     /* dielectric.cpp */
     MTS_BSDF_COATING = 6,        /* coating.cpp */
     MTS_BSDF_BLEND = 7,          /* blendbsdf.cpp */
-    MTS_BSDF_BUMPMAP = 8         /* bumpmap.cpp */
+    MTS_BSDF_BUMPMAP = 8,        /* bumpmap.cpp */
+    MTS_BSDF_TWOSIDED = 9        /* twosided.cpp */
 };
 
 /* node.flags */
@@ -86,7 +87,8 @@ enum {
     MTS_EGLOSSY_TRANSMISSION = 0x00010,
     MTS_EDELTA_REFLECTION = 0x00020,
     MTS_EDELTA_TRANSMISSION = 0x00040,
-    MTS_EBACKSIDE = 0x20000
+    MTS_EFRONTSIDE = 0x08000,
+    MTS_EBACKSIDE = 0x10000
 };
 #define MTS_ESMOOTH (MTS_EDIFFUSE_REFLECTION | MTS_EDIFFUSE_TRANSMISSION | MTS_EGLOSSY_REFLECTION | MTS_EGLOSSY_TRANSMISSION)
 #define MTS_EDELTA (MTS_ENULL | MTS_EDELTA_REFLECTION | MTS_EDELTA_TRANSMISSION)
@@ -121,6 +123,7 @@ typedef struct MtsTexRef {
  *                  f[2] = specularSamplingWeight; child[0] = nested
  *   blendbsdf      t0 = weight; child[0], child[1]
  *   bumpmap        t0 = displacement; child[0] = nested
+ *   twosided       child[0] = front-side BRDF, child[1] = back-side BRDF (= child[0] when only one is given)
  */
 typedef struct MtsBsdfNode {
     int32_t type;

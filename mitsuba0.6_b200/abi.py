@@ -22,13 +22,15 @@ EPSILON = 1e-4
 
 # ---- enums (mirror include/mtscuda.h) --------------------------------------
 BSDF_DIFFUSE, BSDF_CONDUCTOR, BSDF_ROUGHCONDUCTOR, BSDF_PLASTIC, BSDF_ROUGHPLASTIC, \
-    BSDF_DIELECTRIC, BSDF_COATING, BSDF_BLEND, BSDF_BUMPMAP = range(9)
+    BSDF_DIELECTRIC, BSDF_COATING, BSDF_BLEND, BSDF_BUMPMAP, BSDF_TWOSIDED = range(10)
 BF_GGX, BF_SAMPLE_VISIBLE, BF_NONLINEAR, BF_RT_2D = 1, 2, 4, 8
 ENULL, EDIFFUSE_REFLECTION, EDIFFUSE_TRANSMISSION, EGLOSSY_REFLECTION, EGLOSSY_TRANSMISSION, \
     EDELTA_REFLECTION, EDELTA_TRANSMISSION = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20, 0x40
-EBACKSIDE = 0x20000
+EFRONTSIDE = 0x08000
+EBACKSIDE = 0x10000
 ESMOOTH = EDIFFUSE_REFLECTION | EDIFFUSE_TRANSMISSION | EGLOSSY_REFLECTION | EGLOSSY_TRANSMISSION
 EDELTA = ENULL | EDELTA_REFLECTION | EDELTA_TRANSMISSION
+ETRANSMISSION = EDIFFUSE_TRANSMISSION | EGLOSSY_TRANSMISSION | EDELTA_TRANSMISSION | ENULL
 MEASURE_SOLID_ANGLE, MEASURE_DISCRETE = 1, 4
 WRAP = {"repeat": 0, "mirror": 1, "clamp": 2, "zero": 3, "one": 4}
 FILTER = {"nearest": 0, "bilinear": 1}

@@ -646,6 +646,11 @@ template <int D> struct Bsdf {
             if (cosTheta(wo) * cosTheta(woP) <= 0) return f3(0.0f);
             return Next::eval(S, n.child[0], pert, wiP, woP, measure);
         }
+        case MTS_BSDF_TWOSIDED: {  // twosided.cpp:107-119
+            if (cosTheta(wi) > 0) return Next::eval(S, n.child[0], su, wi, wo, measure);
+            wi.z = -wi.z; wo.z = -wo.z;
+            return Next::eval(S, n.child[1], su, wi, wo, measure);
+        }
         default: return leafEval(S, n, su.uv, wi, wo, measure);
         }
     }
@@ -678,6 +683,11 @@ template <int D> struct Bsdf {
             float3 wiP = pert.sh.toLocal(su.sh.toWorld(wi)), woP = pert.sh.toLocal(su.sh.toWorld(wo));
             if (cosTheta(wo) * cosTheta(woP) <= 0) return 0;
             return Next::pdf(S, n.child[0], pert, wiP, woP, measure);
+        }
+        case MTS_BSDF_TWOSIDED: {  // twosided.cpp:121-133
+            if (wi.z > 0) return Next::pdf(S, n.child[0], su, wi, wo, measure);
+            wi.z = -wi.z; wo.z = -wo.z;
+            return Next::pdf(S, n.child[1], su, wi, wo, measure);
         }
         default: return leafPdf(S, n, su.uv, wi, wo, measure);
         }
@@ -740,6 +750,13 @@ template <int D> struct Bsdf {
                 o.wo = su.sh.toLocal(pert.sh.toWorld(woP));
                 if (cosTheta(o.wo) * cosTheta(woP) <= 0) return f3(0.0f);
             }
+            return result;
+        }
+        case MTS_BSDF_TWOSIDED: {  // twosided.cpp:158-180
+            bool flipped = cosTheta(wi) < 0;
+            if (flipped) wi.z = -wi.z;
+            float3 result = Next::sample(S, n.child[flipped ? 1 : 0], su, wi, sample, o);
+            if (flipped && !isZero(result) && o.pdf != 0) o.wo.z = -o.wo.z;
             return result;
         }
         default: return leafSample(S, n, su.uv, wi, sample, o);

@@ -157,7 +157,7 @@ int bsdfDepth(const std::vector<MtsBsdfNode> &nodes, int i, int guard = 0) {
     if (i < 0 || i >= (int)nodes.size() || guard > 64) return 1000;
     const MtsBsdfNode &n = nodes[i];
     if (n.type == MTS_BSDF_COATING || n.type == MTS_BSDF_BUMPMAP) return 1 + bsdfDepth(nodes, n.child[0], guard + 1);
-    if (n.type == MTS_BSDF_BLEND) return 1 + std::max(bsdfDepth(nodes, n.child[0], guard + 1), bsdfDepth(nodes, n.child[1], guard + 1));
+    if (n.type == MTS_BSDF_BLEND || n.type == MTS_BSDF_TWOSIDED) return 1 + std::max(bsdfDepth(nodes, n.child[0], guard + 1), bsdfDepth(nodes, n.child[1], guard + 1));
     return 0;
 }
 
@@ -524,9 +524,9 @@ MTS_API int mtscuda_set_float_pool(MtsContext *c, const float *data, int64_t n) 
 MTS_API int mtscuda_set_bsdfs(MtsContext *c, const MtsBsdfNode *nodes, int32_t n) {
     c->nodes.assign(nodes, nodes + n); c->built = false;
     for (int i = 0; i < n; ++i) {
-        if (nodes[i].type < MTS_BSDF_DIFFUSE || nodes[i].type > MTS_BSDF_BUMPMAP) return fail(MTS_EINVAL, "unknown BSDF type");
+        if (nodes[i].type < MTS_BSDF_DIFFUSE || nodes[i].type > MTS_BSDF_TWOSIDED) return fail(MTS_EINVAL, "unknown BSDF type");
         if (bsdfDepth(c->nodes, i) > kMaxBsdfDepth)
-            return fail(MTS_EINVAL, "BSDF nesting deeper than 4 wrapper levels (coating/blendbsdf/bumpmap) is not supported");
+            return fail(MTS_EINVAL, "BSDF nesting deeper than 4 wrapper levels (coating/blendbsdf/bumpmap/twosided) is not supported");
     }
     return MTS_OK;
 }
@@ -847,7 +847,9 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
     cudaEvent_t ev0, ev1; cudaEventCreate(&ev0); cudaEventCreate(&ev1);
     cudaEventRecord(ev0, st);
 
+    // 4 CTAs/SM (128 registers) measured best on cfg3; 3 (168 registers, fewer spills) kept as the measured alternative
     const int shadeMinB = getenv("MTS_SHADE_MINB") ? atoi(getenv("MTS_SHADE_MINB")) : 4;
+    const bool traceBounces = getenv("MTS_TRACE_BOUNCES") != nullptr;   // per-bounce queue sizes on stderr (matches ncu launches to ray counts)
     const int gridTrace = c->numSMs * TRACE_MINB, gridWide = c->numSMs * 8;
     uint64_t launches = 0, normalRays = 0, shadowRays = 0;
     Counters hc;
@@ -876,9 +878,6 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
             k_shade_miss<<<gridWide, 256, 0, st>>>(S, Wf, R, cur);
             switch (shadeMinB) {
             case 3: k_shade<3><<<c->numSMs * 3, 128, 0, st>>>(S, Wf, R, cur); break;
-            case 5: k_shade<5><<<c->numSMs * 5, 128, 0, st>>>(S, Wf, R, cur); break;
-            case 6: k_shade<6><<<c->numSMs * 6, 128, 0, st>>>(S, Wf, R, cur); break;
-            case 8: k_shade<8><<<c->numSMs * 8, 128, 0, st>>>(S, Wf, R, cur); break;
             default: k_shade<4><<<c->numSMs * 4, 128, 0, st>>>(S, Wf, R, cur); break;
             }
             end();
@@ -895,6 +894,9 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
             normalRays += hc.qCount[cur];
             shadowRays += hc.shadowCount;
             active = hc.qCount[cur ^ 1];
+            if (traceBounces)
+                fprintf(stderr, "[mtscuda] wavefront %llu bounce %d: closest-hit rays %u, shadow rays %u, continuing %u\n",
+                        first / cap, bounce, hc.qCount[cur], hc.shadowCount, active);
             cur ^= 1;
             if (bounce > 4096) break;  // safety net for maxDepth = -1 with rr disabled by huge rrDepth
         }

@@ -365,7 +365,7 @@ CONDUCTOR_PRESETS = {
 }
 
 SUPPORTED_BSDFS = ("diffuse", "conductor", "roughconductor", "plastic", "roughplastic", "dielectric",
-                   "coating", "blendbsdf", "bumpmap")
+                   "coating", "blendbsdf", "bumpmap", "twosided")
 
 
 class Unsupported(ValueError):
@@ -631,6 +631,20 @@ class FlatScene:
             n.t0 = self._ref(self.texref(p, name, 0.0))
             n.child[0] = self.bsdf(nested)
             n.lobes = self.nodes[n.child[0]].lobes
+        elif t == "twosided":
+            # TwoSidedBRDF::addChild / configure (src/bsdfs/twosided.cpp:86-105, 182-193)
+            kids = [c for _, c in p.children_of("bsdf")]
+            if len(kids) == 0:
+                raise ValueError("A nested one-sided material is required!")
+            if len(kids) > 2:
+                raise ValueError("No more than two nested BRDFs can be added!")
+            n.type = abi.BSDF_TWOSIDED
+            n.child[0] = self.bsdf(kids[0])
+            n.child[1] = self.bsdf(kids[1]) if len(kids) == 2 else n.child[0]
+            front, back = self.nodes[n.child[0]].lobes, self.nodes[n.child[1]].lobes
+            n.lobes = ((front & ~abi.EBACKSIDE) | abi.EFRONTSIDE) | ((back & ~abi.EFRONTSIDE) | abi.EBACKSIDE)
+            if n.lobes & abi.ETRANSMISSION:
+                raise ValueError("Only materials without a transmission component can be nested!")
         return idx
 
     def uses_uv_tangents(self, node):

@@ -471,6 +471,10 @@ inline V3 bsdfEval(const Materials &M, int node, const Its &its, V3 wi, V3 wo, i
         if (Frame::cosTheta(wo) * Frame::cosTheta(woP) <= 0) return V3(0.0f);
         return bsdfEval(M, n.child[0], pert, wiP, woP, measure);
     }
+    case MTS_BSDF_TWOSIDED: { /* twosided.cpp:107-119 */
+        if (Frame::cosTheta(wi) > 0) return bsdfEval(M, n.child[0], its, wi, wo, measure);
+        return bsdfEval(M, n.child[1], its, V3(wi.x, wi.y, -wi.z), V3(wo.x, wo.y, -wo.z), measure);
+    }
     }
     return V3(0.0f);
 }
@@ -561,6 +565,10 @@ inline float bsdfPdf(const Materials &M, int node, const Its &its, V3 wi, V3 wo,
         V3 wiP = pert.toLocal(its.toWorld(wi)), woP = pert.toLocal(its.toWorld(wo));
         if (Frame::cosTheta(wo) * Frame::cosTheta(woP) <= 0) return 0;
         return bsdfPdf(M, n.child[0], pert, wiP, woP, measure);
+    }
+    case MTS_BSDF_TWOSIDED: { /* twosided.cpp:121-133 */
+        if (wi.z > 0) return bsdfPdf(M, n.child[0], its, wi, wo, measure);
+        return bsdfPdf(M, n.child[1], its, V3(wi.x, wi.y, -wi.z), V3(wo.x, wo.y, -wo.z), measure);
     }
     }
     return 0.0f;
@@ -719,6 +727,13 @@ inline V3 bsdfSample(const Materials &M, int node, const Its &its, V3 wi, V2 sam
             o.wo = its.toLocal(pert.toWorld(woP));
             if (Frame::cosTheta(o.wo) * Frame::cosTheta(woP) <= 0) return V3(0.0f);
         }
+        return result;
+    }
+    case MTS_BSDF_TWOSIDED: { /* twosided.cpp:158-180 (the pdf-returning overload path.cpp:236 calls) */
+        bool flipped = Frame::cosTheta(wi) < 0;
+        V3 wiF = flipped ? V3(wi.x, wi.y, -wi.z) : wi;
+        V3 result = bsdfSample(M, n.child[flipped ? 1 : 0], its, wiF, sample, o);
+        if (flipped && !isZero(result) && o.pdf != 0) o.wo.z *= -1;
         return result;
     }
     }

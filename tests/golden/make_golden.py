@@ -77,9 +77,43 @@ def images():
     return out
 
 
+def twosided():
+    """twosided.npz: BSDF probes of the TwoSidedBRDF configurations + a converged render of the two-sided scene."""
+    sc, z = G.twosided()
+    rs = mtsref.RefScene(sc)
+    out = {}
+    for name, p in z.items():
+        surf, wi, wo, u = G.bsdf_inputs(name)
+        rb = rs.bsdf(p)
+        smp = rs.bsdf_sample(rb, surf, wi, u)
+        wo2 = G.eval_directions(smp, wo)
+        out["bsdf/%s/sample" % name] = smp
+        for tag, meas in (("sa", 1), ("disc", 4)):
+            v, pdf = rs.bsdf_eval_pdf(rb, surf, wi, wo2, meas)
+            out["bsdf/%s/eval_%s" % (name, tag)] = v
+            out["bsdf/%s/pdf_%s" % (name, tag)] = pdf
+        out["bsdf/%s/type" % name] = np.array([rs.bsdf_type(rb)], dtype=np.int64)
+    for name, make in G.TWOSIDED_IMAGE_SCENES.items():
+        scn = make()
+        rsi = mtsref.RefScene(scn)
+        film = rsi.render()
+        st = rsi.stats
+        w, h, spp = G.scene_dims(scn)
+        out["image/%s/rgb" % name] = M.develop(film).astype(np.float16)
+        out["image/%s/stats" % name] = np.array([st.get("normal_rays", 0) / (w * h * spp), st.get("shadow_rays", 0) / (w * h * spp),
+                                                 st.get("avg_path_length", 0), rsi.render_s, mtsref.load().mtsref_thread_count()], dtype=np.float64)
+        print("%-10s %dx%d %d spp: reference render %.1f s" % (name, w, h, spp, rsi.render_s), flush=True)
+    return out
+
+
 if __name__ == "__main__":
     if not mtsref.available():
         raise SystemExit("oracle/_ref is not built: make -C oracle/refbuild (needs /root/reference)")
+    if "--twosided" in sys.argv:
+        t = twosided()
+        np.savez_compressed(os.path.join(HERE, "twosided.npz"), **t)
+        print("twosided.npz: %d arrays" % len(t))
+        raise SystemExit(0)
     p = probes()
     np.savez_compressed(os.path.join(HERE, "probes.npz"), **p)
     print("probes.npz: %d arrays" % len(p))

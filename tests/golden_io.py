@@ -20,6 +20,10 @@ def zoo(spp=4):
     return util.zoo_scene(width=ZOO_W, height=ZOO_H, spp=spp)
 
 
+def twosided(spp=4):
+    return util.twosided_scene(width=ZOO_W, height=ZOO_H, spp=spp)
+
+
 def cornell_small(spp=64):
     return scenes.cornell_box(CORNELL_RES, CORNELL_RES, spp)
 
@@ -100,6 +104,12 @@ IMAGE_SCENES = {
     "spheres": lambda: scenes.material_spheres(128, 128, 8192, env_size=(512, 256)),
     "caustics": lambda: scenes.caustic_scene(96, 96, 16384, knot=(120, 40)),
     "terrain": lambda: scenes.terrain_scene(160, 90, 4096, grid=200, tex_size=256, env_size=(512, 256)),
+}
+
+
+# scenes of the "next" rows; stored in their own fixture so that the files above stay untouched
+TWOSIDED_IMAGE_SCENES = {
+    "twosided": lambda: twosided(spp=8192)[0],
 }
 
 

@@ -330,3 +330,31 @@ def test_render_vs_reference(gold_images, name, spp, bar):
     err = GC.check_image(g, name, gold_images, spp, bar, lazy_shadow=True)
     print("relMSE(%s, %d spp vs reference) = %.3g" % (name, spp, err))
     g.close()
+
+
+# ---- twosided ------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def gold_twosided():
+    return G.load("twosided.npz")
+
+
+@pytest.fixture(scope="module")
+def gtwosided():
+    sc, z = G.twosided()
+    gpu, cpu, flat = util.make_pair(sc)
+    yield gpu, cpu, flat, z
+    gpu.close()
+    cpu.close()
+
+
+@pytest.mark.parametrize("name", list(util.twosided_bsdfs().keys()))
+def test_twosided_bsdf_vs_reference(gtwosided, gold_twosided, name):
+    gpu, _, flat, z = gtwosided
+    GC.check_bsdf(gpu.ctx, flat, z, name, gold_twosided)
+
+
+def test_twosided_render_vs_reference(gold_twosided):
+    g = M.CudaPath(G.TWOSIDED_IMAGE_SCENES["twosided"](), backend="cuda")
+    err = GC.check_image(g, "twosided", gold_twosided, 8192, 3e-3, lazy_shadow=True)
+    print("relMSE(twosided, 8192 spp vs reference) = %.3g" % err)
+    g.close()

@@ -162,3 +162,71 @@ def random_dirs(rng, n, hemisphere=None):
 def rel_err(a, b, floor=1e-6):
     a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
     return np.abs(a - b) / np.maximum(np.maximum(np.abs(a), np.abs(b)), floor)
+
+
+# ---- twosided (src/bsdfs/twosided.cpp) ------------------------------------------------
+def twosided_bsdfs():
+    """TwoSidedBRDF wrappers: one nested BRDF (used for both sides), two different ones, a wrapper below the
+    adapter, and the adapter below a wrapper."""
+    CU, AU = scenes.CU, scenes.AU
+    z = {}
+    t = Plugin("bsdf", "twosided")
+    t.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.7, 0.4, 0.2)))
+    z["ts_diffuse"] = t
+    t2 = Plugin("bsdf", "twosided")
+    t2.add(Plugin("bsdf", "roughconductor", distribution="ggx", alpha=0.25, **CU))
+    t2.add(Plugin("bsdf", "plastic", intIOR=1.5, diffuseReflectance=Spectrum(0.2, 0.5, 0.3)))
+    z["ts_rc_plastic"] = t2
+    t3 = Plugin("bsdf", "twosided")
+    bm = Plugin("bsdf", "bumpmap")
+    bm.add(Plugin("bsdf", "roughplastic", distribution="beckmann", alpha=0.15, intIOR=1.49,
+                  diffuseReflectance=Spectrum(0.5, 0.3, 0.6)))
+    bt = Plugin("texture", "scale", scale=0.04)
+    bt.add(_tex(11, channels=1, uvscale=2.0))
+    bm.add(bt)
+    t3.add(bm)
+    z["ts_bump_rp"] = t3
+    b = Plugin("bsdf", "blendbsdf", weight=0.4)
+    inner = Plugin("bsdf", "twosided")
+    inner.add(Plugin("bsdf", "conductor", **AU))
+    b.add(inner)
+    b.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.5)))
+    z["blend_ts_cond"] = b
+    return z
+
+
+def twosided_scene(width=96, height=64, spp=4):
+    """Open surfaces seen and lit from both sides: free-standing rectangles carrying the twosided materials (front
+    faces turned towards, away from and edge-on to the light), one plain one-sided rectangle for contrast."""
+    sc = Plugin("scene", "")
+    sc.add(Plugin("integrator", "path", maxDepth=6))
+    s = Plugin("sensor", "perspective", toWorld=hm.look_at([0, 3.5, 10], [0, 1.6, 0], [0, 1, 0]), fov=45.0)
+    s.add(Plugin("sampler", "independent", sampleCount=spp))
+    film = Plugin("film", "hdrfilm", width=width, height=height)
+    film.add(Plugin("rfilter", "gaussian"))
+    s.add(film)
+    sc.add(s)
+    z = twosided_bsdfs()
+    floor = Plugin("shape", "rectangle", toWorld=hm.rotate([1, 0, 0], -90) @ hm.scale([10, 10, 1]))
+    floor.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.5)))
+    sc.add(floor)
+    for i, nm in enumerate(z):
+        # normals alternate between facing the camera (+z) and facing away (-z), tilted about the vertical axis
+        yaw = (180.0 if i % 2 else 0.0) + 25.0 * (i - 1.5)
+        r = Plugin("shape", "rectangle", toWorld=hm.translate([(i - 1.5) * 2.6, 1.6, -0.5 * i]) @ hm.rotate([0, 1, 0], yaw)
+                   @ hm.scale([1.0, 1.4, 1]))
+        r.add(z[nm])
+        sc.add(r)
+    one = Plugin("shape", "rectangle", toWorld=hm.translate([0, 4.2, -3]) @ hm.rotate([0, 1, 0], 180) @ hm.scale([1.5, 0.7, 1]))
+    one.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.2, 0.3, 0.8)))      # back face towards the camera: black
+    sc.add(one)
+    pos, idx, nrm, uv = scenes.torus_knot(40, 12)
+    knot = Plugin("shape", "mesh", toWorld=hm.translate([0, 0.9, 3]) @ hm.scale(0.6))
+    knot.data.update(positions=pos, indices=idx, normals=nrm, texcoords=uv)
+    knot.add(z["ts_rc_plastic"])
+    sc.add(knot)
+    lt = Plugin("shape", "rectangle", toWorld=hm.translate([0, 7, 2]) @ hm.rotate([1, 0, 0], 90) @ hm.scale([1.2, 1.2, 1]))
+    lt.add(Plugin("emitter", "area", radiance=Spectrum(25, 23, 20)))
+    sc.add(lt)
+    sc.add(Plugin("emitter", "point", position=Point(0, 2, -6), intensity=Spectrum(60, 60, 80)))   # lights the far sides
+    return sc, z
