@@ -155,7 +155,21 @@ DEVFN float adaptiveMinT(float3 o, float mint, bool shadow) {
 #endif
 constexpr int kNodeIters = NODE_ITERS;
 
-template <bool ANY, bool COUNT>
+// Traversal stack: the first SH entries of every thread live in shared memory (column `threadIdx.x` of a
+// [SH][kTraceBlock] uint2 array: conflict-free whatever the lanes' stack depths are), deeper entries spill to a
+// per-thread local array.  A purely local stack costs one 32-byte sector per LANE per push/pop (the lanes of a warp
+// sit at different depths), which made the stack more than half of the trace kernels' L1 traffic
+// (profiles/r1e_ncu_full_raw.txt: 1.6 useful bytes per local sector).
+#ifndef TRACE_SMEM_STACK
+#define TRACE_SMEM_STACK 10
+#endif
+constexpr int kSmemStack = TRACE_SMEM_STACK;
+constexpr int kTraceBlock = 128;                   // block size of every kernel that uses the shared stack
+constexpr int kStackCapacity = 32;
+DEVFN void stsStack(uint32_t addr, uint2 v) { asm volatile("st.shared.v2.u32 [%0], {%1, %2};" :: "r"(addr), "r"(v.x), "r"(v.y) : "memory"); }
+DEVFN uint2 ldsStack(uint32_t addr) { uint2 v; asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory"); return v; }
+
+template <bool ANY, bool COUNT, int SH = 0>
 struct Traversal {
     float3 o, d, idir;
     float mint;
@@ -163,7 +177,19 @@ struct Traversal {
     RayHit best;
     uint2 ngroup;
     int sp;
-    uint2 stack[32];
+    uint32_t smBase;                               // shared-memory address of this thread's stack column (SH > 0)
+    uint2 stack[kStackCapacity - SH];
+
+    DEVFN void push(uint2 v) {
+        if (SH > 0 && sp < SH) stsStack(smBase + (uint32_t)sp * (kTraceBlock * 8u), v);
+        else stack[sp - SH] = v;
+        ++sp;
+    }
+    DEVFN uint2 pop() {
+        --sp;
+        if (SH > 0 && sp < SH) return ldsStack(smBase + (uint32_t)sp * (kTraceBlock * 8u));
+        return stack[sp - SH];
+    }
 
     // returns false when the ray is finished before it starts (empty scene / empty interval)
     DEVFN bool init(const DScene &S, float3 o_, float3 d_, float rayMinT, float rayMaxT) {
@@ -194,7 +220,7 @@ struct Traversal {
             const uint32_t slot = (uint32_t)(bit - 24) ^ oct;
             const uint32_t rel = __popc(ngroup.y & 0xffu & ~(0xffffffffu << slot));
             const uint32_t nodeIdx = ngroup.x + rel;
-            if ((ngroup.y & 0xff000000u) && sp < 32) stack[sp++] = ngroup;
+            if ((ngroup.y & 0xff000000u) && sp < kStackCapacity) push(ngroup);
             const float4 *np = reinterpret_cast<const float4 *>(S.bvh + nodeIdx);
             const float4 n0 = __ldg(np);
             const uint4 n1 = __ldg(reinterpret_cast<const uint4 *>(np + 1)), n2 = __ldg(reinterpret_cast<const uint4 *>(np + 2)),
@@ -206,7 +232,7 @@ struct Traversal {
             if (pending) break;
             if ((ngroup.y & 0xff000000u) == 0) {
                 if (sp == 0) return true;
-                ngroup = stack[--sp];
+                ngroup = pop();
             }
         }
         while (pending) {
@@ -221,7 +247,7 @@ struct Traversal {
         }
         if ((ngroup.y & 0xff000000u) == 0) {
             if (sp == 0) return true;
-            ngroup = stack[--sp];
+            ngroup = pop();
         }
         return false;
     }

@@ -131,7 +131,9 @@ template <bool ANY, bool COUNT, class Load, class Done>
 DEVFN void traceQueue(const DScene &S, uint32_t count, uint32_t *cursor, TraceCounters *tc, Load load, Done done) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    Traversal<ANY, COUNT> tr;
+    __shared__ uint2 sstack[kSmemStack > 0 ? kSmemStack * kTraceBlock : 1];
+    Traversal<ANY, COUNT, kSmemStack> tr;
+    tr.smBase = (uint32_t)__cvta_generic_to_shared(&sstack[threadIdx.x]);
     uint32_t item = 0;
     bool busy = false, exhausted = false;
     while (true) {
@@ -168,12 +170,12 @@ __global__ void __launch_bounds__(128, TRACE_MINB) k_intersect(const DScene S, c
     TraceCounters tc = {0, 0};
     const uint32_t *queue = W.queue[qsel];
     traceQueue<false, COUNT>(S, count, &W.ctr->cursor[0], &tc,
-        [&](uint32_t i, Traversal<false, COUNT> &tr) {
+        [&](uint32_t i, Traversal<false, COUNT, kSmemStack> &tr) {
             uint32_t slot = queue[i];
             float4 ro = W.rayO[slot], rd = W.rayD[slot];
             return tr.init(S, f3(ro), f3(rd), ro.w, rd.w);
         },
-        [&](uint32_t i, const Traversal<false, COUNT> &tr) {
+        [&](uint32_t i, const Traversal<false, COUNT, kSmemStack> &tr) {
             uint32_t slot = queue[i];
             RayHit h = tr.result();
             W.hit[slot] = make_float4(h.t, h.u, h.v, __int_as_float(h.prim));
@@ -194,11 +196,11 @@ __global__ void __launch_bounds__(128, TRACE_MINB) k_shadow(const DScene S, cons
     const uint32_t count = W.ctr->shadowCount;
     TraceCounters tc = {0, 0};
     traceQueue<true, COUNT>(S, count, &W.ctr->cursor[1], &tc,
-        [&](uint32_t i, Traversal<true, COUNT> &tr) {
+        [&](uint32_t i, Traversal<true, COUNT, kSmemStack> &tr) {
             float4 ro = W.shO[i], rd = W.shD[i];
             return tr.init(S, f3(ro), f3(rd), ro.w, rd.w);
         },
-        [&](uint32_t i, const Traversal<true, COUNT> &tr) {
+        [&](uint32_t i, const Traversal<true, COUNT, kSmemStack> &tr) {
             if (!tr.hit()) {
                 float4 c = W.shC[i];
                 uint32_t slot = (uint32_t)__float_as_int(c.w);
