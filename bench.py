@@ -397,8 +397,17 @@ def run_cuda(args):
         rays_rank = acc["normal"]
         launches_i = max(acc["intersect_launches"], 1)
         achieved = (rays_rank * b_ray) / (acc["intersect_ms"] / 1e3) / 1e9 if acc["intersect_ms"] > 0 else 0.0
+        # DRAM traffic of the same kernel from the committed `ncu --set full` capture (bytes per ray x this run's rays
+        # per launch): it cannot be measured live, a number taken under a profiler is never a bench value
+        traffic, traffic_src = None, None
+        tpath = os.path.join(ROOT, "profiles", "r1f_traffic_k_intersect.json")
+        if os.path.exists(tpath):
+            with open(tpath) as f:
+                tj = json.load(f)
+            traffic = tj["dram_bytes_per_ray"] * rays_rank / launches_i
+            traffic_src = "profiles/r1f_traffic_k_intersect.json: %.0f DRAM B/ray (ncu dram__bytes_read+write) x rays_per_launch" % tj["dram_bytes_per_ray"]
         roofline = {"bound": "hbm", "kernel": "k_intersect", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                     "bytes_per_ray": b_ray, "nodes_per_ray": nodes_per_ray, "prims_per_ray": prims_per_ray,
                     "bytes_per_shadow_ray": b_sray, "nodes_per_shadow_ray": nodes_per_sray,
                     "rays_per_launch": rays_rank / launches_i,
