@@ -574,41 +574,33 @@ __device__ __noinline__ float3 leafSample(const DScene &S, const MtsBsdfNode &n,
 // wrappers
 // ---------------------------------------------------------------------------------------
 // Surface context the wrappers need (bumpmap perturbs the frame; textures only need uv).
-struct SurfBase {
+struct Surf {
     float2 uv;
     float3 dpdu, dpdv, geoN;
+    Frame sh;
     // one-entry cache of the perturbed frame: eval, pdf and sample of one hit share a single gradient lookup
     mutable int bumpNode;
     mutable Frame bumpCache;
-};
-// What travels down the wrapper levels: a pointer to the immutable hit data plus the (possibly perturbed) shading
-// frame.  bumpmap used to copy the whole 30-float record per level and call; those copies were 35 % of k_shade's
-// local-memory traffic (profiles/r1e_shade_lines.txt).
-struct Surf {
-    const SurfBase *b;
-    Frame sh;
-    bool root;   // sh is the unperturbed frame of the hit: only then may the bump cache (keyed by node) be used
 };
 
 // BumpMap::getFrame (src/bsdfs/bumpmap.cpp:135-159)
 DEVFN Frame bumpFrame(const DScene &S, const MtsBsdfNode &n, const Surf &su) {
     float3 g0, g1;
-    evalTexGradient(S, n.t0, su.b->uv, g0, g1);
+    evalTexGradient(S, n.t0, su.uv, g0, g1);
     float dDispDu = luminance(g0), dDispDv = luminance(g1);
-    float3 dpdu = su.b->dpdu + su.sh.n * (dDispDu - dot(su.sh.n, su.b->dpdu));
-    float3 dpdv = su.b->dpdv + su.sh.n * (dDispDv - dot(su.sh.n, su.b->dpdv));
+    float3 dpdu = su.dpdu + su.sh.n * (dDispDu - dot(su.sh.n, su.dpdu));
+    float3 dpdv = su.dpdv + su.sh.n * (dDispDv - dot(su.sh.n, su.dpdv));
     Frame r;
     r.n = normalize(cross(dpdu, dpdv));
     r.s = normalize(dpdu - r.n * dot(r.n, dpdu));
     r.t = cross(r.n, r.s);
-    if (dot(r.n, su.b->geoN) < 0) r.n = -r.n;
+    if (dot(r.n, su.geoN) < 0) r.n = -r.n;
     return r;
 }
 DEVFN Frame bumpFrameCached(const DScene &S, int node, const MtsBsdfNode &n, const Surf &su) {
-    if (!su.root) return bumpFrame(S, n, su);
-    if (su.b->bumpNode == node) return su.b->bumpCache;
+    if (su.bumpNode == node) return su.bumpCache;
     Frame f = bumpFrame(S, n, su);
-    su.b->bumpNode = node; su.b->bumpCache = f;
+    su.bumpNode = node; su.bumpCache = f;
     return f;
 }
 // SmoothCoating::refractIn / refractOut (src/bsdfs/coating.cpp:208-219)
@@ -632,24 +624,24 @@ template <int D> struct Bsdf {
         case MTS_BSDF_COATING: {  // coating.cpp:221-258
             float eta = n.eta[0], invEta = 1 / eta;
             if (measure == MTS_MEASURE_DISCRETE && fabsf(dot(reflectZ(wi), wo) - 1) < kDeltaEps)
-                return evalTex(S, n.t1, su.b->uv) * fresnelDielectricExt(fabsf(cosTheta(wi)), eta);
+                return evalTex(S, n.t1, su.uv) * fresnelDielectricExt(fabsf(cosTheta(wi)), eta);
             float R12, R21;
             float3 wiP = coatRefractIn(eta, wi, R12), woP = coatRefractIn(eta, wo, R21);
             if (R12 == 1 || R21 == 1) return f3(0.0f);
             float3 result = Next::eval(S, n.child[0], su, wiP, woP, measure) * (1 - R12) * (1 - R21);
-            float3 sigmaA = evalTex(S, n.t0, su.b->uv) * n.f[0];
+            float3 sigmaA = evalTex(S, n.t0, su.uv) * n.f[0];
             if (!isZero(sigmaA)) result *= vexp(-sigmaA * (1 / fabsf(cosTheta(wiP)) + 1 / fabsf(cosTheta(woP))));
             if (measure == MTS_MEASURE_SOLID_ANGLE) result *= invEta * invEta * cosTheta(wo) / cosTheta(woP);
             return result;
         }
         case MTS_BSDF_BLEND: {  // blendbsdf.cpp:135-152
-            float weight = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.b->uv))));
+            float weight = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.uv))));
             return Next::eval(S, n.child[0], su, wi, wo, measure) * (1 - weight) + Next::eval(S, n.child[1], su, wi, wo, measure) * weight;
         }
         case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:161-177
             Frame bf = bumpFrameCached(S, node, n, su);
-            Surf pert;
-            pert.b = su.b; pert.sh = bf; pert.root = false;
+            Surf pert = su;
+            pert.sh = bf; pert.bumpNode = -1;
             float3 wiP = pert.sh.toLocal(su.sh.toWorld(wi)), woP = pert.sh.toLocal(su.sh.toWorld(wo));
             if (cosTheta(wo) * cosTheta(woP) <= 0) return f3(0.0f);
             return Next::eval(S, n.child[0], pert, wiP, woP, measure);
@@ -659,7 +651,7 @@ template <int D> struct Bsdf {
             wi.z = -wi.z; wo.z = -wo.z;
             return Next::eval(S, n.child[1], su, wi, wo, measure);
         }
-        default: return leafEval(S, n, su.b->uv, wi, wo, measure);
+        default: return leafEval(S, n, su.uv, wi, wo, measure);
         }
     }
 
@@ -681,13 +673,13 @@ template <int D> struct Bsdf {
             return p * (1 - probSpecular);
         }
         case MTS_BSDF_BLEND: {  // blendbsdf.cpp:154-173
-            float weight = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.b->uv))));
+            float weight = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.uv))));
             return Next::pdf(S, n.child[0], su, wi, wo, measure) * (1 - weight) + Next::pdf(S, n.child[1], su, wi, wo, measure) * weight;
         }
         case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:179-197
             Frame bf = bumpFrameCached(S, node, n, su);
-            Surf pert;
-            pert.b = su.b; pert.sh = bf; pert.root = false;
+            Surf pert = su;
+            pert.sh = bf; pert.bumpNode = -1;
             float3 wiP = pert.sh.toLocal(su.sh.toWorld(wi)), woP = pert.sh.toLocal(su.sh.toWorld(wo));
             if (cosTheta(wo) * cosTheta(woP) <= 0) return 0;
             return Next::pdf(S, n.child[0], pert, wiP, woP, measure);
@@ -697,7 +689,7 @@ template <int D> struct Bsdf {
             wi.z = -wi.z; wo.z = -wo.z;
             return Next::pdf(S, n.child[1], su, wi, wo, measure);
         }
-        default: return leafPdf(S, n, su.b->uv, wi, wo, measure);
+        default: return leafPdf(S, n, su.uv, wi, wo, measure);
         }
     }
 
@@ -715,13 +707,13 @@ template <int D> struct Bsdf {
             else { sample.x = (sample.x - probSpecular) / (1 - probSpecular); choseSpecular = false; }
             if (choseSpecular) {
                 o.type = MTS_EDELTA_REFLECTION; o.wo = reflectZ(wi); o.eta = 1.0f; o.pdf = probSpecular;
-                return evalTex(S, n.t1, su.b->uv) * (R12 / o.pdf);
+                return evalTex(S, n.t1, su.uv) * (R12 / o.pdf);
             }
             if (R12 == 1.0f) return f3(0.0f);
             float3 result = Next::sample(S, n.child[0], su, wiPrime, sample, o);
             if (isZero(result)) return f3(0.0f);
             float3 woPrime = o.wo;
-            float3 sigmaA = evalTex(S, n.t0, su.b->uv) * n.f[0];
+            float3 sigmaA = evalTex(S, n.t0, su.uv) * n.f[0];
             if (!isZero(sigmaA)) result *= vexp(-sigmaA * (1 / fabsf(cosTheta(wiPrime)) + 1 / fabsf(cosTheta(woPrime))));
             float R21;
             o.wo = coatRefractOut(eta, woPrime, R21);
@@ -733,7 +725,7 @@ template <int D> struct Bsdf {
             return result;
         }
         case MTS_BSDF_BLEND: {  // blendbsdf.cpp:223-262
-            float w1 = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.b->uv))));
+            float w1 = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.uv))));
             float w0 = 1 - w1;
             int entry;
             if (sample.x < w0) { entry = 0; sample.x /= w0; } else { entry = 1; sample.x = (sample.x - w0) / w1; }
@@ -749,8 +741,8 @@ template <int D> struct Bsdf {
         }
         case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:221-240
             Frame bf = bumpFrameCached(S, node, n, su);
-            Surf pert;
-            pert.b = su.b; pert.sh = bf; pert.root = false;
+            Surf pert = su;
+            pert.sh = bf; pert.bumpNode = -1;
             float3 wiP = pert.sh.toLocal(su.sh.toWorld(wi));
             float3 result = Next::sample(S, n.child[0], pert, wiP, sample, o);
             if (!isZero(result)) {
@@ -767,7 +759,7 @@ template <int D> struct Bsdf {
             if (flipped && !isZero(result) && o.pdf != 0) o.wo.z = -o.wo.z;
             return result;
         }
-        default: return leafSample(S, n, su.b->uv, wi, sample, o);
+        default: return leafSample(S, n, su.uv, wi, sample, o);
         }
     }
 };
@@ -775,13 +767,13 @@ template <int D> struct Bsdf {
 // recursion floor: below kMaxBsdfDepth wrappers only leaves are legal (set_bsdfs enforces it)
 template <> struct Bsdf<kMaxBsdfDepth> {
     static __device__ BSDF_NESTED_ATTR float3 eval(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
-        return leafEval(S, S.nodes[node], su.b->uv, wi, wo, measure);
+        return leafEval(S, S.nodes[node], su.uv, wi, wo, measure);
     }
     static __device__ BSDF_NESTED_ATTR float pdf(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
-        return leafPdf(S, S.nodes[node], su.b->uv, wi, wo, measure);
+        return leafPdf(S, S.nodes[node], su.uv, wi, wo, measure);
     }
     static __device__ BSDF_NESTED_ATTR float3 sample(const DScene &S, int node, const Surf &su, float3 wi, float2 sample, BSample &o) {
-        return leafSample(S, S.nodes[node], su.b->uv, wi, sample, o);
+        return leafSample(S, S.nodes[node], su.uv, wi, sample, o);
     }
 };
 

@@ -351,20 +351,21 @@ __global__ void k_hook_hit_records(const DScene S, int64_t n, const float *rays,
     if (ids) { ids[2 * i] = its.shape; ids[2 * i + 1] = its.prim; }
 }
 
-DEVFN SurfBase surfBaseFromArray(const float *s) {
-    SurfBase sb;
-    sb.uv = make_float2(s[0], s[1]);
-    sb.dpdu = f3(s[4], s[5], s[6]); sb.dpdv = f3(s[8], s[9], s[10]);
-    sb.geoN = f3(s[12], s[13], s[14]);
-    sb.bumpNode = -1;
-    return sb;
+DEVFN Surf surfFromArray(const float *s) {
+    Surf su;
+    su.uv = make_float2(s[0], s[1]);
+    su.dpdu = f3(s[4], s[5], s[6]); su.dpdv = f3(s[8], s[9], s[10]);
+    float3 n = f3(s[12], s[13], s[14]);
+    su.geoN = n;
+    su.sh = shadingFrame(n, su.dpdu);
+    su.bumpNode = -1;
+    return su;
 }
 __global__ void k_hook_bsdf_eval_pdf(const DScene S, int bsdf, int64_t n, const float *surf, const float *wi, const float *wo,
                                      int measure, float *outV, float *outP) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const SurfBase sbase = surfBaseFromArray(surf + 16 * i);
-    Surf su; su.b = &sbase; su.sh = shadingFrame(sbase.geoN, sbase.dpdu); su.root = true;
+    Surf su = surfFromArray(surf + 16 * i);
     float3 a = f3(wi[3 * i], wi[3 * i + 1], wi[3 * i + 2]), b = f3(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]);
     float3 v = BsdfRoot::eval(S, bsdf, su, a, b, measure);
     outV[3 * i] = v.x; outV[3 * i + 1] = v.y; outV[3 * i + 2] = v.z;
@@ -373,8 +374,7 @@ __global__ void k_hook_bsdf_eval_pdf(const DScene S, int bsdf, int64_t n, const 
 __global__ void k_hook_bsdf_sample(const DScene S, int bsdf, int64_t n, const float *surf, const float *wi, const float *u, float *out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const SurfBase sbase = surfBaseFromArray(surf + 16 * i);
-    Surf su; su.b = &sbase; su.sh = shadingFrame(sbase.geoN, sbase.dpdu); su.root = true;
+    Surf su = surfFromArray(surf + 16 * i);
     float3 a = f3(wi[3 * i], wi[3 * i + 1], wi[3 * i + 2]);
     BSample bs; bs.wo = f3(0.0f); bs.pdf = 0; bs.eta = 1; bs.type = 0;
     float3 w = BsdfRoot::sample(S, bsdf, su, a, make_float2(u[2 * i], u[2 * i + 1]), bs);

@@ -64,8 +64,8 @@ DEVFN uint32_t warpAppend(uint32_t *counter, bool pred) {
     return base + __popc(mask & ((1u << lane) - 1));
 }
 
-DEVFN SurfBase surfBaseOf(const Hit &h) {
-    SurfBase s; s.uv = h.uv; s.dpdu = h.dpdu; s.dpdv = h.dpdv; s.geoN = h.geoN; s.bumpNode = -1; return s;
+DEVFN Surf surfOf(const Hit &h) {
+    Surf s; s.uv = h.uv; s.dpdu = h.dpdu; s.dpdv = h.dpdv; s.geoN = h.geoN; s.sh = h.sh; s.bumpNode = -1; return s;
 }
 
 // ---- raygen: SamplingIntegrator::renderBlock sample loop + sampleRayDifferential -------------
@@ -290,8 +290,7 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
 
     const int bsdf = shape.bsdf;
     const uint32_t lobes = S.nodes[bsdf].lobes;
-    const SurfBase sbase = surfBaseOf(its);
-    Surf su; su.b = &sbase; su.sh = its.sh; su.root = true;
+    const Surf su = surfOf(its);
     float4 u = rand4(R.seed, meta.x, meta.y, 2 * depth - 1);
 
     // ---- direct illumination sampling (path.cpp:172-200) ----
