@@ -415,6 +415,17 @@ __device__ __noinline__ float3 leafEval(const DScene &S, const MtsBsdfNode &n, f
             return evalTex(S, n.t1, uv) * factor * factor * (1 - F);
         }
     }
+    case MTS_BSDF_THINDIELECTRIC: {  // thindielectric.cpp:145-166
+        float R = fresnelDielectricExt(fabsf(cosTheta(wi)), n.eta[0]), T = 1 - R;
+        if (R < 1) R += T * T * R / (1 - R * R);   // internal reflections: R' = R + TRT + TR^3T + ..
+        if (cosTheta(wi) * cosTheta(wo) >= 0) {
+            if (!discrete || fabsf(dot(reflectZ(wi), wo) - 1) > kDeltaEps) return f3(0.0f);
+            return evalTex(S, n.t0, uv) * R;
+        } else {
+            if (!discrete || fabsf(dot(-wi, wo) - 1) > kDeltaEps) return f3(0.0f);
+            return evalTex(S, n.t1, uv) * (1 - R);
+        }
+    }
     }
     return f3(0.0f);
 }
@@ -472,6 +483,17 @@ __device__ __noinline__ float leafPdf(const DScene &S, const MtsBsdfNode &n, flo
             float3 refr = f3(scale * wi.x, scale * wi.y, cosThetaT);
             if (!discrete || fabsf(dot(refr, wo) - 1) > kDeltaEps) return 0.0f;
             return 1 - F;
+        }
+    }
+    case MTS_BSDF_THINDIELECTRIC: {  // thindielectric.cpp:168-189
+        float R = fresnelDielectricExt(fabsf(cosTheta(wi)), n.eta[0]), T = 1 - R;
+        if (R < 1) R += T * T * R / (1 - R * R);
+        if (cosTheta(wi) * cosTheta(wo) >= 0) {
+            if (!discrete || fabsf(dot(reflectZ(wi), wo) - 1) > kDeltaEps) return 0.0f;
+            return R;
+        } else {
+            if (!discrete || fabsf(dot(-wi, wo) - 1) > kDeltaEps) return 0.0f;
+            return 1 - R;
         }
     }
     }
@@ -565,6 +587,17 @@ __device__ __noinline__ float3 leafSample(const DScene &S, const MtsBsdfNode &n,
         o.pdf = 1 - F;
         float factor = cosThetaT < 0 ? invEta : eta;
         return evalTex(S, n.t1, uv) * (factor * factor);
+    }
+    case MTS_BSDF_THINDIELECTRIC: {  // thindielectric.cpp:191-221 (the pdf-returning overload path.cpp:209 calls)
+        float R = fresnelDielectricExt(fabsf(cosTheta(wi)), n.eta[0]), T = 1 - R;
+        if (R < 1) R += T * T * R / (1 - R * R);
+        o.eta = 1.0f;
+        if (sample.x <= R) {
+            o.type = MTS_EDELTA_REFLECTION; o.wo = reflectZ(wi); o.pdf = R;
+            return evalTex(S, n.t0, uv);
+        }
+        o.type = MTS_ENULL; o.wo = -wi; o.pdf = 1 - R;
+        return evalTex(S, n.t1, uv);
     }
     }
     return f3(0.0f);

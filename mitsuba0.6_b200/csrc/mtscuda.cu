@@ -524,7 +524,7 @@ MTS_API int mtscuda_set_float_pool(MtsContext *c, const float *data, int64_t n) 
 MTS_API int mtscuda_set_bsdfs(MtsContext *c, const MtsBsdfNode *nodes, int32_t n) {
     c->nodes.assign(nodes, nodes + n); c->built = false;
     for (int i = 0; i < n; ++i) {
-        if (nodes[i].type < MTS_BSDF_DIFFUSE || nodes[i].type > MTS_BSDF_TWOSIDED) return fail(MTS_EINVAL, "unknown BSDF type");
+        if (nodes[i].type < MTS_BSDF_DIFFUSE || nodes[i].type > MTS_BSDF_THINDIELECTRIC) return fail(MTS_EINVAL, "unknown BSDF type");
         if (bsdfDepth(c->nodes, i) > kMaxBsdfDepth)
             return fail(MTS_EINVAL, "BSDF nesting deeper than 4 wrapper levels (coating/blendbsdf/bumpmap/twosided) is not supported");
     }

@@ -320,7 +320,7 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
     BSample bs; bs.pdf = 0; bs.eta = 1; bs.type = 0; bs.wo = f3(0.0f);
     float3 bsdfWeight = BsdfRoot::sample(S, bsdf, su, its.wi, make_float2(u.z, u.w), bs);
     if (isZero(bsdfWeight)) { finish(); return; }
-    flags |= PF_SCATTERED;
+    if (bs.type != MTS_ENULL) flags |= PF_SCATTERED;   // path.cpp:213
     const float3 wo = its.sh.toWorld(bs.wo);
     if (R.strictNormals && dot(its.geoN, wo) * cosTheta(bs.wo) <= 0) { finish(); return; }
 
@@ -358,7 +358,7 @@ __global__ void __launch_bounds__(256) k_shade_miss(const DScene S, const Wavefr
             // incremented when this ray was queued, so undo that for the path-length statistic
             if (!first) depth -= 1;
             float4 lv = W.L[slot];
-            if (S.hasEnv && !(first && R.hideEmitters)) {
+            if (S.hasEnv && !(R.hideEmitters && !(flags & PF_SCATTERED))) {   // path.cpp:140, 238-239
                 const float3 d = f3(W.rayD[slot]);
                 const float3 thr = f3(W.thr[slot]);
                 float3 L = f3(lv);

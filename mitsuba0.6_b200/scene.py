@@ -365,7 +365,7 @@ CONDUCTOR_PRESETS = {
 }
 
 SUPPORTED_BSDFS = ("diffuse", "conductor", "roughconductor", "plastic", "roughplastic", "dielectric",
-                   "coating", "blendbsdf", "bumpmap", "twosided")
+                   "coating", "blendbsdf", "bumpmap", "twosided", "thindielectric")
 
 
 class Unsupported(ValueError):
@@ -631,6 +631,17 @@ class FlatScene:
             n.t0 = self._ref(self.texref(p, name, 0.0))
             n.child[0] = self.bsdf(nested)
             n.lobes = self.nodes[n.child[0]].lobes
+        elif t == "thindielectric":
+            # ThinDielectric ctor / configure (src/bsdfs/thindielectric.cpp:71-124)
+            int_ior = hm.lookup_ior(p.get("intIOR"), "bk7")
+            ext_ior = hm.lookup_ior(p.get("extIOR"), "air")
+            if int_ior < 0 or ext_ior < 0:
+                raise ValueError("The interior and exterior indices of refraction must be positive!")
+            n.type = abi.BSDF_THINDIELECTRIC
+            n.eta[0] = F(int_ior) / F(ext_ior)
+            n.t0 = self._ref(self._conserve(self.texref(p, "specularReflectance", Spectrum(1.0))))
+            n.t1 = self._ref(self._conserve(self.texref(p, "specularTransmittance", Spectrum(1.0))))
+            n.lobes = abi.EDELTA_REFLECTION | abi.ENULL | abi.EFRONTSIDE | abi.EBACKSIDE
         elif t == "twosided":
             # TwoSidedBRDF::addChild / configure (src/bsdfs/twosided.cpp:86-105, 182-193)
             kids = [c for _, c in p.children_of("bsdf")]

@@ -444,6 +444,17 @@ inline V3 bsdfEval(const Materials &M, int node, const Its &its, V3 wi, V3 wo, i
             return evalTex(M, n.t1, its) * factor * factor * (1 - F);
         }
     }
+    case MTS_BSDF_THINDIELECTRIC: { /* thindielectric.cpp:145-166 */
+        float R = fresnelDielectricExt(std::fabs(Frame::cosTheta(wi)), n.eta[0]), T = 1 - R;
+        if (R < 1) R += T * T * R / (1 - R * R);
+        if (Frame::cosTheta(wi) * Frame::cosTheta(wo) >= 0) {
+            if (!discrete || std::fabs(dot(reflectZ(wi), wo) - 1) > kDeltaEps) return V3(0.0f);
+            return evalTex(M, n.t0, its) * R;
+        } else {
+            if (!discrete || std::fabs(dot(V3(-wi.x, -wi.y, -wi.z), wo) - 1) > kDeltaEps) return V3(0.0f);
+            return evalTex(M, n.t1, its) * (1 - R);
+        }
+    }
     case MTS_BSDF_COATING: { /* coating.cpp:221-258 */
         float eta = n.eta[0], invEta = 1 / eta;
         if (discrete && std::fabs(dot(reflectZ(wi), wo) - 1) < kDeltaEps) {
@@ -536,6 +547,17 @@ inline float bsdfPdf(const Materials &M, int node, const Its &its, V3 wi, V3 wo,
             V3 refr(scale * wi.x, scale * wi.y, cosThetaT);
             if (!discrete || std::fabs(dot(refr, wo) - 1) > kDeltaEps) return 0.0f;
             return 1 - F;
+        }
+    }
+    case MTS_BSDF_THINDIELECTRIC: { /* thindielectric.cpp:168-189 */
+        float R = fresnelDielectricExt(std::fabs(Frame::cosTheta(wi)), n.eta[0]), T = 1 - R;
+        if (R < 1) R += T * T * R / (1 - R * R);
+        if (Frame::cosTheta(wi) * Frame::cosTheta(wo) >= 0) {
+            if (!discrete || std::fabs(dot(reflectZ(wi), wo) - 1) > kDeltaEps) return 0.0f;
+            return R;
+        } else {
+            if (!discrete || std::fabs(dot(V3(-wi.x, -wi.y, -wi.z), wo) - 1) > kDeltaEps) return 0.0f;
+            return 1 - R;
         }
     }
     case MTS_BSDF_COATING: { /* coating.cpp:260-296 */
@@ -668,6 +690,17 @@ inline V3 bsdfSample(const Materials &M, int node, const Its &its, V3 wi, V2 sam
             float factor = cosThetaT < 0 ? invEta : eta;
             return evalTex(M, n.t1, its) * (factor * factor);
         }
+    }
+    case MTS_BSDF_THINDIELECTRIC: { /* thindielectric.cpp:191-221 */
+        float R = fresnelDielectricExt(std::fabs(Frame::cosTheta(wi)), n.eta[0]), T = 1 - R;
+        if (R < 1) R += T * T * R / (1 - R * R);
+        o.eta = 1.0f;
+        if (sample.x <= R) {
+            o.type = MTS_EDELTA_REFLECTION; o.wo = reflectZ(wi); o.pdf = R;
+            return evalTex(M, n.t0, its);
+        }
+        o.type = MTS_ENULL; o.wo = V3(-wi.x, -wi.y, -wi.z); o.pdf = 1 - R;
+        return evalTex(M, n.t1, its);
     }
     case MTS_BSDF_COATING: { /* coating.cpp:298-371 */
         float eta = n.eta[0], invEta = 1 / eta;

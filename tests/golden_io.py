@@ -20,8 +20,8 @@ def zoo(spp=4):
     return util.zoo_scene(width=ZOO_W, height=ZOO_H, spp=spp)
 
 
-def twosided(spp=4):
-    return util.twosided_scene(width=ZOO_W, height=ZOO_H, spp=spp)
+def twosided(spp=4, hide_env=False):
+    return util.twosided_scene(width=ZOO_W, height=ZOO_H, spp=spp, hide_env=hide_env)
 
 
 def cornell_small(spp=64):
@@ -110,6 +110,7 @@ IMAGE_SCENES = {
 # scenes of the "next" rows; stored in their own fixture so that the files above stay untouched
 TWOSIDED_IMAGE_SCENES = {
     "twosided": lambda: twosided(spp=8192)[0],
+    "thin_hide": lambda: twosided(spp=4096, hide_env=True)[0],
 }
 
 

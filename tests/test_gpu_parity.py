@@ -353,8 +353,9 @@ def test_twosided_bsdf_vs_reference(gtwosided, gold_twosided, name):
     GC.check_bsdf(gpu.ctx, flat, z, name, gold_twosided)
 
 
-def test_twosided_render_vs_reference(gold_twosided):
-    g = M.CudaPath(G.TWOSIDED_IMAGE_SCENES["twosided"](), backend="cuda")
-    err = GC.check_image(g, "twosided", gold_twosided, 8192, 3e-3, lazy_shadow=True)
-    print("relMSE(twosided, 8192 spp vs reference) = %.3g" % err)
+@pytest.mark.parametrize("name,spp,bar", [("twosided", 8192, 3e-3), ("thin_hide", 8192, 5e-3)])
+def test_twosided_render_vs_reference(gold_twosided, name, spp, bar):
+    g = M.CudaPath(G.TWOSIDED_IMAGE_SCENES[name](), backend="cuda")
+    err = GC.check_image(g, name, gold_twosided, spp, bar, lazy_shadow=True)
+    print("relMSE(%s, %d spp vs reference) = %.3g" % (name, spp, err))
     g.close()

@@ -192,10 +192,14 @@ def twosided_bsdfs():
     b.add(inner)
     b.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.5)))
     z["blend_ts_cond"] = b
+    # thindielectric (same 8(f) row): delta reflection + null transmission, internal reflections folded into R
+    z["thin_glass"] = Plugin("bsdf", "thindielectric", intIOR=1.5)
+    z["thin_tinted"] = Plugin("bsdf", "thindielectric", intIOR=1.33, extIOR=1.0, specularReflectance=Spectrum(0.8),
+                              specularTransmittance=Spectrum(0.9, 0.7, 0.5))
     return z
 
 
-def twosided_scene(width=96, height=64, spp=4):
+def twosided_scene(width=96, height=64, spp=4, hide_env=False):
     """Open surfaces seen and lit from both sides: free-standing rectangles carrying the twosided materials (front
     faces turned towards, away from and edge-on to the light), one plain one-sided rectangle for contrast."""
     sc = Plugin("scene", "")
@@ -229,4 +233,12 @@ def twosided_scene(width=96, height=64, spp=4):
     lt.add(Plugin("emitter", "area", radiance=Spectrum(25, 23, 20)))
     sc.add(lt)
     sc.add(Plugin("emitter", "point", position=Point(0, 2, -6), intensity=Spectrum(60, 60, 80)))   # lights the far sides
+    if hide_env:
+        # hideEmitters with an environment map seen directly, through the null-transmission panes (still hidden:
+        # `scattered` stays false, path.cpp:213,238) and by reflection (visible)
+        integ = sc.child("integrator")
+        integ.props["hideEmitters"] = True
+        env = Plugin("emitter", "envmap", scale=0.5)
+        env.data["bitmap"] = scenes.synthetic_envmap(128, 64)
+        sc.add(env)
     return sc, z
