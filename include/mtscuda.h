@@ -68,7 +68,8 @@ enum {
     MTS_BSDF_BLEND = 7,          /* blendbsdf.cpp */
     MTS_BSDF_BUMPMAP = 8,        /* bumpmap.cpp */
     MTS_BSDF_TWOSIDED = 9,       /* twosided.cpp */
-    MTS_BSDF_THINDIELECTRIC = 10 /* thindielectric.cpp */
+    MTS_BSDF_THINDIELECTRIC = 10, /* thindielectric.cpp */
+    MTS_BSDF_MASK = 11           /* mask.cpp */
 };
 
 /* node.flags */
@@ -125,6 +126,7 @@ typedef struct MtsTexRef {
  *   blendbsdf      t0 = weight; child[0], child[1]
  *   bumpmap        t0 = displacement; child[0] = nested
  *   thindielectric t0 = specularReflectance, t1 = specularTransmittance; eta[0]
+ *   mask           t0 = opacity; child[0] = nested
  *   twosided       child[0] = front-side BRDF, child[1] = back-side BRDF (= child[0] when only one is given)
  */
 typedef struct MtsBsdfNode {

@@ -679,6 +679,12 @@ template <int D> struct Bsdf {
             if (cosTheta(wo) * cosTheta(woP) <= 0) return f3(0.0f);
             return Next::eval(S, n.child[0], pert, wiP, woP, measure);
         }
+        case MTS_BSDF_MASK: {  // mask.cpp:106-116
+            float3 opacity = evalTex(S, n.t0, su.uv);
+            if (measure == MTS_MEASURE_SOLID_ANGLE) return Next::eval(S, n.child[0], su, wi, wo, measure) * opacity;
+            if (measure == MTS_MEASURE_DISCRETE && fabsf(1 - dot(wi, -wo)) < kDeltaEps) return f3(1.0f) - opacity;
+            return f3(0.0f);
+        }
         case MTS_BSDF_TWOSIDED: {  // twosided.cpp:107-119
             if (cosTheta(wi) > 0) return Next::eval(S, n.child[0], su, wi, wo, measure);
             wi.z = -wi.z; wo.z = -wo.z;
@@ -716,6 +722,12 @@ template <int D> struct Bsdf {
             float3 wiP = pert.sh.toLocal(su.sh.toWorld(wi)), woP = pert.sh.toLocal(su.sh.toWorld(wo));
             if (cosTheta(wo) * cosTheta(woP) <= 0) return 0;
             return Next::pdf(S, n.child[0], pert, wiP, woP, measure);
+        }
+        case MTS_BSDF_MASK: {  // mask.cpp:118-143
+            float prob = luminance(evalTex(S, n.t0, su.uv));
+            if (measure == MTS_MEASURE_SOLID_ANGLE) return Next::pdf(S, n.child[0], su, wi, wo, measure) * prob;
+            if (measure == MTS_MEASURE_DISCRETE && fabsf(1 - dot(wi, -wo)) < kDeltaEps) return 1 - prob;
+            return 0.0f;
         }
         case MTS_BSDF_TWOSIDED: {  // twosided.cpp:121-133
             if (wi.z > 0) return Next::pdf(S, n.child[0], su, wi, wo, measure);
@@ -784,6 +796,18 @@ template <int D> struct Bsdf {
                 if (cosTheta(o.wo) * cosTheta(woP) <= 0) return f3(0.0f);
             }
             return result;
+        }
+        case MTS_BSDF_MASK: {  // mask.cpp:187-226 (pdf-returning overload)
+            float3 opacity = evalTex(S, n.t0, su.uv);
+            float prob = luminance(opacity);
+            if (sample.x < prob) {
+                sample.x /= prob;
+                float3 result = Next::sample(S, n.child[0], su, wi, sample, o) * opacity / prob;
+                o.pdf *= prob;
+                return result;
+            }
+            o.wo = -wi; o.eta = 1.0f; o.type = MTS_ENULL; o.pdf = 1 - prob;
+            return (f3(1.0f) - opacity) / o.pdf;
         }
         case MTS_BSDF_TWOSIDED: {  // twosided.cpp:158-180
             bool flipped = cosTheta(wi) < 0;

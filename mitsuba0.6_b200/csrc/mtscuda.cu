@@ -156,7 +156,7 @@ template <class T> int devUpload(MtsContext *c, const T *host, size_t n, const T
 int bsdfDepth(const std::vector<MtsBsdfNode> &nodes, int i, int guard = 0) {
     if (i < 0 || i >= (int)nodes.size() || guard > 64) return 1000;
     const MtsBsdfNode &n = nodes[i];
-    if (n.type == MTS_BSDF_COATING || n.type == MTS_BSDF_BUMPMAP) return 1 + bsdfDepth(nodes, n.child[0], guard + 1);
+    if (n.type == MTS_BSDF_COATING || n.type == MTS_BSDF_BUMPMAP || n.type == MTS_BSDF_MASK) return 1 + bsdfDepth(nodes, n.child[0], guard + 1);
     if (n.type == MTS_BSDF_BLEND || n.type == MTS_BSDF_TWOSIDED) return 1 + std::max(bsdfDepth(nodes, n.child[0], guard + 1), bsdfDepth(nodes, n.child[1], guard + 1));
     return 0;
 }
@@ -524,9 +524,9 @@ MTS_API int mtscuda_set_float_pool(MtsContext *c, const float *data, int64_t n) 
 MTS_API int mtscuda_set_bsdfs(MtsContext *c, const MtsBsdfNode *nodes, int32_t n) {
     c->nodes.assign(nodes, nodes + n); c->built = false;
     for (int i = 0; i < n; ++i) {
-        if (nodes[i].type < MTS_BSDF_DIFFUSE || nodes[i].type > MTS_BSDF_THINDIELECTRIC) return fail(MTS_EINVAL, "unknown BSDF type");
+        if (nodes[i].type < MTS_BSDF_DIFFUSE || nodes[i].type > MTS_BSDF_MASK) return fail(MTS_EINVAL, "unknown BSDF type");
         if (bsdfDepth(c->nodes, i) > kMaxBsdfDepth)
-            return fail(MTS_EINVAL, "BSDF nesting deeper than 4 wrapper levels (coating/blendbsdf/bumpmap/twosided) is not supported");
+            return fail(MTS_EINVAL, "BSDF nesting deeper than 4 wrapper levels (coating/blendbsdf/bumpmap/twosided/mask) is not supported");
     }
     return MTS_OK;
 }

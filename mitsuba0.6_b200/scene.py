@@ -365,7 +365,7 @@ CONDUCTOR_PRESETS = {
 }
 
 SUPPORTED_BSDFS = ("diffuse", "conductor", "roughconductor", "plastic", "roughplastic", "dielectric",
-                   "coating", "blendbsdf", "bumpmap", "twosided", "thindielectric")
+                   "coating", "blendbsdf", "bumpmap", "twosided", "thindielectric", "mask")
 
 
 class Unsupported(ValueError):
@@ -642,6 +642,15 @@ class FlatScene:
             n.t0 = self._ref(self._conserve(self.texref(p, "specularReflectance", Spectrum(1.0))))
             n.t1 = self._ref(self._conserve(self.texref(p, "specularTransmittance", Spectrum(1.0))))
             n.lobes = abi.EDELTA_REFLECTION | abi.ENULL | abi.EFRONTSIDE | abi.EBACKSIDE
+        elif t == "mask":
+            # Mask ctor / configure / addChild (src/bsdfs/mask.cpp:62-104, 232-239)
+            nested = p.child("bsdf")
+            if nested is None:
+                raise ValueError("A child BSDF is required")
+            n.type = abi.BSDF_MASK
+            n.t0 = self._ref(self._conserve(self.texref(p, "opacity", Spectrum(0.5))))
+            n.child[0] = self.bsdf(nested)
+            n.lobes = self.nodes[n.child[0]].lobes | abi.ENULL | abi.EFRONTSIDE | abi.EBACKSIDE
         elif t == "twosided":
             # TwoSidedBRDF::addChild / configure (src/bsdfs/twosided.cpp:86-105, 182-193)
             kids = [c for _, c in p.children_of("bsdf")]

@@ -482,6 +482,12 @@ inline V3 bsdfEval(const Materials &M, int node, const Its &its, V3 wi, V3 wo, i
         if (Frame::cosTheta(wo) * Frame::cosTheta(woP) <= 0) return V3(0.0f);
         return bsdfEval(M, n.child[0], pert, wiP, woP, measure);
     }
+    case MTS_BSDF_MASK: { /* mask.cpp:106-116 */
+        V3 opacity = evalTex(M, n.t0, its);
+        if (measure == MTS_MEASURE_SOLID_ANGLE) return bsdfEval(M, n.child[0], its, wi, wo, measure) * opacity;
+        if (measure == MTS_MEASURE_DISCRETE && std::fabs(1 - dot(wi, V3(-wo.x, -wo.y, -wo.z))) < kDeltaEps) return V3(1.0f) - opacity;
+        return V3(0.0f);
+    }
     case MTS_BSDF_TWOSIDED: { /* twosided.cpp:107-119 */
         if (Frame::cosTheta(wi) > 0) return bsdfEval(M, n.child[0], its, wi, wo, measure);
         return bsdfEval(M, n.child[1], its, V3(wi.x, wi.y, -wi.z), V3(wo.x, wo.y, -wo.z), measure);
@@ -587,6 +593,12 @@ inline float bsdfPdf(const Materials &M, int node, const Its &its, V3 wi, V3 wo,
         V3 wiP = pert.toLocal(its.toWorld(wi)), woP = pert.toLocal(its.toWorld(wo));
         if (Frame::cosTheta(wo) * Frame::cosTheta(woP) <= 0) return 0;
         return bsdfPdf(M, n.child[0], pert, wiP, woP, measure);
+    }
+    case MTS_BSDF_MASK: { /* mask.cpp:118-143 */
+        float prob = luminance(evalTex(M, n.t0, its));
+        if (measure == MTS_MEASURE_SOLID_ANGLE) return bsdfPdf(M, n.child[0], its, wi, wo, measure) * prob;
+        if (measure == MTS_MEASURE_DISCRETE && std::fabs(1 - dot(wi, V3(-wo.x, -wo.y, -wo.z))) < kDeltaEps) return 1 - prob;
+        return 0.0f;
     }
     case MTS_BSDF_TWOSIDED: { /* twosided.cpp:121-133 */
         if (wi.z > 0) return bsdfPdf(M, n.child[0], its, wi, wo, measure);
@@ -761,6 +773,18 @@ inline V3 bsdfSample(const Materials &M, int node, const Its &its, V3 wi, V2 sam
             if (Frame::cosTheta(o.wo) * Frame::cosTheta(woP) <= 0) return V3(0.0f);
         }
         return result;
+    }
+    case MTS_BSDF_MASK: { /* mask.cpp:187-226 */
+        V3 opacity = evalTex(M, n.t0, its);
+        float prob = luminance(opacity);
+        if (sample.x < prob) {
+            sample.x /= prob;
+            V3 result = bsdfSample(M, n.child[0], its, wi, sample, o) * opacity / prob;
+            o.pdf *= prob;
+            return result;
+        }
+        o.wo = V3(-wi.x, -wi.y, -wi.z); o.eta = 1.0f; o.type = MTS_ENULL; o.pdf = 1 - prob;
+        return (V3(1.0f) - opacity) / o.pdf;
     }
     case MTS_BSDF_TWOSIDED: { /* twosided.cpp:158-180 (the pdf-returning overload path.cpp:236 calls) */
         bool flipped = Frame::cosTheta(wi) < 0;

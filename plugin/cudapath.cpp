@@ -508,13 +508,18 @@ private:
                 TexInfo r = conserve(parseTexture(s, tex)), t = conserve(parseTexture(s, tex));
                 n.type = MTS_BSDF_THINDIELECTRIC; n.eta[0] = eta; n.t0 = r.ref; n.t1 = t.ref;
                 n.lobes = MTS_EDELTA_REFLECTION | MTS_ENULL | MTS_EFRONTSIDE | MTS_EBACKSIDE;
+            } else if (cls == "Mask") {   /* mask.cpp:76-80: opacity texture, then the nested BSDF */
+                TexInfo op = conserve(parseTexture(s, tex));
+                int nested = parseBsdf(s, seen, tex);
+                n.type = MTS_BSDF_MASK; n.t0 = op.ref; n.child[0] = nested;
+                n.lobes = m_nodes[nested].lobes | MTS_ENULL | MTS_EFRONTSIDE | MTS_EBACKSIDE;
             } else if (cls == "TwoSidedBRDF") {   /* twosided.cpp:77-83: BSDF::serialize, then the two nested instances */
                 int a = parseBsdf(s, seen, tex), b = parseBsdf(s, seen, tex);
                 n.type = MTS_BSDF_TWOSIDED; n.child[0] = a; n.child[1] = b;
                 n.lobes = ((m_nodes[a].lobes & ~MTS_EBACKSIDE) | MTS_EFRONTSIDE) | ((m_nodes[b].lobes & ~MTS_EFRONTSIDE) | MTS_EBACKSIDE);
             } else
                 err("BSDF class " + cls + " is out of scope (diffuse, conductor, roughconductor, plastic, roughplastic, "
-                    "dielectric, coating, blendbsdf, bumpmap, twosided, thindielectric)");
+                    "dielectric, coating, blendbsdf, bumpmap, twosided, thindielectric, mask)");
             m_nodes[idx] = n;
             return idx;
         }

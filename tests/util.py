@@ -194,6 +194,14 @@ def twosided_bsdfs():
     z["blend_ts_cond"] = b
     # thindielectric (same 8(f) row): delta reflection + null transmission, internal reflections folded into R
     z["thin_glass"] = Plugin("bsdf", "thindielectric", intIOR=1.5)
+    # mask (same row): opacity-weighted nested BSDF + null transmission; constant and textured opacity
+    mk = Plugin("bsdf", "mask", opacity=Spectrum(0.3, 0.6, 0.8))
+    mk.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.8, 0.7, 0.3)))
+    z["mask_diffuse"] = mk
+    mk2 = Plugin("bsdf", "mask")
+    mk2.add(_tex(12, channels=3, uvscale=3.0), "opacity")
+    mk2.add(Plugin("bsdf", "roughconductor", distribution="beckmann", alpha=0.2, **AU))
+    z["mask_tex_rc"] = mk2
     z["thin_tinted"] = Plugin("bsdf", "thindielectric", intIOR=1.33, extIOR=1.0, specularReflectance=Spectrum(0.8),
                               specularTransmittance=Spectrum(0.9, 0.7, 0.5))
     return z
