@@ -36,6 +36,23 @@ def test_cudapath_plugin_in_reference_host(name, bar):
 
 
 @needs_ref
+@pytest.mark.parametrize("name,bar", [("twosided", 3e-3), ("thin_hide", 5e-3)])
+def test_cudapath_plugin_next_row_bsdfs(name, bar):
+    # TwoSidedBRDF / ThinDielectric / Mask parsed from the live reference objects (InstanceManager serialization);
+    # thin_hide also passes hideEmitters through the plugin's Properties
+    gold = G.load("twosided.npz")
+    sc = G.TWOSIDED_IMAGE_SCENES[name]()
+    rs = mtsref.RefScene(sc, integrator="cudapath")
+    img = M.develop(rs.render())
+    ref = gold["image/%s/rgb" % name].astype(np.float32)
+    assert np.isfinite(img).all() and img.mean() > 0
+    err = M.rel_mse(img, ref)
+    print("cudapath.so inside the reference host: relMSE(%s) = %.3g" % (name, err))
+    assert abs(img.mean() / ref.mean() - 1) < 0.02
+    assert err < bar, (name, err)
+
+
+@needs_ref
 def test_cudapath_plugin_parameter_errors():
     sc = G.cornell_small(spp=1)
     sc.child("integrator").props["rrDepth"] = 0
