@@ -69,7 +69,8 @@ enum {
     MTS_BSDF_BUMPMAP = 8,        /* bumpmap.cpp */
     MTS_BSDF_TWOSIDED = 9,       /* twosided.cpp */
     MTS_BSDF_THINDIELECTRIC = 10, /* thindielectric.cpp */
-    MTS_BSDF_MASK = 11           /* mask.cpp */
+    MTS_BSDF_MASK = 11,          /* mask.cpp */
+    MTS_BSDF_ROUGHDIELECTRIC = 12 /* roughdielectric.cpp */
 };
 
 /* node.flags */
@@ -92,6 +93,11 @@ enum {
     MTS_EFRONTSIDE = 0x08000,
     MTS_EBACKSIDE = 0x10000
 };
+/* Third random number of the per-function BSDF probes (bsdf_sample takes two): BSDFs that draw from
+ * bRec.sampler (roughdielectric.cpp:405) get this integer hash of the two given numbers, bit-identical in the
+ * reference probe, the oracle and the CUDA library.  The renderers use their own sample streams. */
+#define MTS_PROBE_U3(xbits, ybits, out) do { uint32_t h_ = (xbits) * 0x9E3779B1u ^ (ybits) * 0x85EBCA77u; h_ ^= h_ >> 15; \
+    h_ *= 0xC2B2AE3Du; h_ ^= h_ >> 13; (out) = (float)(h_ >> 8) * (1.0f / 16777216.0f); } while (0)
 #define MTS_ESMOOTH (MTS_EDIFFUSE_REFLECTION | MTS_EDIFFUSE_TRANSMISSION | MTS_EGLOSSY_REFLECTION | MTS_EGLOSSY_TRANSMISSION)
 #define MTS_EDELTA (MTS_ENULL | MTS_EDELTA_REFLECTION | MTS_EDELTA_TRANSMISSION)
 #define MTS_ETRANSMISSION (MTS_EDIFFUSE_TRANSMISSION | MTS_EGLOSSY_TRANSMISSION | MTS_EDELTA_TRANSMISSION | MTS_ENULL)
@@ -127,6 +133,9 @@ typedef struct MtsTexRef {
  *   bumpmap        t0 = displacement; child[0] = nested
  *   thindielectric t0 = specularReflectance, t1 = specularTransmittance; eta[0]
  *   mask           t0 = opacity; child[0] = nested
+ *   roughdielectric t0 = specularReflectance, t1 = alphaU, t2 = alphaV; eta[0] = intIOR/extIOR;
+ *                  specularTransmittance = k[0..2] (scale) x bitmap texture lut[0] (-1: constant) -- a fourth
+ *                  MtsTexRef folded into the otherwise unused k/lut slots
  *   twosided       child[0] = front-side BRDF, child[1] = back-side BRDF (= child[0] when only one is given)
  */
 typedef struct MtsBsdfNode {

@@ -22,7 +22,7 @@ EPSILON = 1e-4
 
 # ---- enums (mirror include/mtscuda.h) --------------------------------------
 BSDF_DIFFUSE, BSDF_CONDUCTOR, BSDF_ROUGHCONDUCTOR, BSDF_PLASTIC, BSDF_ROUGHPLASTIC, \
-    BSDF_DIELECTRIC, BSDF_COATING, BSDF_BLEND, BSDF_BUMPMAP, BSDF_TWOSIDED, BSDF_THINDIELECTRIC, BSDF_MASK = range(12)
+    BSDF_DIELECTRIC, BSDF_COATING, BSDF_BLEND, BSDF_BUMPMAP, BSDF_TWOSIDED, BSDF_THINDIELECTRIC, BSDF_MASK, BSDF_ROUGHDIELECTRIC = range(13)
 BF_GGX, BF_SAMPLE_VISIBLE, BF_NONLINEAR, BF_RT_2D = 1, 2, 4, 8
 ENULL, EDIFFUSE_REFLECTION, EDIFFUSE_TRANSMISSION, EGLOSSY_REFLECTION, EGLOSSY_TRANSMISSION, \
     EDELTA_REFLECTION, EDELTA_TRANSMISSION = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20, 0x40

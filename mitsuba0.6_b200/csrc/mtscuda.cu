@@ -377,6 +377,7 @@ __global__ void k_hook_bsdf_sample(const DScene S, int bsdf, int64_t n, const fl
     Surf su = surfFromArray(surf + 16 * i);
     float3 a = f3(wi[3 * i], wi[3 * i + 1], wi[3 * i + 2]);
     BSample bs; bs.wo = f3(0.0f); bs.pdf = 0; bs.eta = 1; bs.type = 0;
+    MTS_PROBE_U3(__float_as_uint(u[2 * i]), __float_as_uint(u[2 * i + 1]), bs.u3);
     float3 w = BsdfRoot::sample(S, bsdf, su, a, make_float2(u[2 * i], u[2 * i + 1]), bs);
     float *q = out + 12 * i;
     if (isZero(w)) { for (int k = 0; k < 12; ++k) q[k] = 0; return; }
@@ -524,7 +525,7 @@ MTS_API int mtscuda_set_float_pool(MtsContext *c, const float *data, int64_t n) 
 MTS_API int mtscuda_set_bsdfs(MtsContext *c, const MtsBsdfNode *nodes, int32_t n) {
     c->nodes.assign(nodes, nodes + n); c->built = false;
     for (int i = 0; i < n; ++i) {
-        if (nodes[i].type < MTS_BSDF_DIFFUSE || nodes[i].type > MTS_BSDF_MASK) return fail(MTS_EINVAL, "unknown BSDF type");
+        if (nodes[i].type < MTS_BSDF_DIFFUSE || nodes[i].type > MTS_BSDF_ROUGHDIELECTRIC) return fail(MTS_EINVAL, "unknown BSDF type");
         if (bsdfDepth(c->nodes, i) > kMaxBsdfDepth)
             return fail(MTS_EINVAL, "BSDF nesting deeper than 4 wrapper levels (coating/blendbsdf/bumpmap/twosided/mask) is not supported");
     }

@@ -317,7 +317,9 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
     }
 
     // ---- BSDF sampling (path.cpp:203-253) ----
-    BSample bs; bs.pdf = 0; bs.eta = 1; bs.type = 0; bs.wo = f3(0.0f);
+    BSample bs; bs.pdf = 0; bs.eta = 1; bs.type = 0; bs.wo = f3(0.0f); bs.u3 = 0;
+    // EUsesSampler models (roughdielectric.cpp:405 bRec.sampler->next1D()) draw from their own dimension
+    if (lobes & MTS_EGLOSSY_TRANSMISSION) bs.u3 = rand4(R.seed, meta.x, meta.y, 0x4000u + depth).x;
     float3 bsdfWeight = BsdfRoot::sample(S, bsdf, su, its.wi, make_float2(u.z, u.w), bs);
     if (isZero(bsdfWeight)) { finish(); return; }
     if (bs.type != MTS_ENULL) flags |= PF_SCATTERED;   // path.cpp:213

@@ -365,7 +365,7 @@ CONDUCTOR_PRESETS = {
 }
 
 SUPPORTED_BSDFS = ("diffuse", "conductor", "roughconductor", "plastic", "roughplastic", "dielectric",
-                   "coating", "blendbsdf", "bumpmap", "twosided", "thindielectric", "mask")
+                   "coating", "blendbsdf", "bumpmap", "twosided", "thindielectric", "mask", "roughdielectric")
 
 
 class Unsupported(ValueError):
@@ -531,6 +531,26 @@ class FlatScene:
                 au, av = self.texref(p, "alphaU", 0.1), self.texref(p, "alphaV", 0.1)
             n.type, n.t0, n.t1, n.t2 = abi.BSDF_ROUGHCONDUCTOR, self._ref(r), self._ref(au), self._ref(av)
             n.lobes = abi.EGLOSSY_REFLECTION
+        elif t == "roughdielectric":
+            # RoughDielectric ctor / addChild / configure (src/bsdfs/roughdielectric.cpp:183-211, 246-270, 618-636)
+            int_ior = hm.lookup_ior(p.get("intIOR"), "bk7")
+            ext_ior = hm.lookup_ior(p.get("extIOR"), "air")
+            if int_ior < 0 or ext_ior < 0 or int_ior == ext_ior:
+                raise ValueError("The interior and exterior indices of refraction must be positive and differ!")
+            n.type = abi.BSDF_ROUGHDIELECTRIC
+            n.eta[0] = F(int_ior) / F(ext_ior)
+            n.flags = microfacet()
+            if p.child("texture", "alpha") is not None or "alpha" in p.props:
+                au = av = self.texref(p, "alpha", 0.1)
+            else:
+                au, av = self.texref(p, "alphaU", 0.1), self.texref(p, "alphaV", 0.1)
+            r = self._conserve(self.texref(p, "specularReflectance", Spectrum(1.0)))
+            tr = self._ref(self._conserve(self.texref(p, "specularTransmittance", Spectrum(1.0))))
+            n.t0, n.t1, n.t2 = self._ref(r), self._ref(au), self._ref(av)
+            for i in range(3):          # fourth texture reference lives in the k / lut slots (include/mtscuda.h)
+                n.k[i] = tr.scale[i]
+            n.lut[0] = tr.tex
+            n.lobes = abi.EGLOSSY_REFLECTION | abi.EGLOSSY_TRANSMISSION | abi.EFRONTSIDE | abi.EBACKSIDE
         elif t in ("plastic", "roughplastic"):
             int_ior = hm.lookup_ior(p.get("intIOR"), "polypropylene")
             ext_ior = hm.lookup_ior(p.get("extIOR"), "air")

@@ -626,7 +626,9 @@ V3 Li(MtsContext &c, const MtsRenderParams &P, V3 o, V3 d, float mint, float max
 
         /* BSDF sampling */
         BSample bs; bs.pdf = 0; bs.eta = 1; bs.type = 0;
-        V3 bsdfWeight = bsdfSample(c.mat, bsdf, its, its.wi, rng.next2D(), bs);
+        const V2 uBsdf = rng.next2D();
+        if (lobes & MTS_EGLOSSY_TRANSMISSION) bs.u3 = rng.next1D(); /* roughdielectric.cpp:405 */
+        V3 bsdfWeight = bsdfSample(c.mat, bsdf, its, its.wi, uBsdf, bs);
         if (isZero(bsdfWeight)) break;
         scattered |= bs.type != MTS_ENULL;
         const V3 wo = its.toWorld(bs.wo);
@@ -1030,6 +1032,7 @@ MTS_API int mtsoracle_bsdf_sample(MtsContext *c, int32_t bsdf, int64_t n, const 
         V3 a(wi[3 * i], wi[3 * i + 1], wi[3 * i + 2]);
         its.wi = a;
         BSample bs; bs.wo = V3(0.0f); bs.pdf = 0; bs.eta = 1; bs.type = 0;
+        { uint32_t xb, yb; std::memcpy(&xb, u + 2 * i, 4); std::memcpy(&yb, u + 2 * i + 1, 4); MTS_PROBE_U3(xb, yb, bs.u3); }
         V3 w = bsdfSample(c->mat, bsdf, its, a, V2{u[2 * i], u[2 * i + 1]}, bs);
         float *q = out + 12 * i;
         if (isZero(w)) { for (int k = 0; k < 12; ++k) q[k] = 0; continue; }

@@ -113,6 +113,7 @@ struct Microfacet {
         alphaU = std::max(au, 1e-4f); alphaV = std::max(av, 1e-4f); /* :70-71 */
     }
     bool isIsotropic() const { return alphaU == alphaV; }
+    void scaleAlpha(float v) { alphaU *= v; alphaV *= v; } /* :178-180 */
     /* :191-234 */
     float eval(V3 m) const {
         if (Frame::cosTheta(m) <= 0) return 0.0f;
@@ -330,7 +331,8 @@ inline int measureOf(uint32_t sampledType) {
     return (sampledType & MTS_ESMOOTH) ? MTS_MEASURE_SOLID_ANGLE : MTS_MEASURE_DISCRETE;
 }
 
-struct BSample { V3 wo; float pdf; float eta; uint32_t type; };
+struct BSample { V3 wo; float pdf; float eta; uint32_t type; float u3 = 0; }; /* u3: input, bRec.sampler->next1D() of EUsesSampler models */
+inline MtsTexRef roughDielTransmittance(const MtsBsdfNode &n) { MtsTexRef r; r.scale[0] = n.k[0]; r.scale[1] = n.k[1]; r.scale[2] = n.k[2]; r.tex = n.lut[0]; return r; }
 
 V3 bsdfEval(const Materials &M, int node, const Its &its, V3 wi, V3 wo, int measure);
 float bsdfPdf(const Materials &M, int node, const Its &its, V3 wi, V3 wo, int measure);
@@ -444,6 +446,26 @@ inline V3 bsdfEval(const Materials &M, int node, const Its &its, V3 wi, V3 wo, i
             return evalTex(M, n.t1, its) * factor * factor * (1 - F);
         }
     }
+    case MTS_BSDF_ROUGHDIELECTRIC: { /* roughdielectric.cpp:272-348 */
+        if (!solid || Frame::cosTheta(wi) == 0) return V3(0.0f);
+        const float eta = n.eta[0], invEta = 1 / eta;
+        const bool reflect = Frame::cosTheta(wi) * Frame::cosTheta(wo) > 0;
+        V3 H;
+        if (reflect) H = normalize(wo + wi);
+        else H = normalize(wi + wo * (Frame::cosTheta(wi) > 0 ? eta : invEta));
+        H = H * signum(Frame::cosTheta(H));
+        Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(M, n.t1, its)), average(evalTex(M, n.t2, its)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+        const float D = distr.eval(H);
+        if (D == 0) return V3(0.0f);
+        const float F = fresnelDielectricExt(dot(wi, H), eta);
+        const float G = distr.G(wi, wo, H);
+        if (reflect) return evalTex(M, n.t0, its) * (F * D * G / (4.0f * std::fabs(Frame::cosTheta(wi))));
+        const float e = Frame::cosTheta(wi) > 0.0f ? eta : invEta;
+        const float sqrtDenom = dot(wi, H) + e * dot(wo, H);
+        const float value = ((1 - F) * D * G * e * e * dot(wi, H) * dot(wo, H)) / (Frame::cosTheta(wi) * sqrtDenom * sqrtDenom);
+        const float factor = Frame::cosTheta(wi) > 0 ? invEta : eta; /* ERadiance */
+        return evalTex(M, roughDielTransmittance(n), its) * std::fabs(value * factor * factor);
+    }
     case MTS_BSDF_THINDIELECTRIC: { /* thindielectric.cpp:145-166 */
         float R = fresnelDielectricExt(std::fabs(Frame::cosTheta(wi)), n.eta[0]), T = 1 - R;
         if (R < 1) R += T * T * R / (1 - R * R);
@@ -554,6 +576,28 @@ inline float bsdfPdf(const Materials &M, int node, const Its &its, V3 wi, V3 wo,
             if (!discrete || std::fabs(dot(refr, wo) - 1) > kDeltaEps) return 0.0f;
             return 1 - F;
         }
+    }
+    case MTS_BSDF_ROUGHDIELECTRIC: { /* roughdielectric.cpp:350-420 */
+        if (!solid) return 0.0f;
+        const float eta = n.eta[0], invEta = 1 / eta;
+        const bool reflect = Frame::cosTheta(wi) * Frame::cosTheta(wo) > 0;
+        V3 H; float dwh_dwo;
+        if (reflect) {
+            H = normalize(wo + wi);
+            dwh_dwo = 1.0f / (4.0f * dot(wo, H));
+        } else {
+            const float e = Frame::cosTheta(wi) > 0 ? eta : invEta;
+            H = normalize(wi + wo * e);
+            const float sqrtDenom = dot(wi, H) + e * dot(wo, H);
+            dwh_dwo = (e * e * dot(wo, H)) / (sqrtDenom * sqrtDenom);
+        }
+        H = H * signum(Frame::cosTheta(H));
+        Microfacet sampleDistr(n.flags & MTS_BF_GGX, average(evalTex(M, n.t1, its)), average(evalTex(M, n.t2, its)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+        if (!sampleDistr.sampleVisible) sampleDistr.scaleAlpha(1.2f - 0.2f * std::sqrt(std::fabs(Frame::cosTheta(wi))));
+        float prob = sampleDistr.pdf(wi * signum(Frame::cosTheta(wi)), H);
+        const float F = fresnelDielectricExt(dot(wi, H), eta);
+        prob *= reflect ? F : (1 - F);
+        return std::fabs(prob * dwh_dwo);
     }
     case MTS_BSDF_THINDIELECTRIC: { /* thindielectric.cpp:168-189 */
         float R = fresnelDielectricExt(std::fabs(Frame::cosTheta(wi)), n.eta[0]), T = 1 - R;
@@ -702,6 +746,42 @@ inline V3 bsdfSample(const Materials &M, int node, const Its &its, V3 wi, V2 sam
             float factor = cosThetaT < 0 ? invEta : eta;
             return evalTex(M, n.t1, its) * (factor * factor);
         }
+    }
+    case MTS_BSDF_ROUGHDIELECTRIC: { /* roughdielectric.cpp:517-616 (pdf-returning overload) */
+        const float eta = n.eta[0], invEta = 1 / eta;
+        Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(M, n.t1, its)), average(evalTex(M, n.t2, its)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+        Microfacet sampleDistr = distr;
+        if (!distr.sampleVisible) sampleDistr.scaleAlpha(1.2f - 0.2f * std::sqrt(std::fabs(Frame::cosTheta(wi))));
+        float microfacetPDF;
+        const V3 m = sampleDistr.sample(wi * signum(Frame::cosTheta(wi)), sample, microfacetPDF);
+        if (microfacetPDF == 0) return V3(0.0f);
+        o.pdf = microfacetPDF;
+        float cosThetaT;
+        const float F = fresnelDielectricExt(dot(wi, m), cosThetaT, eta);
+        V3 weight(1.0f);
+        bool sampleReflection = true;
+        if (o.u3 > F) { sampleReflection = false; o.pdf *= 1 - F; } else o.pdf *= F; /* bRec.sampler->next1D() */
+        float dwh_dwo;
+        if (sampleReflection) {
+            o.wo = reflectM(wi, m); o.eta = 1.0f; o.type = MTS_EGLOSSY_REFLECTION;
+            if (Frame::cosTheta(wi) * Frame::cosTheta(o.wo) <= 0) return V3(0.0f);
+            weight *= evalTex(M, n.t0, its);
+            dwh_dwo = 1.0f / (4.0f * dot(o.wo, m));
+        } else {
+            if (cosThetaT == 0) return V3(0.0f);
+            const float e = cosThetaT < 0 ? invEta : eta; /* refract(wi, m, eta, cosThetaT), util.cpp:767-772 */
+            o.wo = m * (dot(wi, m) * e + cosThetaT) - wi * e;
+            o.eta = cosThetaT < 0 ? eta : invEta; o.type = MTS_EGLOSSY_TRANSMISSION;
+            if (Frame::cosTheta(wi) * Frame::cosTheta(o.wo) >= 0) return V3(0.0f);
+            const float factor = cosThetaT < 0 ? invEta : eta; /* ERadiance */
+            weight *= evalTex(M, roughDielTransmittance(n), its) * (factor * factor);
+            const float sqrtDenom = dot(wi, m) + o.eta * dot(o.wo, m);
+            dwh_dwo = (o.eta * o.eta * dot(o.wo, m)) / (sqrtDenom * sqrtDenom);
+        }
+        if (distr.sampleVisible) weight *= distr.smithG1(o.wo, m);
+        else weight *= std::fabs(distr.eval(m) * distr.G(wi, o.wo, m) * dot(wi, m) / (microfacetPDF * Frame::cosTheta(wi)));
+        o.pdf *= std::fabs(dwh_dwo);
+        return weight;
     }
     case MTS_BSDF_THINDIELECTRIC: { /* thindielectric.cpp:191-221 */
         float R = fresnelDielectricExt(std::fabs(Frame::cosTheta(wi)), n.eta[0]), T = 1 - R;

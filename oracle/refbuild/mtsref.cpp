@@ -32,6 +32,7 @@
 #include <mitsuba/render/integrator.h>
 #include <mitsuba/render/shape.h>
 #include <chrono>
+#include <cstring>
 #include <iostream>
 #include <map>
 #include <string>
@@ -248,12 +249,29 @@ int mtsref_bsdf_eval_pdf(void *b, int64_t n, const float *surf, const float *wi,
     return 0;
     GUARD_END
 }
+/* BSDFs with EUsesSampler (roughdielectric) draw one more number through bRec.sampler->next1D().  The probes feed
+   it a value derived from the two given numbers by an integer hash (exact on every side; include/mtscuda.h,
+   MTS_PROBE_U3), so the reference, the oracle and the CUDA library see identical inputs. */
+class ProbeSampler : public Sampler {
+public:
+    ProbeSampler() : Sampler(Properties()), value(0) { }
+    Float next1D() { return value; }
+    Point2 next2D() { return Point2(value, value); }
+    Float value;
+};
+static float probeU3(float a, float b) {
+    uint32_t x, y; memcpy(&x, &a, 4); memcpy(&y, &b, 4);
+    uint32_t h = x * 0x9E3779B1u ^ y * 0x85EBCA77u; h ^= h >> 15; h *= 0xC2B2AE3Du; h ^= h >> 13;
+    return (float)(h >> 8) * (1.0f / 16777216.0f);
+}
 int mtsref_bsdf_sample(void *b, int64_t n, const float *surf, const float *wi, const float *u, float *out) {
     GUARD_BEGIN
     const BSDF *bsdf = (const BSDF *)b;
+    ref<ProbeSampler> ps = new ProbeSampler();
     for (int64_t i = 0; i < n; ++i) {
         Intersection its = makeIts(surf + 16 * i);
-        BSDFSamplingRecord bRec(its, NULL, ERadiance);
+        ps->value = probeU3(u[2 * i], u[2 * i + 1]);
+        BSDFSamplingRecord bRec(its, ps.get(), ERadiance);
         bRec.wi = Vector(wi[3 * i], wi[3 * i + 1], wi[3 * i + 2]);
         Float pdf = 0;
         Spectrum w = bsdf->sample(bRec, pdf, Point2(u[2 * i], u[2 * i + 1]));

@@ -442,6 +442,16 @@ private:
                 n.type = MTS_BSDF_ROUGHCONDUCTOR; n.flags = distrFlags(type, sv);
                 n.t0 = r.ref; n.t1 = au.ref; n.t2 = av.ref; n.lobes = MTS_EGLOSSY_REFLECTION;
                 setRGB(eta, n.eta); setRGB(k, n.k);
+            } else if (cls == "RoughDielectric") {   /* roughdielectric.cpp:233-244 */
+                uint32_t type = s->readUInt(); bool sv = s->readBool();
+                TexInfo au = parseTexture(s, tex), av = parseTexture(s, tex);
+                TexInfo r = conserve(parseTexture(s, tex)), t = conserve(parseTexture(s, tex));
+                Float eta = s->readFloat();
+                n.type = MTS_BSDF_ROUGHDIELECTRIC; n.flags = distrFlags(type, sv); n.eta[0] = eta;
+                n.t0 = r.ref; n.t1 = au.ref; n.t2 = av.ref;
+                for (int i = 0; i < 3; ++i) n.k[i] = t.ref.scale[i];   /* fourth texture reference: k / lut slots */
+                n.lut[0] = t.ref.tex;
+                n.lobes = MTS_EGLOSSY_REFLECTION | MTS_EGLOSSY_TRANSMISSION | MTS_EFRONTSIDE | MTS_EBACKSIDE;
             } else if (cls == "SmoothPlastic") {
                 Float eta = s->readFloat(); bool nonlinear = s->readBool();
                 TexInfo sp = conserve(parseTexture(s, tex)), df = conserve(parseTexture(s, tex));
@@ -519,7 +529,7 @@ private:
                 n.lobes = ((m_nodes[a].lobes & ~MTS_EBACKSIDE) | MTS_EFRONTSIDE) | ((m_nodes[b].lobes & ~MTS_EFRONTSIDE) | MTS_EBACKSIDE);
             } else
                 err("BSDF class " + cls + " is out of scope (diffuse, conductor, roughconductor, plastic, roughplastic, "
-                    "dielectric, coating, blendbsdf, bumpmap, twosided, thindielectric, mask)");
+                    "dielectric, coating, blendbsdf, bumpmap, twosided, thindielectric, mask, roughdielectric)");
             m_nodes[idx] = n;
             return idx;
         }

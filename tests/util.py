@@ -202,6 +202,12 @@ def twosided_bsdfs():
     mk2.add(_tex(12, channels=3, uvscale=3.0), "opacity")
     mk2.add(Plugin("bsdf", "roughconductor", distribution="beckmann", alpha=0.2, **AU))
     z["mask_tex_rc"] = mk2
+    # roughdielectric (same row): GGX with visible-normal sampling; anisotropic Beckmann with sampleVisible=false
+    # (Walter's alpha scaling) and tinted transmission.  Uses the third random number (bRec.sampler->next1D()).
+    z["rd_ggx"] = Plugin("bsdf", "roughdielectric", distribution="ggx", alpha=0.2, intIOR=1.5)
+    z["rd_beck_all"] = Plugin("bsdf", "roughdielectric", distribution="beckmann", alphaU=0.15, alphaV=0.3, sampleVisible=False,
+                              intIOR=1.33, extIOR=1.0, specularReflectance=Spectrum(0.9),
+                              specularTransmittance=Spectrum(0.9, 0.8, 0.6))
     z["thin_tinted"] = Plugin("bsdf", "thindielectric", intIOR=1.33, extIOR=1.0, specularReflectance=Spectrum(0.8),
                               specularTransmittance=Spectrum(0.9, 0.7, 0.5))
     return z
