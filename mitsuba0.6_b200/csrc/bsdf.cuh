@@ -340,6 +340,86 @@ struct BSample { float3 wo; float pdf; float eta; uint32_t type; float u3; };   
 // RoughDielectric keeps its fourth texture (specularTransmittance) in the k/lut slots (include/mtscuda.h)
 DEVFN MtsTexRef roughDielTransmittance(const MtsBsdfNode &n) { MtsTexRef r; r.scale[0] = n.k[0]; r.scale[1] = n.k[1]; r.scale[2] = n.k[2]; r.tex = n.lut[0]; return r; }
 
+// RoughDielectric (src/bsdfs/roughdielectric.cpp) in functions of its own: the three leaf switches below stay as small
+// as they were (inlined into them the model cost every material 6 percent of shade time: registers, instruction cache)
+__device__ __noinline__ float3 roughDielEval(const DScene &S, const MtsBsdfNode &n, float2 uv, float3 wi, float3 wo) {  // :272-348
+    if (cosTheta(wi) == 0) return f3(0.0f);
+    const float eta = n.eta[0], invEta = 1 / eta;
+    const bool reflect = cosTheta(wi) * cosTheta(wo) > 0;
+    float3 H;
+    if (reflect) H = normalize(wo + wi);
+    else H = normalize(wi + wo * (cosTheta(wi) > 0 ? eta : invEta));
+    H = H * signum(cosTheta(H));
+    Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+    const float D = distr.eval(H);
+    if (D == 0) return f3(0.0f);
+    const float F = fresnelDielectricExt(dot(wi, H), eta);
+    const float G = distr.G(wi, wo, H);
+    if (reflect) return evalTex(S, n.t0, uv) * (F * D * G / (4.0f * fabsf(cosTheta(wi))));
+    const float e = cosTheta(wi) > 0.0f ? eta : invEta;
+    const float sqrtDenom = dot(wi, H) + e * dot(wo, H);
+    const float value = ((1 - F) * D * G * e * e * dot(wi, H) * dot(wo, H)) / (cosTheta(wi) * sqrtDenom * sqrtDenom);
+    const float factor = cosTheta(wi) > 0 ? invEta : eta;   // ERadiance
+    return evalTex(S, roughDielTransmittance(n), uv) * fabsf(value * factor * factor);
+}
+__device__ __noinline__ float roughDielPdf(const DScene &S, const MtsBsdfNode &n, float2 uv, float3 wi, float3 wo) {  // :350-420
+    const float eta = n.eta[0], invEta = 1 / eta;
+    const bool reflect = cosTheta(wi) * cosTheta(wo) > 0;
+    float3 H; float dwh_dwo;
+    if (reflect) {
+        H = normalize(wo + wi);
+        dwh_dwo = 1.0f / (4.0f * dot(wo, H));
+    } else {
+        const float e = cosTheta(wi) > 0 ? eta : invEta;
+        H = normalize(wi + wo * e);
+        const float sqrtDenom = dot(wi, H) + e * dot(wo, H);
+        dwh_dwo = (e * e * dot(wo, H)) / (sqrtDenom * sqrtDenom);
+    }
+    H = H * signum(cosTheta(H));
+    Microfacet sampleDistr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+    if (!sampleDistr.sampleVisible) sampleDistr.scaleAlpha(1.2f - 0.2f * sqrtf(fabsf(cosTheta(wi))));
+    float prob = sampleDistr.pdf(wi * signum(cosTheta(wi)), H);
+    const float F = fresnelDielectricExt(dot(wi, H), eta);
+    prob *= reflect ? F : (1 - F);
+    return fabsf(prob * dwh_dwo);
+}
+__device__ __noinline__ float3 roughDielSample(const DScene &S, const MtsBsdfNode &n, float2 uv, float3 wi, float2 sample, BSample &o) {  // :517-616
+    const float eta = n.eta[0], invEta = 1 / eta;
+    Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+    Microfacet sampleDistr = distr;
+    if (!distr.sampleVisible) sampleDistr.scaleAlpha(1.2f - 0.2f * sqrtf(fabsf(cosTheta(wi))));
+    float microfacetPDF;
+    const float3 m = sampleDistr.sample(wi * signum(cosTheta(wi)), sample, microfacetPDF);
+    if (microfacetPDF == 0) return f3(0.0f);
+    o.pdf = microfacetPDF;
+    float cosThetaT;
+    const float F = fresnelDielectricExt(dot(wi, m), cosThetaT, eta);
+    float3 weight = f3(1.0f);
+    bool sampleReflection = true;
+    if (o.u3 > F) { sampleReflection = false; o.pdf *= 1 - F; } else o.pdf *= F;   // bRec.sampler->next1D()
+    float dwh_dwo;
+    if (sampleReflection) {
+        o.wo = reflectM(wi, m); o.eta = 1.0f; o.type = MTS_EGLOSSY_REFLECTION;
+        if (cosTheta(wi) * cosTheta(o.wo) <= 0) return f3(0.0f);
+        weight *= evalTex(S, n.t0, uv);
+        dwh_dwo = 1.0f / (4.0f * dot(o.wo, m));
+    } else {
+        if (cosThetaT == 0) return f3(0.0f);
+        const float e = cosThetaT < 0 ? invEta : eta;   // refract(wi, m, eta, cosThetaT), util.cpp:767-772
+        o.wo = m * (dot(wi, m) * e + cosThetaT) - wi * e;
+        o.eta = cosThetaT < 0 ? eta : invEta; o.type = MTS_EGLOSSY_TRANSMISSION;
+        if (cosTheta(wi) * cosTheta(o.wo) >= 0) return f3(0.0f);
+        const float factor = cosThetaT < 0 ? invEta : eta;   // ERadiance
+        weight *= evalTex(S, roughDielTransmittance(n), uv) * (factor * factor);
+        const float sqrtDenom = dot(wi, m) + o.eta * dot(o.wo, m);
+        dwh_dwo = (o.eta * o.eta * dot(o.wo, m)) / (sqrtDenom * sqrtDenom);
+    }
+    if (distr.sampleVisible) weight *= distr.smithG1(o.wo, m);
+    else weight *= fabsf(distr.eval(m) * distr.G(wi, o.wo, m) * dot(wi, m) / (microfacetPDF * cosTheta(wi)));
+    o.pdf *= fabsf(dwh_dwo);
+    return weight;
+}
+
 // ---------------------------------------------------------------------------------------
 // leaf models
 // ---------------------------------------------------------------------------------------
@@ -418,26 +498,7 @@ __device__ __noinline__ float3 leafEval(const DScene &S, const MtsBsdfNode &n, f
             return evalTex(S, n.t1, uv) * factor * factor * (1 - F);
         }
     }
-    case MTS_BSDF_ROUGHDIELECTRIC: {  // roughdielectric.cpp:272-348
-        if (!solid || cosTheta(wi) == 0) return f3(0.0f);
-        const float eta = n.eta[0], invEta = 1 / eta;
-        const bool reflect = cosTheta(wi) * cosTheta(wo) > 0;
-        float3 H;
-        if (reflect) H = normalize(wo + wi);
-        else H = normalize(wi + wo * (cosTheta(wi) > 0 ? eta : invEta));
-        H = H * signum(cosTheta(H));
-        Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
-        const float D = distr.eval(H);
-        if (D == 0) return f3(0.0f);
-        const float F = fresnelDielectricExt(dot(wi, H), eta);
-        const float G = distr.G(wi, wo, H);
-        if (reflect) return evalTex(S, n.t0, uv) * (F * D * G / (4.0f * fabsf(cosTheta(wi))));
-        const float e = cosTheta(wi) > 0.0f ? eta : invEta;
-        const float sqrtDenom = dot(wi, H) + e * dot(wo, H);
-        const float value = ((1 - F) * D * G * e * e * dot(wi, H) * dot(wo, H)) / (cosTheta(wi) * sqrtDenom * sqrtDenom);
-        const float factor = cosTheta(wi) > 0 ? invEta : eta;   // ERadiance
-        return evalTex(S, roughDielTransmittance(n), uv) * fabsf(value * factor * factor);
-    }
+    case MTS_BSDF_ROUGHDIELECTRIC: return solid ? roughDielEval(S, n, uv, wi, wo) : f3(0.0f);
     case MTS_BSDF_THINDIELECTRIC: {  // thindielectric.cpp:145-166
         float R = fresnelDielectricExt(fabsf(cosTheta(wi)), n.eta[0]), T = 1 - R;
         if (R < 1) R += T * T * R / (1 - R * R);   // internal reflections: R' = R + TRT + TR^3T + ..
@@ -508,28 +569,7 @@ __device__ __noinline__ float leafPdf(const DScene &S, const MtsBsdfNode &n, flo
             return 1 - F;
         }
     }
-    case MTS_BSDF_ROUGHDIELECTRIC: {  // roughdielectric.cpp:350-420
-        if (!solid) return 0.0f;
-        const float eta = n.eta[0], invEta = 1 / eta;
-        const bool reflect = cosTheta(wi) * cosTheta(wo) > 0;
-        float3 H; float dwh_dwo;
-        if (reflect) {
-            H = normalize(wo + wi);
-            dwh_dwo = 1.0f / (4.0f * dot(wo, H));
-        } else {
-            const float e = cosTheta(wi) > 0 ? eta : invEta;
-            H = normalize(wi + wo * e);
-            const float sqrtDenom = dot(wi, H) + e * dot(wo, H);
-            dwh_dwo = (e * e * dot(wo, H)) / (sqrtDenom * sqrtDenom);
-        }
-        H = H * signum(cosTheta(H));
-        Microfacet sampleDistr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
-        if (!sampleDistr.sampleVisible) sampleDistr.scaleAlpha(1.2f - 0.2f * sqrtf(fabsf(cosTheta(wi))));
-        float prob = sampleDistr.pdf(wi * signum(cosTheta(wi)), H);
-        const float F = fresnelDielectricExt(dot(wi, H), eta);
-        prob *= reflect ? F : (1 - F);
-        return fabsf(prob * dwh_dwo);
-    }
+    case MTS_BSDF_ROUGHDIELECTRIC: return solid ? roughDielPdf(S, n, uv, wi, wo) : 0.0f;
     case MTS_BSDF_THINDIELECTRIC: {  // thindielectric.cpp:168-189
         float R = fresnelDielectricExt(fabsf(cosTheta(wi)), n.eta[0]), T = 1 - R;
         if (R < 1) R += T * T * R / (1 - R * R);
@@ -633,42 +673,7 @@ __device__ __noinline__ float3 leafSample(const DScene &S, const MtsBsdfNode &n,
         float factor = cosThetaT < 0 ? invEta : eta;
         return evalTex(S, n.t1, uv) * (factor * factor);
     }
-    case MTS_BSDF_ROUGHDIELECTRIC: {  // roughdielectric.cpp:517-616 (pdf-returning overload)
-        const float eta = n.eta[0], invEta = 1 / eta;
-        Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
-        Microfacet sampleDistr = distr;
-        if (!distr.sampleVisible) sampleDistr.scaleAlpha(1.2f - 0.2f * sqrtf(fabsf(cosTheta(wi))));
-        float microfacetPDF;
-        const float3 m = sampleDistr.sample(wi * signum(cosTheta(wi)), sample, microfacetPDF);
-        if (microfacetPDF == 0) return f3(0.0f);
-        o.pdf = microfacetPDF;
-        float cosThetaT;
-        const float F = fresnelDielectricExt(dot(wi, m), cosThetaT, eta);
-        float3 weight = f3(1.0f);
-        bool sampleReflection = true;
-        if (o.u3 > F) { sampleReflection = false; o.pdf *= 1 - F; } else o.pdf *= F;   // bRec.sampler->next1D()
-        float dwh_dwo;
-        if (sampleReflection) {
-            o.wo = reflectM(wi, m); o.eta = 1.0f; o.type = MTS_EGLOSSY_REFLECTION;
-            if (cosTheta(wi) * cosTheta(o.wo) <= 0) return f3(0.0f);
-            weight *= evalTex(S, n.t0, uv);
-            dwh_dwo = 1.0f / (4.0f * dot(o.wo, m));
-        } else {
-            if (cosThetaT == 0) return f3(0.0f);
-            const float e = cosThetaT < 0 ? invEta : eta;   // refract(wi, m, eta, cosThetaT), util.cpp:767-772
-            o.wo = m * (dot(wi, m) * e + cosThetaT) - wi * e;
-            o.eta = cosThetaT < 0 ? eta : invEta; o.type = MTS_EGLOSSY_TRANSMISSION;
-            if (cosTheta(wi) * cosTheta(o.wo) >= 0) return f3(0.0f);
-            const float factor = cosThetaT < 0 ? invEta : eta;   // ERadiance
-            weight *= evalTex(S, roughDielTransmittance(n), uv) * (factor * factor);
-            const float sqrtDenom = dot(wi, m) + o.eta * dot(o.wo, m);
-            dwh_dwo = (o.eta * o.eta * dot(o.wo, m)) / (sqrtDenom * sqrtDenom);
-        }
-        if (distr.sampleVisible) weight *= distr.smithG1(o.wo, m);
-        else weight *= fabsf(distr.eval(m) * distr.G(wi, o.wo, m) * dot(wi, m) / (microfacetPDF * cosTheta(wi)));
-        o.pdf *= fabsf(dwh_dwo);
-        return weight;
-    }
+    case MTS_BSDF_ROUGHDIELECTRIC: return roughDielSample(S, n, uv, wi, sample, o);
     case MTS_BSDF_THINDIELECTRIC: {  // thindielectric.cpp:191-221 (the pdf-returning overload path.cpp:209 calls)
         float R = fresnelDielectricExt(fabsf(cosTheta(wi)), n.eta[0]), T = 1 - R;
         if (R < 1) R += T * T * R / (1 - R * R);
