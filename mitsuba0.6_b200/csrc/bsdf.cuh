@@ -765,16 +765,16 @@ template <int D> struct Bsdf {
             if (cosTheta(wo) * cosTheta(woP) <= 0) return f3(0.0f);
             return Next::eval(S, n.child[0], pert, wiP, woP, measure);
         }
-        case MTS_BSDF_MASK: {  // mask.cpp:106-116
-            float3 opacity = evalTex(S, n.t0, su.uv);
-            if (measure == MTS_MEASURE_SOLID_ANGLE) return Next::eval(S, n.child[0], su, wi, wo, measure) * opacity;
-            if (measure == MTS_MEASURE_DISCRETE && fabsf(1 - dot(wi, -wo)) < kDeltaEps) return f3(1.0f) - opacity;
-            return f3(0.0f);
-        }
-        case MTS_BSDF_TWOSIDED: {  // twosided.cpp:107-119
-            if (cosTheta(wi) > 0) return Next::eval(S, n.child[0], su, wi, wo, measure);
-            wi.z = -wi.z; wo.z = -wo.z;
-            return Next::eval(S, n.child[1], su, wi, wo, measure);
+        case MTS_BSDF_MASK:        // mask.cpp:106-116
+        case MTS_BSDF_TWOSIDED: {  // twosided.cpp:107-119 -- one nested call site for both adapters
+            int child = n.child[0];
+            float3 scale = f3(1.0f);
+            if (n.type == MTS_BSDF_MASK) {
+                scale = evalTex(S, n.t0, su.uv);
+                if (measure != MTS_MEASURE_SOLID_ANGLE)
+                    return (measure == MTS_MEASURE_DISCRETE && fabsf(1 - dot(wi, -wo)) < kDeltaEps) ? f3(1.0f) - scale : f3(0.0f);
+            } else if (!(cosTheta(wi) > 0)) { wi.z = -wi.z; wo.z = -wo.z; child = n.child[1]; }
+            return Next::eval(S, child, su, wi, wo, measure) * scale;
         }
         default: return leafEval(S, n, su.uv, wi, wo, measure);
         }
@@ -809,16 +809,16 @@ template <int D> struct Bsdf {
             if (cosTheta(wo) * cosTheta(woP) <= 0) return 0;
             return Next::pdf(S, n.child[0], pert, wiP, woP, measure);
         }
-        case MTS_BSDF_MASK: {  // mask.cpp:118-143
-            float prob = luminance(evalTex(S, n.t0, su.uv));
-            if (measure == MTS_MEASURE_SOLID_ANGLE) return Next::pdf(S, n.child[0], su, wi, wo, measure) * prob;
-            if (measure == MTS_MEASURE_DISCRETE && fabsf(1 - dot(wi, -wo)) < kDeltaEps) return 1 - prob;
-            return 0.0f;
-        }
+        case MTS_BSDF_MASK:        // mask.cpp:118-143
         case MTS_BSDF_TWOSIDED: {  // twosided.cpp:121-133
-            if (wi.z > 0) return Next::pdf(S, n.child[0], su, wi, wo, measure);
-            wi.z = -wi.z; wo.z = -wo.z;
-            return Next::pdf(S, n.child[1], su, wi, wo, measure);
+            int child = n.child[0];
+            float prob = 1.0f;
+            if (n.type == MTS_BSDF_MASK) {
+                prob = luminance(evalTex(S, n.t0, su.uv));
+                if (measure != MTS_MEASURE_SOLID_ANGLE)
+                    return (measure == MTS_MEASURE_DISCRETE && fabsf(1 - dot(wi, -wo)) < kDeltaEps) ? 1 - prob : 0.0f;
+            } else if (!(wi.z > 0)) { wi.z = -wi.z; wo.z = -wo.z; child = n.child[1]; }
+            return Next::pdf(S, child, su, wi, wo, measure) * prob;
         }
         default: return leafPdf(S, n, su.uv, wi, wo, measure);
         }
@@ -883,23 +883,25 @@ template <int D> struct Bsdf {
             }
             return result;
         }
-        case MTS_BSDF_MASK: {  // mask.cpp:187-226 (pdf-returning overload)
-            float3 opacity = evalTex(S, n.t0, su.uv);
-            float prob = luminance(opacity);
-            if (sample.x < prob) {
-                sample.x /= prob;
-                float3 result = Next::sample(S, n.child[0], su, wi, sample, o) * opacity / prob;
-                o.pdf *= prob;
-                return result;
-            }
-            o.wo = -wi; o.eta = 1.0f; o.type = MTS_ENULL; o.pdf = 1 - prob;
-            return (f3(1.0f) - opacity) / o.pdf;
-        }
+        case MTS_BSDF_MASK:        // mask.cpp:187-226 (pdf-returning overload)
         case MTS_BSDF_TWOSIDED: {  // twosided.cpp:158-180
-            bool flipped = cosTheta(wi) < 0;
-            if (flipped) wi.z = -wi.z;
-            float3 result = Next::sample(S, n.child[flipped ? 1 : 0], su, wi, sample, o);
-            if (flipped && !isZero(result) && o.pdf != 0) o.wo.z = -o.wo.z;
+            const bool mask = n.type == MTS_BSDF_MASK;
+            int child = n.child[0];
+            float3 opacity = f3(1.0f);
+            float prob = 1.0f;
+            bool flipped = false;
+            if (mask) {
+                opacity = evalTex(S, n.t0, su.uv);
+                prob = luminance(opacity);
+                if (!(sample.x < prob)) {
+                    o.wo = -wi; o.eta = 1.0f; o.type = MTS_ENULL; o.pdf = 1 - prob;
+                    return (f3(1.0f) - opacity) / o.pdf;
+                }
+                sample.x /= prob;
+            } else if (cosTheta(wi) < 0) { flipped = true; wi.z = -wi.z; child = n.child[1]; }
+            float3 result = Next::sample(S, child, su, wi, sample, o);
+            if (mask) { result = result * opacity / prob; o.pdf *= prob; }
+            else if (flipped && !isZero(result) && o.pdf != 0) o.wo.z = -o.wo.z;
             return result;
         }
         default: return leafSample(S, n, su.uv, wi, sample, o);

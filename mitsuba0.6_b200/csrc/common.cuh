@@ -293,6 +293,14 @@ DEVFN float4 rand4(uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t bloc
     return make_float4(u01(r.x), u01(r.y), u01(r.z), u01(r.w));
 }
 
+// Same draw plus a fifth uniform assembled from the low 8 bits of the four Philox words, which u01() discards
+// (24 independent bits): the extra number of EUsesSampler BSDFs (roughdielectric.cpp:405) costs nothing.
+DEVFN float4 rand4x(uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t block, float &extra) {
+    uint4 r = philox4x32(make_uint4(pixel, sample, block, 0x6d747363u), make_uint2(seed, 0x63756461u));
+    extra = (float)((r.x & 0xffu) | ((r.y & 0xffu) << 8) | ((r.z & 0xffu) << 16)) * (1.0f / 16777216.0f);
+    return make_float4(u01(r.x), u01(r.y), u01(r.z), u01(r.w));
+}
+
 // power heuristic, src/integrators/path/path.cpp:296-300
 DEVFN float miWeight(float pdfA, float pdfB) { pdfA *= pdfA; pdfB *= pdfB; return pdfA / (pdfA + pdfB); }
 

@@ -64,8 +64,6 @@ DEVFN uint32_t warpAppend(uint32_t *counter, bool pred) {
     return base + __popc(mask & ((1u << lane) - 1));
 }
 
-__device__ __noinline__ float extraRandom(uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t block) { return rand4(seed, pixel, sample, block).x; }
-
 DEVFN Surf surfOf(const Hit &h) {
     Surf s; s.uv = h.uv; s.dpdu = h.dpdu; s.dpdv = h.dpdv; s.geoN = h.geoN; s.sh = h.sh; s.bumpNode = -1; return s;
 }
@@ -293,7 +291,8 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
     const int bsdf = shape.bsdf;
     const uint32_t lobes = S.nodes[bsdf].lobes;
     const Surf su = surfOf(its);
-    float4 u = rand4(R.seed, meta.x, meta.y, 2 * depth - 1);
+    float uExtra;
+    float4 u = rand4x(R.seed, meta.x, meta.y, 2 * depth - 1, uExtra);
 
     // ---- direct illumination sampling (path.cpp:172-200) ----
     float3 refN = ((lobes & (MTS_ETRANSMISSION | MTS_EBACKSIDE)) == 0) ? its.sh.n : f3(0.0f);  // records.inl:160-164
@@ -319,9 +318,8 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
     }
 
     // ---- BSDF sampling (path.cpp:203-253) ----
-    BSample bs; bs.pdf = 0; bs.eta = 1; bs.type = 0; bs.wo = f3(0.0f); bs.u3 = 0;
-    // EUsesSampler models (roughdielectric.cpp:405 bRec.sampler->next1D()) draw from their own dimension
-    if (lobes & MTS_EGLOSSY_TRANSMISSION) bs.u3 = extraRandom(R.seed, meta.x, meta.y, 0x4000u + depth);
+    BSample bs; bs.pdf = 0; bs.eta = 1; bs.type = 0; bs.wo = f3(0.0f);
+    bs.u3 = uExtra;   // EUsesSampler models (roughdielectric.cpp:405 bRec.sampler->next1D()): spare bits of the same Philox draw
     float3 bsdfWeight = BsdfRoot::sample(S, bsdf, su, its.wi, make_float2(u.z, u.w), bs);
     if (isZero(bsdfWeight)) { finish(); return; }
     if (bs.type != MTS_ENULL) flags |= PF_SCATTERED;   // path.cpp:213
