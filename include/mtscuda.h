@@ -179,6 +179,9 @@ typedef struct MtsFilm {
     int32_t width, height;                         /* crop size in pixels */
     float filter_radius;
     float filter_table[MTS_FILTER_RESOLUTION + 1]; /* normalised m_values[], last entry 0 */
+    int32_t has_alpha;                             /* Film::hasAlpha(): also accumulate w * alpha, alpha = 1 where the camera ray
+                                                      hit a surface, else 0 (RadianceQueryRecord::rayIntersect with EOpacity,
+                                                      include/mitsuba/render/records.inl:121-137; integrator.cpp:157-160) */
 } MtsFilm;
 
 /* ---- shapes ---------------------------------------------------------------- */
@@ -239,6 +242,11 @@ typedef struct MtsStats {
     float intersect_ms, shade_ms, shadow_ms, splat_ms, raygen_ms;
     float build_ms;              /* BVH build time of the last build() */
     float upload_ms;
+    /* shade stage split (CUDA events around each kernel): shade_ms = k_shade* only (surface hits), miss_ms = k_shade_miss
+     * (escaped rays), sort_ms = the material counting sort; and the units they processed */
+    float sort_ms, miss_ms;
+    uint64_t shaded_paths;       /* surface hits shaded, summed over bounces (= normal_rays - miss_paths) */
+    uint64_t miss_paths;         /* rays that escaped the scene, summed over bounces */
 } MtsStats;
 
 typedef struct MtsContext MtsContext;
@@ -273,6 +281,9 @@ MTS_API int MTS_FN(render)(MtsContext *ctx, const MtsRenderParams *params, volat
 /* film as width*height*4 floats (sum w*R, sum w*G, sum w*B, sum w); develop divides by the weight
  * (src/libcore/fmtconv.cpp:955-975). */
 MTS_API int MTS_FN(read_film)(MtsContext *ctx, float *out_rgbw);
+/* The alpha plane (width*height floats, sum w*alpha) of a film created with has_alpha = 1: the fourth channel of
+ * the ESpectrumAlphaWeight block the plugin hands to Film::put (src/films/hdrfilm.cpp:391-393). */
+MTS_API int MTS_FN(read_film_alpha)(MtsContext *ctx, float *out_alpha);
 /* Use caller-provided device memory (width*height float4) as the film accumulator, e.g. a torch
  * tensor that is then reduced with NCCL; NULL restores the internal buffer.  CUDA library only. */
 MTS_API int MTS_FN(bind_film)(MtsContext *ctx, void *device_ptr);

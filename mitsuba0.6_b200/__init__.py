@@ -38,19 +38,18 @@ def rel_mse(img, ref, eps=1e-2, trim=0.001):
 
 class CudaPath:
     """Integrator-plugin mirror: CudaPath(scene).render() == `mitsuba scene.xml` with
-    <integrator type="cudapath">.
+    <integrator type="cudapath">.  Runs on libmtscuda (sm_100a) only; there is no CPU path.
 
-    backend="cuda" is the product.  backend="oracle" runs the CPU restatement and exists for
-    tests / the CPU baseline only; nothing falls back from one to the other.
+    `lib` lets the test infrastructure drive another library that exports the same C ABI (the CPU oracle,
+    oracle/oracle_lib.py) through these wrappers; the package itself never passes it.
     """
 
-    def __init__(self, scene, backend="cuda", device=0):
+    def __init__(self, scene, device=0, lib=None):
         if isinstance(scene, str):
             scene = load_xml(scene)
         self.scene = scene
         self.flat = scene if isinstance(scene, _scene.FlatScene) else flatten(scene)
-        self.backend = backend
-        self.ctx = Context(backend, device)
+        self.ctx = Context(device, lib)
         self._cancel = _C.c_int(0)
         self.preprocessed = False
         self.stats = None

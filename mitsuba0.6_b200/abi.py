@@ -1,13 +1,9 @@
 """ctypes binding of the C ABI declared in include/mtscuda.h.
 
-Two libraries export that surface:
-
-* ``libmtscuda.so``  (prefix ``mtscuda_``)  -- the product: hand-written sm_100a kernels.
-* ``libmtsoracle.so`` (prefix ``mtsoracle_``) -- the CPU restatement of the reference
-  (test infrastructure; only tests/, smoke() and bench.py's cpu_baseline may load it).
-
-There is no fallback between the two: asking for the CUDA library when it has not been
-built (or when no GPU is present at call time) raises.
+The package binds exactly one library: ``csrc/libmtscuda.so`` (prefix ``mtscuda_``), the hand-written sm_100a
+kernels.  There is no CPU path and no fallback: when the library has not been built, or no GPU is present at call
+time, the call raises.  ``bind()`` types the entry points of *a* library exporting the header's surface under a given
+prefix; the test infrastructure (oracle/oracle_lib.py) uses it to put the CPU restatement behind the same wrappers.
 """
 import ctypes as C
 import os
@@ -62,7 +58,7 @@ class Camera(C.Structure):
 
 class Film(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("filter_radius", C.c_float),
-                ("filter_table", C.c_float * (FILTER_RESOLUTION + 1))]
+                ("filter_table", C.c_float * (FILTER_RESOLUTION + 1)), ("has_alpha", C.c_int32)]
 
 
 class MeshDesc(C.Structure):
@@ -94,7 +90,9 @@ class Stats(C.Structure):
                 ("shadow_launches", C.c_uint64), ("splat_launches", C.c_uint64),
                 ("render_ms", C.c_float), ("intersect_ms", C.c_float), ("shade_ms", C.c_float),
                 ("shadow_ms", C.c_float), ("splat_ms", C.c_float), ("raygen_ms", C.c_float),
-                ("build_ms", C.c_float), ("upload_ms", C.c_float)]
+                ("build_ms", C.c_float), ("upload_ms", C.c_float),
+                ("sort_ms", C.c_float), ("miss_ms", C.c_float),
+                ("shaded_paths", C.c_uint64), ("miss_paths", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -104,16 +102,13 @@ class Stats(C.Structure):
 ABI_SYMBOLS = [
     "last_error", "create", "destroy", "set_camera", "set_film", "add_texture", "set_float_pool",
     "set_bsdfs", "add_mesh", "add_rectangle", "add_sphere", "add_emitter", "build", "render",
-    "read_film", "bind_film", "set_stream", "get_stats", "sample_rays", "trace", "hit_records", "bsdf_eval_pdf",
+    "read_film", "read_film_alpha", "bind_film", "set_stream", "get_stats", "sample_rays", "trace", "hit_records", "bsdf_eval_pdf",
     "bsdf_sample", "sample_emitter_direct", "eval_environment", "splat",
 ]
 
-LIB_PATHS = {
-    # MTS_CUDA_LIB selects an experimental build of the same library (kernel tuning sweeps); never a different back end
-    "cuda": os.environ.get("MTS_CUDA_LIB") or os.path.join(_HERE, "csrc", "libmtscuda.so"),
-    "oracle": os.path.join(_ROOT, "oracle", "libmtsoracle.so"),
-}
-PREFIX = {"cuda": "mtscuda_", "oracle": "mtsoracle_"}
+# MTS_CUDA_LIB selects an experimental build of the same library (kernel tuning sweeps); never a different back end
+CUDA_LIB_PATH = os.environ.get("MTS_CUDA_LIB") or os.path.join(_HERE, "csrc", "libmtscuda.so")
+CUDA_PREFIX = "mtscuda_"
 
 
 class MtsError(RuntimeError):
@@ -124,16 +119,14 @@ class MtsError(RuntimeError):
 _libs = {}
 
 
-def load(backend):
-    """dlopen one of the two libraries and type its entry points.  Fails loudly."""
-    if backend in _libs:
-        return _libs[backend]
-    path = LIB_PATHS[backend]
+def bind(path, prefix):
+    """dlopen a library that exports the surface of include/mtscuda.h under `prefix` and type its entry points."""
+    key = (path, prefix)
+    if key in _libs:
+        return _libs[key]
     if not os.path.exists(path):
-        raise MtsError("%s is not built (%s missing): run `python -c 'import __graft_entry__ as g; g.build()'`"
-                       % ("libmtscuda" if backend == "cuda" else "libmtsoracle", path))
+        raise MtsError("%s is not built: run `python -c 'import __graft_entry__ as g; g.build()'`" % path)
     lib = C.CDLL(path)
-    p = PREFIX[backend]
     fn = {}
     vp, i32, i64, fp = C.c_void_p, C.c_int32, C.c_int64, C.c_void_p
     sigs = {
@@ -152,6 +145,7 @@ def load(backend):
         "build": (C.c_int, [vp]),
         "render": (C.c_int, [vp, C.POINTER(RenderParams), C.POINTER(C.c_int), C.POINTER(Stats)]),
         "read_film": (C.c_int, [vp, fp]),
+        "read_film_alpha": (C.c_int, [vp, fp]),
         "bind_film": (C.c_int, [vp, vp]),
         "set_stream": (C.c_int, [vp, vp]),
         "get_stats": (C.c_int, [vp, C.POINTER(Stats)]),
@@ -165,13 +159,18 @@ def load(backend):
         "splat": (C.c_int, [vp, i64, fp, fp, i32]),
     }
     for name in ABI_SYMBOLS:
-        f = getattr(lib, p + name)  # AttributeError if a declared symbol is not exported
+        f = getattr(lib, prefix + name)  # AttributeError if a declared symbol is not exported
         f.restype, f.argtypes = sigs[name]
         fn[name] = f
     lib._fn = fn
-    lib._backend = backend
-    _libs[backend] = lib
+    lib._device_tangents = prefix == CUDA_PREFIX   # libmtscuda runs TriMesh::computeUVTangents on the device
+    _libs[key] = lib
     return lib
+
+
+def load():
+    """The product library.  Fails loudly when it is missing."""
+    return bind(CUDA_LIB_PATH, CUDA_PREFIX)
 
 
 def f32(a, shape=None):
@@ -188,9 +187,8 @@ def ptr(a):
 class Context:
     """Owns one MtsContext handle; thin, typed wrappers over the C entry points."""
 
-    def __init__(self, backend="cuda", device=0):
-        self.lib = load(backend)
-        self.backend = backend
+    def __init__(self, device=0, lib=None):
+        self.lib = lib if lib is not None else load()
         self.fn = self.lib._fn
         h = C.c_void_p()
         self._check(self.fn["create"](device, C.byref(h)))
@@ -235,14 +233,14 @@ class Context:
 
     def add_mesh(self, positions, indices, normals=None, texcoords=None, tangents=None, bsdf=0, uv_tangents=False):
         """uv_tangents=True asks for TriMesh::computeUVTangents: on the device for libmtscuda (flag in the descriptor),
-        on the host (hostmath.uv_tangents, the numpy mirror) for the oracle, which takes explicit tangents only."""
+        on the host (hostmath.uv_tangents, the numpy mirror) for a library that takes explicit tangents only."""
         pos = f32(positions, (-1, 3))
         idx = np.ascontiguousarray(indices, dtype=np.uint32).reshape(-1, 3)
         nrm = None if normals is None else f32(normals, (-1, 3))
         uv = None if texcoords is None else f32(texcoords, (-1, 2))
         flag = 0
         if uv_tangents and uv is not None and tangents is None:
-            if self.lib._backend == "cuda":
+            if self.lib._device_tangents:
                 flag = 1
             else:
                 from . import hostmath
@@ -278,6 +276,12 @@ class Context:
         w, h = self.film_size
         out = np.empty((h, w, 4), dtype=np.float32)
         self._check(self.fn["read_film"](self.h, ptr(out)))
+        return out
+
+    def read_film_alpha(self):
+        w, h = self.film_size
+        out = np.empty((h, w), dtype=np.float32)
+        self._check(self.fn["read_film_alpha"](self.h, ptr(out)))
         return out
 
     def bind_film(self, device_ptr):

@@ -14,6 +14,7 @@
 #include <cub/device/device_scan.cuh>
 #include <vector>
 #include "bvh_build.h"
+#include "devmem.h"
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
@@ -594,17 +595,17 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
     auto lap = [&](const char *what) { if (!trace) return; auto t1 = now(); fprintf(stderr, "[bvh] %-10s %.2f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count()); t0 = t1; };
     {
     const size_t maxNodes = 2 * (size_t)n + 2;
-    CK(cudaMalloc(&pLo, sizeof(float4) * n)); CK(cudaMalloc(&pHi, sizeof(float4) * n));
-    CK(cudaMalloc(&idxA, 4 * (size_t)n)); CK(cudaMalloc(&idxB, 4 * (size_t)n));
-    CK(cudaMalloc(&nodeA, 4 * (size_t)n)); CK(cudaMalloc(&nodeB, 4 * (size_t)n));
-    CK(cudaMalloc(&nodes, sizeof(BuildNode) * maxNodes));
-    CK(cudaMalloc(&flags, 4 * maxNodes)); CK(cudaMalloc(&scan, 4 * maxNodes));
-    CK(cudaMalloc(&box, 4 * 12)); CK(cudaMalloc(&nodeCount, 4));
-    CK(cudaMalloc(&src, sizeof(PrimSource) * n));
-    CK(cudaMalloc(&smallList, 4 * ((size_t)n / 2 + 1))); CK(cudaMalloc(&smallCount, 4));
+    CK(devAlloc(&pLo, sizeof(float4) * n, st)); CK(devAlloc(&pHi, sizeof(float4) * n, st));
+    CK(devAlloc(&idxA, 4 * (size_t)n, st)); CK(devAlloc(&idxB, 4 * (size_t)n, st));
+    CK(devAlloc(&nodeA, 4 * (size_t)n, st)); CK(devAlloc(&nodeB, 4 * (size_t)n, st));
+    CK(devAlloc(&nodes, sizeof(BuildNode) * maxNodes, st));
+    CK(devAlloc(&flags, 4 * maxNodes, st)); CK(devAlloc(&scan, 4 * maxNodes, st));
+    CK(devAlloc(&box, 4 * 12, st)); CK(devAlloc(&nodeCount, 4, st));
+    CK(devAlloc(&src, sizeof(PrimSource) * n, st));
+    CK(devAlloc(&smallList, 4 * ((size_t)n / 2 + 1), st)); CK(devAlloc(&smallCount, 4, st));
     CK(cudaMemsetAsync(smallCount, 0, 4, st));
     CK(cub::DeviceScan::ExclusiveSum(nullptr, cubBytes, flags, scan, (int)maxNodes, st));
-    CK(cudaMalloc(&cubTmp, cubBytes));
+    CK(devAlloc(&cubTmp, cubBytes, st));
 
     lap("alloc");
     // primitive sources + bounds
@@ -640,9 +641,9 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
     while (levelStart < levelEnd) {
         size_t nb = (size_t)(levelEnd - levelStart) * 3 * NB;
         if (nb > binCap) {
-            if (bins) CK(cudaFree(bins));
+            devFree(bins, st);
             binCap = nb + nb / 2;
-            CK(cudaMalloc(&bins, sizeof(Bin) * binCap));
+            CK(devAlloc(&bins, sizeof(Bin) * binCap, st));
         }
         k_clear_bins<<<blocks(nb), 256, 0, st>>>(bins, nb);
         k_bin<<<blocks(n, kBinChunk), 256, 0, st>>>(n, idxA, nodeA, pLo, pHi, nodes, levelStart, bins);
@@ -676,10 +677,10 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
     // collapse into eight-wide nodes, level by level (the wide tree of 10M triangles is ~10 levels deep)
     {
         const size_t maxWide = (size_t)nBuild / 2 + 2;   // every wide node consumes at least one binary inner node
-        CK(cudaMalloc(&wide, sizeof(WideNode) * maxWide));
-        CK(cudaMalloc(&srcNode, 4 * maxWide));
-        CK(cudaMalloc(&primCounter, 4));
-        CK(cudaMalloc(&out.prims, sizeof(PrimRecord) * n));
+        CK(devAlloc(&wide, sizeof(WideNode) * maxWide, st));
+        CK(devAlloc(&srcNode, 4 * maxWide, st));
+        CK(devAlloc(&primCounter, 4, st));
+        CK(devAlloc(&out.prims, sizeof(PrimRecord) * n, st));
         int zero = 0, one = 1;
         CK(cudaMemcpyAsync(srcNode, &zero, 4, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(primCounter, &zero, 4, cudaMemcpyHostToDevice, st));
@@ -694,9 +695,10 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
             CK(cudaStreamSynchronize(st));
             if ((size_t)cnt > maxWide) { err = "BVH collapse: node overflow"; goto fail; }
             ws = we; we = cnt;
+            ++out.depth;
         }
         out.numNodes = we;
-        CK(cudaMalloc(&out.nodes, sizeof(WideNode) * (size_t)we));
+        CK(devAlloc(&out.nodes, sizeof(WideNode) * (size_t)we, st));
         CK(cudaMemcpyAsync(out.nodes, wide, sizeof(WideNode) * (size_t)we, cudaMemcpyDeviceToDevice, st));
         CK(cudaStreamSynchronize(st));
     }
@@ -709,15 +711,15 @@ bool buildBvh(const BvhBuildInput &in, BvhBuildOutput &out, cudaStream_t st, std
     out.buildNodes = nBuild;
     lap("collapse");
     }
-    cudaFree(pLo); cudaFree(pHi); cudaFree(idxA); cudaFree(idxB); cudaFree(nodeA); cudaFree(nodeB); cudaFree(nodes);
-    cudaFree(flags); cudaFree(scan); cudaFree(box); cudaFree(nodeCount); cudaFree(bins); cudaFree(cubTmp); cudaFree(src); cudaFree(wide); cudaFree(srcNode); cudaFree(primCounter); cudaFree(smallList); cudaFree(smallCount);
+    devFree(pLo, st); devFree(pHi, st); devFree(idxA, st); devFree(idxB, st); devFree(nodeA, st); devFree(nodeB, st); devFree(nodes, st);
+    devFree(flags, st); devFree(scan, st); devFree(box, st); devFree(nodeCount, st); devFree(bins, st); devFree(cubTmp, st); devFree(src, st); devFree(wide, st); devFree(srcNode, st); devFree(primCounter, st); devFree(smallList, st); devFree(smallCount, st);
     lap("free");
     return true;
 fail:
-    cudaFree(pLo); cudaFree(pHi); cudaFree(idxA); cudaFree(idxB); cudaFree(nodeA); cudaFree(nodeB); cudaFree(nodes);
-    cudaFree(flags); cudaFree(scan); cudaFree(box); cudaFree(nodeCount); cudaFree(bins); cudaFree(cubTmp); cudaFree(src); cudaFree(wide); cudaFree(srcNode); cudaFree(primCounter); cudaFree(smallList); cudaFree(smallCount);
-    if (out.nodes) cudaFree(out.nodes);
-    if (out.prims) cudaFree(out.prims);
+    devFree(pLo, st); devFree(pHi, st); devFree(idxA, st); devFree(idxB, st); devFree(nodeA, st); devFree(nodeB, st); devFree(nodes, st);
+    devFree(flags, st); devFree(scan, st); devFree(box, st); devFree(nodeCount, st); devFree(bins, st); devFree(cubTmp, st); devFree(src, st); devFree(wide, st); devFree(srcNode, st); devFree(primCounter, st); devFree(smallList, st); devFree(smallCount, st);
+    if (out.nodes) devFree(out.nodes, st);
+    if (out.prims) devFree(out.prims, st);
     out = BvhBuildOutput();
     return false;
 }

@@ -20,11 +20,12 @@ struct BvhBuildInput {
 };
 
 struct BvhBuildOutput {
-    WideNode *nodes = nullptr;    // device; caller frees with cudaFree
+    WideNode *nodes = nullptr;    // device (cudaMallocAsync on `stream`); caller frees with cudaFreeAsync
     PrimRecord *prims = nullptr;  // device, in wide-node leaf order
     int numNodes = 0;
     int buildNodes = 0;
     int launches = 0;
+    int depth = 0;                // levels of the wide tree = upper bound of the traversal stack depth
     float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
 };
 

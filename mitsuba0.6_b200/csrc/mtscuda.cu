@@ -7,6 +7,7 @@
 #include <string>
 #include <vector>
 #include "bvh_build.h"
+#include "devmem.h"
 #include "wavefront.cuh"
 
 using namespace mts;
@@ -14,6 +15,7 @@ using namespace mts;
 namespace {
 
 thread_local std::string g_err;
+constexpr int kPollRing = 8;   // bounces in flight between a queue-size copy and the host looking at it
 int fail(int code, const std::string &msg) { g_err = msg; return code; }
 
 #define CUDA_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) \
@@ -36,11 +38,10 @@ template <class T> struct DevVec {
         if (n <= cap) return cudaSuccess;
         size_t ncap = std::max(n, cap + cap / 2);
         T *nd = nullptr;
-        cudaError_t e = cudaMalloc(&nd, sizeof(T) * ncap);
+        cudaError_t e = devAlloc(&nd, sizeof(T) * ncap, st);
         if (e != cudaSuccess) return e;
         if (size) e = cudaMemcpyAsync(nd, data, sizeof(T) * size, cudaMemcpyDeviceToDevice, st);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-        if (data) cudaFree(data);
+        devFree(data, st);   // stream-ordered: released after the copy above
         data = nd; cap = ncap;
         return e;
     }
@@ -53,7 +54,7 @@ template <class T> struct DevVec {
         size += n;
         return e;
     }
-    void release() { if (data) cudaFree(data); data = nullptr; size = cap = 0; }
+    void release(cudaStream_t st) { devFree(data, st); data = nullptr; size = cap = 0; }
 };
 
 struct HostEmitter {
@@ -122,21 +123,25 @@ struct MtsContext {
     std::vector<void *> sceneAllocs;
     bool built = false;
     float4 *filmInternal = nullptr, *filmBound = nullptr;
+    float *filmAlpha = nullptr;                               // sum w * alpha (films with an alpha channel only)
+    uint32_t *hostPoll = nullptr;                             // pinned: next-queue sizes polled without blocking
+    std::vector<cudaEvent_t> eventPool; size_t eventsUsed = 0;
+    int bvhDepth = 0;
     // wavefront
     Wavefront wf; std::vector<void *> wfAllocs; uint32_t wfCapacity = 0;
     MtsStats stats;
 
     MtsContext() { std::memset(&ds, 0, sizeof(ds)); std::memset(&wf, 0, sizeof(wf)); std::memset(&stats, 0, sizeof(stats)); }
-    void freeScene() { for (void *p : sceneAllocs) cudaFree(p); sceneAllocs.clear(); built = false; }
+    void freeScene() { for (void *p : sceneAllocs) devFree(p, stream); sceneAllocs.clear(); built = false; }
     void freeGeometry() {
-        positions.release(); normals.release(); texcoords.release(); tangents.release(); indices.release();
-        for (auto &t : textures) if (t.texels) cudaFree(t.texels);
+        positions.release(stream); normals.release(stream); texcoords.release(stream); tangents.release(stream); indices.release(stream);
+        for (auto &t : textures) devFree(t.texels, stream);
         textures.clear();
-        if (errFlag) cudaFree(errFlag);
+        devFree(errFlag, stream);
         errFlag = nullptr;
-        for (auto &e : emitters) { if (e.envRaw) cudaFree(e.envRaw); e.envRaw = nullptr; }
+        for (auto &e : emitters) { devFree(e.envRaw, stream); e.envRaw = nullptr; }
     }
-    void freeWavefront() { for (void *p : wfAllocs) cudaFree(p); wfAllocs.clear(); wfCapacity = 0; }
+    void freeWavefront() { for (void *p : wfAllocs) devFree(p, stream); wfAllocs.clear(); wfCapacity = 0; }
     float4 *filmPtr() const { return filmBound ? filmBound : filmInternal; }
 };
 
@@ -146,7 +151,7 @@ template <class T> int devUpload(MtsContext *c, const T *host, size_t n, const T
     *out = nullptr;
     if (n == 0) return MTS_OK;
     T *d = nullptr;
-    CUDA_TRY(cudaMalloc(&d, sizeof(T) * n));
+    CUDA_TRY(devAlloc(&d, sizeof(T) * n, c->stream));
     c->sceneAllocs.push_back(d);
     CUDA_TRY(cudaMemcpyAsync(d, host, sizeof(T) * n, cudaMemcpyHostToDevice, c->stream));
     *out = d;
@@ -167,7 +172,7 @@ int ensureWavefront(MtsContext *c, uint32_t cap) {
     c->freeWavefront();
     Wavefront &w = c->wf;
     auto alloc = [&](void **p, size_t bytes) -> cudaError_t {
-        cudaError_t e = cudaMalloc(p, bytes);
+        cudaError_t e = devAlloc(p, bytes, c->stream);
         if (e == cudaSuccess) c->wfAllocs.push_back(*p);
         return e;
     };
@@ -300,33 +305,40 @@ __global__ void k_hook_sample_rays(const DScene S, int64_t n, const float *sp, f
     q[8] = rx.x; q[9] = rx.y; q[10] = rx.z; q[11] = 0; q[12] = ry.x; q[13] = ry.y; q[14] = ry.z; q[15] = 0;
 }
 
-__global__ void k_hook_trace(const DScene S, int64_t n, const float *rays, int shadow, float *hits, int32_t *ids, Counters *ctr) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    TraceCounters tc = {0, 0};
-    if (i < n) {
-        const float *r = rays + 8 * i;
-        float3 o = f3(r[0], r[1], r[2]), d = f3(r[4], r[5], r[6]);
-        RayHit h;
-        float *q = hits + 4 * i;
-        if (shadow) {
-            bool occ = sceneIntersect<true, true>(S, o, d, r[3], r[7], h, &tc);
-            q[0] = occ ? 0.0f : kInf; q[1] = q[2] = q[3] = 0;
-            if (ids) { ids[2 * i] = ids[2 * i + 1] = -1; }
-        } else {
-            bool ok = sceneIntersect<false, true>(S, o, d, r[3], r[7], h, &tc);
-            if (ok) {
-                const float4 *rec = reinterpret_cast<const float4 *>(S.prims + h.prim);
-                float4 p0 = rec[0], p1 = rec[1], p2 = rec[2];
-                bool tri = __float_as_int(p2.w) == 0;
-                q[0] = h.t; q[1] = tri ? h.u : 0.0f; q[2] = tri ? h.v : 0.0f; q[3] = 0;
-                if (ids) { ids[2 * i] = __float_as_int(p0.w); ids[2 * i + 1] = tri ? __float_as_int(p1.w) : 0; }
-            } else {
-                q[0] = kInf; q[1] = q[2] = q[3] = 0;
-                if (ids) { ids[2 * i] = ids[2 * i + 1] = -1; }
-            }
-        }
+// mtscuda_trace drives the PRODUCTION queue kernels (k_intersect / k_shadow: persistent warps, lane refill, shared
+// stack), so the bit-exact intersection tests cover exactly what the renderer runs.  k_trace_load fills the wavefront
+// arrays the way raygen / shade do, k_trace_export turns the hit records back into (t, u, v) + (shape, primitive).
+__global__ void k_trace_load(const Wavefront W, uint32_t n, const float *rays, int shadow) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {
+        Counters *c = W.ctr;
+        c->qCount[0] = shadow ? 0u : n; c->qCount[1] = 0; c->shadowCount = shadow ? n : 0u; c->doneCount = 0; c->cursor[0] = c->cursor[1] = 0;
     }
-    if (ctr) { atomicAdd(&ctr->nodesVisited, (unsigned long long)tc.nodes); atomicAdd(&ctr->primsTested, (unsigned long long)tc.prims); }
+    if (i >= n) return;
+    const float *r = rays + 8 * (size_t)i;
+    const float4 o = make_float4(r[0], r[1], r[2], r[3]), d = make_float4(r[4], r[5], r[6], r[7]);
+    if (shadow) {
+        W.shO[i] = o; W.shD[i] = d; W.shC[i] = make_float4(1.0f, 0.0f, 0.0f, __int_as_float((int)i));
+        W.L[i] = make_float4(0, 0, 0, 0);
+    } else {
+        W.rayO[i] = o; W.rayD[i] = d; W.queue[0][i] = i;
+    }
+}
+__global__ void k_trace_export(const DScene S, const Wavefront W, uint32_t n, int shadow, float *hits, int32_t *ids) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float *q = hits + 4 * (size_t)i;
+    q[1] = q[2] = q[3] = 0;
+    ids[2 * (size_t)i] = ids[2 * (size_t)i + 1] = -1;
+    if (shadow) { q[0] = W.L[i].x != 0.0f ? kInf : 0.0f; return; }   // k_shadow adds the contribution of unoccluded rays
+    const float4 h = W.hit[i];
+    const int prim = __float_as_int(h.w);
+    if (prim < 0) { q[0] = kInf; return; }
+    const float4 *rec = reinterpret_cast<const float4 *>(S.prims + prim);
+    const float4 p0 = rec[0], p1 = rec[1], p2 = rec[2];
+    const bool tri = __float_as_int(p2.w) == 0;
+    q[0] = h.x; q[1] = tri ? h.y : 0.0f; q[2] = tri ? h.z : 0.0f;
+    ids[2 * (size_t)i] = __float_as_int(p0.w); ids[2 * (size_t)i + 1] = tri ? __float_as_int(p1.w) : 0;
 }
 
 __global__ void k_hook_hit_records(const DScene S, int64_t n, const float *rays, float *out, int32_t *ids) {
@@ -412,18 +424,20 @@ __global__ void k_hook_splat(const DScene S, int64_t n, const float *pos, const 
 
 // device staging of host arrays for the hooks
 struct Staged {
+    cudaStream_t st;
     std::vector<void *> ptrs;
-    ~Staged() { for (void *p : ptrs) cudaFree(p); }
-    template <class T> T *in(const T *h, size_t n, cudaStream_t st) {
+    explicit Staged(cudaStream_t s) : st(s) {}
+    ~Staged() { for (void *p : ptrs) devFree(p, st); }
+    template <class T> T *in(const T *h, size_t n, cudaStream_t) {
         T *d = nullptr;
-        if (cudaMalloc(&d, sizeof(T) * std::max<size_t>(n, 1)) != cudaSuccess) return nullptr;
+        if (devAlloc(&d, sizeof(T) * std::max<size_t>(n, 1), st) != cudaSuccess) return nullptr;
         ptrs.push_back(d);
         if (n) cudaMemcpyAsync(d, h, sizeof(T) * n, cudaMemcpyHostToDevice, st);
         return d;
     }
     template <class T> T *out(size_t n) {
         T *d = nullptr;
-        if (cudaMalloc(&d, sizeof(T) * std::max<size_t>(n, 1)) != cudaSuccess) return nullptr;
+        if (devAlloc(&d, sizeof(T) * std::max<size_t>(n, 1), st) != cudaSuccess) return nullptr;
         ptrs.push_back(d);
         return d;
     }
@@ -464,8 +478,10 @@ MTS_API int mtscuda_create(int device, MtsContext **out) {
         c->maxWindow = (size_t)prop.accessPolicyMaxWindowSize;
         if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, c->l2Bytes) != cudaSuccess) { c->l2Bytes = 0; cudaGetLastError(); }
     }
+    devPoolInit(device);
     CUDA_TRY(cudaStreamCreateWithFlags(&c->ownStream, cudaStreamNonBlocking));
     c->stream = c->ownStream;
+    CUDA_TRY(cudaHostAlloc((void **)&c->hostPoll, sizeof(uint32_t) * kPollRing, cudaHostAllocDefault));
     *out = c;
     return MTS_OK;
 }
@@ -474,8 +490,12 @@ MTS_API void mtscuda_destroy(MtsContext *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     c->freeScene(); c->freeWavefront(); c->freeGeometry();
-    if (c->filmInternal) cudaFree(c->filmInternal);
+    devFree(c->filmInternal, c->stream); devFree(c->filmAlpha, c->stream);
+    cudaStreamSynchronize(c->stream);
+    for (cudaEvent_t e : c->eventPool) cudaEventDestroy(e);
+    if (c->hostPoll) cudaFreeHost(c->hostPoll);
     if (c->ownStream) cudaStreamDestroy(c->ownStream);
+    if (getenv("MTS_POOL_TRIM")) devPoolTrim(c->device);
     delete c;
 }
 
@@ -487,11 +507,17 @@ MTS_API int mtscuda_set_camera(MtsContext *c, const MtsCamera *cam) {
 MTS_API int mtscuda_set_film(MtsContext *c, const MtsFilm *f) {
     if (f->width <= 0 || f->height <= 0 || !(f->filter_radius > 0)) return fail(MTS_EINVAL, "bad film description");
     CUDA_TRY(cudaSetDevice(c->device));
-    if (c->filmInternal) { cudaFree(c->filmInternal); c->filmInternal = nullptr; }
+    devFree(c->filmInternal, c->stream); c->filmInternal = nullptr;
+    devFree(c->filmAlpha, c->stream); c->filmAlpha = nullptr;
     c->film = *f; c->hasFilm = true; c->filmBound = nullptr;
     size_t bytes = sizeof(float4) * (size_t)f->width * f->height;
-    CUDA_TRY(cudaMalloc(&c->filmInternal, bytes));
+    CUDA_TRY(devAlloc(&c->filmInternal, bytes, c->stream));
     CUDA_TRY(cudaMemsetAsync(c->filmInternal, 0, bytes, c->stream));
+    if (f->has_alpha) {
+        CUDA_TRY(devAlloc(&c->filmAlpha, bytes / 4, c->stream));
+        CUDA_TRY(cudaMemsetAsync(c->filmAlpha, 0, bytes / 4, c->stream));
+    }
+    c->ds.filmAlpha = c->filmAlpha;
     c->ds.film = c->filmInternal; c->ds.filmW = f->width; c->ds.filmH = f->height;
     c->ds.filterRadius = f->filter_radius;
     std::memcpy(c->ds.filterTable, f->filter_table, sizeof(f->filter_table));
@@ -507,15 +533,15 @@ MTS_API int mtscuda_add_texture(MtsContext *c, const MtsTextureDesc *d, const fl
     const size_t npix = (size_t)d->width * d->height;
     const int stride = d->channels == 1 ? 1 : 4;  // RGB padded to half4
     float *tmp = nullptr;
-    CUDA_TRY(cudaMalloc(&tmp, sizeof(float) * npix * d->channels));
-    cudaError_t e = cudaMalloc(&t.texels, sizeof(__half) * npix * stride);
+    CUDA_TRY(devAlloc(&tmp, sizeof(float) * npix * d->channels, c->stream));
+    cudaError_t e = devAlloc(&t.texels, sizeof(__half) * npix * stride, c->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(tmp, texels, sizeof(float) * npix * d->channels, cudaMemcpyHostToDevice, c->stream);
     if (e == cudaSuccess) {
         k_texels_to_half<<<(unsigned)((npix + 255) / 256), 256, 0, c->stream>>>(tmp, t.texels, npix, d->channels);
         e = cudaStreamSynchronize(c->stream);
     }
-    cudaFree(tmp);
-    if (e != cudaSuccess) { if (t.texels) cudaFree(t.texels); return fail(MTS_ECUDA, std::string("add_texture: ") + cudaGetErrorString(e)); }
+    devFree(tmp, c->stream);
+    if (e != cudaSuccess) { devFree(t.texels, c->stream); return fail(MTS_ECUDA, std::string("add_texture: ") + cudaGetErrorString(e)); }
     c->textures.push_back(t); c->built = false;
     return (int)c->textures.size() - 1;
 }
@@ -542,7 +568,7 @@ MTS_API int mtscuda_add_mesh(MtsContext *c, const MtsMeshDesc *m) {
     s.d.vtxOffset = vOff; s.d.triOffset = tOff; s.d.ntris = m->ntris; s.nverts = m->nverts;
     const bool deviceTangents = m->uv_tangents == 1 && m->texcoords;
     s.d.flags = (m->normals ? 1u : 0u) | (m->texcoords ? 2u : 0u) | ((m->tangents || deviceTangents) ? 4u : 0u);
-    if (!c->errFlag) { CUDA_TRY(cudaMalloc(&c->errFlag, sizeof(int))); CUDA_TRY(cudaMemsetAsync(c->errFlag, 0, sizeof(int), st)); }
+    if (!c->errFlag) { CUDA_TRY(devAlloc(&c->errFlag, sizeof(int), st)); CUDA_TRY(cudaMemsetAsync(c->errFlag, 0, sizeof(int), st)); }
     // the optional per-vertex / per-triangle arrays are kept index-aligned with positions / indices (zeros where absent)
     CUDA_TRY(c->positions.append(m->positions, 3 * (size_t)m->nverts, st));
     CUDA_TRY(c->normals.append(m->normals, 3 * (size_t)m->nverts, st));
@@ -608,7 +634,7 @@ MTS_API int mtscuda_add_emitter(MtsContext *c, const MtsEmitterDesc *d) {
         size_t n = (size_t)d->env_width * d->env_height * 3;
         if (d->env_width > 65534 || d->env_height > 65534) return fail(MTS_EINVAL, "Environment maps images must be smaller than 65536 pixels in width and height");
         CUDA_TRY(cudaSetDevice(c->device));
-        CUDA_TRY(cudaMalloc(&e.envRaw, sizeof(float) * n));   // straight from the caller's buffer; rounded to half on the device
+        CUDA_TRY(devAlloc(&e.envRaw, sizeof(float) * n, c->stream));   // straight from the caller's buffer; rounded to half on the device
         CUDA_TRY(cudaMemcpyAsync(e.envRaw, d->env_texels, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
         CUDA_TRY(cudaStreamSynchronize(c->stream));
         c->envIndex = (int)c->emitters.size();
@@ -682,6 +708,10 @@ MTS_API int mtscuda_build(MtsContext *c) {
     if (!buildBvh(bin, bout, c->stream, berr)) return fail(MTS_ECUDA, "BVH build failed: " + berr);
     if (bout.nodes) c->sceneAllocs.push_back(bout.nodes);
     if (bout.prims) c->sceneAllocs.push_back(bout.prims);
+    c->bvhDepth = bout.depth;
+    if (bout.depth > kStackCapacity)   // the traversal stack holds one node group per level; deeper trees would drop siblings
+        return fail(MTS_EINVAL, "BVH is " + std::to_string(bout.depth) + " wide levels deep, more than the " + std::to_string(kStackCapacity) +
+                    "-entry traversal stack holds (degenerate geometry, e.g. a long chain of nested slivers)");
     S.bvh = bout.nodes; S.prims = bout.prims; S.numPrims = bin.numPrims;
     if (c->l2Bytes && bout.numNodes > 0) {
         // nodes are stored level by level (breadth first), so a prefix window covers the top of the tree
@@ -729,7 +759,7 @@ MTS_API int mtscuda_build(MtsContext *c) {
         DEnvmap &E = S.env;
         if ((rc = devUpload(c, rowWeights.data(), rowWeights.size(), &E.rowWeights))) return rc;
         auto devAlloc = [&](size_t bytes, void **out) -> int {
-            CUDA_TRY(cudaMalloc(out, bytes)); c->sceneAllocs.push_back(*out); return MTS_OK;
+            CUDA_TRY(mts::devAlloc(out, bytes, c->stream)); c->sceneAllocs.push_back(*out); return MTS_OK;
         };
         __half *tex = nullptr; float *cdfCols = nullptr, *cdfRows = nullptr, *rowTerm = nullptr; uint16_t *gRows = nullptr, *gCols = nullptr;
         if ((rc = devAlloc(sizeof(__half) * 4 * (size_t)w * h, (void **)&tex))) return rc;
@@ -837,46 +867,79 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
     if ((rc = ensureWavefront(c, cap))) return rc;
     const Wavefront &Wf = c->wf;
     if (P->clear_film) CUDA_TRY(cudaMemsetAsync(S.film, 0, sizeof(float4) * (size_t)W * H, st));
+    S.filmAlpha = c->filmAlpha;
+    if (P->clear_film && c->filmAlpha) CUDA_TRY(cudaMemsetAsync(c->filmAlpha, 0, sizeof(float) * (size_t)W * H, st));
     CUDA_TRY(cudaMemsetAsync(Wf.ctr, 0, sizeof(Counters), st));
     CUDA_TRY(cudaMemsetAsync(Wf.keyCount, 0, 4 * 3 * (size_t)Wf.numKeys, st));
 
-    const bool timing = true;
+    // CUDA events around every stage (pooled in the context: creating ~50 events per frame showed up in short renders)
     struct Span { cudaEvent_t a, b; int kind; };
     std::vector<Span> spans;
-    auto begin = [&](int kind) { if (!timing) return; Span s; cudaEventCreate(&s.a); cudaEventCreate(&s.b); s.kind = kind; cudaEventRecord(s.a, st); spans.push_back(s); };
-    auto end = [&]() { if (!timing) return; cudaEventRecord(spans.back().b, st); };
-    cudaEvent_t ev0, ev1; cudaEventCreate(&ev0); cudaEventCreate(&ev1);
+    c->eventsUsed = 0;
+    auto newEvent = [&]() {
+        if (c->eventsUsed == c->eventPool.size()) { cudaEvent_t e; cudaEventCreate(&e); c->eventPool.push_back(e); }
+        return c->eventPool[c->eventsUsed++];
+    };
+    auto begin = [&](int kind) { Span s; s.a = newEvent(); s.b = newEvent(); s.kind = kind; cudaEventRecord(s.a, st); spans.push_back(s); };
+    auto end = [&]() { cudaEventRecord(spans.back().b, st); };
+    cudaEvent_t ev0 = newEvent(), ev1 = newEvent();
+    cudaEvent_t pollEv[kPollRing];
+    for (int i = 0; i < kPollRing; ++i) pollEv[i] = newEvent();
     cudaEventRecord(ev0, st);
 
     // 4 CTAs/SM (128 registers) measured best on cfg3; 3 (168 registers, fewer spills) kept as the measured alternative
     const int shadeMinB = getenv("MTS_SHADE_MINB") ? atoi(getenv("MTS_SHADE_MINB")) : 4;
     const bool traceBounces = getenv("MTS_TRACE_BOUNCES") != nullptr;   // per-bounce queue sizes on stderr (matches ncu launches to ray counts)
     const int gridTrace = c->numSMs * TRACE_MINB, gridWide = c->numSMs * 8;
-    uint64_t launches = 0, normalRays = 0, shadowRays = 0;
-    Counters hc;
+    uint64_t launches = 0;
     bool cancelled = false;
+    // The bounce loop never waits for the device.  Every kernel reads its trip count from device memory, so a bounce
+    // whose queue is empty costs a few empty launches; the loop runs maxDepth bounces (a path of depth maxDepth spawns
+    // no further ray, path.cpp:156-165) and leaves early as soon as a *non-blocking* look at a queue size copied back
+    // a few bounces ago shows zero.  Only unbounded renders (maxDepth = -1) fall back to waiting, after kPatience bounces.
+    const int kPatience = 48, kGiveUp = 4096;
     for (unsigned long long first = 0; first < totalItems && !cancelled; first += cap) {
         uint32_t count = (uint32_t)std::min<unsigned long long>(cap, totalItems - first);
         int cur = 0;
-        k_reset_bounce<<<1, 1, 0, st>>>(Wf.ctr, 0);
+        k_begin_wavefront<<<1, 1, 0, st>>>(Wf.ctr);
         begin(0);
         k_raygen<<<gridWide, 256, 0, st>>>(S, Wf, R, first, count, 0);
         end();
         launches += 2;
-        uint32_t active = count;  // upper bound; the real count is on the device
-        for (int bounce = 0; active > 0; ++bounce) {
+        for (int i = 0; i < kPollRing; ++i) c->hostPoll[i] = 0xffffffffu;
+        for (int bounce = 0; P->max_depth < 0 || bounce < P->max_depth; ++bounce) {
             if (cancel && *cancel) { cancelled = true; break; }
-            k_reset_bounce<<<1, 1, 0, st>>>(Wf.ctr, cur ^ 1);
+            if (bounce >= 1) {
+                // slot (j % ring) = number of rays bounce j left for bounce j + 1; a queue that was empty once stays empty
+                bool empty = false;
+                for (int j = bounce - 1; j >= 0 && j > bounce - 4 && !empty; --j)
+                    empty = cudaEventQuery(pollEv[j % kPollRing]) == cudaSuccess && c->hostPoll[j % kPollRing] == 0;
+                if (!empty && P->max_depth < 0 && bounce >= kPatience) {
+                    CUDA_TRY(cudaEventSynchronize(pollEv[(bounce - 1) % kPollRing]));
+                    empty = c->hostPoll[(bounce - 1) % kPollRing] == 0;
+                }
+                cudaGetLastError();   // cudaErrorNotReady of the queries is not an error
+                if (empty) break;
+                if (bounce > kGiveUp) {
+                    k_abandon<<<gridWide, 256, 0, st>>>(Wf, cur);
+                    k_splat<<<gridWide, 256, 0, st>>>(S, Wf, R);
+                    launches += 2;
+                    break;
+                }
+            }
+            k_begin_bounce<<<1, 1, 0, st>>>(Wf.ctr, cur);
             begin(1);
             setBvhWindow(c, st, true);
             if (P->instrument) k_intersect<true><<<gridTrace, 128, 0, st>>>(S, Wf, cur);
             else k_intersect<false><<<gridTrace, 128, 0, st>>>(S, Wf, cur);
             setBvhWindow(c, st, false);
             end();
-            begin(2);
+            begin(5);
             k_sort_offsets<<<1, 32, 0, st>>>(Wf);
             k_sort_scatter<<<gridWide, 256, 0, st>>>(Wf, cur);
-            k_shade_miss<<<gridWide, 256, 0, st>>>(S, Wf, R, cur);
+            end();
+            begin(6); k_shade_miss<<<gridWide, 256, 0, st>>>(S, Wf, R, cur); end();
+            begin(2);
             switch (shadeMinB) {
             case 3: k_shade<3><<<c->numSMs * 3, 128, 0, st>>>(S, Wf, R, cur); break;
             default: k_shade<4><<<c->numSMs * 4, 128, 0, st>>>(S, Wf, R, cur); break;
@@ -890,18 +953,20 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
             end();
             begin(4); k_splat<<<gridWide, 256, 0, st>>>(S, Wf, R); end();
             launches += 8;
-            CUDA_TRY(cudaMemcpyAsync(&hc, Wf.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
-            CUDA_TRY(cudaStreamSynchronize(st));
-            normalRays += hc.qCount[cur];
-            shadowRays += hc.shadowCount;
-            active = hc.qCount[cur ^ 1];
-            if (traceBounces)
-                fprintf(stderr, "[mtscuda] wavefront %llu bounce %d: closest-hit rays %u, shadow rays %u, continuing %u\n",
-                        first / cap, bounce, hc.qCount[cur], hc.shadowCount, active);
+            CUDA_TRY(cudaMemcpyAsync(&c->hostPoll[bounce % kPollRing], &Wf.ctr->qCount[cur ^ 1], sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaEventRecord(pollEv[bounce % kPollRing], st));
+            if (traceBounces) {
+                Counters hc;
+                CUDA_TRY(cudaMemcpyAsync(&hc, Wf.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+                CUDA_TRY(cudaStreamSynchronize(st));
+                fprintf(stderr, "[mtscuda] wavefront %llu bounce %d: closest-hit rays %u, shadow rays %u, continuing %u, escaped so far %llu\n",
+                        first / cap, bounce, hc.qCount[cur], hc.shadowCount, hc.qCount[cur ^ 1], hc.missRays);
+            }
             cur ^= 1;
-            if (bounce > 4096) break;  // safety net for maxDepth = -1 with rr disabled by huge rrDepth
         }
     }
+    k_begin_wavefront<<<1, 1, 0, st>>>(Wf.ctr);   // folds the last bounce's shadow rays into the totals
+    ++launches;
     cudaEventRecord(ev1, st);
     if ((rc = syncCheck(c, "render"))) return rc;
     MtsStats &sx = c->stats;
@@ -909,19 +974,20 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
     std::memset(&sx, 0, sizeof(sx));
     sx.build_ms = build_ms;
     cudaEventElapsedTime(&sx.render_ms, ev0, ev1);
-    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
     for (auto &s : spans) {
         float ms = 0; cudaEventElapsedTime(&ms, s.a, s.b);
-        float *dst = s.kind == 0 ? &sx.raygen_ms : s.kind == 1 ? &sx.intersect_ms : s.kind == 2 ? &sx.shade_ms : s.kind == 3 ? &sx.shadow_ms : &sx.splat_ms;
+        float *dst = s.kind == 0 ? &sx.raygen_ms : s.kind == 1 ? &sx.intersect_ms : s.kind == 2 ? &sx.shade_ms : s.kind == 3 ? &sx.shadow_ms :
+                     s.kind == 4 ? &sx.splat_ms : s.kind == 5 ? &sx.sort_ms : &sx.miss_ms;
         *dst += ms;
         if (s.kind == 1) sx.intersect_launches++; else if (s.kind == 2) sx.shade_launches++;
         else if (s.kind == 3) sx.shadow_launches++; else if (s.kind == 4) sx.splat_launches++;
-        cudaEventDestroy(s.a); cudaEventDestroy(s.b);
     }
+    Counters hc;
     CUDA_TRY(cudaMemcpy(&hc, Wf.ctr, sizeof(Counters), cudaMemcpyDeviceToHost));
     sx.camera_samples = (uint64_t)W * H * (uint64_t)P->spp;
-    sx.normal_rays = normalRays; sx.shadow_rays = shadowRays;
+    sx.normal_rays = hc.normalRays; sx.shadow_rays = hc.shadowRays;
     sx.path_length_sum = hc.pathLenSum;
+    sx.miss_paths = hc.missRays; sx.shaded_paths = hc.normalRays - hc.missRays;
     sx.kernel_launches = launches;
     sx.bvh_nodes_visited = hc.nodesVisited; sx.bvh_prims_tested = hc.primsTested;
     sx.bvh_nodes_visited_shadow = hc.nodesVisitedShadow; sx.bvh_prims_tested_shadow = hc.primsTestedShadow;
@@ -937,13 +1003,21 @@ MTS_API int mtscuda_read_film(MtsContext *c, float *out) {
     return MTS_OK;
 }
 
+MTS_API int mtscuda_read_film_alpha(MtsContext *c, float *out) {
+    if (!c->hasFilm || !c->filmAlpha) return fail(MTS_ESTATE, "the film has no alpha plane (MtsFilm.has_alpha = 0)");
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    CUDA_TRY(cudaMemcpy(out, c->filmAlpha, sizeof(float) * (size_t)c->film.width * c->film.height, cudaMemcpyDeviceToHost));
+    return MTS_OK;
+}
+
 MTS_API int mtscuda_get_stats(MtsContext *c, MtsStats *s) { *s = c->stats; return MTS_OK; }
 
 // ---- per-function entry points --------------------------------------------------------------
 #define HOOK_PREAMBLE(needBuilt) \
     if ((needBuilt) && !c->built) return fail(MTS_ESTATE, "call build() first"); \
     CUDA_TRY(cudaSetDevice(c->device)); \
-    Staged sg; cudaStream_t st = c->stream; c->ds.film = c->filmPtr(); c->ds.cam = c->cam;
+    cudaStream_t st = c->stream; Staged sg(st); c->ds.film = c->filmPtr(); c->ds.cam = c->cam;
 #define NEED(p) if (!(p)) return fail(MTS_ECUDA, "device allocation failed")
 
 MTS_API int mtscuda_sample_rays(MtsContext *c, int64_t n, const float *sp, float *out) {
@@ -957,17 +1031,30 @@ MTS_API int mtscuda_sample_rays(MtsContext *c, int64_t n, const float *sp, float
 
 MTS_API int mtscuda_trace(MtsContext *c, int64_t n, const float *rays, int32_t shadow, float *hits, int32_t *ids) {
     HOOK_PREAMBLE(true)
-    float *dr = sg.in(rays, 8 * n, st), *dh = sg.out<float>(4 * n); int32_t *di = sg.out<int32_t>(2 * n);
-    Counters *ctr = sg.out<Counters>(1); NEED(dr && dh && di && ctr);
-    CUDA_TRY(cudaMemsetAsync(ctr, 0, sizeof(Counters), st));
-    k_hook_trace<<<gridFor(n), 128, 0, st>>>(c->ds, n, dr, shadow, dh, di, ctr);
-    CUDA_TRY(cudaMemcpyAsync(hits, dh, sizeof(float) * 4 * n, cudaMemcpyDeviceToHost, st));
-    if (ids) CUDA_TRY(cudaMemcpyAsync(ids, di, sizeof(int32_t) * 2 * n, cudaMemcpyDeviceToHost, st));
-    Counters hc;
-    CUDA_TRY(cudaMemcpyAsync(&hc, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
-    int rc = syncCheck(c, "trace");
-    c->stats.bvh_nodes_visited = hc.nodesVisited; c->stats.bvh_prims_tested = hc.primsTested;
-    return rc;
+    if (n <= 0) return MTS_OK;
+    const uint32_t chunk = (uint32_t)std::min<int64_t>(n, 1 << 22);
+    int rc;
+    if ((rc = ensureWavefront(c, (chunk + 31u) & ~31u))) return rc;
+    const Wavefront &Wf = c->wf;
+    float *dr = sg.out<float>(8 * (size_t)chunk), *dh = sg.out<float>(4 * (size_t)chunk); int32_t *di = sg.out<int32_t>(2 * (size_t)chunk);
+    NEED(dr && dh && di);
+    CUDA_TRY(cudaMemsetAsync(Wf.ctr, 0, sizeof(Counters), st));
+    CUDA_TRY(cudaMemsetAsync(Wf.keyCount, 0, 4 * 3 * (size_t)Wf.numKeys, st));
+    const int gridTrace = c->numSMs * TRACE_MINB;
+    std::vector<int32_t> idTmp;
+    for (int64_t first = 0; first < n; first += chunk) {
+        const uint32_t m = (uint32_t)std::min<int64_t>(chunk, n - first);
+        CUDA_TRY(cudaMemcpyAsync(dr, rays + 8 * first, sizeof(float) * 8 * m, cudaMemcpyHostToDevice, st));
+        k_trace_load<<<gridFor(m), 128, 0, st>>>(Wf, m, dr, shadow);
+        if (shadow) k_shadow<false><<<gridTrace, 128, 0, st>>>(c->ds, Wf);
+        else k_intersect<false><<<gridTrace, 128, 0, st>>>(c->ds, Wf, 0);
+        k_trace_export<<<gridFor(m), 128, 0, st>>>(c->ds, Wf, m, shadow, dh, di);
+        CUDA_TRY(cudaMemcpyAsync(hits + 4 * first, dh, sizeof(float) * 4 * m, cudaMemcpyDeviceToHost, st));
+        if (ids) CUDA_TRY(cudaMemcpyAsync(ids + 2 * first, di, sizeof(int32_t) * 2 * m, cudaMemcpyDeviceToHost, st));
+        if ((rc = syncCheck(c, "trace"))) return rc;
+    }
+    CUDA_TRY(cudaMemsetAsync(Wf.keyCount, 0, 4 * 3 * (size_t)Wf.numKeys, st));   // k_intersect left its key histogram behind
+    return syncCheck(c, "trace");
 }
 
 MTS_API int mtscuda_hit_records(MtsContext *c, int64_t n, const float *rays, float *out, int32_t *ids) {

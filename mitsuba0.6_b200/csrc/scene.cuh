@@ -89,6 +89,7 @@ struct DScene {
     // sensor + film
     MtsCamera cam;
     float4 *film; int filmW, filmH;
+    float *filmAlpha;   // sum w * alpha, only for films with an alpha channel (else nullptr)
     float filterRadius; float filterTable[MTS_FILTER_RESOLUTION + 1];
 };
 

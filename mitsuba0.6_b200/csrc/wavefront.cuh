@@ -18,6 +18,8 @@ struct Counters {
     uint32_t shadowCount;
     uint32_t doneCount;
     uint32_t cursor[2];     // next unclaimed ray of the intersect / shadow queue (persistent warps pull from these)
+    unsigned long long missRays;                 // rays that escaped (sort key 0), total over all bounces
+    unsigned long long normalRays, shadowRays;   // totals over all bounces ("Normal/Shadow rays traced", skdtree.cpp:46-47), kept on the device
     unsigned long long pathLenSum;
     unsigned long long nodesVisited, primsTested;  // instrumented traces only (closest hit)
     unsigned long long nodesVisitedShadow, primsTestedShadow;
@@ -49,7 +51,8 @@ struct RenderConst {
     uint32_t paddedPixels;   // tilesX*tilesY*32
 };
 
-enum { PF_SCATTERED = 1, PF_PREV_DELTA = 2, PF_PREV_REFN_OK = 4 };
+enum { PF_SCATTERED = 1, PF_PREV_DELTA = 2, PF_PREV_REFN_OK = 4,
+       PF_CAMERA_HIT = 8 };   // the camera ray hit a surface: alpha = 1 (RadianceQueryRecord::rayIntersect, records.inl:121-137)
 
 // One atomicAdd per warp: returns this thread's slot (valid only where pred is true).
 DEVFN uint32_t warpAppend(uint32_t *counter, bool pred) {
@@ -222,6 +225,7 @@ __global__ void k_sort_offsets(const Wavefront W) {
         uint32_t v = k < W.numKeys ? cnt[k] : 0, incl = v;
         for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if ((int)threadIdx.x >= o) incl += t; }
         if (k < W.numKeys) { off[k] = carry + incl - v; cur[k] = 0; cnt[k] = 0; }
+        if (k == 0) W.ctr->missRays += v;
         carry += __shfl_sync(0xffffffffu, incl, 31);
     }
 }
@@ -252,6 +256,7 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
     uint32_t depth = meta.z & 0xffffu, flags = meta.z >> 16;
     const int prim = __float_as_int(hv.w);
     const bool first = depth == 1;
+    if (first) flags |= PF_CAMERA_HIT;
 
     auto finish = [&]() { W.L[slot] = make_float4(L.x, L.y, L.z, 0); W.meta[slot] = make_uint4(meta.x, meta.y, depth | (flags << 16), 0); };
 
@@ -413,7 +418,7 @@ DEVFN void filmAdd(float4 *dst, float4 v) {
     atomicAdd(&dst->x, v.x); atomicAdd(&dst->y, v.y); atomicAdd(&dst->z, v.z); atomicAdd(&dst->w, v.w);
 #endif
 }
-DEVFN void splatSample(const DScene &S, float2 samplePos, float3 value) {
+DEVFN void splatSample(const DScene &S, float2 samplePos, float3 value, float alpha = 1.0f) {
     // reject invalid samples like put() does (:147-151)
     if (!(isfinite(value.x) && isfinite(value.y) && isfinite(value.z)) || value.x < 0 || value.y < 0 || value.z < 0) return;
     const float r = S.filterRadius;
@@ -427,6 +432,7 @@ DEVFN void splatSample(const DScene &S, float2 samplePos, float3 value) {
             float w = S.filterTable[min((int)fabsf((x - px) * scaleFactor), MTS_FILTER_RESOLUTION)] * wy;
             if (w == 0.0f) continue;
             filmAdd(S.film + (size_t)y * S.filmW + x, make_float4(w * value.x, w * value.y, w * value.z, w));
+            if (S.filmAlpha && alpha != 0.0f) atomicAdd(S.filmAlpha + (size_t)y * S.filmW + x, w * alpha);   // imageblock.h:176-186, alpha channel
         }
     }
 }
@@ -439,15 +445,33 @@ __global__ void __launch_bounds__(256) k_splat(const DScene S, const Wavefront W
         uint4 meta = W.meta[slot];
         float4 u = rand4(R.seed, meta.x, meta.y, 0);
         int x = (int)(meta.x % (uint32_t)S.filmW), y = (int)(meta.x / (uint32_t)S.filmW);
-        splatSample(S, make_float2(x + u.x, y + u.y), f3(l));
+        splatSample(S, make_float2(x + u.x, y + u.y), f3(l), ((meta.z >> 16) & PF_CAMERA_HIT) ? 1.0f : 0.0f);
         lenSum += meta.z & 0xffffu;
     }
     for (int o = 16; o > 0; o >>= 1) lenSum += __shfl_xor_sync(0xffffffffu, lenSum, o);
     if ((threadIdx.x & 31) == 0 && lenSum) atomicAdd(&W.ctr->pathLenSum, lenSum);
 }
 
-__global__ void k_reset_bounce(Counters *c, int nextSel) {
-    c->qCount[nextSel] = 0; c->shadowCount = 0; c->doneCount = 0; c->cursor[0] = c->cursor[1] = 0;
+// Bounce bookkeeping on the device (the host never reads a counter inside the bounce loop): add the rays of the
+// bounce that is about to run (closest hit) and of the one that just ran (shadow) to the totals, reset the queues.
+__global__ void k_begin_bounce(Counters *c, int cur) {
+    c->normalRays += c->qCount[cur]; c->shadowRays += c->shadowCount;
+    c->qCount[cur ^ 1] = 0; c->shadowCount = 0; c->doneCount = 0; c->cursor[0] = c->cursor[1] = 0;
+}
+__global__ void k_begin_wavefront(Counters *c) {
+    c->shadowRays += c->shadowCount;
+    c->qCount[0] = c->qCount[1] = 0; c->shadowCount = 0; c->doneCount = 0; c->cursor[0] = c->cursor[1] = 0;
+}
+// Safety net of unbounded renders (maxDepth = -1 with Russian roulette pushed out of reach): the paths still alive
+// when the host gives up are finished with what they have gathered so far and splatted, never dropped.
+__global__ void __launch_bounds__(256) k_abandon(const Wavefront W, int qsel) {
+    const uint32_t count = W.ctr->qCount[qsel];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ((count + 31u) & ~31u); i += gridDim.x * blockDim.x) {
+        const bool valid = i < count;
+        const uint32_t slot = valid ? W.queue[qsel][i] : 0u;
+        uint32_t c = warpAppend(&W.ctr->doneCount, valid);
+        if (valid) W.doneQ[c] = slot;
+    }
 }
 
 } // namespace mts

@@ -216,7 +216,7 @@ def _parse_spectrum(tag, a):
             rgb = _floats(v)
             if len(rgb) == 1:
                 rgb = rgb * 3
-        if tag == "srgb" or v.startswith("#"):
+        if tag == "srgb":   # <rgb> is linear whatever its spelling, only <srgb> is converted (scenehandler.cpp:461-528)
             rgb = [float(x) for x in srgb_to_linear(rgb)]
         return Spectrum(rgb)
     vals = _floats(v) if ":" not in v else None
@@ -738,7 +738,10 @@ def flatten(scene):
     cox, coy = int(film.get("cropOffsetX", 0)), int(film.get("cropOffsetY", 0))
     rf = film.child("rfilter") or Plugin("rfilter", "gaussian")  # Film::configure default, film.cpp:89-96
     radius, table = hm.filter_table(rf.type, rf.get("radius"), rf.get("stddev", 0.5))
-    fs.film = abi.Film(cw, ch, radius, (abi.C.c_float * 32)(*[float(x) for x in table]))
+    # HDRFilm pixelFormat (src/films/hdrfilm.cpp:240-275): the alpha variants make Film::hasAlpha() true
+    pixel_formats = [f.strip().lower() for f in str(film.get("pixelFormat", "rgb")).split(",")]
+    has_alpha = any(f in ("luminancealpha", "rgba", "xyza", "spectrumalpha") for f in pixel_formats)
+    fs.film = abi.Film(cw, ch, radius, (abi.C.c_float * 32)(*[float(x) for x in table]), int(has_alpha))
     fs.film_size = (cw, ch)
     sampler = sensor.child("sampler") or Plugin("sampler", "independent", sampleCount=4)
     if sampler.type != "independent":

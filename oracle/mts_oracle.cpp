@@ -91,6 +91,7 @@ struct MtsContext {
     V3 sceneLo, sceneHi;
     bool built = false;
     std::vector<float> filmBuf; /* w*h*4 */
+    std::vector<float> alphaBuf; /* w*h, films with an alpha channel only */
     MtsStats stats;
     std::atomic<uint64_t> normalRays{0}, shadowRays{0};
 };
@@ -585,10 +586,11 @@ V3 emitterLe(const MtsContext &c, const Its &its, V3 d) { /* AreaLight::eval (ar
 }
 
 /* MIPathTracer::Li (src/integrators/path/path.cpp:119-294) */
-V3 Li(MtsContext &c, const MtsRenderParams &P, V3 o, V3 d, float mint, float maxt, Rng &rng, int &depthOut) {
+V3 Li(MtsContext &c, const MtsRenderParams &P, V3 o, V3 d, float mint, float maxt, Rng &rng, int &depthOut, float *alphaOut = nullptr) {
     Its its; V3 L(0.0f); bool scattered = false;
     Hit h;
     bool valid = sceneIntersect(c, o, d, mint, maxt, false, h);
+    if (alphaOut) *alphaOut = valid ? 1.0f : 0.0f;   /* RadianceQueryRecord::rayIntersect with EOpacity (records.inl:121-137) */
     if (valid) fillIts(c, o, d, h, its);
     V3 throughput(1.0f); float eta = 1.0f;
     int depth = 1; bool emittedOk = true;
@@ -684,7 +686,7 @@ V3 Li(MtsContext &c, const MtsRenderParams &P, V3 o, V3 d, float mint, float max
 
 /* ImageBlock::put (include/mitsuba/render/imageblock.h:144-204) on a border-less full-frame
  * accumulator; equivalent to per-block put + Film::put(block). */
-void splat(const MtsFilm &f, float *buf, V2 samplePos, V3 value) {
+void splat(const MtsFilm &f, float *buf, V2 samplePos, V3 value, float *alphaBuf = nullptr, float alpha = 1.0f) {
     float vals[4] = {value.x, value.y, value.z, 1.0f};
     for (int i = 0; i < 4; ++i) if (!std::isfinite(vals[i]) || vals[i] < 0) return;
     const float r = f.filter_radius;
@@ -699,6 +701,7 @@ void splat(const MtsFilm &f, float *buf, V2 samplePos, V3 value) {
             float w = wx * wy;
             float *dst = buf + ((size_t)y * f.width + x) * 4;
             for (int k = 0; k < 4; ++k) dst[k] += w * vals[k];
+            if (alphaBuf) alphaBuf[(size_t)y * f.width + x] += w * alpha;
         }
     }
 }
@@ -725,6 +728,8 @@ MTS_API int mtsoracle_set_film(MtsContext *c, const MtsFilm *f) {
     if (f->width <= 0 || f->height <= 0 || !(f->filter_radius > 0)) return fail(MTS_EINVAL, "bad film");
     c->film = *f; c->hasFilm = true;
     c->filmBuf.assign((size_t)f->width * f->height * 4, 0.0f);
+    c->alphaBuf.clear();
+    if (f->has_alpha) c->alphaBuf.assign((size_t)f->width * f->height, 0.0f);
     return MTS_OK;
 }
 MTS_API int mtsoracle_add_texture(MtsContext *c, const MtsTextureDesc *d, const float *texels) {
@@ -894,7 +899,8 @@ MTS_API int mtsoracle_render(MtsContext *c, const MtsRenderParams *P, volatile c
     if (P->rr_depth <= 0) return fail(MTS_EINVAL, "'rrDepth' must be set to a value greater than zero!");
     if (P->max_depth <= 0 && P->max_depth != -1) return fail(MTS_EINVAL, "'maxDepth' must be set to -1 (infinite) or a value greater than zero!");
     const int W = c->film.width, H = c->film.height;
-    if (P->clear_film) std::fill(c->filmBuf.begin(), c->filmBuf.end(), 0.0f);
+    if (P->clear_film) { std::fill(c->filmBuf.begin(), c->filmBuf.end(), 0.0f); std::fill(c->alphaBuf.begin(), c->alphaBuf.end(), 0.0f); }
+    const bool hasAlpha = !c->alphaBuf.empty();
     c->normalRays = 0; c->shadowRays = 0;
     auto t0 = std::chrono::steady_clock::now();
     uint64_t pathLen = 0;
@@ -902,7 +908,7 @@ MTS_API int mtsoracle_render(MtsContext *c, const MtsRenderParams *P, volatile c
 #ifdef _OPENMP
     nthreads = omp_get_max_threads();
 #endif
-    std::vector<std::vector<float>> tfilm(nthreads);
+    std::vector<std::vector<float>> tfilm(nthreads), talpha(hasAlpha ? nthreads : 0);
     bool cancelled = false;
 #pragma omp parallel reduction(+ : pathLen)
     {
@@ -912,6 +918,8 @@ MTS_API int mtsoracle_render(MtsContext *c, const MtsRenderParams *P, volatile c
 #endif
         std::vector<float> &buf = tfilm[tid];
         buf.assign((size_t)W * H * 4, 0.0f);
+        float *abuf = nullptr;
+        if (hasAlpha) { talpha[tid].assign((size_t)W * H, 0.0f); abuf = talpha[tid].data(); }
         t_normalRays = t_shadowRays = 0;
 #pragma omp for schedule(dynamic, 1)
         for (int y = 0; y < H; ++y) {
@@ -923,10 +931,10 @@ MTS_API int mtsoracle_render(MtsContext *c, const MtsRenderParams *P, volatile c
                     V2 samplePos{x + u.x, y + u.y};
                     V3 o, d; float mint, maxt;
                     sampleRay(c->cam, samplePos, o, d, mint, maxt);
-                    int depth;
-                    V3 L = Li(*c, *P, o, d, mint, maxt, rng, depth);
+                    int depth; float alpha = 1.0f;
+                    V3 L = Li(*c, *P, o, d, mint, maxt, rng, depth, hasAlpha ? &alpha : nullptr);
                     pathLen += depth;
-                    splat(c->film, buf.data(), samplePos, L);
+                    splat(c->film, buf.data(), samplePos, L, abuf, alpha);
                 }
             }
         }
@@ -937,6 +945,7 @@ MTS_API int mtsoracle_render(MtsContext *c, const MtsRenderParams *P, volatile c
     const long long nf = (long long)c->filmBuf.size();
 #pragma omp parallel for schedule(static)
     for (long long i = 0; i < nf; ++i) { float acc = c->filmBuf[i]; for (auto &b : tfilm) if (!b.empty()) acc += b[i]; c->filmBuf[i] = acc; }
+    for (auto &b : talpha) if (!b.empty()) for (size_t i = 0; i < b.size(); ++i) c->alphaBuf[i] += b[i];
     MtsStats &st = c->stats;
     st.camera_samples = (uint64_t)W * H * P->spp;
     st.normal_rays = c->normalRays; st.shadow_rays = c->shadowRays; st.path_length_sum = pathLen;
@@ -946,6 +955,10 @@ MTS_API int mtsoracle_render(MtsContext *c, const MtsRenderParams *P, volatile c
 }
 
 MTS_API int mtsoracle_read_film(MtsContext *c, float *out) { std::memcpy(out, c->filmBuf.data(), c->filmBuf.size() * sizeof(float)); return MTS_OK; }
+MTS_API int mtsoracle_read_film_alpha(MtsContext *c, float *out) {
+    if (c->alphaBuf.empty()) return fail(MTS_ESTATE, "the film has no alpha plane (MtsFilm.has_alpha = 0)");
+    std::memcpy(out, c->alphaBuf.data(), c->alphaBuf.size() * sizeof(float)); return MTS_OK;
+}
 MTS_API int mtsoracle_bind_film(MtsContext *, void *) { return fail(MTS_EINVAL, "bind_film: device memory is a CUDA-library concept"); }
 MTS_API int mtsoracle_set_stream(MtsContext *, void *) { return fail(MTS_EINVAL, "set_stream: CUDA streams are a CUDA-library concept"); }
 MTS_API int mtsoracle_get_stats(MtsContext *c, MtsStats *s) { *s = c->stats; return MTS_OK; }

@@ -200,7 +200,7 @@ int mtsref_scene_initialize(void *s, double *kdBuildSeconds) {
 }
 
 /* mitsuba.cpp:375-395: RenderJob on the scheduler's workers; the film comes back as (sum w*R, sum w*G, sum w*B, sum w). */
-int mtsref_render(void *s, float *outRGBW, double *seconds, const char *destFile) {
+int mtsref_render(void *s, float *outRGBW, double *seconds, const char *destFile, float *outAlpha /* may be NULL */) {
     GUARD_BEGIN
     Scene *scene = (Scene *)s;
     scene->setDestinationFile(fs::path(destFile ? destFile : "/tmp/mtsref_out"));
@@ -222,6 +222,7 @@ int mtsref_render(void *s, float *outRGBW, double *seconds, const char *destFile
         for (size_t i = 0; i < (size_t)size.x * size.y; ++i) {
             outRGBW[4 * i] = src[ch * i]; outRGBW[4 * i + 1] = src[ch * i + 1]; outRGBW[4 * i + 2] = src[ch * i + 2];
             outRGBW[4 * i + 3] = src[ch * i + ch - 1];
+            if (outAlpha) outAlpha[i] = src[ch * i + ch - 2];   /* ESpectrumAlphaWeight: ..., alpha, weight */
         }
     }
     return 0;

@@ -41,6 +41,11 @@
 MTS_NAMESPACE_BEGIN
 
 static StatsCounter statLaunches("cudapath", "CUDA kernel launches");
+/* the same counters the CPU path feeds (src/librender/skdtree.cpp:46-47, src/integrators/path/path.cpp:24), so that
+   `mitsuba -v` / Statistics::getStats() report the GPU render like a CPU one */
+static StatsCounter statNormalRays("General", "Normal rays traced");
+static StatsCounter statShadowRays("General", "Shadow rays traced");
+static StatsCounter statAvgPathLength("Path tracer", "Average path length", EAverage);
 
 class CudaPath : public Integrator {
 public:
@@ -107,13 +112,23 @@ public:
             } else {
                 check(ctx, rc);
                 statLaunches += st.kernel_launches;
+                statNormalRays += st.normal_rays;
+                statShadowRays += st.shadow_rays;
+                statAvgPathLength.incrementBase(st.camera_samples);
+                statAvgPathLength += st.path_length_sum;
                 Log(EInfo, "cudapath: %.1f ms on the device, %.1f Msamples/s, %.1f Mrays/s (BVH build %.1f ms)",
                     st.render_ms, st.camera_samples / (st.render_ms * 1e3), (st.normal_rays + st.shadow_rays) / (st.render_ms * 1e3), st.build_ms);
                 /* film: (sum w*R, sum w*G, sum w*B, sum w) -> one ESpectrumAlphaWeight block (hdrfilm.cpp:391-393) */
-                std::vector<float> rgbw((size_t) size.x * size.y * 4);
+                std::vector<float> rgbw((size_t) size.x * size.y * 4), alpha;
                 check(ctx, mtscuda_read_film(ctx, rgbw.data()));
+                if (film->hasAlpha()) {   /* sum w * alpha, alpha = 0 where the camera ray escaped (records.inl:121-137) */
+                    alpha.resize((size_t) size.x * size.y);
+                    check(ctx, mtscuda_read_film_alpha(ctx, alpha.data()));
+                }
                 ref<ImageBlock> block = new ImageBlock(Bitmap::ESpectrumAlphaWeight, size, film->getReconstructionFilter());
-                block->setOffset(film->getCropOffset());
+                /* block offsets are relative to the crop window (renderproc.cpp bindResource starts at (0, 0)); the
+                   crop offset itself is already part of the camera's sample-to-camera transform */
+                block->setOffset(Point2i(0, 0));
                 block->clear();
                 Bitmap *bmp = block->getBitmap();
                 const int border = block->getBorderSize(), ch = bmp->getChannelCount(), bw = bmp->getWidth();
@@ -123,7 +138,7 @@ public:
                     Float *d = dst + ((size_t) (y + border) * bw + (x + border)) * ch;
                     Spectrum spec; spec.fromLinearRGB(s[0], s[1], s[2]);
                     for (int k = 0; k < SPECTRUM_SAMPLES; ++k) d[k] = spec[k];
-                    d[SPECTRUM_SAMPLES] = s[3];       /* alpha accumulates w * 1 */
+                    d[SPECTRUM_SAMPLES] = alpha.empty() ? s[3] : alpha[(size_t) y * size.x + x];   /* without EOpacity alpha stays 1: w * 1 */
                     d[SPECTRUM_SAMPLES + 1] = s[3];   /* weight */
                 }
                 film->put(block);
@@ -228,14 +243,13 @@ private:
             c.inv_resolution[0] = invRes.x; c.inv_resolution[1] = invRes.y;
             m_owner->check(m_ctx, mtscuda_set_camera(m_ctx, &c));
 
-            if (film->hasAlpha())
-                SLog(EWarn, "cudapath: the film requests an alpha channel; alpha is reported as the filter weight");
             const ReconstructionFilter *rf = film->getReconstructionFilter();
             MtsFilm mf;
             mf.width = cropSize.x; mf.height = cropSize.y; mf.filter_radius = rf->getRadius();
             for (int i = 0; i <= MTS_FILTER_RESOLUTION; ++i)   /* m_values[i] through the public accessor */
                 mf.filter_table[i] = rf->evalDiscretized((i + 0.5f) * rf->getRadius() / MTS_FILTER_RESOLUTION);
             mf.filter_table[MTS_FILTER_RESOLUTION] = 0;
+            mf.has_alpha = film->hasAlpha() ? 1 : 0;
             m_owner->check(m_ctx, mtscuda_set_film(m_ctx, &mf));
             if (scene->getSampler()->getClass()->getName() != "IndependentSampler")
                 err("sampler class " + scene->getSampler()->getClass()->getName() + " is out of scope (independent)");
@@ -253,12 +267,13 @@ private:
                 m_owner->check(m_ctx, id);
                 return id;
             } else if (cls == "Sphere") {
-                /* sphere.cpp:100-130: the scale of toWorld is folded into the radius */
-                Transform o2w = props.getTransform("toWorld", Transform()) * Transform::translate(Vector(props.getPoint("center", Point(0.0f))));
+                /* sphere.cpp:108-121: objectToWorld = toWorld * scale(1/r) * translate(center), radius *= r */
+                Transform o2w = Transform::translate(Vector(props.getPoint("center", Point(0.0f))));
                 Float radius = props.getFloat("radius", 1.0f);
                 if (props.hasProperty("toWorld")) {
-                    Float r = o2w(Vector(1, 0, 0)).length();
-                    o2w = o2w * Transform::scale(Vector(1 / r));
+                    Transform toWorld = props.getTransform("toWorld");
+                    Float r = toWorld(Vector(1, 0, 0)).length();
+                    o2w = toWorld * Transform::scale(Vector(1 / r)) * o2w;
                     radius *= r;
                 }
                 float m[16]; toRowMajor(o2w, m);

@@ -8,6 +8,7 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))   # oracle_lib: the CPU oracle behind the package wrappers (test infrastructure)
 
 
 def pytest_configure(config):
@@ -17,9 +18,10 @@ def pytest_configure(config):
 @pytest.fixture(scope="session", autouse=True)
 def _built():
     """Build the native libraries once per session if they are missing."""
-    from mitsuba0_6_b200 import abi  # noqa
     import mts_b200  # noqa
-    if not (os.path.exists(abi.LIB_PATHS["cuda"]) and os.path.exists(abi.LIB_PATHS["oracle"])):
+    from mitsuba0_6_b200 import abi  # noqa
+    import oracle_lib
+    if not (os.path.exists(abi.CUDA_LIB_PATH) and os.path.exists(oracle_lib.ORACLE_LIB_PATH)):
         import __graft_entry__ as g
         g.build()
     yield

@@ -16,6 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 sys.path.insert(0, os.path.join(ROOT, "oracle", "refbuild"))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
 
 import numpy as np  # noqa: E402
 import mts_b200 as M  # noqa: E402,F401
@@ -106,9 +107,33 @@ def twosided():
     return out
 
 
+def boundary():
+    """boundary.npz: crop window, sphere transform composition and the alpha channel, rendered by the reference."""
+    out = {}
+    for name, make in G.BOUNDARY_IMAGE_SCENES.items():
+        scn = make()
+        rsi = mtsref.RefScene(scn)
+        film, alpha = rsi.render(alpha=True)
+        out["image/%s/rgb" % name] = M.develop(film).astype(np.float16)
+        w = film[..., 3]
+        out["image/%s/alpha" % name] = np.divide(alpha, w, out=np.zeros_like(alpha), where=w > 0).astype(np.float16)
+        st = rsi.stats
+        h, wd = film.shape[:2]
+        spp = G.scene_dims(scn)[2]
+        out["image/%s/stats" % name] = np.array([st.get("normal_rays", 0) / (wd * h * spp), st.get("shadow_rays", 0) / (wd * h * spp),
+                                                 st.get("avg_path_length", 0), rsi.render_s, mtsref.load().mtsref_thread_count()], dtype=np.float64)
+        print("%-12s %dx%d %d spp: reference render %.1f s" % (name, wd, h, spp, rsi.render_s), flush=True)
+    return out
+
+
 if __name__ == "__main__":
     if not mtsref.available():
         raise SystemExit("oracle/_ref is not built: make -C oracle/refbuild (needs /root/reference)")
+    if "--boundary" in sys.argv:
+        t = boundary()
+        np.savez_compressed(os.path.join(HERE, "boundary.npz"), **t)
+        print("boundary.npz: %d arrays" % len(t))
+        raise SystemExit(0)
     if "--twosided" in sys.argv:
         t = twosided()
         np.savez_compressed(os.path.join(HERE, "twosided.npz"), **t)

@@ -174,3 +174,23 @@ def check_image(path_tracer, name, gold_images, spp, bar, lazy_shadow=False):
         assert abs(rays[1] / st_ref[1] - 1) < 0.01, (name, rays, st_ref[:3])
     assert abs(rays[2] - st_ref[2]) < 0.02, (name, rays, st_ref[:3])
     return err
+
+
+def check_boundary_image(path_tracer, name, gold_boundary, spp, bar):
+    """Crop window / sphere transform composition / alpha channel against the reference's own `path` render."""
+    ref = gold_boundary["image/%s/rgb" % name].astype(np.float32)
+    ref_alpha = gold_boundary["image/%s/alpha" % name].astype(np.float32)
+    film = path_tracer.render(spp=spp, seed=5)
+    img = M.develop(film)
+    assert img.shape == ref.shape, (img.shape, ref.shape)
+    err = M.rel_mse(img, ref)
+    assert abs(img.mean() / ref.mean() - 1) < 0.03, (name, img.mean(), ref.mean())
+    assert err < bar, (name, err, bar)
+    if path_tracer.flat.film.has_alpha:
+        w = film[..., 3]
+        alpha = np.divide(path_tracer.ctx.read_film_alpha(), w, out=np.zeros_like(w), where=w > 0)
+        # pixel-wise coverage: identical where the pixel footprint is fully inside / outside the geometry
+        solid = (ref_alpha == 0) | (ref_alpha == 1)
+        assert np.abs(alpha[solid] - ref_alpha[solid]).max() < 1e-3
+        assert np.abs(alpha - ref_alpha).mean() < 5e-3 and np.abs(alpha - ref_alpha).max() < 0.15
+    return err

@@ -114,6 +114,13 @@ TWOSIDED_IMAGE_SCENES = {
 }
 
 
+# boundary cases (crop window, sphere transform composition, alpha channel); fixture boundary.npz
+BOUNDARY_IMAGE_SCENES = {
+    "crop": lambda: util.cropped_cornell(spp=4096),
+    "sphere_alpha": lambda: util.sphere_alpha_scene(spp=4096),
+}
+
+
 def load(name):
     path = os.path.join(HERE, "golden", name)
     if not os.path.exists(path):

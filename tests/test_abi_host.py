@@ -10,6 +10,7 @@ import numpy as np
 import pytest
 
 import mts_b200 as M
+from oracle_lib import OraclePath
 from mitsuba0_6_b200 import abi, hostmath as hm, scene as ms, scenes
 from mitsuba0_6_b200.scene import Plugin, Point, Spectrum
 
@@ -28,9 +29,11 @@ def test_header_and_binding_agree():
 
 @pytest.mark.parametrize("backend", ["cuda", "oracle"])
 def test_library_exports_every_declared_symbol(backend):
-    lib = ctypes.CDLL(abi.LIB_PATHS[backend])       # dlopen only: no CUDA call is made
+    import oracle_lib
+    path, prefix = {"cuda": (abi.CUDA_LIB_PATH, abi.CUDA_PREFIX), "oracle": (oracle_lib.ORACLE_LIB_PATH, oracle_lib.ORACLE_PREFIX)}[backend]
+    lib = ctypes.CDLL(path)       # dlopen only: no CUDA call is made
     for s in declared_symbols():
-        assert hasattr(lib, abi.PREFIX[backend] + s), s
+        assert hasattr(lib, prefix + s), s
 
 
 def test_struct_sizes_match_the_header(tmp_path):
@@ -52,7 +55,7 @@ def test_cuda_library_has_no_cpu_fallback():
     if torch.cuda.is_available():
         pytest.skip("a GPU is present")
     with pytest.raises(M.MtsError, match="no CUDA device|CPU fallback"):
-        M.CudaPath(scenes.cornell_box(8, 8, 1), backend="cuda")
+        M.CudaPath(scenes.cornell_box(8, 8, 1))
 
 
 def test_integrator_parameter_validation():
@@ -66,7 +69,7 @@ def test_integrator_parameter_validation():
         M.flatten(sc)
     sc.child("integrator").props.update(maxDepth=-1)
     assert M.flatten(sc).params["max_depth"] == -1
-    cpu = M.CudaPath(scenes.cornell_box(8, 8, 1), backend="oracle")
+    cpu = OraclePath(scenes.cornell_box(8, 8, 1))
     with pytest.raises(M.MtsError, match="rrDepth"):
         cpu.render(spp=1, rr_depth=0)
 
@@ -122,8 +125,8 @@ def test_xml_round_trip(tmp_path):
     f1, f2 = M.flatten(sc), M.flatten(sc2)
     assert f1.params == f2.params and f1.spp == f2.spp and len(f1.shapes) == len(f2.shapes)
     assert np.allclose(list(f1.camera.sample_to_camera), list(f2.camera.sample_to_camera))
-    a = M.CudaPath(f1, backend="oracle").render(spp=2, seed=1)
-    b = M.CudaPath(f2, backend="oracle").render(spp=2, seed=1)
+    a = OraclePath(f1).render(spp=2, seed=1)
+    b = OraclePath(f2).render(spp=2, seed=1)
     assert np.allclose(a, b, atol=1e-5)
 
 

@@ -314,7 +314,7 @@ def test_emitters_vs_reference(gzoo, gold):
 
 def test_sensor_and_film_vs_reference(gzoo, gold):
     GC.check_sensor_film(gzoo[0].ctx, gold, "zoo")
-    g = M.CudaPath(G.cornell_small(spp=1), backend="cuda")
+    g = M.CudaPath(G.cornell_small(spp=1))
     g.preprocess()
     GC.check_sensor_film(g.ctx, gold, "cornell")
     g.close()
@@ -326,8 +326,16 @@ def test_sensor_and_film_vs_reference(gzoo, gold):
 @pytest.mark.parametrize("name,spp,bar", [("cornell", 8192, 1e-3), ("terrain", 8192, 1e-3), ("zoo", 8192, 1.5e-2),
                                           ("spheres", 8192, 5e-3), ("caustics", 16384, 1e-2)])
 def test_render_vs_reference(gold_images, name, spp, bar):
-    g = M.CudaPath(G.IMAGE_SCENES[name](), backend="cuda")
+    g = M.CudaPath(G.IMAGE_SCENES[name]())
     err = GC.check_image(g, name, gold_images, spp, bar, lazy_shadow=True)
+    print("relMSE(%s, %d spp vs reference) = %.3g" % (name, spp, err))
+    g.close()
+
+
+@pytest.mark.parametrize("name,spp,bar", [("crop", 8192, 1e-3), ("sphere_alpha", 8192, 1e-3)])
+def test_boundary_cases_vs_reference(name, spp, bar):
+    g = M.CudaPath(G.BOUNDARY_IMAGE_SCENES[name]())
+    err = GC.check_boundary_image(g, name, G.load("boundary.npz"), spp, bar)
     print("relMSE(%s, %d spp vs reference) = %.3g" % (name, spp, err))
     g.close()
 
@@ -355,7 +363,7 @@ def test_twosided_bsdf_vs_reference(gtwosided, gold_twosided, name):
 
 @pytest.mark.parametrize("name,spp,bar", [("twosided", 8192, 3e-3), ("thin_hide", 8192, 5e-3)])
 def test_twosided_render_vs_reference(gold_twosided, name, spp, bar):
-    g = M.CudaPath(G.TWOSIDED_IMAGE_SCENES[name](), backend="cuda")
+    g = M.CudaPath(G.TWOSIDED_IMAGE_SCENES[name]())
     err = GC.check_image(g, name, gold_twosided, spp, bar, lazy_shadow=True)
     print("relMSE(%s, %d spp vs reference) = %.3g" % (name, spp, err))
     g.close()

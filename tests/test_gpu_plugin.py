@@ -53,6 +53,27 @@ def test_cudapath_plugin_next_row_bsdfs(name, bar):
 
 
 @needs_ref
+@pytest.mark.parametrize("name,bar", [("crop", 1.5e-3), ("sphere_alpha", 1.5e-3)])
+def test_cudapath_plugin_boundary_cases(name, bar):
+    # crop window (the block handed to Film::put sits at offset 0 of the window), Sphere `center` under a scaled
+    # toWorld, and the alpha channel of an rgba film -- all through the live reference objects
+    gold = G.load("boundary.npz")
+    sc = G.BOUNDARY_IMAGE_SCENES[name]()
+    rs = mtsref.RefScene(sc, integrator="cudapath")
+    film, alpha = rs.render(alpha=True)
+    img = M.develop(film)
+    ref = gold["image/%s/rgb" % name].astype(np.float32)
+    assert img.shape == ref.shape
+    err = M.rel_mse(img, ref)
+    print("cudapath.so inside the reference host: relMSE(%s) = %.3g" % (name, err))
+    assert abs(img.mean() / ref.mean() - 1) < 0.02 and err < bar, (name, err)
+    w = film[..., 3]
+    a = np.divide(alpha, w, out=np.zeros_like(w), where=w > 0)
+    ra = gold["image/%s/alpha" % name].astype(np.float32)
+    assert np.abs(a - ra).mean() < 5e-3, np.abs(a - ra).mean()
+
+
+@needs_ref
 def test_cudapath_plugin_parameter_errors():
     sc = G.cornell_small(spp=1)
     sc.child("integrator").props["rrDepth"] = 0

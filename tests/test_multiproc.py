@@ -11,6 +11,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 import mts_b200 as M
+from oracle_lib import OraclePath
 from mitsuba0_6_b200 import scenes, sharding
 
 SPP = 9   # odd on purpose: rank 0 gets 5, rank 1 gets 4
@@ -27,7 +28,7 @@ def _free_port():
 def _worker(rank, world, port, out):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), OMP_NUM_THREADS="2")
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    pt = M.CudaPath(scenes.cornell_box(48, 48, SPP), backend="oracle")
+    pt = OraclePath(scenes.cornell_box(48, 48, SPP))
     mine = sharding.render_sharded(pt, SPP, rank, world, seed=3)
     film = torch.from_numpy(mine.copy())
     sharding.reduce_film(film, dst=0)
@@ -59,6 +60,6 @@ def test_two_ranks_gloo(tmp_path):
     assert np.array_equal(reduced, parts[0] + parts[1])                     # the reduction is a plain sum of the films
     assert abs(parts[0][..., 3].sum() / (48 * 48) - 5) < 1e-3 and abs(parts[1][..., 3].sum() / (48 * 48) - 4) < 1e-3
     assert abs(reduced[..., 3].sum() / (48 * 48 * SPP) - 1) < 1e-4          # box filter: total weight = samples
-    single = M.CudaPath(scenes.cornell_box(48, 48, SPP), backend="oracle").render(spp=SPP, seed=11)
+    single = OraclePath(scenes.cornell_box(48, 48, SPP)).render(spp=SPP, seed=11)
     a, b = M.develop(reduced), M.develop(single)
     assert abs(a.mean() / b.mean() - 1) < 0.05                               # statistically the same image

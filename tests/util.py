@@ -3,6 +3,7 @@
 import numpy as np
 
 import mts_b200 as M
+from oracle_lib import OraclePath
 from mitsuba0_6_b200 import hostmath as hm, scenes
 from mitsuba0_6_b200.scene import Plugin, Point, Spectrum
 
@@ -145,7 +146,7 @@ def zoo_scene(width=64, height=48, spp=4, emitters=("area_rect", "area_sphere", 
 def make_pair(scene):
     """(cuda, oracle) CudaPath objects of the same flattened scene."""
     flat = M.flatten(scene)
-    gpu, cpu = M.CudaPath(flat, backend="cuda"), M.CudaPath(flat, backend="oracle")
+    gpu, cpu = M.CudaPath(flat), OraclePath(flat)
     gpu.preprocess()
     cpu.preprocess()
     return gpu, cpu, flat
@@ -256,3 +257,40 @@ def twosided_scene(width=96, height=64, spp=4, hide_env=False):
         env.data["bitmap"] = scenes.synthetic_envmap(128, 64)
         sc.add(env)
     return sc, z
+
+
+# ---- boundary cases of the plugin / host flattening -----------------------------------------
+def cropped_cornell(spp=4):
+    """Cornell box whose film renders a crop window (cropOffsetX/Y > 0): the crop is part of the camera's
+    sample-to-camera transform (perspective.cpp:140-160), block offsets are relative to the window."""
+    sc = scenes.cornell_box(96, 96, spp)
+    film = sc.child("sensor").child("film")
+    film.props.update(cropOffsetX=20, cropOffsetY=30, cropWidth=48, cropHeight=40)
+    return sc
+
+
+def sphere_alpha_scene(width=80, height=60, spp=4):
+    """Spheres with center != 0 under a scaled + rotated toWorld (sphere.cpp:108-121 composes toWorld * scale(1/r) *
+    translate(center)), no environment, an `rgba` film: the alpha channel is 1 where the camera ray hits something."""
+    sc = Plugin("scene", "")
+    sc.add(Plugin("integrator", "path", maxDepth=5))
+    s = Plugin("sensor", "perspective", toWorld=hm.look_at([0, 3, 9], [0, 1, 0], [0, 1, 0]), fov=45.0)
+    s.add(Plugin("sampler", "independent", sampleCount=spp))
+    film = Plugin("film", "hdrfilm", width=width, height=height, pixelFormat="rgba")
+    film.add(Plugin("rfilter", "gaussian"))
+    s.add(film)
+    sc.add(s)
+    floor = Plugin("shape", "rectangle", toWorld=hm.rotate([1, 0, 0], -90) @ hm.scale([4, 4, 1]))
+    floor.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.5)))
+    sc.add(floor)
+    tw = hm.translate([-1.0, 0.2, 0.5]) @ hm.rotate([0, 1, 0], 35) @ hm.rotate([0, 0, 1], 20) @ hm.scale(1.6)
+    a = Plugin("shape", "sphere", center=Point(1.2, 0.9, -0.4), radius=0.5, toWorld=tw)
+    a.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.7, 0.3, 0.2)))
+    sc.add(a)
+    b = Plugin("shape", "sphere", center=Point(-0.8, 0.5, 0.6), radius=0.3, toWorld=hm.translate([0.5, 0, 1.0]) @ hm.scale(2.0))
+    b.add(Plugin("bsdf", "roughconductor", distribution="ggx", alpha=0.2, **scenes.CU))
+    sc.add(b)
+    lt = Plugin("shape", "rectangle", toWorld=hm.translate([0, 6, 1]) @ hm.rotate([1, 0, 0], 90) @ hm.scale([1.2, 1.2, 1]))
+    lt.add(Plugin("emitter", "area", radiance=Spectrum(25, 23, 20)))
+    sc.add(lt)
+    return sc

@@ -18,7 +18,7 @@ def main():
     a = ap.parse_args()
     import mts_b200 as M
     sc, flat, kw, desc, gen_s = bench.build_scene(a.workload, a.spp)
-    gpu = M.CudaPath(flat, backend="cuda")
+    gpu = M.CudaPath(flat)
     gpu.preprocess()
     for i in range(a.renders):
         gpu.render(spp=a.spp, read_back=False, seed=i, wavefront_size=a.wavefront)
