@@ -206,7 +206,7 @@ def image_agreement(gpu_film, ref_film, gpu_spp, ref_spp, block=8):
     return {"value": M.rel_mse(block_mean(a, block), block_mean(b, block)), "block": block,
             "per_pixel": M.rel_mse(a, b), "mean_ratio": float(a.mean() / b.mean()),
             "gpu_spp": int(gpu_spp), "ref_spp": int(ref_spp),
-            "definition": "rel_mse (eps 1e-2, top 0.1% trimmed) of %dx%d-pixel block means, GPU render vs the reference's CPU `path` render of the same frame" % (block, block)}
+            "definition": "rel_mse (eps 1e-2, top 0.1%% trimmed) of %dx%d-pixel block means, GPU render vs the reference's CPU `path` render of the same frame" % (block, block)}
 
 
 class CpuArm:

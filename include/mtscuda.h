@@ -78,7 +78,12 @@ enum {
     MTS_BF_GGX = 1,            /* microfacet.h:48-56: 0 = Beckmann, 1 = GGX */
     MTS_BF_SAMPLE_VISIBLE = 2, /* microfacet.h sampleVisible */
     MTS_BF_NONLINEAR = 4,      /* plastic.cpp / roughplastic.cpp `nonlinear` */
-    MTS_BF_RT_2D = 8           /* roughplastic: alpha is textured -> 2-D rough-transmittance slice */
+    MTS_BF_RT_2D = 8,          /* roughplastic: alpha is textured -> 2-D rough-transmittance slice */
+    MTS_BF_RAY_DIFF = 16       /* BSDF::usesRayDifferentials() of this node as its configure() computes it (e.g.
+                                  diffuse.cpp:101, coating.cpp:172-174, blendbsdf.cpp:130, bumpmap.cpp:96).  Read on the ROOT
+                                  node of a shape's BSDF: Intersection::getBSDF(ray) computes the uv partials of a camera-ray
+                                  hit only then (include/mitsuba/render/records.inl:69-75), and with partials present every
+                                  ewa / trilinear texture of the tree is looked up filtered (src/librender/texture.cpp:104-114) */
 };
 
 /* BSDF lobe-type bits, same values as BSDF::EBSDFType (include/mitsuba/render/bsdf.h) */
@@ -153,7 +158,12 @@ typedef struct MtsBsdfNode {
 
 /* ---- textures (src/textures/bitmap.cpp, include/mitsuba/render/mipmap.h) ---- */
 enum { MTS_WRAP_REPEAT = 0, MTS_WRAP_MIRROR = 1, MTS_WRAP_CLAMP = 2, MTS_WRAP_ZERO = 3, MTS_WRAP_ONE = 4 };
-enum { MTS_FILTER_NEAREST = 0, MTS_FILTER_BILINEAR = 1 };
+/* EMIPFilterType (include/mitsuba/render/mipmap.h:53-62).  TRILINEAR and EWA make the library build the MIP pyramid
+ * (2-lobe Lanczos resampling of the float image, every level rounded to half; mipmap.h:238-262) and filter the
+ * lookups of camera-ray hits (TMIPMap::eval, mipmap.h:629-715; evalEWA :764-834); all other lookups are bilinear at
+ * level 0 (src/textures/bitmap.cpp:431-454). */
+enum { MTS_FILTER_NEAREST = 0, MTS_FILTER_BILINEAR = 1, MTS_FILTER_TRILINEAR = 2, MTS_FILTER_EWA = 3 };
+#define MTS_MAX_MIP_LEVELS 17 /* 65536 texels per side */
 
 typedef struct MtsTextureDesc {
     int32_t width, height;
@@ -162,6 +172,7 @@ typedef struct MtsTextureDesc {
     int32_t filter;         /* bitmap.cpp:431-454: unfiltered lookups are bilinear (or box for `nearest`) */
     float uv_scale[2];      /* Texture2D uscale/vscale, src/librender/texture.cpp:84-94 */
     float uv_offset[2];
+    float max_anisotropy;   /* bitmap.cpp:230-233: `maxAnisotropy` (default 20) for ewa, forced to 1 otherwise */
 } MtsTextureDesc;
 
 /* ---- sensor (src/sensors/perspective.cpp:126-178, 271-297) ------------------ */
@@ -225,6 +236,8 @@ typedef struct MtsRenderParams {
     int32_t clear_film;      /* 1: zero the film first (Scene::render does film->clear()) */
     int32_t wavefront_size;  /* path slots per wavefront; 0 = default */
     int32_t instrument;      /* 1: count BVH nodes visited / primitives tested (slower; never used for timing) */
+    int32_t sample_count;    /* Sampler::getSampleCount() of the whole job: camera-ray differentials are scaled by
+                                1/sqrt(sample_count) (src/librender/integrator.cpp:144-145, 181).  0 = spp * sample_stride */
 } MtsRenderParams;
 
 typedef struct MtsStats {
@@ -252,6 +265,11 @@ typedef struct MtsStats {
 typedef struct MtsContext MtsContext;
 
 /* ---- life cycle ---------------------------------------------------------- */
+/* Bumped whenever a struct or signature of this header changes.  A host compiled against another version would hand
+ * the library structs of the wrong size (MtsStats is written through a caller-provided pointer), so every binding
+ * compares MTS_FN(abi_version)() with the MTS_ABI_VERSION it was compiled with before the first call. */
+#define MTS_ABI_VERSION 4
+MTS_API int32_t MTS_FN(abi_version)(void);
 MTS_API const char *MTS_FN(last_error)(void);
 MTS_API int MTS_FN(create)(int device, MtsContext **out);
 MTS_API void MTS_FN(destroy)(MtsContext *ctx);
@@ -311,8 +329,9 @@ MTS_API int MTS_FN(trace)(MtsContext *ctx, int64_t n, const float *rays, int32_t
  * out: n*24 floats  p(3) t geoN(3) u shN(3) v dpdu(3) pad dpdv(3) pad wi(3) pad */
 MTS_API int MTS_FN(hit_records)(MtsContext *ctx, int64_t n, const float *rays, float *out, int32_t *ids);
 
-/* Surface context for BSDF queries: n*16 floats  uv(2) pad(2) dpdu(3) pad dpdv(3) pad shN(3) pad;
- * geometric normal = shading normal; shading frame = computeShadingFrame(shN, dpdu). */
+/* Surface context for BSDF queries: n*16 floats  uv(2) dudx dvdx dpdu(3) dudy dpdv(3) dvdy shN(3) hasUVPartials;
+ * geometric normal = shading normal; shading frame = computeShadingFrame(shN, dpdu).  The uv partials (slots 2, 3, 7, 11)
+ * are honoured when slot 15 is non-zero (Intersection::hasUVPartials); all zero = an unfiltered lookup. */
 /* BSDF::eval + BSDF::pdf.  wi, wo: n*3 local directions.  out_value: n*3, out_pdf: n. */
 MTS_API int MTS_FN(bsdf_eval_pdf)(MtsContext *ctx, int32_t bsdf, int64_t n, const float *surf, const float *wi,
                                   const float *wo, int32_t measure, float *out_value, float *out_pdf);
@@ -328,6 +347,21 @@ MTS_API int MTS_FN(sample_emitter_direct)(MtsContext *ctx, int64_t n, const floa
 /* Emitter::evalEnvironment (envmap.cpp:380-410, no differentials) and the solid-angle
  * pdf of Scene::pdfEmitterDirect for the environment emitter.  d: n*3.  out: n*4 value(3) pdf */
 MTS_API int MTS_FN(eval_environment)(MtsContext *ctx, int64_t n, const float *d, float *out);
+
+/* Texture2D::eval(its, filter = true) of bitmap texture `tex` (src/librender/texture.cpp:104-114 ->
+ * BitmapTexture::eval, src/textures/bitmap.cpp:431-454, 486-499 -> TMIPMap::eval / evalBilinear / evalBox).
+ * uv: n*2 surface uv (the texture's uscale/offset are applied like Texture2D does); duv: n*4 = dudx dvdx dudy dvdy, or
+ * NULL for lookups without partials.  out: n*3 */
+MTS_API int MTS_FN(texture_eval)(MtsContext *ctx, int32_t tex, int64_t n, const float *uv, const float *duv, float *out);
+
+/* Camera-ray hits with their uv partials: Sensor::sampleRayDifferential(sample_pos) + scaleDifferential(1/sqrt(
+ * sample_count)) + Scene::rayIntersect + Intersection::computePartials (src/librender/intersection.cpp:5-76).
+ * sample_pos: n*2 (pixel units).  out: n*8 floats  dudx dvdx dudy dvdy t hit(1/0) u v */
+MTS_API int MTS_FN(hit_partials)(MtsContext *ctx, int64_t n, const float *sample_pos, int32_t sample_count, float *out);
+
+/* Emitter::evalEnvironment(ray) for camera rays WITH differentials (envmap.cpp:380-410: EWA lookup, maxAnisotropy 10).
+ * sample_pos: n*2 (pixel units).  out: n*3 */
+MTS_API int MTS_FN(eval_environment_camera)(MtsContext *ctx, int64_t n, const float *sample_pos, int32_t sample_count, float *out);
 
 /* ImageBlock::put(pos, spec, alpha) for n samples into the (cleared) film. pos: n*2, value: n*3 */
 MTS_API int MTS_FN(splat)(MtsContext *ctx, int64_t n, const float *pos, const float *value, int32_t clear_first);

@@ -64,12 +64,16 @@ class CudaPath:
     def cancel(self):
         self._cancel.value = 1
 
-    def params(self, spp=None, seed=0, sample_offset=0, sample_stride=1, clear_film=True, wavefront_size=0, instrument=False, **over):
+    def params(self, spp=None, seed=0, sample_offset=0, sample_stride=1, clear_film=True, wavefront_size=0, instrument=False,
+               sample_count=0, **over):
+        """sample_count: Sampler::getSampleCount() of the whole job (scales the camera-ray differentials,
+        integrator.cpp:144-145); 0 = spp * sample_stride, i.e. this call renders the job alone or as one of `stride` ranks."""
         p = dict(self.flat.params)
         p.update(over)
         return abi.RenderParams(int(self.flat.spp if spp is None else spp), int(sample_offset), int(sample_stride),
                                 int(p["max_depth"]), int(p["rr_depth"]), int(p["strict_normals"]),
-                                int(p["hide_emitters"]), int(seed), int(clear_film), int(wavefront_size), int(instrument))
+                                int(p["hide_emitters"]), int(seed), int(clear_film), int(wavefront_size), int(instrument),
+                                int(sample_count))
 
     # Integrator::render -- returns the film as (H, W, 4) = sum w*RGB, sum w
     def render(self, spp=None, read_back=True, **kw):

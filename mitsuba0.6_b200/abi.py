@@ -19,7 +19,7 @@ EPSILON = 1e-4
 # ---- enums (mirror include/mtscuda.h) --------------------------------------
 BSDF_DIFFUSE, BSDF_CONDUCTOR, BSDF_ROUGHCONDUCTOR, BSDF_PLASTIC, BSDF_ROUGHPLASTIC, \
     BSDF_DIELECTRIC, BSDF_COATING, BSDF_BLEND, BSDF_BUMPMAP, BSDF_TWOSIDED, BSDF_THINDIELECTRIC, BSDF_MASK, BSDF_ROUGHDIELECTRIC = range(13)
-BF_GGX, BF_SAMPLE_VISIBLE, BF_NONLINEAR, BF_RT_2D = 1, 2, 4, 8
+BF_GGX, BF_SAMPLE_VISIBLE, BF_NONLINEAR, BF_RT_2D, BF_RAY_DIFF = 1, 2, 4, 8, 16
 ENULL, EDIFFUSE_REFLECTION, EDIFFUSE_TRANSMISSION, EGLOSSY_REFLECTION, EGLOSSY_TRANSMISSION, \
     EDELTA_REFLECTION, EDELTA_TRANSMISSION = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20, 0x40
 EFRONTSIDE = 0x08000
@@ -29,7 +29,7 @@ EDELTA = ENULL | EDELTA_REFLECTION | EDELTA_TRANSMISSION
 ETRANSMISSION = EDIFFUSE_TRANSMISSION | EGLOSSY_TRANSMISSION | EDELTA_TRANSMISSION | ENULL
 MEASURE_SOLID_ANGLE, MEASURE_DISCRETE = 1, 4
 WRAP = {"repeat": 0, "mirror": 1, "clamp": 2, "zero": 3, "one": 4}
-FILTER = {"nearest": 0, "bilinear": 1}
+FILTER = {"nearest": 0, "bilinear": 1, "trilinear": 2, "ewa": 3}
 EMITTER_AREA, EMITTER_POINT, EMITTER_ENVMAP = 0, 1, 2
 
 
@@ -47,7 +47,7 @@ class BsdfNode(C.Structure):
 class TextureDesc(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("channels", C.c_int32),
                 ("wrap_u", C.c_int32), ("wrap_v", C.c_int32), ("filter", C.c_int32),
-                ("uv_scale", C.c_float * 2), ("uv_offset", C.c_float * 2)]
+                ("uv_scale", C.c_float * 2), ("uv_offset", C.c_float * 2), ("max_anisotropy", C.c_float)]
 
 
 class Camera(C.Structure):
@@ -78,7 +78,7 @@ class RenderParams(C.Structure):
     _fields_ = [("spp", C.c_int32), ("sample_offset", C.c_int32), ("sample_stride", C.c_int32),
                 ("max_depth", C.c_int32), ("rr_depth", C.c_int32), ("strict_normals", C.c_int32),
                 ("hide_emitters", C.c_int32), ("seed", C.c_uint32), ("clear_film", C.c_int32),
-                ("wavefront_size", C.c_int32), ("instrument", C.c_int32)]
+                ("wavefront_size", C.c_int32), ("instrument", C.c_int32), ("sample_count", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -99,11 +99,12 @@ class Stats(C.Structure):
 
 
 # every symbol include/mtscuda.h declares (tests check that the libraries export all of them)
+ABI_VERSION = 4   # MTS_ABI_VERSION of include/mtscuda.h these mirrors were written against
 ABI_SYMBOLS = [
-    "last_error", "create", "destroy", "set_camera", "set_film", "add_texture", "set_float_pool",
+    "abi_version", "last_error", "create", "destroy", "set_camera", "set_film", "add_texture", "set_float_pool",
     "set_bsdfs", "add_mesh", "add_rectangle", "add_sphere", "add_emitter", "build", "render",
     "read_film", "read_film_alpha", "bind_film", "set_stream", "get_stats", "sample_rays", "trace", "hit_records", "bsdf_eval_pdf",
-    "bsdf_sample", "sample_emitter_direct", "eval_environment", "splat",
+    "bsdf_sample", "sample_emitter_direct", "eval_environment", "texture_eval", "hit_partials", "eval_environment_camera", "splat",
 ]
 
 # MTS_CUDA_LIB selects an experimental build of the same library (kernel tuning sweeps); never a different back end
@@ -130,6 +131,7 @@ def bind(path, prefix):
     fn = {}
     vp, i32, i64, fp = C.c_void_p, C.c_int32, C.c_int64, C.c_void_p
     sigs = {
+        "abi_version": (C.c_int32, []),
         "last_error": (C.c_char_p, []),
         "create": (C.c_int, [C.c_int, C.POINTER(vp)]),
         "destroy": (None, [vp]),
@@ -156,6 +158,9 @@ def bind(path, prefix):
         "bsdf_sample": (C.c_int, [vp, i32, i64, fp, fp, fp, fp]),
         "sample_emitter_direct": (C.c_int, [vp, i64, fp, fp, fp, fp]),
         "eval_environment": (C.c_int, [vp, i64, fp, fp]),
+        "texture_eval": (C.c_int, [vp, i32, i64, fp, fp, fp]),
+        "hit_partials": (C.c_int, [vp, i64, fp, i32, fp]),
+        "eval_environment_camera": (C.c_int, [vp, i64, fp, i32, fp]),
         "splat": (C.c_int, [vp, i64, fp, fp, i32]),
     }
     for name in ABI_SYMBOLS:
@@ -163,6 +168,9 @@ def bind(path, prefix):
         f.restype, f.argtypes = sigs[name]
         fn[name] = f
     lib._fn = fn
+    if fn["abi_version"]() != ABI_VERSION:
+        raise MtsError("%s implements ABI version %d, this binding was written for version %d -- rebuild the library"
+                       % (path, fn["abi_version"](), ABI_VERSION))
     lib._device_tangents = prefix == CUDA_PREFIX   # libmtscuda runs TriMesh::computeUVTangents on the device
     _libs[key] = lib
     return lib
@@ -341,6 +349,25 @@ class Context:
         dd = f32(d, (-1, 3))
         out = np.empty((dd.shape[0], 4), dtype=np.float32)
         self._check(self.fn["eval_environment"](self.h, dd.shape[0], ptr(dd), ptr(out)))
+        return out
+
+    def texture_eval(self, tex, uv, duv=None):
+        u = f32(uv, (-1, 2))
+        d = None if duv is None else f32(duv, (-1, 4))
+        out = np.empty((u.shape[0], 3), dtype=np.float32)
+        self._check(self.fn["texture_eval"](self.h, int(tex), u.shape[0], ptr(u), ptr(d), ptr(out)))
+        return out
+
+    def hit_partials(self, sample_pos, sample_count):
+        sp = f32(sample_pos, (-1, 2))
+        out = np.empty((sp.shape[0], 8), dtype=np.float32)
+        self._check(self.fn["hit_partials"](self.h, sp.shape[0], ptr(sp), int(sample_count), ptr(out)))
+        return out
+
+    def eval_environment_camera(self, sample_pos, sample_count):
+        sp = f32(sample_pos, (-1, 2))
+        out = np.empty((sp.shape[0], 3), dtype=np.float32)
+        self._check(self.fn["eval_environment_camera"](self.h, sp.shape[0], ptr(sp), int(sample_count), ptr(out)))
         return out
 
     def splat(self, pos, value, clear_first=True):

@@ -18,10 +18,20 @@ namespace mts {
 #define BSDF_NESTED_ATTR __noinline__
 #endif
 constexpr int kMaxBsdfDepth = BSDF_MAX_DEPTH;  // wrapper nesting levels supported above a leaf
+#define MTS_MIPMAP_LUT_SIZE 64   // include/mitsuba/render/mipmap.h:37
 
 // ---------------------------------------------------------------------------------------
-// Textures: TMIPMap level 0 (include/mitsuba/render/mipmap.h:503-626)
+// Textures: TMIPMap (include/mitsuba/render/mipmap.h:503-834)
 // ---------------------------------------------------------------------------------------
+// Where a texture is looked up: surface uv and, for camera-ray hits of BSDFs that use ray differentials, the uv partials
+// of Intersection::computePartials (dudx, dvdx, dudy, dvdy).  `filtered` = Intersection::hasUVPartials.
+struct TexCtx {
+    float2 uv;
+    float4 duv;
+    bool filtered;
+};
+DEVFN TexCtx texCtx(float2 uv) { TexCtx t; t.uv = uv; t.duv = make_float4(0, 0, 0, 0); t.filtered = false; return t; }
+
 // evalTexel coordinate handling (mipmap.h:503-563): returns the wrapped coordinate, or -1 / -2 when the lookup
 // yields the constant 0 / 1 (EZero / EOne boundary conditions)
 DEVFN int wrapCoord(int x, int size, int mode) {
@@ -34,21 +44,26 @@ DEVFN int wrapCoord(int x, int size, int mode) {
         default: return -2;
     }
 }
-// The four texels of a bilinear footprint.  Coordinates are wrapped once per row / column and all four loads are
-// issued back to back (one round trip to L2/HBM instead of four dependent ones).
+DEVFN float3 texelAt(const __half *base, int channels, size_t i) {
+    if (channels == 1) return f3(__half2float(__ldg(base + i)));
+    const uint2 raw = __ldg(reinterpret_cast<const uint2 *>(base) + i);
+    const float2 fa = __half22float2(*reinterpret_cast<const __half2 *>(&raw.x)), fb = __half22float2(*reinterpret_cast<const __half2 *>(&raw.y));
+    return f3(fa.x, fa.y, fb.x);
+}
+// The four texels of a bilinear footprint on one pyramid level.  Coordinates are wrapped once per row / column and
+// all four loads are issued back to back (one round trip to L2/HBM instead of four dependent ones).
 struct Quad { float3 p00, p10, p01, p11; };
-DEVFN Quad texQuad(const DTexture &t, int x0, int y0) {
-    const int xa = wrapCoord(x0, t.width, t.wrapU), xb = wrapCoord(x0 + 1, t.width, t.wrapU);
-    const int ya = wrapCoord(y0, t.height, t.wrapV), yb = wrapCoord(y0 + 1, t.height, t.wrapV);
+DEVFN Quad texQuad(const DTexture &t, const __half *base, int w, int h, int x0, int y0) {
+    const int xa = wrapCoord(x0, w, t.wrapU), xb = wrapCoord(x0 + 1, w, t.wrapU);
+    const int ya = wrapCoord(y0, h, t.wrapV), yb = wrapCoord(y0 + 1, h, t.wrapV);
     const int cxa = max(xa, 0), cxb = max(xb, 0), cya = max(ya, 0), cyb = max(yb, 0);
-    const size_t i00 = (size_t)cya * t.width + cxa, i10 = (size_t)cya * t.width + cxb,
-                 i01 = (size_t)cyb * t.width + cxa, i11 = (size_t)cyb * t.width + cxb;
+    const size_t i00 = (size_t)cya * w + cxa, i10 = (size_t)cya * w + cxb, i01 = (size_t)cyb * w + cxa, i11 = (size_t)cyb * w + cxb;
     Quad q;
     if (t.channels == 1) {
-        const __half h00 = __ldg(t.texels + i00), h10 = __ldg(t.texels + i10), h01 = __ldg(t.texels + i01), h11 = __ldg(t.texels + i11);
+        const __half h00 = __ldg(base + i00), h10 = __ldg(base + i10), h01 = __ldg(base + i01), h11 = __ldg(base + i11);
         q.p00 = f3(__half2float(h00)); q.p10 = f3(__half2float(h10)); q.p01 = f3(__half2float(h01)); q.p11 = f3(__half2float(h11));
     } else {
-        const uint2 *tx = reinterpret_cast<const uint2 *>(t.texels);
+        const uint2 *tx = reinterpret_cast<const uint2 *>(base);
         const uint2 r00 = __ldg(tx + i00), r10 = __ldg(tx + i10), r01 = __ldg(tx + i01), r11 = __ldg(tx + i11);
         auto cvt = [](uint2 raw) {
             float2 fa = __half22float2(*reinterpret_cast<const __half2 *>(&raw.x)), fb = __half22float2(*reinterpret_cast<const __half2 *>(&raw.y));
@@ -67,26 +82,40 @@ DEVFN Quad texQuad(const DTexture &t, int x0, int y0) {
     }
     return q;
 }
-DEVFN float3 texel(const DTexture &t, int x, int y) {
-    const int xa = wrapCoord(x, t.width, t.wrapU);
+// evalTexel(level, x, y), mipmap.h:503-563
+DEVFN float3 texel(const DTexture &t, const __half *base, int w, int h, int x, int y) {
+    const int xa = wrapCoord(x, w, t.wrapU);
     if (xa < 0) return f3(xa == -2 ? 1.0f : 0.0f);
-    const int ya = wrapCoord(y, t.height, t.wrapV);
+    const int ya = wrapCoord(y, h, t.wrapV);
     if (ya < 0) return f3(ya == -2 ? 1.0f : 0.0f);
-    size_t i = (size_t)ya * t.width + xa;
-    if (t.channels == 1) return f3(__half2float(__ldg(t.texels + i)));
-    uint2 raw = __ldg(reinterpret_cast<const uint2 *>(t.texels) + i);
-    float2 fa = __half22float2(*reinterpret_cast<__half2 *>(&raw.x)), fb = __half22float2(*reinterpret_cast<__half2 *>(&raw.y));
-    return f3(fa.x, fa.y, fb.x);
+    return texelAt(base, t.channels, (size_t)ya * w + xa);
 }
-// evalBilinear(0, uv) / evalBox(0, uv), mipmap.h:566-596
+DEVFN const __half *mipBase(const DTexture &t, int level) { return t.texels + (size_t)t.levelOffset[level] * (t.channels == 1 ? 1 : 4); }
+// evalBox(level, uv), mipmap.h:566-569
+DEVFN float3 mipBox(const DTexture &t, int level, float2 uv) {
+    const int w = t.levelW[level], h = t.levelH[level];
+    return texel(t, mipBase(t, level), w, h, floorToInt(uv.x * w), floorToInt(uv.y * h));
+}
+// evalBilinear(level, uv), mipmap.h:575-596
+DEVFN float3 mipBilinear(const DTexture &t, int level, float2 uv) {
+    if (!isfinite(uv.x) || !isfinite(uv.y)) return f3(0.0f);
+    if (level >= t.levels) return mipBox(t, t.levels - 1, uv);
+    const int w = t.levelW[level], h = t.levelH[level];
+    float u = uv.x * w - 0.5f, v = uv.y * h - 0.5f;
+    int xPos = floorToInt(u), yPos = floorToInt(v);
+    float dx1 = u - xPos, dx2 = 1.0f - dx1, dy1 = v - yPos, dy2 = 1.0f - dy1;
+    const Quad q = texQuad(t, mipBase(t, level), w, h, xPos, yPos);
+    return q.p00 * dx2 * dy2 + q.p01 * dx2 * dy1 + q.p10 * dx1 * dy2 + q.p11 * dx1 * dy1;
+}
+// evalBilinear(0, uv) / evalBox(0, uv): the unfiltered lookup of BitmapTexture::eval(uv) (bitmap.cpp:431-454)
 DEVFN float3 texLookup(const DTexture &t, float2 uv) {
     if (t.filter == MTS_FILTER_NEAREST)
-        return texel(t, floorToInt(uv.x * t.width), floorToInt(uv.y * t.height));
+        return texel(t, t.texels, t.width, t.height, floorToInt(uv.x * t.width), floorToInt(uv.y * t.height));
     if (!isfinite(uv.x) || !isfinite(uv.y)) return f3(0.0f);
     float u = uv.x * t.width - 0.5f, v = uv.y * t.height - 0.5f;
     int xPos = floorToInt(u), yPos = floorToInt(v);
     float dx1 = u - xPos, dx2 = 1.0f - dx1, dy1 = v - yPos, dy2 = 1.0f - dy1;
-    const Quad q = texQuad(t, xPos, yPos);
+    const Quad q = texQuad(t, t.texels, t.width, t.height, xPos, yPos);
     return q.p00 * dx2 * dy2 + q.p01 * dx2 * dy1 + q.p10 * dx1 * dy2 + q.p11 * dx1 * dy1;
 }
 // evalGradientBilinear(0, uv), mipmap.h:601-626
@@ -95,20 +124,94 @@ DEVFN void texGradient(const DTexture &t, float2 uv, float3 &g0, float3 &g1) {
     float u = uv.x * t.width - 0.5f, v = uv.y * t.height - 0.5f;
     int xPos = floorToInt(u), yPos = floorToInt(v);
     float dx = u - xPos, dy = v - yPos;
-    const Quad q = texQuad(t, xPos, yPos);
+    const Quad q = texQuad(t, t.texels, t.width, t.height, xPos, yPos);
     float3 tmp = q.p01 + q.p10 - q.p11;
     g0 = (q.p10 + q.p00 * (dy - 1) - tmp * dy) * (float)t.width;
     g1 = (q.p01 + q.p00 * (dx - 1) - tmp * dx) * (float)t.height;
 }
-// Texture2D::eval (src/librender/texture.cpp:104-114) + ScalingTexture (src/textures/scale.cpp:86-88)
-DEVFN float3 evalTex(const DScene &S, const MtsTexRef &r, float2 uv) {
+// evalEWA(level, uv, A, B, C), mipmap.h:764-834.  The running quadratic q is updated with separately rounded adds (no
+// FMA contraction) like the host code, because it indexes the weight table.
+static __device__ __noinline__ float3 mipEWA(const DTexture &t, int level, float2 uv, float A, float B, float C) {
+    if (!isfinite(A + B + C + uv.x + uv.y)) return f3(0.0f);
+    if (level >= t.levels) return mipBox(t, t.levels - 1, uv);
+    const int w = t.levelW[level], h = t.levelH[level];
+    const __half *base = mipBase(t, level);
+    const float u = uv.x * w - 0.5f, v = uv.y * h - 0.5f;
+    const float ratioX = (float)w / (float)t.width, ratioY = (float)h / (float)t.height;   // m_sizeRatio
+    A /= ratioX * ratioX; B /= ratioX * ratioY; C /= ratioY * ratioY;
+    const float invDet = 1.0f / (-B * B + 4.0f * A * C), deltaU = 2.0f * sqrtf(C * invDet), deltaV = 2.0f * sqrtf(A * invDet);
+    const int u0 = (int)ceilf(u - deltaU), u1 = floorToInt(u + deltaU), v0 = (int)ceilf(v - deltaV), v1 = floorToInt(v + deltaV);
+    const float As = A * MTS_MIPMAP_LUT_SIZE, Bs = B * MTS_MIPMAP_LUT_SIZE, Cs = C * MTS_MIPMAP_LUT_SIZE;
+    float3 result = f3(0.0f);
+    float denominator = 0.0f;
+    const float ddq = 2 * As, uu0 = (float)u0 - u;
+    for (int vt = v0; vt <= v1; ++vt) {
+        const float vv = (float)vt - v;
+        float q = __fadd_rn(__fmul_rn(__fmul_rn(As, uu0), uu0), __fmul_rn(__fadd_rn(__fmul_rn(Bs, uu0), __fmul_rn(Cs, vv)), vv));
+        float dq = __fadd_rn(__fmul_rn(As, __fadd_rn(__fmul_rn(2.0f, uu0), 1.0f)), __fmul_rn(Bs, vv));
+        for (int ut = u0; ut <= u1; ++ut) {
+            if (q < (float)MTS_MIPMAP_LUT_SIZE) {
+                const uint32_t qi = (uint32_t)q;
+                if (qi < MTS_MIPMAP_LUT_SIZE) {
+                    const float weight = __ldg(t.weightLut + (int)q);
+                    result += texel(t, base, w, h, ut, vt) * weight;
+                    denominator += weight;
+                }
+            }
+            q = __fadd_rn(q, dq);
+            dq = __fadd_rn(dq, ddq);
+        }
+    }
+    if (denominator == 0) return mipBilinear(t, level, uv);
+    return result / denominator;
+}
+// TMIPMap::eval(uv, d0, d1), mipmap.h:629-715: level selection, trilinear interpolation, anisotropy clamp, EWA
+static __device__ __noinline__ float3 mipEval(const DTexture &t, float2 uv, float2 d0, float2 d1) {
+    if (t.filter == MTS_FILTER_NEAREST) return mipBox(t, 0, uv);
+    if (t.filter == MTS_FILTER_BILINEAR) return mipBilinear(t, 0, uv);
+    const float du0 = d0.x * t.width, dv0 = d0.y * t.height, du1 = d1.x * t.width, dv1 = d1.y * t.height;
+    float A = dv0 * dv0 + dv1 * dv1, B = -2.0f * (du0 * dv0 + du1 * dv1), C = du0 * du0 + du1 * du1, F = A * C - B * B * 0.25f;
+    const float root = hypot2(A - C, B), Aprime = 0.5f * (A + C - root), Cprime = 0.5f * (A + C + root);
+    float majorRadius = Aprime != 0 ? sqrtf(F / Aprime) : 0, minorRadius = Cprime != 0 ? sqrtf(F / Cprime) : 0;
+    const float invLn2 = 1.4426950408889634f;   // math::log2 = fastlog * (1 / log 2), src/libcore/math.cpp:103-106
+    if (t.filter == MTS_FILTER_TRILINEAR || !(minorRadius > 0) || !(majorRadius > 0) || F < 0) {
+        const float level = fastlog(fmaxf(majorRadius, kEps)) * invLn2;
+        const int ilevel = floorToInt(level);
+        if (ilevel < 0) return mipBilinear(t, 0, uv);
+        const float a = level - ilevel;
+        return mipBilinear(t, ilevel, uv) * (1.0f - a) + mipBilinear(t, ilevel + 1, uv) * a;
+    }
+    if (minorRadius * t.maxAnisotropy < majorRadius) {
+        minorRadius = majorRadius / t.maxAnisotropy;
+        float sinTheta, cosTheta_;
+        sincosf(0.5f * atanf(B / (A - C)), &sinTheta, &cosTheta_);
+        const float a2 = majorRadius * majorRadius, b2 = minorRadius * minorRadius, sinTheta2 = sinTheta * sinTheta,
+                    cosTheta2_ = cosTheta_ * cosTheta_, sin2Theta = 2 * sinTheta * cosTheta_;
+        A = a2 * cosTheta2_ + b2 * sinTheta2;
+        B = (a2 - b2) * sin2Theta;
+        C = a2 * sinTheta2 + b2 * cosTheta2_;
+        F = a2 * b2;
+    }
+    const float scale = 1.0f / F;
+    A *= scale; B *= scale; C *= scale;
+    const float level = fmaxf(0.0f, fastlog(minorRadius) * invLn2);
+    const int ilevel = (int)level;
+    const float a = level - ilevel;
+    if (majorRadius < 1 || !(A > 0 && C > 0)) return mipBilinear(t, ilevel, uv);
+    return mipEWA(t, ilevel, uv, A, B, C) * (1.0f - a) + mipEWA(t, ilevel + 1, uv, A, B, C) * a;
+}
+// Texture2D::eval(its, filter = true) (src/librender/texture.cpp:104-114) + ScalingTexture (src/textures/scale.cpp:86-88)
+DEVFN float3 evalTex(const Mats S, const MtsTexRef &r, const TexCtx &tc) {
     float3 s = f3(r.scale[0], r.scale[1], r.scale[2]);
     if (r.tex < 0) return s;
     const DTexture &t = S.textures[r.tex];
-    return texLookup(t, make_float2(uv.x * t.uvScale.x + t.uvOffset.x, uv.y * t.uvScale.y + t.uvOffset.y)) * s;
+    const float2 uv = make_float2(tc.uv.x * t.uvScale.x + t.uvOffset.x, tc.uv.y * t.uvScale.y + t.uvOffset.y);
+    if (tc.filtered && t.filter >= MTS_FILTER_TRILINEAR)   // bitmap.cpp:486-499; nearest / bilinear ignore the partials (mipmap.h:630-633)
+        return mipEval(t, uv, make_float2(tc.duv.x * t.uvScale.x, tc.duv.y * t.uvScale.y), make_float2(tc.duv.z * t.uvScale.x, tc.duv.w * t.uvScale.y)) * s;
+    return texLookup(t, uv) * s;
 }
 // Texture2D::evalGradient (texture.cpp:116-124) + ScalingTexture::evalGradient (scale.cpp:90-94)
-DEVFN void evalTexGradient(const DScene &S, const MtsTexRef &r, float2 uv, float3 &g0, float3 &g1) {
+DEVFN void evalTexGradient(const Mats S, const MtsTexRef &r, float2 uv, float3 &g0, float3 &g1) {
     if (r.tex < 0) { g0 = g1 = f3(0.0f); return; }
     const DTexture &t = S.textures[r.tex];
     texGradient(t, make_float2(uv.x * t.uvScale.x + t.uvOffset.x, uv.y * t.uvScale.y + t.uvOffset.y), g0, g1);
@@ -310,7 +413,7 @@ DEVFN float cubicInterp2D(float px, float py, const float *values, int sx, int s
     return result;
 }
 // RoughTransmittance::eval on the host-reduced slices (src/bsdfs/rtrans.h:183-233)
-DEVFN float roughTransmittance(const DScene &S, const MtsBsdfNode &n, float ct, float alpha) {
+DEVFN float roughTransmittance(const Mats S, const MtsBsdfNode &n, float ct, float alpha) {
     if (!(ct >= 0)) return 0.f;
     float warpedCosTheta = sqrtf(sqrtf(fabsf(ct))), result;  // std::pow(x, 0.25)
     const float *tab = S.pool + n.lut[0];
@@ -322,7 +425,7 @@ DEVFN float roughTransmittance(const DScene &S, const MtsBsdfNode &n, float ct, 
     return fminf(1.0f, fmaxf(0.0f, result));
 }
 // 1 - m_internalRoughTransmittance->evalDiffuse(alpha)  (roughplastic.cpp:366, rtrans.h:249-285)
-DEVFN float roughInternalFdr(const DScene &S, const MtsBsdfNode &n, float alpha) {
+DEVFN float roughInternalFdr(const Mats S, const MtsBsdfNode &n, float alpha) {
     if (!(n.flags & MTS_BF_RT_2D)) return n.f[3];
     float warpedAlpha = sqrtf(sqrtf((alpha - n.f[0]) / (n.f[1] - n.f[0])));
     float r = cubicInterp1D(warpedAlpha, S.pool + n.lut[3], n.lut[2]);
@@ -337,12 +440,22 @@ DEVFN float3 nodeEta(const MtsBsdfNode &n) { return f3(n.eta[0], n.eta[1], n.eta
 DEVFN float3 nodeK(const MtsBsdfNode &n) { return f3(n.k[0], n.k[1], n.k[2]); }
 
 struct BSample { float3 wo; float pdf; float eta; uint32_t type; float u3; };   // u3: input, the extra number of EUsesSampler models
-// RoughDielectric keeps its fourth texture (specularTransmittance) in the k/lut slots (include/mtscuda.h)
+
+// The texture parameters of one leaf model at one hit (slot use: include/mtscuda.h), looked up ONCE per hit and leaf:
+// eval, pdf and sample of a bounce share them (the reference's lazy per-call Texture::eval returns the same values).
+// c3 = roughdielectric's specularTransmittance, kept in the k / lut slots of the node.
+struct LeafTex { float3 c0, c1, c2, c3; };
 DEVFN MtsTexRef roughDielTransmittance(const MtsBsdfNode &n) { MtsTexRef r; r.scale[0] = n.k[0]; r.scale[1] = n.k[1]; r.scale[2] = n.k[2]; r.tex = n.lut[0]; return r; }
+DEVFN LeafTex resolveLeaf(const Mats S, const MtsBsdfNode &n, const TexCtx &tc) {
+    LeafTex lt;
+    lt.c0 = evalTex(S, n.t0, tc); lt.c1 = evalTex(S, n.t1, tc); lt.c2 = evalTex(S, n.t2, tc);
+    lt.c3 = n.type == MTS_BSDF_ROUGHDIELECTRIC ? evalTex(S, roughDielTransmittance(n), tc) : f3(0.0f);
+    return lt;
+}
 
 // RoughDielectric (src/bsdfs/roughdielectric.cpp) in functions of its own: the three leaf switches below stay as small
 // as they were (inlined into them the model cost every material 6 percent of shade time: registers, instruction cache)
-__device__ __noinline__ float3 roughDielEval(const DScene &S, const MtsBsdfNode &n, float2 uv, float3 wi, float3 wo) {  // :272-348
+static __device__ __noinline__ float3 roughDielEval(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float3 wo) {  // :272-348
     if (cosTheta(wi) == 0) return f3(0.0f);
     const float eta = n.eta[0], invEta = 1 / eta;
     const bool reflect = cosTheta(wi) * cosTheta(wo) > 0;
@@ -350,19 +463,19 @@ __device__ __noinline__ float3 roughDielEval(const DScene &S, const MtsBsdfNode 
     if (reflect) H = normalize(wo + wi);
     else H = normalize(wi + wo * (cosTheta(wi) > 0 ? eta : invEta));
     H = H * signum(cosTheta(H));
-    Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+    Microfacet distr(n.flags & MTS_BF_GGX, average(lt.c1), average(lt.c2), n.flags & MTS_BF_SAMPLE_VISIBLE);
     const float D = distr.eval(H);
     if (D == 0) return f3(0.0f);
     const float F = fresnelDielectricExt(dot(wi, H), eta);
     const float G = distr.G(wi, wo, H);
-    if (reflect) return evalTex(S, n.t0, uv) * (F * D * G / (4.0f * fabsf(cosTheta(wi))));
+    if (reflect) return lt.c0 * (F * D * G / (4.0f * fabsf(cosTheta(wi))));
     const float e = cosTheta(wi) > 0.0f ? eta : invEta;
     const float sqrtDenom = dot(wi, H) + e * dot(wo, H);
     const float value = ((1 - F) * D * G * e * e * dot(wi, H) * dot(wo, H)) / (cosTheta(wi) * sqrtDenom * sqrtDenom);
     const float factor = cosTheta(wi) > 0 ? invEta : eta;   // ERadiance
-    return evalTex(S, roughDielTransmittance(n), uv) * fabsf(value * factor * factor);
+    return lt.c3 * fabsf(value * factor * factor);
 }
-__device__ __noinline__ float roughDielPdf(const DScene &S, const MtsBsdfNode &n, float2 uv, float3 wi, float3 wo) {  // :350-420
+static __device__ __noinline__ float roughDielPdf(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float3 wo) {  // :350-420
     const float eta = n.eta[0], invEta = 1 / eta;
     const bool reflect = cosTheta(wi) * cosTheta(wo) > 0;
     float3 H; float dwh_dwo;
@@ -376,16 +489,16 @@ __device__ __noinline__ float roughDielPdf(const DScene &S, const MtsBsdfNode &n
         dwh_dwo = (e * e * dot(wo, H)) / (sqrtDenom * sqrtDenom);
     }
     H = H * signum(cosTheta(H));
-    Microfacet sampleDistr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+    Microfacet sampleDistr(n.flags & MTS_BF_GGX, average(lt.c1), average(lt.c2), n.flags & MTS_BF_SAMPLE_VISIBLE);
     if (!sampleDistr.sampleVisible) sampleDistr.scaleAlpha(1.2f - 0.2f * sqrtf(fabsf(cosTheta(wi))));
     float prob = sampleDistr.pdf(wi * signum(cosTheta(wi)), H);
     const float F = fresnelDielectricExt(dot(wi, H), eta);
     prob *= reflect ? F : (1 - F);
     return fabsf(prob * dwh_dwo);
 }
-__device__ __noinline__ float3 roughDielSample(const DScene &S, const MtsBsdfNode &n, float2 uv, float3 wi, float2 sample, BSample &o) {  // :517-616
+static __device__ __noinline__ float3 roughDielSample(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float2 sample, BSample &o) {  // :517-616
     const float eta = n.eta[0], invEta = 1 / eta;
-    Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+    Microfacet distr(n.flags & MTS_BF_GGX, average(lt.c1), average(lt.c2), n.flags & MTS_BF_SAMPLE_VISIBLE);
     Microfacet sampleDistr = distr;
     if (!distr.sampleVisible) sampleDistr.scaleAlpha(1.2f - 0.2f * sqrtf(fabsf(cosTheta(wi))));
     float microfacetPDF;
@@ -401,7 +514,7 @@ __device__ __noinline__ float3 roughDielSample(const DScene &S, const MtsBsdfNod
     if (sampleReflection) {
         o.wo = reflectM(wi, m); o.eta = 1.0f; o.type = MTS_EGLOSSY_REFLECTION;
         if (cosTheta(wi) * cosTheta(o.wo) <= 0) return f3(0.0f);
-        weight *= evalTex(S, n.t0, uv);
+        weight *= lt.c0;
         dwh_dwo = 1.0f / (4.0f * dot(o.wo, m));
     } else {
         if (cosThetaT == 0) return f3(0.0f);
@@ -410,7 +523,7 @@ __device__ __noinline__ float3 roughDielSample(const DScene &S, const MtsBsdfNod
         o.eta = cosThetaT < 0 ? eta : invEta; o.type = MTS_EGLOSSY_TRANSMISSION;
         if (cosTheta(wi) * cosTheta(o.wo) >= 0) return f3(0.0f);
         const float factor = cosThetaT < 0 ? invEta : eta;   // ERadiance
-        weight *= evalTex(S, roughDielTransmittance(n), uv) * (factor * factor);
+        weight *= lt.c3 * (factor * factor);
         const float sqrtDenom = dot(wi, m) + o.eta * dot(o.wo, m);
         dwh_dwo = (o.eta * o.eta * dot(o.wo, m)) / (sqrtDenom * sqrtDenom);
     }
@@ -423,22 +536,64 @@ __device__ __noinline__ float3 roughDielSample(const DScene &S, const MtsBsdfNod
 // ---------------------------------------------------------------------------------------
 // leaf models
 // ---------------------------------------------------------------------------------------
-__device__ __noinline__ float3 leafEval(const DScene &S, const MtsBsdfNode &n, float2 uv, float3 wi, float3 wo, int measure) {
+// RoughPlastic::eval / pdf in the solid angle measure (src/bsdfs/roughplastic.cpp:326-382, 384-437); inlined into the leaf
+// switches AND into roughplastic's sample(), which returns eval / pdf of the sampled direction (:494-500)
+DEVFN float3 roughPlasticEval(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float3 wo) {
+    if (cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return f3(0.0f);
+    float eta = n.eta[0];
+    float a = average(lt.c2);
+    Microfacet distr(n.flags & MTS_BF_GGX, a, a, n.flags & MTS_BF_SAMPLE_VISIBLE);
+    float3 result = f3(0.0f);
+    {
+        const float3 H = normalize(wo + wi);
+        const float D = distr.eval(H);
+        const float F = fresnelDielectricExt(dot(wi, H), eta);
+        const float G = distr.G(wi, wo, H);
+        float value = F * D * G / (4.0f * cosTheta(wi));
+        result += lt.c1 * value;
+    }
+    {
+        float3 diff = lt.c0;
+        float T12 = roughTransmittance(S, n, cosTheta(wi), distr.alphaU);
+        float T21 = roughTransmittance(S, n, cosTheta(wo), distr.alphaU);
+        float Fdr = roughInternalFdr(S, n, distr.alphaU);
+        if (n.flags & MTS_BF_NONLINEAR) diff = diff / (f3(1.0f) - diff * Fdr); else diff = diff / (1 - Fdr);
+        float invEta2 = 1.0f / (eta * eta);
+        result += diff * (kInvPi * cosTheta(wo) * T12 * T21 * invEta2);
+    }
+    return result;
+}
+DEVFN float roughPlasticPdf(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float3 wo) {
+    if (cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return 0.0f;
+    float a = average(lt.c2);
+    Microfacet distr(n.flags & MTS_BF_GGX, a, a, n.flags & MTS_BF_SAMPLE_VISIBLE);
+    const float3 H = normalize(wo + wi);
+    float w = n.f[2];
+    float probSpecular = 1 - roughTransmittance(S, n, cosTheta(wi), distr.alphaU);
+    probSpecular = (probSpecular * w) / (probSpecular * w + (1 - probSpecular) * (1 - w));
+    float probDiffuse = 1 - probSpecular;
+    const float dwh_dwo = 1.0f / (4.0f * dot(wo, H));
+    const float prob = distr.pdf(wi, H);
+    float result = prob * dwh_dwo * probSpecular;
+    result += probDiffuse * squareToCosineHemispherePdf(wo);
+    return result;
+}
+DEVFN float3 leafEvalImpl(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float3 wo, int measure) {
     const bool solid = measure == MTS_MEASURE_SOLID_ANGLE, discrete = measure == MTS_MEASURE_DISCRETE;
     switch (n.type) {
     case MTS_BSDF_DIFFUSE:  // src/bsdfs/diffuse.cpp:110-118
         if (!solid || cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return f3(0.0f);
-        return evalTex(S, n.t0, uv) * (kInvPi * cosTheta(wo));
+        return lt.c0 * (kInvPi * cosTheta(wo));
     case MTS_BSDF_CONDUCTOR:  // conductor.cpp:223-237
         if (!discrete || cosTheta(wi) <= 0 || cosTheta(wo) <= 0 || fabsf(dot(reflectZ(wi), wo) - 1) > kDeltaEps) return f3(0.0f);
-        return evalTex(S, n.t0, uv) * fresnelConductorExact(cosTheta(wi), nodeEta(n), nodeK(n));
+        return lt.c0 * fresnelConductorExact(cosTheta(wi), nodeEta(n), nodeK(n));
     case MTS_BSDF_ROUGHCONDUCTOR: {  // roughconductor.cpp:257-294
         if (!solid || cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return f3(0.0f);
         float3 H = normalize(wo + wi);
-        Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+        Microfacet distr(n.flags & MTS_BF_GGX, average(lt.c1), average(lt.c2), n.flags & MTS_BF_SAMPLE_VISIBLE);
         const float D = distr.eval(H);
         if (D == 0) return f3(0.0f);
-        const float3 F = fresnelConductorExact(dot(wi, H), nodeEta(n), nodeK(n)) * evalTex(S, n.t0, uv);
+        const float3 F = fresnelConductorExact(dot(wi, H), nodeEta(n), nodeK(n)) * lt.c0;
         const float G = distr.G(wi, wo, H);
         float model = D * G / (4.0f * cosTheta(wi));
         return F * model;
@@ -448,73 +603,49 @@ __device__ __noinline__ float3 leafEval(const DScene &S, const MtsBsdfNode &n, f
         float eta = n.eta[0];
         float Fi = fresnelDielectricExt(cosTheta(wi), eta);
         if (discrete) {
-            if (fabsf(dot(reflectZ(wi), wo) - 1) < kDeltaEps) return evalTex(S, n.t1, uv) * Fi;
+            if (fabsf(dot(reflectZ(wi), wo) - 1) < kDeltaEps) return lt.c1 * Fi;
         } else if (solid) {
             float Fo = fresnelDielectricExt(cosTheta(wo), eta);
-            float3 diff = evalTex(S, n.t0, uv);
+            float3 diff = lt.c0;
             if (n.flags & MTS_BF_NONLINEAR) diff = diff / (f3(1.0f) - diff * n.f[0]); else diff = diff / (1 - n.f[0]);
             float invEta2 = 1 / (eta * eta);
             return diff * (squareToCosineHemispherePdf(wo) * invEta2 * (1 - Fi) * (1 - Fo));
         }
         return f3(0.0f);
     }
-    case MTS_BSDF_ROUGHPLASTIC: {  // roughplastic.cpp:326-382
-        if (!solid || cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return f3(0.0f);
-        float eta = n.eta[0];
-        float a = average(evalTex(S, n.t2, uv));
-        Microfacet distr(n.flags & MTS_BF_GGX, a, a, n.flags & MTS_BF_SAMPLE_VISIBLE);
-        float3 result = f3(0.0f);
-        {
-            const float3 H = normalize(wo + wi);
-            const float D = distr.eval(H);
-            const float F = fresnelDielectricExt(dot(wi, H), eta);
-            const float G = distr.G(wi, wo, H);
-            float value = F * D * G / (4.0f * cosTheta(wi));
-            result += evalTex(S, n.t1, uv) * value;
-        }
-        {
-            float3 diff = evalTex(S, n.t0, uv);
-            float T12 = roughTransmittance(S, n, cosTheta(wi), distr.alphaU);
-            float T21 = roughTransmittance(S, n, cosTheta(wo), distr.alphaU);
-            float Fdr = roughInternalFdr(S, n, distr.alphaU);
-            if (n.flags & MTS_BF_NONLINEAR) diff = diff / (f3(1.0f) - diff * Fdr); else diff = diff / (1 - Fdr);
-            float invEta2 = 1.0f / (eta * eta);
-            result += diff * (kInvPi * cosTheta(wo) * T12 * T21 * invEta2);
-        }
-        return result;
-    }
+    case MTS_BSDF_ROUGHPLASTIC: return solid ? roughPlasticEval(S, n, lt, wi, wo) : f3(0.0f);
     case MTS_BSDF_DIELECTRIC: {  // dielectric.cpp:228-253
         float eta = n.eta[0], invEta = 1 / eta;
         float cosThetaT;
         float F = fresnelDielectricExt(cosTheta(wi), cosThetaT, eta);
         if (cosTheta(wi) * cosTheta(wo) >= 0) {
             if (!discrete || fabsf(dot(reflectZ(wi), wo) - 1) > kDeltaEps) return f3(0.0f);
-            return evalTex(S, n.t0, uv) * F;
+            return lt.c0 * F;
         } else {
             float scale = -(cosThetaT < 0 ? invEta : eta);
             float3 refr = f3(scale * wi.x, scale * wi.y, cosThetaT);
             if (!discrete || fabsf(dot(refr, wo) - 1) > kDeltaEps) return f3(0.0f);
             float factor = cosThetaT < 0 ? invEta : eta;  // ERadiance
-            return evalTex(S, n.t1, uv) * factor * factor * (1 - F);
+            return lt.c1 * factor * factor * (1 - F);
         }
     }
-    case MTS_BSDF_ROUGHDIELECTRIC: return solid ? roughDielEval(S, n, uv, wi, wo) : f3(0.0f);
+    case MTS_BSDF_ROUGHDIELECTRIC: return solid ? roughDielEval(S, n, lt, wi, wo) : f3(0.0f);
     case MTS_BSDF_THINDIELECTRIC: {  // thindielectric.cpp:145-166
         float R = fresnelDielectricExt(fabsf(cosTheta(wi)), n.eta[0]), T = 1 - R;
         if (R < 1) R += T * T * R / (1 - R * R);   // internal reflections: R' = R + TRT + TR^3T + ..
         if (cosTheta(wi) * cosTheta(wo) >= 0) {
             if (!discrete || fabsf(dot(reflectZ(wi), wo) - 1) > kDeltaEps) return f3(0.0f);
-            return evalTex(S, n.t0, uv) * R;
+            return lt.c0 * R;
         } else {
             if (!discrete || fabsf(dot(-wi, wo) - 1) > kDeltaEps) return f3(0.0f);
-            return evalTex(S, n.t1, uv) * (1 - R);
+            return lt.c1 * (1 - R);
         }
     }
     }
     return f3(0.0f);
 }
 
-__device__ __noinline__ float leafPdf(const DScene &S, const MtsBsdfNode &n, float2 uv, float3 wi, float3 wo, int measure) {
+DEVFN float leafPdfImpl(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float3 wo, int measure) {
     const bool solid = measure == MTS_MEASURE_SOLID_ANGLE, discrete = measure == MTS_MEASURE_DISCRETE;
     switch (n.type) {
     case MTS_BSDF_DIFFUSE:  // diffuse.cpp:120-127
@@ -526,7 +657,7 @@ __device__ __noinline__ float leafPdf(const DScene &S, const MtsBsdfNode &n, flo
     case MTS_BSDF_ROUGHCONDUCTOR: {  // roughconductor.cpp:296-321
         if (!solid || cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return 0.0f;
         float3 H = normalize(wo + wi);
-        Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+        Microfacet distr(n.flags & MTS_BF_GGX, average(lt.c1), average(lt.c2), n.flags & MTS_BF_SAMPLE_VISIBLE);
         if (distr.sampleVisible) return distr.eval(H) * distr.smithG1(wi, H) / (4.0f * cosTheta(wi));
         return distr.pdf(wi, H) / (4 * absDot(wo, H));
     }
@@ -540,21 +671,7 @@ __device__ __noinline__ float leafPdf(const DScene &S, const MtsBsdfNode &n, flo
         } else if (solid) return squareToCosineHemispherePdf(wo) * (1 - probSpecular);
         return 0.0f;
     }
-    case MTS_BSDF_ROUGHPLASTIC: {  // roughplastic.cpp:384-437
-        if (!solid || cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return 0.0f;
-        float a = average(evalTex(S, n.t2, uv));
-        Microfacet distr(n.flags & MTS_BF_GGX, a, a, n.flags & MTS_BF_SAMPLE_VISIBLE);
-        const float3 H = normalize(wo + wi);
-        float w = n.f[2];
-        float probSpecular = 1 - roughTransmittance(S, n, cosTheta(wi), distr.alphaU);
-        probSpecular = (probSpecular * w) / (probSpecular * w + (1 - probSpecular) * (1 - w));
-        float probDiffuse = 1 - probSpecular;
-        const float dwh_dwo = 1.0f / (4.0f * dot(wo, H));
-        const float prob = distr.pdf(wi, H);
-        float result = prob * dwh_dwo * probSpecular;
-        result += probDiffuse * squareToCosineHemispherePdf(wo);
-        return result;
-    }
+    case MTS_BSDF_ROUGHPLASTIC: return solid ? roughPlasticPdf(S, n, lt, wi, wo) : 0.0f;
     case MTS_BSDF_DIELECTRIC: {  // dielectric.cpp:255-275
         float eta = n.eta[0], invEta = 1 / eta;
         float cosThetaT;
@@ -569,7 +686,7 @@ __device__ __noinline__ float leafPdf(const DScene &S, const MtsBsdfNode &n, flo
             return 1 - F;
         }
     }
-    case MTS_BSDF_ROUGHDIELECTRIC: return solid ? roughDielPdf(S, n, uv, wi, wo) : 0.0f;
+    case MTS_BSDF_ROUGHDIELECTRIC: return solid ? roughDielPdf(S, n, lt, wi, wo) : 0.0f;
     case MTS_BSDF_THINDIELECTRIC: {  // thindielectric.cpp:168-189
         float R = fresnelDielectricExt(fabsf(cosTheta(wi)), n.eta[0]), T = 1 - R;
         if (R < 1) R += T * T * R / (1 - R * R);
@@ -585,28 +702,42 @@ __device__ __noinline__ float leafPdf(const DScene &S, const MtsBsdfNode &n, flo
     return 0.0f;
 }
 
-__device__ __noinline__ float3 leafSample(const DScene &S, const MtsBsdfNode &n, float2 uv, float3 wi, float2 sample, BSample &o) {
+// Entry points.  The bodies above are force-inlined into each of them, so that the fused eval + pdf of the light-sampling
+// step (and roughplastic's sample, which returns eval / pdf) computes the shared terms -- half vector, D, G, Fresnel,
+// rough-transmittance lookups -- once.
+static __device__ __noinline__ float3 leafEval(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float3 wo, int measure) {
+    return leafEvalImpl(S, n, lt, wi, wo, measure);
+}
+static __device__ __noinline__ float leafPdf(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float3 wo, int measure) {
+    return leafPdfImpl(S, n, lt, wi, wo, measure);
+}
+static __device__ __noinline__ float3 leafEvalPdf(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float3 wo, int measure, float &pdf) {
+    pdf = leafPdfImpl(S, n, lt, wi, wo, measure);
+    return leafEvalImpl(S, n, lt, wi, wo, measure);
+}
+
+static __device__ __noinline__ float3 leafSample(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float2 sample, BSample &o) {
     switch (n.type) {
     case MTS_BSDF_DIFFUSE:  // diffuse.cpp:141-150
         if (cosTheta(wi) <= 0) return f3(0.0f);
         o.wo = squareToCosineHemisphere(sample);
         o.eta = 1.0f; o.type = MTS_EDIFFUSE_REFLECTION;
         o.pdf = squareToCosineHemispherePdf(o.wo);
-        return evalTex(S, n.t0, uv);
+        return lt.c0;
     case MTS_BSDF_CONDUCTOR:  // conductor.cpp:270-286
         if (cosTheta(wi) <= 0) return f3(0.0f);
         o.type = MTS_EDELTA_REFLECTION; o.wo = reflectZ(wi); o.eta = 1.0f; o.pdf = 1;
-        return evalTex(S, n.t0, uv) * fresnelConductorExact(cosTheta(wi), nodeEta(n), nodeK(n));
+        return lt.c0 * fresnelConductorExact(cosTheta(wi), nodeEta(n), nodeK(n));
     case MTS_BSDF_ROUGHCONDUCTOR: {  // roughconductor.cpp:368-410
         if (cosTheta(wi) < 0) return f3(0.0f);
-        Microfacet distr(n.flags & MTS_BF_GGX, average(evalTex(S, n.t1, uv)), average(evalTex(S, n.t2, uv)), n.flags & MTS_BF_SAMPLE_VISIBLE);
+        Microfacet distr(n.flags & MTS_BF_GGX, average(lt.c1), average(lt.c2), n.flags & MTS_BF_SAMPLE_VISIBLE);
         float pdf;
         float3 m = distr.sample(wi, sample, pdf);
         o.pdf = pdf;
         if (pdf == 0) return f3(0.0f);
         o.wo = reflectM(wi, m); o.eta = 1.0f; o.type = MTS_EGLOSSY_REFLECTION;
         if (cosTheta(o.wo) <= 0) return f3(0.0f);
-        float3 F = fresnelConductorExact(dot(wi, m), nodeEta(n), nodeK(n)) * evalTex(S, n.t0, uv);
+        float3 F = fresnelConductorExact(dot(wi, m), nodeEta(n), nodeK(n)) * lt.c0;
         float weight;
         if (distr.sampleVisible) weight = distr.smithG1(o.wo, m);
         else weight = distr.eval(m) * distr.G(wi, o.wo, m) * dot(wi, m) / (pdf * cosTheta(wi));
@@ -622,12 +753,12 @@ __device__ __noinline__ float3 leafSample(const DScene &S, const MtsBsdfNode &n,
         float probSpecular = (Fi * w) / (Fi * w + (1 - Fi) * (1 - w));
         if (sample.x < probSpecular) {
             o.type = MTS_EDELTA_REFLECTION; o.wo = reflectZ(wi); o.pdf = probSpecular;
-            return evalTex(S, n.t1, uv) * Fi / probSpecular;
+            return lt.c1 * Fi / probSpecular;
         }
         o.type = MTS_EDIFFUSE_REFLECTION;
         o.wo = squareToCosineHemisphere(make_float2((sample.x - probSpecular) / (1 - probSpecular), sample.y));
         float Fo = fresnelDielectricExt(cosTheta(o.wo), eta);
-        float3 diff = evalTex(S, n.t0, uv);
+        float3 diff = lt.c0;
         if (n.flags & MTS_BF_NONLINEAR) diff = diff / (f3(1.0f) - diff * n.f[0]); else diff = diff / (1 - n.f[0]);
         o.pdf = (1 - probSpecular) * squareToCosineHemispherePdf(o.wo);
         float invEta2 = 1 / (eta * eta);
@@ -636,7 +767,7 @@ __device__ __noinline__ float3 leafSample(const DScene &S, const MtsBsdfNode &n,
     case MTS_BSDF_ROUGHPLASTIC: {  // roughplastic.cpp:439-501
         if (cosTheta(wi) <= 0) return f3(0.0f);
         bool choseSpecular = true;
-        float a = average(evalTex(S, n.t2, uv));
+        float a = average(lt.c2);
         Microfacet distr(n.flags & MTS_BF_GGX, a, a, n.flags & MTS_BF_SAMPLE_VISIBLE);
         float w = n.f[2];
         float probSpecular = 1 - roughTransmittance(S, n, cosTheta(wi), distr.alphaU);
@@ -653,9 +784,9 @@ __device__ __noinline__ float3 leafSample(const DScene &S, const MtsBsdfNode &n,
             o.wo = squareToCosineHemisphere(sample);
         }
         o.eta = 1.0f;
-        o.pdf = leafPdf(S, n, uv, wi, o.wo, MTS_MEASURE_SOLID_ANGLE);
+        o.pdf = roughPlasticPdf(S, n, lt, wi, o.wo);   // roughplastic.cpp:494-500: pdf() and eval() / pdf, solid angle measure
         if (o.pdf == 0) return f3(0.0f);
-        return leafEval(S, n, uv, wi, o.wo, MTS_MEASURE_SOLID_ANGLE) / o.pdf;
+        return roughPlasticEval(S, n, lt, wi, o.wo) / o.pdf;
     }
     case MTS_BSDF_DIELECTRIC: {  // dielectric.cpp:277-299
         float eta = n.eta[0], invEta = 1 / eta;
@@ -663,7 +794,7 @@ __device__ __noinline__ float3 leafSample(const DScene &S, const MtsBsdfNode &n,
         float F = fresnelDielectricExt(cosTheta(wi), cosThetaT, eta);
         if (sample.x <= F) {
             o.type = MTS_EDELTA_REFLECTION; o.wo = reflectZ(wi); o.eta = 1.0f; o.pdf = F;
-            return evalTex(S, n.t0, uv);
+            return lt.c0;
         }
         o.type = MTS_EDELTA_TRANSMISSION;
         float scale = -(cosThetaT < 0 ? invEta : eta);
@@ -671,19 +802,19 @@ __device__ __noinline__ float3 leafSample(const DScene &S, const MtsBsdfNode &n,
         o.eta = cosThetaT < 0 ? eta : invEta;
         o.pdf = 1 - F;
         float factor = cosThetaT < 0 ? invEta : eta;
-        return evalTex(S, n.t1, uv) * (factor * factor);
+        return lt.c1 * (factor * factor);
     }
-    case MTS_BSDF_ROUGHDIELECTRIC: return roughDielSample(S, n, uv, wi, sample, o);
+    case MTS_BSDF_ROUGHDIELECTRIC: return roughDielSample(S, n, lt, wi, sample, o);
     case MTS_BSDF_THINDIELECTRIC: {  // thindielectric.cpp:191-221 (the pdf-returning overload path.cpp:209 calls)
         float R = fresnelDielectricExt(fabsf(cosTheta(wi)), n.eta[0]), T = 1 - R;
         if (R < 1) R += T * T * R / (1 - R * R);
         o.eta = 1.0f;
         if (sample.x <= R) {
             o.type = MTS_EDELTA_REFLECTION; o.wo = reflectZ(wi); o.pdf = R;
-            return evalTex(S, n.t0, uv);
+            return lt.c0;
         }
         o.type = MTS_ENULL; o.wo = -wi; o.pdf = 1 - R;
-        return evalTex(S, n.t1, uv);
+        return lt.c1;
     }
     }
     return f3(0.0f);
@@ -694,7 +825,7 @@ __device__ __noinline__ float3 leafSample(const DScene &S, const MtsBsdfNode &n,
 // ---------------------------------------------------------------------------------------
 // Surface context the wrappers need (bumpmap perturbs the frame; textures only need uv).
 struct Surf {
-    float2 uv;
+    TexCtx tc;
     float3 dpdu, dpdv, geoN;
     Frame sh;
     // one-entry cache of the perturbed frame: eval, pdf and sample of one hit share a single gradient lookup
@@ -703,9 +834,9 @@ struct Surf {
 };
 
 // BumpMap::getFrame (src/bsdfs/bumpmap.cpp:135-159)
-DEVFN Frame bumpFrame(const DScene &S, const MtsBsdfNode &n, const Surf &su) {
+DEVFN Frame bumpFrame(const Mats S, const MtsBsdfNode &n, const Surf &su) {
     float3 g0, g1;
-    evalTexGradient(S, n.t0, su.uv, g0, g1);
+    evalTexGradient(S, n.t0, su.tc.uv, g0, g1);
     float dDispDu = luminance(g0), dDispDv = luminance(g1);
     float3 dpdu = su.dpdu + su.sh.n * (dDispDu - dot(su.sh.n, su.dpdu));
     float3 dpdv = su.dpdv + su.sh.n * (dDispDv - dot(su.sh.n, su.dpdv));
@@ -716,7 +847,7 @@ DEVFN Frame bumpFrame(const DScene &S, const MtsBsdfNode &n, const Surf &su) {
     if (dot(r.n, su.geoN) < 0) r.n = -r.n;
     return r;
 }
-DEVFN Frame bumpFrameCached(const DScene &S, int node, const MtsBsdfNode &n, const Surf &su) {
+DEVFN Frame bumpFrameCached(const Mats S, int node, const MtsBsdfNode &n, const Surf &su) {
     if (su.bumpNode == node) return su.bumpCache;
     Frame f = bumpFrame(S, n, su);
     su.bumpNode = node; su.bumpCache = f;
@@ -737,24 +868,24 @@ DEVFN float3 coatRefractOut(float eta, float3 wi, float &R) {
 template <int D> struct Bsdf {
     typedef Bsdf<D + 1> Next;
 
-    static __device__ BSDF_NESTED_ATTR float3 eval(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
+    static __device__ BSDF_NESTED_ATTR float3 eval(const Mats S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
         const MtsBsdfNode &n = S.nodes[node];
         switch (n.type) {
         case MTS_BSDF_COATING: {  // coating.cpp:221-258
             float eta = n.eta[0], invEta = 1 / eta;
             if (measure == MTS_MEASURE_DISCRETE && fabsf(dot(reflectZ(wi), wo) - 1) < kDeltaEps)
-                return evalTex(S, n.t1, su.uv) * fresnelDielectricExt(fabsf(cosTheta(wi)), eta);
+                return evalTex(S, n.t1, su.tc) * fresnelDielectricExt(fabsf(cosTheta(wi)), eta);
             float R12, R21;
             float3 wiP = coatRefractIn(eta, wi, R12), woP = coatRefractIn(eta, wo, R21);
             if (R12 == 1 || R21 == 1) return f3(0.0f);
             float3 result = Next::eval(S, n.child[0], su, wiP, woP, measure) * (1 - R12) * (1 - R21);
-            float3 sigmaA = evalTex(S, n.t0, su.uv) * n.f[0];
+            float3 sigmaA = evalTex(S, n.t0, su.tc) * n.f[0];
             if (!isZero(sigmaA)) result *= vexp(-sigmaA * (1 / fabsf(cosTheta(wiP)) + 1 / fabsf(cosTheta(woP))));
             if (measure == MTS_MEASURE_SOLID_ANGLE) result *= invEta * invEta * cosTheta(wo) / cosTheta(woP);
             return result;
         }
         case MTS_BSDF_BLEND: {  // blendbsdf.cpp:135-152
-            float weight = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.uv))));
+            float weight = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.tc))));
             return Next::eval(S, n.child[0], su, wi, wo, measure) * (1 - weight) + Next::eval(S, n.child[1], su, wi, wo, measure) * weight;
         }
         case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:161-177
@@ -770,17 +901,17 @@ template <int D> struct Bsdf {
             int child = n.child[0];
             float3 scale = f3(1.0f);
             if (n.type == MTS_BSDF_MASK) {
-                scale = evalTex(S, n.t0, su.uv);
+                scale = evalTex(S, n.t0, su.tc);
                 if (measure != MTS_MEASURE_SOLID_ANGLE)
                     return (measure == MTS_MEASURE_DISCRETE && fabsf(1 - dot(wi, -wo)) < kDeltaEps) ? f3(1.0f) - scale : f3(0.0f);
             } else if (!(cosTheta(wi) > 0)) { wi.z = -wi.z; wo.z = -wo.z; child = n.child[1]; }
             return Next::eval(S, child, su, wi, wo, measure) * scale;
         }
-        default: return leafEval(S, n, su.uv, wi, wo, measure);
+        default: return leafEval(S, n, resolveLeaf(S, n, su.tc), wi, wo, measure);
         }
     }
 
-    static __device__ BSDF_NESTED_ATTR float pdf(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
+    static __device__ BSDF_NESTED_ATTR float pdf(const Mats S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
         const MtsBsdfNode &n = S.nodes[node];
         switch (n.type) {
         case MTS_BSDF_COATING: {  // coating.cpp:260-296
@@ -798,7 +929,7 @@ template <int D> struct Bsdf {
             return p * (1 - probSpecular);
         }
         case MTS_BSDF_BLEND: {  // blendbsdf.cpp:154-173
-            float weight = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.uv))));
+            float weight = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.tc))));
             return Next::pdf(S, n.child[0], su, wi, wo, measure) * (1 - weight) + Next::pdf(S, n.child[1], su, wi, wo, measure) * weight;
         }
         case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:179-197
@@ -814,17 +945,17 @@ template <int D> struct Bsdf {
             int child = n.child[0];
             float prob = 1.0f;
             if (n.type == MTS_BSDF_MASK) {
-                prob = luminance(evalTex(S, n.t0, su.uv));
+                prob = luminance(evalTex(S, n.t0, su.tc));
                 if (measure != MTS_MEASURE_SOLID_ANGLE)
                     return (measure == MTS_MEASURE_DISCRETE && fabsf(1 - dot(wi, -wo)) < kDeltaEps) ? 1 - prob : 0.0f;
             } else if (!(wi.z > 0)) { wi.z = -wi.z; wo.z = -wo.z; child = n.child[1]; }
             return Next::pdf(S, child, su, wi, wo, measure) * prob;
         }
-        default: return leafPdf(S, n, su.uv, wi, wo, measure);
+        default: return leafPdf(S, n, resolveLeaf(S, n, su.tc), wi, wo, measure);
         }
     }
 
-    static __device__ BSDF_NESTED_ATTR float3 sample(const DScene &S, int node, const Surf &su, float3 wi, float2 sample, BSample &o) {
+    static __device__ BSDF_NESTED_ATTR float3 sample(const Mats S, int node, const Surf &su, float3 wi, float2 sample, BSample &o) {
         const MtsBsdfNode &n = S.nodes[node];
         switch (n.type) {
         case MTS_BSDF_COATING: {  // coating.cpp:298-371
@@ -838,13 +969,13 @@ template <int D> struct Bsdf {
             else { sample.x = (sample.x - probSpecular) / (1 - probSpecular); choseSpecular = false; }
             if (choseSpecular) {
                 o.type = MTS_EDELTA_REFLECTION; o.wo = reflectZ(wi); o.eta = 1.0f; o.pdf = probSpecular;
-                return evalTex(S, n.t1, su.uv) * (R12 / o.pdf);
+                return evalTex(S, n.t1, su.tc) * (R12 / o.pdf);
             }
             if (R12 == 1.0f) return f3(0.0f);
             float3 result = Next::sample(S, n.child[0], su, wiPrime, sample, o);
             if (isZero(result)) return f3(0.0f);
             float3 woPrime = o.wo;
-            float3 sigmaA = evalTex(S, n.t0, su.uv) * n.f[0];
+            float3 sigmaA = evalTex(S, n.t0, su.tc) * n.f[0];
             if (!isZero(sigmaA)) result *= vexp(-sigmaA * (1 / fabsf(cosTheta(wiPrime)) + 1 / fabsf(cosTheta(woPrime))));
             float R21;
             o.wo = coatRefractOut(eta, woPrime, R21);
@@ -856,7 +987,7 @@ template <int D> struct Bsdf {
             return result;
         }
         case MTS_BSDF_BLEND: {  // blendbsdf.cpp:223-262
-            float w1 = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.uv))));
+            float w1 = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.tc))));
             float w0 = 1 - w1;
             int entry;
             if (sample.x < w0) { entry = 0; sample.x /= w0; } else { entry = 1; sample.x = (sample.x - w0) / w1; }
@@ -891,7 +1022,7 @@ template <int D> struct Bsdf {
             float prob = 1.0f;
             bool flipped = false;
             if (mask) {
-                opacity = evalTex(S, n.t0, su.uv);
+                opacity = evalTex(S, n.t0, su.tc);
                 prob = luminance(opacity);
                 if (!(sample.x < prob)) {
                     o.wo = -wi; o.eta = 1.0f; o.type = MTS_ENULL; o.pdf = 1 - prob;
@@ -904,24 +1035,127 @@ template <int D> struct Bsdf {
             else if (flipped && !isZero(result) && o.pdf != 0) o.wo.z = -o.wo.z;
             return result;
         }
-        default: return leafSample(S, n, su.uv, wi, sample, o);
+        default: return leafSample(S, n, resolveLeaf(S, n, su.tc), wi, sample, o);
         }
     }
 };
 
 // recursion floor: below kMaxBsdfDepth wrappers only leaves are legal (set_bsdfs enforces it)
 template <> struct Bsdf<kMaxBsdfDepth> {
-    static __device__ BSDF_NESTED_ATTR float3 eval(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
-        return leafEval(S, S.nodes[node], su.uv, wi, wo, measure);
+    static __device__ BSDF_NESTED_ATTR float3 eval(const Mats S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
+        return leafEval(S, S.nodes[node], resolveLeaf(S, S.nodes[node], su.tc), wi, wo, measure);
     }
-    static __device__ BSDF_NESTED_ATTR float pdf(const DScene &S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
-        return leafPdf(S, S.nodes[node], su.uv, wi, wo, measure);
+    static __device__ BSDF_NESTED_ATTR float pdf(const Mats S, int node, const Surf &su, float3 wi, float3 wo, int measure) {
+        return leafPdf(S, S.nodes[node], resolveLeaf(S, S.nodes[node], su.tc), wi, wo, measure);
     }
-    static __device__ BSDF_NESTED_ATTR float3 sample(const DScene &S, int node, const Surf &su, float3 wi, float2 sample, BSample &o) {
-        return leafSample(S, S.nodes[node], su.uv, wi, sample, o);
+    static __device__ BSDF_NESTED_ATTR float3 sample(const Mats S, int node, const Surf &su, float3 wi, float2 sample, BSample &o) {
+        return leafSample(S, S.nodes[node], resolveLeaf(S, S.nodes[node], su.tc), wi, sample, o);
     }
 };
 
 typedef Bsdf<0> BsdfRoot;
+
+// ---------------------------------------------------------------------------------------
+// Shade classes: what MIPathTracer::Li needs from the BSDF of one hit (eval + pdf of the light sample, sample of the
+// next direction), specialised by the shape of the BSDF tree so that the common cases run without the generic
+// wrapper recursion -- no per-level Surf copies on the stack, leaf textures fetched once per hit, far less code
+// per kernel.  mtscuda_build() classifies every root BSDF (shadeClassOf, mtscuda.cu) and orders the material sort
+// keys by class, so each class is one contiguous range of the sorted queue and gets its own k_shade<> instance.
+//   SHADE_LAMBERT  root is `diffuse`
+//   SHADE_LEAF     root is any leaf model, optionally below the frame / side adapters twosided -> bumpmap
+//                  (leaf | bumpmap(leaf) | twosided(x [, y]) with x, y = leaf | bumpmap(leaf))
+//   SHADE_GENERIC  everything else (coating, blendbsdf, mask, deeper nestings): Bsdf<0> recursion
+// ---------------------------------------------------------------------------------------
+enum { SHADE_LAMBERT = 0, SHADE_LEAF = 1, SHADE_GENERIC = 2, SHADE_CLASSES = 3 };
+// evalPdf(): when the pdf is wanted.  The fused classes always produce it (it shares its terms with the value); the
+// generic class evaluates it separately and skips it when nothing will use it.
+enum { PDF_NONE = 0, PDF_IF_LIT = 1, PDF_ALWAYS = 2 };
+
+template <int CLASS> struct Material;
+
+template <> struct Material<SHADE_GENERIC> {
+    const Mats S; int node; const Surf &su;
+    DEVFN Material(const Mats S_, int node_, const Surf &su_, float3) : S(S_), node(node_), su(su_) {}
+    DEVFN float3 evalPdf(float3 wi, float3 wo, int measure, int pdfMode, float &pdf) const {
+        pdf = 0.0f;
+        const float3 v = BsdfRoot::eval(S, node, su, wi, wo, measure);
+        if (pdfMode == PDF_ALWAYS || (pdfMode == PDF_IF_LIT && !isZero(v))) pdf = BsdfRoot::pdf(S, node, su, wi, wo, measure);
+        return v;
+    }
+    DEVFN float3 sample(float3 wi, float2 u, BSample &bs) const { return BsdfRoot::sample(S, node, su, wi, u, bs); }
+};
+
+template <> struct Material<SHADE_LEAF> {
+    const Mats S;
+    const MtsBsdfNode *n;   // the leaf
+    LeafTex lt;
+    Frame sh, pf;           // shading frame of the hit, perturbed frame of the bumpmap adapter
+    float3 wiLeaf;          // incident direction as the leaf sees it
+    bool bump, flipped;
+    DEVFN Material(const Mats S_, int root, const Surf &su, float3 wi) : S(S_), sh(su.sh), bump(false), flipped(false) {
+        const MtsBsdfNode *r = &S.nodes[root];
+        if (r->type == MTS_BSDF_TWOSIDED) {   // twosided.cpp:107-180: the back side sees the mirrored configuration
+            int child = r->child[0];
+            if (!(cosTheta(wi) > 0)) { wi.z = -wi.z; flipped = true; child = r->child[1]; }
+            r = &S.nodes[child];
+        }
+        if (r->type == MTS_BSDF_BUMPMAP) {    // bumpmap.cpp:161-240: same directions expressed in the perturbed frame
+            bump = true;
+            pf = bumpFrame(S, *r, su);
+            wi = pf.toLocal(sh.toWorld(wi));
+            r = &S.nodes[r->child[0]];
+        }
+        n = r; wiLeaf = wi;
+        lt = resolveLeaf(S, *n, su.tc);
+    }
+    DEVFN float3 evalPdf(float3, float3 wo, int measure, int, float &pdf) const {
+        if (flipped) wo.z = -wo.z;
+        float3 woL = wo;
+        if (bump) {
+            woL = pf.toLocal(sh.toWorld(wo));
+            if (cosTheta(wo) * cosTheta(woL) <= 0) { pdf = 0.0f; return f3(0.0f); }
+        }
+        return leafEvalPdf(S, *n, lt, wiLeaf, woL, measure, pdf);
+    }
+    DEVFN float3 sample(float3, float2 u, BSample &bs) const {
+        const float3 r = leafSample(S, *n, lt, wiLeaf, u, bs);
+        if (isZero(r)) return r;
+        if (bump) {
+            const float3 woP = bs.wo;
+            bs.wo = sh.toLocal(pf.toWorld(woP));
+            if (cosTheta(bs.wo) * cosTheta(woP) <= 0) return f3(0.0f);
+        }
+        if (flipped && bs.pdf != 0) bs.wo.z = -bs.wo.z;
+        return r;
+    }
+};
+
+template <> struct Material<SHADE_LAMBERT> {   // src/bsdfs/diffuse.cpp:110-150, everything inline
+    float3 reflectance;
+    DEVFN Material(const Mats S, int root, const Surf &su, float3) { reflectance = evalTex(S, S.nodes[root].t0, su.tc); }
+    DEVFN float3 evalPdf(float3 wi, float3 wo, int measure, int, float &pdf) const {
+        if (measure != MTS_MEASURE_SOLID_ANGLE || cosTheta(wi) <= 0 || cosTheta(wo) <= 0) { pdf = 0.0f; return f3(0.0f); }
+        pdf = squareToCosineHemispherePdf(wo);
+        return reflectance * (kInvPi * cosTheta(wo));
+    }
+    DEVFN float3 sample(float3 wi, float2 u, BSample &bs) const {
+        if (cosTheta(wi) <= 0) return f3(0.0f);
+        bs.wo = squareToCosineHemisphere(u);
+        bs.eta = 1.0f; bs.type = MTS_EDIFFUSE_REFLECTION;
+        bs.pdf = squareToCosineHemispherePdf(bs.wo);
+        return reflectance;
+    }
+};
+
+// Classification of a root BSDF (host side: mtscuda_build; also used by the per-function test entry points)
+inline int shadeClassOf(const MtsBsdfNode *nodes, int root) {
+    auto isLeaf = [&](int i) { const int t = nodes[i].type; return t != MTS_BSDF_COATING && t != MTS_BSDF_BLEND && t != MTS_BSDF_BUMPMAP && t != MTS_BSDF_TWOSIDED && t != MTS_BSDF_MASK; };
+    auto leafOrBump = [&](int i) { return isLeaf(i) || (nodes[i].type == MTS_BSDF_BUMPMAP && isLeaf(nodes[i].child[0])); };
+    if (nodes[root].type == MTS_BSDF_DIFFUSE) return SHADE_LAMBERT;
+    if (leafOrBump(root)) return SHADE_LEAF;
+    if (nodes[root].type == MTS_BSDF_TWOSIDED && leafOrBump(nodes[root].child[0]) && leafOrBump(nodes[root].child[1])) return SHADE_LEAF;
+    return SHADE_GENERIC;
+}
+
 
 } // namespace mts

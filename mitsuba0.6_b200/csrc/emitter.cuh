@@ -1,6 +1,7 @@
 // emitter.cuh -- direct illumination sampling for area, point and environment-map emitters.
 #pragma once
 #include "geometry.cuh"
+#include "bsdf.cuh"
 
 namespace mts {
 
@@ -159,6 +160,16 @@ DEVFN float3 envEval(const DEnvmap &e, float3 dWorld) {
     float3 value1, value2; int yPos;
     envBilinear(e, uvx * e.width - 0.5f, uvy * e.height - 0.5f, value1, value2, yPos);
     return (value1 + value2) * e.scale;
+}
+// evalEnvironment of a ray with differentials (:391-407): texture-space partials of the lat-long map, then TMIPMap::eval
+DEVFN float3 envEvalDiff(const DScene &S, const DEnvmap &e, float3 dWorld, float3 rxD, float3 ryD) {
+    const float3 v = xfVec(e.toLocal, dWorld);
+    const float2 uv = make_float2(atan2f(v.x, -v.z) * kInvTwoPi, safe_acos(v.y) * kInvPi);
+    const float3 dvdx = xfVec(e.toLocal, rxD) - v, dvdy = xfVec(e.toLocal, ryD) - v;
+    const float t1 = kInvTwoPi / (v.x * v.x + v.z * v.z), t2 = -kInvPi / fmaxf(safe_sqrt(1.0f - v.y * v.y), kEps);
+    const float2 d0 = make_float2(t1 * (dvdx.z * v.x - dvdx.x * v.z), t2 * dvdx.y);
+    const float2 d1 = make_float2(t1 * (dvdy.z * v.x - dvdy.x * v.z), t2 * dvdy.y);
+    return mipEval(*e.mip, uv, d0, d1) * e.scale;
 }
 // BSphere::rayIntersect (include/mitsuba/core/bsphere.h:88-95)
 DEVFN bool bsphereIntersect(const DEnvmap &e, float3 o, float3 d, float &nearT, float &farT) {

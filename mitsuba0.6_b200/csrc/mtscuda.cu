@@ -9,6 +9,7 @@
 #include "bvh_build.h"
 #include "devmem.h"
 #include "wavefront.cuh"
+#include "shade_launch.h"
 
 using namespace mts;
 
@@ -28,7 +29,7 @@ struct HostShape {
     float lo[3], hi[3];  // analytic bounds
 };
 
-struct HostTex { MtsTextureDesc d; __half *texels = nullptr; };  // texels live on the device (converted there)
+struct HostTex { MtsTextureDesc d; DTexture dt; };  // dt.texels: the MIP pyramid, built and kept on the device
 
 // Growable device array: scene buffers are appended straight from the caller's host pointers (no host staging
 // copy), so the plugin-facing upload runs at PCIe speed.
@@ -127,6 +128,8 @@ struct MtsContext {
     uint32_t *hostPoll = nullptr;                             // pinned: next-queue sizes polled without blocking
     std::vector<cudaEvent_t> eventPool; size_t eventsUsed = 0;
     int bvhDepth = 0;
+    float *ewaLut = nullptr;                                  // EWA weight table shared by all MIP maps
+    uint32_t numKeys = 1, classKey[SHADE_CLASSES + 1] = {1, 1, 1, 1};   // material sort keys (set by build)
     // wavefront
     Wavefront wf; std::vector<void *> wfAllocs; uint32_t wfCapacity = 0;
     MtsStats stats;
@@ -135,7 +138,7 @@ struct MtsContext {
     void freeScene() { for (void *p : sceneAllocs) devFree(p, stream); sceneAllocs.clear(); built = false; }
     void freeGeometry() {
         positions.release(stream); normals.release(stream); texcoords.release(stream); tangents.release(stream); indices.release(stream);
-        for (auto &t : textures) devFree(t.texels, stream);
+        for (auto &t : textures) devFree((void *)t.dt.texels, stream);
         textures.clear();
         devFree(errFlag, stream);
         errFlag = nullptr;
@@ -167,7 +170,8 @@ int bsdfDepth(const std::vector<MtsBsdfNode> &nodes, int i, int guard = 0) {
 }
 
 int ensureWavefront(MtsContext *c, uint32_t cap) {
-    const uint32_t numKeys = (uint32_t)c->nodes.size() + 1;
+    const uint32_t numKeys = c->numKeys;
+    for (int k = 0; k <= SHADE_CLASSES; ++k) c->wf.classKey[k] = c->classKey[k];
     if (c->wfCapacity >= cap && c->wf.numKeys == numKeys) return MTS_OK;
     c->freeWavefront();
     Wavefront &w = c->wf;
@@ -187,6 +191,7 @@ int ensureWavefront(MtsContext *c, uint32_t cap) {
     CUDA_TRY(alloc((void **)&w.keyCount, 4 * 3 * (size_t)numKeys));
     CUDA_TRY(cudaMemsetAsync(w.keyCount, 0, 4 * 3 * (size_t)numKeys, c->stream));
     w.numKeys = numKeys;
+    for (int k = 0; k <= SHADE_CLASSES; ++k) w.classKey[k] = c->classKey[k];
     CUDA_TRY(alloc((void **)&w.ctr, sizeof(Counters)));
     w.capacity = cap;
     c->wfCapacity = cap;
@@ -294,6 +299,131 @@ __global__ void k_env_finish(const float *__restrict__ rowTerm, int h, float *__
     *rowSumOut = rowSum;
 }
 
+// ---- MIP pyramid (TMIPMap ctor, include/mitsuba/render/mipmap.h:162-303) ------------------------------------------
+__global__ void k_clamp_negative(float *p, size_t n) {   // Spectrum::clampNegative of the base image (:228-236)
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && p[i] < 0) p[i] = 0.0f;
+}
+// One axis of Bitmap::resample (src/libcore/bitmap.cpp:2259-2328) = Resampler::resampleAndClamp
+// (include/mitsuba/core/rfilter.h:229-340, boundary handling :432-458).  The taps are accumulated in the host code's
+// order with separately rounded products and sums, so every level equals the host computation bit for bit.
+__global__ void k_resample_axis(const float *__restrict__ src, float *__restrict__ dst, int sw, int sh, int tw, int th, int ch,
+                                int axis, int bc, const int *__restrict__ start, const float *__restrict__ weights, int taps, float hi) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t)tw * th) return;
+    const int x = (int)(idx % tw), y = (int)(idx / tw);
+    const int t = axis == 0 ? x : y, res = axis == 0 ? sw : sh;
+    const int s0 = start[t];
+    const float *wts = weights + (size_t)t * taps;
+    for (int c = 0; c < ch; ++c) {
+        float result = 0.0f;
+        for (int j = 0; j < taps; ++j) {
+            int pos = s0 + j;
+            float v;
+            bool constant = false;
+            if (pos < 0 || pos >= res) {
+                switch (bc) {
+                    case MTS_WRAP_CLAMP: pos = min(max(pos, 0), res - 1); break;
+                    case MTS_WRAP_REPEAT: pos = wrapRepeat(pos, res); break;
+                    case MTS_WRAP_MIRROR: pos = wrapRepeat(pos, 2 * res); if (pos >= res) pos = 2 * res - pos - 1; break;
+                    case MTS_WRAP_ZERO: constant = true; v = 0.0f; break;
+                    default: constant = true; v = 1.0f; break;
+                }
+            }
+            if (!constant) v = axis == 0 ? src[((size_t)y * sw + pos) * ch + c] : src[((size_t)pos * sw + x) * ch + c];
+            result = __fadd_rn(result, __fmul_rn(v, wts[j]));
+        }
+        dst[idx * ch + c] = fminf(hi, fmaxf(0.0f, result));
+    }
+}
+
+// LanczosSincFilter::eval, 2 lobes (src/rfilters/lanczos.cpp:38-50)
+static float lanczos2(float x) {
+    const float radius = 2.0f;
+    x = std::fabs(x);
+    if (x < kEps) return 1.0f;
+    else if (x > radius) return 0.0f;
+    float x1 = kPi * x, x2 = x1 / radius;
+    return (std::sin(x1) * std::sin(x2)) / (x1 * x2);
+}
+// Resampler ctor in resampling mode (rfilter.h:123-176)
+static void resamplerWeights(int sourceRes, int targetRes, int &taps, std::vector<int> &start, std::vector<float> &weights) {
+    float filterRadius = 2.0f, scale = 1.0f, invScale = 1.0f;
+    if (targetRes < sourceRes) { scale = (float)sourceRes / (float)targetRes; invScale = 1 / scale; filterRadius *= scale; }
+    taps = (int)std::ceil(filterRadius * 2);
+    start.resize(targetRes); weights.resize((size_t)taps * targetRes);
+    for (int i = 0; i < targetRes; i++) {
+        float center = (i + 0.5f) / targetRes * sourceRes;
+        start[i] = (int)std::floor(center - filterRadius + 0.5f);
+        float sum = 0;
+        for (int j = 0; j < taps; j++) {
+            float pos = start[i] + j + 0.5f - center;
+            float weight = lanczos2(pos * invScale);
+            weights[(size_t)i * taps + j] = weight;
+            sum += weight;
+        }
+        float normalization = 1.0f / sum;
+        for (int j = 0; j < taps; j++) weights[(size_t)i * taps + j] *= normalization;
+    }
+}
+
+// Builds the pyramid of `raw` (w*h*ch floats on the device; negative values are clamped in place) into one half buffer
+// and describes it in `out`.  trilinear / ewa: every further level is resampled from the previous FLOAT level (x pass,
+// then y pass, clamped to [0, maxValue]) and rounded to half.
+static int buildPyramid(MtsContext *c, float *raw, int w, int h, int ch, int bcu, int bcv, int filter, float maxAniso, float maxValue, DTexture &out) {
+    cudaStream_t st = c->stream;
+    const int stride = ch == 1 ? 1 : 4;
+    std::vector<int> lw(1, w), lh(1, h);
+    if (filter == MTS_FILTER_TRILINEAR || filter == MTS_FILTER_EWA)
+        while (lw.back() > 1 || lh.back() > 1) { int nw = std::max(1, (lw.back() + 1) / 2), nh = std::max(1, (lh.back() + 1) / 2); lw.push_back(nw); lh.push_back(nh); }
+    if ((int)lw.size() > MTS_MAX_MIP_LEVELS || w > 65535 || h > 65535) return fail(MTS_EINVAL, "texture too large for the MIP pyramid");
+    size_t total = 0;
+    for (size_t l = 0; l < lw.size(); ++l) { out.levelOffset[l] = (uint32_t)total; out.levelW[l] = (uint16_t)lw[l]; out.levelH[l] = (uint16_t)lh[l]; total += (size_t)lw[l] * lh[l]; }
+    if (total > 0xffffffffull) return fail(MTS_EINVAL, "texture too large for the MIP pyramid");
+    for (size_t l = lw.size(); l < MTS_MAX_MIP_LEVELS; ++l) { out.levelOffset[l] = 0; out.levelW[l] = out.levelH[l] = 0; }
+    __half *pyr = nullptr;
+    CUDA_TRY(devAlloc(&pyr, sizeof(__half) * total * stride, st));
+    auto grid = [](size_t n) { return (unsigned)((n + 255) / 256); };
+    const size_t n0 = (size_t)w * h;
+    k_clamp_negative<<<grid(n0 * ch), 256, 0, st>>>(raw, n0 * ch);
+    k_texels_to_half<<<grid(n0), 256, 0, st>>>(raw, pyr, n0, ch);
+    float *cur = raw; bool ownCur = false;
+    cudaError_t e = cudaSuccess;
+    for (size_t l = 1; l < lw.size() && e == cudaSuccess; ++l) {
+        const int sw = lw[l - 1], sh = lh[l - 1], tw = lw[l], th = lh[l];
+        float *tmp = nullptr, *next = nullptr; int *dStart = nullptr; float *dW = nullptr;
+        const float *src = cur;
+        auto pass = [&](int axis, int sW, int sH, int tW, int tH, int bc, float **dst) {
+            int taps; std::vector<int> start; std::vector<float> weights;
+            resamplerWeights(axis == 0 ? sW : sH, axis == 0 ? tW : tH, taps, start, weights);
+            if (e == cudaSuccess) e = devAlloc(dst, sizeof(float) * (size_t)tW * tH * ch, st);
+            if (e == cudaSuccess) e = devAlloc(&dStart, sizeof(int) * start.size(), st);
+            if (e == cudaSuccess) e = devAlloc(&dW, sizeof(float) * weights.size(), st);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(dStart, start.data(), sizeof(int) * start.size(), cudaMemcpyHostToDevice, st);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(dW, weights.data(), sizeof(float) * weights.size(), cudaMemcpyHostToDevice, st);
+            if (e == cudaSuccess) k_resample_axis<<<grid((size_t)tW * tH), 256, 0, st>>>(src, *dst, sW, sH, tW, tH, ch, axis, bc, dStart, dW, taps, maxValue);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);   // the host weight vectors go out of scope
+            devFree(dStart, st); devFree(dW, st); dStart = nullptr; dW = nullptr;
+        };
+        if (sw != tw) { pass(0, sw, sh, tw, sh, bcu, &tmp); src = tmp; }
+        if (sh != th) pass(1, tw, sh, tw, th, bcv, &next);
+        else { next = tmp; tmp = nullptr; }
+        if (tmp) devFree(tmp, st);
+        if (ownCur) devFree(cur, st);
+        cur = next; ownCur = true;
+        if (e == cudaSuccess && cur) k_texels_to_half<<<grid((size_t)tw * th), 256, 0, st>>>(cur, pyr + (size_t)out.levelOffset[l] * stride, (size_t)tw * th, ch);
+    }
+    if (ownCur && cur) devFree(cur, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { devFree(pyr, st); return fail(MTS_ECUDA, std::string("MIP pyramid: ") + cudaGetErrorString(e)); }
+    out.texels = pyr; out.width = w; out.height = h; out.channels = ch; out.wrapU = bcu; out.wrapV = bcv; out.filter = filter;
+    out.uvScale = make_float2(1, 1); out.uvOffset = make_float2(0, 0);
+    out.levels = (int)lw.size();
+    out.maxAnisotropy = filter == MTS_FILTER_EWA ? maxAniso : 1.0f;   // bitmap.cpp:230-233
+    out.weightLut = c->ewaLut;
+    return MTS_OK;
+}
+
 // ---- kernels behind the per-function entry points -------------------------------------------
 __global__ void k_hook_sample_rays(const DScene S, int64_t n, const float *sp, float *out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -363,38 +493,36 @@ __global__ void k_hook_hit_records(const DScene S, int64_t n, const float *rays,
     if (ids) { ids[2 * i] = its.shape; ids[2 * i + 1] = its.prim; }
 }
 
-DEVFN Surf surfFromArray(const float *s) {
-    Surf su;
-    su.uv = make_float2(s[0], s[1]);
-    su.dpdu = f3(s[4], s[5], s[6]); su.dpdv = f3(s[8], s[9], s[10]);
-    float3 n = f3(s[12], s[13], s[14]);
-    su.geoN = n;
-    su.sh = shadingFrame(n, su.dpdu);
-    su.bumpNode = -1;
-    return su;
-}
-__global__ void k_hook_bsdf_eval_pdf(const DScene S, int bsdf, int64_t n, const float *surf, const float *wi, const float *wo,
-                                     int measure, float *outV, float *outP) {
+__global__ void k_hook_texture_eval(const DScene S, int tex, int64_t n, const float *uv, const float *duv, float *out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    Surf su = surfFromArray(surf + 16 * i);
-    float3 a = f3(wi[3 * i], wi[3 * i + 1], wi[3 * i + 2]), b = f3(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]);
-    float3 v = BsdfRoot::eval(S, bsdf, su, a, b, measure);
-    outV[3 * i] = v.x; outV[3 * i + 1] = v.y; outV[3 * i + 2] = v.z;
-    outP[i] = BsdfRoot::pdf(S, bsdf, su, a, b, measure);
+    TexCtx tc = texCtx(make_float2(uv[2 * i], uv[2 * i + 1]));
+    if (duv) { tc.duv = make_float4(duv[4 * i], duv[4 * i + 1], duv[4 * i + 2], duv[4 * i + 3]); tc.filtered = true; }
+    MtsTexRef r; r.scale[0] = r.scale[1] = r.scale[2] = 1.0f; r.tex = tex;
+    const float3 v = evalTex(S, r, tc);
+    out[3 * i] = v.x; out[3 * i + 1] = v.y; out[3 * i + 2] = v.z;
 }
-__global__ void k_hook_bsdf_sample(const DScene S, int bsdf, int64_t n, const float *surf, const float *wi, const float *u, float *out) {
+__global__ void k_hook_hit_partials(const DScene S, int64_t n, const float *sp, float diffScale, float *out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    Surf su = surfFromArray(surf + 16 * i);
-    float3 a = f3(wi[3 * i], wi[3 * i + 1], wi[3 * i + 2]);
-    BSample bs; bs.wo = f3(0.0f); bs.pdf = 0; bs.eta = 1; bs.type = 0;
-    MTS_PROBE_U3(__float_as_uint(u[2 * i]), __float_as_uint(u[2 * i + 1]), bs.u3);
-    float3 w = BsdfRoot::sample(S, bsdf, su, a, make_float2(u[2 * i], u[2 * i + 1]), bs);
-    float *q = out + 12 * i;
-    if (isZero(w)) { for (int k = 0; k < 12; ++k) q[k] = 0; return; }
-    q[0] = w.x; q[1] = w.y; q[2] = w.z; q[3] = bs.pdf; q[4] = bs.wo.x; q[5] = bs.wo.y; q[6] = bs.wo.z;
-    q[7] = bs.eta; q[8] = (float)bs.type; q[9] = q[10] = q[11] = 0;
+    float3 o, d, rxD, ryD; float mint, maxt;
+    cameraRay(S.cam, make_float2(sp[2 * i], sp[2 * i + 1]), o, d, mint, maxt);
+    float3 o2, d2;
+    cameraRayDiff(S.cam, make_float2(sp[2 * i], sp[2 * i + 1]), diffScale, o2, d2, rxD, ryD);
+    float *q = out + 8 * i;
+    RayHit h;
+    if (!sceneIntersect<false, false>(S, o, d, mint, maxt, h)) { for (int k = 0; k < 8; ++k) q[k] = 0; return; }
+    Hit its; fillHit(S, o, d, h, its);
+    const float4 p = computePartials(its.p, its.geoN, its.dpdu, its.dpdv, o, rxD, ryD);
+    q[0] = p.x; q[1] = p.y; q[2] = p.z; q[3] = p.w; q[4] = its.t; q[5] = 1.0f; q[6] = its.uv.x; q[7] = its.uv.y;
+}
+__global__ void k_hook_eval_env_camera(const DScene S, int64_t n, const float *sp, float diffScale, float *out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float3 o, d, rxD, ryD;
+    cameraRayDiff(S.cam, make_float2(sp[2 * i], sp[2 * i + 1]), diffScale, o, d, rxD, ryD);
+    const float3 v = envEvalDiff(S, S.env, d, rxD, ryD);
+    out[3 * i] = v.x; out[3 * i + 1] = v.y; out[3 * i + 2] = v.z;
 }
 __global__ void k_hook_sample_emitter(const DScene S, int64_t n, const float *ref, const float *refn, const float *u, float *out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -456,6 +584,7 @@ int syncCheck(MtsContext *c, const char *what) {
 // =============================================================================================
 extern "C" {
 
+MTS_API int32_t mtscuda_abi_version(void) { return MTS_ABI_VERSION; }
 MTS_API const char *mtscuda_last_error(void) { return g_err.c_str(); }
 
 MTS_API int mtscuda_create(int device, MtsContext **out) {
@@ -482,6 +611,16 @@ MTS_API int mtscuda_create(int device, MtsContext **out) {
     CUDA_TRY(cudaStreamCreateWithFlags(&c->ownStream, cudaStreamNonBlocking));
     c->stream = c->ownStream;
     CUDA_TRY(cudaHostAlloc((void **)&c->hostPoll, sizeof(uint32_t) * kPollRing, cudaHostAllocDefault));
+    {   // EWA Gaussian weight table (mipmap.h:296-302; math::fastexp evaluates in double, include/mitsuba/core/math.h:185-187)
+        float lut[MTS_MIPMAP_LUT_SIZE];
+        for (int i = 0; i < MTS_MIPMAP_LUT_SIZE; ++i) {
+            const float r2 = (float)i / (float)(MTS_MIPMAP_LUT_SIZE - 1);
+            lut[i] = (float)std::exp((double)(-2.0f * r2)) - (float)std::exp((double)-2.0f);
+        }
+        CUDA_TRY(devAlloc(&c->ewaLut, sizeof(lut), c->stream));
+        CUDA_TRY(cudaMemcpyAsync(c->ewaLut, lut, sizeof(lut), cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+    }
     *out = c;
     return MTS_OK;
 }
@@ -490,7 +629,7 @@ MTS_API void mtscuda_destroy(MtsContext *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     c->freeScene(); c->freeWavefront(); c->freeGeometry();
-    devFree(c->filmInternal, c->stream); devFree(c->filmAlpha, c->stream);
+    devFree(c->filmInternal, c->stream); devFree(c->filmAlpha, c->stream); devFree(c->ewaLut, c->stream);
     cudaStreamSynchronize(c->stream);
     for (cudaEvent_t e : c->eventPool) cudaEventDestroy(e);
     if (c->hostPoll) cudaFreeHost(c->hostPoll);
@@ -527,21 +666,19 @@ MTS_API int mtscuda_set_film(MtsContext *c, const MtsFilm *f) {
 MTS_API int mtscuda_add_texture(MtsContext *c, const MtsTextureDesc *d, const float *texels) {
     if (d->channels != 1 && d->channels != 3) return fail(MTS_EINVAL, "texture channels must be 1 or 3");
     if (d->width <= 0 || d->height <= 0) return fail(MTS_EINVAL, "bad texture size");
-    if (d->filter != MTS_FILTER_NEAREST && d->filter != MTS_FILTER_BILINEAR) return fail(MTS_EINVAL, "unsupported texture filter");
+    if (d->filter < MTS_FILTER_NEAREST || d->filter > MTS_FILTER_EWA) return fail(MTS_EINVAL, "unknown texture filter type");
     CUDA_TRY(cudaSetDevice(c->device));
     HostTex t; t.d = *d;
     const size_t npix = (size_t)d->width * d->height;
-    const int stride = d->channels == 1 ? 1 : 4;  // RGB padded to half4
-    float *tmp = nullptr;
-    CUDA_TRY(devAlloc(&tmp, sizeof(float) * npix * d->channels, c->stream));
-    cudaError_t e = devAlloc(&t.texels, sizeof(__half) * npix * stride, c->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(tmp, texels, sizeof(float) * npix * d->channels, cudaMemcpyHostToDevice, c->stream);
-    if (e == cudaSuccess) {
-        k_texels_to_half<<<(unsigned)((npix + 255) / 256), 256, 0, c->stream>>>(tmp, t.texels, npix, d->channels);
-        e = cudaStreamSynchronize(c->stream);
-    }
-    devFree(tmp, c->stream);
-    if (e != cudaSuccess) { devFree(t.texels, c->stream); return fail(MTS_ECUDA, std::string("add_texture: ") + cudaGetErrorString(e)); }
+    float *raw = nullptr;
+    CUDA_TRY(devAlloc(&raw, sizeof(float) * npix * d->channels, c->stream));
+    cudaError_t e = cudaMemcpyAsync(raw, texels, sizeof(float) * npix * d->channels, cudaMemcpyHostToDevice, c->stream);
+    int rc = MTS_OK;
+    if (e == cudaSuccess) rc = buildPyramid(c, raw, d->width, d->height, d->channels, d->wrap_u, d->wrap_v, d->filter, d->max_anisotropy, 1.0f /* TMIPMap maxValue default */, t.dt);
+    devFree(raw, c->stream);
+    if (e != cudaSuccess) return fail(MTS_ECUDA, std::string("add_texture: ") + cudaGetErrorString(e));
+    if (rc != MTS_OK) return rc;
+    t.dt.uvScale = make_float2(d->uv_scale[0], d->uv_scale[1]); t.dt.uvOffset = make_float2(d->uv_offset[0], d->uv_offset[1]);
     c->textures.push_back(t); c->built = false;
     return (int)c->textures.size() - 1;
 }
@@ -699,6 +836,26 @@ MTS_API int mtscuda_build(MtsContext *c) {
         }
     }
     if ((rc = devUpload(c, cdfs.data(), cdfs.size(), &S.areaCdfs))) return rc;
+    // material sort keys: the distinct root BSDFs ordered by shade class, so that every k_shade<CLASS> instance owns one
+    // contiguous range of the sorted queue (key 0 = escaped rays)
+    {
+        std::vector<int> roots;
+        for (auto &s : c->shapes) roots.push_back(s.d.bsdf);
+        std::sort(roots.begin(), roots.end());
+        roots.erase(std::unique(roots.begin(), roots.end()), roots.end());
+        std::stable_sort(roots.begin(), roots.end(), [&](int a, int b) { return shadeClassOf(c->nodes.data(), a) < shadeClassOf(c->nodes.data(), b); });
+        std::vector<uint32_t> keyOf(c->nodes.size(), 0u);
+        for (int k = 0; k <= SHADE_CLASSES; ++k) c->classKey[k] = (uint32_t)roots.size() + 1;
+        for (size_t r = 0; r < roots.size(); ++r) {
+            keyOf[roots[r]] = (uint32_t)r + 1;
+            const int cls = shadeClassOf(c->nodes.data(), roots[r]);
+            for (int k = 0; k <= cls; ++k) c->classKey[k] = std::min(c->classKey[k], (uint32_t)r + 1);
+        }
+        // classes without any BSDF start where the next populated class starts
+        for (int k = SHADE_CLASSES - 1; k >= 0; --k) c->classKey[k] = std::min(c->classKey[k], c->classKey[k + 1]);
+        c->numKeys = (uint32_t)roots.size() + 1;
+        for (auto &s : c->shapes) s.d.sortKey = keyOf[s.d.bsdf];
+    }
     std::vector<DShape> dshapes; for (auto &s : c->shapes) dshapes.push_back(s.d);
     if ((rc = devUpload(c, dshapes.data(), dshapes.size(), &S.shapes))) return rc;
     S.numShapes = (int)dshapes.size();
@@ -723,13 +880,7 @@ MTS_API int mtscuda_build(MtsContext *c) {
     S.numNodes = (int)c->nodes.size();
     if ((rc = devUpload(c, c->pool.data(), c->pool.size(), &S.pool))) return rc;
     std::vector<DTexture> dtex;
-    for (auto &t : c->textures) {
-        DTexture d;
-        d.texels = t.texels; d.width = t.d.width; d.height = t.d.height; d.channels = t.d.channels;
-        d.wrapU = t.d.wrap_u; d.wrapV = t.d.wrap_v; d.filter = t.d.filter;
-        d.uvScale = make_float2(t.d.uv_scale[0], t.d.uv_scale[1]); d.uvOffset = make_float2(t.d.uv_offset[0], t.d.uv_offset[1]);
-        dtex.push_back(d);
-    }
+    for (auto &t : c->textures) dtex.push_back(t.dt);
     if ((rc = devUpload(c, dtex.data(), dtex.size(), &S.textures))) return rc;
     S.numTextures = (int)dtex.size();
     // emitter pmf (src/librender/scene.cpp:375-380)
@@ -762,7 +913,12 @@ MTS_API int mtscuda_build(MtsContext *c) {
             CUDA_TRY(mts::devAlloc(out, bytes, c->stream)); c->sceneAllocs.push_back(*out); return MTS_OK;
         };
         __half *tex = nullptr; float *cdfCols = nullptr, *cdfRows = nullptr, *rowTerm = nullptr; uint16_t *gRows = nullptr, *gCols = nullptr;
-        if ((rc = devAlloc(sizeof(__half) * 4 * (size_t)w * h, (void **)&tex))) return rc;
+        // the texels as a TMIPMap: repeat-u / clamp-v, EWA, maxAnisotropy 10, unbounded values (envmap.cpp:138-182)
+        DTexture envMip;
+        if ((rc = buildPyramid(c, he.envRaw, w, h, 3, MTS_WRAP_REPEAT, MTS_WRAP_CLAMP, MTS_FILTER_EWA, 10.0f, INFINITY, envMip))) return rc;
+        c->sceneAllocs.push_back((void *)envMip.texels);
+        if ((rc = devUpload(c, &envMip, 1, &E.mip))) return rc;
+        tex = const_cast<__half *>(envMip.texels);   // k_env_rows rewrites level 0 with the same values
         if ((rc = devAlloc(sizeof(float) * (size_t)(w + 1) * h, (void **)&cdfCols))) return rc;
         if ((rc = devAlloc(sizeof(float) * (size_t)(h + 1), (void **)&cdfRows))) return rc;
         if ((rc = devAlloc(sizeof(float) * (size_t)(h + 1), (void **)&rowTerm))) return rc;   // [h] receives the total
@@ -859,6 +1015,7 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
     R.maxDepth = P->max_depth; R.rrDepth = P->rr_depth; R.strictNormals = P->strict_normals; R.hideEmitters = P->hide_emitters;
     R.seed = P->seed; R.sampleOffset = P->sample_offset; R.sampleStride = P->sample_stride > 0 ? P->sample_stride : 1;
     R.tilesX = (W + 7) / 8; R.tilesY = (H + 3) / 4; R.paddedPixels = (uint32_t)R.tilesX * R.tilesY * 32u;
+    R.diffScale = 1.0f / std::sqrt((float)(P->sample_count > 0 ? P->sample_count : P->spp * R.sampleStride));   // integrator.cpp:144-145
     const unsigned long long totalItems = (unsigned long long)R.paddedPixels * (unsigned long long)P->spp;
     uint32_t cap = P->wavefront_size > 0 ? (uint32_t)P->wavefront_size : (1u << 25);   // 32 Mi path slots (5.5 GB of state): large wavefronts amortise the latency-bound tail bounces
     cap = (uint32_t)std::min<unsigned long long>(std::max<unsigned long long>(totalItems, 32), cap);
@@ -888,7 +1045,6 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
     cudaEventRecord(ev0, st);
 
     // 4 CTAs/SM (128 registers) measured best on cfg3; 3 (168 registers, fewer spills) kept as the measured alternative
-    const int shadeMinB = getenv("MTS_SHADE_MINB") ? atoi(getenv("MTS_SHADE_MINB")) : 4;
     const bool traceBounces = getenv("MTS_TRACE_BOUNCES") != nullptr;   // per-bounce queue sizes on stderr (matches ncu launches to ray counts)
     const int gridTrace = c->numSMs * TRACE_MINB, gridWide = c->numSMs * 8;
     uint64_t launches = 0;
@@ -940,10 +1096,10 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
             end();
             begin(6); k_shade_miss<<<gridWide, 256, 0, st>>>(S, Wf, R, cur); end();
             begin(2);
-            switch (shadeMinB) {
-            case 3: k_shade<3><<<c->numSMs * 3, 128, 0, st>>>(S, Wf, R, cur); break;
-            default: k_shade<4><<<c->numSMs * 4, 128, 0, st>>>(S, Wf, R, cur); break;
-            }
+            // one instance per shade class that has BSDFs in this scene (each walks its own range of the sorted queue)
+            if (Wf.classKey[SHADE_LAMBERT] < Wf.classKey[SHADE_LAMBERT + 1]) { launchShade<SHADE_LAMBERT>(S, Wf, R, cur, c->numSMs, st); ++launches; }
+            if (Wf.classKey[SHADE_LEAF] < Wf.classKey[SHADE_LEAF + 1]) { launchShade<SHADE_LEAF>(S, Wf, R, cur, c->numSMs, st); ++launches; }
+            if (Wf.classKey[SHADE_GENERIC] < Wf.classKey[SHADE_GENERIC + 1]) { launchShade<SHADE_GENERIC>(S, Wf, R, cur, c->numSMs, st); ++launches; }
             end();
             begin(3);
             setBvhWindow(c, st, true);
@@ -952,7 +1108,7 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
             setBvhWindow(c, st, false);
             end();
             begin(4); k_splat<<<gridWide, 256, 0, st>>>(S, Wf, R); end();
-            launches += 8;
+            launches += 7;
             CUDA_TRY(cudaMemcpyAsync(&c->hostPoll[bounce % kPollRing], &Wf.ctr->qCount[cur ^ 1], sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
             CUDA_TRY(cudaEventRecord(pollEv[bounce % kPollRing], st));
             if (traceBounces) {
@@ -1072,7 +1228,11 @@ MTS_API int mtscuda_bsdf_eval_pdf(MtsContext *c, int32_t bsdf, int64_t n, const 
     HOOK_PREAMBLE(true)
     float *ds_ = sg.in(surf, 16 * n, st), *dwi = sg.in(wi, 3 * n, st), *dwo = sg.in(wo, 3 * n, st);
     float *dv = sg.out<float>(3 * n), *dp = sg.out<float>(n); NEED(ds_ && dwi && dwo && dv && dp);
-    k_hook_bsdf_eval_pdf<<<gridFor(n), 128, 0, st>>>(c->ds, bsdf, n, ds_, dwi, dwo, measure, dv, dp);
+    switch (shadeClassOf(c->nodes.data(), bsdf)) {   // the same code path k_shade<CLASS> runs for this BSDF
+    case SHADE_LAMBERT: launchBsdfEvalPdf<SHADE_LAMBERT>(c->ds, bsdf, n, ds_, dwi, dwo, measure, dv, dp, st); break;
+    case SHADE_LEAF: launchBsdfEvalPdf<SHADE_LEAF>(c->ds, bsdf, n, ds_, dwi, dwo, measure, dv, dp, st); break;
+    default: launchBsdfEvalPdf<SHADE_GENERIC>(c->ds, bsdf, n, ds_, dwi, dwo, measure, dv, dp, st); break;
+    }
     CUDA_TRY(cudaMemcpyAsync(out_value, dv, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaMemcpyAsync(out_pdf, dp, sizeof(float) * n, cudaMemcpyDeviceToHost, st));
     return syncCheck(c, "bsdf_eval_pdf");
@@ -1083,7 +1243,11 @@ MTS_API int mtscuda_bsdf_sample(MtsContext *c, int32_t bsdf, int64_t n, const fl
     HOOK_PREAMBLE(true)
     float *ds_ = sg.in(surf, 16 * n, st), *dwi = sg.in(wi, 3 * n, st), *du = sg.in(u, 2 * n, st), *dout = sg.out<float>(12 * n);
     NEED(ds_ && dwi && du && dout);
-    k_hook_bsdf_sample<<<gridFor(n), 128, 0, st>>>(c->ds, bsdf, n, ds_, dwi, du, dout);
+    switch (shadeClassOf(c->nodes.data(), bsdf)) {
+    case SHADE_LAMBERT: launchBsdfSample<SHADE_LAMBERT>(c->ds, bsdf, n, ds_, dwi, du, dout, st); break;
+    case SHADE_LEAF: launchBsdfSample<SHADE_LEAF>(c->ds, bsdf, n, ds_, dwi, du, dout, st); break;
+    default: launchBsdfSample<SHADE_GENERIC>(c->ds, bsdf, n, ds_, dwi, du, dout, st); break;
+    }
     CUDA_TRY(cudaMemcpyAsync(out, dout, sizeof(float) * 12 * n, cudaMemcpyDeviceToHost, st));
     return syncCheck(c, "bsdf_sample");
 }
@@ -1104,6 +1268,39 @@ MTS_API int mtscuda_eval_environment(MtsContext *c, int64_t n, const float *d, f
     k_hook_eval_env<<<gridFor(n), 128, 0, st>>>(c->ds, n, dd, dout);
     CUDA_TRY(cudaMemcpyAsync(out, dout, sizeof(float) * 4 * n, cudaMemcpyDeviceToHost, st));
     return syncCheck(c, "eval_environment");
+}
+
+MTS_API int mtscuda_texture_eval(MtsContext *c, int32_t tex, int64_t n, const float *uv, const float *duv, float *out) {
+    if (tex < 0 || tex >= (int)c->textures.size()) return fail(MTS_EINVAL, "bad texture index");
+    HOOK_PREAMBLE(true)
+    float *duv_ = sg.in(uv, 2 * n, st), *dd = duv ? sg.in(duv, 4 * n, st) : nullptr, *dout = sg.out<float>(3 * n);
+    NEED(duv_ && dout && (!duv || dd));
+    k_hook_texture_eval<<<gridFor(n), 128, 0, st>>>(c->ds, tex, n, duv_, dd, dout);
+    CUDA_TRY(cudaMemcpyAsync(out, dout, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, st));
+    return syncCheck(c, "texture_eval");
+}
+
+MTS_API int mtscuda_hit_partials(MtsContext *c, int64_t n, const float *sample_pos, int32_t sample_count, float *out) {
+    if (sample_count <= 0) return fail(MTS_EINVAL, "sample_count must be positive");
+    HOOK_PREAMBLE(true)
+    if (!c->hasCam) return fail(MTS_ESTATE, "no camera set");
+    c->ds.cam = c->cam;
+    float *dsp = sg.in(sample_pos, 2 * n, st), *dout = sg.out<float>(8 * n); NEED(dsp && dout);
+    k_hook_hit_partials<<<gridFor(n), 128, 0, st>>>(c->ds, n, dsp, 1.0f / std::sqrt((float)sample_count), dout);
+    CUDA_TRY(cudaMemcpyAsync(out, dout, sizeof(float) * 8 * n, cudaMemcpyDeviceToHost, st));
+    return syncCheck(c, "hit_partials");
+}
+
+MTS_API int mtscuda_eval_environment_camera(MtsContext *c, int64_t n, const float *sample_pos, int32_t sample_count, float *out) {
+    if (sample_count <= 0) return fail(MTS_EINVAL, "sample_count must be positive");
+    HOOK_PREAMBLE(true)
+    if (!c->hasCam) return fail(MTS_ESTATE, "no camera set");
+    if (!c->ds.hasEnv) return fail(MTS_ESTATE, "the scene has no environment emitter");
+    c->ds.cam = c->cam;
+    float *dsp = sg.in(sample_pos, 2 * n, st), *dout = sg.out<float>(3 * n); NEED(dsp && dout);
+    k_hook_eval_env_camera<<<gridFor(n), 128, 0, st>>>(c->ds, n, dsp, 1.0f / std::sqrt((float)sample_count), dout);
+    CUDA_TRY(cudaMemcpyAsync(out, dout, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, st));
+    return syncCheck(c, "eval_environment_camera");
 }
 
 MTS_API int mtscuda_splat(MtsContext *c, int64_t n, const float *pos, const float *value, int32_t clear_first) {

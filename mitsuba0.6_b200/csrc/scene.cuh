@@ -4,13 +4,19 @@
 
 namespace mts {
 
-// Bitmap texture, level 0 only (TMIPMap stores half precision; 3-channel texels are padded to
-// half4 so one bilinear tap is one aligned 8-byte load).
+// Bitmap texture = TMIPMap (include/mitsuba/render/mipmap.h): half-precision texels like the reference stores them;
+// 3-channel texels are padded to half4 so one bilinear tap is one aligned 8-byte load.  Level 0 starts at `texels`;
+// ewa / trilinear textures carry the whole pyramid (level l at texel offset levelOffset[l], row-major).
 struct DTexture {
     const __half *texels;
     int width, height, channels;  // channels: 1 or 3 (3 -> stored as 4 halves)
     int wrapU, wrapV, filter;
     float2 uvScale, uvOffset;
+    int levels;                   // 1 for nearest / bilinear
+    float maxAnisotropy;
+    const float *weightLut;       // EWA Gaussian weight table, MTS_MIPMAP_LUT_SIZE entries (mipmap.h:296-302)
+    uint32_t levelOffset[MTS_MAX_MIP_LEVELS];
+    uint16_t levelW[MTS_MAX_MIP_LEVELS], levelH[MTS_MAX_MIP_LEVELS];
 };
 
 constexpr int kGuideRows = 256, kGuideCols = 64;
@@ -18,6 +24,8 @@ enum { SHAPE_MESH = 0, SHAPE_RECT = 1, SHAPE_SPHERE = 2 };
 
 struct DShape {
     int type, bsdf, emitter, flip;
+    uint32_t sortKey;                             // material sort key of the root BSDF (1 + rank in shade-class order)
+    uint32_t pad0[3];
     // mesh: offsets into the concatenated vertex / triangle arrays
     uint32_t vtxOffset, triOffset, ntris, flags;  // flags: 1 normals, 2 uvs, 4 tangents
     uint32_t cdfOffset;                           // area CDF (ntris+1 floats) when the mesh is an emitter
@@ -47,6 +55,8 @@ struct DEnvmap {
     float3 bsCenter; float bsRadius;
     int emitterIndex;
     float prob;
+    const DTexture *mip;     // (device memory) the same texels as a MIP map (repeat-u / clamp-v, EWA, maxAnisotropy 10; envmap.cpp:138-182):
+                             // camera rays carry differentials and are looked up filtered (:391-407)
 };
 
 // Eight-wide BVH node with quantised child boxes, 80 bytes = five 16-byte loads per visit (the layout of
@@ -69,11 +79,17 @@ struct WideNode {
 //   analytic: p0.w = shape, p2.w = 1 (rectangle) / 2 (sphere)
 struct PrimRecord { float4 p0, p1, p2; };
 
-struct DScene {
-    // materials
-    const MtsBsdfNode *nodes; int numNodes;
-    const DTexture *textures; int numTextures;
+// What the BSDF code reads of the scene.  Passed BY VALUE (three pointers in registers) into the BSDF functions: a
+// reference to the kernel-parameter DScene handed to a non-inlined function would make the compiler copy the whole
+// scene descriptor into every thread's local memory.
+struct Mats {
+    const MtsBsdfNode *nodes;
+    const DTexture *textures;
     const float *pool;
+};
+
+struct DScene : Mats {
+    int numNodes, numTextures;
     // geometry
     const DShape *shapes; int numShapes;
     const float *positions;   // 3 floats / vertex

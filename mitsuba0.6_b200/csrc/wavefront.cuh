@@ -34,11 +34,12 @@ struct Wavefront {
     float4 *shO, *shD, *shC; // shadow ray origin/dir (+mint/maxt), contribution rgb + path slot
     uint32_t *queue[2];
     uint32_t *doneQ;
-    // material sort of the active queue: key 0 = miss, 1 + root BSDF node otherwise
+    // material sort of the active queue: key 0 = miss, DShape::sortKey otherwise (root BSDFs ordered by shade class)
     uint32_t *keys;          // per queue position, written by intersect
     uint32_t *sorted;        // queue[cur] reordered by key; what shade consumes
     uint32_t *keyCount;      // numKeys histogram, then numKeys offsets, then numKeys cursors
     uint32_t numKeys;
+    uint32_t classKey[SHADE_CLASSES + 1];   // sort keys [classKey[c], classKey[c+1]) belong to shade class c (key 0 = miss)
     Counters *ctr;
     uint32_t capacity;
 };
@@ -49,6 +50,7 @@ struct RenderConst {
     int sampleOffset, sampleStride;
     int tilesX, tilesY;      // 8x4 pixel tiles
     uint32_t paddedPixels;   // tilesX*tilesY*32
+    float diffScale;         // 1/sqrt(sampler sample count): RayDifferential::scaleDifferential, integrator.cpp:144-145,181
 };
 
 enum { PF_SCATTERED = 1, PF_PREV_DELTA = 2, PF_PREV_REFN_OK = 4,
@@ -68,11 +70,44 @@ DEVFN uint32_t warpAppend(uint32_t *counter, bool pred) {
 }
 
 DEVFN Surf surfOf(const Hit &h) {
-    Surf s; s.uv = h.uv; s.dpdu = h.dpdu; s.dpdv = h.dpdv; s.geoN = h.geoN; s.sh = h.sh; s.bumpNode = -1; return s;
+    Surf s; s.tc = texCtx(h.uv); s.dpdu = h.dpdu; s.dpdv = h.dpdv; s.geoN = h.geoN; s.sh = h.sh; s.bumpNode = -1; return s;
+}
+
+// The camera ray through `samplePos` with its differentials scaled like SamplingIntegrator::renderBlock does
+// (sampleRayDifferential, perspective.cpp:271-297; scaleDifferential, ray.h:163-168).  Origins coincide with o.
+DEVFN void cameraRayDiff(const MtsCamera &cam, float2 samplePos, float diffScale, float3 &o, float3 &d, float3 &rxD, float3 &ryD) {
+    float mint, maxt;
+    cameraRay(cam, samplePos, o, d, mint, maxt, &rxD, &ryD);
+    rxD = d + (rxD - d) * diffScale;
+    ryD = d + (ryD - d) * diffScale;
+}
+
+// Intersection::computePartials (src/librender/intersection.cpp:5-76): uv partials wrt. the screen position from the
+// offset rays' intersections with the tangent plane.  Returns dudx dvdx dudy dvdy.
+DEVFN float4 computePartials(float3 p, float3 n, float3 dpdu, float3 dpdv, float3 o, float3 rxD, float3 ryD) {
+    if (isZero(dpdu) && isZero(dpdv)) return make_float4(0, 0, 0, 0);
+    const float pp = dot(n, p), po = dot(n, o), prx = dot(n, rxD), pry = dot(n, ryD);
+    if (prx == 0 || pry == 0) return make_float4(0, 0, 0, 0);
+    const float tx = (pp - po) / prx, ty = (pp - po) / pry;
+    const float ax = fabsf(n.x), ay = fabsf(n.y), az = fabsf(n.z);
+    int a0, a1;
+    if (ax > ay && ax > az) { a0 = 1; a1 = 2; } else if (ay > az) { a0 = 0; a1 = 2; } else { a0 = 0; a1 = 1; }
+    auto comp = [](float3 v, int a) { return a == 0 ? v.x : a == 1 ? v.y : v.z; };
+    const float A00 = comp(dpdu, a0), A01 = comp(dpdv, a0), A10 = comp(dpdu, a1), A11 = comp(dpdv, a1);
+    const float3 px = o + rxD * tx, py = o + ryD * ty;
+    const float bx0 = comp(px, a0) - comp(p, a0), bx1 = comp(px, a1) - comp(p, a1);
+    const float by0 = comp(py, a0) - comp(p, a0), by1 = comp(py, a1) - comp(p, a1);
+    const float det = A00 * A11 - A01 * A10;
+    // solveLinearSystem2x2 (src/libcore/util.cpp:527-539); the failure values are the reference's (:64-74, including
+    // its `dudy = 0; dudy = 1` slip, which leaves dvdy at its initial 0)
+    if (fabsf(det) <= 2.93873587705571876e-39f) return make_float4(1, 0, 1, 0);
+    const float inv = 1.0f / det;
+    return make_float4((A11 * bx0 - A01 * bx1) * inv, (A00 * bx1 - A10 * bx0) * inv,
+                       (A11 * by0 - A01 * by1) * inv, (A00 * by1 - A10 * by0) * inv);
 }
 
 // ---- raygen: SamplingIntegrator::renderBlock sample loop + sampleRayDifferential -------------
-__global__ void __launch_bounds__(256) k_raygen(const DScene S, const Wavefront W, const RenderConst R,
+static __global__ void __launch_bounds__(256) k_raygen(const DScene S, const Wavefront W, const RenderConst R,
                                                 unsigned long long firstItem, uint32_t count, int qsel) {
     for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < ((count + 31u) & ~31u); j += gridDim.x * blockDim.x) {
         bool valid = j < count;
@@ -168,7 +203,7 @@ DEVFN void traceQueue(const DScene &S, uint32_t count, uint32_t *cursor, TraceCo
 // ---- intersect: Scene::rayIntersect -> ShapeKDTree::rayIntersect(ray, its) --------------------
 // Also emits the shade sort key of every ray (0 = escaped, 1 + BSDF root of the hit shape) and its histogram.
 template <bool COUNT>
-__global__ void __launch_bounds__(128, TRACE_MINB) k_intersect(const DScene S, const Wavefront W, int qsel) {
+static __global__ void __launch_bounds__(128, TRACE_MINB) k_intersect(const DScene S, const Wavefront W, int qsel) {
     const uint32_t count = W.ctr->qCount[qsel];
     TraceCounters tc = {0, 0};
     const uint32_t *queue = W.queue[qsel];
@@ -185,7 +220,7 @@ __global__ void __launch_bounds__(128, TRACE_MINB) k_intersect(const DScene S, c
             uint32_t key = 0;
             if (h.prim >= 0) {
                 int shape = __float_as_int(__ldg(reinterpret_cast<const float4 *>(S.prims + h.prim)).w);
-                key = 1u + (uint32_t)S.shapes[shape].bsdf;
+                key = S.shapes[shape].sortKey;
             }
             W.keys[i] = key;
             keyedAppend(W.keyCount, key);   // lanes finishing in the same step share one atomicAdd per key
@@ -195,7 +230,7 @@ __global__ void __launch_bounds__(128, TRACE_MINB) k_intersect(const DScene S, c
 
 // ---- shadow: ShapeKDTree::rayIntersect(ray) for Scene::sampleEmitterDirect --------------------
 template <bool COUNT>
-__global__ void __launch_bounds__(128, TRACE_MINB) k_shadow(const DScene S, const Wavefront W) {
+static __global__ void __launch_bounds__(128, TRACE_MINB) k_shadow(const DScene S, const Wavefront W) {
     const uint32_t count = W.ctr->shadowCount;
     TraceCounters tc = {0, 0};
     traceQueue<true, COUNT>(S, count, &W.ctr->cursor[1], &tc,
@@ -216,7 +251,7 @@ __global__ void __launch_bounds__(128, TRACE_MINB) k_shadow(const DScene S, cons
 }
 
 // ---- material sort: counting sort of the active queue by key (histogram from intersect) --------
-__global__ void k_sort_offsets(const Wavefront W) {
+static __global__ void k_sort_offsets(const Wavefront W) {
     // one warp; numKeys is small (BSDF nodes + 1)
     uint32_t *cnt = W.keyCount, *off = W.keyCount + W.numKeys, *cur = W.keyCount + 2 * W.numKeys;
     uint32_t carry = 0;
@@ -229,7 +264,7 @@ __global__ void k_sort_offsets(const Wavefront W) {
         carry += __shfl_sync(0xffffffffu, incl, 31);
     }
 }
-__global__ void __launch_bounds__(256) k_sort_scatter(const Wavefront W, int qsel) {
+static __global__ void __launch_bounds__(256) k_sort_scatter(const Wavefront W, int qsel) {
     const uint32_t count = W.ctr->qCount[qsel];
     const uint32_t rounded = (count + 31u) & ~31u;
     const uint32_t *off = W.keyCount + W.numKeys;
@@ -245,6 +280,7 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const Wavefront W, int qse
 // ---- shade: one iteration of the Li loop ----------------------------------------------------
 struct ShadeOut { bool next, shadow, done; float4 shO, shD, shC; };
 
+template <int CLASS>
 DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, uint32_t slot, ShadeOut &out) {
     out.next = false; out.shadow = false; out.done = true;
     float4 ro = W.rayO[slot], rd = W.rayD[slot], hv = W.hit[slot];
@@ -295,7 +331,17 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
 
     const int bsdf = shape.bsdf;
     const uint32_t lobes = S.nodes[bsdf].lobes;
-    const Surf su = surfOf(its);
+    Surf su = surfOf(its);
+    if (first && (S.nodes[bsdf].flags & MTS_BF_RAY_DIFF)) {
+        // Intersection::getBSDF(ray) (records.inl:69-75): only the camera ray carries differentials (path.cpp:225 drops them)
+        const float4 us = rand4(R.seed, meta.x, meta.y, 0);
+        const int x = (int)(meta.x % (uint32_t)S.filmW), y = (int)(meta.x / (uint32_t)S.filmW);
+        float3 co, cd, rxD, ryD;
+        cameraRayDiff(S.cam, make_float2(x + us.x, y + us.y), R.diffScale, co, cd, rxD, ryD);
+        su.tc.duv = computePartials(its.p, its.geoN, its.dpdu, its.dpdv, co, rxD, ryD);
+        su.tc.filtered = true;
+    }
+    const Material<CLASS> mat(S, bsdf, su, its.wi);
     float uExtra;
     float4 u = rand4x(R.seed, meta.x, meta.y, 2 * depth - 1, uExtra);
 
@@ -307,12 +353,12 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
         float3 value = sampleEmitterDirect(S, dr, make_float2(u.x, u.y));
         if (!isZero(value)) {
             float3 wo = its.sh.toLocal(dr.d);
-            float3 bsdfVal = BsdfRoot::eval(S, bsdf, su, its.wi, wo, MTS_MEASURE_SOLID_ANGLE);
+            // area and environment emitters are "on surface"; the point emitter is not
+            const bool wantPdf = S.emitters[dr.emitter].type != MTS_EMITTER_POINT && dr.measure == MTS_MEASURE_SOLID_ANGLE;
+            float bsdfPdf;
+            float3 bsdfVal = mat.evalPdf(its.wi, wo, MTS_MEASURE_SOLID_ANGLE, wantPdf ? PDF_IF_LIT : PDF_NONE, bsdfPdf);
             if (!isZero(bsdfVal) && (!R.strictNormals || dot(its.geoN, dr.d) * cosTheta(wo) > 0)) {
-                // area and environment emitters are "on surface"; the point emitter is not
-                bool onSurface = S.emitters[dr.emitter].type != MTS_EMITTER_POINT;
-                float bsdfPdf = (onSurface && dr.measure == MTS_MEASURE_SOLID_ANGLE)
-                    ? BsdfRoot::pdf(S, bsdf, su, its.wi, wo, MTS_MEASURE_SOLID_ANGLE) : 0.0f;
+                if (!wantPdf) bsdfPdf = 0.0f;
                 float3 c = thr * value * bsdfVal * miWeight(dr.pdf, bsdfPdf);
                 out.shadow = true;
                 out.shO = make_float4(dr.ref.x, dr.ref.y, dr.ref.z, kEps);
@@ -325,7 +371,7 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
     // ---- BSDF sampling (path.cpp:203-253) ----
     BSample bs; bs.pdf = 0; bs.eta = 1; bs.type = 0; bs.wo = f3(0.0f);
     bs.u3 = uExtra;   // EUsesSampler models (roughdielectric.cpp:405 bRec.sampler->next1D()): spare bits of the same Philox draw
-    float3 bsdfWeight = BsdfRoot::sample(S, bsdf, su, its.wi, make_float2(u.z, u.w), bs);
+    float3 bsdfWeight = mat.sample(its.wi, make_float2(u.z, u.w), bs);
     if (isZero(bsdfWeight)) { finish(); return; }
     if (bs.type != MTS_ENULL) flags |= PF_SCATTERED;   // path.cpp:213
     const float3 wo = its.sh.toWorld(bs.wo);
@@ -349,7 +395,7 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
 // Escaped rays (sort key 0) are shaded by their own small kernel: no hit record, no BSDF code, 40 registers, full
 // occupancy -- after the first bounce three of four rays of an outdoor scene end here.
 // path.cpp:136-143 (camera ray) / :238-248,257-264 (BSDF-sampled ray escaping to the envmap)
-__global__ void __launch_bounds__(256) k_shade_miss(const DScene S, const Wavefront W, const RenderConst R, int qsel) {
+static __global__ void __launch_bounds__(256) k_shade_miss(const DScene S, const Wavefront W, const RenderConst R, int qsel) {
     const uint32_t total = W.ctr->qCount[qsel];
     const uint32_t count = W.numKeys > 1 ? min(W.keyCount[W.numKeys + 1], total) : total;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ((count + 31u) & ~31u); i += gridDim.x * blockDim.x) {
@@ -370,7 +416,12 @@ __global__ void __launch_bounds__(256) k_shade_miss(const DScene S, const Wavefr
                 const float3 thr = f3(W.thr[slot]);
                 float3 L = f3(lv);
                 if (first) {
-                    L += thr * envEval(S.env, d);
+                    // Emitter::evalEnvironment(RayDifferential) of the camera ray: EWA lookup (envmap.cpp:380-410)
+                    const float4 us = rand4(R.seed, meta.x, meta.y, 0);
+                    const int x = (int)(meta.x % (uint32_t)S.filmW), y = (int)(meta.x / (uint32_t)S.filmW);
+                    float3 co, cd, rxD, ryD;
+                    cameraRayDiff(S.cam, make_float2(x + us.x, y + us.y), R.diffScale, co, cd, rxD, ryD);
+                    L += thr * envEvalDiff(S, S.env, d, rxD, ryD);
                 } else {
                     const float3 o = f3(W.rayO[slot]);
                     float nearT, farT;  // fillDirectSamplingRecord, envmap.cpp:358-374
@@ -389,17 +440,29 @@ __global__ void __launch_bounds__(256) k_shade_miss(const DScene S, const Wavefr
     }
 }
 
-template <int MINB>
-__global__ void __launch_bounds__(128, MINB) k_shade(const DScene S, const Wavefront W, const RenderConst R, int qsel) {
+// One instance per shade class; the class's paths are the contiguous range of the sorted queue whose keys lie in
+// [classKey[CLASS], classKey[CLASS + 1]).
+template <int CLASS> struct ShadeLaunch;
+template <> struct ShadeLaunch<SHADE_LAMBERT> { static constexpr int kThreads = 128, kMinBlocks = 5; };
+template <> struct ShadeLaunch<SHADE_LEAF>    { static constexpr int kThreads = 128, kMinBlocks = 4; };
+template <> struct ShadeLaunch<SHADE_GENERIC> { static constexpr int kThreads = 128, kMinBlocks = 4; };
+
+DEVFN uint32_t sortedBegin(const Wavefront &W, uint32_t key, uint32_t count) {   // first queue position with sort key >= key
+    return key < W.numKeys ? min(W.keyCount[W.numKeys + key], count) : count;
+}
+
+template <int CLASS>
+static __global__ void __launch_bounds__(ShadeLaunch<CLASS>::kThreads, ShadeLaunch<CLASS>::kMinBlocks)
+k_shade(const DScene S, const Wavefront W, const RenderConst R, int qsel) {
     const uint32_t count = W.ctr->qCount[qsel];
-    const uint32_t firstHit = W.numKeys > 1 ? min(W.keyCount[W.numKeys + 1], count) : count;   // keys >= 1; key 0 -> k_shade_miss
-    const uint32_t rounded = firstHit + ((count - firstHit + 31u) & ~31u);
-    for (uint32_t i = firstHit + blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
+    const uint32_t first = sortedBegin(W, W.classKey[CLASS], count), last = sortedBegin(W, W.classKey[CLASS + 1], count);
+    const uint32_t rounded = first + ((last - first + 31u) & ~31u);
+    for (uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
         ShadeOut out; out.next = out.shadow = out.done = false;
         uint32_t slot = 0;
-        if (i < count) {
+        if (i < last) {
             slot = W.sorted[i];
-            shadePath(S, W, R, slot, out);
+            shadePath<CLASS>(S, W, R, slot, out);
         }
         uint32_t a = warpAppend(&W.ctr->qCount[qsel ^ 1], out.next);
         if (out.next) W.queue[qsel ^ 1][a] = slot;
@@ -436,7 +499,7 @@ DEVFN void splatSample(const DScene &S, float2 samplePos, float3 value, float al
         }
     }
 }
-__global__ void __launch_bounds__(256) k_splat(const DScene S, const Wavefront W, const RenderConst R) {
+static __global__ void __launch_bounds__(256) k_splat(const DScene S, const Wavefront W, const RenderConst R) {
     const uint32_t count = W.ctr->doneCount;
     unsigned long long lenSum = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
@@ -454,17 +517,17 @@ __global__ void __launch_bounds__(256) k_splat(const DScene S, const Wavefront W
 
 // Bounce bookkeeping on the device (the host never reads a counter inside the bounce loop): add the rays of the
 // bounce that is about to run (closest hit) and of the one that just ran (shadow) to the totals, reset the queues.
-__global__ void k_begin_bounce(Counters *c, int cur) {
+static __global__ void k_begin_bounce(Counters *c, int cur) {
     c->normalRays += c->qCount[cur]; c->shadowRays += c->shadowCount;
     c->qCount[cur ^ 1] = 0; c->shadowCount = 0; c->doneCount = 0; c->cursor[0] = c->cursor[1] = 0;
 }
-__global__ void k_begin_wavefront(Counters *c) {
+static __global__ void k_begin_wavefront(Counters *c) {
     c->shadowRays += c->shadowCount;
     c->qCount[0] = c->qCount[1] = 0; c->shadowCount = 0; c->doneCount = 0; c->cursor[0] = c->cursor[1] = 0;
 }
 // Safety net of unbounded renders (maxDepth = -1 with Russian roulette pushed out of reach): the paths still alive
 // when the host gives up are finished with what they have gathered so far and splatted, never dropped.
-__global__ void __launch_bounds__(256) k_abandon(const Wavefront W, int qsel) {
+static __global__ void __launch_bounds__(256) k_abandon(const Wavefront W, int qsel) {
     const uint32_t count = W.ctr->qCount[qsel];
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ((count + 31u) & ~31u); i += gridDim.x * blockDim.x) {
         const bool valid = i < count;

@@ -409,18 +409,18 @@ class FlatScene:
         elif gamma is not None and float(gamma) not in (1.0,) and kind == "srgb":
             img = np.power(img, F(gamma))
         ft = p.get("filterType", "ewa").lower()
-        if ft not in abi.FILTER:
-            raise Unsupported("bitmap filterType '%s' is not supported yet (in scope this round: bilinear, "
-                              "nearest; EWA/trilinear pre-filtering of primary hits is a 'next' row)" % ft)
+        if ft not in abi.FILTER:   # bitmap.cpp:220-231
+            raise ValueError("Unknown filter type '%s' -- must be 'ewa', 'trilinear', or 'nearest'!" % ft)
+        max_aniso = float(p.get("maxAnisotropy", 20.0)) if ft == "ewa" else 1.0   # bitmap.cpp:230-233
         wm = p.get("wrapMode", "repeat")
         uvscale = p.get("uvscale", 1.0)
         d = abi.TextureDesc(img.shape[1], img.shape[0], img.shape[2],
                             abi.WRAP[p.get("wrapModeU", wm)], abi.WRAP[p.get("wrapModeV", wm)], abi.FILTER[ft],
                             (abi.C.c_float * 2)(p.get("uscale", uvscale), p.get("vscale", uvscale)),
-                            (abi.C.c_float * 2)(p.get("uoffset", 0.0), p.get("voffset", 0.0)))
+                            (abi.C.c_float * 2)(p.get("uoffset", 0.0), p.get("voffset", 0.0)), max_aniso)
         if p.get("channel") is not None:
             raise Unsupported("bitmap `channel` selection is not supported")
-        half = img.astype(np.float16).astype(F)  # TMIPMap stores half (mipmap.h)
+        half = np.maximum(img, 0).astype(np.float16).astype(F)  # TMIPMap stores half and clamps negative texels (mipmap.h:228-236)
         stats = dict(min=half.reshape(-1, img.shape[2]).min(0), max=half.reshape(-1, img.shape[2]).max(0),
                      avg=half.reshape(-1, img.shape[2]).astype(np.float64).mean(0))
         for k in stats:
@@ -685,7 +685,24 @@ class FlatScene:
             n.lobes = ((front & ~abi.EBACKSIDE) | abi.EFRONTSIDE) | ((back & ~abi.EFRONTSIDE) | abi.EBACKSIDE)
             if n.lobes & abi.ETRANSMISSION:
                 raise ValueError("Only materials without a transmission component can be nested!")
+        if self._uses_ray_differentials(n):
+            n.flags |= abi.BF_RAY_DIFF
         return idx
+
+    def _uses_ray_differentials(self, n):
+        """BSDF::usesRayDifferentials() as every plugin's configure() computes it: a bitmap texture always asks for
+        them (src/textures/bitmap.cpp:541-543), constants never (include/mitsuba/hw/basicshader.h:72); bumpmap always
+        (bumpmap.cpp:96); blendbsdf / mask / twosided only look at the nested BSDFs (blendbsdf.cpp:130, mask.cpp:108,
+        twosided.cpp:91-92), not at their own weight / opacity texture."""
+        kids = any(self.nodes[c].flags & abi.BF_RAY_DIFF for c in n.child if c >= 0)
+        if n.type == abi.BSDF_BUMPMAP:
+            return True
+        if n.type in (abi.BSDF_BLEND, abi.BSDF_MASK, abi.BSDF_TWOSIDED):
+            return kids
+        own = any(r.tex >= 0 for r in (n.t0, n.t1, n.t2))
+        if n.type == abi.BSDF_ROUGHDIELECTRIC:
+            own = own or n.lut[0] >= 0      # specularTransmittance lives in the k / lut slots
+        return own or kids
 
     def uses_uv_tangents(self, node):
         """bumpmap forces UV tangents / anisotropic models want them; TriMesh::configure computes them

@@ -60,7 +60,8 @@ struct Emitter {
     float weight = 1, scale = 1;
     M44 toWorld, toLocal;
     int w = 0, h = 0;
-    std::vector<float> tex;                       /* w*h*3, half-rounded */
+    std::vector<float> tex;                       /* w*h*3, half-rounded (= mip level 0) */
+    MipMap mip;                                   /* m_mipmap: EWA pyramid for camera rays with differentials */
     std::vector<float> cdfRows, cdfCols, rowWeights;
     float normalization = 0;
     V3 bsCenter; float bsRadius = 0;              /* m_sceneBSphere */
@@ -489,6 +490,15 @@ V3 envEval(const Emitter &e, V3 dWorld) {
            envTexel(e, xPos + 1, yPos) * dx1 * dy2 + envTexel(e, xPos + 1, yPos + 1) * dx1 * dy1;
     return r * e.scale;
 }
+/* evalEnvironment of a ray with differentials (:391-407) */
+V3 envEvalDiff(const Emitter &e, V3 dWorld, V3 rxD, V3 ryD) {
+    V3 v = e.toLocal.vec(dWorld);
+    V2 uv{std::atan2(v.x, -v.z) * kInvTwoPi, safe_acos(v.y) * kInvPi};
+    V3 dvdx = e.toLocal.vec(rxD) - v, dvdy = e.toLocal.vec(ryD) - v;
+    float t1 = kInvTwoPi / (v.x * v.x + v.z * v.z), t2 = -kInvPi / std::max(safe_sqrt(1.0f - v.y * v.y), kEps);
+    V2 dudx{t1 * (dvdx.z * v.x - dvdx.x * v.z), t2 * dvdx.y}, dudy{t1 * (dvdy.z * v.x - dvdy.x * v.z), t2 * dvdy.y};
+    return e.mip.eval(uv, dudx, dudy) * e.scale;
+}
 /* BSphere::rayIntersect (include/mitsuba/core/bsphere.h:88-95) */
 bool bsphereIntersect(const Emitter &e, V3 o, V3 d, float &nearT, float &farT) {
     V3 oc = o - e.bsCenter;
@@ -577,6 +587,47 @@ void sampleRay(const MtsCamera &cam, V2 samplePos, V3 &o, V3 &d, float &mint, fl
     if (ry) *ry = c2w.vec(normalize(nearP + V3(cam.dy[0], cam.dy[1], cam.dy[2])));
 }
 
+/* The offset rays of a camera ray after RayDifferential::scaleDifferential (ray.h:163-168; integrator.cpp:144-145,181) */
+struct RayDiff { bool has = false; V3 o, rxD, ryD; };
+RayDiff sampleRayDiff(const MtsCamera &cam, V2 samplePos, float scale) {
+    RayDiff r; V3 d, rx, ry; float mint, maxt;
+    sampleRay(cam, samplePos, r.o, d, mint, maxt, &rx, &ry);
+    r.rxD = d + (rx - d) * scale; r.ryD = d + (ry - d) * scale; r.has = true;
+    return r;
+}
+inline float diffScaleOf(const MtsRenderParams &P) {
+    int n = P.sample_count > 0 ? P.sample_count : P.spp * (P.sample_stride > 0 ? P.sample_stride : 1);
+    return 1.0f / std::sqrt((float)n);
+}
+inline float comp(V3 v, int a) { return a == 0 ? v.x : a == 1 ? v.y : v.z; }
+/* Intersection::computePartials (src/librender/intersection.cpp:5-76) */
+void computePartials(Its &its, const RayDiff &ray) {
+    if (its.hasUVPartials || !ray.has) return;
+    its.hasUVPartials = true;
+    if (isZero(its.dpdu) && isZero(its.dpdv)) { its.dudx = its.dvdx = its.dudy = its.dvdy = 0.0f; return; }
+    const V3 n = its.geo.n;
+    const float pp = dot(n, its.p), pox = dot(n, ray.o), poy = dot(n, ray.o), prx = dot(n, ray.rxD), pry = dot(n, ray.ryD);
+    if (prx == 0 || pry == 0) { its.dudx = its.dvdx = its.dudy = its.dvdy = 0.0f; return; }
+    const float tx = (pp - pox) / prx, ty = (pp - poy) / pry;
+    float absX = std::fabs(n.x), absY = std::fabs(n.y), absZ = std::fabs(n.z);
+    int a0, a1;
+    if (absX > absY && absX > absZ) { a0 = 1; a1 = 2; } else if (absY > absZ) { a0 = 0; a1 = 2; } else { a0 = 0; a1 = 1; }
+    const float A00 = comp(its.dpdu, a0), A01 = comp(its.dpdv, a0), A10 = comp(its.dpdu, a1), A11 = comp(its.dpdv, a1);
+    const V3 px = ray.o + ray.rxD * tx, py = ray.o + ray.ryD * ty;
+    const float Bx0 = comp(px, a0) - comp(its.p, a0), Bx1 = comp(px, a1) - comp(its.p, a1);
+    const float By0 = comp(py, a0) - comp(its.p, a0), By1 = comp(py, a1) - comp(its.p, a1);
+    /* solveLinearSystem2x2 (src/libcore/util.cpp:527-539); RCPOVERFLOW = 2^-128 in single precision */
+    const float det = A00 * A11 - A01 * A10;
+    if (std::fabs(det) <= 2.93873587705571876e-39f) {
+        its.dudx = 1; its.dvdx = 0;
+        its.dudy = 1; /* intersection.cpp:72-74 assigns dudy twice (0, then 1); dvdy keeps its initial value */
+        return;
+    }
+    const float inverse = 1.0f / det;
+    its.dudx = (A11 * Bx0 - A01 * Bx1) * inverse; its.dvdx = (A00 * Bx1 - A10 * Bx0) * inverse;
+    its.dudy = (A11 * By0 - A01 * By1) * inverse; its.dvdy = (A00 * By1 - A10 * By0) * inverse;
+}
+
 inline float miWeight(float pdfA, float pdfB) { pdfA *= pdfA; pdfB *= pdfB; return pdfA / (pdfA + pdfB); }
 
 V3 emitterLe(const MtsContext &c, const Its &its, V3 d) { /* AreaLight::eval (area.cpp:104-109) */
@@ -586,7 +637,8 @@ V3 emitterLe(const MtsContext &c, const Its &its, V3 d) { /* AreaLight::eval (ar
 }
 
 /* MIPathTracer::Li (src/integrators/path/path.cpp:119-294) */
-V3 Li(MtsContext &c, const MtsRenderParams &P, V3 o, V3 d, float mint, float maxt, Rng &rng, int &depthOut, float *alphaOut = nullptr) {
+V3 Li(MtsContext &c, const MtsRenderParams &P, V3 o, V3 d, float mint, float maxt, Rng &rng, int &depthOut, float *alphaOut = nullptr,
+      RayDiff ray = RayDiff()) {
     Its its; V3 L(0.0f); bool scattered = false;
     Hit h;
     bool valid = sceneIntersect(c, o, d, mint, maxt, false, h);
@@ -597,11 +649,14 @@ V3 Li(MtsContext &c, const MtsRenderParams &P, V3 o, V3 d, float mint, float max
     const Emitter *env = c.envIndex >= 0 ? &c.emitters[c.envIndex] : nullptr;
     while (depth <= P.max_depth || P.max_depth < 0) {
         if (!valid) {
-            if (emittedOk && (!P.hide_emitters || scattered) && env) L += throughput * envEval(*env, d);
+            if (emittedOk && (!P.hide_emitters || scattered) && env)
+                L += throughput * (ray.has ? envEvalDiff(*env, d, ray.rxD, ray.ryD) : envEval(*env, d));   /* path.cpp:136-143 */
             break;
         }
         const Shape &shape = c.shapes[its.shape];
         const int bsdf = shape.bsdf;
+        /* Intersection::getBSDF(ray) (records.inl:69-75): partials only when the BSDF asks for ray differentials */
+        if (c.mat.nodes[bsdf].flags & MTS_BF_RAY_DIFF) computePartials(its, ray);
         const uint32_t lobes = c.mat.nodes[bsdf].lobes;
         if (shape.emitter >= 0 && emittedOk && (!P.hide_emitters || scattered)) L += throughput * emitterLe(c, its, -d);
         if ((depth >= P.max_depth && P.max_depth > 0) ||
@@ -639,8 +694,10 @@ V3 Li(MtsContext &c, const MtsRenderParams &P, V3 o, V3 d, float mint, float max
 
         bool hitEmitter = false; V3 value;
         o = its.p; d = wo;
+        ray.has = false;   /* `ray = Ray(its.p, wo, ray.time)` drops the differentials (path.cpp:225, ray.h:196-209) */
         valid = sceneIntersect(c, o, d, kEps, INFINITY, false, h);
         if (valid) {
+            its = Its();
             fillIts(c, o, d, h, its);
             if (c.shapes[its.shape].emitter >= 0) {
                 value = emitterLe(c, its, -d);
@@ -713,6 +770,7 @@ float triArea(V3 p0, V3 p1, V3 p2) { return 0.5f * length(cross(p1 - p0, p2 - p0
 /* ======================================================================== */
 extern "C" {
 
+MTS_API int32_t mtsoracle_abi_version(void) { return MTS_ABI_VERSION; }
 MTS_API const char *mtsoracle_last_error(void) { return g_err.c_str(); }
 
 MTS_API int mtsoracle_create(int, MtsContext **out) {
@@ -734,10 +792,9 @@ MTS_API int mtsoracle_set_film(MtsContext *c, const MtsFilm *f) {
 }
 MTS_API int mtsoracle_add_texture(MtsContext *c, const MtsTextureDesc *d, const float *texels) {
     if (d->channels != 1 && d->channels != 3) return fail(MTS_EINVAL, "texture channels must be 1 or 3");
+    if (d->filter < MTS_FILTER_NEAREST || d->filter > MTS_FILTER_EWA) return fail(MTS_EINVAL, "unknown texture filter type");
     Tex t; t.d = *d;
-    size_t n = (size_t)d->width * d->height * d->channels;
-    t.tx.resize(n);
-    for (size_t i = 0; i < n; ++i) t.tx[i] = roundToHalf(texels[i]);
+    t.mip.build(texels, d->width, d->height, d->channels, d->wrap_u, d->wrap_v, d->filter, d->max_anisotropy, 1.0f /* TMIPMap maxValue default */);
     c->mat.textures.push_back(std::move(t));
     return (int)c->mat.textures.size() - 1;
 }
@@ -787,8 +844,9 @@ MTS_API int mtsoracle_add_emitter(MtsContext *c, const MtsEmitterDesc *d) {
         if (c->envIndex >= 0) return fail(MTS_EINVAL, "only one environment emitter is allowed");
         e.toWorld = m44_from(d->to_world); e.toLocal = m44_inverse(e.toWorld);
         e.w = d->env_width; e.h = d->env_height;
-        size_t n = (size_t)e.w * e.h * 3; e.tex.resize(n);
-        for (size_t i = 0; i < n; ++i) e.tex[i] = roundToHalf(d->env_texels[i]);
+        /* envmap.cpp:138-182: EWA MIP map, repeat-u / clamp-v, maxAnisotropy 10, unbounded values */
+        e.mip.build(d->env_texels, e.w, e.h, 3, MTS_WRAP_REPEAT, MTS_WRAP_CLAMP, MTS_FILTER_EWA, 10.0f, INFINITY);
+        e.tex = e.mip.levels[0].tx;
         c->envIndex = (int)c->emitters.size();
     }
     c->emitters.push_back(std::move(e)); c->built = false;
@@ -910,6 +968,7 @@ MTS_API int mtsoracle_render(MtsContext *c, const MtsRenderParams *P, volatile c
 #endif
     std::vector<std::vector<float>> tfilm(nthreads), talpha(hasAlpha ? nthreads : 0);
     bool cancelled = false;
+    const float diffScale = diffScaleOf(*P);
 #pragma omp parallel reduction(+ : pathLen)
     {
         int tid = 0;
@@ -932,7 +991,7 @@ MTS_API int mtsoracle_render(MtsContext *c, const MtsRenderParams *P, volatile c
                     V3 o, d; float mint, maxt;
                     sampleRay(c->cam, samplePos, o, d, mint, maxt);
                     int depth; float alpha = 1.0f;
-                    V3 L = Li(*c, *P, o, d, mint, maxt, rng, depth, hasAlpha ? &alpha : nullptr);
+                    V3 L = Li(*c, *P, o, d, mint, maxt, rng, depth, hasAlpha ? &alpha : nullptr, sampleRayDiff(c->cam, samplePos, diffScale));
                     pathLen += depth;
                     splat(c->film, buf.data(), samplePos, L, abuf, alpha);
                 }
@@ -1018,6 +1077,7 @@ MTS_API int mtsoracle_hit_records(MtsContext *c, int64_t n, const float *rays, f
 
 static void surfToIts(const float *s, Its &its) {
     its.uv = V2{s[0], s[1]};
+    if (s[15] != 0.0f) { its.hasUVPartials = true; its.dudx = s[2]; its.dvdx = s[3]; its.dudy = s[7]; its.dvdy = s[11]; }
     its.dpdu = V3(s[4], s[5], s[6]); its.dpdv = V3(s[8], s[9], s[10]);
     V3 n(s[12], s[13], s[14]);
     its.geo = Frame(n);
@@ -1077,6 +1137,51 @@ MTS_API int mtsoracle_eval_environment(MtsContext *c, int64_t n, const float *d,
         V3 v = envEval(e, dir);
         out[4 * i] = v.x; out[4 * i + 1] = v.y; out[4 * i + 2] = v.z;
         out[4 * i + 3] = envPdfDirection(e, e.toLocal.vec(dir)) * emProb;
+    }
+    return MTS_OK;
+}
+MTS_API int mtsoracle_texture_eval(MtsContext *c, int32_t tex, int64_t n, const float *uv, const float *duv, float *out) {
+    if (tex < 0 || tex >= (int)c->mat.textures.size()) return fail(MTS_EINVAL, "bad texture index");
+    MtsTexRef r; r.scale[0] = r.scale[1] = r.scale[2] = 1.0f; r.tex = tex;
+    for (int64_t i = 0; i < n; ++i) {
+        Its its; its.uv = V2{uv[2 * i], uv[2 * i + 1]};
+        if (duv) { its.hasUVPartials = true; its.dudx = duv[4 * i]; its.dvdx = duv[4 * i + 1]; its.dudy = duv[4 * i + 2]; its.dvdy = duv[4 * i + 3]; }
+        V3 v = evalTex(c->mat, r, its);
+        out[3 * i] = v.x; out[3 * i + 1] = v.y; out[3 * i + 2] = v.z;
+    }
+    return MTS_OK;
+}
+MTS_API int mtsoracle_hit_partials(MtsContext *c, int64_t n, const float *sp, int32_t sample_count, float *out) {
+    if (!c->built) return fail(MTS_ESTATE, "hit_partials before build");
+    if (!c->hasCam) return fail(MTS_ESTATE, "no camera set");
+    if (sample_count <= 0) return fail(MTS_EINVAL, "sample_count must be positive");
+    const float scale = 1.0f / std::sqrt((float)sample_count);
+    for (int64_t i = 0; i < n; ++i) {
+        V2 pos{sp[2 * i], sp[2 * i + 1]};
+        V3 o, d; float mint, maxt;
+        sampleRay(c->cam, pos, o, d, mint, maxt);
+        float *q = out + 8 * i;
+        Hit h;
+        if (!sceneIntersect(*c, o, d, mint, maxt, false, h)) { for (int k = 0; k < 8; ++k) q[k] = 0; continue; }
+        Its its; fillIts(*c, o, d, h, its);
+        computePartials(its, sampleRayDiff(c->cam, pos, scale));
+        q[0] = its.dudx; q[1] = its.dvdx; q[2] = its.dudy; q[3] = its.dvdy; q[4] = its.t; q[5] = 1.0f; q[6] = its.uv.x; q[7] = its.uv.y;
+    }
+    return MTS_OK;
+}
+MTS_API int mtsoracle_eval_environment_camera(MtsContext *c, int64_t n, const float *sp, int32_t sample_count, float *out) {
+    if (!c->built || c->envIndex < 0) return fail(MTS_ESTATE, "the scene has no environment emitter");
+    if (!c->hasCam) return fail(MTS_ESTATE, "no camera set");
+    if (sample_count <= 0) return fail(MTS_EINVAL, "sample_count must be positive");
+    const float scale = 1.0f / std::sqrt((float)sample_count);
+    const Emitter &e = c->emitters[c->envIndex];
+    for (int64_t i = 0; i < n; ++i) {
+        V2 pos{sp[2 * i], sp[2 * i + 1]};
+        V3 o, d; float mint, maxt;
+        sampleRay(c->cam, pos, o, d, mint, maxt);
+        RayDiff rd = sampleRayDiff(c->cam, pos, scale);
+        V3 v = envEvalDiff(e, d, rd.rxD, rd.ryD);
+        out[3 * i] = v.x; out[3 * i + 1] = v.y; out[3 * i + 2] = v.z;
     }
     return MTS_OK;
 }

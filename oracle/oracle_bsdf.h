@@ -10,6 +10,7 @@
 #pragma once
 #include <vector>
 #include "oracle_math.h"
+#include "oracle_mipmap.h"
 #define MTS_PREFIX mtsoracle_
 #include "../include/mtscuda.h"
 
@@ -17,7 +18,7 @@ namespace orc {
 
 struct Tex {
     MtsTextureDesc d;
-    std::vector<float> tx; /* channels * w * h, values already rounded through half */
+    MipMap mip;   /* level 0 (+ the Lanczos pyramid for trilinear / ewa), values rounded through half */
 };
 
 /* Subset of `Intersection` (include/mitsuba/render/shape.h:36-172) */
@@ -28,6 +29,8 @@ struct Its {
     V3 dpdu, dpdv;
     V3 wi;
     int shape, prim;
+    bool hasUVPartials = false;                      /* shape.h:154-166: set by computePartials for camera-ray hits */
+    float dudx = 0, dvdx = 0, dudy = 0, dvdy = 0;
     V3 toLocal(V3 v) const { return sh.toLocal(v); }
     V3 toWorld(V3 v) const { return sh.toWorld(v); }
 };
@@ -38,59 +41,27 @@ struct Materials {
     std::vector<float> pool;
 };
 
-/* ---- TMIPMap level-0 lookups (include/mitsuba/render/mipmap.h:503-626) ---- */
-inline bool wrapCoord(int &x, int size, int mode, float &constant) {
-    if (x < 0 || x >= size) {
-        switch (mode) {
-            case MTS_WRAP_REPEAT: x = modulo(x, size); break;
-            case MTS_WRAP_CLAMP: x = clampi(x, 0, size - 1); break;
-            case MTS_WRAP_MIRROR: x = modulo(x, 2 * size); if (x >= size) x = 2 * size - x - 1; break;
-            case MTS_WRAP_ZERO: constant = 0.0f; return false;
-            case MTS_WRAP_ONE: constant = 1.0f; return false;
-        }
-    }
-    return true;
-}
-inline V3 evalTexel(const Tex &t, int x, int y) {
-    float c;
-    if (!wrapCoord(x, t.d.width, t.d.wrap_u, c)) return V3(c);
-    if (!wrapCoord(y, t.d.height, t.d.wrap_v, c)) return V3(c);
-    const float *p = &t.tx[((size_t)y * t.d.width + x) * t.d.channels];
-    return t.d.channels == 1 ? V3(p[0]) : V3(p[0], p[1], p[2]);
-}
-/* mipmap.h:575-596 evalBilinear(0, uv) / :566-569 evalBox */
+/* BitmapTexture::eval(uv) (src/textures/bitmap.cpp:431-454): unfiltered = bilinear at level 0, box for `nearest` */
 inline V3 texLookup(const Tex &t, V2 uv) {
-    if (t.d.filter == MTS_FILTER_NEAREST)
-        return evalTexel(t, floorToInt(uv.x * t.d.width), floorToInt(uv.y * t.d.height));
-    if (!std::isfinite(uv.x) || !std::isfinite(uv.y)) return V3(0.0f);
-    float u = uv.x * t.d.width - 0.5f, v = uv.y * t.d.height - 0.5f;
-    int xPos = floorToInt(u), yPos = floorToInt(v);
-    float dx1 = u - xPos, dx2 = 1.0f - dx1, dy1 = v - yPos, dy2 = 1.0f - dy1;
-    return evalTexel(t, xPos, yPos) * dx2 * dy2 + evalTexel(t, xPos, yPos + 1) * dx2 * dy1 +
-           evalTexel(t, xPos + 1, yPos) * dx1 * dy2 + evalTexel(t, xPos + 1, yPos + 1) * dx1 * dy1;
+    if (t.d.filter == MTS_FILTER_NEAREST) return t.mip.evalBox(0, uv);
+    return t.mip.evalBilinear(0, uv);
 }
-/* mipmap.h:601-626 evalGradientBilinear(0, uv) */
+/* BitmapTexture::evalGradient (bitmap.cpp:456-480) -> mipmap.h:601-626 evalGradientBilinear(0, uv) */
 inline void texGradient(const Tex &t, V2 uv, V3 grad[2]) {
-    if (t.d.filter == MTS_FILTER_NEAREST || !std::isfinite(uv.x) || !std::isfinite(uv.y)) {
-        grad[0] = grad[1] = V3(0.0f); return;
-    }
-    float u = uv.x * t.d.width - 0.5f, v = uv.y * t.d.height - 0.5f;
-    int xPos = floorToInt(u), yPos = floorToInt(v);
-    float dx = u - xPos, dy = v - yPos;
-    V3 p00 = evalTexel(t, xPos, yPos), p10 = evalTexel(t, xPos + 1, yPos);
-    V3 p01 = evalTexel(t, xPos, yPos + 1), p11 = evalTexel(t, xPos + 1, yPos + 1);
-    V3 tmp = p01 + p10 - p11;
-    grad[0] = (p10 + p00 * (dy - 1) - tmp * dy) * (float)t.d.width;
-    grad[1] = (p01 + p00 * (dx - 1) - tmp * dx) * (float)t.d.height;
+    if (t.d.filter == MTS_FILTER_NEAREST) { grad[0] = grad[1] = V3(0.0f); return; }
+    t.mip.evalGradientBilinear(uv, grad);
 }
 
-/* Texture2D::eval (src/librender/texture.cpp:104-114) + ScalingTexture (scale.cpp:86-88);
- * constants: basicshader.h:40,97.  No filtered lookups (bilinear filter type). */
+/* Texture2D::eval(its, filter = true) (src/librender/texture.cpp:104-114) + ScalingTexture (scale.cpp:86-88);
+ * constants: basicshader.h:40,97.  With uv partials the lookup goes through TMIPMap::eval (bitmap.cpp:486-499). */
 inline V3 evalTex(const Materials &m, const MtsTexRef &r, const Its &its) {
     V3 s(r.scale[0], r.scale[1], r.scale[2]);
     if (r.tex < 0) return s;
     const Tex &t = m.textures[r.tex];
     V2 uv{its.uv.x * t.d.uv_scale[0] + t.d.uv_offset[0], its.uv.y * t.d.uv_scale[1] + t.d.uv_offset[1]};
+    if (its.hasUVPartials)
+        return t.mip.eval(uv, V2{its.dudx * t.d.uv_scale[0], its.dvdx * t.d.uv_scale[1]},
+                          V2{its.dudy * t.d.uv_scale[0], its.dvdy * t.d.uv_scale[1]}) * s;
     return texLookup(t, uv) * s;
 }
 /* Texture2D::evalGradient (texture.cpp:116-124) + ScalingTexture::evalGradient (scale.cpp:90-94);

@@ -62,7 +62,7 @@ const Class *classOf(const std::string &kind) {
 }
 
 Intersection makeIts(const float *s) {
-    /* same convention as the `surf` arrays of include/mtscuda.h: uv(2) pad(2) dpdu(3) pad dpdv(3) pad n(3) pad */
+    /* same convention as the `surf` arrays of include/mtscuda.h: uv(2) dudx dvdx dpdu(3) dudy dpdv(3) dvdy n(3) hasUVPartials */
     Intersection its;
     its.p = Point(0.0f);
     its.t = 1.0f;
@@ -73,7 +73,8 @@ Intersection makeIts(const float *s) {
     its.geoFrame = Frame(n);
     its.shFrame.n = n;
     computeShadingFrame(its.shFrame.n, its.dpdu, its.shFrame);
-    its.hasUVPartials = false;
+    its.hasUVPartials = s[15] != 0.0f;
+    its.dudx = s[2]; its.dvdx = s[3]; its.dudy = s[7]; its.dvdy = s[11];
     its.time = 0;
     its.shape = NULL;
     its.primIndex = 0;
@@ -369,6 +370,54 @@ int mtsref_eval_environment(void *s, int64_t n, const float *d, float *out) {
         dRec.refN = Normal(0.0f);
         if (env->fillDirectSamplingRecord(dRec, ray)) { dRec.object = env; out[4 * i + 3] = scene->pdfEmitterDirect(dRec); }
         else out[4 * i + 3] = 0;
+    }
+    return 0;
+    GUARD_END
+}
+/* Texture::eval(its, filter = true) of a texture object, with or without uv partials */
+int mtsref_texture_eval(void *t, int64_t n, const float *uv, const float *duv, float *out) {
+    GUARD_BEGIN
+    const Texture *tex = (const Texture *)t;
+    const float zero[16] = {0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+    for (int64_t i = 0; i < n; ++i) {
+        Intersection its = makeIts(zero);
+        its.uv = Point2(uv[2 * i], uv[2 * i + 1]);
+        if (duv) { its.hasUVPartials = true; its.dudx = duv[4 * i]; its.dvdx = duv[4 * i + 1]; its.dudy = duv[4 * i + 2]; its.dvdy = duv[4 * i + 3]; }
+        rgb(tex->eval(its, true), out + 3 * i);
+    }
+    return 0;
+    GUARD_END
+}
+/* What SamplingIntegrator::renderBlock hands to Li (integrator.cpp:144-145, 178-181) */
+static void cameraRay(const Sensor *sensor, const float *sp, int sampleCount, RayDifferential &ray) {
+    sensor->sampleRayDifferential(ray, Point2(sp[0], sp[1]), Point2(0.5f), 0.0f);
+    ray.scaleDifferential(1.0f / std::sqrt((Float)sampleCount));
+}
+/* Scene::rayIntersect + Intersection::computePartials for camera rays.  out: n*8 = dudx dvdx dudy dvdy t hit u v */
+int mtsref_hit_partials(void *s, int64_t n, const float *sp, int sampleCount, float *out) {
+    GUARD_BEGIN
+    const Scene *scene = (const Scene *)s;
+    for (int64_t i = 0; i < n; ++i) {
+        RayDifferential ray; cameraRay(scene->getSensor(), sp + 2 * i, sampleCount, ray);
+        Intersection its;
+        float *q = out + 8 * i;
+        for (int k = 0; k < 8; ++k) q[k] = 0;
+        if (!scene->rayIntersect(ray, its)) continue;
+        its.computePartials(ray);
+        q[0] = its.dudx; q[1] = its.dvdx; q[2] = its.dudy; q[3] = its.dvdy; q[4] = its.t; q[5] = 1.0f; q[6] = its.uv.x; q[7] = its.uv.y;
+    }
+    return 0;
+    GUARD_END
+}
+/* Emitter::evalEnvironment of camera rays WITH differentials (envmap.cpp:380-410) */
+int mtsref_eval_environment_camera(void *s, int64_t n, const float *sp, int sampleCount, float *out) {
+    GUARD_BEGIN
+    const Scene *scene = (const Scene *)s;
+    const Emitter *env = scene->getEnvironmentEmitter();
+    if (!env) return fail("no environment emitter");
+    for (int64_t i = 0; i < n; ++i) {
+        RayDifferential ray; cameraRay(scene->getSensor(), sp + 2 * i, sampleCount, ray);
+        rgb(env->evalEnvironment(ray), out + 3 * i);
     }
     return 0;
     GUARD_END

@@ -52,6 +52,8 @@ def load(threads=0, log_level=300):   # ELogLevel: 0 trace, 100 debug, 200 info,
         "mtsref_sample_emitter_direct": (C.c_int, [vp, i64, vp, vp, vp, vp]),
         "mtsref_eval_environment": (C.c_int, [vp, i64, vp, vp]), "mtsref_sample_rays": (C.c_int, [vp, i64, vp, vp]),
         "mtsref_splat": (C.c_int, [vp, i64, vp, vp, vp]),
+        "mtsref_texture_eval": (C.c_int, [vp, i64, vp, vp, vp]), "mtsref_hit_partials": (C.c_int, [vp, i64, vp, C.c_int, vp]),
+        "mtsref_eval_environment_camera": (C.c_int, [vp, i64, vp, C.c_int, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -247,6 +249,27 @@ class RefScene:
         dd = _f32(d, (-1, 3))
         out = np.empty((dd.shape[0], 4), np.float32)
         _chk(self.lib.mtsref_eval_environment(self.scene.h, dd.shape[0], _p(dd), _p(out)))
+        return out
+
+    def texture_eval(self, texture_plugin, uv, duv=None):
+        """Texture::eval(its, filter=True) of a texture plugin of this scene; duv = dudx dvdx dudy dvdy or None."""
+        t = self.objects[id(texture_plugin)]
+        u = _f32(uv, (-1, 2))
+        d = None if duv is None else _f32(duv, (-1, 4))
+        out = np.empty((u.shape[0], 3), np.float32)
+        _chk(self.lib.mtsref_texture_eval(t.h, u.shape[0], _p(u), None if d is None else _p(d), _p(out)))
+        return out
+
+    def hit_partials(self, pos, sample_count):
+        sp = _f32(pos, (-1, 2))
+        out = np.empty((sp.shape[0], 8), np.float32)
+        _chk(self.lib.mtsref_hit_partials(self.scene.h, sp.shape[0], _p(sp), int(sample_count), _p(out)))
+        return out
+
+    def eval_environment_camera(self, pos, sample_count):
+        sp = _f32(pos, (-1, 2))
+        out = np.empty((sp.shape[0], 3), np.float32)
+        _chk(self.lib.mtsref_eval_environment_camera(self.scene.h, sp.shape[0], _p(sp), int(sample_count), _p(out)))
         return out
 
     def sample_rays(self, pos):

@@ -87,6 +87,9 @@ public:
     bool render(Scene *scene, RenderQueue *queue, const RenderJob *job, int sceneResID, int sensorResID, int samplerResID) {
         m_cancel = 0;
         MtsContext *ctx = NULL;
+        if (mtscuda_abi_version() != MTS_ABI_VERSION)
+            Log(EError, "libmtscuda implements ABI version %i, this plugin was compiled against version %i -- rebuild both "
+                "from the same include/mtscuda.h", (int) mtscuda_abi_version(), (int) MTS_ABI_VERSION);
         check(NULL, mtscuda_create(m_device, &ctx));
         bool ok = false;
         try {
@@ -103,6 +106,7 @@ public:
             p.max_depth = m_maxDepth; p.rr_depth = m_rrDepth;
             p.strict_normals = m_strictNormals; p.hide_emitters = m_hideEmitters;
             p.seed = m_seed; p.clear_film = 1;
+            p.sample_count = p.spp;                      /* scales the camera-ray differentials (integrator.cpp:144-145) */
             Log(EInfo, "Starting render job (%ix%i, " SIZE_T_FMT " samples, CUDA device %i) ..", size.x, size.y,
                 scene->getSampler()->getSampleCount(), m_device);
             MtsStats st;
@@ -346,6 +350,8 @@ private:
             std::map<uint32_t, int> seen;
             std::map<uint32_t, TexInfo> tex;   /* object ids are unique per InstanceManager, i.e. per root BSDF */
             int idx = parseBsdf(ms, seen, tex);
+            /* only the root's flag is read by the library (Intersection::getBSDF(ray), records.inl:69-75) */
+            if (b->usesRayDifferentials()) m_nodes[idx].flags |= MTS_BF_RAY_DIFF;
             m_bsdfIds[b] = idx;
             return idx;
         }
@@ -378,7 +384,7 @@ private:
                 std::string filename = s->readString();
                 uint32_t filterType = s->readUInt(), wrapU = s->readUInt(), wrapV = s->readUInt();
                 Float gamma = s->readFloat();
-                s->readFloat();                          /* maxAnisotropy */
+                Float maxAnisotropy = s->readFloat();
                 std::string channel = s->readString();
                 size_t size = s->readSize();
                 if (!channel.empty()) err("bitmap `channel` selection is not supported by cudapath");
@@ -389,15 +395,16 @@ private:
                 if (gamma != 0) bmp->setGamma(gamma);
                 const bool mono = bmp->getPixelFormat() == Bitmap::ELuminance || bmp->getPixelFormat() == Bitmap::ELuminanceAlpha;
                 ref<Bitmap> lin = bmp->convert(mono ? Bitmap::ELuminance : Bitmap::ERGB, Bitmap::EFloat32, 1.0f);
-                /* EMIPFilterType: ENearest 0, EBilinear 1, ETrilinear 2, EEWA 3 (mipmap.h) */
-                if (filterType > 1)
-                    err("bitmap filterType ewa/trilinear is not supported yet by cudapath (use bilinear or nearest)");
+                /* EMIPFilterType: ENearest 0, EBilinear 1, ETrilinear 2, EEWA 3 (mipmap.h) = MTS_FILTER_* */
+                if (filterType > 3) err("unknown bitmap filter type");
                 MtsTextureDesc d;
+                memset(&d, 0, sizeof(d));
                 d.width = lin->getWidth(); d.height = lin->getHeight(); d.channels = mono ? 1 : 3;
                 /* ReconstructionFilter::EBoundaryCondition: EClamp 0, ERepeat 1, EMirror 2, EZero 3, EOne 4 */
                 static const int wrapMap[5] = { MTS_WRAP_CLAMP, MTS_WRAP_REPEAT, MTS_WRAP_MIRROR, MTS_WRAP_ZERO, MTS_WRAP_ONE };
                 d.wrap_u = wrapMap[std::min(wrapU, 4u)]; d.wrap_v = wrapMap[std::min(wrapV, 4u)];
-                d.filter = filterType == 0 ? MTS_FILTER_NEAREST : MTS_FILTER_BILINEAR;
+                d.filter = (int32_t) filterType;
+                d.max_anisotropy = maxAnisotropy;           /* already forced to 1 for non-EWA filters (bitmap.cpp:232-233) */
                 d.uv_scale[0] = uvScale.x; d.uv_scale[1] = uvScale.y; d.uv_offset[0] = uvOffset.x; d.uv_offset[1] = uvOffset.y;
                 int tid = mtscuda_add_texture(m_ctx, &d, lin->getFloat32Data());
                 m_owner->check(m_ctx, tid);

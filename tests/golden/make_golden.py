@@ -126,9 +126,49 @@ def boundary():
     return out
 
 
+def mip():
+    """mip.npz: TMIPMap lookups with uv partials, Intersection::computePartials of camera rays, the environment map seen
+    through ray differentials, BSDF queries on intersections that carry partials, and a converged render of a scene
+    whose bitmap textures use the default filterType (ewa)."""
+    out = {}
+    scn, tex, mats = G.mip()
+    rs = mtsref.RefScene(scn)
+    for name, t in tex.items():
+        uv, duv = G.texture_inputs(name)
+        out["tex/%s/filtered" % name] = rs.texture_eval(t, uv, duv)
+        out["tex/%s/plain" % name] = rs.texture_eval(t, uv)
+    pos = G.partial_positions()
+    for cnt in G.MIP_SAMPLE_COUNTS:
+        out["partials/%d" % cnt] = rs.hit_partials(pos, cnt)
+        out["envcam/%d" % cnt] = rs.eval_environment_camera(pos, cnt)
+    for name, p in mats.items():
+        surf, wi, wo, u = G.mip_bsdf_inputs(name)
+        rb = rs.bsdf(p)
+        smp = rs.bsdf_sample(rb, surf, wi, u)
+        wo2 = G.eval_directions(smp, wo)
+        out["bsdf/%s/sample" % name] = smp
+        for tag, meas in (("sa", 1), ("disc", 4)):
+            v, pdf = rs.bsdf_eval_pdf(rb, surf, wi, wo2, meas)
+            out["bsdf/%s/eval_%s" % (name, tag)] = v
+            out["bsdf/%s/pdf_%s" % (name, tag)] = pdf
+    film = rs.render()
+    st = rs.stats
+    w, h, spp = G.scene_dims(scn)
+    out["image/mip/rgb"] = M.develop(film).astype(np.float16)
+    out["image/mip/stats"] = np.array([st.get("normal_rays", 0) / (w * h * spp), st.get("shadow_rays", 0) / (w * h * spp),
+                                       st.get("avg_path_length", 0), rs.render_s, mtsref.load().mtsref_thread_count()], dtype=np.float64)
+    print("mip        %dx%d %d spp: reference render %.1f s" % (w, h, spp, rs.render_s), flush=True)
+    return out
+
+
 if __name__ == "__main__":
     if not mtsref.available():
         raise SystemExit("oracle/_ref is not built: make -C oracle/refbuild (needs /root/reference)")
+    if "--mip" in sys.argv:
+        t = mip()
+        np.savez_compressed(os.path.join(HERE, "mip.npz"), **t)
+        print("mip.npz: %d arrays" % len(t))
+        raise SystemExit(0)
     if "--boundary" in sys.argv:
         t = boundary()
         np.savez_compressed(os.path.join(HERE, "boundary.npz"), **t)

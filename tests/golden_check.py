@@ -27,9 +27,9 @@ def _pct(a, q):
     return float(np.percentile(a, q)) if len(a) else 0.0
 
 
-def check_bsdf(ctx, flat, z, name, gold):
+def check_bsdf(ctx, flat, z, name, gold, inputs=None):
     b = flat._bsdf_ids[id(z[name])]
-    surf, wi, wo, u = G.bsdf_inputs(name)
+    surf, wi, wo, u = (inputs or G.bsdf_inputs)(name)
     ref_s = gold["bsdf/%s/sample" % name]
     got_s = ctx.bsdf_sample(b, surf, wi, u)
     # sampled lobe type and validity
@@ -174,6 +174,43 @@ def check_image(path_tracer, name, gold_images, spp, bar, lazy_shadow=False):
         assert abs(rays[1] / st_ref[1] - 1) < 0.01, (name, rays, st_ref[:3])
     assert abs(rays[2] - st_ref[2]) < 0.02, (name, rays, st_ref[:3])
     return err
+
+
+def check_texture(ctx, flat, tex, name, gold):
+    """TMIPMap::eval / evalBilinear / evalBox through Texture2D::eval(its, filter=True) against the reference."""
+    tid = flat._tex_ids[id(tex[name])][0]
+    uv, duv = G.texture_inputs(name)
+    plain = np.abs(ctx.texture_eval(tid, uv) - gold["tex/%s/plain" % name]).max(axis=1)
+    # texel coordinates reach 2.5 * uscale * width: the bilinear weights carry that many ulps
+    assert _pct(plain, 99) < 2e-5 and plain.max() < 2e-4, (name, _pct(plain, 99), plain.max())
+    e = np.abs(ctx.texture_eval(tid, uv, duv) - gold["tex/%s/filtered" % name]).max(axis=1)
+    assert _pct(e, 95) < 1e-5, (name, _pct(e, 95))
+    assert _pct(e, 99) < 1e-4, (name, _pct(e, 99))
+    # the EWA weight table is indexed by (int) q of a running quadratic: one ulp in q across an integer changes one tap's
+    # weight, and one ulp in the level selection swaps the pyramid level of a lookup that sits on the boundary
+    assert (e > 2e-3).mean() <= 2e-3 and e.max() < 0.1, (name, (e > 2e-3).mean(), e.max())
+    return _pct(e, 99)
+
+
+def check_partials(ctx, gold):
+    pos = G.partial_positions()
+    worst = 0.0
+    for cnt in G.MIP_SAMPLE_COUNTS:
+        ref, got = gold["partials/%d" % cnt], ctx.hit_partials(pos, cnt)
+        assert (ref[:, 5] == got[:, 5]).mean() > 0.999
+        hit = (ref[:, 5] > 0) & (got[:, 5] > 0)
+        assert np.abs(ref[hit, 4] - got[hit, 4]).max() < 1e-3       # t
+        assert np.abs(ref[hit, 6:8] - got[hit, 6:8]).max() < 1e-3   # uv
+        # the partials are differences of nearly equal points (offset-ray hit minus hit): relative to the largest component
+        rel = (np.abs(ref[hit, :4] - got[hit, :4]) / (np.abs(ref[hit, :4]).max(axis=1, keepdims=True) + 1e-9)).max(axis=1)
+        # ... and the offset shrinks with 1/sqrt(sample count) while the ulp of the hit point does not
+        tol = 3e-4 * max(1.0, cnt ** 0.5 / 4)
+        assert _pct(rel, 99) < tol and rel.max() < 20 * tol, (cnt, _pct(rel, 99), rel.max())
+        worst = max(worst, _pct(rel, 99))
+        env_ref, env = gold["envcam/%d" % cnt], ctx.eval_environment_camera(pos, cnt)
+        e = util.rel_err(env, env_ref, 1e-3).max(axis=1)
+        assert _pct(e, 99) < 1e-3 and (e > 0.05).mean() < 2e-3, (cnt, _pct(e, 99), e.max())
+    return worst
 
 
 def check_boundary_image(path_tracer, name, gold_boundary, spp, bar):

@@ -90,6 +90,42 @@ def splat_inputs(w=ZOO_W, h=ZOO_H):
     return pos, val
 
 
+# ---- MIP maps / ray differentials (fixture mip.npz) -----------------------------------------------------------------
+MIP_W, MIP_H, MIP_SPP = 96, 64, 4096
+N_TEX, N_PARTIALS = 4000, 3000
+MIP_SAMPLE_COUNTS = (1, 16, 4096)
+
+
+def mip(spp=MIP_SPP):
+    return util.mip_scene(width=MIP_W, height=MIP_H, spp=spp)
+
+
+def texture_inputs(name):
+    """uv beyond [0,1] (wrap modes) and uv partials from magnification to strong, anisotropic minification."""
+    rng = np.random.RandomState(zlib.crc32(("tex/" + name).encode()))
+    uv = rng.uniform(-1.5, 2.5, (N_TEX, 2)).astype(F)
+    mag = 10 ** rng.uniform(-4, -0.3, (N_TEX, 1))
+    duv = (rng.normal(size=(N_TEX, 4)) * mag).astype(F)
+    duv[::50, 2:] = 0            # degenerate footprints take the trilinear branch of TMIPMap::eval
+    duv[7::50] = 0
+    return uv, duv
+
+
+def mip_bsdf_inputs(name):
+    """bsdf_inputs with Intersection::hasUVPartials set (surf slots 2, 3, 7, 11, 15)."""
+    surf, wi, wo, u = bsdf_inputs("mip/" + name)
+    rng = np.random.RandomState(zlib.crc32(("mipduv/" + name).encode()))
+    n = surf.shape[0]
+    duv = (rng.normal(size=(n, 4)) * 10 ** rng.uniform(-3.5, -0.5, (n, 1))).astype(F)
+    surf[:, 2], surf[:, 3], surf[:, 7], surf[:, 11], surf[:, 15] = duv[:, 0], duv[:, 1], duv[:, 2], duv[:, 3], 1.0
+    return surf, wi, wo, u
+
+
+def partial_positions():
+    rng = np.random.RandomState(21)
+    return (rng.rand(N_PARTIALS, 2) * [MIP_W, MIP_H]).astype(F)
+
+
 def scene_dims(sc):
     s = sc.child("sensor")
     f = s.child("film")

@@ -294,3 +294,79 @@ def sphere_alpha_scene(width=80, height=60, spp=4):
     lt.add(Plugin("emitter", "area", radiance=Spectrum(25, 23, 20)))
     sc.add(lt)
     return sc
+
+
+def _pattern(w, h, channels=3, seed=11):
+    """High-frequency texture (checker + stripes + noise) whose minified appearance depends on the filter."""
+    rng = np.random.RandomState(seed)
+    y, x = np.mgrid[0:h, 0:w]
+    chk = ((x // 3 + y // 2) % 2).astype(F)
+    img = np.stack([0.1 + 0.8 * chk, 0.5 + 0.45 * np.sin(x * 1.3), 0.5 + 0.45 * np.cos(y * 0.9)], axis=2).astype(F)
+    img = np.clip(img + rng.uniform(-0.08, 0.08, img.shape).astype(F), 0.0, 1.0)
+    return img[:, :, :channels] if channels == 3 else img[:, :, :1]
+
+
+def mip_textures():
+    """Bitmap textures that exercise the MIP map: default filter (ewa, maxAnisotropy 20), low anisotropy, trilinear, odd
+    sizes (the Lanczos pyramid rounds sizes up), every wrap mode, uv scale / offset, one channel."""
+    def tex(w, h, ch=3, seed=11, **kw):
+        t = Plugin("texture", "bitmap", gamma=1.0, **kw)
+        t.data["bitmap"] = _pattern(w, h, ch, seed)
+        return t
+    return {
+        "ewa": tex(96, 80, uscale=400.0, vscale=400.0),   # on the floor: hundreds of texels per pixel even at 1/64 footprint
+        "ewa_aniso2": tex(61, 47, seed=12, maxAnisotropy=2.0, uscale=5.0, vscale=7.0, wrapMode="mirror"),
+        "trilinear": tex(64, 64, seed=13, filterType="trilinear", uscale=9.0, vscale=9.0),
+        "ewa_clamp_mono": tex(50, 33, ch=1, seed=14, wrapModeU="clamp", wrapModeV="zero", uoffset=0.1, voffset=-0.2),
+        "ewa_one": tex(37, 64, seed=15, wrapModeU="one", wrapModeV="repeat", uscale=3.0, vscale=2.0),
+        "bilinear": tex(48, 48, seed=16, filterType="bilinear", uscale=6.0, vscale=6.0),
+        "nearest": tex(48, 48, seed=17, filterType="nearest", uscale=6.0, vscale=6.0),
+    }
+
+
+def mip_scene(width=96, height=64, spp=4, envmap=True):
+    """A textured ground plane seen at a grazing angle (strong minification + anisotropy), textured spheres and a
+    bump-mapped cube, under an environment map that camera rays see through the EWA lookup.  All bitmap textures
+    use the reference's default filterType (ewa) unless they say otherwise."""
+    sc = Plugin("scene", "")
+    sc.add(Plugin("integrator", "path", maxDepth=4))
+    s = Plugin("sensor", "perspective", toWorld=hm.look_at([0, 1.2, 9], [0, 0.6, 0], [0, 1, 0]), fov=55.0)
+    s.add(Plugin("sampler", "independent", sampleCount=spp))
+    film = Plugin("film", "hdrfilm", width=width, height=height)
+    film.add(Plugin("rfilter", "gaussian"))
+    s.add(film)
+    sc.add(s)
+    t = mip_textures()
+    floor = Plugin("shape", "rectangle", toWorld=hm.rotate([1, 0, 0], -90) @ hm.scale([30, 30, 1]))
+    fb = Plugin("bsdf", "diffuse")
+    fb.add(t["ewa"], "reflectance")
+    floor.add(fb)
+    sc.add(floor)
+    mats = {}
+    b = Plugin("bsdf", "diffuse"); b.add(t["ewa_aniso2"], "reflectance"); mats["diffuse_aniso2"] = b
+    b = Plugin("bsdf", "roughplastic", distribution="ggx", alpha=0.15); b.add(t["trilinear"], "diffuseReflectance"); mats["rp_trilinear"] = b
+    b = Plugin("bsdf", "roughconductor", distribution="beckmann", **scenes.CU); b.add(t["ewa_clamp_mono"], "alpha"); mats["rc_alpha_tex"] = b
+    inner = Plugin("bsdf", "diffuse"); inner.add(t["ewa_one"], "reflectance")
+    b = Plugin("bsdf", "twosided"); b.add(inner); mats["twosided_one"] = b
+    b = Plugin("bsdf", "diffuse"); b.add(t["bilinear"], "reflectance"); mats["diffuse_bilinear"] = b
+    for i, nm in enumerate(mats):
+        sp = Plugin("shape", "sphere", center=Point((i - 2) * 2.1, 1.0, 2.0 - 0.8 * i), radius=1.0)
+        sp.add(mats[nm])
+        sc.add(sp)
+    cube = Plugin("shape", "cube", toWorld=hm.translate([0, 0.7, 5.5]) @ hm.rotate([0, 1, 0], 30) @ hm.scale([0.7, 0.7, 0.7]))
+    inner = Plugin("bsdf", "diffuse"); inner.add(t["nearest"], "reflectance")
+    bump = Plugin("bsdf", "bumpmap")
+    disp = Plugin("texture", "scale", scale=0.05); disp.add(_tex(31, channels=1, size=32))
+    bump.add(disp); bump.add(inner)
+    cube.add(bump)
+    sc.add(cube)
+    mats["bump_nearest"] = bump
+    mats["floor"] = fb
+    lt = Plugin("shape", "rectangle", toWorld=hm.translate([0, 8, 3]) @ hm.rotate([1, 0, 0], 90) @ hm.scale([2.0, 2.0, 1]))
+    lt.add(Plugin("emitter", "area", radiance=Spectrum(18, 17, 15)))
+    sc.add(lt)
+    if envmap:
+        env = Plugin("emitter", "envmap", scale=0.8, toWorld=hm.rotate([0, 1, 0], 25.0))
+        env.data["bitmap"] = scenes.synthetic_envmap(160, 80)
+        sc.add(env)
+    return sc, t, mats
