@@ -28,8 +28,9 @@ import numpy as np  # noqa: E402
 WORKLOADS = {
     # name: (generator, kwargs, description)
     "terrain": ("terrain_scene", dict(width=1920, height=1080, spp=128, max_depth=8),
-                "configs[2]: procedural 10M-triangle terrain (9,999,392 tris) with bitmap textures + bumpmap, "
-                "1920x1080, 128 spp, maxDepth 8, gaussian rfilter, area light + envmap"),
+                "configs[2]: procedural 10M-triangle terrain (9,999,392 tris), four 4096^2 RGB bitmap textures (default "
+                "filterType ewa) + 4096^2 bump map, bumpmap over roughplastic and over diffuse, 1920x1080, 128 spp, "
+                "maxDepth 8, gaussian rfilter, area light + envmap"),
     "spheres": ("material_spheres", dict(width=1024, height=1024, spp=256, max_depth=8),
                 "configs[1]: 25 spheres roughconductor/roughplastic/dielectric/coating over envmap, 1024x1024, 256 spp"),
     "cornell": ("cornell_box", dict(width=512, height=512, spp=64, max_depth=5),

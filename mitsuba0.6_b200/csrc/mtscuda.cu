@@ -1115,8 +1115,15 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
                 Counters hc;
                 CUDA_TRY(cudaMemcpyAsync(&hc, Wf.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
                 CUDA_TRY(cudaStreamSynchronize(st));
-                fprintf(stderr, "[mtscuda] wavefront %llu bounce %d: closest-hit rays %u, shadow rays %u, continuing %u, escaped so far %llu\n",
-                        first / cap, bounce, hc.qCount[cur], hc.shadowCount, hc.qCount[cur ^ 1], hc.missRays);
+                std::vector<uint32_t> off(Wf.numKeys + 1);
+                CUDA_TRY(cudaMemcpyAsync(off.data(), Wf.keyCount + Wf.numKeys, sizeof(uint32_t) * Wf.numKeys, cudaMemcpyDeviceToHost, st));
+                CUDA_TRY(cudaStreamSynchronize(st));
+                off[Wf.numKeys] = hc.qCount[cur];
+                uint32_t perClass[SHADE_CLASSES];
+                for (int k = 0; k < SHADE_CLASSES; ++k) perClass[k] = off[std::min(Wf.classKey[k + 1], Wf.numKeys)] - off[std::min(Wf.classKey[k], Wf.numKeys)];
+                fprintf(stderr, "[mtscuda] wavefront %llu bounce %d: closest-hit rays %u, shadow rays %u, continuing %u, escaped so far %llu, "
+                        "shaded lambert/leaf/generic %u %u %u\n",
+                        first / cap, bounce, hc.qCount[cur], hc.shadowCount, hc.qCount[cur ^ 1], hc.missRays, perClass[0], perClass[1], perClass[2]);
             }
             cur ^= 1;
         }

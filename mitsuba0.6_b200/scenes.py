@@ -160,10 +160,13 @@ def terrain_mesh(n=2237, size=20.0, height=2.5, seed=7):
     return pos, idx, nrm.reshape(-1, 3).astype(F), uv
 
 
-def procedural_texture(size=4096, seed=11, channels=3):
+def procedural_texture(size=4096, seed=11, channels=3, base=None):
+    """fBm pattern mapped through a seeded colour ramp.  `base`: a normalised heightfield to reuse (the fBm synthesis
+    dominates the cost; scenes with several large textures derive them from one field)."""
     rng = np.random.RandomState(seed)
-    base = fbm_heightfield(size, octaves=7, seed=seed)
-    base = (base - base.min()) / (base.max() - base.min())
+    if base is None:
+        base = fbm_heightfield(size, octaves=7, seed=seed)
+        base = (base - base.min()) / (base.max() - base.min())
     if channels == 1:
         return base.astype(F)[:, :, None]
     c0, c1 = rng.uniform(0.05, 0.4, 3), rng.uniform(0.5, 0.95, 3)
@@ -171,8 +174,10 @@ def procedural_texture(size=4096, seed=11, channels=3):
 
 
 def terrain_scene(width=1920, height=1080, spp=128, max_depth=8, grid=2237, tex_size=4096, rfilter="gaussian",
-                  env_size=(2048, 1024)):
-    """cfg3 / cfg5: ~10M-triangle textured + bump-mapped terrain, one area light + envmap."""
+                  env_size=(2048, 1024), filter_type="ewa"):
+    """cfg3 / cfg5 (synthetic inputs): ~10M-triangle terrain, four tex_size^2 RGB bitmap textures
+    and a tex_size^2 luminance bump map -- `bumpmap` over roughplastic (terrain) and over diffuse (slab) -- one area
+    light + envmap.  The bitmaps use the reference's default filterType (ewa) unless told otherwise."""
     sc = Plugin("scene", "")
     sc.add(Plugin("integrator", "path", maxDepth=int(max_depth)))
     sc.add(_sensor([0, 6.5, 15], [0, 0.2, 0], [0, 1, 0], 45, width, height, spp, rfilter))
@@ -182,27 +187,41 @@ def terrain_scene(width=1920, height=1080, spp=128, max_depth=8, grid=2237, tex_
     pos, idx, nrm, uv = terrain_mesh(grid)
     mesh = Plugin("shape", "mesh")
     mesh.data.update(positions=pos, indices=idx, normals=nrm, texcoords=uv)
-    albedo = Plugin("texture", "bitmap", filterType="bilinear", gamma=1.0, uvscale=4.0)
-    albedo.data["bitmap"] = procedural_texture(tex_size, seed=11)
-    bumptex = Plugin("texture", "bitmap", filterType="bilinear", gamma=1.0, uvscale=8.0)
+    field = fbm_heightfield(tex_size, octaves=7, seed=11)
+    field = (field - field.min()) / (field.max() - field.min())
+
+    def rgb(k, **kw):   # four different textures from one fBm field: rotated / mirrored, own colour ramp
+        t = Plugin("texture", "bitmap", filterType=filter_type, gamma=1.0, **kw)
+        t.data["bitmap"] = procedural_texture(tex_size, seed=11 + 10 * k, base=np.rot90(field, k) if k < 3 else field[::-1])
+        return t
+    albedo, spec, slab_tex, block_tex = rgb(0, uvscale=4.0), rgb(1, uvscale=4.0), rgb(2), rgb(3)
+    bumptex = Plugin("texture", "bitmap", filterType=filter_type, gamma=1.0, uvscale=8.0)
     bumptex.data["bitmap"] = procedural_texture(tex_size, seed=12, channels=1)
     sc_tex = Plugin("texture", "scale", scale=0.02)
     sc_tex.add(bumptex)
     rp = Plugin("bsdf", "roughplastic", distribution="ggx", alpha=0.15, intIOR=1.49)
     rp.add(albedo, "diffuseReflectance")
+    rp.add(spec, "specularReflectance")
     bump = Plugin("bsdf", "bumpmap")
     bump.add(rp)
     bump.add(sc_tex)
     mesh.add(bump)
     sc.add(mesh)
-    # a second textured object: diffuse bump-mapped slab
+    # bumpmap over diffuse: a textured slab ...
     slab = Plugin("shape", "cube", toWorld=hm.translate([3.0, 2.2, 1.0]) @ hm.rotate([0, 1, 0], 30) @ hm.scale([1.2, 0.8, 1.2]))
-    dtex = Plugin("texture", "bitmap", filterType="bilinear", gamma=1.0)
-    dtex.data["bitmap"] = procedural_texture(min(tex_size, 1024), seed=13)
     db = Plugin("bsdf", "diffuse")
-    db.add(dtex, "reflectance")
-    slab.add(db)
+    db.add(slab_tex, "reflectance")
+    sbump = Plugin("bsdf", "bumpmap")
+    sbump.add(db)
+    sbump.add(sc_tex)
+    slab.add(sbump)
     sc.add(slab)
+    # ... and a plain textured block
+    block = Plugin("shape", "cube", toWorld=hm.translate([-3.5, 1.8, 3.0]) @ hm.rotate([0, 1, 0], -20) @ hm.scale([0.9, 0.6, 0.9]))
+    bb = Plugin("bsdf", "diffuse")
+    bb.add(block_tex, "reflectance")
+    block.add(bb)
+    sc.add(block)
     light = Plugin("emitter", "area", radiance=Spectrum(60.0, 55.0, 45.0))
     sc.add(_rect(hm.translate([-4, 7, 2]) @ hm.rotate([1, 0, 0], 90) @ hm.scale([1.0, 1.0, 1.0]), _diffuse((0, 0, 0)), light))
     return sc

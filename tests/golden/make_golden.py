@@ -164,6 +164,18 @@ def mip():
 if __name__ == "__main__":
     if not mtsref.available():
         raise SystemExit("oracle/_ref is not built: make -C oracle/refbuild (needs /root/reference)")
+    if "--only" in sys.argv:   # re-render single entries of images.npz (a scene generator changed), keep the rest
+        names = sys.argv[sys.argv.index("--only") + 1].split(",")
+        old = dict(np.load(os.path.join(HERE, "images.npz")))
+        keep = dict(G.IMAGE_SCENES)
+        for k in list(G.IMAGE_SCENES):
+            if k not in names:
+                del G.IMAGE_SCENES[k]
+        old.update(images())
+        G.IMAGE_SCENES.update(keep)
+        np.savez_compressed(os.path.join(HERE, "images.npz"), **old)
+        print("images.npz: re-rendered %s" % names)
+        raise SystemExit(0)
     if "--mip" in sys.argv:
         t = mip()
         np.savez_compressed(os.path.join(HERE, "mip.npz"), **t)

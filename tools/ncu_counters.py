@@ -23,12 +23,16 @@ def main():
     bounces = []
     prev_escaped = 0
     for line in open(trace):
-        m = re.search(r"wavefront (\d+) bounce (\d+): closest-hit rays (\d+), shadow rays (\d+), continuing (\d+)(?:, escaped so far (\d+))?", line)
+        m = re.search(r"wavefront (\d+) bounce (\d+): closest-hit rays (\d+), shadow rays (\d+), continuing (\d+)(?:, escaped so far (\d+))?"
+                      r"(?:, shaded lambert/leaf/generic (\d+) (\d+) (\d+))?", line)
         if not m or int(m.group(1)) != 0:
             continue
         rays, srays = int(m.group(3)), int(m.group(4))
         esc = int(m.group(6)) if m.group(6) else prev_escaped
-        bounces.append({"intersect": rays, "shadow": srays, "shade": rays - (esc - prev_escaped), "miss": esc - prev_escaped})
+        b = {"intersect": rays, "shadow": srays, "shade": rays - (esc - prev_escaped), "miss": esc - prev_escaped}
+        if m.group(7):
+            b.update(shade0=int(m.group(7)), shade1=int(m.group(8)), shade2=int(m.group(9)))
+        bounces.append(b)
         prev_escaped = esc
     if rep.endswith(".csv"):      # `ncu -i cap.ncu-rep --page raw --csv` already run where the capture was taken
         out = open(rep).read()
@@ -45,11 +49,13 @@ def main():
         kind = "intersect" if "k_intersect" in name else "shadow" if "k_shadow" in name else "miss" if "k_shade_miss" in name else "shade" if "k_shade" in name else None
         if kind is None:
             continue
-        n = seen.get(kind, 0)
-        seen[kind] = n + 1
+        cls = re.search(r"k_shade<\(?(?:\w+::)*\w*\)?(\d)>", name) if kind == "shade" else None
+        sub = kind + (cls.group(1) if cls else "")      # one k_shade instance per shade class and bounce
+        n = seen.get(sub, 0)
+        seen[sub] = n + 1
         if n >= len(bounces):
             continue
-        units = bounces[n][kind]
+        units = bounces[n].get(sub, bounces[n][kind])
         if units <= 0:
             continue
 
@@ -66,7 +72,7 @@ def main():
 
         t_unit = rows[1][h.index("gpu__time_duration.sum")] if "gpu__time_duration.sum" in h else "ms"
         t_ms = f("gpu__time_duration.sum") * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(t_unit, 1.0)
-        e = {"kernel": name[:60], "bounce": n, "units": units, "ms_under_ncu": t_ms,
+        e = {"kernel": name[:60], "sub": sub, "bounce": n, "units": units, "ms_under_ncu": t_ms,
              "dram_bytes": in_bytes("dram__bytes_read.sum") + in_bytes("dram__bytes_write.sum"),
              "warp_inst": f("smsp__inst_executed.sum"), "lanes_per_inst": f("smsp__thread_inst_executed_per_inst_executed.ratio"),
              "issue_active_pct": f("smsp__issue_active.avg.pct_of_peak_sustained_active"),
@@ -80,7 +86,18 @@ def main():
         ls = per.get(kind)
         if not ls:
             continue
-        units = sum(e["units"] for e in ls)
+        if kind == "shade":   # per-class launches: count every covered bounce's shaded paths once
+            cov = sorted({e["bounce"] for e in ls})
+            units = sum(bounces[b]["shade"] for b in cov)
+            for c in ("shade0", "shade1", "shade2"):
+                lc = [e for e in ls if e["sub"] == c]
+                if lc:
+                    uc = sum(e["units"] for e in lc)
+                    res["k_" + c] = {"dram_bytes_per_unit": sum(e["dram_bytes"] for e in lc) / uc, "warp_inst_per_unit": sum(e["warp_inst"] for e in lc) / uc,
+                                     "ms_under_ncu": sum(e["ms_under_ncu"] for e in lc), "units_covered": uc, "registers": lc[0]["registers"],
+                                     "stall_no_instruction": max(e["stall_no_instruction"] for e in lc), "warps_active_pct": lc[0]["warps_active_pct"]}
+        else:
+            units = sum(e["units"] for e in ls)
         wi = sum(e["warp_inst"] for e in ls)
         res[key] = {"dram_bytes_per_unit": sum(e["dram_bytes"] for e in ls) / units,
                     "warp_inst_per_unit": wi / units,
