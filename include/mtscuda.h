@@ -272,6 +272,15 @@ typedef struct MtsContext MtsContext;
 MTS_API int32_t MTS_FN(abi_version)(void);
 MTS_API const char *MTS_FN(last_error)(void);
 MTS_API int MTS_FN(create)(int device, MtsContext **out);
+/* A context that renders on several GPUs of the box -- the counterpart of the reference's `-p N` worker pool
+ * (src/mitsuba/mitsuba.cpp:277-327, src/librender/renderproc.cpp:118-182), behind cudapath's `devices` parameter.
+ * devices[0] is the primary: it receives the scene description, and build() replicates the staged scene to the other
+ * devices GPU-to-GPU (every device then builds its own acceleration structure concurrently, one host thread each).
+ * render() gives device d the samples d, d+n, d+2n, ... of every pixel (the union is the single-device sample set) and
+ * sums the films on the primary over NVLink; read_film / get_stats / the per-function entry points act on the primary.
+ * All devices need peer access to devices[0].  n = 1 is the same as create(). */
+MTS_API int MTS_FN(create_multi)(const int32_t *devices, int32_t n, MtsContext **out);
+MTS_API int MTS_FN(device_count)(MtsContext *ctx);
 MTS_API void MTS_FN(destroy)(MtsContext *ctx);
 
 /* ---- scene description (what cudapath::render() extracts from Scene) */

@@ -44,12 +44,16 @@ class CudaPath:
     oracle/oracle_lib.py) through these wrappers; the package itself never passes it.
     """
 
-    def __init__(self, scene, device=0, lib=None):
+    def __init__(self, scene, device=0, lib=None, devices=None):
+        """devices: list of GPUs of this box that share the render (cudapath's `devices` parameter counts them from
+        `device`); None / one entry = a single GPU."""
         if isinstance(scene, str):
             scene = load_xml(scene)
         self.scene = scene
         self.flat = scene if isinstance(scene, _scene.FlatScene) else flatten(scene)
-        self.ctx = Context(device, lib)
+        if devices is None and int(self.flat.params.get("devices", 1)) > 1:
+            devices = [int(self.flat.params.get("device", device)) + i for i in range(int(self.flat.params["devices"]))]
+        self.ctx = Context(device, lib, devices=devices if devices and len(devices) > 1 else None)
         self._cancel = _C.c_int(0)
         self.preprocessed = False
         self.stats = None

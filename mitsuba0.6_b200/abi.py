@@ -101,7 +101,7 @@ class Stats(C.Structure):
 # every symbol include/mtscuda.h declares (tests check that the libraries export all of them)
 ABI_VERSION = 4   # MTS_ABI_VERSION of include/mtscuda.h these mirrors were written against
 ABI_SYMBOLS = [
-    "abi_version", "last_error", "create", "destroy", "set_camera", "set_film", "add_texture", "set_float_pool",
+    "abi_version", "last_error", "create", "create_multi", "device_count", "destroy", "set_camera", "set_film", "add_texture", "set_float_pool",
     "set_bsdfs", "add_mesh", "add_rectangle", "add_sphere", "add_emitter", "build", "render",
     "read_film", "read_film_alpha", "bind_film", "set_stream", "get_stats", "sample_rays", "trace", "hit_records", "bsdf_eval_pdf",
     "bsdf_sample", "sample_emitter_direct", "eval_environment", "texture_eval", "hit_partials", "eval_environment_camera", "splat",
@@ -132,6 +132,8 @@ def bind(path, prefix):
     vp, i32, i64, fp = C.c_void_p, C.c_int32, C.c_int64, C.c_void_p
     sigs = {
         "abi_version": (C.c_int32, []),
+        "create_multi": (C.c_int, [C.POINTER(C.c_int32), C.c_int32, C.POINTER(vp)]),
+        "device_count": (C.c_int, [vp]),
         "last_error": (C.c_char_p, []),
         "create": (C.c_int, [C.c_int, C.POINTER(vp)]),
         "destroy": (None, [vp]),
@@ -195,11 +197,17 @@ def ptr(a):
 class Context:
     """Owns one MtsContext handle; thin, typed wrappers over the C entry points."""
 
-    def __init__(self, device=0, lib=None):
+    def __init__(self, device=0, lib=None, devices=None):
+        """device: one GPU.  devices: a list of GPUs of this box rendering together (mtscuda_create_multi; devices[0]
+        is the primary) -- cudapath's `devices` parameter."""
         self.lib = lib if lib is not None else load()
         self.fn = self.lib._fn
         h = C.c_void_p()
-        self._check(self.fn["create"](device, C.byref(h)))
+        if devices is not None and len(devices) > 0:
+            arr = (C.c_int32 * len(devices))(*[int(d) for d in devices])
+            self._check(self.fn["create_multi"](arr, len(devices), C.byref(h)))
+        else:
+            self._check(self.fn["create"](device, C.byref(h)))
         self.h = h
         self._keep = []
 
@@ -207,6 +215,9 @@ class Context:
         if rc < 0:
             raise MtsError(self.fn["last_error"]().decode("utf-8", "replace") or ("error %d" % rc))
         return rc
+
+    def device_count(self):
+        return int(self.fn["device_count"](self.h))
 
     def close(self):
         if getattr(self, "h", None):

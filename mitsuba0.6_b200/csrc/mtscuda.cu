@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 #include "bvh_build.h"
 #include "devmem.h"
@@ -29,7 +30,7 @@ struct HostShape {
     float lo[3], hi[3];  // analytic bounds
 };
 
-struct HostTex { MtsTextureDesc d; DTexture dt; };  // dt.texels: the MIP pyramid, built and kept on the device
+struct HostTex { MtsTextureDesc d; DTexture dt; size_t bytes = 0; };  // dt.texels: the MIP pyramid, built and kept on the device
 
 // Growable device array: scene buffers are appended straight from the caller's host pointers (no host staging
 // copy), so the plugin-facing upload runs at PCIe speed.
@@ -50,7 +51,7 @@ template <class T> struct DevVec {
     cudaError_t append(const T *host, size_t n, cudaStream_t st) {
         cudaError_t e = reserve(size + n, st);
         if (e != cudaSuccess || n == 0) return e;
-        if (host) e = cudaMemcpyAsync(data + size, host, sizeof(T) * n, cudaMemcpyHostToDevice, st);
+        if (host) e = cudaMemcpyAsync(data + size, host, sizeof(T) * n, cudaMemcpyDefault, st);   // host or (UVA) device memory
         else e = cudaMemsetAsync(data + size, 0, sizeof(T) * n, st);
         size += n;
         return e;
@@ -130,6 +131,9 @@ struct MtsContext {
     int bvhDepth = 0;
     float *ewaLut = nullptr;                                  // EWA weight table shared by all MIP maps
     uint32_t numKeys = 1, classKey[SHADE_CLASSES + 1] = {1, 1, 1, 1};   // material sort keys (set by build)
+    // multi-device group (mtscuda_create_multi): this context is the primary; every peer is a full single-device context on
+    // another GPU of the box that receives a copy of the scene over NVLink and renders its share of the samples
+    std::vector<MtsContext *> peers;
     // wavefront
     Wavefront wf; std::vector<void *> wfAllocs; uint32_t wfCapacity = 0;
     MtsStats stats;
@@ -370,7 +374,8 @@ static void resamplerWeights(int sourceRes, int targetRes, int &taps, std::vecto
 // Builds the pyramid of `raw` (w*h*ch floats on the device; negative values are clamped in place) into one half buffer
 // and describes it in `out`.  trilinear / ewa: every further level is resampled from the previous FLOAT level (x pass,
 // then y pass, clamped to [0, maxValue]) and rounded to half.
-static int buildPyramid(MtsContext *c, float *raw, int w, int h, int ch, int bcu, int bcv, int filter, float maxAniso, float maxValue, DTexture &out) {
+static int buildPyramid(MtsContext *c, float *raw, int w, int h, int ch, int bcu, int bcv, int filter, float maxAniso, float maxValue, DTexture &out,
+                        size_t *outBytes = nullptr) {
     cudaStream_t st = c->stream;
     const int stride = ch == 1 ? 1 : 4;
     std::vector<int> lw(1, w), lh(1, h);
@@ -421,6 +426,7 @@ static int buildPyramid(MtsContext *c, float *raw, int w, int h, int ch, int bcu
     out.levels = (int)lw.size();
     out.maxAnisotropy = filter == MTS_FILTER_EWA ? maxAniso : 1.0f;   // bitmap.cpp:230-233
     out.weightLut = c->ewaLut;
+    if (outBytes) *outBytes = sizeof(__half) * total * stride;
     return MTS_OK;
 }
 
@@ -627,6 +633,8 @@ MTS_API int mtscuda_create(int device, MtsContext **out) {
 
 MTS_API void mtscuda_destroy(MtsContext *c) {
     if (!c) return;
+    for (MtsContext *p : c->peers) mtscuda_destroy(p);
+    c->peers.clear();
     cudaSetDevice(c->device);
     c->freeScene(); c->freeWavefront(); c->freeGeometry();
     devFree(c->filmInternal, c->stream); devFree(c->filmAlpha, c->stream); devFree(c->ewaLut, c->stream);
@@ -672,9 +680,9 @@ MTS_API int mtscuda_add_texture(MtsContext *c, const MtsTextureDesc *d, const fl
     const size_t npix = (size_t)d->width * d->height;
     float *raw = nullptr;
     CUDA_TRY(devAlloc(&raw, sizeof(float) * npix * d->channels, c->stream));
-    cudaError_t e = cudaMemcpyAsync(raw, texels, sizeof(float) * npix * d->channels, cudaMemcpyHostToDevice, c->stream);
+    cudaError_t e = cudaMemcpyAsync(raw, texels, sizeof(float) * npix * d->channels, cudaMemcpyDefault, c->stream);
     int rc = MTS_OK;
-    if (e == cudaSuccess) rc = buildPyramid(c, raw, d->width, d->height, d->channels, d->wrap_u, d->wrap_v, d->filter, d->max_anisotropy, 1.0f /* TMIPMap maxValue default */, t.dt);
+    if (e == cudaSuccess) rc = buildPyramid(c, raw, d->width, d->height, d->channels, d->wrap_u, d->wrap_v, d->filter, d->max_anisotropy, 1.0f /* TMIPMap maxValue default */, t.dt, &t.bytes);
     devFree(raw, c->stream);
     if (e != cudaSuccess) return fail(MTS_ECUDA, std::string("add_texture: ") + cudaGetErrorString(e));
     if (rc != MTS_OK) return rc;
@@ -772,7 +780,7 @@ MTS_API int mtscuda_add_emitter(MtsContext *c, const MtsEmitterDesc *d) {
         if (d->env_width > 65534 || d->env_height > 65534) return fail(MTS_EINVAL, "Environment maps images must be smaller than 65536 pixels in width and height");
         CUDA_TRY(cudaSetDevice(c->device));
         CUDA_TRY(devAlloc(&e.envRaw, sizeof(float) * n, c->stream));   // straight from the caller's buffer; rounded to half on the device
-        CUDA_TRY(cudaMemcpyAsync(e.envRaw, d->env_texels, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
+        CUDA_TRY(cudaMemcpyAsync(e.envRaw, d->env_texels, sizeof(float) * n, cudaMemcpyDefault, c->stream));
         CUDA_TRY(cudaStreamSynchronize(c->stream));
         c->envIndex = (int)c->emitters.size();
     } else if (d->type != MTS_EMITTER_POINT) return fail(MTS_EINVAL, "unsupported emitter type");
@@ -780,7 +788,7 @@ MTS_API int mtscuda_add_emitter(MtsContext *c, const MtsEmitterDesc *d) {
     return (int)c->emitters.size() - 1;
 }
 
-MTS_API int mtscuda_build(MtsContext *c) {
+static int buildOne(MtsContext *c) {
     CUDA_TRY(cudaSetDevice(c->device));
     if (c->emitters.empty())
         return fail(MTS_EINVAL, "scene has no emitters (the reference would add a sunsky emitter, which is out of scope)");
@@ -1000,7 +1008,7 @@ MTS_API int mtscuda_set_stream(MtsContext *c, void *cuda_stream) {
     return MTS_OK;
 }
 
-MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile const int *cancel, MtsStats *stats) {
+static int renderOne(MtsContext *c, const MtsRenderParams *P, volatile const int *cancel, MtsStats *stats) {
     if (!c->built || !c->hasCam || !c->hasFilm) return fail(MTS_ESTATE, "render before build/set_camera/set_film");
     // MonteCarloIntegrator parameter validation (src/librender/integrator.cpp:190-225)
     if (P->rr_depth <= 0) return fail(MTS_EINVAL, "'rrDepth' must be set to a value greater than zero!");
@@ -1156,6 +1164,190 @@ MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile con
     sx.bvh_nodes_visited_shadow = hc.nodesVisitedShadow; sx.bvh_prims_tested_shadow = hc.primsTestedShadow;
     if (stats) *stats = sx;
     return cancelled ? fail(MTS_ECANCELLED, "render cancelled") : MTS_OK;
+}
+
+// ---- multi-device groups --------------------------------------------------------------------------------------------
+// The reference scales a render over the cores of a box with `-p N` (src/mitsuba/mitsuba.cpp:277-327: one worker per
+// core, image blocks handed out by RenderProcess).  cudapath scales it over the GPUs of a box: every device renders the
+// FULL frame with its own subset of the sample indices (sample s goes to device s mod N, so the union is exactly the
+// single-device sample set), and the films are summed on the primary over NVLink.  One host thread per device.
+} // extern "C"
+namespace {
+
+// Runs fn(device index) for every device of the group concurrently; returns the first error (code + message).
+template <class Fn> int forEachDevice(MtsContext *c, Fn fn) {
+    const int n = 1 + (int)c->peers.size();
+    std::vector<int> rc(n, MTS_OK);
+    std::vector<std::string> msg(n);
+    std::vector<std::thread> th;
+    for (int d = 1; d < n; ++d)
+        th.emplace_back([&, d]() { rc[d] = fn(d); if (rc[d] != MTS_OK) msg[d] = g_err; });   // g_err is thread-local
+    rc[0] = fn(0);
+    if (rc[0] != MTS_OK) msg[0] = g_err;
+    for (auto &t : th) t.join();
+    for (int d = 0; d < n; ++d) if (rc[d] != MTS_OK) return fail(rc[d], "device " + std::to_string(d ? c->peers[d - 1]->device : c->device) + ": " + msg[d]);
+    return MTS_OK;
+}
+
+template <class T> cudaError_t peerCopy(DevVec<T> &dst, int dstDev, cudaStream_t dstStream, const DevVec<T> &src, int srcDev) {
+    dst.release(dstStream);
+    if (!src.size) return cudaSuccess;
+    cudaError_t e = dst.reserve(src.size, dstStream);
+    if (e != cudaSuccess) return e;
+    dst.size = src.size;
+    return cudaMemcpyPeerAsync(dst.data, dstDev, src.data, srcDev, sizeof(T) * src.size, dstStream);
+}
+
+// Gives peer `p` the staged scene of the primary: host-side descriptions are copied, device-resident inputs (vertex /
+// index / tangent arrays, texture pyramids, raw envmap texels) travel GPU to GPU.  The peer then runs its own build().
+int replicateScene(const MtsContext *c, MtsContext *p) {
+    CUDA_TRY(cudaSetDevice(p->device));
+    cudaStream_t st = p->stream;
+    p->freeScene(); p->freeGeometry();
+    p->cam = c->cam; p->hasCam = c->hasCam;
+    if (c->hasFilm && (!p->hasFilm || std::memcmp(&p->film, &c->film, sizeof(MtsFilm)) != 0)) {
+        int rc = mtscuda_set_film(p, &c->film);
+        if (rc != MTS_OK) return rc;
+    }
+    p->nodes = c->nodes; p->pool = c->pool; p->shapes = c->shapes; p->envIndex = c->envIndex;
+    CUDA_TRY(peerCopy(p->positions, p->device, st, c->positions, c->device));
+    CUDA_TRY(peerCopy(p->normals, p->device, st, c->normals, c->device));
+    CUDA_TRY(peerCopy(p->texcoords, p->device, st, c->texcoords, c->device));
+    CUDA_TRY(peerCopy(p->tangents, p->device, st, c->tangents, c->device));
+    CUDA_TRY(peerCopy(p->indices, p->device, st, c->indices, c->device));
+    for (const HostTex &t : c->textures) {
+        HostTex q = t;
+        __half *px = nullptr;
+        CUDA_TRY(devAlloc(&px, t.bytes, st));
+        q.dt.texels = px; q.dt.weightLut = p->ewaLut;
+        p->textures.push_back(q);
+        CUDA_TRY(cudaMemcpyPeerAsync(px, p->device, t.dt.texels, c->device, t.bytes, st));
+    }
+    for (const HostEmitter &e : c->emitters) {
+        HostEmitter q; q.d = e.d;
+        if (e.envRaw) {
+            const size_t bytes = sizeof(float) * 3 * (size_t)e.d.env_width * e.d.env_height;
+            CUDA_TRY(devAlloc(&q.envRaw, bytes, st));
+            CUDA_TRY(cudaMemcpyPeerAsync(q.envRaw, p->device, e.envRaw, c->device, bytes, st));
+        }
+        p->emitters.push_back(q);
+    }
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return MTS_OK;
+}
+
+// film[primary] += sum of the peers' films, read over NVLink (peer access is enabled by create_multi); fixed order
+struct PeerFilms { const float4 *film[15]; const float *alpha[15]; int n; };
+__global__ void k_film_reduce(float4 *__restrict__ dst, float *__restrict__ dstAlpha, const PeerFilms P, size_t npix) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (size_t)gridDim.x * blockDim.x) {
+        float4 a = dst[i];
+        for (int k = 0; k < P.n; ++k) { const float4 b = P.film[k][i]; a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }
+        dst[i] = a;
+        if (dstAlpha) { float v = dstAlpha[i]; for (int k = 0; k < P.n; ++k) v += P.alpha[k][i]; dstAlpha[i] = v; }
+    }
+}
+
+} // namespace
+extern "C" {
+
+MTS_API int mtscuda_create_multi(const int32_t *devices, int32_t n, MtsContext **out) {
+    if (!out || !devices || n < 1) return fail(MTS_EINVAL, "create_multi: bad arguments");
+    if (n > 16) return fail(MTS_EINVAL, "create_multi: at most 16 devices");
+    for (int i = 0; i < n; ++i) for (int j = 0; j < i; ++j) if (devices[i] == devices[j]) return fail(MTS_EINVAL, "create_multi: device listed twice");
+    MtsContext *c = nullptr;
+    int rc = mtscuda_create(devices[0], &c);
+    if (rc != MTS_OK) return rc;
+    for (int i = 1; i < n; ++i) {
+        MtsContext *p = nullptr;
+        rc = mtscuda_create(devices[i], &p);
+        if (rc == MTS_OK) {
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, devices[0], devices[i]);
+            if (!can) { rc = fail(MTS_EINVAL, "create_multi: no peer access between devices " + std::to_string(devices[0]) + " and " + std::to_string(devices[i])); mtscuda_destroy(p); }
+        }
+        if (rc != MTS_OK) { mtscuda_destroy(c); return rc; }
+        c->peers.push_back(p);
+        // the primary reads the peers' films; the peers pull the scene from the primary
+        cudaSetDevice(devices[0]); if (cudaDeviceEnablePeerAccess(devices[i], 0) != cudaSuccess) cudaGetLastError();   // already enabled is fine
+        cudaSetDevice(devices[i]); if (cudaDeviceEnablePeerAccess(devices[0], 0) != cudaSuccess) cudaGetLastError();
+    }
+    cudaSetDevice(devices[0]);
+    *out = c;
+    return MTS_OK;
+}
+
+MTS_API int mtscuda_device_count(MtsContext *c) { return 1 + (int)c->peers.size(); }
+
+MTS_API int mtscuda_build(MtsContext *c) {
+    if (c->peers.empty()) return buildOne(c);
+    // peers copy the staged inputs and build their own acceleration structure while the primary builds its own
+    return forEachDevice(c, [&](int d) -> int {
+        if (d == 0) return buildOne(c);
+        MtsContext *p = c->peers[d - 1];
+        int rc = replicateScene(c, p);
+        return rc != MTS_OK ? rc : buildOne(p);
+    });
+}
+
+MTS_API int mtscuda_render(MtsContext *c, const MtsRenderParams *P, volatile const int *cancel, MtsStats *stats) {
+    if (c->peers.empty()) return renderOne(c, P, cancel, stats);
+    if (!c->built) return fail(MTS_ESTATE, "call build() first");
+    const int n = 1 + (int)c->peers.size();
+    const int stride = P->sample_stride > 0 ? P->sample_stride : 1;
+    std::vector<MtsStats> st(n);
+    std::vector<MtsRenderParams> pp(n, *P);
+    for (int d = 0; d < n; ++d) {
+        // device d renders samples d, d + n, d + 2n, ... of this call's sample set
+        pp[d].spp = P->spp / n + (d < P->spp % n ? 1 : 0);
+        pp[d].sample_offset = P->sample_offset + d * stride;
+        pp[d].sample_stride = stride * n;
+        pp[d].sample_count = P->sample_count > 0 ? P->sample_count : P->spp * stride;
+        if (d > 0) pp[d].clear_film = 1;
+        std::memset(&st[d], 0, sizeof(MtsStats));
+    }
+    int rc = forEachDevice(c, [&](int d) -> int {
+        MtsContext *x = d ? c->peers[d - 1] : c;
+        if (pp[d].spp == 0) {
+            if (pp[d].clear_film) {   // nothing to render here, but the film that gets reduced must not hold an earlier frame
+                cudaSetDevice(x->device);
+                cudaMemsetAsync(x->filmPtr(), 0, sizeof(float4) * (size_t)x->film.width * x->film.height, x->stream);
+                if (x->filmAlpha) cudaMemsetAsync(x->filmAlpha, 0, sizeof(float) * (size_t)x->film.width * x->film.height, x->stream);
+                cudaStreamSynchronize(x->stream);
+            }
+            return MTS_OK;
+        }
+        return renderOne(x, &pp[d], cancel, &st[d]);
+    });
+    if (rc != MTS_OK && rc != MTS_ECANCELLED) return rc;
+    // film reduce on the primary over NVLink
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    PeerFilms pf; pf.n = n - 1;
+    for (int k = 0; k < n - 1; ++k) { pf.film[k] = c->peers[k]->filmPtr(); pf.alpha[k] = c->peers[k]->filmAlpha; }
+    const size_t npix = (size_t)c->film.width * c->film.height;
+    cudaEventRecord(e0, c->stream);
+    k_film_reduce<<<c->numSMs * 4, 256, 0, c->stream>>>(c->filmPtr(), c->filmAlpha, pf, npix);
+    cudaEventRecord(e1, c->stream);
+    int rc2 = syncCheck(c, "film reduce");
+    float reduceMs = 0; cudaEventElapsedTime(&reduceMs, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (rc2 != MTS_OK) return rc2;
+    // merged statistics: counts add up, times are those of the slowest device
+    MtsStats m = st[0];
+    for (int d = 1; d < n; ++d) {
+        const MtsStats &s = st[d];
+        m.camera_samples += s.camera_samples; m.normal_rays += s.normal_rays; m.shadow_rays += s.shadow_rays;
+        m.path_length_sum += s.path_length_sum; m.kernel_launches += s.kernel_launches; m.bvh_nodes_visited += s.bvh_nodes_visited;
+        m.bvh_prims_tested += s.bvh_prims_tested; m.bvh_nodes_visited_shadow += s.bvh_nodes_visited_shadow; m.bvh_prims_tested_shadow += s.bvh_prims_tested_shadow;
+        m.shaded_paths += s.shaded_paths; m.miss_paths += s.miss_paths;
+        m.render_ms = std::max(m.render_ms, s.render_ms);
+    }
+    m.render_ms += reduceMs;
+    m.kernel_launches += 1;
+    m.build_ms = c->stats.build_ms;
+    c->stats = m;
+    if (stats) *stats = m;
+    return rc;
 }
 
 MTS_API int mtscuda_read_film(MtsContext *c, float *out) {

@@ -744,7 +744,10 @@ def flatten(scene):
     if md <= 0 and md != -1:
         raise ValueError("'maxDepth' must be set to -1 (infinite) or a value greater than zero!")
     fs.params = dict(max_depth=md, rr_depth=rr, strict_normals=bool(integ.get("strictNormals", False)),
-                     hide_emitters=bool(integ.get("hideEmitters", False)))
+                     hide_emitters=bool(integ.get("hideEmitters", False)),
+                     device=int(integ.get("device", 0)), devices=int(integ.get("devices", 1)))   # cudapath extras
+    if not 1 <= fs.params["devices"] <= 16:
+        raise ValueError("'devices' must be between 1 and 16!")
     # ---- sensor / film / sampler ----
     sensor = scene.child("sensor")
     if sensor is None or sensor.type != "perspective":

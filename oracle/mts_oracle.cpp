@@ -771,6 +771,8 @@ float triArea(V3 p0, V3 p1, V3 p2) { return 0.5f * length(cross(p1 - p0, p2 - p0
 extern "C" {
 
 MTS_API int32_t mtsoracle_abi_version(void) { return MTS_ABI_VERSION; }
+MTS_API int mtsoracle_create_multi(const int32_t *, int32_t, MtsContext **) { return fail(MTS_EINVAL, "create_multi: devices are a CUDA-library concept"); }
+MTS_API int mtsoracle_device_count(MtsContext *) { return 1; }
 MTS_API const char *mtsoracle_last_error(void) { return g_err.c_str(); }
 
 MTS_API int mtsoracle_create(int, MtsContext **out) {

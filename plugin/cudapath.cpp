@@ -56,6 +56,11 @@ public:
         m_strictNormals = props.getBoolean("strictNormals", false);
         m_hideEmitters = props.getBoolean("hideEmitters", false);
         m_device = props.getInteger("device", 0);          /* optional extras must be queried */
+        /* `devices`: how many GPUs of the box share the render, starting at `device` (the analogue of `mitsuba -p N`):
+           each takes every N-th sample of every pixel, the films are summed over NVLink (mtscuda_create_multi) */
+        m_devices = props.getInteger("devices", 1);
+        if (m_devices < 1 || m_devices > 16)
+            Log(EError, "'devices' must be between 1 and 16!");
         m_seed = (uint32_t) props.getInteger("seed", 0);
         if (m_rrDepth <= 0)
             Log(EError, "'rrDepth' must be set to a value greater than zero!");
@@ -69,6 +74,7 @@ public:
         m_strictNormals = stream->readBool();
         m_hideEmitters = stream->readBool();
         m_device = stream->readInt();
+        m_devices = stream->readInt();
         m_seed = stream->readUInt();
     }
 
@@ -79,6 +85,7 @@ public:
         stream->writeBool(m_strictNormals);
         stream->writeBool(m_hideEmitters);
         stream->writeInt(m_device);
+        stream->writeInt(m_devices);
         stream->writeUInt(m_seed);
     }
 
@@ -90,7 +97,12 @@ public:
         if (mtscuda_abi_version() != MTS_ABI_VERSION)
             Log(EError, "libmtscuda implements ABI version %i, this plugin was compiled against version %i -- rebuild both "
                 "from the same include/mtscuda.h", (int) mtscuda_abi_version(), (int) MTS_ABI_VERSION);
-        check(NULL, mtscuda_create(m_device, &ctx));
+        if (m_devices > 1) {
+            std::vector<int32_t> ids(m_devices);
+            for (int i = 0; i < m_devices; ++i) ids[i] = m_device + i;
+            check(NULL, mtscuda_create_multi(&ids[0], m_devices, &ctx));
+        } else
+            check(NULL, mtscuda_create(m_device, &ctx));
         bool ok = false;
         try {
             Flattener f(this, ctx);
@@ -107,8 +119,8 @@ public:
             p.strict_normals = m_strictNormals; p.hide_emitters = m_hideEmitters;
             p.seed = m_seed; p.clear_film = 1;
             p.sample_count = p.spp;                      /* scales the camera-ray differentials (integrator.cpp:144-145) */
-            Log(EInfo, "Starting render job (%ix%i, " SIZE_T_FMT " samples, CUDA device %i) ..", size.x, size.y,
-                scene->getSampler()->getSampleCount(), m_device);
+            Log(EInfo, "Starting render job (%ix%i, " SIZE_T_FMT " samples, %i CUDA device%s from %i) ..", size.x, size.y,
+                scene->getSampler()->getSampleCount(), m_devices, m_devices > 1 ? "s" : "", m_device);
             MtsStats st;
             int rc = mtscuda_render(ctx, &p, &m_cancel, &st);
             if (rc == MTS_ECANCELLED) {
@@ -159,7 +171,7 @@ public:
     std::string toString() const {
         std::ostringstream oss;
         oss << "CudaPath[" << endl << "  maxDepth = " << m_maxDepth << "," << endl << "  rrDepth = " << m_rrDepth << ","
-            << endl << "  strictNormals = " << m_strictNormals << "," << endl << "  device = " << m_device << endl << "]";
+            << endl << "  strictNormals = " << m_strictNormals << "," << endl << "  device = " << m_device << "," << endl << "  devices = " << m_devices << endl << "]";
         return oss.str();
     }
 
@@ -570,7 +582,7 @@ private:
         std::map<const BSDF *, int> m_bsdfIds;
     };
 
-    int m_maxDepth, m_rrDepth, m_device;
+    int m_maxDepth, m_rrDepth, m_device, m_devices;
     bool m_strictNormals, m_hideEmitters;
     uint32_t m_seed;
     volatile int m_cancel;

@@ -74,6 +74,20 @@ def test_cudapath_plugin_boundary_cases(name, bar):
 
 
 @needs_ref
+def test_cudapath_plugin_default_filter_type_scene():
+    """Stock bitmap textures (filterType ewa, maxAnisotropy 20) and the filtered environment map through the plugin:
+    usesRayDifferentials() of the live BSDFs decides which hits get uv partials."""
+    gold = G.load("mip.npz")
+    sc = G.mip()[0]
+    rs = mtsref.RefScene(sc, integrator="cudapath")
+    img = M.develop(rs.render())
+    ref = gold["image/mip/rgb"].astype(np.float32)
+    err = M.rel_mse(img, ref)
+    print("cudapath.so inside the reference host: relMSE(mip) = %.3g" % err)
+    assert abs(img.mean() / ref.mean() - 1) < 0.02 and err < 3e-3, err
+
+
+@needs_ref
 def test_cudapath_plugin_parameter_errors():
     sc = G.cornell_small(spp=1)
     sc.child("integrator").props["rrDepth"] = 0
