@@ -70,8 +70,12 @@ enum {
     MTS_BSDF_TWOSIDED = 9,       /* twosided.cpp */
     MTS_BSDF_THINDIELECTRIC = 10, /* thindielectric.cpp */
     MTS_BSDF_MASK = 11,          /* mask.cpp */
-    MTS_BSDF_ROUGHDIELECTRIC = 12 /* roughdielectric.cpp */
+    MTS_BSDF_ROUGHDIELECTRIC = 12, /* roughdielectric.cpp */
+    MTS_BSDF_MIXTURE = 13,       /* mixturebsdf.cpp */
+    MTS_BSDF_ROUGHCOATING = 14,  /* roughcoating.cpp */
+    MTS_BSDF_NORMALMAP = 15      /* normalmap.cpp */
 };
+#define MTS_MIXTURE_MAX 16 /* nested BSDFs of one mixturebsdf node */
 
 /* node.flags */
 enum {
@@ -103,6 +107,7 @@ enum {
  * reference probe, the oracle and the CUDA library.  The renderers use their own sample streams. */
 #define MTS_PROBE_U3(xbits, ybits, out) do { uint32_t h_ = (xbits) * 0x9E3779B1u ^ (ybits) * 0x85EBCA77u; h_ ^= h_ >> 15; \
     h_ *= 0xC2B2AE3Du; h_ ^= h_ >> 13; (out) = (float)(h_ >> 8) * (1.0f / 16777216.0f); } while (0)
+#define MTS_EALL 0x001FF /* BSDF::EAll: every diffuse, glossy, delta and 1-D delta lobe bit */
 #define MTS_ESMOOTH (MTS_EDIFFUSE_REFLECTION | MTS_EDIFFUSE_TRANSMISSION | MTS_EGLOSSY_REFLECTION | MTS_EGLOSSY_TRANSMISSION)
 #define MTS_EDELTA (MTS_ENULL | MTS_EDELTA_REFLECTION | MTS_EDELTA_TRANSMISSION)
 #define MTS_ETRANSMISSION (MTS_EDIFFUSE_TRANSMISSION | MTS_EGLOSSY_TRANSMISSION | MTS_EDELTA_TRANSMISSION | MTS_ENULL)
@@ -142,6 +147,13 @@ typedef struct MtsTexRef {
  *                  specularTransmittance = k[0..2] (scale) x bitmap texture lut[0] (-1: constant) -- a fourth
  *                  MtsTexRef folded into the otherwise unused k/lut slots
  *   twosided       child[0] = front-side BRDF, child[1] = back-side BRDF (= child[0] when only one is given)
+ *   mixturebsdf    lut[1] = N nested BSDFs (1..MTS_MIXTURE_MAX), lut[0] = offset of 3N + 1 floats in the float pool:
+ *                  N node indices (stored as floats), N weights (m_weights after the energy-conservation rescale),
+ *                  N + 1 entries of the normalised DiscreteDistribution CDF (m_pdf, include/mitsuba/core/pmf.h)
+ *   roughcoating   t0 = sigmaA, t1 = specularReflectance, t2 = alpha; eta[0]; f[0] = alphaMin, f[1] = alphaMax of the
+ *                  LUT, f[2] = specularSamplingWeight, f[3] = thickness; lut[0..2] = rough-transmittance slice as for
+ *                  roughplastic (external table only); child[0] = nested
+ *   normalmap      t0 = normals; child[0] = nested
  */
 typedef struct MtsBsdfNode {
     int32_t type;
@@ -268,7 +280,7 @@ typedef struct MtsContext MtsContext;
 /* Bumped whenever a struct or signature of this header changes.  A host compiled against another version would hand
  * the library structs of the wrong size (MtsStats is written through a caller-provided pointer), so every binding
  * compares MTS_FN(abi_version)() with the MTS_ABI_VERSION it was compiled with before the first call. */
-#define MTS_ABI_VERSION 4
+#define MTS_ABI_VERSION 5
 MTS_API int32_t MTS_FN(abi_version)(void);
 MTS_API const char *MTS_FN(last_error)(void);
 MTS_API int MTS_FN(create)(int device, MtsContext **out);

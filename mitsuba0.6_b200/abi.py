@@ -17,8 +17,10 @@ FILTER_RESOLUTION = 31
 EPSILON = 1e-4
 
 # ---- enums (mirror include/mtscuda.h) --------------------------------------
-BSDF_DIFFUSE, BSDF_CONDUCTOR, BSDF_ROUGHCONDUCTOR, BSDF_PLASTIC, BSDF_ROUGHPLASTIC, \
-    BSDF_DIELECTRIC, BSDF_COATING, BSDF_BLEND, BSDF_BUMPMAP, BSDF_TWOSIDED, BSDF_THINDIELECTRIC, BSDF_MASK, BSDF_ROUGHDIELECTRIC = range(13)
+(BSDF_DIFFUSE, BSDF_CONDUCTOR, BSDF_ROUGHCONDUCTOR, BSDF_PLASTIC, BSDF_ROUGHPLASTIC,
+    BSDF_DIELECTRIC, BSDF_COATING, BSDF_BLEND, BSDF_BUMPMAP, BSDF_TWOSIDED, BSDF_THINDIELECTRIC, BSDF_MASK, BSDF_ROUGHDIELECTRIC,
+    BSDF_MIXTURE, BSDF_ROUGHCOATING, BSDF_NORMALMAP) = range(16)
+MIXTURE_MAX = 16
 BF_GGX, BF_SAMPLE_VISIBLE, BF_NONLINEAR, BF_RT_2D, BF_RAY_DIFF = 1, 2, 4, 8, 16
 ENULL, EDIFFUSE_REFLECTION, EDIFFUSE_TRANSMISSION, EGLOSSY_REFLECTION, EGLOSSY_TRANSMISSION, \
     EDELTA_REFLECTION, EDELTA_TRANSMISSION = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20, 0x40
@@ -99,7 +101,7 @@ class Stats(C.Structure):
 
 
 # every symbol include/mtscuda.h declares (tests check that the libraries export all of them)
-ABI_VERSION = 4   # MTS_ABI_VERSION of include/mtscuda.h these mirrors were written against
+ABI_VERSION = 5   # MTS_ABI_VERSION of include/mtscuda.h these mirrors were written against
 ABI_SYMBOLS = [
     "abi_version", "last_error", "create", "create_multi", "device_count", "destroy", "set_camera", "set_film", "add_texture", "set_float_pool",
     "set_bsdfs", "add_mesh", "add_rectangle", "add_sphere", "add_emitter", "build", "render",

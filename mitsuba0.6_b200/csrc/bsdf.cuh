@@ -34,8 +34,7 @@ DEVFN TexCtx texCtx(float2 uv) { TexCtx t; t.uv = uv; t.duv = make_float4(0, 0, 
 
 // evalTexel coordinate handling (mipmap.h:503-563): returns the wrapped coordinate, or -1 / -2 when the lookup
 // yields the constant 0 / 1 (EZero / EOne boundary conditions)
-DEVFN int wrapCoord(int x, int size, int mode) {
-    if (x >= 0 && x < size) return x;
+DEVOL int wrapCoordOutside(int x, int size, int mode) {
     switch (mode) {
         case MTS_WRAP_REPEAT: return wrapRepeat(x, size);
         case MTS_WRAP_CLAMP: return clampi(x, 0, size - 1);
@@ -43,6 +42,10 @@ DEVFN int wrapCoord(int x, int size, int mode) {
         case MTS_WRAP_ZERO: return -1;
         default: return -2;
     }
+}
+DEVFN int wrapCoord(int x, int size, int mode) {   // the in-range test stays inline, the boundary conditions are one shared copy
+    if (x >= 0 && x < size) return x;
+    return wrapCoordOutside(x, size, mode);
 }
 DEVFN float3 texelAt(const __half *base, int channels, size_t i) {
     if (channels == 1) return f3(__half2float(__ldg(base + i)));
@@ -53,6 +56,15 @@ DEVFN float3 texelAt(const __half *base, int channels, size_t i) {
 // The four texels of a bilinear footprint on one pyramid level.  Coordinates are wrapped once per row / column and
 // all four loads are issued back to back (one round trip to L2/HBM instead of four dependent ones).
 struct Quad { float3 p00, p10, p01, p11; };
+// EZero / EOne boundary conditions (rare): a coordinate outside the image yields the constant (mipmap.h:503-563)
+DEVOL void quadBoundaryConstants(Quad &q, int xa, int xb, int ya, int yb) {
+    const int bx0 = xa < 0 ? xa : 0, bx1 = xb < 0 ? xb : 0, by0 = ya < 0 ? ya : 0, by1 = yb < 0 ? yb : 0;
+    auto konst = [](int cx, int cy) { return f3((cx == -2 || (cx == 0 && cy == -2)) ? 1.0f : 0.0f); };  // u is tested first
+    if (bx0 | by0) q.p00 = konst(bx0, by0);
+    if (bx1 | by0) q.p10 = konst(bx1, by0);
+    if (bx0 | by1) q.p01 = konst(bx0, by1);
+    if (bx1 | by1) q.p11 = konst(bx1, by1);
+}
 DEVFN Quad texQuad(const DTexture &t, const __half *base, int w, int h, int x0, int y0) {
     const int xa = wrapCoord(x0, w, t.wrapU), xb = wrapCoord(x0 + 1, w, t.wrapU);
     const int ya = wrapCoord(y0, h, t.wrapV), yb = wrapCoord(y0 + 1, h, t.wrapV);
@@ -71,15 +83,7 @@ DEVFN Quad texQuad(const DTexture &t, const __half *base, int w, int h, int x0, 
         };
         q.p00 = cvt(r00); q.p10 = cvt(r10); q.p01 = cvt(r01); q.p11 = cvt(r11);
     }
-    // EZero / EOne boundary conditions (rare): a coordinate outside the image yields the constant
-    const int bx0 = xa < 0 ? xa : 0, bx1 = xb < 0 ? xb : 0, by0 = ya < 0 ? ya : 0, by1 = yb < 0 ? yb : 0;
-    if (bx0 | bx1 | by0 | by1) {
-        auto konst = [](int cx, int cy) { return f3((cx == -2 || (cx == 0 && cy == -2)) ? 1.0f : 0.0f); };  // u is tested first
-        if (bx0 | by0) q.p00 = konst(bx0, by0);
-        if (bx1 | by0) q.p10 = konst(bx1, by0);
-        if (bx0 | by1) q.p01 = konst(bx0, by1);
-        if (bx1 | by1) q.p11 = konst(bx1, by1);
-    }
+    if ((xa | xb | ya | yb) < 0) quadBoundaryConstants(q, xa, xb, ya, yb);
     return q;
 }
 // evalTexel(level, x, y), mipmap.h:503-563
@@ -129,57 +133,117 @@ DEVFN void texGradient(const DTexture &t, float2 uv, float3 &g0, float3 &g1) {
     g0 = (q.p10 + q.p00 * (dy - 1) - tmp * dy) * (float)t.width;
     g1 = (q.p01 + q.p00 * (dx - 1) - tmp * dx) * (float)t.height;
 }
-// evalEWA(level, uv, A, B, C), mipmap.h:764-834.  The running quadratic q is updated with separately rounded adds (no
-// FMA contraction) like the host code, because it indexes the weight table.
-static __device__ __noinline__ float3 mipEWA(const DTexture &t, int level, float2 uv, float A, float B, float C) {
-    if (!isfinite(A + B + C + uv.x + uv.y)) return f3(0.0f);
-    if (level >= t.levels) return mipBox(t, t.levels - 1, uv);
-    const int w = t.levelW[level], h = t.levelH[level];
-    const __half *base = mipBase(t, level);
+// ---- evalEWA(level, uv, A, B, C), mipmap.h:764-834 -------------------------------------------------------------------
+// The reference walks the bounding box of the ellipse row by row and weights every texel whose running quadratic q lies
+// below the table size.  The walk here visits the same texels in the same order with the same separately rounded
+// updates of q (it indexes the weight table, so no FMA contraction), but
+//   * with the row's wrapped v coordinate and base pointer hoisted out of the column walk,
+//   * and optionally for TWO textures that share their geometry (size, uv transform, wrap modes: the albedo / specular
+//     pair of a material), which then share the footprint, the weights and the walk.
+DEVFN bool sameTextureGeometry(const DTexture &a, const DTexture &b) {
+    return a.width == b.width && a.height == b.height && a.levels == b.levels && a.wrapU == b.wrapU && a.wrapV == b.wrapV &&
+           a.filter == b.filter && a.maxAnisotropy == b.maxAnisotropy && a.uvScale.x == b.uvScale.x && a.uvScale.y == b.uvScale.y &&
+           a.uvOffset.x == b.uvOffset.x && a.uvOffset.y == b.uvOffset.y;
+}
+// wrapCoord with the common cases inline: inside the image, or a repeating power-of-two image
+DEVFN int wrapCoordFast(int x, int size, int mode) {
+    if ((unsigned)x < (unsigned)size) return x;
+    if (mode == MTS_WRAP_REPEAT && (size & (size - 1)) == 0) return x & (size - 1);
+    return wrapCoordOutside(x, size, mode);
+}
+// evalEWA on ONE level for one or two textures (tb == nullptr: one): the value(s) of the level
+template <bool PAIR>
+DEVFN void ewaWalk(const DTexture &ta, const DTexture *tb, int level, float2 uv, float A0, float B0, float C0, float3 &outA, float3 &outB) {
+    outB = f3(0.0f);
+    if (!isfinite(A0 + B0 + C0 + uv.x + uv.y)) { outA = f3(0.0f); return; }
+    if (level >= ta.levels) { outA = mipBox(ta, ta.levels - 1, uv); if (PAIR) outB = mipBox(*tb, tb->levels - 1, uv); return; }
+    const int w = ta.levelW[level], h = ta.levelH[level];
     const float u = uv.x * w - 0.5f, v = uv.y * h - 0.5f;
-    const float ratioX = (float)w / (float)t.width, ratioY = (float)h / (float)t.height;   // m_sizeRatio
-    A /= ratioX * ratioX; B /= ratioX * ratioY; C /= ratioY * ratioY;
+    const float ratioX = (float)w / (float)ta.width, ratioY = (float)h / (float)ta.height;   // m_sizeRatio
+    const float A = A0 / (ratioX * ratioX), B = B0 / (ratioX * ratioY), C = C0 / (ratioY * ratioY);
     const float invDet = 1.0f / (-B * B + 4.0f * A * C), deltaU = 2.0f * sqrtf(C * invDet), deltaV = 2.0f * sqrtf(A * invDet);
     const int u0 = (int)ceilf(u - deltaU), u1 = floorToInt(u + deltaU), v0 = (int)ceilf(v - deltaV), v1 = floorToInt(v + deltaV);
     const float As = A * MTS_MIPMAP_LUT_SIZE, Bs = B * MTS_MIPMAP_LUT_SIZE, Cs = C * MTS_MIPMAP_LUT_SIZE;
-    float3 result = f3(0.0f);
-    float denominator = 0.0f;
     const float ddq = 2 * As, uu0 = (float)u0 - u;
+    const bool monoA = ta.channels == 1, monoB = PAIR ? tb->channels == 1 : false;
+    const __half *baseA = mipBase(ta, level), *baseB = PAIR ? mipBase(*tb, level) : nullptr;
+    float3 sumA = f3(0.0f), sumB = f3(0.0f);
+    float den = 0.0f;
     for (int vt = v0; vt <= v1; ++vt) {
         const float vv = (float)vt - v;
         float q = __fadd_rn(__fmul_rn(__fmul_rn(As, uu0), uu0), __fmul_rn(__fadd_rn(__fmul_rn(Bs, uu0), __fmul_rn(Cs, vv)), vv));
         float dq = __fadd_rn(__fmul_rn(As, __fadd_rn(__fmul_rn(2.0f, uu0), 1.0f)), __fmul_rn(Bs, vv));
+        const int ya = wrapCoordFast(vt, h, ta.wrapV);       // hoisted out of the column walk
+        const size_t off = (size_t)max(ya, 0) * w;
+        const __half *rowA = baseA + off * (monoA ? 1 : 4), *rowB = PAIR ? baseB + off * (monoB ? 1 : 4) : nullptr;
         for (int ut = u0; ut <= u1; ++ut) {
             if (q < (float)MTS_MIPMAP_LUT_SIZE) {
                 const uint32_t qi = (uint32_t)q;
                 if (qi < MTS_MIPMAP_LUT_SIZE) {
-                    const float weight = __ldg(t.weightLut + (int)q);
-                    result += texel(t, base, w, h, ut, vt) * weight;
-                    denominator += weight;
+                    const float weight = __ldg(ta.weightLut + (int)q);
+                    const int xa = wrapCoordFast(ut, w, ta.wrapU);
+                    float3 texA, texB = f3(0.0f);
+                    if (xa < 0) texA = texB = f3(xa == -2 ? 1.0f : 0.0f);          // EZero / EOne: u is tested first (evalTexel, mipmap.h:503-563)
+                    else if (ya < 0) texA = texB = f3(ya == -2 ? 1.0f : 0.0f);
+                    else { texA = texelAt(rowA, monoA ? 1 : 3, (size_t)xa); if (PAIR) texB = texelAt(rowB, monoB ? 1 : 3, (size_t)xa); }
+                    sumA += texA * weight;
+                    if (PAIR) sumB += texB * weight;
+                    den += weight;
                 }
             }
             q = __fadd_rn(q, dq);
             dq = __fadd_rn(dq, ddq);
         }
     }
-    if (denominator == 0) return mipBilinear(t, level, uv);
-    return result / denominator;
+    if (den == 0) { outA = mipBilinear(ta, level, uv); if (PAIR) outB = mipBilinear(*tb, level, uv); return; }   // mipmap.h:829-830
+    outA = sumA / den;
+    if (PAIR) outB = sumB / den;
 }
-// TMIPMap::eval(uv, d0, d1), mipmap.h:629-715: level selection, trilinear interpolation, anisotropy clamp, EWA
-static __device__ __noinline__ float3 mipEval(const DTexture &t, float2 uv, float2 d0, float2 d1) {
-    if (t.filter == MTS_FILTER_NEAREST) return mipBox(t, 0, uv);
-    if (t.filter == MTS_FILTER_BILINEAR) return mipBilinear(t, 0, uv);
+// kept out of line: one copy of each walk per kernel.  evalEWA(ilevel) * (1 - a) + evalEWA(ilevel + 1) * a, mipmap.h:712-713
+static __device__ __noinline__ float3 mipEWA2(const DTexture &t, int ilevel, float2 uv, float A, float B, float C, float a) {
+    float3 l0, l1, unused;
+    ewaWalk<false>(t, nullptr, ilevel, uv, A, B, C, l0, unused);
+    ewaWalk<false>(t, nullptr, ilevel + 1, uv, A, B, C, l1, unused);
+    return l0 * (1.0f - a) + l1 * a;
+}
+static __device__ __noinline__ void mipEWA2Pair(const DTexture &ta, const DTexture &tb, int ilevel, float2 uv, float A, float B, float C, float a,
+                                                float3 &ra, float3 &rb) {
+    float3 a0, a1, b0, b1;
+    ewaWalk<true>(ta, &tb, ilevel, uv, A, B, C, a0, b0);
+    ewaWalk<true>(ta, &tb, ilevel + 1, uv, A, B, C, a1, b1);
+    ra = a0 * (1.0f - a) + a1 * a;
+    rb = b0 * (1.0f - a) + b1 * a;
+}
+// math::hypot2 (include/mitsuba/core/math.h) with separately rounded operations
+DEVFN float hypot2Exact(float a, float b) {
+    if (fabsf(a) > fabsf(b)) { const float r = __fdiv_rn(b, a); return __fmul_rn(fabsf(a), sqrtf(__fadd_rn(1.0f, __fmul_rn(r, r)))); }
+    if (b != 0.0f) { const float r = __fdiv_rn(a, b); return __fmul_rn(fabsf(b), sqrtf(__fadd_rn(1.0f, __fmul_rn(r, r)))); }
+    return 0.0f;
+}
+// TMIPMap::eval(uv, d0, d1), mipmap.h:629-715: level selection, trilinear interpolation, anisotropy clamp.  What is left
+// to do after the footprint analysis: one bilinear lookup, two (trilinear), or the EWA walk of two levels.
+struct MipFoot { int kind, ilevel; float a, A, B, C; };
+enum { FOOT_BOX0 = 0, FOOT_BILINEAR = 1, FOOT_TRILINEAR = 2, FOOT_EWA = 3 };
+DEVFN MipFoot mipFootprint(const DTexture &t, float2 d0, float2 d1) {
+    MipFoot f; f.kind = FOOT_BILINEAR; f.ilevel = 0; f.a = 0; f.A = f.B = f.C = 0;
+    if (t.filter == MTS_FILTER_NEAREST) { f.kind = FOOT_BOX0; return f; }
+    if (t.filter == MTS_FILTER_BILINEAR) return f;
+    // Degenerate footprints (one partial zero, F = AC - B^2/4 = 0 up to rounding) decide the branch below by the SIGN of
+    // rounding noise: every product and sum is rounded separately, as the host code does (no FMA contraction), so that
+    // the same branch is taken as in the reference.
     const float du0 = d0.x * t.width, dv0 = d0.y * t.height, du1 = d1.x * t.width, dv1 = d1.y * t.height;
-    float A = dv0 * dv0 + dv1 * dv1, B = -2.0f * (du0 * dv0 + du1 * dv1), C = du0 * du0 + du1 * du1, F = A * C - B * B * 0.25f;
-    const float root = hypot2(A - C, B), Aprime = 0.5f * (A + C - root), Cprime = 0.5f * (A + C + root);
-    float majorRadius = Aprime != 0 ? sqrtf(F / Aprime) : 0, minorRadius = Cprime != 0 ? sqrtf(F / Cprime) : 0;
+    float A = __fadd_rn(__fmul_rn(dv0, dv0), __fmul_rn(dv1, dv1)), B = __fmul_rn(-2.0f, __fadd_rn(__fmul_rn(du0, dv0), __fmul_rn(du1, dv1))),
+          C = __fadd_rn(__fmul_rn(du0, du0), __fmul_rn(du1, du1)), F = __fsub_rn(__fmul_rn(A, C), __fmul_rn(__fmul_rn(B, B), 0.25f));
+    const float root = hypot2Exact(__fsub_rn(A, C), B), Aprime = __fmul_rn(0.5f, __fsub_rn(__fadd_rn(A, C), root)),
+                Cprime = __fmul_rn(0.5f, __fadd_rn(__fadd_rn(A, C), root));
+    float majorRadius = Aprime != 0 ? sqrtf(__fdiv_rn(F, Aprime)) : 0, minorRadius = Cprime != 0 ? sqrtf(__fdiv_rn(F, Cprime)) : 0;
     const float invLn2 = 1.4426950408889634f;   // math::log2 = fastlog * (1 / log 2), src/libcore/math.cpp:103-106
     if (t.filter == MTS_FILTER_TRILINEAR || !(minorRadius > 0) || !(majorRadius > 0) || F < 0) {
         const float level = fastlog(fmaxf(majorRadius, kEps)) * invLn2;
         const int ilevel = floorToInt(level);
-        if (ilevel < 0) return mipBilinear(t, 0, uv);
-        const float a = level - ilevel;
-        return mipBilinear(t, ilevel, uv) * (1.0f - a) + mipBilinear(t, ilevel + 1, uv) * a;
+        if (ilevel < 0) return f;
+        f.kind = FOOT_TRILINEAR; f.ilevel = ilevel; f.a = level - ilevel;
+        return f;
     }
     if (minorRadius * t.maxAnisotropy < majorRadius) {
         minorRadius = majorRadius / t.maxAnisotropy;
@@ -195,13 +259,25 @@ static __device__ __noinline__ float3 mipEval(const DTexture &t, float2 uv, floa
     const float scale = 1.0f / F;
     A *= scale; B *= scale; C *= scale;
     const float level = fmaxf(0.0f, fastlog(minorRadius) * invLn2);
-    const int ilevel = (int)level;
-    const float a = level - ilevel;
-    if (majorRadius < 1 || !(A > 0 && C > 0)) return mipBilinear(t, ilevel, uv);
-    return mipEWA(t, ilevel, uv, A, B, C) * (1.0f - a) + mipEWA(t, ilevel + 1, uv, A, B, C) * a;
+    f.ilevel = (int)level;
+    f.a = level - f.ilevel;
+    if (majorRadius < 1 || !(A > 0 && C > 0)) return f;   // evalBilinear(ilevel, uv)
+    f.kind = FOOT_EWA; f.A = A; f.B = B; f.C = C;
+    return f;
+}
+DEVFN float3 mipEvalFoot(const DTexture &t, float2 uv, const MipFoot &f) {
+    switch (f.kind) {
+    case FOOT_BOX0: return mipBox(t, 0, uv);
+    case FOOT_BILINEAR: return mipBilinear(t, f.ilevel, uv);
+    case FOOT_TRILINEAR: return mipBilinear(t, f.ilevel, uv) * (1.0f - f.a) + mipBilinear(t, f.ilevel + 1, uv) * f.a;
+    default: return mipEWA2(t, f.ilevel, uv, f.A, f.B, f.C, f.a);
+    }
+}
+static __device__ __noinline__ float3 mipEval(const DTexture &t, float2 uv, float2 d0, float2 d1) {
+    return mipEvalFoot(t, uv, mipFootprint(t, d0, d1));
 }
 // Texture2D::eval(its, filter = true) (src/librender/texture.cpp:104-114) + ScalingTexture (src/textures/scale.cpp:86-88)
-DEVFN float3 evalTex(const Mats S, const MtsTexRef &r, const TexCtx &tc) {
+DEVOL float3 evalTex(const Mats S, const MtsTexRef &r, const TexCtx &tc) {
     float3 s = f3(r.scale[0], r.scale[1], r.scale[2]);
     if (r.tex < 0) return s;
     const DTexture &t = S.textures[r.tex];
@@ -209,6 +285,46 @@ DEVFN float3 evalTex(const Mats S, const MtsTexRef &r, const TexCtx &tc) {
     if (tc.filtered && t.filter >= MTS_FILTER_TRILINEAR)   // bitmap.cpp:486-499; nearest / bilinear ignore the partials (mipmap.h:630-633)
         return mipEval(t, uv, make_float2(tc.duv.x * t.uvScale.x, tc.duv.y * t.uvScale.y), make_float2(tc.duv.z * t.uvScale.x, tc.duv.w * t.uvScale.y)) * s;
     return texLookup(t, uv) * s;
+}
+// A filtered lookup whose EWA walk is left to a kernel of its own (k_shade_ewa of the staged shade): only a fraction of
+// the lanes of a warp need a walk at all, and those that do wait on dependent texel loads -- as one job per thread pair the
+// walks run with full warps at high occupancy.  slotA: which of the two texture slots texA fills (texB always fills slot 1).
+struct EwaDefer { int texA, texB, slotA, ilevel; float a, A, B, C; float2 uv; bool pending; };
+DEVFN void deferEwa(EwaDefer &d, int texA, int texB, int slotA, const MipFoot &foot, float2 uv) {
+    d.pending = true; d.texA = texA; d.texB = texB; d.slotA = slotA; d.ilevel = foot.ilevel;
+    d.a = foot.a; d.A = foot.A; d.B = foot.B; d.C = foot.C; d.uv = uv;
+}
+// Two texture slots of one material at one hit.  Bitmaps that share their geometry (the usual albedo / specular pair) and
+// are filtered with EWA share one footprint analysis and one walk over the texels.  With `defer` the walk is not done here.
+DEVOL void evalTexPair(const Mats S, const MtsTexRef &ra, const MtsTexRef &rb, const TexCtx &tc, float3 &ca, float3 &cb, EwaDefer *defer) {
+    if (tc.filtered) {
+        const bool fa = ra.tex >= 0 && S.textures[max(ra.tex, 0)].filter == MTS_FILTER_EWA;
+        const bool fb = rb.tex >= 0 && S.textures[max(rb.tex, 0)].filter == MTS_FILTER_EWA;
+        if (fa || fb) {
+            const DTexture &ta = S.textures[fa ? ra.tex : rb.tex];
+            const float2 uv = make_float2(tc.uv.x * ta.uvScale.x + ta.uvOffset.x, tc.uv.y * ta.uvScale.y + ta.uvOffset.y);
+            const MipFoot foot = mipFootprint(ta, make_float2(tc.duv.x * ta.uvScale.x, tc.duv.y * ta.uvScale.y),
+                                              make_float2(tc.duv.z * ta.uvScale.x, tc.duv.w * ta.uvScale.y));
+            if (fa && fb && sameTextureGeometry(ta, S.textures[rb.tex])) {
+                const DTexture &tb = S.textures[rb.tex];
+                float3 va = f3(0.0f), vb = f3(0.0f);
+                if (foot.kind == FOOT_EWA) {
+                    if (defer) { deferEwa(*defer, ra.tex, rb.tex, 0, foot, uv); ca = cb = f3(0.0f); return; }
+                    mipEWA2Pair(ta, tb, foot.ilevel, uv, foot.A, foot.B, foot.C, foot.a, va, vb);
+                } else { va = mipEvalFoot(ta, uv, foot); vb = mipEvalFoot(tb, uv, foot); }
+                ca = va * f3(ra.scale[0], ra.scale[1], ra.scale[2]);
+                cb = vb * f3(rb.scale[0], rb.scale[1], rb.scale[2]);
+                return;
+            }
+            if (defer && foot.kind == FOOT_EWA) {   // one walk can be deferred: that of the first EWA texture
+                deferEwa(*defer, fa ? ra.tex : rb.tex, -1, fa ? 0 : 1, foot, uv);
+                if (fa) { ca = f3(0.0f); cb = evalTex(S, rb, tc); } else { cb = f3(0.0f); ca = evalTex(S, ra, tc); }
+                return;
+            }
+        }
+    }
+    ca = evalTex(S, ra, tc);
+    cb = evalTex(S, rb, tc);
 }
 // Texture2D::evalGradient (texture.cpp:116-124) + ScalingTexture::evalGradient (scale.cpp:90-94)
 DEVFN void evalTexGradient(const Mats S, const MtsTexRef &r, float2 uv, float3 &g0, float3 &g1) {
@@ -232,7 +348,7 @@ struct Microfacet {
     DEVFN bool isIsotropic() const { return alphaU == alphaV; }
     DEVFN void scaleAlpha(float v) { alphaU *= v; alphaV *= v; }   // :96-99
     // :191-234
-    DEVFN float eval(float3 m) const {
+    DEVOLM float eval(float3 m) const {
         if (cosTheta(m) <= 0) return 0.0f;
         float ct2 = cosTheta2(m);
         float be = ((m.x * m.x) / (alphaU * alphaU) + (m.y * m.y) / (alphaV * alphaV)) / ct2;
@@ -250,7 +366,7 @@ struct Microfacet {
         return sqrtf(cosPhi2 * alphaU * alphaU + sinPhi2 * alphaV * alphaV);
     }
     // :477-514
-    DEVFN float smithG1(float3 v, float3 m) const {
+    DEVOLM float smithG1(float3 v, float3 m) const {
         if (dot(v, m) * cosTheta(v) <= 0) return 0.0f;
         float tt = fabsf(tanTheta(v));
         if (tt == 0.0f) return 1.0f;
@@ -272,7 +388,7 @@ struct Microfacet {
     }
     DEVFN float pdf(float3 wi, float3 m) const { return sampleVisible ? pdfVisible(wi, m) : pdfAll(m); }
     // :287-395
-    DEVFN float3 sampleAll(float2 sample, float &pdf) const {
+    DEVOLM float3 sampleAll(float2 sample, float &pdf) const {
         float cosThetaM, sinPhiM, cosPhiM, alphaSqr;
         if (isIsotropic()) {
             sincosf((2.0f * kPi) * sample.y, &sinPhiM, &cosPhiM);
@@ -353,7 +469,7 @@ struct Microfacet {
         return slope;
     }
     // :421-459
-    DEVFN float3 sampleVisibleNormal(float3 _wi, float2 sample) const {
+    DEVOLM float3 sampleVisibleNormal(float3 _wi, float2 sample) const {
         float3 wi = normalize(f3(alphaU * _wi.x, alphaV * _wi.y, _wi.z));
         float theta = 0, phi = 0;
         if (wi.z < 0.99999f) { theta = acosf(wi.z); phi = atan2f(wi.y, wi.x); }
@@ -413,7 +529,7 @@ DEVFN float cubicInterp2D(float px, float py, const float *values, int sx, int s
     return result;
 }
 // RoughTransmittance::eval on the host-reduced slices (src/bsdfs/rtrans.h:183-233)
-DEVFN float roughTransmittance(const Mats S, const MtsBsdfNode &n, float ct, float alpha) {
+DEVOL float roughTransmittance(const Mats S, const MtsBsdfNode &n, float ct, float alpha) {
     if (!(ct >= 0)) return 0.f;
     float warpedCosTheta = sqrtf(sqrtf(fabsf(ct))), result;  // std::pow(x, 0.25)
     const float *tab = S.pool + n.lut[0];
@@ -446,9 +562,10 @@ struct BSample { float3 wo; float pdf; float eta; uint32_t type; float u3; };   
 // c3 = roughdielectric's specularTransmittance, kept in the k / lut slots of the node.
 struct LeafTex { float3 c0, c1, c2, c3; };
 DEVFN MtsTexRef roughDielTransmittance(const MtsBsdfNode &n) { MtsTexRef r; r.scale[0] = n.k[0]; r.scale[1] = n.k[1]; r.scale[2] = n.k[2]; r.tex = n.lut[0]; return r; }
-DEVFN LeafTex resolveLeaf(const Mats S, const MtsBsdfNode &n, const TexCtx &tc) {
+DEVFN LeafTex resolveLeaf(const Mats S, const MtsBsdfNode &n, const TexCtx &tc, EwaDefer *defer = nullptr) {
     LeafTex lt;
-    lt.c0 = evalTex(S, n.t0, tc); lt.c1 = evalTex(S, n.t1, tc); lt.c2 = evalTex(S, n.t2, tc);
+    evalTexPair(S, n.t0, n.t1, tc, lt.c0, lt.c1, defer);
+    lt.c2 = evalTex(S, n.t2, tc);
     lt.c3 = n.type == MTS_BSDF_ROUGHDIELECTRIC ? evalTex(S, roughDielTransmittance(n), tc) : f3(0.0f);
     return lt;
 }
@@ -538,7 +655,7 @@ static __device__ __noinline__ float3 roughDielSample(const Mats S, const MtsBsd
 // ---------------------------------------------------------------------------------------
 // RoughPlastic::eval / pdf in the solid angle measure (src/bsdfs/roughplastic.cpp:326-382, 384-437); inlined into the leaf
 // switches AND into roughplastic's sample(), which returns eval / pdf of the sampled direction (:494-500)
-DEVFN float3 roughPlasticEval(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float3 wo) {
+DEVOL float3 roughPlasticEval(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float3 wo) {
     if (cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return f3(0.0f);
     float eta = n.eta[0];
     float a = average(lt.c2);
@@ -563,7 +680,7 @@ DEVFN float3 roughPlasticEval(const Mats S, const MtsBsdfNode &n, const LeafTex 
     }
     return result;
 }
-DEVFN float roughPlasticPdf(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float3 wo) {
+DEVOL float roughPlasticPdf(const Mats S, const MtsBsdfNode &n, const LeafTex &lt, float3 wi, float3 wo) {
     if (cosTheta(wi) <= 0 || cosTheta(wo) <= 0) return 0.0f;
     float a = average(lt.c2);
     Microfacet distr(n.flags & MTS_BF_GGX, a, a, n.flags & MTS_BF_SAMPLE_VISIBLE);
@@ -847,9 +964,23 @@ DEVFN Frame bumpFrame(const Mats S, const MtsBsdfNode &n, const Surf &su) {
     if (dot(r.n, su.geoN) < 0) r.n = -r.n;
     return r;
 }
+// NormalMap::getFrame (src/bsdfs/normalmap.cpp:106-123): the texture is read unfiltered (m_normals->eval(its, false))
+DEVFN Frame normalMapFrame(const Mats S, const MtsBsdfNode &n, const Surf &su) {
+    const float3 v = evalTex(S, n.t0, texCtx(su.tc.uv));
+    const float3 nl = f3(2 * v.x - 1, 2 * v.y - 1, 2 * v.z - 1);
+    Frame r;
+    r.n = normalize(su.sh.toWorld(nl));
+    r.s = normalize(su.dpdu - r.n * dot(r.n, su.dpdu));
+    r.t = cross(r.n, r.s);
+    return r;
+}
+// the frame adapters: bumpmap and normalmap differ only in how the perturbed frame is found
+DEVFN Frame perturbedFrame(const Mats S, const MtsBsdfNode &n, const Surf &su) {
+    return n.type == MTS_BSDF_NORMALMAP ? normalMapFrame(S, n, su) : bumpFrame(S, n, su);
+}
 DEVFN Frame bumpFrameCached(const Mats S, int node, const MtsBsdfNode &n, const Surf &su) {
     if (su.bumpNode == node) return su.bumpCache;
-    Frame f = bumpFrame(S, n, su);
+    Frame f = perturbedFrame(S, n, su);
     su.bumpNode = node; su.bumpCache = f;
     return f;
 }
@@ -864,6 +995,38 @@ DEVFN float3 coatRefractOut(float eta, float3 wi, float &R) {
     R = fresnelDielectricExt(fabsf(cosTheta(wi)), cosThetaT, invEta);
     return f3(eta * wi.x, eta * wi.y, -signum(cosTheta(wi)) * cosThetaT);
 }
+
+// RoughCoating::refractTo (src/bsdfs/roughcoating.cpp:232-253); etaTo = 1/eta towards the interior, eta towards the exterior
+DEVFN float3 roughCoatRefract(float etaTo, float3 wi) {
+    const float sinThetaTSqr = etaTo * etaTo * sinTheta2(wi);
+    if (sinThetaTSqr >= 1.0f) return f3(0.0f);
+    const float cosThetaT = sqrtf(1.0f - sinThetaTSqr);
+    return f3(etaTo * wi.x, etaTo * wi.y, cosTheta(wi) > 0.0f ? cosThetaT : -cosThetaT);
+}
+// probability of the specular lobe of roughcoating (roughcoating.cpp:332-343, 388-397)
+DEVFN float roughCoatProbSpecular(const Mats S, const MtsBsdfNode &n, float3 wi, float alpha) {
+    float probSpecular = 1 - roughTransmittance(S, n, fabsf(cosTheta(wi)), alpha);
+    const float w = n.f[2];
+    return (probSpecular * w) / (probSpecular * w + (1 - probSpecular) * (1 - w));
+}
+// MixtureBSDF tables in the float pool (include/mtscuda.h): N child indices, N weights, N + 1 CDF entries
+struct MixtureTab {
+    const float *p; int n;
+    DEVFN MixtureTab(const Mats S, const MtsBsdfNode &nd) : p(S.pool + nd.lut[0]), n(nd.lut[1]) {}
+    DEVFN int child(int i) const { return (int)__ldg(p + i); }
+    DEVFN float weight(int i) const { return __ldg(p + n + i); }
+    DEVFN float cdf(int i) const { return __ldg(p + 2 * n + i); }
+    DEVFN float pdf(int i) const { return cdf(i + 1) - cdf(i); }   // DiscreteDistribution::operator[], pmf.h
+    // DiscreteDistribution::sampleReuse (pmf.h:124-136, 164-169)
+    DEVFN int sampleReuse(float &u) const {
+        int lb = 0;                                   // std::lower_bound over the N + 1 CDF entries
+        while (lb < n + 1 && cdf(lb) < u) ++lb;
+        int index = min(n - 1, max(0, lb - 1));
+        while (pdf(index) == 0 && index < n) ++index;
+        u = (u - cdf(index)) / (cdf(index + 1) - cdf(index));
+        return index;
+    }
+};
 
 template <int D> struct Bsdf {
     typedef Bsdf<D + 1> Next;
@@ -888,6 +1051,38 @@ template <int D> struct Bsdf {
             float weight = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.tc))));
             return Next::eval(S, n.child[0], su, wi, wo, measure) * (1 - weight) + Next::eval(S, n.child[1], su, wi, wo, measure) * weight;
         }
+        case MTS_BSDF_MIXTURE: {  // mixturebsdf.cpp:174-189
+            const MixtureTab mt(S, n);
+            float3 result = f3(0.0f);
+            for (int i = 0; i < mt.n; ++i) result += Next::eval(S, mt.child(i), su, wi, wo, measure) * mt.weight(i);
+            return result;
+        }
+        case MTS_BSDF_ROUGHCOATING: {  // roughcoating.cpp:255-314
+            const float eta = n.eta[0], invEta = 1 / eta;
+            const bool hasNested = (S.nodes[n.child[0]].lobes & MTS_EALL) != 0, hasSpecular = measure == MTS_MEASURE_SOLID_ANGLE;
+            const float alpha = average(evalTex(S, n.t2, su.tc));
+            const Microfacet distr(n.flags & MTS_BF_GGX, alpha, alpha, n.flags & MTS_BF_SAMPLE_VISIBLE);
+            float3 result = f3(0.0f);
+            if (hasSpecular && cosTheta(wo) * cosTheta(wi) > 0) {
+                const float3 H = normalize(wo + wi) * signum(cosTheta(wo));
+                const float Dm = distr.eval(H);
+                const float F = fresnelDielectricExt(absDot(wi, H), eta);
+                const float G = distr.G(wi, wo, H);
+                const float value = F * Dm * G / (4.0f * fabsf(cosTheta(wi)));
+                result += evalTex(S, n.t1, su.tc) * value;
+            }
+            if (hasNested) {
+                const float3 wiI = roughCoatRefract(invEta, wi), woI = roughCoatRefract(invEta, wo);
+                float3 nested = Next::eval(S, n.child[0], su, wiI, woI, measure) *
+                    roughTransmittance(S, n, fabsf(cosTheta(wi)), distr.alphaU) * roughTransmittance(S, n, fabsf(cosTheta(wo)), distr.alphaU);
+                const float3 sigmaA = evalTex(S, n.t0, su.tc) * n.f[3];
+                if (!isZero(sigmaA)) nested *= vexp(-sigmaA * (1 / fabsf(cosTheta(wiI)) + 1 / fabsf(cosTheta(woI))));
+                if (measure == MTS_MEASURE_SOLID_ANGLE) nested *= invEta * invEta * cosTheta(wo) / cosTheta(woI);
+                result += nested;
+            }
+            return result;
+        }
+        case MTS_BSDF_NORMALMAP:  // normalmap.cpp:162-179 -- same adapter as bumpmap around another frame
         case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:161-177
             Frame bf = bumpFrameCached(S, node, n, su);
             Surf pert = su;
@@ -932,6 +1127,34 @@ template <int D> struct Bsdf {
             float weight = fminf(1.0f, fmaxf(0.0f, average(evalTex(S, n.t0, su.tc))));
             return Next::pdf(S, n.child[0], su, wi, wo, measure) * (1 - weight) + Next::pdf(S, n.child[1], su, wi, wo, measure) * weight;
         }
+        case MTS_BSDF_MIXTURE: {  // mixturebsdf.cpp:191-206
+            const MixtureTab mt(S, n);
+            float result = 0.0f;
+            for (int i = 0; i < mt.n; ++i) result += Next::pdf(S, mt.child(i), su, wi, wo, measure) * mt.pdf(i);
+            return result;
+        }
+        case MTS_BSDF_ROUGHCOATING: {  // roughcoating.cpp:316-376
+            const float eta = n.eta[0], invEta = 1 / eta;
+            const bool hasNested = (S.nodes[n.child[0]].lobes & MTS_EALL) != 0, hasSpecular = measure == MTS_MEASURE_SOLID_ANGLE;
+            const float3 H = normalize(wo + wi) * signum(cosTheta(wo));
+            const float alpha = average(evalTex(S, n.t2, su.tc));
+            const Microfacet distr(n.flags & MTS_BF_GGX, alpha, alpha, n.flags & MTS_BF_SAMPLE_VISIBLE);
+            float probNested = 1.0f, probSpecular = 1.0f;
+            if (hasSpecular && hasNested) { probSpecular = roughCoatProbSpecular(S, n, wi, distr.alphaU); probNested = 1 - probSpecular; }
+            float result = 0.0f;
+            if (hasSpecular && cosTheta(wo) * cosTheta(wi) > 0) {
+                const float dwh_dwo = 1.0f / (4.0f * absDot(wo, H));
+                result = distr.pdf(wi, H) * dwh_dwo * probSpecular;
+            }
+            if (hasNested) {
+                const float3 wiI = roughCoatRefract(invEta, wi), woI = roughCoatRefract(invEta, wo);
+                float prob = Next::pdf(S, n.child[0], su, wiI, woI, measure);
+                if (measure == MTS_MEASURE_SOLID_ANGLE) prob *= invEta * invEta * cosTheta(wo) / cosTheta(woI);
+                result += prob * probNested;
+            }
+            return result;
+        }
+        case MTS_BSDF_NORMALMAP:  // normalmap.cpp:181-197
         case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:179-197
             Frame bf = bumpFrameCached(S, node, n, su);
             Surf pert = su;
@@ -1001,6 +1224,49 @@ template <int D> struct Bsdf {
             result += Next::eval(S, n.child[1 - entry], su, wi, o.wo, measure) * wOther;
             return result / o.pdf;
         }
+        case MTS_BSDF_MIXTURE: {  // mixturebsdf.cpp:244-268 (the pdf-returning overload path.cpp:209 calls)
+            const MixtureTab mt(S, n);
+            const int entry = mt.sampleReuse(sample.x);
+            float3 result = Next::sample(S, mt.child(entry), su, wi, sample, o);
+            if (isZero(result)) return result;
+            result *= mt.weight(entry) * o.pdf;
+            o.pdf *= mt.pdf(entry);
+            const int measure = measureOf(o.type);
+            for (int i = 0; i < mt.n; ++i) {
+                if (i == entry) continue;
+                o.pdf += Next::pdf(S, mt.child(i), su, wi, o.wo, measure) * mt.pdf(i);
+                result += Next::eval(S, mt.child(i), su, wi, o.wo, measure) * mt.weight(i);
+            }
+            return result / o.pdf;
+        }
+        case MTS_BSDF_ROUGHCOATING: {  // roughcoating.cpp:378-448
+            const float eta = n.eta[0], invEta = 1 / eta;
+            const bool hasNested = (S.nodes[n.child[0]].lobes & MTS_EALL) != 0;
+            bool choseSpecular = true;
+            const float alpha = average(evalTex(S, n.t2, su.tc));
+            const Microfacet distr(n.flags & MTS_BF_GGX, alpha, alpha, n.flags & MTS_BF_SAMPLE_VISIBLE);
+            if (hasNested) {
+                const float probSpecular = roughCoatProbSpecular(S, n, wi, distr.alphaU);
+                if (sample.y < probSpecular) sample.y /= probSpecular;
+                else { sample.y = (sample.y - probSpecular) / (1 - probSpecular); choseSpecular = false; }
+            }
+            if (choseSpecular) {
+                float dummy;
+                const float3 m = distr.sampleVisible ? distr.sampleVisibleNormal(wi, sample) : distr.sampleAll(sample, dummy);
+                o.wo = reflectM(wi, m); o.type = MTS_EGLOSSY_REFLECTION; o.eta = 1.0f;
+                if (cosTheta(o.wo) * cosTheta(wi) <= 0) return f3(0.0f);
+            } else {
+                const float3 result = Next::sample(S, n.child[0], su, roughCoatRefract(invEta, wi), sample, o);
+                if (isZero(result)) return f3(0.0f);
+                o.wo = roughCoatRefract(eta, o.wo);
+                if (isZero(o.wo)) return f3(0.0f);
+            }
+            const int measure = measureOf(o.type);   // "guard against numerical imprecisions": pdf() and eval() / pdf
+            o.pdf = pdf(S, node, su, wi, o.wo, measure);
+            if (o.pdf == 0) return f3(0.0f);
+            return eval(S, node, su, wi, o.wo, measure) / o.pdf;
+        }
+        case MTS_BSDF_NORMALMAP:  // normalmap.cpp:218-239
         case MTS_BSDF_BUMPMAP: {  // bumpmap.cpp:221-240
             Frame bf = bumpFrameCached(S, node, n, su);
             Surf pert = su;
@@ -1089,25 +1355,30 @@ template <> struct Material<SHADE_LEAF> {
     const Mats S;
     const MtsBsdfNode *n;   // the leaf
     LeafTex lt;
-    Frame sh, pf;           // shading frame of the hit, perturbed frame of the bumpmap adapter
+    Frame sh, pf;           // shading frame of the hit, perturbed frame of the bumpmap / normalmap adapter
     float3 wiLeaf;          // incident direction as the leaf sees it
     bool bump, flipped;
-    DEVFN Material(const Mats S_, int root, const Surf &su, float3 wi) : S(S_), sh(su.sh), bump(false), flipped(false) {
+    DEVFN Material(const Mats S_, int root, const Surf &su, float3 wi, EwaDefer *defer = nullptr) : S(S_), sh(su.sh), bump(false), flipped(false) {
         const MtsBsdfNode *r = &S.nodes[root];
         if (r->type == MTS_BSDF_TWOSIDED) {   // twosided.cpp:107-180: the back side sees the mirrored configuration
             int child = r->child[0];
             if (!(cosTheta(wi) > 0)) { wi.z = -wi.z; flipped = true; child = r->child[1]; }
             r = &S.nodes[child];
         }
-        if (r->type == MTS_BSDF_BUMPMAP) {    // bumpmap.cpp:161-240: same directions expressed in the perturbed frame
+        if (r->type == MTS_BSDF_BUMPMAP || r->type == MTS_BSDF_NORMALMAP) {   // bumpmap.cpp:161-240, normalmap.cpp:162-239: same directions expressed in the perturbed frame
             bump = true;
-            pf = bumpFrame(S, *r, su);
+            pf = perturbedFrame(S, *r, su);
             wi = pf.toLocal(sh.toWorld(wi));
             r = &S.nodes[r->child[0]];
         }
         n = r; wiLeaf = wi;
-        lt = resolveLeaf(S, *n, su.tc);
+        lt = resolveLeaf(S, *n, su.tc, defer);
     }
+    // the staged shade kernels resolve a hit once (constructor above, k_surface) and rebuild the material from the stored
+    // surface record in the scatter kernel
+    DEVFN Material(const Mats S_, int leaf, const LeafTex &lt_, const Frame &sh_, const Frame &pf_, float3 wiLeaf_, bool bump_, bool flipped_)
+        : S(S_), n(&S_.nodes[leaf]), lt(lt_), sh(sh_), pf(pf_), wiLeaf(wiLeaf_), bump(bump_), flipped(flipped_) {}
+    DEVFN int leafIndex() const { return (int)(n - S.nodes); }
     DEVFN float3 evalPdf(float3, float3 wo, int measure, int, float &pdf) const {
         if (flipped) wo.z = -wo.z;
         float3 woL = wo;
@@ -1147,10 +1418,14 @@ template <> struct Material<SHADE_LAMBERT> {   // src/bsdfs/diffuse.cpp:110-150,
     }
 };
 
+inline bool isWrapperBsdf(int t) {
+    return t == MTS_BSDF_COATING || t == MTS_BSDF_BLEND || t == MTS_BSDF_BUMPMAP || t == MTS_BSDF_TWOSIDED || t == MTS_BSDF_MASK ||
+           t == MTS_BSDF_MIXTURE || t == MTS_BSDF_ROUGHCOATING || t == MTS_BSDF_NORMALMAP;
+}
 // Classification of a root BSDF (host side: mtscuda_build; also used by the per-function test entry points)
 inline int shadeClassOf(const MtsBsdfNode *nodes, int root) {
-    auto isLeaf = [&](int i) { const int t = nodes[i].type; return t != MTS_BSDF_COATING && t != MTS_BSDF_BLEND && t != MTS_BSDF_BUMPMAP && t != MTS_BSDF_TWOSIDED && t != MTS_BSDF_MASK; };
-    auto leafOrBump = [&](int i) { return isLeaf(i) || (nodes[i].type == MTS_BSDF_BUMPMAP && isLeaf(nodes[i].child[0])); };
+    auto isLeaf = [&](int i) { return !isWrapperBsdf(nodes[i].type); };
+    auto leafOrBump = [&](int i) { return isLeaf(i) || ((nodes[i].type == MTS_BSDF_BUMPMAP || nodes[i].type == MTS_BSDF_NORMALMAP) && isLeaf(nodes[i].child[0])); };
     if (nodes[root].type == MTS_BSDF_DIFFUSE) return SHADE_LAMBERT;
     if (leafOrBump(root)) return SHADE_LEAF;
     if (nodes[root].type == MTS_BSDF_TWOSIDED && leafOrBump(nodes[root].child[0]) && leafOrBump(nodes[root].child[1])) return SHADE_LEAF;

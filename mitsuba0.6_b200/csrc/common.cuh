@@ -13,6 +13,19 @@
 #include "../../include/mtscuda.h"
 
 #define DEVFN __device__ __forceinline__
+// Mid-size helpers that one path calls several times (microfacet terms, Fresnel terms, rough-transmittance lookups, texture
+// lookups): kept out of line so that a kernel holds ONE copy instead of one per call site -- the shade kernels are bound by
+// instruction fetch, not by call overhead.  -DMTS_OUTLINE=0 restores full inlining for A/B runs.
+#ifndef MTS_OUTLINE
+#define MTS_OUTLINE 1
+#endif
+#if MTS_OUTLINE
+#define DEVOL static __device__ __noinline__
+#define DEVOLM __device__ __noinline__
+#else
+#define DEVOL __device__ __forceinline__
+#define DEVOLM __device__ __forceinline__
+#endif
 #define HDFN __host__ __device__ __forceinline__
 
 namespace mts {
@@ -194,7 +207,7 @@ DEVFN Frame shadingFrame(float3 n, float3 dpdu) {
 }
 
 // src/libcore/util.cpp:651-681
-DEVFN float fresnelDielectricExt(float cosThetaI_, float &cosThetaT_, float eta) {
+DEVOL float fresnelDielectricExt(float cosThetaI_, float &cosThetaT_, float eta) {
     if (eta == 1) { cosThetaT_ = -cosThetaI_; return 0.0f; }
     float scale = (cosThetaI_ > 0) ? 1 / eta : eta,
           cosThetaTSqr = 1 - (1 - cosThetaI_ * cosThetaI_) * (scale * scale);
@@ -209,7 +222,7 @@ DEVFN float fresnelDielectricExt(float cosThetaI_, float &cosThetaT_, float eta)
 DEVFN float fresnelDielectricExt(float cosThetaI, float eta) { float t; return fresnelDielectricExt(cosThetaI, t, eta); }
 
 // src/libcore/util.cpp:739-761
-DEVFN float3 fresnelConductorExact(float cosThetaI, float3 eta, float3 k) {
+DEVOL float3 fresnelConductorExact(float cosThetaI, float3 eta, float3 k) {
     float cosThetaI2 = cosThetaI * cosThetaI, sinThetaI2 = 1 - cosThetaI2, sinThetaI4 = sinThetaI2 * sinThetaI2;
     float3 temp1 = eta * eta - k * k - f3(sinThetaI2),
            a2pb2 = vsafe_sqrt(temp1 * temp1 + k * k * eta * eta * 4.0f),

@@ -107,6 +107,8 @@ struct MtsContext {
     int device = 0;
     cudaStream_t stream = nullptr, ownStream = nullptr;
     int numSMs = 148;
+    bool deferEwa = true;      // staged shade: EWA texture walks as a kernel of their own (MTS_EWA_INLINE=1: inside k_shade_surface)
+    bool stagedShade = true;   // leaf class as k_shade_surface + k_shade_scatter (MTS_SHADE_FUSED=1 in the environment: one k_shade<SHADE_LEAF>)
     size_t l2Bytes = 0, l2WindowBytes = 0, maxWindow = 0; float l2HitRatio = 0;   // persisting-L2 set-up (0 = off)
     // staged scene
     MtsCamera cam; bool hasCam = false;
@@ -165,18 +167,31 @@ template <class T> int devUpload(MtsContext *c, const T *host, size_t n, const T
     return MTS_OK;
 }
 
-int bsdfDepth(const std::vector<MtsBsdfNode> &nodes, int i, int guard = 0) {
+// Wrapper levels above the deepest leaf below node i; >= 1000 for malformed trees (bad child index, cycle, bad mixture table).
+int bsdfDepth(const std::vector<MtsBsdfNode> &nodes, const std::vector<float> &pool, int i, int guard = 0) {
     if (i < 0 || i >= (int)nodes.size() || guard > 64) return 1000;
     const MtsBsdfNode &n = nodes[i];
-    if (n.type == MTS_BSDF_COATING || n.type == MTS_BSDF_BUMPMAP || n.type == MTS_BSDF_MASK) return 1 + bsdfDepth(nodes, n.child[0], guard + 1);
-    if (n.type == MTS_BSDF_BLEND || n.type == MTS_BSDF_TWOSIDED) return 1 + std::max(bsdfDepth(nodes, n.child[0], guard + 1), bsdfDepth(nodes, n.child[1], guard + 1));
+    if (n.type == MTS_BSDF_COATING || n.type == MTS_BSDF_BUMPMAP || n.type == MTS_BSDF_MASK || n.type == MTS_BSDF_ROUGHCOATING || n.type == MTS_BSDF_NORMALMAP)
+        return 1 + bsdfDepth(nodes, pool, n.child[0], guard + 1);
+    if (n.type == MTS_BSDF_BLEND || n.type == MTS_BSDF_TWOSIDED)
+        return 1 + std::max(bsdfDepth(nodes, pool, n.child[0], guard + 1), bsdfDepth(nodes, pool, n.child[1], guard + 1));
+    if (n.type == MTS_BSDF_MIXTURE) {
+        const int cnt = n.lut[1], off = n.lut[0];
+        if (cnt < 1 || cnt > MTS_MIXTURE_MAX || off < 0 || (size_t)off + 3 * (size_t)cnt + 1 > pool.size()) return 1000;
+        int d = 0;
+        for (int k = 0; k < cnt; ++k) d = std::max(d, bsdfDepth(nodes, pool, (int)pool[off + k], guard + 1));
+        return 1 + d;
+    }
     return 0;
 }
+
+const char *kDepthError = "BSDF nesting deeper than 4 wrapper levels (coating/blendbsdf/bumpmap/twosided/mask/mixturebsdf/roughcoating/normalmap) is not supported";
 
 int ensureWavefront(MtsContext *c, uint32_t cap) {
     const uint32_t numKeys = c->numKeys;
     for (int k = 0; k <= SHADE_CLASSES; ++k) c->wf.classKey[k] = c->classKey[k];
-    if (c->wfCapacity >= cap && c->wf.numKeys == numKeys) return MTS_OK;
+    const bool needRec = c->stagedShade && c->classKey[SHADE_LEAF] < c->classKey[SHADE_LEAF + 1];
+    if (c->wfCapacity >= cap && c->wf.numKeys == numKeys && needRec == (c->wf.rec != nullptr) && (needRec && c->deferEwa) == (c->wf.ewaJobs != nullptr)) return MTS_OK;
     c->freeWavefront();
     Wavefront &w = c->wf;
     auto alloc = [&](void **p, size_t bytes) -> cudaError_t {
@@ -189,6 +204,14 @@ int ensureWavefront(MtsContext *c, uint32_t cap) {
     CUDA_TRY(alloc((void **)&w.L, sizeof(float4) * cap)); CUDA_TRY(alloc((void **)&w.meta, sizeof(uint4) * cap));
     CUDA_TRY(alloc((void **)&w.shO, sizeof(float4) * cap)); CUDA_TRY(alloc((void **)&w.shD, sizeof(float4) * cap));
     CUDA_TRY(alloc((void **)&w.shC, sizeof(float4) * cap));
+    w.rec = nullptr;
+    if (needRec)   // surface records of k_shade_surface -> k_shade_scatter
+        CUDA_TRY(alloc((void **)&w.rec, sizeof(float4) * (size_t)kSurfRows * cap));
+    w.ewaJobs = nullptr; w.ewaC = nullptr;
+    if (needRec && c->deferEwa) {
+        CUDA_TRY(alloc((void **)&w.ewaJobs, sizeof(float4) * 2 * (size_t)cap));
+        CUDA_TRY(alloc((void **)&w.ewaC, sizeof(float) * (size_t)cap));
+    }
     CUDA_TRY(alloc((void **)&w.queue[0], 4 * (size_t)cap)); CUDA_TRY(alloc((void **)&w.queue[1], 4 * (size_t)cap));
     CUDA_TRY(alloc((void **)&w.doneQ, 4 * (size_t)cap));
     CUDA_TRY(alloc((void **)&w.keys, 4 * (size_t)cap)); CUDA_TRY(alloc((void **)&w.sorted, 4 * (size_t)cap));
@@ -695,11 +718,14 @@ MTS_API int mtscuda_set_float_pool(MtsContext *c, const float *data, int64_t n) 
 
 MTS_API int mtscuda_set_bsdfs(MtsContext *c, const MtsBsdfNode *nodes, int32_t n) {
     c->nodes.assign(nodes, nodes + n); c->built = false;
+    bool hasMixture = false;
     for (int i = 0; i < n; ++i) {
-        if (nodes[i].type < MTS_BSDF_DIFFUSE || nodes[i].type > MTS_BSDF_ROUGHDIELECTRIC) return fail(MTS_EINVAL, "unknown BSDF type");
-        if (bsdfDepth(c->nodes, i) > kMaxBsdfDepth)
-            return fail(MTS_EINVAL, "BSDF nesting deeper than 4 wrapper levels (coating/blendbsdf/bumpmap/twosided/mask) is not supported");
+        if (nodes[i].type < MTS_BSDF_DIFFUSE || nodes[i].type > MTS_BSDF_NORMALMAP) return fail(MTS_EINVAL, "unknown BSDF type");
+        hasMixture |= nodes[i].type == MTS_BSDF_MIXTURE;
     }
+    // mixturebsdf keeps its child list in the float pool, which may arrive later: such node sets are checked by build()
+    for (int i = 0; i < n && !hasMixture; ++i)
+        if (bsdfDepth(c->nodes, c->pool, i) > kMaxBsdfDepth) return fail(MTS_EINVAL, kDepthError);
     return MTS_OK;
 }
 
@@ -794,6 +820,11 @@ static int buildOne(MtsContext *c) {
         return fail(MTS_EINVAL, "scene has no emitters (the reference would add a sunsky emitter, which is out of scope)");
     if (c->nodes.empty()) return fail(MTS_EINVAL, "no BSDFs set");
     for (auto &s : c->shapes) if (s.d.bsdf < 0 || s.d.bsdf >= (int)c->nodes.size()) return fail(MTS_EINVAL, "shape references a bad BSDF index");
+    for (int i = 0; i < (int)c->nodes.size(); ++i) {
+        const int d = bsdfDepth(c->nodes, c->pool, i);
+        if (d >= 1000) return fail(MTS_EINVAL, "malformed BSDF tree (bad child index, cycle or mixturebsdf table)");
+        if (d > kMaxBsdfDepth) return fail(MTS_EINVAL, kDepthError);
+    }
     for (auto &n : c->nodes) {
         const MtsTexRef *tr[3] = {&n.t0, &n.t1, &n.t2};
         for (auto t : tr) if (t->tex >= (int)c->textures.size()) return fail(MTS_EINVAL, "BSDF references a bad texture index");
@@ -1029,6 +1060,8 @@ static int renderOne(MtsContext *c, const MtsRenderParams *P, volatile const int
     cap = (uint32_t)std::min<unsigned long long>(std::max<unsigned long long>(totalItems, 32), cap);
     cap = (cap + 31u) & ~31u;
     int rc;
+    c->stagedShade = getenv("MTS_SHADE_FUSED") == nullptr;
+    c->deferEwa = getenv("MTS_EWA_INLINE") == nullptr;
     if ((rc = ensureWavefront(c, cap))) return rc;
     const Wavefront &Wf = c->wf;
     if (P->clear_film) CUDA_TRY(cudaMemsetAsync(S.film, 0, sizeof(float4) * (size_t)W * H, st));
@@ -1106,7 +1139,15 @@ static int renderOne(MtsContext *c, const MtsRenderParams *P, volatile const int
             begin(2);
             // one instance per shade class that has BSDFs in this scene (each walks its own range of the sorted queue)
             if (Wf.classKey[SHADE_LAMBERT] < Wf.classKey[SHADE_LAMBERT + 1]) { launchShade<SHADE_LAMBERT>(S, Wf, R, cur, c->numSMs, st); ++launches; }
-            if (Wf.classKey[SHADE_LEAF] < Wf.classKey[SHADE_LEAF + 1]) { launchShade<SHADE_LEAF>(S, Wf, R, cur, c->numSMs, st); ++launches; }
+            if (Wf.classKey[SHADE_LEAF] < Wf.classKey[SHADE_LEAF + 1]) {
+                if (Wf.rec) {
+                    launchSurface(S, Wf, R, cur, c->numSMs, st);
+                    if (Wf.ewaJobs && bounce == 0) { launchEwa(S, Wf, c->numSMs, st); ++launches; }   // only camera rays carry differentials (path.cpp:225)
+                    launchScatter(S, Wf, R, cur, c->numSMs, st);
+                    launches += 2;
+                }
+                else { launchShade<SHADE_LEAF>(S, Wf, R, cur, c->numSMs, st); ++launches; }
+            }
             if (Wf.classKey[SHADE_GENERIC] < Wf.classKey[SHADE_GENERIC + 1]) { launchShade<SHADE_GENERIC>(S, Wf, R, cur, c->numSMs, st); ++launches; }
             end();
             begin(3);

@@ -1,5 +1,6 @@
 // shade_inst.cu -- one shade class per translation unit (see shade_launch.h):
-//   nvcc -DSHADE_CLASS={0,1,2} -DSHADE_PART={0,1}   part 0 = k_shade<CLASS>, part 1 = the BSDF test entry points
+//   nvcc -DSHADE_CLASS={0,1,2} -DSHADE_PART={0,1}   part 0 = k_shade<CLASS>, part 1 = the BSDF test entry points;
+//   class 1 (leaf) also has part 2 = k_shade_surface and part 3 = k_shade_scatter, the staged form of its k_shade
 #include <algorithm>
 #include "shade_launch.h"
 
@@ -13,6 +14,24 @@ namespace mts {
 
 template <> void launchShade<SHADE_CLASS>(const DScene &S, const Wavefront &W, const RenderConst &R, int qsel, int numSMs, cudaStream_t st) {
     k_shade<SHADE_CLASS><<<numSMs * ShadeLaunch<SHADE_CLASS>::kMinBlocks, ShadeLaunch<SHADE_CLASS>::kThreads, 0, st>>>(S, W, R, qsel);
+}
+
+#elif SHADE_PART == 2
+
+void launchSurface(const DScene &S, const Wavefront &W, const RenderConst &R, int qsel, int numSMs, cudaStream_t st) {
+    k_shade_surface<SHADE_CLASS><<<numSMs * SURFACE_MINB, 128, 0, st>>>(S, W, R, qsel);
+}
+
+#elif SHADE_PART == 4
+
+void launchEwa(const DScene &S, const Wavefront &W, int numSMs, cudaStream_t st) {
+    k_shade_ewa<SHADE_CLASS><<<numSMs * 8, 256, 0, st>>>(S, W);
+}
+
+#elif SHADE_PART == 3
+
+void launchScatter(const DScene &S, const Wavefront &W, const RenderConst &R, int qsel, int numSMs, cudaStream_t st) {
+    k_shade_scatter<SHADE_CLASS><<<numSMs * SCATTER_MINB, 128, 0, st>>>(S, W, R, qsel);
 }
 
 #else

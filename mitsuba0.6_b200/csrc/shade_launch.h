@@ -10,6 +10,10 @@ namespace mts {
 
 // k_shade<CLASS> over the class's range of the sorted queue (persistent grid sized from the SM count)
 template <int CLASS> void launchShade(const DScene &S, const Wavefront &W, const RenderConst &R, int qsel, int numSMs, cudaStream_t st);
+// the staged form of the leaf class: k_shade_surface (part 2) then k_shade_scatter (part 3), each its own translation unit
+void launchSurface(const DScene &S, const Wavefront &W, const RenderConst &R, int qsel, int numSMs, cudaStream_t st);
+void launchEwa(const DScene &S, const Wavefront &W, int numSMs, cudaStream_t st);
+void launchScatter(const DScene &S, const Wavefront &W, const RenderConst &R, int qsel, int numSMs, cudaStream_t st);
 // mtscuda_bsdf_eval_pdf / mtscuda_bsdf_sample through Material<CLASS> (all pointers are device pointers)
 template <int CLASS> void launchBsdfEvalPdf(const DScene &S, int bsdf, int64_t n, const float *surf, const float *wi, const float *wo,
                                             int measure, float *outV, float *outP, cudaStream_t st);

@@ -17,6 +17,7 @@ struct Counters {
     uint32_t qCount[2];     // active queue sizes (ping-pong)
     uint32_t shadowCount;
     uint32_t doneCount;
+    uint32_t ewaCount;      // deferred EWA texture walks of the current bounce (k_shade_surface -> k_shade_ewa)
     uint32_t cursor[2];     // next unclaimed ray of the intersect / shadow queue (persistent warps pull from these)
     unsigned long long missRays;                 // rays that escaped (sort key 0), total over all bounces
     unsigned long long normalRays, shadowRays;   // totals over all bounces ("Normal/Shadow rays traced", skdtree.cpp:46-47), kept on the device
@@ -32,6 +33,9 @@ struct Wavefront {
     float4 *L;               // radiance rgb, pdf of the BSDF sample that produced the current ray
     uint4 *meta;             // pixel index, global sample index, depth | flags << 16, unused
     float4 *shO, *shD, *shC; // shadow ray origin/dir (+mint/maxt), contribution rgb + path slot
+    float4 *rec;             // surface records of the staged shade kernels: kSurfRows rows of `capacity` float4, indexed by sorted-queue position
+    float4 *ewaJobs;         // deferred EWA walks: 2 rows of `capacity` float4 (target / textures / level / lerp weight; uv, A, B) ...
+    float *ewaC;             // ... and the ellipse coefficient C
     uint32_t *queue[2];
     uint32_t *doneQ;
     // material sort of the active queue: key 0 = miss, DShape::sortKey otherwise (root BSDFs ordered by shade class)
@@ -280,9 +284,21 @@ static __global__ void __launch_bounds__(256) k_sort_scatter(const Wavefront W, 
 // ---- shade: one iteration of the Li loop ----------------------------------------------------
 struct ShadeOut { bool next, shadow, done; float4 shO, shD, shC; };
 
-template <int CLASS>
-DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, uint32_t slot, ShadeOut &out) {
-    out.next = false; out.shadow = false; out.done = true;
+// What the second half of an iteration (light sampling, BSDF sampling) needs to know about the hit and the path.
+struct PathVertex {
+    float3 p, geoN, wi;
+    Frame sh;
+    float3 thr, L;
+    float eta;
+    uint32_t depth, flags, lobes;
+    uint4 meta;
+    uint32_t touched;   // what shadeVertex changed of the stored path state: 1 = L, 2 = throughput, 4 = flags (staged shade writes only these back)
+};
+
+// First half of an iteration: hit record, emission + MIS of the previous BSDF sample, Russian roulette, depth / normal
+// tests (path.cpp:145-165, 257-264, 276-286).  Returns false when the path ends here (its state has been finished).
+// On success `su` is the surface context of the hit (with the uv partials of a camera-ray hit) and `bsdf` its root BSDF.
+DEVFN bool shadeVertex(const DScene &S, const Wavefront &W, const RenderConst &R, uint32_t slot, PathVertex &v, Surf &su, int &bsdf) {
     float4 ro = W.rayO[slot], rd = W.rayD[slot], hv = W.hit[slot];
     float4 tv = W.thr[slot], lv = W.L[slot];
     uint4 meta = W.meta[slot];
@@ -292,7 +308,8 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
     uint32_t depth = meta.z & 0xffffu, flags = meta.z >> 16;
     const int prim = __float_as_int(hv.w);
     const bool first = depth == 1;
-    if (first) flags |= PF_CAMERA_HIT;
+    uint32_t touched = 0;
+    if (first) { flags |= PF_CAMERA_HIT; touched |= 4u; }
 
     auto finish = [&]() { W.L[slot] = make_float4(L.x, L.y, L.z, 0); W.meta[slot] = make_uint4(meta.x, meta.y, depth | (flags << 16), 0); };
 
@@ -304,6 +321,7 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
     if (shape.emitter >= 0) {
         const DEmitter &em = S.emitters[shape.emitter];
         float3 Le = areaLe(em, its.sh.n, -d);
+        touched |= 1u;
         if (first) {
             if (!R.hideEmitters) L += thr * Le;  // path.cpp:148-150
         } else {
@@ -320,18 +338,18 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
         if ((int)(depth - 1) >= R.rrDepth) {
             float q = fminf(maxc(thr) * eta * eta, 0.95f);
             float4 u = rand4(R.seed, meta.x, meta.y, 2 * depth - 2);
-            if (u.x >= q) { finish(); return; }
+            if (u.x >= q) { finish(); return false; }
             thr = thr / q;
+            touched |= 2u;
         }
     }
 
     // path.cpp:156-165
     if ((R.maxDepth > 0 && (int)depth >= R.maxDepth) ||
-        (R.strictNormals && dot(d, its.geoN) * cosTheta(its.wi) >= 0)) { finish(); return; }
+        (R.strictNormals && dot(d, its.geoN) * cosTheta(its.wi) >= 0)) { finish(); return false; }
 
-    const int bsdf = shape.bsdf;
-    const uint32_t lobes = S.nodes[bsdf].lobes;
-    Surf su = surfOf(its);
+    bsdf = shape.bsdf;
+    su = surfOf(its);
     if (first && (S.nodes[bsdf].flags & MTS_BF_RAY_DIFF)) {
         // Intersection::getBSDF(ray) (records.inl:69-75): only the camera ray carries differentials (path.cpp:225 drops them)
         const float4 us = rand4(R.seed, meta.x, meta.y, 0);
@@ -341,23 +359,39 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
         su.tc.duv = computePartials(its.p, its.geoN, its.dpdu, its.dpdv, co, rxD, ryD);
         su.tc.filtered = true;
     }
-    const Material<CLASS> mat(S, bsdf, su, its.wi);
+    v.p = its.p; v.geoN = its.geoN; v.wi = its.wi; v.sh = its.sh;
+    v.thr = thr; v.L = L; v.eta = eta; v.depth = depth; v.flags = flags; v.meta = meta;
+    v.lobes = S.nodes[bsdf].lobes;
+    v.touched = touched;
+    return true;
+}
+
+// Second half: direct illumination sampling (path.cpp:172-200) and BSDF sampling (path.cpp:203-253).
+template <class Mat>
+DEVFN void shadeScatter(const DScene &S, const Wavefront &W, const RenderConst &R, uint32_t slot, const PathVertex &v, const Mat &mat, ShadeOut &out) {
+    float3 thr = v.thr;
+    const float3 L = v.L;
+    float eta = v.eta;
+    uint32_t depth = v.depth, flags = v.flags;
+    const uint4 meta = v.meta;
+    const uint32_t lobes = v.lobes;
+    auto finish = [&]() { W.L[slot] = make_float4(L.x, L.y, L.z, 0); W.meta[slot] = make_uint4(meta.x, meta.y, depth | (flags << 16), 0); };
     float uExtra;
     float4 u = rand4x(R.seed, meta.x, meta.y, 2 * depth - 1, uExtra);
 
     // ---- direct illumination sampling (path.cpp:172-200) ----
-    float3 refN = ((lobes & (MTS_ETRANSMISSION | MTS_EBACKSIDE)) == 0) ? its.sh.n : f3(0.0f);  // records.inl:160-164
+    float3 refN = ((lobes & (MTS_ETRANSMISSION | MTS_EBACKSIDE)) == 0) ? v.sh.n : f3(0.0f);  // records.inl:160-164
     if (lobes & MTS_ESMOOTH) {
-        DRec dr; dr.ref = its.p; dr.refN = refN; dr.pdf = 0; dr.emitter = -1; dr.measure = 0; dr.dist = 0;
+        DRec dr; dr.ref = v.p; dr.refN = refN; dr.pdf = 0; dr.emitter = -1; dr.measure = 0; dr.dist = 0;
         dr.d = f3(0.0f); dr.n = f3(0.0f); dr.p = f3(0.0f);
         float3 value = sampleEmitterDirect(S, dr, make_float2(u.x, u.y));
         if (!isZero(value)) {
-            float3 wo = its.sh.toLocal(dr.d);
+            float3 wo = v.sh.toLocal(dr.d);
             // area and environment emitters are "on surface"; the point emitter is not
             const bool wantPdf = S.emitters[dr.emitter].type != MTS_EMITTER_POINT && dr.measure == MTS_MEASURE_SOLID_ANGLE;
             float bsdfPdf;
-            float3 bsdfVal = mat.evalPdf(its.wi, wo, MTS_MEASURE_SOLID_ANGLE, wantPdf ? PDF_IF_LIT : PDF_NONE, bsdfPdf);
-            if (!isZero(bsdfVal) && (!R.strictNormals || dot(its.geoN, dr.d) * cosTheta(wo) > 0)) {
+            float3 bsdfVal = mat.evalPdf(v.wi, wo, MTS_MEASURE_SOLID_ANGLE, wantPdf ? PDF_IF_LIT : PDF_NONE, bsdfPdf);
+            if (!isZero(bsdfVal) && (!R.strictNormals || dot(v.geoN, dr.d) * cosTheta(wo) > 0)) {
                 if (!wantPdf) bsdfPdf = 0.0f;
                 float3 c = thr * value * bsdfVal * miWeight(dr.pdf, bsdfPdf);
                 out.shadow = true;
@@ -371,11 +405,11 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
     // ---- BSDF sampling (path.cpp:203-253) ----
     BSample bs; bs.pdf = 0; bs.eta = 1; bs.type = 0; bs.wo = f3(0.0f);
     bs.u3 = uExtra;   // EUsesSampler models (roughdielectric.cpp:405 bRec.sampler->next1D()): spare bits of the same Philox draw
-    float3 bsdfWeight = mat.sample(its.wi, make_float2(u.z, u.w), bs);
+    float3 bsdfWeight = mat.sample(v.wi, make_float2(u.z, u.w), bs);
     if (isZero(bsdfWeight)) { finish(); return; }
     if (bs.type != MTS_ENULL) flags |= PF_SCATTERED;   // path.cpp:213
-    const float3 wo = its.sh.toWorld(bs.wo);
-    if (R.strictNormals && dot(its.geoN, wo) * cosTheta(bs.wo) <= 0) { finish(); return; }
+    const float3 wo = v.sh.toWorld(bs.wo);
+    if (R.strictNormals && dot(v.geoN, wo) * cosTheta(bs.wo) <= 0) { finish(); return; }
 
     thr *= bsdfWeight;
     eta *= bs.eta;
@@ -384,12 +418,21 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
     if (dot(wo, refN) >= 0) flags |= PF_PREV_REFN_OK;
     depth += 1;
 
-    W.rayO[slot] = make_float4(its.p.x, its.p.y, its.p.z, kEps);
+    W.rayO[slot] = make_float4(v.p.x, v.p.y, v.p.z, kEps);
     W.rayD[slot] = make_float4(wo.x, wo.y, wo.z, kInf);
     W.thr[slot] = make_float4(thr.x, thr.y, thr.z, eta);
     W.L[slot] = make_float4(L.x, L.y, L.z, bs.pdf);
     W.meta[slot] = make_uint4(meta.x, meta.y, depth | (flags << 16), 0);
     out.next = true; out.done = false;
+}
+
+template <int CLASS>
+DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, uint32_t slot, ShadeOut &out) {
+    out.next = false; out.shadow = false; out.done = true;
+    PathVertex v; Surf su; int bsdf;
+    if (!shadeVertex(S, W, R, slot, v, su, bsdf)) return;
+    const Material<CLASS> mat(S, bsdf, su, v.wi);
+    shadeScatter(S, W, R, slot, v, mat, out);
 }
 
 // Escaped rays (sort key 0) are shaded by their own small kernel: no hit record, no BSDF code, 40 registers, full
@@ -473,6 +516,174 @@ k_shade(const DScene S, const Wavefront W, const RenderConst R, int qsel) {
     }
 }
 
+// ---- staged shade of the leaf class -------------------------------------------------------------------------------
+// k_shade<SHADE_LEAF> as one kernel is half a megabyte of machine code (hit record, ray differentials, MIP / EWA texture
+// filtering, bump frames, emitter sampling, nine BSDF models): the warps of an SM sit at different places of a program far
+// larger than the instruction caches and stall on instruction fetch (profiles/r2b: stall_no_instruction 14 cycles per
+// issue at the camera-ray bounce).  The staged form runs the iteration as two kernels over the same range of the sorted
+// queue, handing over one "surface record" per queue position (coalesced float4 rows, kSurfRows x capacity):
+//   k_shade_surface  hit record, emission + MIS, Russian roulette, depth tests, uv partials, textures and perturbed frame;
+//                    EWA texture walks of camera-ray hits are queued, not done
+//   k_shade_ewa      the queued EWA walks, one thread pair per lookup (camera-ray bounce only)
+//   k_shade_scatter  emitter sampling + BSDF eval/pdf (shadow ray), BSDF sampling (next ray)
+// Same arithmetic on the same fp32 values as the fused kernel.
+constexpr int kSurfRows = 10;
+#ifndef SURFACE_MINB
+#define SURFACE_MINB 4
+#endif
+#ifndef SCATTER_MINB
+#define SCATTER_MINB 4
+#endif
+enum { SR_BUMP = 1u << 24, SR_FLIPPED = 1u << 25, SR_ALIVE = 1u << 26, SR_NFLIP = 1u << 27,
+       SR_SMOOTH = 1u << 28,    // the root BSDF has smooth lobes (light sampling applies, path.cpp:172)
+       SR_ONESIDED = 1u << 29,  // no transmission / back-side lobes: refN = shading normal (records.inl:160-164)
+       SR_NODE_MASK = 0xffffffu };
+
+template <int CLASS>
+static __global__ void __launch_bounds__(128, SURFACE_MINB) k_shade_surface(const DScene S, const Wavefront W, const RenderConst R, int qsel) {
+    const uint32_t count = W.ctr->qCount[qsel];
+    const uint32_t first = sortedBegin(W, W.classKey[SHADE_LEAF], count), last = sortedBegin(W, W.classKey[SHADE_LEAF + 1], count);
+    const uint32_t rounded = first + ((last - first + 31u) & ~31u);
+    const size_t cap = W.capacity;
+    for (uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
+        bool done = false;
+        uint32_t slot = 0;
+        if (i < last) {
+            slot = W.sorted[i];
+            PathVertex v; Surf su; int bsdf;
+            if (!shadeVertex(S, W, R, slot, v, su, bsdf)) {
+                done = true;
+                W.rec[i] = make_float4(0, 0, 0, __uint_as_float(0u));
+            } else {
+                EwaDefer ewa; ewa.pending = false;
+                const Material<SHADE_LEAF> mat(S, bsdf, su, v.wi, W.ewaJobs ? &ewa : nullptr);
+                if (ewa.pending) {   // the walk runs in k_shade_ewa, which fills c0 / c1 of this record
+                    const uint32_t j = atomicAdd(&W.ctr->ewaCount, 1u);
+                    W.ewaJobs[j] = make_float4(__uint_as_float(i), __uint_as_float((uint32_t)ewa.texA | ((uint32_t)(ewa.texB & 0xffff) << 16)),
+                                               __uint_as_float((uint32_t)ewa.ilevel | ((uint32_t)ewa.slotA << 8)), ewa.a);
+                    W.ewaJobs[cap + j] = make_float4(ewa.uv.x, ewa.uv.y, ewa.A, ewa.B);
+                    W.ewaC[j] = ewa.C;
+                }
+                uint32_t info = (uint32_t)mat.leafIndex() | SR_ALIVE | (mat.bump ? SR_BUMP : 0u) | (mat.flipped ? SR_FLIPPED : 0u);
+                if (v.lobes & MTS_ESMOOTH) info |= SR_SMOOTH;
+                if ((v.lobes & (MTS_ETRANSMISSION | MTS_EBACKSIDE)) == 0) info |= SR_ONESIDED;
+                if (mat.bump && dot(cross(mat.pf.n, mat.pf.s), mat.pf.t) < 0) info |= SR_NFLIP;   // bumpmap.cpp:156-157 flips n after t was built
+                float4 *r = W.rec + i;
+                r[0] = make_float4(v.p.x, v.p.y, v.p.z, __uint_as_float(info));
+                r[cap] = make_float4(v.sh.n.x, v.sh.n.y, v.sh.n.z, v.geoN.x);
+                r[2 * cap] = make_float4(v.sh.s.x, v.sh.s.y, v.sh.s.z, v.geoN.y);
+                r[3 * cap] = make_float4(v.wi.x, v.wi.y, v.wi.z, v.geoN.z);
+                r[4 * cap] = make_float4(mat.lt.c0.x, mat.lt.c0.y, mat.lt.c0.z, mat.wiLeaf.x);
+                r[5 * cap] = make_float4(mat.lt.c1.x, mat.lt.c1.y, mat.lt.c1.z, mat.wiLeaf.y);
+                r[6 * cap] = make_float4(mat.lt.c2.x, mat.lt.c2.y, mat.lt.c2.z, mat.wiLeaf.z);
+                if (mat.bump) {
+                    r[7 * cap] = make_float4(mat.pf.n.x, mat.pf.n.y, mat.pf.n.z, 0);
+                    r[8 * cap] = make_float4(mat.pf.s.x, mat.pf.s.y, mat.pf.s.z, 0);
+                }
+                if (mat.n->type == MTS_BSDF_ROUGHDIELECTRIC) r[9 * cap] = make_float4(mat.lt.c3.x, mat.lt.c3.y, mat.lt.c3.z, 0);
+                // path state the first half changed (the scatter kernel reads it back by slot)
+                if (v.touched & 1u) W.L[slot] = make_float4(v.L.x, v.L.y, v.L.z, 0);
+                if (v.touched & 2u) W.thr[slot] = make_float4(v.thr.x, v.thr.y, v.thr.z, v.eta);
+                if (v.touched & 4u) W.meta[slot] = make_uint4(v.meta.x, v.meta.y, v.depth | (v.flags << 16), 0);
+            }
+        }
+        uint32_t c = warpAppend(&W.ctr->doneCount, done);
+        if (done) W.doneQ[c] = slot;
+    }
+}
+
+// The deferred EWA walks: one thread pair per lookup (even lane: pyramid level ilevel, odd lane: ilevel + 1), results
+// combined as evalEWA(ilevel) * (1 - a) + evalEWA(ilevel + 1) * a (mipmap.h:712-713), scaled (ScalingTexture) and stored
+// into the c0 / c1 rows of the surface record.
+template <int CLASS>
+static __global__ void __launch_bounds__(256) k_shade_ewa(const DScene S, const Wavefront W) {
+    const uint32_t count = W.ctr->ewaCount;
+    const size_t cap = W.capacity;
+    const uint32_t rounded = (2u * count + 31u) & ~31u;
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < rounded; t += gridDim.x * blockDim.x) {
+        const uint32_t j = t >> 1, lvl = t & 1u;
+        const bool valid = j < count;
+        float3 va = f3(0.0f), vb = f3(0.0f);
+        float4 j0 = make_float4(0, 0, 0, 0);
+        if (valid) {
+            j0 = W.ewaJobs[j];
+            const float4 j1 = W.ewaJobs[cap + j];
+            const float C = W.ewaC[j];
+            const uint32_t tex = __float_as_uint(j0.y), li = __float_as_uint(j0.z);
+            const int texA = (int)(tex & 0xffffu), texB = (int)(tex >> 16), level = (int)(li & 0xffu) + (int)lvl;
+            if (texB != 0xffff) ewaWalk<true>(S.textures[texA], &S.textures[texB], level, make_float2(j1.x, j1.y), j1.z, j1.w, C, va, vb);
+            else ewaWalk<false>(S.textures[texA], nullptr, level, make_float2(j1.x, j1.y), j1.z, j1.w, C, va, vb);
+        }
+        // the odd lane hands its level to the even lane
+        const float3 oa = f3(__shfl_down_sync(0xffffffffu, va.x, 1), __shfl_down_sync(0xffffffffu, va.y, 1), __shfl_down_sync(0xffffffffu, va.z, 1));
+        const float3 ob = f3(__shfl_down_sync(0xffffffffu, vb.x, 1), __shfl_down_sync(0xffffffffu, vb.y, 1), __shfl_down_sync(0xffffffffu, vb.z, 1));
+        if (valid && lvl == 0) {
+            const float a = j0.w;
+            const uint32_t pos = __float_as_uint(j0.x), tex = __float_as_uint(j0.y), slotA = (__float_as_uint(j0.z) >> 8) & 1u;
+            float4 *r = W.rec + pos;
+            const MtsBsdfNode &n = S.nodes[__float_as_uint(r[0].w) & SR_NODE_MASK];
+            const MtsTexRef &ra = slotA ? n.t1 : n.t0;
+            const float3 ca = (va * (1.0f - a) + oa * a) * f3(ra.scale[0], ra.scale[1], ra.scale[2]);
+            float4 *rowA = r + (4 + slotA) * cap;
+            float4 cur = *rowA;
+            *rowA = make_float4(ca.x, ca.y, ca.z, cur.w);
+            if ((tex >> 16) != 0xffffu) {
+                const float3 cb = (vb * (1.0f - a) + ob * a) * f3(n.t1.scale[0], n.t1.scale[1], n.t1.scale[2]);
+                float4 *rowB = r + 5 * cap;
+                cur = *rowB;
+                *rowB = make_float4(cb.x, cb.y, cb.z, cur.w);
+            }
+        }
+    }
+}
+
+template <int CLASS>
+static __global__ void __launch_bounds__(128, SCATTER_MINB) k_shade_scatter(const DScene S, const Wavefront W, const RenderConst R, int qsel) {
+    const uint32_t count = W.ctr->qCount[qsel];
+    const uint32_t first = sortedBegin(W, W.classKey[SHADE_LEAF], count), last = sortedBegin(W, W.classKey[SHADE_LEAF + 1], count);
+    const uint32_t rounded = first + ((last - first + 31u) & ~31u);
+    const size_t cap = W.capacity;
+    for (uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
+        ShadeOut out; out.next = out.shadow = out.done = false;
+        uint32_t slot = 0;
+        if (i < last) {
+            const float4 *r = W.rec + i;
+            const float4 r0 = r[0];
+            const uint32_t info = __float_as_uint(r0.w);
+            if (info & SR_ALIVE) {
+                slot = W.sorted[i];
+                const float4 r1 = r[cap], r2 = r[2 * cap], r3 = r[3 * cap], r4 = r[4 * cap], r5 = r[5 * cap], r6 = r[6 * cap];
+                const float4 tv = W.thr[slot], lv = W.L[slot];
+                const uint4 meta = W.meta[slot];
+                PathVertex v;
+                v.p = f3(r0); v.geoN = f3(r1.w, r2.w, r3.w); v.wi = f3(r3);
+                v.sh.n = f3(r1); v.sh.s = f3(r2); v.sh.t = cross(v.sh.n, v.sh.s);
+                v.thr = f3(tv); v.eta = tv.w; v.L = f3(lv);
+                v.depth = meta.z & 0xffffu; v.flags = meta.z >> 16; v.meta = meta;
+                const int leaf = (int)(info & SR_NODE_MASK);
+                LeafTex lt; lt.c0 = f3(r4); lt.c1 = f3(r5); lt.c2 = f3(r6); lt.c3 = f3(0.0f);
+                if (S.nodes[leaf].type == MTS_BSDF_ROUGHDIELECTRIC) lt.c3 = f3(r[9 * cap]);
+                Frame pf = v.sh;
+                if (info & SR_BUMP) {
+                    pf.n = f3(r[7 * cap]); pf.s = f3(r[8 * cap]);
+                    pf.t = cross((info & SR_NFLIP) ? -pf.n : pf.n, pf.s);
+                }
+                // shadeScatter only asks the two questions the flags answer
+                v.lobes = ((info & SR_SMOOTH) ? MTS_EDIFFUSE_REFLECTION : 0u) | ((info & SR_ONESIDED) ? 0u : MTS_EBACKSIDE);
+                const Material<SHADE_LEAF> mat(S, leaf, lt, v.sh, pf, f3(r4.w, r5.w, r6.w), (info & SR_BUMP) != 0, (info & SR_FLIPPED) != 0);
+                out.done = true;
+                shadeScatter(S, W, R, slot, v, mat, out);
+            }
+        }
+        uint32_t a = warpAppend(&W.ctr->qCount[qsel ^ 1], out.next);
+        if (out.next) W.queue[qsel ^ 1][a] = slot;
+        uint32_t b = warpAppend(&W.ctr->shadowCount, out.shadow);
+        if (out.shadow) { W.shO[b] = out.shO; W.shD[b] = out.shD; W.shC[b] = out.shC; }
+        uint32_t c = warpAppend(&W.ctr->doneCount, out.done);
+        if (out.done) W.doneQ[c] = slot;
+    }
+}
+
 // ---- splat: ImageBlock::put(pos, spec, alpha) (include/mitsuba/render/imageblock.h:124-204) ----
 DEVFN void filmAdd(float4 *dst, float4 v) {
 #if __CUDA_ARCH__ >= 900
@@ -519,11 +730,11 @@ static __global__ void __launch_bounds__(256) k_splat(const DScene S, const Wave
 // bounce that is about to run (closest hit) and of the one that just ran (shadow) to the totals, reset the queues.
 static __global__ void k_begin_bounce(Counters *c, int cur) {
     c->normalRays += c->qCount[cur]; c->shadowRays += c->shadowCount;
-    c->qCount[cur ^ 1] = 0; c->shadowCount = 0; c->doneCount = 0; c->cursor[0] = c->cursor[1] = 0;
+    c->qCount[cur ^ 1] = 0; c->shadowCount = 0; c->doneCount = 0; c->ewaCount = 0; c->cursor[0] = c->cursor[1] = 0;
 }
 static __global__ void k_begin_wavefront(Counters *c) {
     c->shadowRays += c->shadowCount;
-    c->qCount[0] = c->qCount[1] = 0; c->shadowCount = 0; c->doneCount = 0; c->cursor[0] = c->cursor[1] = 0;
+    c->qCount[0] = c->qCount[1] = 0; c->shadowCount = 0; c->doneCount = 0; c->ewaCount = 0; c->cursor[0] = c->cursor[1] = 0;
 }
 // Safety net of unbounded renders (maxDepth = -1 with Russian roulette pushed out of reach): the paths still alive
 // when the host gives up are finished with what they have gathered so far and splatted, never dropped.

@@ -365,7 +365,8 @@ CONDUCTOR_PRESETS = {
 }
 
 SUPPORTED_BSDFS = ("diffuse", "conductor", "roughconductor", "plastic", "roughplastic", "dielectric",
-                   "coating", "blendbsdf", "bumpmap", "twosided", "thindielectric", "mask", "roughdielectric")
+                   "coating", "blendbsdf", "bumpmap", "twosided", "thindielectric", "mask", "roughdielectric",
+                   "mixturebsdf", "roughcoating", "normalmap")
 
 
 class Unsupported(ValueError):
@@ -386,6 +387,7 @@ class FlatScene:
         self.spp = 4
         self._tex_ids = {}
         self._bsdf_ids = {}
+        self._mix_children = {}   # node index -> nested node indices of a mixturebsdf
 
     # ---- textures ---------------------------------------------------------
     def _bitmap(self, p):
@@ -685,6 +687,99 @@ class FlatScene:
             n.lobes = ((front & ~abi.EBACKSIDE) | abi.EFRONTSIDE) | ((back & ~abi.EFRONTSIDE) | abi.EBACKSIDE)
             if n.lobes & abi.ETRANSMISSION:
                 raise ValueError("Only materials without a transmission component can be nested!")
+        elif t == "mixturebsdf":
+            # MixtureBSDF ctor / addChild / configure (src/bsdfs/mixturebsdf.cpp:60-98, 114-172)
+            kids = [c for _, c in p.children_of("bsdf")]
+            weights = [F(x) for x in str(p.get("weights", "")).replace(",", " ").replace(";", " ").split()]
+            if not weights:
+                raise ValueError("No weights were supplied!")
+            if len(kids) != len(weights):
+                raise ValueError("BSDF count mismatch: %d bsdfs, but specified %d weights" % (len(kids), len(weights)))
+            if len(kids) > abi.MIXTURE_MAX:
+                raise Unsupported("mixturebsdf with more than %d nested BSDFs" % abi.MIXTURE_MAX)
+            for w in weights:
+                if w < 0:
+                    raise ValueError("Invalid BSDF weight: %f" % w)
+            total = F(0)
+            for w in weights:
+                total = F(total + w)
+            if total <= 0:
+                raise ValueError("The weights must sum to a value greater than zero!")
+            if p.get("ensureEnergyConservation", True) and total > 1:
+                scale = F(1.0) / total
+                weights = [F(w * scale) for w in weights]
+            cdf = [F(0)]                                    # DiscreteDistribution::append / normalize (pmf.h:58-66, 101-114)
+            for w in weights:
+                cdf.append(F(cdf[-1] + w))
+            norm = F(1.0) / cdf[-1]
+            cdf = [cdf[0]] + [F(c * norm) for c in cdf[1:]]
+            cdf[-1] = F(1.0)
+            children = [self.bsdf(k) for k in kids]
+            n.type = abi.BSDF_MIXTURE
+            n.lut[0], n.lut[1] = len(self.pool), len(kids)
+            self.pool += [float(c) for c in children] + [float(w) for w in weights] + [float(c) for c in cdf]
+            lobes = 0
+            for c in children:
+                lobes |= self.nodes[c].lobes
+            n.lobes = lobes
+            self._mix_children[idx] = children
+        elif t == "roughcoating":
+            # RoughCoating ctor / addChild / configure (src/bsdfs/roughcoating.cpp:113-148, 180-225, 450-470)
+            int_ior = hm.lookup_ior(p.get("intIOR"), "bk7")
+            ext_ior = hm.lookup_ior(p.get("extIOR"), "air")
+            if int_ior < 0 or ext_ior < 0 or int_ior == ext_ior:
+                raise ValueError("The interior and exterior indices of refraction must be positive and differ!")
+            nested = p.child("bsdf")
+            if nested is None:
+                raise ValueError("A child BSDF instance is required")
+            if "alphaU" in p.props or "alphaV" in p.props:
+                raise ValueError("The 'roughplastic' plugin currently does not support anisotropic microfacet distributions!")
+            eta = float(F(int_ior) / F(ext_ior))
+            n.type = abi.BSDF_ROUGHCOATING
+            n.eta[0] = eta
+            n.flags = microfacet()
+            thickness = float(p.get("thickness", 1.0))
+            n.f[3] = thickness
+            sig = self.texref(p, "sigmaA", Spectrum(0.0))
+            avg_abs = float(np.mean([F(math.exp(float(F(x) * F(-2 * thickness)))) for x in sig["avg"]]))
+            n.f[2] = F(1.0) / (F(avg_abs) + F(1.0))        # m_specularSamplingWeight, roughcoating.cpp:200-203
+            a = self.texref(p, "alpha", 0.1)
+            n.t0 = self._ref(sig)
+            n.t1 = self._ref(self._conserve(self.texref(p, "specularReflectance", Spectrum(1.0))))
+            n.t2 = self._ref(a)
+            rt = hm.RoughTransmittance("ggx" if n.flags & abi.BF_GGX else "beckmann")
+            rt.check_eta(eta)
+            rt.check_alpha(float(np.mean(a["min"])))
+            rt.check_alpha(float(np.mean(a["max"])))
+            ext2d, _ = rt.reduce_eta(eta)
+            n.f[0], n.f[1] = rt.alpha_min, rt.alpha_max
+            n.lut[1], n.lut[2] = rt.n_theta, rt.n_alpha
+            n.lut[0] = len(self.pool)
+            if a["const"]:
+                alpha_cfg = float(F(np.mean(a["scale"].astype(F))))
+                ext1d, _ = rt.reduce_alpha(ext2d, np.zeros(rt.n_alpha, dtype=F), alpha_cfg)
+                self.pool += [float(x) for x in ext1d]
+            else:
+                n.flags |= abi.BF_RT_2D
+                self.pool += [float(x) for x in ext2d.reshape(-1)]
+            n.child[0] = self.bsdf(nested)
+            n.lobes = self.nodes[n.child[0]].lobes | abi.EGLOSSY_REFLECTION | abi.EFRONTSIDE | abi.EBACKSIDE
+        elif t == "normalmap":
+            # NormalMap addChild / configure (src/bsdfs/normalmap.cpp:58-104)
+            nested = p.child("bsdf")
+            normals = p.child("texture")
+            if nested is None:
+                raise ValueError("A child BSDF instance is required")
+            if normals is None:
+                raise ValueError("A normal map texture must be specified")
+            if normals.type == "bitmap" and normals.get("gamma") is None:
+                raise ValueError("When using a bitmap texture as a normal map, please explicitly specify the 'gamma' "
+                                 "parameter of the bitmap plugin.")
+            n.type = abi.BSDF_NORMALMAP
+            name = [nm for nm, c in p.children if c is normals][0]
+            n.t0 = self._ref(self.texref(p, name, 0.0))
+            n.child[0] = self.bsdf(nested)
+            n.lobes = self.nodes[n.child[0]].lobes
         if self._uses_ray_differentials(n):
             n.flags |= abi.BF_RAY_DIFF
         return idx
@@ -695,10 +790,12 @@ class FlatScene:
         (bumpmap.cpp:96); blendbsdf / mask / twosided only look at the nested BSDFs (blendbsdf.cpp:130, mask.cpp:108,
         twosided.cpp:91-92), not at their own weight / opacity texture."""
         kids = any(self.nodes[c].flags & abi.BF_RAY_DIFF for c in n.child if c >= 0)
-        if n.type == abi.BSDF_BUMPMAP:
+        if n.type in (abi.BSDF_BUMPMAP, abi.BSDF_NORMALMAP):     # bumpmap.cpp:96, normalmap.cpp:69
             return True
         if n.type in (abi.BSDF_BLEND, abi.BSDF_MASK, abi.BSDF_TWOSIDED):
             return kids
+        if n.type == abi.BSDF_MIXTURE:                           # mixturebsdf.cpp:166
+            return any(self.nodes[c].flags & abi.BF_RAY_DIFF for c in self._mix_children[self.nodes.index(n)])
         own = any(r.tex >= 0 for r in (n.t0, n.t1, n.t2))
         if n.type == abi.BSDF_ROUGHDIELECTRIC:
             own = own or n.lut[0] >= 0      # specularTransmittance lives in the k / lut slots

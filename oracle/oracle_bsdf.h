@@ -324,6 +324,54 @@ inline Frame bumpFrame(const Materials &M, const MtsBsdfNode &n, const Its &its)
     return r;
 }
 
+/* NormalMap::getFrame (src/bsdfs/normalmap.cpp:106-123); the texture is read unfiltered (`eval(its, false)`) */
+inline Frame normalMapFrame(const Materials &M, const MtsBsdfNode &n, const Its &its) {
+    Its plain(its);
+    plain.hasUVPartials = false;
+    V3 v = evalTex(M, n.t0, plain);
+    V3 nl(2 * v.x - 1, 2 * v.y - 1, 2 * v.z - 1);
+    Frame r;
+    r.n = normalize(its.sh.toWorld(nl));
+    r.s = normalize(its.dpdu - r.n * dot(r.n, its.dpdu));
+    r.t = cross(r.n, r.s);
+    return r;
+}
+inline Frame perturbedFrame(const Materials &M, const MtsBsdfNode &n, const Its &its) {
+    return n.type == MTS_BSDF_NORMALMAP ? normalMapFrame(M, n, its) : bumpFrame(M, n, its);
+}
+
+/* RoughCoating::refractTo (src/bsdfs/roughcoating.cpp:232-253); etaTo = 1/eta towards the interior, eta towards the exterior */
+inline V3 roughCoatRefract(float etaTo, V3 wi) {
+    float sinThetaTSqr = etaTo * etaTo * Frame::sinTheta2(wi);
+    if (sinThetaTSqr >= 1.0f) return V3(0.0f);
+    float cosThetaT = std::sqrt(1.0f - sinThetaTSqr);
+    return V3(etaTo * wi.x, etaTo * wi.y, Frame::cosTheta(wi) > 0.0f ? cosThetaT : -cosThetaT);
+}
+/* roughcoating.cpp:332-343, 388-397 */
+inline float roughCoatProbSpecular(const Materials &M, const MtsBsdfNode &n, V3 wi, float alpha) {
+    float probSpecular = 1 - roughTransmittance(M, n, std::fabs(Frame::cosTheta(wi)), alpha);
+    float w = n.f[2];
+    return (probSpecular * w) / (probSpecular * w + (1 - probSpecular) * (1 - w));
+}
+/* MixtureBSDF tables in the float pool (include/mtscuda.h): N child indices, N weights, N + 1 CDF entries */
+struct MixtureTab {
+    const float *p; int n;
+    MixtureTab(const Materials &M, const MtsBsdfNode &nd) : p(M.pool.data() + nd.lut[0]), n(nd.lut[1]) {}
+    int child(int i) const { return (int)p[i]; }
+    float weight(int i) const { return p[n + i]; }
+    float cdf(int i) const { return p[2 * n + i]; }
+    float pdf(int i) const { return cdf(i + 1) - cdf(i); }
+    /* DiscreteDistribution::sampleReuse (include/mitsuba/core/pmf.h:124-136, 164-169) */
+    int sampleReuse(float &u) const {
+        const float *b = p + 2 * n, *e = b + n + 1;
+        const float *entry = std::lower_bound(b, e, u);
+        int index = (int)std::min((ptrdiff_t)(n - 1), std::max((ptrdiff_t)0, entry - b - 1));
+        while (pdf(index) == 0 && index < n) ++index;
+        u = (u - cdf(index)) / (cdf(index + 1) - cdf(index));
+        return index;
+    }
+};
+
 /* SmoothCoating::refractIn/refractOut (src/bsdfs/coating.cpp:208-219) */
 inline V3 coatRefractIn(float eta, V3 wi, float &R) {
     float cosThetaT; float invEta = 1 / eta;
@@ -468,9 +516,43 @@ inline V3 bsdfEval(const Materials &M, int node, const Its &its, V3 wi, V3 wo, i
         float weight = std::min(1.0f, std::max(0.0f, average(evalTex(M, n.t0, its))));
         return bsdfEval(M, n.child[0], its, wi, wo, measure) * (1 - weight) + bsdfEval(M, n.child[1], its, wi, wo, measure) * weight;
     }
+    case MTS_BSDF_MIXTURE: { /* mixturebsdf.cpp:174-189 */
+        MixtureTab mt(M, n);
+        V3 result(0.0f);
+        for (int i = 0; i < mt.n; ++i) result += bsdfEval(M, mt.child(i), its, wi, wo, measure) * mt.weight(i);
+        return result;
+    }
+    case MTS_BSDF_ROUGHCOATING: { /* roughcoating.cpp:255-314 */
+        float eta = n.eta[0], invEta = 1 / eta;
+        bool hasNested = (M.nodes[n.child[0]].lobes & MTS_EALL) != 0, hasSpecular = solid;
+        float alpha = average(evalTex(M, n.t2, its));
+        Microfacet distr(n.flags & MTS_BF_GGX, alpha, alpha, n.flags & MTS_BF_SAMPLE_VISIBLE);
+        V3 result(0.0f);
+        if (hasSpecular && Frame::cosTheta(wo) * Frame::cosTheta(wi) > 0) {
+            V3 H = normalize(wo + wi) * signum(Frame::cosTheta(wo));
+            float D = distr.eval(H);
+            float F = fresnelDielectricExt(absDot(wi, H), eta);
+            float G = distr.G(wi, wo, H);
+            float value = F * D * G / (4.0f * std::fabs(Frame::cosTheta(wi)));
+            result += evalTex(M, n.t1, its) * value;
+        }
+        if (hasNested) {
+            V3 wiI = roughCoatRefract(invEta, wi), woI = roughCoatRefract(invEta, wo);
+            V3 nested = bsdfEval(M, n.child[0], its, wiI, woI, measure) *
+                roughTransmittance(M, n, std::fabs(Frame::cosTheta(wi)), distr.alphaU) *
+                roughTransmittance(M, n, std::fabs(Frame::cosTheta(wo)), distr.alphaU);
+            V3 sigmaA = evalTex(M, n.t0, its) * n.f[3];
+            if (!isZero(sigmaA))
+                nested *= vexp(-sigmaA * (1 / std::fabs(Frame::cosTheta(wiI)) + 1 / std::fabs(Frame::cosTheta(woI))));
+            if (solid) nested *= invEta * invEta * Frame::cosTheta(wo) / Frame::cosTheta(woI);
+            result += nested;
+        }
+        return result;
+    }
+    case MTS_BSDF_NORMALMAP: /* normalmap.cpp:162-179 */
     case MTS_BSDF_BUMPMAP: { /* bumpmap.cpp:161-177 */
         Its pert(its);
-        pert.sh = bumpFrame(M, n, its);
+        pert.sh = perturbedFrame(M, n, its);
         V3 wiP = pert.toLocal(its.toWorld(wi)), woP = pert.toLocal(its.toWorld(wo));
         if (Frame::cosTheta(wo) * Frame::cosTheta(woP) <= 0) return V3(0.0f);
         return bsdfEval(M, n.child[0], pert, wiP, woP, measure);
@@ -602,9 +684,37 @@ inline float bsdfPdf(const Materials &M, int node, const Its &its, V3 wi, V3 wo,
         float weight = std::min(1.0f, std::max(0.0f, average(evalTex(M, n.t0, its))));
         return bsdfPdf(M, n.child[0], its, wi, wo, measure) * (1 - weight) + bsdfPdf(M, n.child[1], its, wi, wo, measure) * weight;
     }
+    case MTS_BSDF_MIXTURE: { /* mixturebsdf.cpp:191-206 */
+        MixtureTab mt(M, n);
+        float result = 0.0f;
+        for (int i = 0; i < mt.n; ++i) result += bsdfPdf(M, mt.child(i), its, wi, wo, measure) * mt.pdf(i);
+        return result;
+    }
+    case MTS_BSDF_ROUGHCOATING: { /* roughcoating.cpp:316-376 */
+        float eta = n.eta[0], invEta = 1 / eta;
+        bool hasNested = (M.nodes[n.child[0]].lobes & MTS_EALL) != 0, hasSpecular = measure == MTS_MEASURE_SOLID_ANGLE;
+        V3 H = normalize(wo + wi) * signum(Frame::cosTheta(wo));
+        float alpha = average(evalTex(M, n.t2, its));
+        Microfacet distr(n.flags & MTS_BF_GGX, alpha, alpha, n.flags & MTS_BF_SAMPLE_VISIBLE);
+        float probNested = 1.0f, probSpecular = 1.0f;
+        if (hasSpecular && hasNested) { probSpecular = roughCoatProbSpecular(M, n, wi, distr.alphaU); probNested = 1 - probSpecular; }
+        float result = 0.0f;
+        if (hasSpecular && Frame::cosTheta(wo) * Frame::cosTheta(wi) > 0) {
+            float dwh_dwo = 1.0f / (4.0f * absDot(wo, H));
+            result = distr.pdf(wi, H) * dwh_dwo * probSpecular;
+        }
+        if (hasNested) {
+            V3 wiI = roughCoatRefract(invEta, wi), woI = roughCoatRefract(invEta, wo);
+            float prob = bsdfPdf(M, n.child[0], its, wiI, woI, measure);
+            if (measure == MTS_MEASURE_SOLID_ANGLE) prob *= invEta * invEta * Frame::cosTheta(wo) / Frame::cosTheta(woI);
+            result += prob * probNested;
+        }
+        return result;
+    }
+    case MTS_BSDF_NORMALMAP: /* normalmap.cpp:181-197 */
     case MTS_BSDF_BUMPMAP: { /* bumpmap.cpp:179-197 */
         Its pert(its);
-        pert.sh = bumpFrame(M, n, its);
+        pert.sh = perturbedFrame(M, n, its);
         V3 wiP = pert.toLocal(its.toWorld(wi)), woP = pert.toLocal(its.toWorld(wo));
         if (Frame::cosTheta(wo) * Frame::cosTheta(woP) <= 0) return 0;
         return bsdfPdf(M, n.child[0], pert, wiP, woP, measure);
@@ -813,9 +923,52 @@ inline V3 bsdfSample(const Materials &M, int node, const Its &its, V3 wi, V2 sam
         result += bsdfEval(M, n.child[other], its, wi, o.wo, measure) * weights[other];
         return result / o.pdf;
     }
+    case MTS_BSDF_MIXTURE: { /* mixturebsdf.cpp:244-268 (the pdf-returning overload path.cpp:209 calls) */
+        MixtureTab mt(M, n);
+        int entry = mt.sampleReuse(sample.x);
+        V3 result = bsdfSample(M, mt.child(entry), its, wi, sample, o);
+        if (isZero(result)) return result;
+        result *= mt.weight(entry) * o.pdf;
+        o.pdf *= mt.pdf(entry);
+        int measure = measureOf(o.type);
+        for (int i = 0; i < mt.n; ++i) {
+            if (i == entry) continue;
+            o.pdf += bsdfPdf(M, mt.child(i), its, wi, o.wo, measure) * mt.pdf(i);
+            result += bsdfEval(M, mt.child(i), its, wi, o.wo, measure) * mt.weight(i);
+        }
+        return result / o.pdf;
+    }
+    case MTS_BSDF_ROUGHCOATING: { /* roughcoating.cpp:378-448 */
+        float eta = n.eta[0], invEta = 1 / eta;
+        bool hasNested = (M.nodes[n.child[0]].lobes & MTS_EALL) != 0;
+        bool choseSpecular = true;
+        float alpha = average(evalTex(M, n.t2, its));
+        Microfacet distr(n.flags & MTS_BF_GGX, alpha, alpha, n.flags & MTS_BF_SAMPLE_VISIBLE);
+        if (hasNested) {
+            float probSpecular = roughCoatProbSpecular(M, n, wi, distr.alphaU);
+            if (sample.y < probSpecular) sample.y /= probSpecular;
+            else { sample.y = (sample.y - probSpecular) / (1 - probSpecular); choseSpecular = false; }
+        }
+        if (choseSpecular) {
+            float dummy;
+            V3 m = distr.sampleVisible ? distr.sampleVisibleNormal(wi, sample) : distr.sampleAll(sample, dummy);
+            o.wo = reflectM(wi, m); o.type = MTS_EGLOSSY_REFLECTION; o.eta = 1.0f;
+            if (Frame::cosTheta(o.wo) * Frame::cosTheta(wi) <= 0) return V3(0.0f);
+        } else {
+            V3 result = bsdfSample(M, n.child[0], its, roughCoatRefract(invEta, wi), sample, o);
+            if (isZero(result)) return V3(0.0f);
+            o.wo = roughCoatRefract(eta, o.wo);
+            if (isZero(o.wo)) return V3(0.0f);
+        }
+        int measure = measureOf(o.type);
+        o.pdf = bsdfPdf(M, node, its, wi, o.wo, measure);
+        if (o.pdf == 0) return V3(0.0f);
+        return bsdfEval(M, node, its, wi, o.wo, measure) / o.pdf;
+    }
+    case MTS_BSDF_NORMALMAP: /* normalmap.cpp:218-239 */
     case MTS_BSDF_BUMPMAP: { /* bumpmap.cpp:221-240 */
         Its pert(its);
-        pert.sh = bumpFrame(M, n, its);
+        pert.sh = perturbedFrame(M, n, its);
         V3 wiP = pert.toLocal(its.toWorld(wi));
         V3 result = bsdfSample(M, n.child[0], pert, wiP, sample, o);
         if (!isZero(result)) {

@@ -561,9 +561,54 @@ private:
                 int a = parseBsdf(s, seen, tex), b = parseBsdf(s, seen, tex);
                 n.type = MTS_BSDF_TWOSIDED; n.child[0] = a; n.child[1] = b;
                 n.lobes = ((m_nodes[a].lobes & ~MTS_EBACKSIDE) | MTS_EFRONTSIDE) | ((m_nodes[b].lobes & ~MTS_EFRONTSIDE) | MTS_EBACKSIDE);
+            } else if (cls == "MixtureBSDF") {   /* mixturebsdf.cpp:105-113: count, then (weight, nested instance) pairs */
+                size_t count = s->readSize();
+                if (count < 1 || count > MTS_MIXTURE_MAX) err("mixturebsdf: 1..16 nested BSDFs are supported");
+                std::vector<float> weights(count), cdf(count + 1, 0.0f);
+                std::vector<int> kids(count);
+                for (size_t i = 0; i < count; ++i) { weights[i] = s->readFloat(); kids[i] = parseBsdf(s, seen, tex); }
+                /* the weights are the configured ones (already rescaled, mixturebsdf.cpp:131-143); m_pdf as configure() builds
+                   it: DiscreteDistribution::append / normalize (include/mitsuba/core/pmf.h:58-66, 101-114) */
+                for (size_t i = 0; i < count; ++i) cdf[i + 1] = cdf[i] + weights[i];
+                if (!(cdf[count] > 0)) err("The weights must sum to a value greater than zero!");
+                const float norm = 1.0f / cdf[count];
+                for (size_t i = 1; i <= count; ++i) cdf[i] *= norm;
+                cdf[count] = 1.0f;
+                n.type = MTS_BSDF_MIXTURE; n.lut[0] = (int32_t) m_pool.size(); n.lut[1] = (int32_t) count;
+                for (size_t i = 0; i < count; ++i) { m_pool.push_back((float) kids[i]); n.lobes |= m_nodes[kids[i]].lobes; }
+                m_pool.insert(m_pool.end(), weights.begin(), weights.end());
+                m_pool.insert(m_pool.end(), cdf.begin(), cdf.end());
+            } else if (cls == "RoughCoating") {   /* roughcoating.cpp:167-178 */
+                uint32_t type = s->readUInt(); bool sv = s->readBool();
+                int nested = parseBsdf(s, seen, tex);
+                TexInfo sig = parseTexture(s, tex), sp = conserve(parseTexture(s, tex)), al = parseTexture(s, tex);
+                Float eta = s->readFloat(), thickness = s->readFloat();
+                n.type = MTS_BSDF_ROUGHCOATING; n.flags = distrFlags(type, sv); n.eta[0] = eta; n.child[0] = nested;
+                n.t0 = sig.ref; n.t1 = sp.ref; n.t2 = al.ref; n.f[3] = thickness;
+                Float avgAbsorption = (sig.avg * (-2 * thickness)).exp().average();   /* roughcoating.cpp:200-203 */
+                n.f[2] = 1.0f / (avgAbsorption + 1.0f);
+                ref<RoughTransmittance> rt = new RoughTransmittance((MicrofacetDistribution::EType) type);   /* :209-222 */
+                rt->checkEta(eta); rt->checkAlpha(al.min.average()); rt->checkAlpha(al.max.average());
+                rt->setEta(eta);
+                n.f[0] = rt->getAlphaMin(); n.f[1] = rt->getAlphaMax();
+                n.lut[1] = (int32_t) rt->m_thetaSamples; n.lut[2] = (int32_t) rt->m_alphaSamples;
+                n.lut[0] = (int32_t) m_pool.size();
+                if (al.constant) {
+                    rt->setAlpha((al.ref.scale[0] + al.ref.scale[1] + al.ref.scale[2]) * (1.0f / 3.0f));
+                    m_pool.insert(m_pool.end(), rt->m_trans, rt->m_trans + rt->m_thetaSamples);
+                } else {
+                    n.flags |= MTS_BF_RT_2D;
+                    m_pool.insert(m_pool.end(), rt->m_trans, rt->m_trans + rt->m_alphaSamples * rt->m_thetaSamples);
+                }
+                n.lobes = m_nodes[nested].lobes | MTS_EGLOSSY_REFLECTION | MTS_EFRONTSIDE | MTS_EBACKSIDE;
+            } else if (cls == "NormalMap") {   /* normalmap.cpp:74-79: nested BSDF, then the normal texture */
+                int nested = parseBsdf(s, seen, tex);
+                TexInfo nm = parseTexture(s, tex);
+                n.type = MTS_BSDF_NORMALMAP; n.t0 = nm.ref; n.child[0] = nested; n.lobes = m_nodes[nested].lobes;
             } else
                 err("BSDF class " + cls + " is out of scope (diffuse, conductor, roughconductor, plastic, roughplastic, "
-                    "dielectric, coating, blendbsdf, bumpmap, twosided, thindielectric, mask, roughdielectric)");
+                    "dielectric, coating, blendbsdf, bumpmap, twosided, thindielectric, mask, roughdielectric, mixturebsdf, "
+                    "roughcoating, normalmap)");
             m_nodes[idx] = n;
             return idx;
         }

@@ -107,6 +107,36 @@ def twosided():
     return out
 
 
+def nextrow():
+    """nextrow.npz: BSDF probes of the mixturebsdf / roughcoating / normalmap configurations, the albedo / specular texture
+    pair looked up with uv partials (shared EWA walk), and a converged render of a scene that uses them all."""
+    sc, z = G.nextrow()
+    rs = mtsref.RefScene(sc)
+    out = {}
+    for name, p in z.items():
+        surf, wi, wo, u = G.mip_bsdf_inputs(name) if name in G.NEXTROW_WITH_PARTIALS else G.bsdf_inputs(name)
+        rb = rs.bsdf(p)
+        smp = rs.bsdf_sample(rb, surf, wi, u)
+        wo2 = G.eval_directions(smp, wo)
+        out["bsdf/%s/sample" % name] = smp
+        for tag, meas in (("sa", 1), ("disc", 4)):
+            v, pdf = rs.bsdf_eval_pdf(rb, surf, wi, wo2, meas)
+            out["bsdf/%s/eval_%s" % (name, tag)] = v
+            out["bsdf/%s/pdf_%s" % (name, tag)] = pdf
+        out["bsdf/%s/type" % name] = np.array([rs.bsdf_type(rb)], dtype=np.int64)
+    for name, make in G.NEXTROW_IMAGE_SCENES.items():
+        scn = make()
+        rsi = mtsref.RefScene(scn)
+        film = rsi.render()
+        st = rsi.stats
+        w, h, spp = G.scene_dims(scn)
+        out["image/%s/rgb" % name] = M.develop(film).astype(np.float16)
+        out["image/%s/stats" % name] = np.array([st.get("normal_rays", 0) / (w * h * spp), st.get("shadow_rays", 0) / (w * h * spp),
+                                                 st.get("avg_path_length", 0), rsi.render_s, mtsref.load().mtsref_thread_count()], dtype=np.float64)
+        print("%-10s %dx%d %d spp: reference render %.1f s" % (name, w, h, spp, rsi.render_s), flush=True)
+    return out
+
+
 def boundary():
     """boundary.npz: crop window, sphere transform composition and the alpha channel, rendered by the reference."""
     out = {}
@@ -185,6 +215,11 @@ if __name__ == "__main__":
         t = boundary()
         np.savez_compressed(os.path.join(HERE, "boundary.npz"), **t)
         print("boundary.npz: %d arrays" % len(t))
+        raise SystemExit(0)
+    if "--nextrow" in sys.argv:
+        t = nextrow()
+        np.savez_compressed(os.path.join(HERE, "nextrow.npz"), **t)
+        print("nextrow.npz: %d arrays" % len(t))
         raise SystemExit(0)
     if "--twosided" in sys.argv:
         t = twosided()

@@ -24,6 +24,10 @@ def twosided(spp=4, hide_env=False):
     return util.twosided_scene(width=ZOO_W, height=ZOO_H, spp=spp, hide_env=hide_env)
 
 
+def nextrow(spp=4):
+    return util.nextrow_scene(width=ZOO_W, height=ZOO_H, spp=spp)
+
+
 def cornell_small(spp=64):
     return scenes.cornell_box(CORNELL_RES, CORNELL_RES, spp)
 
@@ -151,6 +155,10 @@ TWOSIDED_IMAGE_SCENES = {
 
 
 # boundary cases (crop window, sphere transform composition, alpha channel); fixture boundary.npz
+NEXTROW_WITH_PARTIALS = ("rp_pair_ewa", "nmap_rp")   # probed on intersections that carry uv partials (mip_bsdf_inputs)
+NEXTROW_IMAGE_SCENES = {
+    "nextrow": lambda: nextrow(spp=16384)[0],
+}
 BOUNDARY_IMAGE_SCENES = {
     "crop": lambda: util.cropped_cornell(spp=4096),
     "sphere_alpha": lambda: util.sphere_alpha_scene(spp=4096),

@@ -369,6 +369,36 @@ def test_twosided_render_vs_reference(gold_twosided, name, spp, bar):
     g.close()
 
 
+
+# ---- mixturebsdf / roughcoating / normalmap (the rest of SURVEY 8(f) rank 1): fixture nextrow.npz ----------------------
+@pytest.fixture(scope="module")
+def gold_nextrow():
+    return G.load("nextrow.npz")
+
+
+@pytest.fixture(scope="module")
+def gnextrow():
+    sc, z = G.nextrow()
+    gpu, cpu, flat = util.make_pair(sc)
+    yield gpu, cpu, flat, z
+    gpu.close()
+    cpu.close()
+
+
+@pytest.mark.parametrize("name", list(util.nextrow_bsdfs().keys()))
+def test_nextrow_bsdf_vs_reference(gnextrow, gold_nextrow, name):
+    gpu, _, flat, z = gnextrow
+    inputs = (lambda n: G.mip_bsdf_inputs(n)) if name in G.NEXTROW_WITH_PARTIALS else None
+    GC.check_bsdf(gpu.ctx, flat, z, name, gold_nextrow, inputs=inputs)
+
+
+def test_nextrow_render_vs_reference(gold_nextrow):
+    g = M.CudaPath(G.NEXTROW_IMAGE_SCENES["nextrow"]())
+    err = GC.check_image(g, "nextrow", gold_nextrow, 16384, 2e-3, lazy_shadow=True)
+    print("relMSE(nextrow, 16384 spp vs reference) = %.3g" % err)
+    g.close()
+
+
 # ---- MIP maps + ray differentials (rows a7, a11, a24): fixture mip.npz ---------------------------------------------
 @pytest.fixture(scope="module")
 def mip_pair():

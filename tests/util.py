@@ -214,6 +214,117 @@ def twosided_bsdfs():
     return z
 
 
+
+# ---- mixturebsdf, roughcoating, normalmap (the rest of the row) --------------------------------
+def _normal_tex(seed, size=64, **kw):
+    """Tangent-space normal map: unit normals around +z stored as 0.5 * (n + 1) (src/bsdfs/normalmap.cpp:110-112)."""
+    rng = np.random.RandomState(seed)
+    n = np.concatenate([rng.uniform(-0.35, 0.35, (size, size, 2)), np.ones((size, size, 1))], -1)
+    n /= np.linalg.norm(n, axis=2, keepdims=True)
+    t = Plugin("texture", "bitmap", filterType="bilinear", gamma=1.0, **kw)
+    t.data["bitmap"] = (0.5 * (n + 1)).astype(F)
+    return t
+
+
+def nextrow_bsdfs():
+    """MixtureBSDF (2 and 3 nested models, weights above and below one), RoughCoating (constant / textured roughness,
+    absorbing layer, back side) and NormalMap (below and above other adapters)."""
+    CU, AU = scenes.CU, scenes.AU
+    z = {}
+    m = Plugin("bsdf", "mixturebsdf", weights="0.7, 0.2")
+    m.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.6, 0.3, 0.2)))
+    m.add(Plugin("bsdf", "roughconductor", distribution="ggx", alpha=0.2, **CU))
+    z["mix_diff_rc"] = m
+    m3 = Plugin("bsdf", "mixturebsdf", weights="0.8 0.6 0.4")          # sums to 1.8: rescaled (mixturebsdf.cpp:131-143)
+    m3.add(Plugin("bsdf", "plastic", intIOR=1.5, diffuseReflectance=Spectrum(0.2, 0.4, 0.6)))
+    m3.add(Plugin("bsdf", "conductor", **AU))
+    d = Plugin("bsdf", "diffuse")
+    d.add(_tex(21, uvscale=2.0), "reflectance")
+    m3.add(d)
+    z["mix3_rescaled"] = m3
+    mg = Plugin("bsdf", "mixturebsdf", weights="0.5;0.5")                # transmission below a mixture
+    mg.add(Plugin("bsdf", "dielectric", intIOR=1.5))
+    mg.add(Plugin("bsdf", "roughplastic", distribution="beckmann", alpha=0.2, intIOR=1.5, diffuseReflectance=Spectrum(0.7, 0.2, 0.2)))
+    z["mix_glass_rp"] = mg
+    rc = Plugin("bsdf", "roughcoating", distribution="ggx", alpha=0.15, intIOR=1.5)
+    rc.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.7, 0.5, 0.2)))
+    z["rcoat_diffuse"] = rc
+    rc2 = Plugin("bsdf", "roughcoating", distribution="beckmann", intIOR=1.7, extIOR=1.0, thickness=2.0,
+                 sigmaA=Spectrum(0.3, 0.1, 0.6), specularReflectance=Spectrum(0.9, 0.95, 0.8))
+    rc2.add(_alpha_tex(22), "alpha")
+    rc2.add(Plugin("bsdf", "roughconductor", distribution="beckmann", alpha=0.3, **AU))
+    z["rcoat_tex_rcond"] = rc2
+    rc3 = Plugin("bsdf", "roughcoating", distribution="ggx", alpha=0.3, sampleVisible=False, intIOR=1.33)
+    rc3.add(Plugin("bsdf", "plastic", intIOR=1.6, diffuseReflectance=Spectrum(0.3, 0.6, 0.4)))
+    z["rcoat_all_plastic"] = rc3
+    # albedo / specular bitmaps of one geometry with the default filterType (ewa): the two lookups share one EWA walk
+    rp = Plugin("bsdf", "roughplastic", distribution="ggx", alpha=0.2, intIOR=1.5)
+    for k, slot in ((31, "diffuseReflectance"), (32, "specularReflectance")):
+        t = _tex(k, uvscale=3.0, size=128)
+        t.props["filterType"] = "ewa"
+        rp.add(t, slot)
+    z["rp_pair_ewa"] = rp
+    nm = Plugin("bsdf", "normalmap")
+    nm.add(_normal_tex(23, uvscale=2.0))
+    nm.add(Plugin("bsdf", "roughplastic", distribution="ggx", alpha=0.1, intIOR=1.49, diffuseReflectance=Spectrum(0.3, 0.5, 0.7)))
+    z["nmap_rp"] = nm
+    ts = Plugin("bsdf", "twosided")
+    nm2 = Plugin("bsdf", "normalmap")
+    nm2.add(_normal_tex(24, uvscale=3.0))
+    nm2.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.6, 0.6, 0.3)))
+    ts.add(nm2)
+    z["ts_nmap_diffuse"] = ts
+    nm3 = Plugin("bsdf", "normalmap")                                     # normalmap above a wrapper: generic shade class
+    nm3.add(_normal_tex(25, uvscale=1.5))
+    ct = Plugin("bsdf", "coating", intIOR=1.5, sigmaA=Spectrum(0.2, 0.4, 0.1))
+    ct.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.5, 0.4, 0.6)))
+    nm3.add(ct)
+    z["nmap_coating"] = nm3
+    return z
+
+
+def _alpha_tex(seed, size=64):
+    """Roughness texture inside the range of the rough-transmittance tables."""
+    rng = np.random.RandomState(seed)
+    t = Plugin("texture", "bitmap", filterType="bilinear", gamma=1.0, uvscale=2.0)
+    t.data["bitmap"] = rng.uniform(0.08, 0.45, (size, size, 1)).astype(F)
+    return t
+
+
+def nextrow_scene(width=96, height=64, spp=4):
+    """Spheres and a knot carrying the nextrow materials over a diffuse floor, lit by an area light and an envmap."""
+    sc = Plugin("scene", "")
+    sc.add(Plugin("integrator", "path", maxDepth=6))
+    s = Plugin("sensor", "perspective", toWorld=hm.look_at([0, 4.0, 11], [0, 1.0, 0], [0, 1, 0]), fov=45.0)
+    s.add(Plugin("sampler", "independent", sampleCount=spp))
+    film = Plugin("film", "hdrfilm", width=width, height=height)
+    film.add(Plugin("rfilter", "gaussian"))
+    s.add(film)
+    sc.add(s)
+    z = nextrow_bsdfs()
+    floor = Plugin("shape", "rectangle", toWorld=hm.rotate([1, 0, 0], -90) @ hm.scale([12, 12, 1]))
+    floor.add(Plugin("bsdf", "diffuse", reflectance=Spectrum(0.5)))
+    sc.add(floor)
+    names = list(z)
+    for i, nm in enumerate(names):
+        col, row = i % 5, i // 5
+        sp = Plugin("shape", "sphere", center=Point((col - 2) * 2.3, 1.0, -2.6 * row), radius=1.0)
+        sp.add(z[nm])
+        sc.add(sp)
+    pos, idx, nrm, uv = scenes.torus_knot(40, 12)
+    knot = Plugin("shape", "mesh", toWorld=hm.translate([0, 0.9, 3.2]) @ hm.scale(0.6))
+    knot.data.update(positions=pos, indices=idx, normals=nrm, texcoords=uv)
+    knot.add(z["nmap_rp"])
+    sc.add(knot)
+    lt = Plugin("shape", "rectangle", toWorld=hm.translate([0, 8, 2]) @ hm.rotate([1, 0, 0], 90) @ hm.scale([1.5, 1.5, 1]))
+    lt.add(Plugin("emitter", "area", radiance=Spectrum(22, 20, 18)))
+    sc.add(lt)
+    env = Plugin("emitter", "envmap", scale=0.6)
+    env.data["bitmap"] = scenes.synthetic_envmap(128, 64)
+    sc.add(env)
+    return sc, z
+
+
 def twosided_scene(width=96, height=64, spp=4, hide_env=False):
     """Open surfaces seen and lit from both sides: free-standing rectangles carrying the twosided materials (front
     faces turned towards, away from and edge-on to the light), one plain one-sided rectangle for contrast."""
