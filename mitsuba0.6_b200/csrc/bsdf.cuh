@@ -151,55 +151,81 @@ DEVFN int wrapCoordFast(int x, int size, int mode) {
     if (mode == MTS_WRAP_REPEAT && (size & (size - 1)) == 0) return x & (size - 1);
     return wrapCoordOutside(x, size, mode);
 }
-// evalEWA on ONE level for one or two textures (tb == nullptr: one): the value(s) of the level
-template <bool PAIR>
-DEVFN void ewaWalk(const DTexture &ta, const DTexture *tb, int level, float2 uv, float A0, float B0, float C0, float3 &outA, float3 &outB) {
-    outB = f3(0.0f);
-    if (!isfinite(A0 + B0 + C0 + uv.x + uv.y)) { outA = f3(0.0f); return; }
-    if (level >= ta.levels) { outA = mipBox(ta, ta.levels - 1, uv); if (PAIR) outB = mipBox(*tb, tb->levels - 1, uv); return; }
-    const int w = ta.levelW[level], h = ta.levelH[level];
-    const float u = uv.x * w - 0.5f, v = uv.y * h - 0.5f;
-    const float ratioX = (float)w / (float)ta.width, ratioY = (float)h / (float)ta.height;   // m_sizeRatio
+// evalEWA on ONE level in three pieces -- the bounding box of the ellipse, one row of the box, the final division -- so
+// that the rows of a walk can be shared out among the lanes of a group (k_shade_ewa) or walked by one thread (ewaWalk).
+struct EwaLevel {
+    int kind;            // EWA_WALK, or the value is known without a walk: EWA_ZERO (non-finite input), EWA_BOX (beyond the pyramid), EWA_BILINEAR (empty box)
+    int w, h, u0, u1, v0, v1;
+    float u, v, As, Bs, Cs, ddq, uu0;
+};
+enum { EWA_WALK = 0, EWA_ZERO = 1, EWA_BOX = 2, EWA_BILINEAR = 3 };
+DEVFN EwaLevel ewaSetup(const DTexture &ta, int level, float2 uv, float A0, float B0, float C0) {
+    EwaLevel L;
+    L.kind = EWA_WALK; L.w = L.h = 1; L.u0 = L.v0 = 0; L.u1 = L.v1 = -1; L.u = L.v = L.As = L.Bs = L.Cs = L.ddq = L.uu0 = 0;
+    if (!isfinite(A0 + B0 + C0 + uv.x + uv.y)) { L.kind = EWA_ZERO; return L; }
+    if (level >= ta.levels) { L.kind = EWA_BOX; return L; }
+    L.w = ta.levelW[level]; L.h = ta.levelH[level];
+    L.u = uv.x * L.w - 0.5f; L.v = uv.y * L.h - 0.5f;
+    const float ratioX = (float)L.w / (float)ta.width, ratioY = (float)L.h / (float)ta.height;   // m_sizeRatio
     const float A = A0 / (ratioX * ratioX), B = B0 / (ratioX * ratioY), C = C0 / (ratioY * ratioY);
     const float invDet = 1.0f / (-B * B + 4.0f * A * C), deltaU = 2.0f * sqrtf(C * invDet), deltaV = 2.0f * sqrtf(A * invDet);
-    const int u0 = (int)ceilf(u - deltaU), u1 = floorToInt(u + deltaU), v0 = (int)ceilf(v - deltaV), v1 = floorToInt(v + deltaV);
-    const float As = A * MTS_MIPMAP_LUT_SIZE, Bs = B * MTS_MIPMAP_LUT_SIZE, Cs = C * MTS_MIPMAP_LUT_SIZE;
-    const float ddq = 2 * As, uu0 = (float)u0 - u;
+    L.u0 = (int)ceilf(L.u - deltaU); L.u1 = floorToInt(L.u + deltaU); L.v0 = (int)ceilf(L.v - deltaV); L.v1 = floorToInt(L.v + deltaV);
+    L.As = A * MTS_MIPMAP_LUT_SIZE; L.Bs = B * MTS_MIPMAP_LUT_SIZE; L.Cs = C * MTS_MIPMAP_LUT_SIZE;
+    L.ddq = 2 * L.As; L.uu0 = (float)L.u0 - L.u;
+    if (L.u1 < L.u0 || L.v1 < L.v0) L.kind = EWA_BILINEAR;   // no texel: denominator 0 -> evalBilinear (mipmap.h:829-830)
+    return L;
+}
+DEVFN int ewaRows(const EwaLevel &L) { return L.kind == EWA_WALK ? L.v1 - L.v0 + 1 : 0; }
+template <bool PAIR>
+DEVFN void ewaRow(const DTexture &ta, const DTexture *tb, int level, const EwaLevel &L, int vt, float3 &sumA, float3 &sumB, float &den) {
     const bool monoA = ta.channels == 1, monoB = PAIR ? tb->channels == 1 : false;
-    const __half *baseA = mipBase(ta, level), *baseB = PAIR ? mipBase(*tb, level) : nullptr;
-    float3 sumA = f3(0.0f), sumB = f3(0.0f);
-    float den = 0.0f;
-    for (int vt = v0; vt <= v1; ++vt) {
-        const float vv = (float)vt - v;
-        float q = __fadd_rn(__fmul_rn(__fmul_rn(As, uu0), uu0), __fmul_rn(__fadd_rn(__fmul_rn(Bs, uu0), __fmul_rn(Cs, vv)), vv));
-        float dq = __fadd_rn(__fmul_rn(As, __fadd_rn(__fmul_rn(2.0f, uu0), 1.0f)), __fmul_rn(Bs, vv));
-        const int ya = wrapCoordFast(vt, h, ta.wrapV);       // hoisted out of the column walk
-        const size_t off = (size_t)max(ya, 0) * w;
-        const __half *rowA = baseA + off * (monoA ? 1 : 4), *rowB = PAIR ? baseB + off * (monoB ? 1 : 4) : nullptr;
-        for (int ut = u0; ut <= u1; ++ut) {
-            if (q < (float)MTS_MIPMAP_LUT_SIZE) {
-                const uint32_t qi = (uint32_t)q;
-                if (qi < MTS_MIPMAP_LUT_SIZE) {
-                    const float weight = __ldg(ta.weightLut + (int)q);
-                    const int xa = wrapCoordFast(ut, w, ta.wrapU);
-                    float3 texA, texB = f3(0.0f);
-                    if (xa < 0) texA = texB = f3(xa == -2 ? 1.0f : 0.0f);          // EZero / EOne: u is tested first (evalTexel, mipmap.h:503-563)
-                    else if (ya < 0) texA = texB = f3(ya == -2 ? 1.0f : 0.0f);
-                    else { texA = texelAt(rowA, monoA ? 1 : 3, (size_t)xa); if (PAIR) texB = texelAt(rowB, monoB ? 1 : 3, (size_t)xa); }
-                    sumA += texA * weight;
-                    if (PAIR) sumB += texB * weight;
-                    den += weight;
-                }
+    const float vv = (float)vt - L.v;
+    float q = __fadd_rn(__fmul_rn(__fmul_rn(L.As, L.uu0), L.uu0), __fmul_rn(__fadd_rn(__fmul_rn(L.Bs, L.uu0), __fmul_rn(L.Cs, vv)), vv));
+    float dq = __fadd_rn(__fmul_rn(L.As, __fadd_rn(__fmul_rn(2.0f, L.uu0), 1.0f)), __fmul_rn(L.Bs, vv));
+    const int ya = wrapCoordFast(vt, L.h, ta.wrapV);       // hoisted out of the column walk
+    const size_t off = (size_t)max(ya, 0) * L.w;
+    const __half *rowA = mipBase(ta, level) + off * (monoA ? 1 : 4), *rowB = PAIR ? mipBase(*tb, level) + off * (monoB ? 1 : 4) : nullptr;
+    for (int ut = L.u0; ut <= L.u1; ++ut) {
+        if (q < (float)MTS_MIPMAP_LUT_SIZE) {
+            const uint32_t qi = (uint32_t)q;
+            if (qi < MTS_MIPMAP_LUT_SIZE) {
+                const float weight = __ldg(ta.weightLut + (int)q);
+                const int xa = wrapCoordFast(ut, L.w, ta.wrapU);
+                float3 texA, texB = f3(0.0f);
+                if (xa < 0) texA = texB = f3(xa == -2 ? 1.0f : 0.0f);          // EZero / EOne: u is tested first (evalTexel, mipmap.h:503-563)
+                else if (ya < 0) texA = texB = f3(ya == -2 ? 1.0f : 0.0f);
+                else { texA = texelAt(rowA, monoA ? 1 : 3, (size_t)xa); if (PAIR) texB = texelAt(rowB, monoB ? 1 : 3, (size_t)xa); }
+                sumA += texA * weight;
+                if (PAIR) sumB += texB * weight;
+                den += weight;
             }
-            q = __fadd_rn(q, dq);
-            dq = __fadd_rn(dq, ddq);
         }
+        q = __fadd_rn(q, dq);
+        dq = __fadd_rn(dq, L.ddq);
     }
-    if (den == 0) { outA = mipBilinear(ta, level, uv); if (PAIR) outB = mipBilinear(*tb, level, uv); return; }   // mipmap.h:829-830
+}
+template <bool PAIR>
+DEVFN void ewaFinish(const DTexture &ta, const DTexture *tb, int level, float2 uv, const EwaLevel &L, float3 sumA, float3 sumB, float den,
+                     float3 &outA, float3 &outB) {
+    outB = f3(0.0f);
+    if (L.kind == EWA_ZERO) { outA = f3(0.0f); return; }
+    if (L.kind == EWA_BOX) { outA = mipBox(ta, ta.levels - 1, uv); if (PAIR) outB = mipBox(*tb, tb->levels - 1, uv); return; }
+    if (L.kind == EWA_BILINEAR || den == 0) { outA = mipBilinear(ta, level, uv); if (PAIR) outB = mipBilinear(*tb, level, uv); return; }   // mipmap.h:829-830
     outA = sumA / den;
     if (PAIR) outB = sumB / den;
 }
-// kept out of line: one copy of each walk per kernel.  evalEWA(ilevel) * (1 - a) + evalEWA(ilevel + 1) * a, mipmap.h:712-713
+// one thread walks the whole level
+template <bool PAIR>
+DEVFN void ewaWalk(const DTexture &ta, const DTexture *tb, int level, float2 uv, float A0, float B0, float C0, float3 &outA, float3 &outB) {
+    const EwaLevel L = ewaSetup(ta, level, uv, A0, B0, C0);
+    float3 sumA = f3(0.0f), sumB = f3(0.0f);
+    float den = 0.0f;
+    if (L.kind == EWA_WALK) for (int vt = L.v0; vt <= L.v1; ++vt) ewaRow<PAIR>(ta, tb, level, L, vt, sumA, sumB, den);
+    ewaFinish<PAIR>(ta, tb, level, uv, L, sumA, sumB, den, outA, outB);
+}
+// kept out of line: one copy of each walk per kernel.  evalEWA(ilevel) * (1 - a) + evalEWA(ilevel + 1) * a, mipmap.h:712-713.
+// (Measured alternatives, both slower on B200 -- profiles/r2h, r2j: the rows of a walk dealt out to groups of 4 / 8 / 16 lanes,
+// and one flat loop over the accepted texels of both levels; the plain nested loops below compile to the tightest code.)
 static __device__ __noinline__ float3 mipEWA2(const DTexture &t, int ilevel, float2 uv, float A, float B, float C, float a) {
     float3 l0, l1, unused;
     ewaWalk<false>(t, nullptr, ilevel, uv, A, B, C, l0, unused);

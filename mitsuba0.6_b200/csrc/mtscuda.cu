@@ -108,7 +108,9 @@ struct MtsContext {
     cudaStream_t stream = nullptr, ownStream = nullptr;
     int numSMs = 148;
     bool deferEwa = true;      // staged shade: EWA texture walks as a kernel of their own (MTS_EWA_INLINE=1: inside k_shade_surface)
-    bool stagedShade = true;   // leaf class as k_shade_surface + k_shade_scatter (MTS_SHADE_FUSED=1 in the environment: one k_shade<SHADE_LEAF>)
+    bool leafTextured = false; // a leaf-class material of the built scene reads a bitmap texture
+    bool stagedShade = true;   // leaf class as k_shade_surface (+ k_shade_ewa) + k_shade_scatter; default: where its materials are textured
+                               // (MTS_SHADE_FUSED=1 / MTS_SHADE_STAGED=1 in the environment force one form)
     size_t l2Bytes = 0, l2WindowBytes = 0, maxWindow = 0; float l2HitRatio = 0;   // persisting-L2 set-up (0 = off)
     // staged scene
     MtsCamera cam; bool hasCam = false;
@@ -207,10 +209,11 @@ int ensureWavefront(MtsContext *c, uint32_t cap) {
     w.rec = nullptr;
     if (needRec)   // surface records of k_shade_surface -> k_shade_scatter
         CUDA_TRY(alloc((void **)&w.rec, sizeof(float4) * (size_t)kSurfRows * cap));
-    w.ewaJobs = nullptr; w.ewaC = nullptr;
+    w.ewaJobs = nullptr; w.ewaC = nullptr; w.ewaOrder = nullptr;
     if (needRec && c->deferEwa) {
         CUDA_TRY(alloc((void **)&w.ewaJobs, sizeof(float4) * 2 * (size_t)cap));
         CUDA_TRY(alloc((void **)&w.ewaC, sizeof(float) * (size_t)cap));
+        CUDA_TRY(alloc((void **)&w.ewaOrder, sizeof(uint32_t) * (size_t)cap));
     }
     CUDA_TRY(alloc((void **)&w.queue[0], 4 * (size_t)cap)); CUDA_TRY(alloc((void **)&w.queue[1], 4 * (size_t)cap));
     CUDA_TRY(alloc((void **)&w.doneQ, 4 * (size_t)cap));
@@ -894,6 +897,19 @@ static int buildOne(MtsContext *c) {
         for (int k = SHADE_CLASSES - 1; k >= 0; --k) c->classKey[k] = std::min(c->classKey[k], c->classKey[k + 1]);
         c->numKeys = (uint32_t)roots.size() + 1;
         for (auto &s : c->shapes) s.d.sortKey = keyOf[s.d.bsdf];
+        // Staged or fused shade of the leaf class?  Measured (profiles/r2e, r2m): the staged form wins by 2x where hits
+        // look up bitmap textures (the texture / MIP / EWA code is what outgrows the instruction caches), the fused,
+        // fully inlined kernel by 10-25 % where the materials are constants (no handover of surface records).
+        c->leafTextured = false;
+        for (int root : roots) {
+            if (shadeClassOf(c->nodes.data(), root) != SHADE_LEAF) continue;
+            std::vector<int> todo(1, root);
+            while (!todo.empty()) {
+                const MtsBsdfNode &n = c->nodes[todo.back()]; todo.pop_back();
+                if (n.t0.tex >= 0 || n.t1.tex >= 0 || n.t2.tex >= 0 || (n.type == MTS_BSDF_ROUGHDIELECTRIC && n.lut[0] >= 0)) c->leafTextured = true;
+                if (isWrapperBsdf(n.type) && n.type != MTS_BSDF_MIXTURE) for (int ch : n.child) if (ch >= 0) todo.push_back(ch);
+            }
+        }
     }
     std::vector<DShape> dshapes; for (auto &s : c->shapes) dshapes.push_back(s.d);
     if ((rc = devUpload(c, dshapes.data(), dshapes.size(), &S.shapes))) return rc;
@@ -1060,7 +1076,7 @@ static int renderOne(MtsContext *c, const MtsRenderParams *P, volatile const int
     cap = (uint32_t)std::min<unsigned long long>(std::max<unsigned long long>(totalItems, 32), cap);
     cap = (cap + 31u) & ~31u;
     int rc;
-    c->stagedShade = getenv("MTS_SHADE_FUSED") == nullptr;
+    c->stagedShade = getenv("MTS_SHADE_FUSED") ? false : getenv("MTS_SHADE_STAGED") ? true : c->leafTextured;
     c->deferEwa = getenv("MTS_EWA_INLINE") == nullptr;
     if ((rc = ensureWavefront(c, cap))) return rc;
     const Wavefront &Wf = c->wf;
@@ -1142,7 +1158,7 @@ static int renderOne(MtsContext *c, const MtsRenderParams *P, volatile const int
             if (Wf.classKey[SHADE_LEAF] < Wf.classKey[SHADE_LEAF + 1]) {
                 if (Wf.rec) {
                     launchSurface(S, Wf, R, cur, c->numSMs, st);
-                    if (Wf.ewaJobs && bounce == 0) { launchEwa(S, Wf, c->numSMs, st); ++launches; }   // only camera rays carry differentials (path.cpp:225)
+                    if (Wf.ewaJobs && bounce == 0) { launchEwa(S, Wf, c->numSMs, st); launches += 4; }   // only camera rays carry differentials (path.cpp:225)
                     launchScatter(S, Wf, R, cur, c->numSMs, st);
                     launches += 2;
                 }

@@ -25,7 +25,10 @@ void launchSurface(const DScene &S, const Wavefront &W, const RenderConst &R, in
 #elif SHADE_PART == 4
 
 void launchEwa(const DScene &S, const Wavefront &W, int numSMs, cudaStream_t st) {
-    k_shade_ewa<SHADE_CLASS><<<numSMs * 8, 256, 0, st>>>(S, W);
+    k_ewa_bin<<<numSMs * 8, 256, 0, st>>>(S, W);
+    k_ewa_offsets<<<1, 32, 0, st>>>(W);
+    k_ewa_scatter<<<numSMs * 8, 256, 0, st>>>(W);
+    k_shade_ewa<SHADE_CLASS><<<numSMs * EWA_MINB, 256, 0, st>>>(S, W);
 }
 
 #elif SHADE_PART == 3

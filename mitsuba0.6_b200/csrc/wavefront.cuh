@@ -18,6 +18,7 @@ struct Counters {
     uint32_t shadowCount;
     uint32_t doneCount;
     uint32_t ewaCount;      // deferred EWA texture walks of the current bounce (k_shade_surface -> k_shade_ewa)
+    uint32_t ewaBin[3 * 16]; // size-class histogram, offsets and cursors of the walks (kEwaBins each; all zero between uses)
     uint32_t cursor[2];     // next unclaimed ray of the intersect / shadow queue (persistent warps pull from these)
     unsigned long long missRays;                 // rays that escaped (sort key 0), total over all bounces
     unsigned long long normalRays, shadowRays;   // totals over all bounces ("Normal/Shadow rays traced", skdtree.cpp:46-47), kept on the device
@@ -36,6 +37,7 @@ struct Wavefront {
     float4 *rec;             // surface records of the staged shade kernels: kSurfRows rows of `capacity` float4, indexed by sorted-queue position
     float4 *ewaJobs;         // deferred EWA walks: 2 rows of `capacity` float4 (target / textures / level / lerp weight; uv, A, B) ...
     float *ewaC;             // ... and the ellipse coefficient C
+    uint32_t *ewaOrder;      // the walks ordered by size class
     uint32_t *queue[2];
     uint32_t *doneQ;
     // material sort of the active queue: key 0 = miss, DShape::sortKey otherwise (root BSDFs ordered by shade class)
@@ -592,47 +594,81 @@ static __global__ void __launch_bounds__(128, SURFACE_MINB) k_shade_surface(cons
     }
 }
 
-// The deferred EWA walks: one thread pair per lookup (even lane: pyramid level ilevel, odd lane: ilevel + 1), results
-// combined as evalEWA(ilevel) * (1 - a) + evalEWA(ilevel + 1) * a (mipmap.h:712-713), scaled (ScalingTexture) and stored
-// into the c0 / c1 rows of the surface record.
-template <int CLASS>
-static __global__ void __launch_bounds__(256) k_shade_ewa(const DScene S, const Wavefront W) {
+// The deferred EWA walks: one thread per lookup, both pyramid levels (evalEWA(ilevel) * (1 - a) + evalEWA(ilevel + 1) * a,
+// mipmap.h:712-713), scaled (ScalingTexture) and stored into the c0 / c1 rows of the surface record.  Footprints vary by
+// more than an order of magnitude between neighbouring paths (unsorted, a warp ran with 10 of 32 lanes busy), so the
+// lookups are first binned by the number of texels their two bounding boxes hold (k_ewa_bin: log2 bins, counting sort
+// like the material sort) and a warp walks 32 lookups of one size class.
+constexpr int kEwaBins = 16;
+#ifndef EWA_MINB
+#define EWA_MINB 4
+#endif
+DEVFN uint32_t ewaJobSize(const DScene &S, const float4 j0, const float4 j1, float C) {
+    const uint32_t tex = __float_as_uint(j0.y), li = __float_as_uint(j0.z);
+    const DTexture &ta = S.textures[tex & 0xffffu];
+    const int ilevel = (int)(li & 0xffu);
+    const EwaLevel L0 = ewaSetup(ta, ilevel, make_float2(j1.x, j1.y), j1.z, j1.w, C), L1 = ewaSetup(ta, ilevel + 1, make_float2(j1.x, j1.y), j1.z, j1.w, C);
+    return (uint32_t)(ewaRows(L0) * max(L0.u1 - L0.u0 + 1, 0) + ewaRows(L1) * max(L1.u1 - L1.u0 + 1, 0));
+}
+static __global__ void __launch_bounds__(256) k_ewa_bin(const DScene S, const Wavefront W) {
     const uint32_t count = W.ctr->ewaCount;
     const size_t cap = W.capacity;
-    const uint32_t rounded = (2u * count + 31u) & ~31u;
-    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < rounded; t += gridDim.x * blockDim.x) {
-        const uint32_t j = t >> 1, lvl = t & 1u;
-        const bool valid = j < count;
-        float3 va = f3(0.0f), vb = f3(0.0f);
-        float4 j0 = make_float4(0, 0, 0, 0);
-        if (valid) {
-            j0 = W.ewaJobs[j];
-            const float4 j1 = W.ewaJobs[cap + j];
-            const float C = W.ewaC[j];
-            const uint32_t tex = __float_as_uint(j0.y), li = __float_as_uint(j0.z);
-            const int texA = (int)(tex & 0xffffu), texB = (int)(tex >> 16), level = (int)(li & 0xffu) + (int)lvl;
-            if (texB != 0xffff) ewaWalk<true>(S.textures[texA], &S.textures[texB], level, make_float2(j1.x, j1.y), j1.z, j1.w, C, va, vb);
-            else ewaWalk<false>(S.textures[texA], nullptr, level, make_float2(j1.x, j1.y), j1.z, j1.w, C, va, vb);
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < ((count + 31u) & ~31u); j += gridDim.x * blockDim.x) {
+        uint32_t key = kNoKey;
+        if (j < count) {
+            const uint32_t taps = ewaJobSize(S, W.ewaJobs[j], W.ewaJobs[cap + j], W.ewaC[j]);
+            key = min((uint32_t)kEwaBins - 1u, 32u - (uint32_t)__clz(taps));   // 0 taps -> bin 0, else 1 + floor(log2)
+            W.keys[j] = key;    // (the material sort is done with `keys` by the time the shade kernels run)
         }
-        // the odd lane hands its level to the even lane
-        const float3 oa = f3(__shfl_down_sync(0xffffffffu, va.x, 1), __shfl_down_sync(0xffffffffu, va.y, 1), __shfl_down_sync(0xffffffffu, va.z, 1));
-        const float3 ob = f3(__shfl_down_sync(0xffffffffu, vb.x, 1), __shfl_down_sync(0xffffffffu, vb.y, 1), __shfl_down_sync(0xffffffffu, vb.z, 1));
-        if (valid && lvl == 0) {
-            const float a = j0.w;
-            const uint32_t pos = __float_as_uint(j0.x), tex = __float_as_uint(j0.y), slotA = (__float_as_uint(j0.z) >> 8) & 1u;
-            float4 *r = W.rec + pos;
-            const MtsBsdfNode &n = S.nodes[__float_as_uint(r[0].w) & SR_NODE_MASK];
-            const MtsTexRef &ra = slotA ? n.t1 : n.t0;
-            const float3 ca = (va * (1.0f - a) + oa * a) * f3(ra.scale[0], ra.scale[1], ra.scale[2]);
-            float4 *rowA = r + (4 + slotA) * cap;
-            float4 cur = *rowA;
-            *rowA = make_float4(ca.x, ca.y, ca.z, cur.w);
-            if ((tex >> 16) != 0xffffu) {
-                const float3 cb = (vb * (1.0f - a) + ob * a) * f3(n.t1.scale[0], n.t1.scale[1], n.t1.scale[2]);
-                float4 *rowB = r + 5 * cap;
-                cur = *rowB;
-                *rowB = make_float4(cb.x, cb.y, cb.z, cur.w);
-            }
+        keyedAppend(W.ctr->ewaBin, key);
+    }
+}
+static __global__ void k_ewa_offsets(const Wavefront W) {   // one warp: exclusive scan of the kEwaBins counts
+    uint32_t *cnt = W.ctr->ewaBin, *off = cnt + kEwaBins, *cur = cnt + 2 * kEwaBins;
+    const uint32_t k = threadIdx.x;
+    uint32_t v = k < kEwaBins ? cnt[k] : 0, incl = v;
+    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if ((int)threadIdx.x >= o) incl += t; }
+    if (k < kEwaBins) { off[k] = incl - v; cur[k] = 0; cnt[k] = 0; }
+}
+static __global__ void __launch_bounds__(256) k_ewa_scatter(const Wavefront W) {
+    const uint32_t count = W.ctr->ewaCount;
+    const uint32_t *off = W.ctr->ewaBin + kEwaBins;
+    uint32_t *cur = W.ctr->ewaBin + 2 * kEwaBins;
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < ((count + 31u) & ~31u); j += gridDim.x * blockDim.x) {
+        const uint32_t key = j < count ? W.keys[j] : kNoKey;
+        const uint32_t pos = keyedAppend(cur, key);
+        // largest size class first: the long walks start while the machine is full
+        if (key != kNoKey) W.ewaOrder[count - 1u - (off[key] + pos)] = j;
+    }
+}
+template <int CLASS>
+static __global__ void __launch_bounds__(256, EWA_MINB) k_shade_ewa(const DScene S, const Wavefront W) {
+    const uint32_t count = W.ctr->ewaCount;
+    const size_t cap = W.capacity;
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < count; t += gridDim.x * blockDim.x) {
+        const uint32_t j = W.ewaOrder[t];
+        const float4 j0 = W.ewaJobs[j], j1 = W.ewaJobs[cap + j];
+        const float C = W.ewaC[j], a = j0.w;
+        const uint32_t tex = __float_as_uint(j0.y), li = __float_as_uint(j0.z);
+        const int texA = (int)(tex & 0xffffu), texB = (int)(tex >> 16), ilevel = (int)(li & 0xffu);
+        const bool pair = texB != 0xffff;
+        const float2 uv = make_float2(j1.x, j1.y);
+        float3 va, vb = f3(0.0f);
+        if (pair) mipEWA2Pair(S.textures[texA], S.textures[texB], ilevel, uv, j1.z, j1.w, C, a, va, vb);
+        else va = mipEWA2(S.textures[texA], ilevel, uv, j1.z, j1.w, C, a);
+        const uint32_t pos = __float_as_uint(j0.x), slotA = (li >> 8) & 1u;
+        float4 *r = W.rec + pos;
+        const MtsBsdfNode &n = S.nodes[__float_as_uint(r[0].w) & SR_NODE_MASK];
+        const MtsTexRef &ra = slotA ? n.t1 : n.t0;
+        const float3 ca = va * f3(ra.scale[0], ra.scale[1], ra.scale[2]);
+        float4 *rowA = r + (4 + slotA) * cap;
+        float4 cur = *rowA;
+        *rowA = make_float4(ca.x, ca.y, ca.z, cur.w);
+        if (pair) {
+            const float3 cb = vb * f3(n.t1.scale[0], n.t1.scale[1], n.t1.scale[2]);
+            float4 *rowB = r + 5 * cap;
+            cur = *rowB;
+            *rowB = make_float4(cb.x, cb.y, cb.z, cur.w);
         }
     }
 }

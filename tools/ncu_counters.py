@@ -49,10 +49,11 @@ def main():
         kind = "intersect" if "k_intersect" in name else "shadow" if "k_shadow" in name else "miss" if "k_shade_miss" in name else "shade" if "k_shade" in name else None
         if kind is None:
             continue
-        cls = re.search(r"k_shade<\(?(?:\w+::)*\w*\)?(\d)>", name) if kind == "shade" else None
-        sub = kind + (cls.group(1) if cls else "")      # one k_shade instance per shade class and bounce
-        n = seen.get(sub, 0)
-        seen[sub] = n + 1
+        cls = re.search(r"(k_shade\w*)<\(?(?:\w+::)*\w*\)?(\d)>", name) if kind == "shade" else None
+        sub = kind + (cls.group(2) if cls else "")      # one k_shade instance per shade class and bounce ...
+        stage = cls.group(1) + cls.group(2) if cls else sub   # ... or, staged, k_shade_surface / k_shade_ewa / k_shade_scatter
+        n = seen.get(stage, 0)
+        seen[stage] = n + 1
         if n >= len(bounces):
             continue
         units = bounces[n].get(sub, bounces[n][kind])
@@ -72,7 +73,7 @@ def main():
 
         t_unit = rows[1][h.index("gpu__time_duration.sum")] if "gpu__time_duration.sum" in h else "ms"
         t_ms = f("gpu__time_duration.sum") * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(t_unit, 1.0)
-        e = {"kernel": name[:60], "sub": sub, "bounce": n, "units": units, "ms_under_ncu": t_ms,
+        e = {"kernel": name[:60], "sub": sub, "stage": stage, "bounce": n, "units": units, "ms_under_ncu": t_ms,
              "dram_bytes": in_bytes("dram__bytes_read.sum") + in_bytes("dram__bytes_write.sum"),
              "warp_inst": f("smsp__inst_executed.sum"), "lanes_per_inst": f("smsp__thread_inst_executed_per_inst_executed.ratio"),
              "issue_active_pct": f("smsp__issue_active.avg.pct_of_peak_sustained_active"),
@@ -92,7 +93,7 @@ def main():
             for c in ("shade0", "shade1", "shade2"):
                 lc = [e for e in ls if e["sub"] == c]
                 if lc:
-                    uc = sum(e["units"] for e in lc)
+                    uc = sum(bounces[b].get(c, 0) for b in sorted({e["bounce"] for e in lc}))   # staged kernels share the paths of a bounce
                     res["k_" + c] = {"dram_bytes_per_unit": sum(e["dram_bytes"] for e in lc) / uc, "warp_inst_per_unit": sum(e["warp_inst"] for e in lc) / uc,
                                      "ms_under_ncu": sum(e["ms_under_ncu"] for e in lc), "units_covered": uc, "registers": lc[0]["registers"],
                                      "stall_no_instruction": max(e["stall_no_instruction"] for e in lc), "warps_active_pct": lc[0]["warps_active_pct"]}
