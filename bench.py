@@ -37,6 +37,8 @@ WORKLOADS = {
                 "configs[0]: Cornell box 512x512, 64 spp, maxDepth 5, box rfilter"),
     "caustics": ("caustic_scene", dict(width=1024, height=1024, spp=512, max_depth=16),
                  "configs[3]: blendbsdf + conductor + dielectric caustic scene, 1024x1024, 512 spp, maxDepth 16"),
+    "terrain4k": ("terrain_scene", dict(width=3840, height=2160, spp=1024, max_depth=16),
+                  "configs[4]: the cfg3 scene at 3840x2160, 1024 spp, maxDepth 16 (sample-split over the ranks, NCCL film reduce)"),
     # reduced variant for quick functional checks of this script (NOT a bench configuration)
     "terrain_small": ("terrain_scene", dict(width=480, height=270, spp=8, max_depth=8, grid=300, tex_size=512),
                       "debug: 180k-triangle terrain"),
@@ -182,9 +184,9 @@ def measured_peak():
 RAY_IN, HIT_OUT, SHADOW_OUT, PRIM_BYTES = 32, 16, 4, 48
 
 
-REF_SPP = {"terrain": 8, "spheres": 16, "cornell": 64, "caustics": 16, "terrain_small": 8}   # bounded CPU samples (reference arm, per step)
+REF_SPP = {"terrain": 8, "terrain4k": 4, "spheres": 16, "cornell": 64, "caustics": 16, "terrain_small": 8}   # bounded CPU samples (reference arm, per step)
 # the cpu_baseline leg of the CUDA arm also supplies the reference IMAGE of the relMSE figure: one render, more samples
-REF_SPP_IMAGE = {"terrain": 32, "spheres": 32, "cornell": 64, "caustics": 32, "terrain_small": 16}
+REF_SPP_IMAGE = {"terrain": 32, "terrain4k": 8, "spheres": 32, "cornell": 64, "caustics": 32, "terrain_small": 16}
 
 
 def reference_built():
@@ -317,6 +319,8 @@ def kernel_counters():
     return {}
 
 
+B_HANDOVER = 320   # staged shade (scenes whose leaf materials read bitmaps): one 160-byte surface record written by
+                   # k_shade_surface and read by k_shade_scatter per hit
 B_SHADE = 436   # algorithmic bytes of one shaded surface hit (ray 32 + hit 16 + state 48 + geometry 108 +
                 # material 64 + texels 32(+32 bump) + next ray 32 + shadow ray 48 + state 48 + queue indices 8)
 
@@ -480,6 +484,8 @@ def run_cuda(args):
         g3.close()
         b_ray = RAY_IN + HIT_OUT + node_bytes * nodes_per_ray + PRIM_BYTES * prims_per_ray
         b_sray = RAY_IN + SHADOW_OUT + node_bytes * nodes_per_sray + PRIM_BYTES * prims_per_sray
+        staged = any(r.tex >= 0 for n in flat.nodes for r in (n.t0, n.t1, n.t2))     # what mtscuda_build decides (leafTextured)
+        b_shade = B_SHADE + (B_HANDOVER if staged else 0)
         # this rank's own kernel times (CUDA events around every launch on the launching stream)
         times = {k: acc[k] for k in ("intersect_ms", "shade_ms", "shadow_ms", "splat_ms", "raygen_ms", "sort_ms", "miss_ms")}
         peak, peak_src = measured_peak()
@@ -487,7 +493,7 @@ def run_cuda(args):
         sm_mhz = (clk or {}).get("sm_mhz")
         rl = {
             "k_intersect": kernel_roofline("k_intersect", acc["normal_rays"], acc["intersect_ms"], acc["intersect_launches"], b_ray, peak, peak_src, sm_mhz, num_sms, kc),
-            "k_shade": kernel_roofline("k_shade", acc["shaded_paths"], acc["shade_ms"], acc["shade_launches"], B_SHADE, peak, peak_src, sm_mhz, num_sms, kc),
+            "k_shade": kernel_roofline("k_shade", acc["shaded_paths"], acc["shade_ms"], acc["shade_launches"], b_shade, peak, peak_src, sm_mhz, num_sms, kc),
             "k_shadow": kernel_roofline("k_shadow", acc["shadow_rays"], acc["shadow_ms"], acc["shadow_launches"], b_sray, peak, peak_src, sm_mhz, num_sms, kc),
         }
         rl["k_intersect"].update(nodes_per_ray=nodes_per_ray, prims_per_ray=prims_per_ray)
@@ -499,7 +505,7 @@ def run_cuda(args):
         roofline["other_kernels"] = {k: v for k, v in rl.items() if k != dominant}
         # whole pipeline, SURVEY 8(d): (rays x B_ray + shadow rays x B_sray + shaded hits x B_shade + samples x B_film) / time
         b_film = 24 + 32 * (1 if flat.film.filter_radius < 1 else 16)
-        pipe_bytes = acc["normal_rays"] * b_ray + acc["shadow_rays"] * b_sray + acc["shaded_paths"] * B_SHADE + acc["camera_samples"] * b_film
+        pipe_bytes = acc["normal_rays"] * b_ray + acc["shadow_rays"] * b_sray + acc["shaded_paths"] * b_shade + acc["camera_samples"] * b_film
         roofline["pipeline"] = {"bytes_per_sample": pipe_bytes / max(acc["camera_samples"], 1),
                                 "achieved": pipe_bytes / (acc["render_ms"] / 1e3) / 1e9, "frac": pipe_bytes / (acc["render_ms"] / 1e3) / 1e9 / peak}
         line = {"metric": "Msamples/s", "value": msamples, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,

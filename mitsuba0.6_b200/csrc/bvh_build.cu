@@ -451,8 +451,10 @@ __device__ __forceinline__ PrimRecord makePrimRecord(const PrimSource &s, const 
         float3 v1 = make_float3(pos[3 * (size_t)i1], pos[3 * (size_t)i1 + 1], pos[3 * (size_t)i1 + 2]);
         float3 v2 = make_float3(pos[3 * (size_t)i2], pos[3 * (size_t)i2 + 1], pos[3 * (size_t)i2 + 2]);
         r.p0 = make_float4(v0.x, v0.y, v0.z, __int_as_float(s.shape));
-        r.p1 = make_float4(v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, __int_as_float((int)s.prim));
-        r.p2 = make_float4(v2.x - v0.x, v2.y - v0.y, v2.z - v0.z, __int_as_float(0));
+        // the three vertices themselves (not v0 + edges): neighbouring triangles then hold bit-identical copies of their
+        // shared vertices, which is what makes the edge tests of primIntersect watertight
+        r.p1 = make_float4(v1.x, v1.y, v1.z, __int_as_float((int)s.prim));
+        r.p2 = make_float4(v2.x, v2.y, v2.z, __int_as_float(0));
     } else {
         r.p0 = make_float4(0, 0, 0, __int_as_float(s.shape));
         r.p1 = make_float4(0, 0, 0, __int_as_float(0));

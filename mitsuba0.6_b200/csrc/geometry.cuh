@@ -33,27 +33,52 @@ DEVFN bool sphereIntersect(const DShape &s, float3 o, float3 d, float mint, floa
     return true;
 }
 
-// One primitive of a leaf.  Triangles use the Moeller-Trumbore test on the 48-byte (v0,e1,e2)
-// record (the reference's TriAccel is the same 48 bytes, include/mitsuba/render/triaccel.h:37-51);
-// u,v are the barycentrics of v1,v2 exactly as TriAccel::rayIntersect returns them.
-DEVFN bool primIntersect(const DScene &S, int slot, float3 o, float3 d, float mint, float maxt, RayHit &h) {
+// Per-ray constants of the watertight triangle test (Woop, Benthin, Wald 2013): the permutation that makes z the dominant
+// axis of the direction, and the shear that maps the direction onto +z.
+struct RayShear { int kx, ky, kz; float Sx, Sy, Sz; };
+DEVFN float comp3(float3 v, int a) { return a == 0 ? v.x : a == 1 ? v.y : v.z; }
+DEVFN RayShear rayShear(float3 d) {
+    RayShear r;
+    const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    r.kz = (ax > ay && ax > az) ? 0 : (ay > az ? 1 : 2);
+    r.kx = r.kz == 2 ? 0 : r.kz + 1; r.ky = r.kx == 2 ? 0 : r.kx + 1;
+    const float dz = comp3(d, r.kz);
+    if (dz < 0.0f) { const int t = r.kx; r.kx = r.ky; r.ky = t; }   // preserve the winding
+    r.Sz = 1.0f / dz; r.Sx = comp3(d, r.kx) * r.Sz; r.Sy = comp3(d, r.ky) * r.Sz;
+    return r;
+}
+// One primitive of a leaf.  Triangles: the 48-byte record holds the three vertices (the reference's TriAccel is the same
+// 48 bytes, include/mitsuba/render/triaccel.h:37-51); the test is the watertight one -- the scaled barycentrics U, V, W
+// are 2-D edge functions of the sheared vertices, each computed from two vertices only and with separately rounded
+// products, so the two triangles that share an edge get the exact negative of each other's value and a ray can never
+// slip between them.  (The Moeller-Trumbore test used in round 1 leaked 6e-5 of the camera rays through the
+// 9,999,392-triangle terrain: found by tests/test_gpu_fullsize.py against the reference's kd-tree.)  u, v are the
+// barycentrics of v1, v2 exactly as TriAccel::rayIntersect returns them.
+DEVFN bool primIntersect(const DScene &S, int slot, float3 o, float3 d, const RayShear &rs, float mint, float maxt, RayHit &h) {
     const float4 *rec = reinterpret_cast<const float4 *>(S.prims + slot);
     float4 p0 = __ldg(rec), p1 = __ldg(rec + 1), p2 = __ldg(rec + 2);
     int type = __float_as_int(p2.w);
     if (type == 0) {
-        float3 e1 = f3(p1), e2 = f3(p2);
-        float3 pv = cross(d, e2);
-        float det = dot(e1, pv);
+        const float3 A = f3(p0) - o, B = f3(p1) - o, C = f3(p2) - o;
+        const float Akz = comp3(A, rs.kz), Bkz = comp3(B, rs.kz), Ckz = comp3(C, rs.kz);
+        const float Ax = comp3(A, rs.kx) - rs.Sx * Akz, Ay = comp3(A, rs.ky) - rs.Sy * Akz;
+        const float Bx = comp3(B, rs.kx) - rs.Sx * Bkz, By = comp3(B, rs.ky) - rs.Sy * Bkz;
+        const float Cx = comp3(C, rs.kx) - rs.Sx * Ckz, Cy = comp3(C, rs.ky) - rs.Sy * Ckz;
+        float U = __fsub_rn(__fmul_rn(Cx, By), __fmul_rn(Cy, Bx));
+        float V = __fsub_rn(__fmul_rn(Ax, Cy), __fmul_rn(Ay, Cx));
+        float W = __fsub_rn(__fmul_rn(Bx, Ay), __fmul_rn(By, Ax));
+        if (U == 0.0f || V == 0.0f || W == 0.0f) {   // on an edge in fp32: decide in double
+            U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+            V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+            W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+        }
+        if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
+        const float det = U + V + W;
         if (det == 0.0f) return false;
-        float inv = 1.0f / det;
-        float3 tv = o - f3(p0);
-        float u = dot(tv, pv) * inv;
-        float3 qv = cross(tv, e1);
-        float v = dot(d, qv) * inv;
-        float t = dot(e2, qv) * inv;
-        if (!(u >= 0.0f && v >= 0.0f && u + v <= 1.0f)) return false;
-        if (t < mint || t > maxt) return false;
-        h.t = t; h.u = u; h.v = v; h.prim = slot;
+        const float inv = 1.0f / det;
+        const float t = (U * (rs.Sz * Akz) + V * (rs.Sz * Bkz) + W * (rs.Sz * Ckz)) * inv;
+        if (!(t >= mint && t <= maxt)) return false;
+        h.t = t; h.u = V * inv; h.v = W * inv; h.prim = slot;
         return true;
     }
     const DShape &s = S.shapes[__float_as_int(p0.w)];
@@ -160,6 +185,9 @@ constexpr int kNodeIters = NODE_ITERS;
 // per-thread local array.  A purely local stack costs one 32-byte sector per LANE per push/pop (the lanes of a warp
 // sit at different depths), which made the stack more than half of the trace kernels' L1 traffic
 // (profiles/r1e_ncu_full_raw.txt: 1.6 useful bytes per local sector).
+#ifndef TRACE_SMEM_NODES
+#define TRACE_SMEM_NODES 0
+#endif
 #ifndef TRACE_SMEM_STACK
 #define TRACE_SMEM_STACK 10
 #endif
@@ -178,6 +206,7 @@ struct Traversal {
     uint2 ngroup;
     int sp;
     uint32_t smBase;                               // shared-memory address of this thread's stack column (SH > 0)
+    const float4 *topNodes = nullptr;              // per-CTA shared-memory copy of the top of the tree (TRACE_SMEM_NODES > 0)
     uint2 stack[kStackCapacity - SH];
 
     DEVFN void push(uint2 v) {
@@ -221,10 +250,22 @@ struct Traversal {
             const uint32_t rel = __popc(ngroup.y & 0xffu & ~(0xffffffffu << slot));
             const uint32_t nodeIdx = ngroup.x + rel;
             if ((ngroup.y & 0xff000000u) && sp < kStackCapacity) push(ngroup);
-            const float4 *np = reinterpret_cast<const float4 *>(S.bvh + nodeIdx);
-            const float4 n0 = __ldg(np);
-            const uint4 n1 = __ldg(reinterpret_cast<const uint4 *>(np + 1)), n2 = __ldg(reinterpret_cast<const uint4 *>(np + 2)),
-                        n3 = __ldg(reinterpret_cast<const uint4 *>(np + 3)), n4 = __ldg(reinterpret_cast<const uint4 *>(np + 4));
+            float4 n0; uint4 n1, n2, n3, n4;
+#if TRACE_SMEM_NODES > 0
+            // experiment (north_star: "BVH nodes staged through shared memory"): the first TRACE_SMEM_NODES nodes -- the top
+            // levels, stored breadth first -- are read from a per-CTA copy in shared memory.  Measured: no gain, see DESIGN 4.
+            if (nodeIdx < (uint32_t)TRACE_SMEM_NODES && topNodes) {
+                const float4 *sp4 = topNodes + 5 * nodeIdx;
+                n0 = sp4[0]; n1 = *reinterpret_cast<const uint4 *>(sp4 + 1); n2 = *reinterpret_cast<const uint4 *>(sp4 + 2);
+                n3 = *reinterpret_cast<const uint4 *>(sp4 + 3); n4 = *reinterpret_cast<const uint4 *>(sp4 + 4);
+            } else
+#endif
+            {
+                const float4 *np = reinterpret_cast<const float4 *>(S.bvh + nodeIdx);
+                n0 = __ldg(np);
+                n1 = __ldg(reinterpret_cast<const uint4 *>(np + 1)); n2 = __ldg(reinterpret_cast<const uint4 *>(np + 2));
+                n3 = __ldg(reinterpret_cast<const uint4 *>(np + 3)); n4 = __ldg(reinterpret_cast<const uint4 *>(np + 4));
+            }
             if (COUNT) ctr->nodes++;
             const uint32_t hits = wideNodeHits(n0, n1, n2, n3, n4, o, idir, oct, mint, best.t);
             ngroup = make_uint2(n1.x, (hits & 0xff000000u) | ((uint32_t)__float_as_int(n0.w) >> 24));
@@ -235,12 +276,13 @@ struct Traversal {
                 ngroup = pop();
             }
         }
+        const RayShear rs = rayShear(d);   // recomputed per leaf batch (a few instructions) rather than held in registers across node visits
         while (pending) {
             const int j = __ffs((int)pending) - 1;
             pending &= pending - 1;
             if (COUNT) ctr->prims++;
             RayHit h;
-            if (primIntersect(S, (int)(primBase + j), o, d, mint, best.t, h)) {
+            if (primIntersect(S, (int)(primBase + j), o, d, rs, mint, best.t, h)) {
                 if (ANY) { best = h; return true; }
                 if (h.t < best.t || best.prim < 0) best = h;
             }

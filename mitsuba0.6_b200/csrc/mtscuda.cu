@@ -924,7 +924,7 @@ static int buildOne(MtsContext *c) {
     if (bout.depth > kStackCapacity)   // the traversal stack holds one node group per level; deeper trees would drop siblings
         return fail(MTS_EINVAL, "BVH is " + std::to_string(bout.depth) + " wide levels deep, more than the " + std::to_string(kStackCapacity) +
                     "-entry traversal stack holds (degenerate geometry, e.g. a long chain of nested slivers)");
-    S.bvh = bout.nodes; S.prims = bout.prims; S.numPrims = bin.numPrims;
+    S.bvh = bout.nodes; S.prims = bout.prims; S.numPrims = bin.numPrims; S.numNodesBvh = (int)bout.numNodes;
     if (c->l2Bytes && bout.numNodes > 0) {
         // nodes are stored level by level (breadth first), so a prefix window covers the top of the tree
         c->l2WindowBytes = std::min<size_t>(sizeof(WideNode) * (size_t)bout.numNodes, c->maxWindow);

@@ -75,7 +75,7 @@ struct WideNode {
 };
 
 // 48-byte primitive record in leaf order.
-//   triangle: p0 = (v0, shape), p1 = (e1 = v1-v0, prim index), p2 = (e2 = v2-v0, 0)
+//   triangle: p0 = (v0, shape), p1 = (v1, prim index), p2 = (v2, 0)
 //   analytic: p0.w = shape, p2.w = 1 (rectangle) / 2 (sphere)
 struct PrimRecord { float4 p0, p1, p2; };
 
@@ -98,7 +98,7 @@ struct DScene : Mats {
     const uint32_t *indices;  // 3 / triangle, already offset into the global vertex arrays
     const float *tangents;    // 6 floats / triangle
     const float *areaCdfs;
-    const WideNode *bvh; const PrimRecord *prims; int numPrims;
+    const WideNode *bvh; const PrimRecord *prims; int numPrims, numNodesBvh;
     // emitters
     const DEmitter *emitters; const float *emitterCdf; int numEmitters;
     DEnvmap env; int hasEnv;

@@ -178,6 +178,16 @@ DEVFN void traceQueue(const DScene &S, uint32_t count, uint32_t *cursor, TraceCo
     __shared__ uint2 sstack[kSmemStack > 0 ? kSmemStack * kTraceBlock : 1];
     Traversal<ANY, COUNT, kSmemStack> tr;
     tr.smBase = (uint32_t)__cvta_generic_to_shared(&sstack[threadIdx.x]);
+#if TRACE_SMEM_NODES > 0
+    __shared__ float4 stop[5 * TRACE_SMEM_NODES];
+    {
+        const uint32_t nTop = min((uint32_t)TRACE_SMEM_NODES, (uint32_t)S.numNodesBvh);
+        const float4 *src = reinterpret_cast<const float4 *>(S.bvh);
+        for (uint32_t k = threadIdx.x; k < 5 * nTop; k += blockDim.x) stop[k] = __ldg(src + k);
+        __syncthreads();
+        tr.topNodes = nTop == (uint32_t)TRACE_SMEM_NODES ? stop : nullptr;
+    }
+#endif
     uint32_t item = 0;
     bool busy = false, exhausted = false;
     while (true) {

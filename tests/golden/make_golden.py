@@ -137,6 +137,17 @@ def nextrow():
     return out
 
 
+def fullsize():
+    """fullsize.npz: closest hits of the reference's kd-tree on the full 9,999,392-triangle cfg3 terrain (fallback fixture of
+    tests/test_gpu_fullsize.py, which asks oracle/_ref directly where it is present)."""
+    rs = mtsref.RefScene(G.fullsize_scene())
+    rays = G.fullsize_rays(G.N_FULLSIZE_GOLDEN, rs.sample_rays)
+    h, ids = rs.trace(rays)
+    prim = np.where(np.isfinite(h[:, 0]), ids[:, 1], -1).astype(np.int32)
+    print("fullsize: %d rays, %.1f %% hit, kd-tree build %.1f s" % (len(rays), 100 * np.isfinite(h[:, 0]).mean(), rs.kd_build_s), flush=True)
+    return {"trace/t": h[:, 0].copy(), "trace/shape": ids[:, 0].astype(np.int8), "trace/prim": prim}
+
+
 def boundary():
     """boundary.npz: crop window, sphere transform composition and the alpha channel, rendered by the reference."""
     out = {}
@@ -215,6 +226,11 @@ if __name__ == "__main__":
         t = boundary()
         np.savez_compressed(os.path.join(HERE, "boundary.npz"), **t)
         print("boundary.npz: %d arrays" % len(t))
+        raise SystemExit(0)
+    if "--fullsize" in sys.argv:
+        t = fullsize()
+        np.savez_compressed(os.path.join(HERE, "fullsize.npz"), **t)
+        print("fullsize.npz: %d arrays" % len(t))
         raise SystemExit(0)
     if "--nextrow" in sys.argv:
         t = nextrow()

@@ -70,6 +70,41 @@ def check_bsdf(ctx, flat, z, name, gold, inputs=None):
     return worst
 
 
+def compare_trace(rays, got, ref, perturb_trace, max_mismatch=1e-3, jitter=1e-4, dump=None):
+    """Hit/miss + shape id + primitive id of `got` = (hits, ids) against `ref` = (t, ids): identical except for ties (both hit
+    at the same distance) and grazing rays (the checker `perturb_trace(rays) -> ids` changes its own answer under a 1e-4
+    perturbation of the direction -- `jitter`, to be chosen well below the angular size of a primitive).  Returns (mismatches,
+    excused as ties, excused as grazing)."""
+    h, ids = got
+    rt, rids = ref
+    hit_g, hit_r = np.isfinite(h[:, 0]), np.isfinite(rt)
+    same = (hit_g == hit_r) & (ids == rids).all(axis=1)
+    bad = np.nonzero(~same)[0]
+    assert len(bad) / len(rays) < max_mismatch, "hit/prim-id mismatch on %d of %d rays" % (len(bad), len(rays))
+    n_tie = n_graze = 0
+    if len(bad):
+        tie = hit_g[bad] & hit_r[bad] & (np.abs(h[bad, 0] - rt[bad]) <= 1e-4 * np.maximum(1, rt[bad]))
+        n_tie = int(tie.sum())
+        rest = bad[~tie]
+        if len(rest):
+            assert perturb_trace is not None, ("non-tie intersection mismatch", rays[rest][:3], ids[rest][:3], rids[rest][:3])
+            excused = np.zeros(len(rest), dtype=bool)
+            jr = np.random.RandomState(11)
+            for _ in range(16):
+                jit = rays[rest].copy()
+                jit[:, 4:7] += jr.normal(scale=jitter, size=(len(rest), 3)).astype(F)
+                jit[:, 4:7] /= np.linalg.norm(jit[:, 4:7], axis=1, keepdims=True)
+                excused |= (perturb_trace(jit) == ids[rest]).all(axis=1)
+            if dump is not None and not excused.all():
+                np.savez(dump, rays=rays[rest[~excused]], got_ids=ids[rest[~excused]], ref_ids=rids[rest[~excused]], got_t=h[rest[~excused], 0],
+                         ref_t=rt[rest[~excused]], n_bad=len(bad), n_tie=n_tie, n_rest=len(rest))
+            assert excused.all(), ("non-grazing intersection mismatch", rays[rest[~excused]][:3], ids[rest[~excused]][:3], rids[rest[~excused]][:3])
+            n_graze = int(excused.sum())
+    ok = same & hit_g
+    assert np.all(np.abs(h[ok, 0] - rt[ok]) <= 1e-4 * np.maximum(1, rt[ok]))
+    return len(bad), n_tie, n_graze
+
+
 def check_trace(ctx, gold, oracle_ctx=None):
     rays = G.trace_rays()
     h, ids = ctx.trace(rays)

@@ -165,6 +165,32 @@ BOUNDARY_IMAGE_SCENES = {
 }
 
 
+# ---- the full-size cfg3 geometry (9,999,392 triangles): closest-hit parity on the BVH that carries the headline number --------
+N_FULLSIZE_LIVE, N_FULLSIZE_GOLDEN = 1 << 20, 1 << 17
+
+
+def fullsize_scene():
+    """terrain_scene at BASELINE.json's full triangle count; small textures (the test traces rays, it does not shade)."""
+    return scenes.terrain_scene(1920, 1080, 1, grid=2237, tex_size=64, env_size=(64, 32))
+
+
+def fullsize_rays(n, camera_rays):
+    """Half camera rays (`camera_rays(film positions) -> (n, 16)` rows o, d as sample_rays returns them), half random chords
+    through the terrain's bounding volume and rays leaving points above the surface (secondary-ray statistics)."""
+    rng = np.random.RandomState(77)
+    nc = n // 2
+    pos = rng.uniform([0, 0], [1920, 1080], (nc, 2)).astype(F)
+    cam = camera_rays(pos)
+    rays = np.zeros((n, 8), dtype=F)
+    rays[:nc, 0:3], rays[:nc, 3], rays[:nc, 4:7], rays[:nc, 7] = cam[:, 0:3], cam[:, 3], cam[:, 4:7], cam[:, 7]
+    lo, hi = np.array([-11, -4.0, -11.0]), np.array([11, 6.0, 11.0])
+    a, b = rng.uniform(lo, hi, (n - nc, 3)), rng.uniform(lo, hi, (n - nc, 3))
+    d = b - a
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays[nc:, 0:3], rays[nc:, 3], rays[nc:, 4:7], rays[nc:, 7] = a, 1e-4, d, np.inf
+    return rays
+
+
 def load(name):
     path = os.path.join(HERE, "golden", name)
     if not os.path.exists(path):
