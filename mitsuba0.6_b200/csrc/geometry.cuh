@@ -185,6 +185,9 @@ constexpr int kNodeIters = NODE_ITERS;
 // per-thread local array.  A purely local stack costs one 32-byte sector per LANE per push/pop (the lanes of a warp
 // sit at different depths), which made the stack more than half of the trace kernels' L1 traffic
 // (profiles/r1e_ncu_full_raw.txt: 1.6 useful bytes per local sector).
+#ifndef TRACE_SHEAR_IN_STATE
+#define TRACE_SHEAR_IN_STATE 0
+#endif
 #ifndef TRACE_SMEM_NODES
 #define TRACE_SMEM_NODES 0
 #endif
@@ -205,6 +208,9 @@ struct Traversal {
     RayHit best;
     uint2 ngroup;
     int sp;
+#if TRACE_SHEAR_IN_STATE
+    RayShear shear;
+#endif
     uint32_t smBase;                               // shared-memory address of this thread's stack column (SH > 0)
     const float4 *topNodes = nullptr;              // per-CTA shared-memory copy of the top of the tree (TRACE_SMEM_NODES > 0)
     uint2 stack[kStackCapacity - SH];
@@ -233,6 +239,9 @@ struct Traversal {
         oct = (idir.x >= 0 ? 1u : 0u) | (idir.y >= 0 ? 2u : 0u) | (idir.z >= 0 ? 4u : 0u);
         sp = 0;
         ngroup = make_uint2(0u, 0x80000000u);
+#if TRACE_SHEAR_IN_STATE
+        shear = rayShear(d);
+#endif
         return true;
     }
 
@@ -276,7 +285,11 @@ struct Traversal {
                 ngroup = pop();
             }
         }
+#if TRACE_SHEAR_IN_STATE
+        const RayShear rs = shear;
+#else
         const RayShear rs = rayShear(d);   // recomputed per leaf batch (a few instructions) rather than held in registers across node visits
+#endif
         while (pending) {
             const int j = __ffs((int)pending) - 1;
             pending &= pending - 1;

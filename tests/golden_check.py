@@ -70,10 +70,12 @@ def check_bsdf(ctx, flat, z, name, gold, inputs=None):
     return worst
 
 
-def compare_trace(rays, got, ref, perturb_trace, max_mismatch=1e-3, jitter=1e-4, dump=None):
+def compare_trace(rays, got, ref, perturb_trace, max_mismatch=1e-3, jitter=1e-4, dump=None, perturb_got=None):
     """Hit/miss + shape id + primitive id of `got` = (hits, ids) against `ref` = (t, ids): identical except for ties (both hit
     at the same distance) and grazing rays (the checker `perturb_trace(rays) -> ids` changes its own answer under a 1e-4
-    perturbation of the direction -- `jitter`, to be chosen well below the angular size of a primitive).  Returns (mismatches,
+    perturbation of the direction -- `jitter`, to be chosen well below the angular size of a primitive; with `perturb_got` also
+    when the tested implementation's answer turns into the checker's under the same perturbation: an edge-on triangle that
+    one of the two finds and the other does not).  Returns (mismatches,
     excused as ties, excused as grazing)."""
     h, ids = got
     rt, rids = ref
@@ -95,6 +97,8 @@ def compare_trace(rays, got, ref, perturb_trace, max_mismatch=1e-3, jitter=1e-4,
                 jit[:, 4:7] += jr.normal(scale=jitter, size=(len(rest), 3)).astype(F)
                 jit[:, 4:7] /= np.linalg.norm(jit[:, 4:7], axis=1, keepdims=True)
                 excused |= (perturb_trace(jit) == ids[rest]).all(axis=1)
+                if perturb_got is not None:
+                    excused |= (perturb_got(jit) == rids[rest]).all(axis=1)
             if dump is not None and not excused.all():
                 np.savez(dump, rays=rays[rest[~excused]], got_ids=ids[rest[~excused]], ref_ids=rids[rest[~excused]], got_t=h[rest[~excused], 0],
                          ref_t=rt[rest[~excused]], n_bad=len(bad), n_tie=n_tie, n_rest=len(rest))

@@ -42,7 +42,7 @@ def test_fullsize_terrain_prim_ids_vs_reference():
     both_miss = ~np.isfinite(rt) & ~np.isfinite(h[:, 0])
     ids = ids.copy()
     ids[both_miss] = rids[both_miss]
-    n_bad, n_tie, n_graze = GC.compare_trace(rays, (h, ids), (rt, rids), perturb, max_mismatch=1e-3, jitter=2e-6,
+    n_bad, n_tie, n_graze = GC.compare_trace(rays, (h, ids), (rt, rids), perturb, max_mismatch=1e-3, jitter=2e-6, perturb_got=lambda r: gpu.ctx.trace(r)[1],
                                               dump=os.path.join(ROOT, "gpurun_out", "fullsize_unexplained.npz") if os.path.isdir(os.path.join(ROOT, "gpurun_out")) else None)   # fp32 ties on the shared edges of 0.009-unit triangles: ~1e-4 of the rays
     hit = np.isfinite(rt).mean()
     print("full-size terrain: %d rays vs %s, %.1f %% hit, %d mismatches (%d ties, %d grazing), 0 unexplained"
