@@ -185,7 +185,35 @@ def load():
     return bind(CUDA_LIB_PATH, CUDA_PREFIX)
 
 
+class DeviceArray:
+    """A buffer that already lives in device memory (for instance the result of an NVLink all-gather of a scene that the
+    ranks of a job uploaded in slices): the library copies it device to device (cudaMemcpyDefault / UVA) exactly like a
+    host buffer.  `owner` keeps the allocation alive."""
+
+    def __init__(self, data_ptr, shape, dtype, owner=None):
+        self.data_ptr, self.shape, self.dtype, self.owner = int(data_ptr), tuple(int(x) for x in shape), np.dtype(dtype), owner
+
+    @property
+    def size(self):
+        return int(np.prod(self.shape))
+
+    @property
+    def nbytes(self):
+        return self.size * self.dtype.itemsize
+
+    def reshape(self, shape):
+        shape = tuple(shape) if isinstance(shape, (tuple, list)) else (shape,)
+        if -1 in shape:
+            known = int(np.prod([x for x in shape if x != -1]))
+            shape = tuple(self.size // known if x == -1 else x for x in shape)
+        assert int(np.prod(shape)) == self.size
+        return DeviceArray(self.data_ptr, shape, self.dtype, self.owner)
+
+
 def f32(a, shape=None):
+    if isinstance(a, DeviceArray):
+        assert a.dtype == np.float32
+        return a.reshape(shape) if shape is not None else a
     a = np.ascontiguousarray(a, dtype=np.float32)
     if shape is not None:
         a = a.reshape(shape)
@@ -193,6 +221,8 @@ def f32(a, shape=None):
 
 
 def ptr(a):
+    if isinstance(a, DeviceArray):
+        return C.c_void_p(a.data_ptr)
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
@@ -256,7 +286,7 @@ class Context:
         """uv_tangents=True asks for TriMesh::computeUVTangents: on the device for libmtscuda (flag in the descriptor),
         on the host (hostmath.uv_tangents, the numpy mirror) for a library that takes explicit tangents only."""
         pos = f32(positions, (-1, 3))
-        idx = np.ascontiguousarray(indices, dtype=np.uint32).reshape(-1, 3)
+        idx = indices.reshape((-1, 3)) if isinstance(indices, DeviceArray) else np.ascontiguousarray(indices, dtype=np.uint32).reshape(-1, 3)
         nrm = None if normals is None else f32(normals, (-1, 3))
         uv = None if texcoords is None else f32(texcoords, (-1, 2))
         flag = 0
@@ -281,7 +311,7 @@ class Context:
     def add_emitter(self, desc, texels=None):
         if texels is not None:
             t = f32(texels)
-            desc.env_texels = t.ctypes.data
+            desc.env_texels = t.data_ptr if isinstance(t, DeviceArray) else t.ctypes.data
         return self._check(self.fn["add_emitter"](self.h, C.byref(desc)))
 
     def build(self):

@@ -67,11 +67,8 @@ DEVFN bool primIntersect(const DScene &S, int slot, float3 o, float3 d, const Ra
         float U = __fsub_rn(__fmul_rn(Cx, By), __fmul_rn(Cy, Bx));
         float V = __fsub_rn(__fmul_rn(Ax, Cy), __fmul_rn(Ay, Cx));
         float W = __fsub_rn(__fmul_rn(Bx, Ay), __fmul_rn(By, Ax));
-        if (U == 0.0f || V == 0.0f || W == 0.0f) {   // on an edge in fp32: decide in double
-            U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
-            V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
-            W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
-        }
+        // an exact zero (the ray passes through an edge or a vertex in fp32) counts as inside for BOTH triangles of the edge:
+        // a double hit at the same distance instead of Woop's double-precision tie-break -- never a leak
         if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
         const float det = U + V + W;
         if (det == 0.0f) return false;

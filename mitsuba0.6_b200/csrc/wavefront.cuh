@@ -544,7 +544,7 @@ constexpr int kSurfRows = 10;
 #define SURFACE_MINB 4
 #endif
 #ifndef SCATTER_MINB
-#define SCATTER_MINB 4
+#define SCATTER_MINB 6
 #endif
 enum { SR_BUMP = 1u << 24, SR_FLIPPED = 1u << 25, SR_ALIVE = 1u << 26, SR_NFLIP = 1u << 27,
        SR_SMOOTH = 1u << 28,    // the root BSDF has smooth lobes (light sampling applies, path.cpp:172)

@@ -1007,14 +1007,10 @@ def flatten(scene):
 
 
 def upload(fs, ctx):
-    """Issue the C-ABI calls for a flattened scene (order: textures, LUTs, BSDFs, shapes, emitters)."""
+    """Issue the C-ABI calls for a flattened scene.  Geometry goes first: texture uploads run on a stream of their own
+    inside the library, so the copy engine is busy with the texels while build() constructs the BVH."""
     ctx.set_camera(fs.camera)
     ctx.set_film(fs.film)
-    for d, tex in fs.textures:
-        ctx.add_texture(d, tex)
-    if fs.pool:
-        ctx.set_float_pool(np.asarray(fs.pool, dtype=F))
-    ctx.set_bsdfs(fs.nodes)
     for s in fs.shapes:
         if s[0] == "rectangle":
             ctx.add_rectangle(s[1], s[2])
@@ -1024,6 +1020,11 @@ def upload(fs, ctx):
             d = s[1]
             ctx.add_mesh(d["positions"], d["indices"], d["normals"], d["texcoords"], d["tangents"], d["bsdf"],
                          uv_tangents=d.get("uv_tangents", False))
+    for d, tex in fs.textures:
+        ctx.add_texture(d, tex)
+    if fs.pool:
+        ctx.set_float_pool(np.asarray(fs.pool, dtype=F))
+    ctx.set_bsdfs(fs.nodes)
     for d, tex in fs.emitters:
         ctx.add_emitter(d, tex)
     ctx.build()

@@ -142,7 +142,7 @@ IMAGE_SCENES = {
     "zoo": lambda: zoo(spp=131072)[0],
     "cornell": lambda: scenes.cornell_box(CORNELL_RES, CORNELL_RES, 4096),
     "spheres": lambda: scenes.material_spheres(128, 128, 65536, env_size=(512, 256)),
-    "caustics": lambda: scenes.caustic_scene(96, 96, 262144, knot=(120, 40)),
+    "caustics": lambda: scenes.caustic_scene(64, 64, 1048576, knot=(120, 40)),
     "terrain": lambda: scenes.terrain_scene(160, 90, 4096, grid=200, tex_size=256, env_size=(512, 256)),
 }
 
