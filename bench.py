@@ -118,6 +118,51 @@ def pin_scene(flat):
     return flat
 
 
+def gather_scene(flat, rank, world):
+    """End-to-end leg with N ranks: every rank copies 1/N of each large scene array from pinned host memory to its GPU
+    over its own PCIe link, and one NCCL all-gather per array over NVLink gives every GPU the whole scene -- each host byte
+    crosses PCIe once per JOB instead of once per rank.  Returns a shallow copy of `flat` whose large arrays are
+    abi.DeviceArray views of the gathered buffers (libmtscuda takes them like host buffers: cudaMemcpyDefault), and the
+    bytes this rank copied host to device."""
+    import copy
+    import torch
+    import torch.distributed as dist
+    from mitsuba0_6_b200 import abi
+    h2d = 0
+    keep = []
+
+    def gather(a):
+        nonlocal h2d
+        if not isinstance(a, np.ndarray) or a.nbytes < (1 << 16):
+            return a
+        assert a.dtype.itemsize == 4 and a.flags["C_CONTIGUOUS"]
+        flat32 = a.reshape(-1).view(np.int32)                      # float32 / uint32 travel as 32-bit words
+        n = flat32.size
+        chunk = (n + world - 1) // world
+        lo, hi = min(rank * chunk, n), min((rank + 1) * chunk, n)
+        full = torch.empty(world * chunk, dtype=torch.int32, device="cuda")
+        mine = full[rank * chunk:(rank + 1) * chunk]
+        if hi > lo:
+            mine[:hi - lo].copy_(torch.from_numpy(flat32[lo:hi]), non_blocking=True)   # pinned host -> this rank's slice
+            h2d += 4 * (hi - lo)
+        dist.all_gather_into_tensor(full, mine)                    # in place: every rank contributes its own slice
+        keep.append(full)
+        return abi.DeviceArray(full.data_ptr(), a.shape, a.dtype, owner=full)
+
+    f2 = copy.copy(flat)
+    f2.textures = [(d, gather(t)) for d, t in flat.textures]
+    f2.emitters = [(d, gather(t) if t is not None else None) for d, t in flat.emitters]
+    shapes = []
+    for s in flat.shapes:
+        if s[0] == "mesh":
+            s = (s[0], {k: gather(v) for k, v in s[1].items()}) + tuple(s[2:])
+        shapes.append(s)
+    f2.shapes = shapes
+    f2._gathered = keep
+    torch.cuda.current_stream().synchronize()    # the library reads the buffers on its own stream
+    return f2, h2d
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
 
@@ -439,7 +484,12 @@ def run_cuda(args):
         for i in range(1 + max(1, min(args.steps, 3))):
             sync()
             t0 = time.time()
-            g2 = M.CudaPath(flat, device=local)
+            if world > 1:     # sharded upload + NVLink all-gather (see gather_scene)
+                flat_e2e, h2d_rank = gather_scene(flat, rank, world)
+                t_gather = time.time()
+            else:
+                flat_e2e, h2d_rank, t_gather = flat, h2d, t0
+            g2 = M.CudaPath(flat_e2e, device=local)
             g2.preprocess()
             t1 = time.time()
             if world > 1:
@@ -458,6 +508,8 @@ def run_cuda(args):
             if i > 0:
                 e2e_ms.append((t3 - t0) * 1e3)
                 parts = {"upload_build_ms": (t1 - t0) * 1e3, "render_ms": (t2 - t1) * 1e3, "reduce_readback_ms": (t3 - t2) * 1e3}
+                if world > 1:
+                    parts["sharded_h2d_allgather_ms"] = (t_gather - t0) * 1e3
             e2e_build_ms = g2.ctx.get_stats().build_ms
             g2.close()
             del g2
@@ -466,6 +518,9 @@ def run_cuda(args):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e_t = float(tt.item())
         e2e = {"value": W * H * spp_total / (e2e_t / 1e3) / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,
+               "h2d_bytes_per_step_per_rank": h2d_rank,
+               "upload": "whole scene from pinned host memory" if world == 1 else
+                         "each rank copies 1/%d of every large array over its own PCIe link, NCCL all-gather over NVLink" % world,
                "d2h_bytes_per_step": d2h, "ms_per_step": e2e_t, "bvh_build_ms": e2e_build_ms, "rank0_breakdown_ms": parts,
                "includes": "context + scene upload from pinned host memory + GPU BVH build + render + device-side film reduce + film read-back on rank 0"}
 
