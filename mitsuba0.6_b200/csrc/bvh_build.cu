@@ -24,7 +24,10 @@ namespace mts {
 
 constexpr int NB = 16;            // SAH bins per axis
 constexpr int kMaxLeaf = 3;       // primitives per leaf (a wide-node leaf child encodes 1..3 in unary)
-constexpr float kCostTrav = 1.0f, kCostIsect = 1.2f;
+#ifndef BVH_COST_ISECT
+#define BVH_COST_ISECT 1.2f
+#endif
+constexpr float kCostTrav = 1.0f, kCostIsect = BVH_COST_ISECT;
 constexpr int kSmall = 32;        // nodes of at most one primitive per lane are finished by k_small_subtrees
 
 struct BuildNode {

@@ -18,6 +18,7 @@ for o in mtscuda bvh_build shade_c0p0 shade_c0p1 shade_c1p0 shade_c1p1 shade_c1p
   if [ $hit = 1 ]; then
     out=../../build/${o}_$name.o
     if [ "$o" = "mtscuda" ]; then nvcc $FLAGS "$@" -c mtscuda.cu -o $out
+    elif [ "$o" = "bvh_build" ]; then nvcc $FLAGS "$@" -c bvh_build.cu -o $out
     else
       cp=${o#shade_c}; cls=${cp%p*}; part=${cp#*p}
       nvcc $FLAGS "$@" -DSHADE_CLASS=$cls -DSHADE_PART=$part -c shade_inst.cu -o $out
