@@ -456,8 +456,13 @@ __device__ __forceinline__ PrimRecord makePrimRecord(const PrimSource &s, const 
         r.p0 = make_float4(v0.x, v0.y, v0.z, __int_as_float(s.shape));
         // the three vertices themselves (not v0 + edges): neighbouring triangles then hold bit-identical copies of their
         // shared vertices, which is what makes the edge tests of primIntersect watertight
+#if TRI_TEST_WOOP
         r.p1 = make_float4(v1.x, v1.y, v1.z, __int_as_float((int)s.prim));
         r.p2 = make_float4(v2.x, v2.y, v2.z, __int_as_float(0));
+#else
+        r.p1 = make_float4(v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, __int_as_float((int)s.prim));
+        r.p2 = make_float4(v2.x - v0.x, v2.y - v0.y, v2.z - v0.z, __int_as_float(0));
+#endif
     } else {
         r.p0 = make_float4(0, 0, 0, __int_as_float(s.shape));
         r.p1 = make_float4(0, 0, 0, __int_as_float(0));

@@ -58,6 +58,31 @@ DEVFN bool primIntersect(const DScene &S, int slot, float3 o, float3 d, const Ra
     const float4 *rec = reinterpret_cast<const float4 *>(S.prims + slot);
     float4 p0 = __ldg(rec), p1 = __ldg(rec + 1), p2 = __ldg(rec + 2);
     int type = __float_as_int(p2.w);
+#if !TRI_TEST_WOOP
+    if (type == 0) {
+        // Moeller-Trumbore on (v0, e1, e2), made conservative: u, v and 1 - u - v may be negative by `tol`, an upper bound
+        // of the fp32 error of their own evaluation (products of |tv| ~ distance and |e| ~ triangle size divided by det:
+        // 1e-4 ... 1e-3 for a 0.009-unit triangle seen from 15 units).  The two triangles of an edge then overlap by at
+        // least the error either of them makes, and a ray can not pass between them.
+        const float3 e1 = f3(p1), e2 = f3(p2);
+        const float3 pv = cross(d, e2);
+        const float det = dot(e1, pv);
+        if (det == 0.0f) return false;
+        const float inv = 1.0f / det;
+        const float3 tv = o - f3(p0);
+        const float u = dot(tv, pv) * inv;
+        const float3 qv = cross(tv, e1);
+        const float v = dot(d, qv) * inv;
+        const float m1 = fabsf(e1.x) + fabsf(e1.y) + fabsf(e1.z), m2 = fabsf(e2.x) + fabsf(e2.y) + fabsf(e2.z);
+        const float mt = fabsf(tv.x) + fabsf(tv.y) + fabsf(tv.z), me = fmaxf(m1, m2);
+        const float tol = fminf(1.9e-6f * me * (mt + 2.0f * me) * fabsf(inv), 1e-2f);     // 32 eps * |e| * (|tv| + 2 |e|) / |det|
+        if (!(u >= -tol && v >= -tol && u + v <= 1.0f + 2.0f * tol)) return false;
+        const float t = dot(e2, qv) * inv;
+        if (!(t >= mint && t <= maxt)) return false;
+        h.t = t; h.u = u; h.v = v; h.prim = slot;
+        return true;
+    }
+#else
     if (type == 0) {
         const float3 A = f3(p0) - o, B = f3(p1) - o, C = f3(p2) - o;
         const float Akz = comp3(A, rs.kz), Bkz = comp3(B, rs.kz), Ckz = comp3(C, rs.kz);
@@ -78,6 +103,7 @@ DEVFN bool primIntersect(const DScene &S, int slot, float3 o, float3 d, const Ra
         h.t = t; h.u = V * inv; h.v = W * inv; h.prim = slot;
         return true;
     }
+#endif
     const DShape &s = S.shapes[__float_as_int(p0.w)];
     float t, lx = 0, ly = 0;
     bool ok = (type == 1) ? rectIntersect(s, o, d, mint, maxt, t, lx, ly) : sphereIntersect(s, o, d, mint, maxt, t);
@@ -284,8 +310,10 @@ struct Traversal {
         }
 #if TRACE_SHEAR_IN_STATE
         const RayShear rs = shear;
-#else
+#elif TRI_TEST_WOOP
         const RayShear rs = rayShear(d);   // recomputed per leaf batch (a few instructions) rather than held in registers across node visits
+#else
+        RayShear rs; rs.kx = rs.ky = rs.kz = 0; rs.Sx = rs.Sy = rs.Sz = 0;   // unused by the Moeller-Trumbore form
 #endif
         while (pending) {
             const int j = __ffs((int)pending) - 1;

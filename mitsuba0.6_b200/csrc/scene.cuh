@@ -74,8 +74,18 @@ struct WideNode {
     uint4 n1, n2, n3, n4;
 };
 
+// Triangle test of the trace kernels (geometry.cuh primIntersect), which also decides what a triangle's record holds:
+//   0  conservative Moeller-Trumbore: record = (v0, e1, e2); a hit is accepted when the barycentrics lie inside the
+//      triangle enlarged by the fp32 error bound of their own evaluation -- neighbouring triangles overlap by that
+//      margin, so no ray slips between them (a ray in the margin hits both, at the same distance)
+//   1  Woop / Benthin / Wald 2013: record = (v0, v1, v2); sign-consistent edge functions on the shared vertices (default)
+// Measured on cfg3 (profiles/r2z_tritest.txt): form 0 is 3.4 % faster on the frame, but 1.7 % of the rays then report the
+// NEIGHBOUR of the reference's triangle (same distance, inside the overlap margin) against 1.3e-4 with form 1.
+#ifndef TRI_TEST_WOOP
+#define TRI_TEST_WOOP 1
+#endif
 // 48-byte primitive record in leaf order.
-//   triangle: p0 = (v0, shape), p1 = (v1, prim index), p2 = (v2, 0)
+//   triangle: p0 = (v0, shape), p1 = (e1 = v1-v0 | v1, prim index), p2 = (e2 = v2-v0 | v2, 0)   (see TRI_TEST_WOOP)
 //   analytic: p0.w = shape, p2.w = 1 (rectangle) / 2 (sphere)
 struct PrimRecord { float4 p0, p1, p2; };
 
