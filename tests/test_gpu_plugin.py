@@ -21,7 +21,7 @@ needs_ref = pytest.mark.skipif(not os.path.exists(os.path.join(mtsref.REF_DIR, "
 
 
 @needs_ref
-@pytest.mark.parametrize("name,bar", [("cornell", 1e-3), ("zoo", 1.2e-3), ("terrain", 1e-3), ("spheres", 1.5e-3)]   # measured 7.8e-5, 7.9e-4, 2.6e-4, 9.3e-4)
+@pytest.mark.parametrize("name,bar", [("cornell", 1e-3), ("zoo", 1.2e-3), ("terrain", 1e-3), ("spheres", 1.5e-3)])   # measured 7.8e-5, 7.9e-4, 2.6e-4, 9.3e-4
 def test_cudapath_plugin_in_reference_host(name, bar):
     gold = G.load("images.npz")
     sc = G.IMAGE_SCENES[name]()
@@ -36,7 +36,7 @@ def test_cudapath_plugin_in_reference_host(name, bar):
 
 
 @needs_ref
-@pytest.mark.parametrize("name,bar", [("twosided", 1e-3), ("thin_hide", 1.5e-3)]   # measured 5.7e-5, 7.7e-4)
+@pytest.mark.parametrize("name,bar", [("twosided", 1e-3), ("thin_hide", 1.5e-3)])   # measured 5.7e-5, 7.7e-4
 def test_cudapath_plugin_next_row_bsdfs(name, bar):
     # TwoSidedBRDF / ThinDielectric / Mask parsed from the live reference objects (InstanceManager serialization);
     # thin_hide also passes hideEmitters through the plugin's Properties
