@@ -147,6 +147,7 @@ static __global__ void __launch_bounds__(256) k_raygen(const DScene S, const Wav
 // Lanes of a warp that hold the same key elect a leader that reserves room for all of them with one atomicAdd.
 // Returns this lane's position (valid only where key != kNoKey).
 constexpr uint32_t kNoKey = 0xffffffffu;
+constexpr uint32_t kSortSmemKeys = 512;   // sort keys (distinct root BSDFs + 1) up to which the sort counts per CTA in shared memory
 DEVFN uint32_t keyedAppend(uint32_t *counters, uint32_t key) {
     unsigned active = __activemask();
     unsigned peers = __match_any_sync(active, key);
@@ -223,6 +224,8 @@ static __global__ void __launch_bounds__(128, TRACE_MINB) k_intersect(const DSce
     const uint32_t count = W.ctr->qCount[qsel];
     TraceCounters tc = {0, 0};
     const uint32_t *queue = W.queue[qsel];
+    // (the key histogram stays in global memory: counting it per CTA in shared memory cost 0.8 ms per wavefront in spills,
+    //  profiles/r3a_sort.txt -- unlike k_sort_scatter, where the per-CTA form is 8x faster)
     traceQueue<false, COUNT>(S, count, &W.ctr->cursor[0], &tc,
         [&](uint32_t i, Traversal<false, COUNT, kSmemStack> &tr) {
             uint32_t slot = queue[i];
@@ -280,16 +283,38 @@ static __global__ void k_sort_offsets(const Wavefront W) {
         carry += __shfl_sync(0xffffffffu, incl, 31);
     }
 }
+// Positions are handed out per CTA: the 256 entries of a trip count their keys in shared memory (warp-aggregated), one
+// global atomicAdd per key and CTA reserves the range, and every entry lands at range start + its rank within the CTA.
+// (One global atomic per key and WARP on a handful of hot counters was atomic-bound: 2.1 ms per wavefront for 35 M
+// entries, 200 GB/s.)  Scenes with more sort keys than kSortSmemKeys fall back to the per-warp form.
 static __global__ void __launch_bounds__(256) k_sort_scatter(const Wavefront W, int qsel) {
     const uint32_t count = W.ctr->qCount[qsel];
-    const uint32_t rounded = (count + 31u) & ~31u;
     const uint32_t *off = W.keyCount + W.numKeys;
     uint32_t *cur = W.keyCount + 2 * W.numKeys;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
+    if (W.numKeys > kSortSmemKeys) {
+        const uint32_t rounded = (count + 31u) & ~31u;
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
+            uint32_t key = kNoKey, slot = 0;
+            if (i < count) { key = W.keys[i]; slot = W.queue[qsel][i]; }
+            uint32_t pos = keyedAppend(cur, key);
+            if (key != kNoKey) W.sorted[off[key] + pos] = slot;
+        }
+        return;
+    }
+    __shared__ uint32_t sCnt[kSortSmemKeys], sBase[kSortSmemKeys];
+    const uint32_t rounded = (count + 255u) & ~255u;
+    for (uint32_t base = blockIdx.x * blockDim.x; base < rounded; base += gridDim.x * blockDim.x) {   // whole CTAs take part in every trip
+        const uint32_t i = base + threadIdx.x;
+        for (uint32_t k = threadIdx.x; k < W.numKeys; k += blockDim.x) sCnt[k] = 0;
+        __syncthreads();
         uint32_t key = kNoKey, slot = 0;
         if (i < count) { key = W.keys[i]; slot = W.queue[qsel][i]; }
-        uint32_t pos = keyedAppend(cur, key);
-        if (key != kNoKey) W.sorted[off[key] + pos] = slot;
+        const uint32_t pos = keyedAppend(sCnt, key);          // rank within the CTA (shared-memory atomics)
+        __syncthreads();
+        for (uint32_t k = threadIdx.x; k < W.numKeys; k += blockDim.x) { const uint32_t c = sCnt[k]; if (c) sBase[k] = atomicAdd(cur + k, c); }
+        __syncthreads();
+        if (key != kNoKey) W.sorted[off[key] + sBase[key] + pos] = slot;
+        __syncthreads();
     }
 }
 
