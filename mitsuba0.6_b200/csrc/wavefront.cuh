@@ -13,14 +13,20 @@
 
 namespace mts {
 
+// Every counter that a kernel's warps bump concurrently sits in a 128-byte line of its own (COUNTER_LINE): the queue
+// appends of one shade kernel (next / shadow / done) are three streams of one-per-warp atomics, and atomics on one line
+// are served one after the other by the same L2 slice.
+#ifndef COUNTER_LINE
+#define COUNTER_LINE 128
+#endif
 struct Counters {
-    uint32_t qCount[2];     // active queue sizes (ping-pong)
-    uint32_t shadowCount;
-    uint32_t doneCount;
-    uint32_t ewaCount;      // deferred EWA texture walks of the current bounce (k_shade_surface -> k_shade_ewa)
-    uint32_t ewaBin[3 * 16]; // size-class histogram, offsets and cursors of the walks (kEwaBins each; all zero between uses)
-    uint32_t cursor[2];     // next unclaimed ray of the intersect / shadow queue (persistent warps pull from these)
-    unsigned long long missRays;                 // rays that escaped (sort key 0), total over all bounces
+    alignas(COUNTER_LINE) uint32_t qCount[2];     // active queue sizes (ping-pong: one is read, the other appended to)
+    alignas(COUNTER_LINE) uint32_t shadowCount;
+    alignas(COUNTER_LINE) uint32_t doneCount;
+    alignas(COUNTER_LINE) uint32_t ewaCount;      // deferred EWA texture walks of the current bounce (k_shade_surface -> k_shade_ewa)
+    alignas(COUNTER_LINE) uint32_t cursor[2];     // next unclaimed ray of the intersect / shadow queue (persistent warps pull from these)
+    alignas(COUNTER_LINE) uint32_t ewaBin[3 * 16]; // size-class histogram, offsets and cursors of the walks (kEwaBins each; all zero between uses)
+    alignas(COUNTER_LINE) unsigned long long missRays;                 // rays that escaped (sort key 0), total over all bounces
     unsigned long long normalRays, shadowRays;   // totals over all bounces ("Normal/Shadow rays traced", skdtree.cpp:46-47), kept on the device
     unsigned long long pathLenSum;
     unsigned long long nodesVisited, primsTested;  // instrumented traces only (closest hit)
