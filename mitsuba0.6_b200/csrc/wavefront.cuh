@@ -81,6 +81,30 @@ DEVFN uint32_t warpAppend(uint32_t *counter, bool pred) {
     return base + __popc(mask & ((1u << lane) - 1));
 }
 
+// One atomicAdd per CTA: every thread of the block must call it (same trip count for all warps).  The light kernels
+// (raygen, escaped rays) bump one global counter once per warp otherwise -- half a million atomics on one address in
+// half a millisecond.
+DEVFN uint32_t blockAppend(uint32_t *counter, bool pred) {
+    __shared__ uint32_t sWarpCount[32], sBlockBase;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+    const unsigned mask = __ballot_sync(0xffffffffu, pred);
+    if (lane == 0) sWarpCount[warp] = __popc(mask);
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t v = lane < nwarps ? sWarpCount[lane] : 0, incl = v;
+        for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+        uint32_t base = 0;
+        if (lane == 0 && total) base = atomicAdd(counter, total);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (lane < nwarps) sWarpCount[lane] = base + incl - v;
+    }
+    __syncthreads();
+    const uint32_t r = sWarpCount[warp] + __popc(mask & ((1u << lane) - 1));
+    __syncthreads();   // the next call reuses the shared array
+    return pred ? r : 0xffffffffu;
+}
+
 DEVFN Surf surfOf(const Hit &h) {
     Surf s; s.tc = texCtx(h.uv); s.dpdu = h.dpdu; s.dpdv = h.dpdv; s.geoN = h.geoN; s.sh = h.sh; s.bumpNode = -1; return s;
 }
@@ -121,7 +145,7 @@ DEVFN float4 computePartials(float3 p, float3 n, float3 dpdu, float3 dpdv, float
 // ---- raygen: SamplingIntegrator::renderBlock sample loop + sampleRayDifferential -------------
 static __global__ void __launch_bounds__(256) k_raygen(const DScene S, const Wavefront W, const RenderConst R,
                                                 unsigned long long firstItem, uint32_t count, int qsel) {
-    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < ((count + 31u) & ~31u); j += gridDim.x * blockDim.x) {
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < ((count + 255u) & ~255u); j += gridDim.x * blockDim.x) {   // 256-thread CTAs, whole CTAs per trip
         bool valid = j < count;
         uint32_t pixel = 0, sample = 0;
         int x = 0, y = 0;
@@ -145,7 +169,7 @@ static __global__ void __launch_bounds__(256) k_raygen(const DScene S, const Wav
             W.L[j] = make_float4(0, 0, 0, 0);
             W.meta[j] = make_uint4(pixel, sample, 1u, 0u);
         }
-        uint32_t slot = warpAppend(&W.ctr->qCount[qsel], valid);
+        uint32_t slot = blockAppend(&W.ctr->qCount[qsel], valid);
         if (valid) W.queue[qsel][slot] = j;
     }
 }
@@ -484,7 +508,7 @@ DEVFN void shadePath(const DScene &S, const Wavefront &W, const RenderConst &R, 
 static __global__ void __launch_bounds__(256) k_shade_miss(const DScene S, const Wavefront W, const RenderConst R, int qsel) {
     const uint32_t total = W.ctr->qCount[qsel];
     const uint32_t count = W.numKeys > 1 ? min(W.keyCount[W.numKeys + 1], total) : total;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ((count + 31u) & ~31u); i += gridDim.x * blockDim.x) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ((count + 255u) & ~255u); i += gridDim.x * blockDim.x) {   // whole CTAs per trip
         const bool valid = i < count;
         uint32_t slot = 0;
         if (valid) {
@@ -521,7 +545,7 @@ static __global__ void __launch_bounds__(256) k_shade_miss(const DScene S, const
             W.L[slot] = make_float4(lv.x, lv.y, lv.z, 0);
             W.meta[slot] = make_uint4(meta.x, meta.y, depth | (flags << 16), 0);
         }
-        uint32_t c = warpAppend(&W.ctr->doneCount, valid);
+        uint32_t c = blockAppend(&W.ctr->doneCount, valid);
         if (valid) W.doneQ[c] = slot;
     }
 }
@@ -601,7 +625,7 @@ static __global__ void __launch_bounds__(128, SURFACE_MINB) k_shade_surface(cons
                 EwaDefer ewa; ewa.pending = false;
                 const Material<SHADE_LEAF> mat(S, bsdf, su, v.wi, W.ewaJobs ? &ewa : nullptr);
                 if (ewa.pending) {   // the walk runs in k_shade_ewa, which fills c0 / c1 of this record
-                    const uint32_t j = atomicAdd(&W.ctr->ewaCount, 1u);
+                    const uint32_t j = warpAppend(&W.ctr->ewaCount, true);   // one atomic per warp (the lanes that queue a walk)
                     W.ewaJobs[j] = make_float4(__uint_as_float(i), __uint_as_float((uint32_t)ewa.texA | ((uint32_t)(ewa.texB & 0xffff) << 16)),
                                                __uint_as_float((uint32_t)ewa.ilevel | ((uint32_t)ewa.slotA << 8)), ewa.a);
                     W.ewaJobs[cap + j] = make_float4(ewa.uv.x, ewa.uv.y, ewa.A, ewa.B);
