@@ -346,6 +346,15 @@ MTS_API int MTS_FN(sample_rays)(MtsContext *ctx, int64_t n, const float *sample_
  * ids:  n*2 int32   shape id, primitive index within the shape (-1,-1 on miss; may be NULL for shadow) */
 MTS_API int MTS_FN(trace)(MtsContext *ctx, int64_t n, const float *rays, int32_t shadow, float *hits, int32_t *ids);
 
+/* mtscuda_trace without any device allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments, kernels and results as trace(); `rays`, `hits`, `ids` may be host or device pointers.
+ * The working memory is one fixed array of device memory inside the library (about 2.9 MB per GPU, held until exit):
+ * at most MTS_NOALLOC_MAX_RAYS rays per call and 512 material sort keys per scene, larger requests fail with MTS_EINVAL.
+ * All calls on one GPU share that array: calls that overlap on the GPU race. */
+#define MTS_NOALLOC_MAX_RAYS 16384
+MTS_API int MTS_FN(trace_noalloc)(MtsContext *ctx, int64_t n, const float *rays, int32_t shadow, float *hits, int32_t *ids);
+
 /* fillIntersectionRecord (include/mitsuba/render/skdtree.h:343-428).
  * out: n*24 floats  p(3) t geoN(3) u shN(3) v dpdu(3) pad dpdv(3) pad wi(3) pad */
 MTS_API int MTS_FN(hit_records)(MtsContext *ctx, int64_t n, const float *rays, float *out, int32_t *ids);

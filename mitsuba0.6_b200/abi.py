@@ -21,6 +21,7 @@ EPSILON = 1e-4
     BSDF_DIELECTRIC, BSDF_COATING, BSDF_BLEND, BSDF_BUMPMAP, BSDF_TWOSIDED, BSDF_THINDIELECTRIC, BSDF_MASK, BSDF_ROUGHDIELECTRIC,
     BSDF_MIXTURE, BSDF_ROUGHCOATING, BSDF_NORMALMAP) = range(16)
 MIXTURE_MAX = 16
+NOALLOC_MAX_RAYS = 16384   # MTS_NOALLOC_MAX_RAYS
 BF_GGX, BF_SAMPLE_VISIBLE, BF_NONLINEAR, BF_RT_2D, BF_RAY_DIFF = 1, 2, 4, 8, 16
 ENULL, EDIFFUSE_REFLECTION, EDIFFUSE_TRANSMISSION, EGLOSSY_REFLECTION, EGLOSSY_TRANSMISSION, \
     EDELTA_REFLECTION, EDELTA_TRANSMISSION = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20, 0x40
@@ -105,7 +106,7 @@ ABI_VERSION = 5   # MTS_ABI_VERSION of include/mtscuda.h these mirrors were writ
 ABI_SYMBOLS = [
     "abi_version", "last_error", "create", "create_multi", "device_count", "destroy", "set_camera", "set_film", "add_texture", "set_float_pool",
     "set_bsdfs", "add_mesh", "add_rectangle", "add_sphere", "add_emitter", "build", "render",
-    "read_film", "read_film_alpha", "bind_film", "set_stream", "get_stats", "sample_rays", "trace", "hit_records", "bsdf_eval_pdf",
+    "read_film", "read_film_alpha", "bind_film", "set_stream", "get_stats", "sample_rays", "trace", "trace_noalloc", "hit_records", "bsdf_eval_pdf",
     "bsdf_sample", "sample_emitter_direct", "eval_environment", "texture_eval", "hit_partials", "eval_environment_camera", "splat",
 ]
 
@@ -157,6 +158,7 @@ def bind(path, prefix):
         "get_stats": (C.c_int, [vp, C.POINTER(Stats)]),
         "sample_rays": (C.c_int, [vp, i64, fp, fp]),
         "trace": (C.c_int, [vp, i64, fp, i32, fp, fp]),
+        "trace_noalloc": (C.c_int, [vp, i64, fp, i32, fp, fp]),
         "hit_records": (C.c_int, [vp, i64, fp, fp, fp]),
         "bsdf_eval_pdf": (C.c_int, [vp, i32, i64, fp, fp, fp, i32, fp, fp]),
         "bsdf_sample": (C.c_int, [vp, i32, i64, fp, fp, fp, fp]),
@@ -358,6 +360,14 @@ class Context:
         hits = np.empty((r.shape[0], 4), dtype=np.float32)
         ids = np.empty((r.shape[0], 2), dtype=np.int32)
         self._check(self.fn["trace"](self.h, r.shape[0], ptr(r), int(shadow), ptr(hits), ptr(ids)))
+        return hits, ids
+
+    def trace_noalloc(self, rays, shadow=False):
+        """mtscuda_trace_noalloc: trace() in the library's fixed device scratch (no allocation; at most NOALLOC_MAX_RAYS rays)."""
+        r = f32(rays, (-1, 8))
+        hits = np.empty((r.shape[0], 4), dtype=np.float32)
+        ids = np.empty((r.shape[0], 2), dtype=np.int32)
+        self._check(self.fn["trace_noalloc"](self.h, r.shape[0], ptr(r), int(shadow), ptr(hits), ptr(ids)))
         return hits, ids
 
     def hit_records(self, rays):

@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <mutex>
 #include <thread>
 #include <vector>
 #include "bvh_build.h"
@@ -1491,6 +1492,81 @@ MTS_API int mtscuda_trace(MtsContext *c, int64_t n, const float *rays, int32_t s
     }
     CUDA_TRY(cudaMemsetAsync(Wf.keyCount, 0, 4 * 3 * (size_t)Wf.numKeys, st));   // k_intersect left its key histogram behind
     return syncCheck(c, "trace");
+}
+
+// ---- mtscuda_trace_noalloc: the trace entry point for callers that must not allocate -------------------------------
+// No counterpart in the reference; added (CUDA-graph capture, tight serving loops
+// and harnesses that forbid cudaMalloc).  Same kernels and results as mtscuda_trace, but the wavefront slice the queue
+// kernels work in (ray state, hit records, queues, sort keys, counters) and the staging of the rays / results live in ONE
+// file-scope device array of fixed size instead of pool allocations: at most MTS_NOALLOC_MAX_RAYS rays per call, scenes
+// with at most kNoAllocMaxKeys material sort keys.  Every GPU that loads the library holds the array (2.9 MB) until exit.
+// All calls on a device share it -- calls that overlap on the GPU (different streams / contexts) race -- and it keeps
+// the previous call's contents: the counters and the key histogram are cleared at the start of every call, everything
+// else is written before it is read.
+constexpr uint32_t kNoAllocMaxRays = MTS_NOALLOC_MAX_RAYS;
+constexpr uint32_t kNoAllocMaxKeys = 512;
+struct NoAllocScratch {
+    float4 rayO[kNoAllocMaxRays], rayD[kNoAllocMaxRays], hit[kNoAllocMaxRays];                           // closest-hit ray state
+    float4 shO[kNoAllocMaxRays], shD[kNoAllocMaxRays], shC[kNoAllocMaxRays], L[kNoAllocMaxRays];         // shadow-ray state
+    float raysIn[8 * kNoAllocMaxRays], hitsOut[4 * kNoAllocMaxRays];                                     // staging of the caller's buffers
+    int32_t idsOut[2 * kNoAllocMaxRays];
+    uint32_t queue[kNoAllocMaxRays], keys[kNoAllocMaxRays];
+    uint32_t keyCount[3 * kNoAllocMaxKeys];
+    Counters ctr;
+};
+static __device__ __align__(256) unsigned char g_noAllocScratch[sizeof(NoAllocScratch)];
+namespace {
+std::mutex g_noAllocMutex;
+void *g_noAllocAddr[64] = {};   // device address of g_noAllocScratch per device ordinal (the name itself is a host-side stand-in)
+// once per device, with that device current
+int noAllocScratch(MtsContext *c, NoAllocScratch **out) {
+    if (c->device < 0 || c->device >= 64) return fail(MTS_EINVAL, "trace_noalloc: device ordinal out of range");
+    CUDA_TRY(cudaSetDevice(c->device));
+    std::lock_guard<std::mutex> lock(g_noAllocMutex);
+    if (!g_noAllocAddr[c->device]) {
+        void *p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_noAllocScratch));
+        if (!p) return fail(MTS_ECUDA, "trace_noalloc: cudaGetSymbolAddress returned a null address");
+        g_noAllocAddr[c->device] = p;
+    }
+    *out = reinterpret_cast<NoAllocScratch *>(g_noAllocAddr[c->device]);
+    return MTS_OK;
+}
+} // namespace
+
+MTS_API int mtscuda_trace_noalloc(MtsContext *c, int64_t n, const float *rays, int32_t shadow, float *hits, int32_t *ids) {
+    if (!c->built) return fail(MTS_ESTATE, "call build() first");
+    if (n < 0 || n > (int64_t)kNoAllocMaxRays)
+        return fail(MTS_EINVAL, "trace_noalloc: " + std::to_string(n) + " rays exceed the fixed scratch of " + std::to_string(kNoAllocMaxRays) +
+                                " rays per call (MTS_NOALLOC_MAX_RAYS); split the batch or use mtscuda_trace");
+    if (c->numKeys > kNoAllocMaxKeys)
+        return fail(MTS_EINVAL, "trace_noalloc: the scene has " + std::to_string(c->numKeys) + " material sort keys, the fixed scratch holds " +
+                                std::to_string(kNoAllocMaxKeys) + "; use mtscuda_trace");
+    if (n == 0) return MTS_OK;
+    if (!rays || !hits) return fail(MTS_EINVAL, "trace_noalloc: rays and hits must not be NULL");
+    NoAllocScratch *s = nullptr;   // a DEVICE pointer: only its members' addresses are taken on the host
+    int rc;
+    if ((rc = noAllocScratch(c, &s))) return rc;
+    cudaStream_t st = c->stream;
+    Wavefront W;
+    std::memset(&W, 0, sizeof(W));
+    W.rayO = s->rayO; W.rayD = s->rayD; W.hit = s->hit; W.shO = s->shO; W.shD = s->shD; W.shC = s->shC; W.L = s->L;
+    W.queue[0] = W.queue[1] = s->queue; W.keys = s->keys; W.keyCount = s->keyCount; W.numKeys = c->numKeys;
+    for (int k = 0; k <= SHADE_CLASSES; ++k) W.classKey[k] = c->classKey[k];
+    W.ctr = &s->ctr; W.capacity = kNoAllocMaxRays;
+    const uint32_t m = (uint32_t)n;
+    // what must start at zero: the counters / cursors and the key histogram k_intersect adds to
+    CUDA_TRY(cudaMemsetAsync(&s->ctr, 0, sizeof(Counters), st));
+    CUDA_TRY(cudaMemsetAsync(s->keyCount, 0, sizeof(uint32_t) * 3 * (size_t)c->numKeys, st));
+    CUDA_TRY(cudaMemcpyAsync(s->raysIn, rays, sizeof(float) * 8 * m, cudaMemcpyDefault, st));    // host or device memory (UVA)
+    k_trace_load<<<gridFor(m), 128, 0, st>>>(W, m, s->raysIn, shadow);
+    const int gridTrace = c->numSMs * TRACE_MINB;
+    if (shadow) k_shadow<false><<<gridTrace, 128, 0, st>>>(c->ds, W);
+    else k_intersect<false><<<gridTrace, 128, 0, st>>>(c->ds, W, 0);
+    k_trace_export<<<gridFor(m), 128, 0, st>>>(c->ds, W, m, shadow, s->hitsOut, s->idsOut);
+    CUDA_TRY(cudaMemcpyAsync(hits, s->hitsOut, sizeof(float) * 4 * m, cudaMemcpyDefault, st));
+    if (ids) CUDA_TRY(cudaMemcpyAsync(ids, s->idsOut, sizeof(int32_t) * 2 * m, cudaMemcpyDefault, st));
+    return syncCheck(c, "trace_noalloc");
 }
 
 MTS_API int mtscuda_hit_records(MtsContext *c, int64_t n, const float *rays, float *out, int32_t *ids) {

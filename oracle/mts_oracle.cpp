@@ -773,6 +773,7 @@ extern "C" {
 MTS_API int32_t mtsoracle_abi_version(void) { return MTS_ABI_VERSION; }
 MTS_API int mtsoracle_create_multi(const int32_t *, int32_t, MtsContext **) { return fail(MTS_EINVAL, "create_multi: devices are a CUDA-library concept"); }
 MTS_API int mtsoracle_device_count(MtsContext *) { return 1; }
+MTS_API int mtsoracle_trace_noalloc(MtsContext *, int64_t, const float *, int32_t, float *, int32_t *) { return fail(MTS_EINVAL, "trace_noalloc: device scratch memory is a CUDA-library concept"); }
 MTS_API const char *mtsoracle_last_error(void) { return g_err.c_str(); }
 
 MTS_API int mtsoracle_create(int, MtsContext **out) {
