@@ -365,10 +365,19 @@ DEVFN void fillHit(const DScene &S, float3 o, float3 d, const RayHit &rh, Hit &i
         // All per-vertex / per-triangle attribute arrays are index-aligned with the positions (zeros where a mesh has
         // none), so every gather is issued unconditionally and back to back -- one memory round trip -- and the
         // shape flags only select what is used.
+        // Sectors per hit: the vertex positions come with the primitive record already loaded above (bit-identical copies),
+        // normals + texcoords from the interleaved array (one 32-byte sector per vertex instead of three 12 / 12 / 8-byte
+        // gathers from separate arrays).
+#if TRI_TEST_WOOP
+        float3 q0 = f3(p0), q1 = f3(p1), q2 = f3(p2);
+#else
         float3 q0 = loadF3(S.positions, i0), q1 = loadF3(S.positions, i1), q2 = loadF3(S.positions, i2);
-        float3 n0 = loadF3(S.normals, i0), n1 = loadF3(S.normals, i1), n2 = loadF3(S.normals, i2);
-        float2 t0 = __ldg(reinterpret_cast<const float2 *>(S.texcoords) + i0), t1 = __ldg(reinterpret_cast<const float2 *>(S.texcoords) + i1),
-               t2 = __ldg(reinterpret_cast<const float2 *>(S.texcoords) + i2);
+#endif
+        const float4 a0 = __ldg(S.vtxAttr + 2 * (size_t)i0), a1 = __ldg(S.vtxAttr + 2 * (size_t)i1), a2 = __ldg(S.vtxAttr + 2 * (size_t)i2);
+        const float v0 = __ldg(reinterpret_cast<const float *>(S.vtxAttr + 2 * (size_t)i0 + 1)), v1 = __ldg(reinterpret_cast<const float *>(S.vtxAttr + 2 * (size_t)i1 + 1)),
+                    v2 = __ldg(reinterpret_cast<const float *>(S.vtxAttr + 2 * (size_t)i2 + 1));
+        float3 n0 = f3(a0), n1 = f3(a1), n2 = f3(a2);
+        float2 t0 = make_float2(a0.w, v0), t1 = make_float2(a1.w, v1), t2 = make_float2(a2.w, v2);
         float3 tgu = loadF3(S.tangents, 2 * (uint32_t)gt), tgv = loadF3(S.tangents, 2 * (uint32_t)gt + 1);
         its.p = q0 * bx + q1 * by + q2 * bz;
         float3 side1 = q1 - q0, side2 = q2 - q0;

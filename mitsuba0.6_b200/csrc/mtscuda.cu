@@ -114,6 +114,8 @@ struct MtsContext {
     bool upPending = false;
     int numSMs = 148;
     bool deferEwa = true;      // staged shade: EWA texture walks as a kernel of their own (MTS_EWA_INLINE=1: inside k_shade_surface)
+    bool raySort = false;      // MTS_RAY_SORT=1: bin the rays of bounce >= 1 by octant and origin cell before k_intersect
+    float sceneLo[3] = {0, 0, 0}, sceneHi[3] = {1, 1, 1};   // bounds of the geometry (BVH root)
     bool leafTextured = false; // a leaf-class material of the built scene reads a bitmap texture
     bool stagedShade = true;   // leaf class as k_shade_surface (+ k_shade_ewa) + k_shade_scatter; default: where its materials are textured
                                // (MTS_SHADE_FUSED=1 / MTS_SHADE_STAGED=1 in the environment force one form)
@@ -200,7 +202,8 @@ int ensureWavefront(MtsContext *c, uint32_t cap) {
     const uint32_t numKeys = c->numKeys;
     for (int k = 0; k <= SHADE_CLASSES; ++k) c->wf.classKey[k] = c->classKey[k];
     const bool needRec = c->stagedShade && c->classKey[SHADE_LEAF] < c->classKey[SHADE_LEAF + 1];
-    if (c->wfCapacity >= cap && c->wf.numKeys == numKeys && needRec == (c->wf.rec != nullptr) && (needRec && c->deferEwa) == (c->wf.ewaJobs != nullptr)) return MTS_OK;
+    if (c->wfCapacity >= cap && c->wf.numKeys == numKeys && needRec == (c->wf.rec != nullptr) && (needRec && c->deferEwa) == (c->wf.ewaJobs != nullptr) &&
+        c->raySort == (c->wf.raySortBin != nullptr)) return MTS_OK;
     c->freeWavefront();
     Wavefront &w = c->wf;
     auto alloc = [&](void **p, size_t bytes) -> cudaError_t {
@@ -216,6 +219,11 @@ int ensureWavefront(MtsContext *c, uint32_t cap) {
     w.rec = nullptr;
     if (needRec)   // surface records of k_shade_surface -> k_shade_scatter
         CUDA_TRY(alloc((void **)&w.rec, sizeof(float4) * (size_t)kSurfRows * cap));
+    w.raySortBin = nullptr;
+    if (c->raySort) {
+        CUDA_TRY(alloc((void **)&w.raySortBin, sizeof(uint32_t) * 3 * kRaySortKeys));
+        CUDA_TRY(cudaMemsetAsync(w.raySortBin, 0, sizeof(uint32_t) * 3 * kRaySortKeys, c->stream));
+    }
     w.ewaJobs = nullptr; w.ewaC = nullptr; w.ewaOrder = nullptr;
     if (needRec && c->deferEwa) {
         CUDA_TRY(alloc((void **)&w.ewaJobs, sizeof(float4) * 2 * (size_t)cap));
@@ -245,6 +253,13 @@ __global__ void k_texels_to_half(const float *__restrict__ src, __half *__restri
         dst[4 * i] = __float2half_rn(src[3 * i]); dst[4 * i + 1] = __float2half_rn(src[3 * i + 1]);
         dst[4 * i + 2] = __float2half_rn(src[3 * i + 2]); dst[4 * i + 3] = __float2half_rn(0.0f);
     }
+}
+// normals + texcoords of every vertex interleaved into one 32-byte record (DScene::vtxAttr)
+__global__ void k_pack_vertex_attrs(const float *__restrict__ nrm, const float *__restrict__ uv, size_t nverts, float4 *__restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nverts) return;
+    out[2 * i] = make_float4(nrm[3 * i], nrm[3 * i + 1], nrm[3 * i + 2], uv[2 * i]);
+    out[2 * i + 1] = make_float4(uv[2 * i + 1], 0.0f, 0.0f, 0.0f);
 }
 // mesh-local vertex indices -> global ones, with the range check of the mesh loaders
 __global__ void k_offset_indices(uint32_t *idx, size_t n, uint32_t nverts, uint32_t vOff, int *err) {
@@ -864,6 +879,16 @@ static int buildOne(MtsContext *c) {
     // geometry already lives on the device (appended by add_mesh)
     S.positions = c->positions.data; S.normals = c->normals.data; S.texcoords = c->texcoords.data;
     S.indices = c->indices.data; S.tangents = c->tangents.data;
+    {
+        const size_t nverts = c->positions.size / 3;
+        float4 *va = nullptr;
+        if (nverts) {
+            CUDA_TRY(devAlloc(&va, sizeof(float4) * 2 * nverts, c->stream));
+            c->sceneAllocs.push_back(va);
+            k_pack_vertex_attrs<<<(unsigned)((nverts + 255) / 256), 256, 0, c->stream>>>(c->normals.data, c->texcoords.data, nverts, va);
+        }
+        S.vtxAttr = va;
+    }
     // area CDFs of emitter meshes: TriMesh::prepareSamplingTable (src/librender/trimesh.cpp:388-403),
     // sequential fp32 accumulation like DiscreteDistribution::append/normalize (host, from a read-back of that mesh)
     std::vector<float> cdfs;
@@ -949,6 +974,7 @@ static int buildOne(MtsContext *c) {
         return fail(MTS_EINVAL, "BVH is " + std::to_string(bout.depth) + " wide levels deep, more than the " + std::to_string(kStackCapacity) +
                     "-entry traversal stack holds (degenerate geometry, e.g. a long chain of nested slivers)");
     S.bvh = bout.nodes; S.prims = bout.prims; S.numPrims = bin.numPrims; S.numNodesBvh = (int)bout.numNodes;
+    for (int a = 0; a < 3; ++a) { c->sceneLo[a] = bin.numPrims ? bout.lo[a] : 0.0f; c->sceneHi[a] = bin.numPrims ? bout.hi[a] : 1.0f; }
     if (c->l2Bytes && bout.numNodes > 0) {
         // nodes are stored level by level (breadth first), so a prefix window covers the top of the tree
         c->l2WindowBytes = std::min<size_t>(sizeof(WideNode) * (size_t)bout.numNodes, c->maxWindow);
@@ -1103,6 +1129,7 @@ static int renderOne(MtsContext *c, const MtsRenderParams *P, volatile const int
     int rc;
     c->stagedShade = getenv("MTS_SHADE_FUSED") ? false : getenv("MTS_SHADE_STAGED") ? true : c->leafTextured;
     c->deferEwa = getenv("MTS_EWA_INLINE") == nullptr;
+    c->raySort = getenv("MTS_RAY_SORT") != nullptr;
     if ((rc = ensureWavefront(c, cap))) return rc;
     const Wavefront &Wf = c->wf;
     if (P->clear_film) CUDA_TRY(cudaMemsetAsync(S.film, 0, sizeof(float4) * (size_t)W * H, st));
@@ -1166,38 +1193,55 @@ static int renderOne(MtsContext *c, const MtsRenderParams *P, volatile const int
                 }
             }
             k_begin_bounce<<<1, 1, 0, st>>>(Wf.ctr, cur);
+            Wavefront Wb = Wf;   // this bounce's view of the wavefront
+            if (Wf.raySortBin && bounce >= 1) {
+                // ray sort: queue[cur] -> `sorted` by (octant, origin cell); for the rest of the bounce the two buffers swap roles
+                // (k_intersect reads the reordered queue, the material sort writes back into the old queue buffer)
+                begin(5);
+                Wavefront Ws = Wf; Ws.keyCount = Wf.raySortBin; Ws.numKeys = kRaySortKeys;
+                RaySortGrid G;
+                G.lo = make_float3(c->sceneLo[0], c->sceneLo[1], c->sceneLo[2]);
+                G.invCell = make_float3(4.0f / std::max(c->sceneHi[0] - c->sceneLo[0], 1e-20f), 4.0f / std::max(c->sceneHi[1] - c->sceneLo[1], 1e-20f),
+                                        4.0f / std::max(c->sceneHi[2] - c->sceneLo[2], 1e-20f));
+                k_raysort_keys<<<gridWide, 256, 0, st>>>(Ws, cur, G);
+                k_raysort_offsets<<<1, 32, 0, st>>>(Ws);
+                k_sort_scatter<<<gridWide, 256, 0, st>>>(Ws, cur);
+                end();
+                launches += 3;
+                Wb.queue[cur] = Wf.sorted; Wb.sorted = Wf.queue[cur];
+            }
             begin(1);
             setBvhWindow(c, st, true);
-            if (P->instrument) k_intersect<true><<<gridTrace, 128, 0, st>>>(S, Wf, cur);
-            else k_intersect<false><<<gridTrace, 128, 0, st>>>(S, Wf, cur);
+            if (P->instrument) k_intersect<true><<<gridTrace, 128, 0, st>>>(S, Wb, cur);
+            else k_intersect<false><<<gridTrace, 128, 0, st>>>(S, Wb, cur);
             setBvhWindow(c, st, false);
             end();
             begin(5);
-            k_sort_offsets<<<1, 32, 0, st>>>(Wf);
-            k_sort_scatter<<<gridWide, 256, 0, st>>>(Wf, cur);
+            k_sort_offsets<<<1, 32, 0, st>>>(Wb);
+            k_sort_scatter<<<gridWide, 256, 0, st>>>(Wb, cur);
             end();
-            begin(6); k_shade_miss<<<gridWide, 256, 0, st>>>(S, Wf, R, cur); end();
+            begin(6); k_shade_miss<<<gridWide, 256, 0, st>>>(S, Wb, R, cur); end();
             begin(2);
             // one instance per shade class that has BSDFs in this scene (each walks its own range of the sorted queue)
-            if (Wf.classKey[SHADE_LAMBERT] < Wf.classKey[SHADE_LAMBERT + 1]) { launchShade<SHADE_LAMBERT>(S, Wf, R, cur, c->numSMs, st); ++launches; }
-            if (Wf.classKey[SHADE_LEAF] < Wf.classKey[SHADE_LEAF + 1]) {
-                if (Wf.rec) {
-                    launchSurface(S, Wf, R, cur, c->numSMs, st);
-                    if (Wf.ewaJobs && bounce == 0) { launchEwa(S, Wf, c->numSMs, st); launches += 4; }   // only camera rays carry differentials (path.cpp:225)
-                    launchScatter(S, Wf, R, cur, c->numSMs, st);
+            if (Wb.classKey[SHADE_LAMBERT] < Wb.classKey[SHADE_LAMBERT + 1]) { launchShade<SHADE_LAMBERT>(S, Wb, R, cur, c->numSMs, st); ++launches; }
+            if (Wb.classKey[SHADE_LEAF] < Wb.classKey[SHADE_LEAF + 1]) {
+                if (Wb.rec) {
+                    launchSurface(S, Wb, R, cur, c->numSMs, st);
+                    if (Wb.ewaJobs && bounce == 0) { launchEwa(S, Wb, c->numSMs, st); launches += 4; }   // only camera rays carry differentials (path.cpp:225)
+                    launchScatter(S, Wb, R, cur, c->numSMs, st);
                     launches += 2;
                 }
-                else { launchShade<SHADE_LEAF>(S, Wf, R, cur, c->numSMs, st); ++launches; }
+                else { launchShade<SHADE_LEAF>(S, Wb, R, cur, c->numSMs, st); ++launches; }
             }
-            if (Wf.classKey[SHADE_GENERIC] < Wf.classKey[SHADE_GENERIC + 1]) { launchShade<SHADE_GENERIC>(S, Wf, R, cur, c->numSMs, st); ++launches; }
+            if (Wb.classKey[SHADE_GENERIC] < Wb.classKey[SHADE_GENERIC + 1]) { launchShade<SHADE_GENERIC>(S, Wb, R, cur, c->numSMs, st); ++launches; }
             end();
             begin(3);
             setBvhWindow(c, st, true);
-            if (P->instrument) k_shadow<true><<<gridTrace, 128, 0, st>>>(S, Wf);
-            else k_shadow<false><<<gridTrace, 128, 0, st>>>(S, Wf);
+            if (P->instrument) k_shadow<true><<<gridTrace, 128, 0, st>>>(S, Wb);
+            else k_shadow<false><<<gridTrace, 128, 0, st>>>(S, Wb);
             setBvhWindow(c, st, false);
             end();
-            begin(4); k_splat<<<gridWide, 256, 0, st>>>(S, Wf, R); end();
+            begin(4); k_splat<<<gridWide, 256, 0, st>>>(S, Wb, R); end();
             launches += 7;
             CUDA_TRY(cudaMemcpyAsync(&c->hostPoll[bounce % kPollRing], &Wf.ctr->qCount[cur ^ 1], sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
             CUDA_TRY(cudaEventRecord(pollEv[bounce % kPollRing], st));

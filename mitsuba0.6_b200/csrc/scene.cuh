@@ -105,6 +105,8 @@ struct DScene : Mats {
     const float *positions;   // 3 floats / vertex
     const float *normals;     // 3 floats / vertex (valid where the shape has normals)
     const float *texcoords;   // 2 floats / vertex
+    const float4 *vtxAttr;    // the same normals and texcoords interleaved, 32 bytes = one sector per vertex: (nx, ny, nz, u), (v, 0, 0, 0);
+                              // what the shade kernels gather (built by mtscuda_build; the separate arrays stay for the emitter code)
     const uint32_t *indices;  // 3 / triangle, already offset into the global vertex arrays
     const float *tangents;    // 6 floats / triangle
     const float *areaCdfs;

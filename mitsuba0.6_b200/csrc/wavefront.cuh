@@ -50,6 +50,7 @@ struct Wavefront {
     uint32_t *keys;          // per queue position, written by intersect
     uint32_t *sorted;        // queue[cur] reordered by key; what shade consumes
     uint32_t *keyCount;      // numKeys histogram, then numKeys offsets, then numKeys cursors
+    uint32_t *raySortBin;    // the same three arrays for the ray sort (kRaySortKeys each; MTS_RAY_SORT=1), else null
     uint32_t numKeys;
     uint32_t classKey[SHADE_CLASSES + 1];   // sort keys [classKey[c], classKey[c+1]) belong to shade class c (key 0 = miss)
     Counters *ctr;
@@ -345,6 +346,42 @@ static __global__ void __launch_bounds__(256) k_sort_scatter(const Wavefront W, 
         __syncthreads();
         if (key != kNoKey) W.sorted[off[key] + sBase[key] + pos] = slot;
         __syncthreads();
+    }
+}
+
+// ---- ray sort (MTS_RAY_SORT=1) -----------------------------------------------------------
+// Bins the rays of a bounce by direction octant and origin cell (8 x 4x4x4 = 512 keys, counting sort like the material
+// sort) before k_intersect, so that the 32 rays a warp pulls from the queue start in the same region of the tree and
+// visit the children of a node in the same order.  Camera rays are coherent already: used from the first bounce on.
+constexpr uint32_t kRaySortKeys = 512;
+struct RaySortGrid { float3 lo, invCell; };
+static __global__ void __launch_bounds__(256) k_raysort_keys(const Wavefront W, int qsel, const RaySortGrid G) {
+    __shared__ uint32_t sCnt[kRaySortKeys];
+    const uint32_t count = W.ctr->qCount[qsel];
+    for (uint32_t k = threadIdx.x; k < kRaySortKeys; k += blockDim.x) sCnt[k] = 0;
+    __syncthreads();
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const uint32_t slot = W.queue[qsel][i];
+        const float4 o = W.rayO[slot], d = W.rayD[slot];
+        const int cx = min(3, max(0, (int)((o.x - G.lo.x) * G.invCell.x))), cy = min(3, max(0, (int)((o.y - G.lo.y) * G.invCell.y))),
+                  cz = min(3, max(0, (int)((o.z - G.lo.z) * G.invCell.z)));
+        const uint32_t oct = (d.x >= 0 ? 1u : 0u) | (d.y >= 0 ? 2u : 0u) | (d.z >= 0 ? 4u : 0u);
+        const uint32_t key = (oct << 6) | (uint32_t)(cz << 4 | cy << 2 | cx);
+        W.keys[i] = key;
+        atomicAdd(&sCnt[key], 1u);
+    }
+    __syncthreads();
+    for (uint32_t k = threadIdx.x; k < kRaySortKeys; k += blockDim.x) { const uint32_t c = sCnt[k]; if (c) atomicAdd(W.keyCount + k, c); }
+}
+static __global__ void k_raysort_offsets(const Wavefront W) {   // one warp; W.keyCount / numKeys = the ray-sort bins
+    uint32_t *cnt = W.keyCount, *off = W.keyCount + W.numKeys, *cur = W.keyCount + 2 * W.numKeys;
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < W.numKeys; base += 32) {
+        const uint32_t k = base + threadIdx.x;
+        uint32_t v = k < W.numKeys ? cnt[k] : 0, incl = v;
+        for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if ((int)threadIdx.x >= o) incl += t; }
+        if (k < W.numKeys) { off[k] = carry + incl - v; cur[k] = 0; cnt[k] = 0; }
+        carry += __shfl_sync(0xffffffffu, incl, 31);
     }
 }
 
