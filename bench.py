@@ -579,6 +579,23 @@ def run_cuda(args):
             line["relmse"] = image_agreement(gpu_film, arm.film, spp_total * args.steps, arm.spp)
             line["rays_per_sample_reference"] = cb["rays_per_sample"]
             del arm
+        if world == 1 and not args.no_cpu_baseline and e2e and reference_built():
+            # Cross-check of `e2e` through the drop-in plugin itself: the unchanged reference host (PluginManager, Scene,
+            # RenderQueue / RenderJob, HDRFilm) renders the same scene at full spp with `cudapath.so` as its integrator --
+            # pageable TriMesh / Bitmap buffers, flattening inside render(), film through Film::put.
+            try:
+                import mtsref
+                t_p = time.time()
+                rp = mtsref.RefScene(sc, integrator="cudapath")
+                rp.render()                                   # first job: context creation, lazy module load
+                rp.render()
+                line["e2e"]["plugin"] = {"value": W * H * spp_total / rp.render_s / 1e6, "unit": "Msamples/s", "ms_per_step": rp.render_s * 1e3,
+                                         "what": "RenderJob of the reference host with integrator `cudapath` (second of two jobs), "
+                                                 "scene flattening + upload + build + render + Film::put inside the job",
+                                         "setup_s": time.time() - t_p}
+                del rp
+            except Exception as e:   # a secondary measurement must never take the headline line down
+                line["e2e"]["plugin"] = {"error": "%s: %s" % (type(e).__name__, e)}
         if world == 1 and args.other_configs and not args.no_cpu_baseline:
             line["other_configs"] = other_configs(args, local)
         print(json.dumps(line), flush=True)

@@ -17,6 +17,16 @@
  * src/bsdfs/roughplastic.cpp serialize()) and that stream is parsed here.  Scenes using plugins outside the scope of
  * the path are rejected with Log(EError, ...), never rendered differently.
  */
+#include <mitsuba/mitsuba.h>
+/* InstanceManager keeps the object <-> id tables of a serialization private; the flattener needs them to get from an id in
+   the stream back to the live Texture (whose texels it then reads through Texture::getBitmap() instead of decoding the
+   image file a second time).  Access only -- the class is compiled inside libmitsuba-core as it is. */
+#if defined(__MITSUBA_CORE_SERIALIZATION_H_)
+#error "serialization.h must not have been included yet"
+#endif
+#define private public
+#include <mitsuba/core/serialization.h>
+#undef private
 #include <mitsuba/render/scene.h>
 #include <mitsuba/render/renderqueue.h>
 #include <mitsuba/render/renderjob.h>
@@ -29,6 +39,8 @@
 #include <mitsuba/core/fstream.h>
 #include <map>
 #include <vector>
+#include <cstdlib>
+#include <sys/time.h>
 
 #include "mtscuda.h"
 
@@ -46,6 +58,28 @@ static StatsCounter statLaunches("cudapath", "CUDA kernel launches");
 static StatsCounter statNormalRays("General", "Normal rays traced");
 static StatsCounter statShadowRays("General", "Shadow rays traced");
 static StatsCounter statAvgPathLength("Path tracer", "Average path length", EAverage);
+
+/* The stream the material graph is serialized into.  BitmapTexture::serialize (src/textures/bitmap.cpp) appends the whole
+   image FILE to the stream, through Stream::copyTo's 512-byte blocks (src/libcore/stream.cpp:428-441) -- a gigabyte of
+   copying for the textures of one scene that the flattener never looks at (it reads the texels from the live texture).
+   This stream keeps everything except those blocks: a write of exactly 512 bytes is counted, not stored, and the parser
+   skips the correspondingly shorter blob (dropped()). */
+class FieldStream : public MemoryStream {
+public:
+    FieldStream() : MemoryStream(4096), m_inRun(false), m_lastStored(0) {}
+    void write(const void *ptr, size_t size) {
+        /* a blob follows its 8-byte length (writeSize); anything else of 512 bytes is an ordinary field */
+        if (size == 512 && (m_inRun || m_lastStored == 8)) { m_dropped[getPos()] += size; m_inRun = true; return; }
+        m_inRun = false; m_lastStored = size;
+        MemoryStream::write(ptr, size);
+    }
+    /* bytes dropped at stored position `pos` */
+    size_t dropped(size_t pos) const { std::map<size_t, size_t>::const_iterator it = m_dropped.find(pos); return it == m_dropped.end() ? 0 : it->second; }
+private:
+    std::map<size_t, size_t> m_dropped;
+    bool m_inRun;
+    size_t m_lastStored;
+};
 
 class CudaPath : public Integrator {
 public:
@@ -94,6 +128,11 @@ public:
     bool render(Scene *scene, RenderQueue *queue, const RenderJob *job, int sceneResID, int sensorResID, int samplerResID) {
         m_cancel = 0;
         MtsContext *ctx = NULL;
+        /* MTS_PLUGIN_TIMING=1: wall-clock of the stages of this call on stderr */
+        const bool timing = getenv("MTS_PLUGIN_TIMING") != NULL;
+        struct Clock { static double now() { timeval tv; gettimeofday(&tv, NULL); return tv.tv_sec + 1e-6 * tv.tv_usec; } };
+        const double tStart = Clock::now();
+        double tCreate = 0, tFlatten = 0, tBuild = 0, tRender = 0;
         if (mtscuda_abi_version() != MTS_ABI_VERSION)
             Log(EError, "libmtscuda implements ABI version %i, this plugin was compiled against version %i -- rebuild both "
                 "from the same include/mtscuda.h", (int) mtscuda_abi_version(), (int) MTS_ABI_VERSION);
@@ -105,9 +144,12 @@ public:
             check(NULL, mtscuda_create(m_device, &ctx));
         bool ok = false;
         try {
+            tCreate = Clock::now();
             Flattener f(this, ctx);
             f.run(scene);
+            tFlatten = Clock::now();
             check(ctx, mtscuda_build(ctx));
+            tBuild = Clock::now();
 
             Film *film = scene->getFilm();
             const Vector2i size = film->getCropSize();
@@ -123,6 +165,7 @@ public:
                 scene->getSampler()->getSampleCount(), m_devices, m_devices > 1 ? "s" : "", m_device);
             MtsStats st;
             int rc = mtscuda_render(ctx, &p, &m_cancel, &st);
+            tRender = Clock::now();
             if (rc == MTS_ECANCELLED) {
                 Log(EWarn, "Rendering was cancelled");
             } else {
@@ -159,6 +202,12 @@ public:
                 }
                 film->put(block);
                 ok = true;
+                if (timing)
+                    fprintf(stderr, "[cudapath] flatten: serialize %.0f ms, getBitmap %.0f ms, half->float + stats %.0f ms, add_texture %.0f ms, add_mesh %.0f ms\n",
+                            f.m_tSerialize * 1e3, f.m_tGetBitmap * 1e3, f.m_tConvert * 1e3, f.m_tAddTexture * 1e3, f.m_tMesh * 1e3);
+                if (timing)
+                    fprintf(stderr, "[cudapath] create %.0f ms, flatten + upload %.0f ms, build %.0f ms, render %.0f ms, film %.0f ms\n",
+                            (tCreate - tStart) * 1e3, (tFlatten - tCreate) * 1e3, (tBuild - tFlatten) * 1e3, (tRender - tBuild) * 1e3, (Clock::now() - tRender) * 1e3);
             }
         } catch (...) {
             mtscuda_destroy(ctx);
@@ -189,7 +238,8 @@ private:
 
     class Flattener {
     public:
-        Flattener(const CudaPath *owner, MtsContext *ctx) : m_owner(owner), m_ctx(ctx) {}
+        Flattener(const CudaPath *owner, MtsContext *ctx) : m_owner(owner), m_ctx(ctx), m_tSerialize(0), m_tGetBitmap(0), m_tConvert(0), m_tAddTexture(0), m_tMesh(0) {}
+        static double now() { timeval tv; gettimeofday(&tv, NULL); return tv.tv_sec + 1e-6 * tv.tv_usec; }
 
         void run(const Scene *scene) {
             sensorAndFilm(scene);
@@ -310,7 +360,9 @@ private:
                 d.uv_tangents = (mesh->hasUVTangents() && d.texcoords) ? 1 : 0;
                 d.nverts = (uint32_t) mesh->getVertexCount(); d.ntris = (uint32_t) mesh->getTriangleCount();
                 d.bsdf = bsdfIndex;
+                const double tM = now();
                 int id = mtscuda_add_mesh(m_ctx, &d);
+                m_tMesh += now() - tM;
                 m_owner->check(m_ctx, id);
                 return id;
             }
@@ -355,10 +407,15 @@ private:
             if (!b) err("shape without a BSDF");
             std::map<const BSDF *, int>::iterator it = m_bsdfIds.find(b);
             if (it != m_bsdfIds.end()) return it->second;
-            ref<MemoryStream> ms = new MemoryStream();
+            ref<FieldStream> ms = new FieldStream();
             ref<InstanceManager> mgr = new InstanceManager();
+            const double tS = now();
             mgr->serialize(ms, b);
+            m_tSerialize += now() - tS;
             ms->seek(0);
+            m_idToObj.clear();                  /* id in the stream -> live object of this serialization */
+            for (std::map<const SerializableObject *, unsigned int>::const_iterator i2 = mgr->m_objToId.begin(); i2 != mgr->m_objToId.end(); ++i2)
+                m_idToObj[i2->second] = i2->first;
             std::map<uint32_t, int> seen;
             std::map<uint32_t, TexInfo> tex;   /* object ids are unique per InstanceManager, i.e. per root BSDF */
             int idx = parseBsdf(ms, seen, tex);
@@ -400,37 +457,68 @@ private:
                 std::string channel = s->readString();
                 size_t size = s->readSize();
                 if (!channel.empty()) err("bitmap `channel` selection is not supported by cudapath");
-                ref<MemoryStream> img = new MemoryStream(size);
-                s->copyTo(img, size);
-                img->seek(0);
-                ref<Bitmap> bmp = new Bitmap(Bitmap::EAuto, img);
-                if (gamma != 0) bmp->setGamma(gamma);
-                const bool mono = bmp->getPixelFormat() == Bitmap::ELuminance || bmp->getPixelFormat() == Bitmap::ELuminanceAlpha;
-                ref<Bitmap> lin = bmp->convert(mono ? Bitmap::ELuminance : Bitmap::ERGB, Bitmap::EFloat32, 1.0f);
-                /* EMIPFilterType: ENearest 0, EBilinear 1, ETrilinear 2, EEWA 3 (mipmap.h) = MTS_FILTER_* */
+                /* the image file itself: not decoded again (see below), and mostly not even stored (FieldStream) */
+                const FieldStream *fs = dynamic_cast<const FieldStream *>(s);
+                const size_t dropped = fs ? fs->dropped(s->getPos()) : 0;
+                if (dropped > size) err("bitmap texture: inconsistent serialization stream");
+                s->seek(s->getPos() + (size - dropped));
                 if (filterType > 3) err("unknown bitmap filter type");
+                /* One upload per live texture object, however many BSDFs (and serializations) refer to it */
+                const SerializableObject *obj = m_idToObj.count(id) ? m_idToObj[id] : NULL;
+                if (!obj) err("bitmap texture: object lookup failed");
+                std::map<const SerializableObject *, TexInfo>::const_iterator hit = m_texByObject.find(obj);
+                if (hit != m_texByObject.end()) { seen[id] = hit->second; return hit->second; }
+                /* Level 0 of the texture's own MIP map (TMIPMap::toBitmap, mipmap.h:486-497): the texels exactly as the
+                   reference looks them up -- gamma-corrected, clamped, rounded to half */
+                const Texture *texObj = static_cast<const Texture *>(obj);
+                const double tG = now();
+                ref<Bitmap> level0 = texObj->getBitmap(Vector2i(-1, -1));
+                m_tGetBitmap += now() - tG;
+                const bool mono = level0->getPixelFormat() == Bitmap::ELuminance || level0->getPixelFormat() == Bitmap::ELuminanceAlpha;
+                (void) gamma;
                 MtsTextureDesc d;
                 memset(&d, 0, sizeof(d));
-                d.width = lin->getWidth(); d.height = lin->getHeight(); d.channels = mono ? 1 : 3;
+                d.width = level0->getWidth(); d.height = level0->getHeight(); d.channels = mono ? 1 : 3;
                 /* ReconstructionFilter::EBoundaryCondition: EClamp 0, ERepeat 1, EMirror 2, EZero 3, EOne 4 */
                 static const int wrapMap[5] = { MTS_WRAP_CLAMP, MTS_WRAP_REPEAT, MTS_WRAP_MIRROR, MTS_WRAP_ZERO, MTS_WRAP_ONE };
                 d.wrap_u = wrapMap[std::min(wrapU, 4u)]; d.wrap_v = wrapMap[std::min(wrapV, 4u)];
-                d.filter = (int32_t) filterType;
+                d.filter = (int32_t) filterType;            /* EMIPFilterType: ENearest 0, EBilinear 1, ETrilinear 2, EEWA 3 = MTS_FILTER_* */
                 d.max_anisotropy = maxAnisotropy;           /* already forced to 1 for non-EWA filters (bitmap.cpp:232-233) */
                 d.uv_scale[0] = uvScale.x; d.uv_scale[1] = uvScale.y; d.uv_offset[0] = uvOffset.x; d.uv_offset[1] = uvOffset.y;
-                int tid = mtscuda_add_texture(m_ctx, &d, lin->getFloat32Data());
-                m_owner->check(m_ctx, tid);
-                /* statistics on the half-precision texels the MIP map stores */
-                const float *px = lin->getFloat32Data();
-                const size_t n = (size_t) d.width * d.height;
+                /* half -> float on all host cores, statistics (Texture::getMinimum / getMaximum / getAverage) in the same pass */
+                const size_t n = (size_t) d.width * d.height, nval = n * (size_t) d.channels;
+                if (level0->getComponentFormat() != Bitmap::EFloat16 || level0->getChannelCount() != d.channels)
+                    err("bitmap texture: unexpected MIP map storage format");
+                const double tC = now();
+                const half *src = (const half *) level0->getData();
+                /* not a std::vector: its zero-fill would touch the 0.2 GB of a 4096^2 RGB image once more, on one thread */
+                struct FloatBuf { float *p; FloatBuf(size_t n) : p((float *) malloc(sizeof(float) * std::max<size_t>(n, 1))) {} ~FloatBuf() { free(p); } } texelBuf(nval);
+                if (!texelBuf.p) err("out of memory");
+                float *texels = texelBuf.p;
                 double sum[3] = {0, 0, 0}; float mn[3] = {1e30f, 1e30f, 1e30f}, mx[3] = {-1e30f, -1e30f, -1e30f};
-                for (size_t i = 0; i < n; ++i) for (int c = 0; c < 3; ++c) {
-                    float v = (float) half(px[d.channels == 1 ? i : 3 * i + c]);
-                    sum[c] += v; mn[c] = std::min(mn[c], v); mx[c] = std::max(mx[c], v);
+                const int ch = d.channels;
+                #pragma omp parallel
+                {
+                    double lsum[3] = {0, 0, 0}; float lmn[3] = {1e30f, 1e30f, 1e30f}, lmx[3] = {-1e30f, -1e30f, -1e30f};
+                    #pragma omp for schedule(static) nowait
+                    for (long long i = 0; i < (long long) n; ++i) for (int c = 0; c < ch; ++c) {
+                        const float v = (float) src[(size_t) i * ch + c];
+                        texels[(size_t) i * ch + c] = v;
+                        lsum[c] += v; lmn[c] = std::min(lmn[c], v); lmx[c] = std::max(lmx[c], v);
+                    }
+                    #pragma omp critical
+                    for (int c = 0; c < ch; ++c) { sum[c] += lsum[c]; mn[c] = std::min(mn[c], lmn[c]); mx[c] = std::max(mx[c], lmx[c]); }
                 }
+                if (ch == 1) { sum[1] = sum[2] = sum[0]; mn[1] = mn[2] = mn[0]; mx[1] = mx[2] = mx[0]; }
+                const double tA = now();
+                m_tConvert += tA - tC;
+                int tid = mtscuda_add_texture(m_ctx, &d, texels);
+                m_owner->check(m_ctx, tid);
+                m_tAddTexture += now() - tA;
                 t.ref.scale[0] = t.ref.scale[1] = t.ref.scale[2] = 1; t.ref.tex = tid; t.constant = false;
                 t.min.fromLinearRGB(mn[0], mn[1], mn[2]); t.max.fromLinearRGB(mx[0], mx[1], mx[2]);
                 t.avg.fromLinearRGB((Float) (sum[0] / n), (Float) (sum[1] / n), (Float) (sum[2] / n));
+                m_texByObject[obj] = t;
             } else
                 err("texture class " + cls + " is out of scope (bitmap, scale, constants)");
             seen[id] = t;
@@ -625,6 +713,11 @@ private:
         std::vector<MtsBsdfNode> m_nodes;
         std::vector<float> m_pool;
         std::map<const BSDF *, int> m_bsdfIds;
+    public:
+        double m_tSerialize, m_tGetBitmap, m_tConvert, m_tAddTexture, m_tMesh;   /* MTS_PLUGIN_TIMING */
+    private:
+        std::map<uint32_t, const SerializableObject *> m_idToObj;           /* of the serialization being parsed */
+        std::map<const SerializableObject *, TexInfo> m_texByObject;        /* uploaded bitmap textures */
     };
 
     int m_maxDepth, m_rrDepth, m_device, m_devices;
