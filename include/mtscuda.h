@@ -185,7 +185,10 @@ typedef struct MtsTextureDesc {
     float uv_scale[2];      /* Texture2D uscale/vscale, src/librender/texture.cpp:84-94 */
     float uv_offset[2];
     float max_anisotropy;   /* bitmap.cpp:230-233: `maxAnisotropy` (default 20) for ewa, forced to 1 otherwise */
+    int32_t texel_format;   /* MTS_TEXEL_F32 (0): `texels` are float32; MTS_TEXEL_F16: IEEE half, the storage type of TMIPMap
+                               (mipmap.h:143-160) -- what Texture::getBitmap() of a live reference texture hands out */
 } MtsTextureDesc;
+enum { MTS_TEXEL_F32 = 0, MTS_TEXEL_F16 = 1 };
 
 /* ---- sensor (src/sensors/perspective.cpp:126-178, 271-297) ------------------ */
 typedef struct MtsCamera {
@@ -280,7 +283,7 @@ typedef struct MtsContext MtsContext;
 /* Bumped whenever a struct or signature of this header changes.  A host compiled against another version would hand
  * the library structs of the wrong size (MtsStats is written through a caller-provided pointer), so every binding
  * compares MTS_FN(abi_version)() with the MTS_ABI_VERSION it was compiled with before the first call. */
-#define MTS_ABI_VERSION 5
+#define MTS_ABI_VERSION 6
 MTS_API int32_t MTS_FN(abi_version)(void);
 MTS_API const char *MTS_FN(last_error)(void);
 MTS_API int MTS_FN(create)(int device, MtsContext **out);

@@ -50,7 +50,7 @@ class BsdfNode(C.Structure):
 class TextureDesc(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("channels", C.c_int32),
                 ("wrap_u", C.c_int32), ("wrap_v", C.c_int32), ("filter", C.c_int32),
-                ("uv_scale", C.c_float * 2), ("uv_offset", C.c_float * 2), ("max_anisotropy", C.c_float)]
+                ("uv_scale", C.c_float * 2), ("uv_offset", C.c_float * 2), ("max_anisotropy", C.c_float), ("texel_format", C.c_int32)]
 
 
 class Camera(C.Structure):
@@ -102,7 +102,7 @@ class Stats(C.Structure):
 
 
 # every symbol include/mtscuda.h declares (tests check that the libraries export all of them)
-ABI_VERSION = 5   # MTS_ABI_VERSION of include/mtscuda.h these mirrors were written against
+ABI_VERSION = 6   # MTS_ABI_VERSION of include/mtscuda.h these mirrors were written against
 ABI_SYMBOLS = [
     "abi_version", "last_error", "create", "create_multi", "device_count", "destroy", "set_camera", "set_film", "add_texture", "set_float_pool",
     "set_bsdfs", "add_mesh", "add_rectangle", "add_sphere", "add_emitter", "build", "render",
@@ -273,6 +273,8 @@ class Context:
         self._check(self.fn["set_film"](self.h, C.byref(film)))
 
     def add_texture(self, desc, texels):
+        if desc.texel_format == 1:      # MTS_TEXEL_F16: an object holding a contiguous float16 array `.a`
+            return self._check(self.fn["add_texture"](self.h, C.byref(desc), texels.a.ctypes.data_as(C.c_void_p)))
         t = f32(texels)
         return self._check(self.fn["add_texture"](self.h, C.byref(desc), ptr(t)))
 

@@ -254,6 +254,10 @@ __global__ void k_texels_to_half(const float *__restrict__ src, __half *__restri
         dst[4 * i + 2] = __float2half_rn(src[3 * i + 2]); dst[4 * i + 3] = __float2half_rn(0.0f);
     }
 }
+__global__ void k_half_to_float(const __half *__restrict__ src, float *__restrict__ dst, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = __half2float(src[i]);
+}
 // normals + texcoords of every vertex interleaved into one 32-byte record (DScene::vtxAttr)
 __global__ void k_pack_vertex_attrs(const float *__restrict__ nrm, const float *__restrict__ uv, size_t nverts, float4 *__restrict__ out) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -727,6 +731,7 @@ MTS_API int mtscuda_add_texture(MtsContext *c, const MtsTextureDesc *d, const fl
     if (d->channels != 1 && d->channels != 3) return fail(MTS_EINVAL, "texture channels must be 1 or 3");
     if (d->width <= 0 || d->height <= 0) return fail(MTS_EINVAL, "bad texture size");
     if (d->filter < MTS_FILTER_NEAREST || d->filter > MTS_FILTER_EWA) return fail(MTS_EINVAL, "unknown texture filter type");
+    if (d->texel_format != MTS_TEXEL_F32 && d->texel_format != MTS_TEXEL_F16) return fail(MTS_EINVAL, "unknown texel format");
     CUDA_TRY(cudaSetDevice(c->device));
     HostTex t; t.d = *d;
     const size_t npix = (size_t)d->width * d->height;
@@ -741,7 +746,16 @@ MTS_API int mtscuda_add_texture(MtsContext *c, const MtsTextureDesc *d, const fl
         ~StreamSwap() { c->stream = saved; }
     } swap(c);
     CUDA_TRY(devAlloc(&raw, sizeof(float) * npix * d->channels, c->stream));
-    cudaError_t e = cudaMemcpyAsync(raw, texels, sizeof(float) * npix * d->channels, cudaMemcpyDefault, c->stream);
+    cudaError_t e;
+    if (d->texel_format == MTS_TEXEL_F16) {   // half texels: half the bytes over PCIe, widened on the device (exact)
+        __half *rawHalf = nullptr;
+        CUDA_TRY(devAlloc(&rawHalf, sizeof(__half) * npix * d->channels, c->stream));
+        e = cudaMemcpyAsync(rawHalf, texels, sizeof(__half) * npix * d->channels, cudaMemcpyDefault, c->stream);
+        const size_t nval = npix * d->channels;
+        if (e == cudaSuccess) k_half_to_float<<<(unsigned)((nval + 255) / 256), 256, 0, c->stream>>>(rawHalf, raw, nval);
+        devFree(rawHalf, c->stream);
+    } else
+        e = cudaMemcpyAsync(raw, texels, sizeof(float) * npix * d->channels, cudaMemcpyDefault, c->stream);
     int rc = MTS_OK;
     if (e == cudaSuccess) rc = buildPyramid(c, raw, d->width, d->height, d->channels, d->wrap_u, d->wrap_v, d->filter, d->max_anisotropy, 1.0f /* TMIPMap maxValue default */, t.dt, &t.bytes);
     devFree(raw, c->stream);

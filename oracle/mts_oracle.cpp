@@ -797,6 +797,20 @@ MTS_API int mtsoracle_add_texture(MtsContext *c, const MtsTextureDesc *d, const 
     if (d->channels != 1 && d->channels != 3) return fail(MTS_EINVAL, "texture channels must be 1 or 3");
     if (d->filter < MTS_FILTER_NEAREST || d->filter > MTS_FILTER_EWA) return fail(MTS_EINVAL, "unknown texture filter type");
     Tex t; t.d = *d;
+    std::vector<float> fromHalf;
+    if (d->texel_format == MTS_TEXEL_F16) {   /* IEEE half input: widen (exact) */
+        const uint16_t *h = reinterpret_cast<const uint16_t *>(texels);
+        fromHalf.resize((size_t)d->width * d->height * d->channels);
+        for (size_t i = 0; i < fromHalf.size(); ++i) {
+            const uint32_t sign = (uint32_t)(h[i] & 0x8000u) << 16, e = (h[i] >> 10) & 0x1fu, m = h[i] & 0x3ffu;
+            float v;
+            if (e == 0) v = std::ldexp((float)m, -24);
+            else if (e == 31) v = m ? NAN : INFINITY;
+            else v = std::ldexp((float)(m | 0x400u), (int)e - 25);
+            fromHalf[i] = sign ? -v : v;
+        }
+        texels = fromHalf.data();
+    } else if (d->texel_format != MTS_TEXEL_F32) return fail(MTS_EINVAL, "unknown texel format");
     t.mip.build(texels, d->width, d->height, d->channels, d->wrap_u, d->wrap_v, d->filter, d->max_anisotropy, 1.0f /* TMIPMap maxValue default */);
     c->mat.textures.push_back(std::move(t));
     return (int)c->mat.textures.size() - 1;

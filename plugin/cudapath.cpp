@@ -96,6 +96,10 @@ public:
         if (m_devices < 1 || m_devices > 16)
             Log(EError, "'devices' must be between 1 and 16!");
         m_seed = (uint32_t) props.getInteger("seed", 0);
+        /* `exactTextures` (default true; false, or MTS_CUDAPATH_FAST_TEXTURES=1 in the environment, selects the fast route):
+           build the MIP pyramids from the decoded image FILES like the reference does, instead of from level 0 of the
+           reference's own pyramid (see parseTexture) */
+        m_exactTextures = props.getBoolean("exactTextures", getenv("MTS_CUDAPATH_FAST_TEXTURES") == NULL);
         if (m_rrDepth <= 0)
             Log(EError, "'rrDepth' must be set to a value greater than zero!");
         if (m_maxDepth <= 0 && m_maxDepth != -1)
@@ -110,6 +114,7 @@ public:
         m_device = stream->readInt();
         m_devices = stream->readInt();
         m_seed = stream->readUInt();
+        m_exactTextures = stream->readBool();
     }
 
     void serialize(Stream *stream, InstanceManager *manager) const {
@@ -121,6 +126,7 @@ public:
         stream->writeInt(m_device);
         stream->writeInt(m_devices);
         stream->writeUInt(m_seed);
+        stream->writeBool(m_exactTextures);
     }
 
     void cancel() { m_cancel = 1; }   /* may arrive from another thread (scene.cpp:451-456) */
@@ -203,7 +209,7 @@ public:
                 film->put(block);
                 ok = true;
                 if (timing)
-                    fprintf(stderr, "[cudapath] flatten: serialize %.0f ms, getBitmap %.0f ms, half->float + stats %.0f ms, add_texture %.0f ms, add_mesh %.0f ms\n",
+                    fprintf(stderr, "[cudapath] flatten: serialize %.0f ms, getBitmap %.0f ms, texel statistics %.0f ms, add_texture %.0f ms, add_mesh %.0f ms\n",
                             f.m_tSerialize * 1e3, f.m_tGetBitmap * 1e3, f.m_tConvert * 1e3, f.m_tAddTexture * 1e3, f.m_tMesh * 1e3);
                 if (timing)
                     fprintf(stderr, "[cudapath] create %.0f ms, flatten + upload %.0f ms, build %.0f ms, render %.0f ms, film %.0f ms\n",
@@ -470,9 +476,22 @@ private:
                 if (hit != m_texByObject.end()) { seen[id] = hit->second; return hit->second; }
                 /* Level 0 of the texture's own MIP map (TMIPMap::toBitmap, mipmap.h:486-497): the texels exactly as the
                    reference looks them up -- gamma-corrected, clamped, rounded to half */
+                /* Default (exactTextures): decode the image file and hand over the unrounded floats -- the library then builds
+                   the same pyramid as the reference, bit for bit (about 0.05 s per 4096^2 PFM image, more for compressed
+                   formats).  Fast route: level 0 of the texture's own MIP map as half texels; identical at level 0, but the
+                   coarser levels are then resampled from half-rounded texels where the reference resamples the unrounded
+                   image: a fraction of the texels of levels >= 1 differ by one half ulp (4.9e-4 relative). */
                 const Texture *texObj = static_cast<const Texture *>(obj);
                 const double tG = now();
-                ref<Bitmap> level0 = texObj->getBitmap(Vector2i(-1, -1));
+                ref<Bitmap> level0;
+                if (m_owner->m_exactTextures && !filename.empty() && fs::exists(fs::path(filename))) {
+                    ref<FileStream> is = new FileStream(fs::path(filename), FileStream::EReadOnly);
+                    ref<Bitmap> bmp = new Bitmap(Bitmap::EAuto, is);
+                    if (gamma != 0) bmp->setGamma(gamma);
+                    const bool monoFile = bmp->getPixelFormat() == Bitmap::ELuminance || bmp->getPixelFormat() == Bitmap::ELuminanceAlpha;
+                    level0 = bmp->convert(monoFile ? Bitmap::ELuminance : Bitmap::ERGB, Bitmap::EFloat32, 1.0f);
+                } else
+                    level0 = texObj->getBitmap(Vector2i(-1, -1));
                 m_tGetBitmap += now() - tG;
                 const bool mono = level0->getPixelFormat() == Bitmap::ELuminance || level0->getPixelFormat() == Bitmap::ELuminanceAlpha;
                 (void) gamma;
@@ -485,16 +504,16 @@ private:
                 d.filter = (int32_t) filterType;            /* EMIPFilterType: ENearest 0, EBilinear 1, ETrilinear 2, EEWA 3 = MTS_FILTER_* */
                 d.max_anisotropy = maxAnisotropy;           /* already forced to 1 for non-EWA filters (bitmap.cpp:232-233) */
                 d.uv_scale[0] = uvScale.x; d.uv_scale[1] = uvScale.y; d.uv_offset[0] = uvOffset.x; d.uv_offset[1] = uvOffset.y;
-                /* half -> float on all host cores, statistics (Texture::getMinimum / getMaximum / getAverage) in the same pass */
-                const size_t n = (size_t) d.width * d.height, nval = n * (size_t) d.channels;
-                if (level0->getComponentFormat() != Bitmap::EFloat16 || level0->getChannelCount() != d.channels)
-                    err("bitmap texture: unexpected MIP map storage format");
+                /* the half texels go to the library as they are (MTS_TEXEL_F16); one parallel pass over them for the statistics
+                   (Texture::getMinimum / getMaximum / getAverage) */
+                const size_t n = (size_t) d.width * d.height;
+                const bool isHalf = level0->getComponentFormat() == Bitmap::EFloat16;
+                if ((!isHalf && level0->getComponentFormat() != Bitmap::EFloat32) || level0->getChannelCount() != d.channels)
+                    err("bitmap texture: unexpected texel storage format");
                 const double tC = now();
                 const half *src = (const half *) level0->getData();
-                /* not a std::vector: its zero-fill would touch the 0.2 GB of a 4096^2 RGB image once more, on one thread */
-                struct FloatBuf { float *p; FloatBuf(size_t n) : p((float *) malloc(sizeof(float) * std::max<size_t>(n, 1))) {} ~FloatBuf() { free(p); } } texelBuf(nval);
-                if (!texelBuf.p) err("out of memory");
-                float *texels = texelBuf.p;
+                const float *srcF = (const float *) level0->getData();
+                d.texel_format = isHalf ? MTS_TEXEL_F16 : MTS_TEXEL_F32;
                 double sum[3] = {0, 0, 0}; float mn[3] = {1e30f, 1e30f, 1e30f}, mx[3] = {-1e30f, -1e30f, -1e30f};
                 const int ch = d.channels;
                 #pragma omp parallel
@@ -502,8 +521,8 @@ private:
                     double lsum[3] = {0, 0, 0}; float lmn[3] = {1e30f, 1e30f, 1e30f}, lmx[3] = {-1e30f, -1e30f, -1e30f};
                     #pragma omp for schedule(static) nowait
                     for (long long i = 0; i < (long long) n; ++i) for (int c = 0; c < ch; ++c) {
-                        const float v = (float) src[(size_t) i * ch + c];
-                        texels[(size_t) i * ch + c] = v;
+                        /* statistics on the half values the MIP map stores, whichever form is uploaded */
+                        const float v = isHalf ? (float) src[(size_t) i * ch + c] : (float) half(srcF[(size_t) i * ch + c]);
                         lsum[c] += v; lmn[c] = std::min(lmn[c], v); lmx[c] = std::max(lmx[c], v);
                     }
                     #pragma omp critical
@@ -512,7 +531,7 @@ private:
                 if (ch == 1) { sum[1] = sum[2] = sum[0]; mn[1] = mn[2] = mn[0]; mx[1] = mx[2] = mx[0]; }
                 const double tA = now();
                 m_tConvert += tA - tC;
-                int tid = mtscuda_add_texture(m_ctx, &d, texels);
+                int tid = mtscuda_add_texture(m_ctx, &d, srcF);
                 m_owner->check(m_ctx, tid);
                 m_tAddTexture += now() - tA;
                 t.ref.scale[0] = t.ref.scale[1] = t.ref.scale[2] = 1; t.ref.tex = tid; t.constant = false;
@@ -721,7 +740,7 @@ private:
     };
 
     int m_maxDepth, m_rrDepth, m_device, m_devices;
-    bool m_strictNormals, m_hideEmitters;
+    bool m_strictNormals, m_hideEmitters, m_exactTextures;
     uint32_t m_seed;
     volatile int m_cancel;
 };

@@ -459,3 +459,23 @@ def test_mip_scene_large_footprints_vs_oracle(mip_pair, count):
     print("relMSE(mip, sample_count %d, GPU 2048 spp vs oracle 2048 spp) = %.3g" % (count, err))
     # noise floor of two independent 2048-spp renders of this scene: ~6.5e-4 (measured with the oracle)
     assert abs(a.mean() / b.mean() - 1) < 0.01 and err < 1.5e-3, (count, err, a.mean(), b.mean())
+
+
+def test_half_texel_input_equals_float_input(mip_pair):
+    """MtsTextureDesc.texel_format = MTS_TEXEL_F16 (the plugin's texture path) gives the same pyramid as float input."""
+    import copy
+    gpu, _, flat, tex, _ = mip_pair
+    flat_h = copy.copy(gpu.flat)
+    flat_h.textures = []
+    for d, t in gpu.flat.textures:
+        d2 = abi.TextureDesc.from_buffer_copy(d)
+        d2.texel_format = 1
+        flat_h.textures.append((d2, util.HalfTexels(np.maximum(t, 0).astype(np.float16))))
+    g2 = M.CudaPath(flat_h)
+    g2.preprocess()
+    uv, duv = G.texture_inputs(sorted(tex)[0])
+    for tid in range(len(gpu.flat.textures)):
+        # (see the oracle test of the same name: level 0 identical, coarser levels within a half ulp)
+        assert np.array_equal(gpu.ctx.texture_eval(tid, uv), g2.ctx.texture_eval(tid, uv))
+        assert np.abs(gpu.ctx.texture_eval(tid, uv, duv) - g2.ctx.texture_eval(tid, uv, duv)).max() < 1e-3
+    g2.close()

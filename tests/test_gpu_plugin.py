@@ -74,16 +74,20 @@ def test_cudapath_plugin_boundary_cases(name, bar):
 
 
 @needs_ref
-def test_cudapath_plugin_default_filter_type_scene():
+@pytest.mark.parametrize("exact", [True, False])
+def test_cudapath_plugin_default_filter_type_scene(exact, monkeypatch):
     """Stock bitmap textures (filterType ewa, maxAnisotropy 20) and the filtered environment map through the plugin:
-    usesRayDifferentials() of the live BSDFs decides which hits get uv partials."""
+    usesRayDifferentials() of the live BSDFs decides which hits get uv partials.  Both texture routes of the plugin:
+    the re-decoded image file (`exactTextures`, the default) and level 0 of the live MIP map as half texels."""
+    if not exact:
+        monkeypatch.setenv("MTS_CUDAPATH_FAST_TEXTURES", "1")
     gold = G.load("mip.npz")
     sc = G.mip()[0]
     rs = mtsref.RefScene(sc, integrator="cudapath")
     img = M.develop(rs.render())
     ref = gold["image/mip/rgb"].astype(np.float32)
     err = M.rel_mse(img, ref)
-    print("cudapath.so inside the reference host: relMSE(mip) = %.3g" % err)
+    print("cudapath.so inside the reference host: relMSE(mip%s) = %.3g" % ("" if exact else ", fast texture route", err))
     assert abs(img.mean() / ref.mean() - 1) < 0.02 and err < 3e-3, err
 
 

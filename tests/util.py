@@ -481,3 +481,11 @@ def mip_scene(width=96, height=64, spp=4, envmap=True):
         env.data["bitmap"] = scenes.synthetic_envmap(160, 80)
         sc.add(env)
     return sc, t, mats
+
+
+class HalfTexels:
+    """float16 texels for Context.add_texture with texel_format = MTS_TEXEL_F16 (passed through as raw memory)."""
+
+    def __init__(self, a):
+        self.a = np.ascontiguousarray(a, dtype=np.float16)
+        self.nbytes = self.a.nbytes
