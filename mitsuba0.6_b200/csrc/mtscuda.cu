@@ -136,6 +136,7 @@ struct MtsContext {
     DScene ds;
     std::vector<void *> sceneAllocs;
     bool built = false;
+    bool peerFilm = false;     // peer of a multi-device group: film / alpha plane from cudaMalloc, readable by the primary over NVLink
     float4 *filmInternal = nullptr, *filmBound = nullptr;
     float *filmAlpha = nullptr;                               // sum w * alpha (films with an alpha channel only)
     uint32_t *hostPoll = nullptr;                             // pinned: next-queue sizes polled without blocking
@@ -163,6 +164,11 @@ struct MtsContext {
     }
     void freeWavefront() { for (void *p : wfAllocs) devFree(p, stream); wfAllocs.clear(); wfCapacity = 0; }
     float4 *filmPtr() const { return filmBound ? filmBound : filmInternal; }
+    void freeFilm() {
+        if (peerFilm) { if (filmInternal || filmAlpha) cudaStreamSynchronize(stream); cudaFree(filmInternal); cudaFree(filmAlpha); }
+        else { devFree(filmInternal, stream); devFree(filmAlpha, stream); }
+        filmInternal = nullptr; filmAlpha = nullptr;
+    }
 };
 
 namespace {
@@ -691,7 +697,7 @@ MTS_API void mtscuda_destroy(MtsContext *c) {
     c->peers.clear();
     cudaSetDevice(c->device);
     c->freeScene(); c->freeWavefront(); c->freeGeometry();
-    devFree(c->filmInternal, c->stream); devFree(c->filmAlpha, c->stream); devFree(c->ewaLut, c->stream);
+    c->freeFilm(); devFree(c->ewaLut, c->stream);
     cudaStreamSynchronize(c->stream);
     for (cudaEvent_t e : c->eventPool) cudaEventDestroy(e);
     if (c->hostPoll) cudaFreeHost(c->hostPoll);
@@ -710,14 +716,15 @@ MTS_API int mtscuda_set_camera(MtsContext *c, const MtsCamera *cam) {
 MTS_API int mtscuda_set_film(MtsContext *c, const MtsFilm *f) {
     if (f->width <= 0 || f->height <= 0 || !(f->filter_radius > 0)) return fail(MTS_EINVAL, "bad film description");
     CUDA_TRY(cudaSetDevice(c->device));
-    devFree(c->filmInternal, c->stream); c->filmInternal = nullptr;
-    devFree(c->filmAlpha, c->stream); c->filmAlpha = nullptr;
+    c->freeFilm();
     c->film = *f; c->hasFilm = true; c->filmBound = nullptr;
     size_t bytes = sizeof(float4) * (size_t)f->width * f->height;
-    CUDA_TRY(devAlloc(&c->filmInternal, bytes, c->stream));
+    if (c->peerFilm) CUDA_TRY(cudaMalloc((void **)&c->filmInternal, bytes));
+    else CUDA_TRY(devAlloc(&c->filmInternal, bytes, c->stream));
     CUDA_TRY(cudaMemsetAsync(c->filmInternal, 0, bytes, c->stream));
     if (f->has_alpha) {
-        CUDA_TRY(devAlloc(&c->filmAlpha, bytes / 4, c->stream));
+        if (c->peerFilm) CUDA_TRY(cudaMalloc((void **)&c->filmAlpha, bytes / 4));
+        else CUDA_TRY(devAlloc(&c->filmAlpha, bytes / 4, c->stream));
         CUDA_TRY(cudaMemsetAsync(c->filmAlpha, 0, bytes / 4, c->stream));
     }
     c->ds.filmAlpha = c->filmAlpha;
@@ -1410,6 +1417,11 @@ MTS_API int mtscuda_create_multi(const int32_t *devices, int32_t n, MtsContext *
         // the primary reads the peers' films; the peers pull the scene from the primary
         cudaSetDevice(devices[0]); if (cudaDeviceEnablePeerAccess(devices[i], 0) != cudaSuccess) cudaGetLastError();   // already enabled is fine
         cudaSetDevice(devices[i]); if (cudaDeviceEnablePeerAccess(devices[0], 0) != cudaSuccess) cudaGetLastError();
+        // The peers' films are read by the primary's reduce kernel.  Memory of the stream-ordered pools (devmem.h) is private to
+        // its device -- cudaDeviceEnablePeerAccess covers cudaMalloc memory only, and opening the pools with
+        // cudaMemPoolSetAccess made the large allocations of a 10 M-triangle scene fail with "out of memory" -- so the film of
+        // a peer context is a plain cudaMalloc allocation (set_film).
+        p->peerFilm = true;
     }
     cudaSetDevice(devices[0]);
     *out = c;
