@@ -118,51 +118,6 @@ def pin_scene(flat):
     return flat
 
 
-def gather_scene(flat, rank, world):
-    """End-to-end leg with N ranks: every rank copies 1/N of each large scene array from pinned host memory to its GPU
-    over its own PCIe link, and one NCCL all-gather per array over NVLink gives every GPU the whole scene -- each host byte
-    crosses PCIe once per JOB instead of once per rank.  Returns a shallow copy of `flat` whose large arrays are
-    abi.DeviceArray views of the gathered buffers (libmtscuda takes them like host buffers: cudaMemcpyDefault), and the
-    bytes this rank copied host to device."""
-    import copy
-    import torch
-    import torch.distributed as dist
-    from mitsuba0_6_b200 import abi
-    h2d = 0
-    keep = []
-
-    def gather(a):
-        nonlocal h2d
-        if not isinstance(a, np.ndarray) or a.nbytes < (1 << 16):
-            return a
-        assert a.dtype.itemsize == 4 and a.flags["C_CONTIGUOUS"]
-        flat32 = a.reshape(-1).view(np.int32)                      # float32 / uint32 travel as 32-bit words
-        n = flat32.size
-        chunk = (n + world - 1) // world
-        lo, hi = min(rank * chunk, n), min((rank + 1) * chunk, n)
-        full = torch.empty(world * chunk, dtype=torch.int32, device="cuda")
-        mine = full[rank * chunk:(rank + 1) * chunk]
-        if hi > lo:
-            mine[:hi - lo].copy_(torch.from_numpy(flat32[lo:hi]), non_blocking=True)   # pinned host -> this rank's slice
-            h2d += 4 * (hi - lo)
-        dist.all_gather_into_tensor(full, mine)                    # in place: every rank contributes its own slice
-        keep.append(full)
-        return abi.DeviceArray(full.data_ptr(), a.shape, a.dtype, owner=full)
-
-    f2 = copy.copy(flat)
-    f2.textures = [(d, gather(t)) for d, t in flat.textures]
-    f2.emitters = [(d, gather(t) if t is not None else None) for d, t in flat.emitters]
-    shapes = []
-    for s in flat.shapes:
-        if s[0] == "mesh":
-            s = (s[0], {k: gather(v) for k, v in s[1].items()}) + tuple(s[2:])
-        shapes.append(s)
-    f2.shapes = shapes
-    f2._gathered = keep
-    torch.cuda.current_stream().synchronize()    # the library reads the buffers on its own stream
-    return f2, h2d
-
-
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
 
@@ -485,7 +440,7 @@ def run_cuda(args):
             sync()
             t0 = time.time()
             if world > 1:     # sharded upload + NVLink all-gather (see gather_scene)
-                flat_e2e, h2d_rank = gather_scene(flat, rank, world)
+                flat_e2e, h2d_rank = M.sharding.gather_scene(flat, rank, world)
                 t_gather = time.time()
             else:
                 flat_e2e, h2d_rank, t_gather = flat, h2d, t0

@@ -203,6 +203,12 @@ class DeviceArray:
     def nbytes(self):
         return self.size * self.dtype.itemsize
 
+    def host_view(self):
+        """numpy view of a buffer that lives in host memory after all (a CPU torch tensor as `owner`: the gloo tests)."""
+        if getattr(self.owner, "is_cuda", True):
+            raise TypeError("DeviceArray.host_view: the buffer is device memory")
+        return self.owner.numpy().reshape(-1)[:self.size].view(self.dtype).reshape(self.shape)
+
     def reshape(self, shape):
         shape = tuple(shape) if isinstance(shape, (tuple, list)) else (shape,)
         if -1 in shape:
@@ -299,7 +305,8 @@ class Context:
                 flag = 1
             else:
                 from . import hostmath
-                tangents = hostmath.uv_tangents(pos, uv, idx)
+                hv = lambda a: a.host_view() if isinstance(a, DeviceArray) else a
+                tangents = hostmath.uv_tangents(hv(pos), hv(uv), hv(idx))
         tg = None if tangents is None else f32(tangents, (-1, 6))
         d = MeshDesc(ptr(pos), ptr(nrm), ptr(uv), ptr(idx), ptr(tg), pos.shape[0], idx.shape[0], bsdf, flag)
         return self._check(self.fn["add_mesh"](self.h, C.byref(d)))
